@@ -1,0 +1,101 @@
+/* nkbs.h — C ABI of the B200-native nerfacto / semantic-NeRF-W ray-batch path.
+ *
+ * Plain C: raw DEVICE pointers (unless marked HOST), sizes and scalars.  The caller (PyTorch) owns
+ * every buffer; the library never allocates, frees or retains device memory, and never synchronises:
+ * all work is enqueued on `stream` (a cudaStream_t passed as void*).  Every entry point returns 0 on
+ * success and a negative code on error; nkbs_last_error() then returns a per-thread message.
+ * Tensors are contiguous row-major fp32 unless stated; N = R*S samples, ray-major (n = r*S + s).
+ *
+ * Each entry replaces an operator of the third-party `nerfstudio` package (0.3.x, torch path) that
+ * the reference reaches at the cited call sites (relative to the reference tree).  The reference has
+ * no FFI of its own; INTEGRATION.md shows the ctypes binding a maintainer adds on the reference side.
+ */
+#ifndef NKBS_H
+#define NKBS_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+int nkbs_version(void);
+const char* nkbs_last_error(void);
+
+/* K1 — position front end + HashEncoding forward.
+ * replaces: SceneContraction + HashEncoding.pytorch_fwd inside NerfactoField.get_density /
+ *           HashMLPDensityField.get_density  (nerfacto.py:275-311,397-398; semantic_nerfw.py:102-126,187-188)
+ * mode 0: x = normalised positions in [0,1]            (HashEncoding.forward itself)
+ * mode 1: x = raw positions [N,3] -> contraction/aabb -> (x+2)/4 -> selector
+ * mode 2: positions = origins[r] + directions[r]*(starts+ends)/2 from per-ray data, then as mode 1
+ * aabb, scalings: HOST pointers ([6] and [L]).  xn/selector/indices may be NULL.
+ * indices: int64 [N,L,8] table rows in the torch path's corner order (parity checks). */
+int nkbs_encode_fwd(int32_t mode, const float* x, const float* origins, const float* directions,
+                    const float* starts, const float* ends, int64_t R, int32_t S, int32_t contraction,
+                    const float* aabb, const float* table, const float* scalings, int32_t L, int32_t log2_T,
+                    int32_t F, float* xn, float* selector, float* features, int64_t* indices, void* stream);
+
+/* K2 — HashEncoding backward: scatters dfeat [N,2L] into dtable [L*T,2] (accumulates).
+ * replaces: autograd of hash_table[hashed_k] gathers (same call sites as K1).
+ * dedup_levels: levels [0,dedup_levels) merge duplicate rows inside a warp before the vector
+ * reduction; <0 = all levels. */
+int nkbs_encode_bwd(const float* xn, const float* dfeat, int64_t N, const float* scalings, int32_t L,
+                    int32_t log2_T, int32_t F, int32_t dedup_levels, float* dtable, void* stream);
+
+/* K3 (fp32) — fused MLP of 1..3 nn.Linear layers (torch [out,in] weights), widths <= 64.
+ * replaces: field_components.mlp.MLP + field-head activations (nerfacto.py:275-311,398;
+ *           semantic_nerfw.py:102-126,188).
+ * dims: HOST [nl+1]; W,b,dW,db: HOST arrays of nl DEVICE pointers.  relu_mask bit l = ReLU after layer l.
+ * out_act: 0 none, 1 sigmoid, 2 density (ch0 = exp(raw)*selector, trunc_exp backward), 3 transient
+ * heads (ch0 softplus, ch1-3 sigmoid, ch4 softplus).  selector [N] may be NULL.
+ * bwd recomputes the forward from x; dx may be NULL; dW/db are accumulated into. */
+int nkbs_mlp_fwd(const float* x, int64_t N, int32_t nl, const int32_t* dims, const float* const* W,
+                 const float* const* b, int32_t relu_mask, int32_t out_act, const float* selector, float* y,
+                 void* stream);
+int nkbs_mlp_bwd(const float* x, const float* dy, int64_t N, int32_t nl, const int32_t* dims,
+                 const float* const* W, const float* const* b, int32_t relu_mask, int32_t out_act,
+                 const float* selector, float* dx, float* const* dW, float* const* db, void* stream);
+
+/* K4 — head-MLP input assembly  h = [SH16((d+1)/2) | geo | embedding row]  and its backward.
+ * replaces: SHEncoding + Embedding + torch.cat in NerfactoField.get_outputs (nerfacto.py:398;
+ *           semantic_nerfw.py:188).  cam NULL -> emb_const [emb_dim] is used (eval). */
+int nkbs_assemble_fwd(int64_t N, int32_t S, int32_t sh_dim, int32_t geo_dim, int32_t emb_dim,
+                      const float* directions, int32_t dir_per_ray, const float* geo, const int64_t* cam,
+                      int32_t cam_per_ray, const float* emb, const float* emb_const, int64_t num_images,
+                      float* h, void* stream);
+int nkbs_assemble_bwd(int64_t N, int32_t S, int32_t sh_dim, int32_t geo_dim, int32_t emb_dim,
+                      const float* dh, float* dgeo, const int64_t* cam, int32_t cam_per_ray, float* demb,
+                      void* stream);
+
+/* K5 — samplers.  replaces: UniformLinDispPiecewiseSampler and PDFSampler inside
+ * ProposalNetworkSampler (nerfacto.py:325-332,397; semantic_nerfw.py:132-137,187).
+ * lin = torch.linspace(0,1,S+1); u_base = torch.linspace(0,1-1/nb,nb) (device copies of the host
+ * tables).  t_rand/rand NULL = eval (no jitter / centred).  anneal_dev: optional device scalar that
+ * overrides `anneal` (lets a captured CUDA graph see a new value every replay).  out_inds (int64 [R,nb]) may be NULL. */
+int nkbs_initial_sampler(int64_t R, int32_t S, const float* lin, const float* t_rand, int32_t rand_per_bin,
+                         const float* nears, const float* fars, float* sbins, float* ebins, void* stream);
+int nkbs_pdf_sample(int64_t R, int32_t S, int32_t num_bins, const float* weights, float anneal,
+                    const float* anneal_dev,
+                    float histogram_padding, float eps, const float* sbins, const float* u_base,
+                    const float* rand, int32_t rand_per_bin, const float* nears, const float* fars,
+                    float* out_sbins, float* out_ebins, int64_t* out_inds, void* stream);
+
+/* K6/K7 — ray-major compositing.  replaces: RaySamples.get_weights + RGB/Accumulation/Depth/
+ * Semantic/Uncertainty renderers (nerfacto.py:399-449; semantic_nerfw.py:190-229).
+ * Exactly one of density / weights_in.  Every output may be NULL.  bg_mode 0 last_sample, 1 black,
+ * 2 white.  depth_exp = clip(depth_exp_raw, steps.min(), steps.max()) over the whole batch;
+ * depth_mask = 1 where the clip is the identity; minmax_ws = int32[2] workspace. */
+int nkbs_composite_fwd(int64_t R, int32_t S, const float* density, const float* weights_in,
+                       const float* starts, const float* ends, const float* rgb, const float* sem, int32_t C,
+                       int32_t bg_mode, int32_t eval_mode, float* weights, float* rgb_out, float* acc_out,
+                       float* depth_exp_raw, float* depth_exp, float* depth_mask, float* depth_med,
+                       float* sem_out, int32_t* minmax_ws, void* stream);
+int nkbs_composite_bwd(int64_t R, int32_t S, const float* density, const float* weights, const float* starts,
+                       const float* ends, const float* rgb, const float* sem, int32_t C, int32_t bg_mode,
+                       int32_t sem_weight_grad, const float* acc, const float* depth_raw,
+                       const float* g_weights, const float* g_rgb, const float* g_acc, const float* g_depth,
+                       const float* g_sem, float* d_density, float* d_weights, float* d_rgb, float* d_sem,
+                       void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

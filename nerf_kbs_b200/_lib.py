@@ -1,0 +1,90 @@
+"""ctypes binding of libnkbs.so (include/nkbs.h).  There is no CPU or eager fallback: if the shared
+library is missing or an entry point fails, the caller gets an exception."""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import torch
+
+_HERE = Path(__file__).resolve().parent
+_LIB_PATH = _HERE / "libnkbs.so"
+
+_p = C.c_void_p
+_i32 = C.c_int32
+_i64 = C.c_int64
+_f = C.c_float
+
+# name -> argtypes, in the order of include/nkbs.h
+SIGNATURES = {
+    "nkbs_encode_fwd": [_i32, _p, _p, _p, _p, _p, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p],
+    "nkbs_encode_bwd": [_p, _p, _i64, _p, _i32, _i32, _i32, _i32, _p, _p],
+    "nkbs_mlp_fwd": [_p, _i64, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p],
+    "nkbs_mlp_bwd": [_p, _p, _i64, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _p],
+    "nkbs_assemble_fwd": [_i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32, _p, _p, _i64, _p, _p],
+    "nkbs_assemble_bwd": [_i64, _i32, _i32, _i32, _i32, _p, _p, _p, _i32, _p, _p],
+    "nkbs_initial_sampler": [_i64, _i32, _p, _p, _i32, _p, _p, _p, _p, _p],
+    "nkbs_pdf_sample": [_i64, _i32, _i32, _p, _f, _p, _f, _f, _p, _p, _p, _i32, _p, _p, _p, _p, _p, _p],
+    "nkbs_composite_fwd": [_i64, _i32, _p, _p, _p, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
+    "nkbs_composite_bwd": [_i64, _i32, _p, _p, _p, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
+}
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """Load libnkbs.so (built in-tree by nerf_kbs_b200.build).  Raises if it is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not _LIB_PATH.exists():
+        raise RuntimeError(
+            f"{_LIB_PATH} is missing: build it with `python -m nerf_kbs_b200.build` "
+            "(there is no CPU fallback for the nkbs kernels)")
+    lib = C.CDLL(str(_LIB_PATH))
+    lib.nkbs_version.restype = C.c_int
+    lib.nkbs_last_error.restype = C.c_char_p
+    for name, args in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.argtypes = args
+        fn.restype = C.c_int
+    _lib = lib
+    return lib
+
+
+def ptr(t):
+    """Device pointer of a contiguous tensor (None -> NULL)."""
+    if t is None:
+        return None
+    assert t.is_contiguous(), "nkbs kernels take contiguous tensors"
+    return t.data_ptr()
+
+
+def stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def call(name: str, *args) -> None:
+    lib = load()
+    rc = getattr(lib, name)(*args)
+    if rc != 0:
+        raise RuntimeError(f"{name} failed ({rc}): {lib.nkbs_last_error().decode()}")
+
+
+def require_cuda(*tensors) -> None:
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("nkbs operators run on CUDA tensors only (no CPU fallback)")
+
+
+def host_floats(vals):
+    arr = (C.c_float * len(vals))(*[float(v) for v in vals])
+    return arr
+
+
+def host_i32(vals):
+    return (C.c_int32 * len(vals))(*[int(v) for v in vals])
+
+
+def host_ptrs(tensors):
+    return (C.c_void_p * len(tensors))(*[ptr(t) for t in tensors])

@@ -1,0 +1,374 @@
+// K6/K7: ray-major volume compositing, forward and backward, one warp per ray.
+// Replaces RaySamples.get_weights and the RGB / Accumulation / Depth(median, expected) / Semantic /
+// Uncertainty renderers reached from ref:nerfacto.py:399-449 and ref:semantic_nerfw.py:190-229
+// (SURVEY a11, a13-a18, A.8).
+#include <float.h>
+#include "common.cuh"
+
+namespace {
+
+constexpr int kWarpsPerCta = 8;
+constexpr int kThreads = kWarpsPerCta * 32;
+constexpr int kMaxS = 512;   // samples per ray held in a warp's shared-memory strip
+
+struct CompArgs {
+  int64_t R;
+  int S;
+  // weights source: density (compute alpha/transmittance) or precomputed weights
+  const float* density;   // [R,S] or null
+  const float* weights_in;// [R,S] or null
+  const float* starts;    // [R,S] euclidean bin starts (needed for density and depth)
+  const float* ends;      // [R,S]
+  const float* rgb;       // [R,S,3] or null
+  const float* sem;       // [R,S,C] or null
+  int C;
+  int bg_mode;            // 0 last_sample, 1 black, 2 white
+  int eval_mode;          // nan_to_num rgb in, clamp out
+  // outputs (nullable)
+  float* weights;         // [R,S]
+  float* rgb_out;         // [R,3]
+  float* acc_out;         // [R]
+  float* depth_exp;       // [R] unclipped expected depth
+  float* depth_med;       // [R]
+  float* sem_out;         // [R,C]
+  int* minmax;            // [2] ordered-int keys of min/max step (for the expected-depth clip)
+};
+
+__device__ __forceinline__ int float_key(float f) {
+  int i = __float_as_int(f);
+  return i >= 0 ? i : i ^ 0x7fffffff;
+}
+__device__ __forceinline__ float key_float(int k) { return __int_as_float(k >= 0 ? k : k ^ 0x7fffffff); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_incl_scan(float v, int lane) {
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    float n = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane >= o) v += n;
+  }
+  return v;
+}
+__device__ __forceinline__ float nan_to_num(float w) {
+  if (w != w) return 0.f;
+  if (w > FLT_MAX) return FLT_MAX;
+  if (w < -FLT_MAX) return -FLT_MAX;
+  return w;
+}
+
+__global__ void __launch_bounds__(kThreads) composite_fwd_kernel(const CompArgs a) {
+  extern __shared__ float s_w[];  // [kWarpsPerCta][S]
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  float* sw = s_w + wid * a.S;
+  const int S = a.S;
+  float lmin = FLT_MAX, lmax = -FLT_MAX;
+  for (int64_t r = blockIdx.x * (int64_t)kWarpsPerCta + wid; r < a.R; r += (int64_t)gridDim.x * kWarpsPerCta) {
+    const int64_t base = r * S;
+    float carry = 0.f;  // exclusive prefix of delta*sigma entering this 32-sample chunk
+    float acc = 0.f, dsum = 0.f;
+    for (int s0 = 0; s0 < S; s0 += 32) {
+      int s = s0 + lane;
+      bool live = s < S;
+      float st = 0.f, en = 0.f, w = 0.f;
+      if (live && a.starts) {
+        st = a.starts[base + s];
+        en = a.ends[base + s];
+      }
+      if (a.density) {
+        float x = live ? (en - st) * a.density[base + s] : 0.f;
+        float incl = warp_incl_scan(x, lane);
+        float excl = carry + (incl - x);
+        // alphas * transmittance, nan_to_num as in get_weights
+        w = live ? nan_to_num((1.f - expf(-x)) * expf(-excl)) : 0.f;
+        carry += __shfl_sync(0xffffffffu, incl, 31);
+      } else if (live) {
+        w = a.weights_in[base + s];
+      }
+      if (live) {
+        sw[s] = w;
+        if (a.weights) a.weights[base + s] = w;
+        float step = (st + en) / 2.f;
+        acc += w;
+        dsum += w * step;
+        lmin = fminf(lmin, step);
+        lmax = fmaxf(lmax, step);
+      }
+    }
+    acc = warp_sum(acc);
+    dsum = warp_sum(dsum);
+    __syncwarp();
+    if (a.acc_out && lane == 0) a.acc_out[r] = acc;
+    if (a.depth_exp && lane == 0) a.depth_exp[r] = dsum / (acc + 1e-10f);
+    if (a.depth_med) {
+      // inclusive cumsum in sample order (torch.cumsum on the CPU), first index with cum >= 0.5
+      if (lane == 0) {
+        float cum = 0.f;
+        int idx = S;
+        for (int s = 0; s < S; ++s) {
+          cum += sw[s];
+          if (cum >= 0.5f) {
+            idx = s;
+            break;
+          }
+        }
+        if (idx > S - 1) idx = S - 1;
+        a.depth_med[r] = (a.starts[base + idx] + a.ends[base + idx]) / 2.f;
+      }
+    }
+    if (a.rgb_out) {
+      // lanes 0..2 = colour channel accumulators would idle 29 lanes; instead stride the flat [S*3] strip
+      float c0 = 0.f, c1 = 0.f, c2 = 0.f;
+      const float* rgb = a.rgb + base * 3;
+      for (int s = lane; s < S; s += 32) {
+        float w = sw[s];
+        float r0 = rgb[3 * s], g0 = rgb[3 * s + 1], b0 = rgb[3 * s + 2];
+        if (a.eval_mode) {
+          r0 = nan_to_num(r0);
+          g0 = nan_to_num(g0);
+          b0 = nan_to_num(b0);
+        }
+        c0 += w * r0;
+        c1 += w * g0;
+        c2 += w * b0;
+      }
+      c0 = warp_sum(c0);
+      c1 = warp_sum(c1);
+      c2 = warp_sum(c2);
+      if (lane < 3) {
+        float comp = lane == 0 ? c0 : (lane == 1 ? c1 : c2);
+        float bg = 0.f;
+        if (a.bg_mode == 0) {
+          bg = rgb[3 * (S - 1) + lane];
+          if (a.eval_mode) bg = nan_to_num(bg);
+        } else if (a.bg_mode == 2) {
+          bg = 1.f;
+        }
+        comp = comp + bg * (1.0f - acc);
+        if (a.eval_mode) comp = fminf(fmaxf(comp, 0.f), 1.f);
+        a.rgb_out[r * 3 + lane] = comp;
+      }
+    }
+    if (a.sem_out) {
+      // lanes over classes: each sample's C logits are one contiguous read
+      const float* sem = a.sem + base * a.C;
+      for (int c0 = 0; c0 < a.C; c0 += 32) {
+        int c = c0 + lane;
+        float v = 0.f;
+        if (c < a.C)
+          for (int s = 0; s < S; ++s) v += sw[s] * sem[(int64_t)s * a.C + c];
+        if (c < a.C) a.sem_out[r * a.C + c] = v;
+      }
+    }
+    __syncwarp();
+  }
+  if (a.minmax) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      lmin = fminf(lmin, __shfl_xor_sync(0xffffffffu, lmin, o));
+      lmax = fmaxf(lmax, __shfl_xor_sync(0xffffffffu, lmax, o));
+    }
+    if (lane == 0 && lmin <= lmax) {
+      atomicMin(a.minmax, float_key(lmin));
+      atomicMax(a.minmax + 1, float_key(lmax));
+    }
+  }
+}
+
+__global__ void minmax_init_kernel(int* mm) {
+  mm[0] = float_key(FLT_MAX);
+  mm[1] = float_key(-FLT_MAX);
+}
+
+// depth = clip(raw, steps.min(), steps.max()); mask = 1 where the clip passed the value through
+__global__ void clip_depth_kernel(const float* raw, const int* mm, int64_t R, float* out, float* mask) {
+  float lo = key_float(mm[0]), hi = key_float(mm[1]);
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < R; r += (int64_t)gridDim.x * blockDim.x) {
+    float v = raw[r];
+    out[r] = fminf(fmaxf(v, lo), hi);
+    if (mask) mask[r] = (v >= lo && v <= hi) ? 1.f : 0.f;
+  }
+}
+
+struct CompBwdArgs {
+  int64_t R;
+  int S;
+  const float* density;    // [R,S] or null (then d_weights is produced instead of d_density)
+  const float* weights;    // [R,S] saved forward weights
+  const float* starts;
+  const float* ends;
+  const float* rgb;        // [R,S,3] or null
+  const float* sem;        // [R,S,C] or null
+  int C;
+  int bg_mode;
+  int sem_weight_grad;     // pass_semantic_gradients
+  const float* acc;        // [R] saved accumulation
+  const float* depth_raw;  // [R] saved unclipped expected depth (needed when g_depth given)
+  // upstream gradients (nullable)
+  const float* g_weights;  // [R,S]
+  const float* g_rgb;      // [R,3]
+  const float* g_acc;      // [R]
+  const float* g_depth;    // [R] gradient w.r.t. the unclipped expected depth
+  const float* g_sem;      // [R,C]
+  // outputs
+  float* d_density;        // [R,S]
+  float* d_weights;        // [R,S]
+  float* d_rgb;            // [R,S,3]
+  float* d_sem;            // [R,S,C]
+};
+
+__global__ void __launch_bounds__(kThreads) composite_bwd_kernel(const CompBwdArgs a) {
+  extern __shared__ float s_buf[];  // [kWarpsPerCta][2][S]
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int S = a.S;
+  float* sw = s_buf + wid * 2 * S;
+  float* sg = sw + S;
+  for (int64_t r = blockIdx.x * (int64_t)kWarpsPerCta + wid; r < a.R; r += (int64_t)gridDim.x * kWarpsPerCta) {
+    const int64_t base = r * S;
+    const float acc = a.acc ? a.acc[r] : 0.f;
+    float gr[3] = {0.f, 0.f, 0.f}, bg[3] = {0.f, 0.f, 0.f};
+    if (a.g_rgb) {
+      gr[0] = a.g_rgb[r * 3];
+      gr[1] = a.g_rgb[r * 3 + 1];
+      gr[2] = a.g_rgb[r * 3 + 2];
+      if (a.bg_mode == 0) {
+        bg[0] = a.rgb[(base + S - 1) * 3];
+        bg[1] = a.rgb[(base + S - 1) * 3 + 1];
+        bg[2] = a.rgb[(base + S - 1) * 3 + 2];
+      } else if (a.bg_mode == 2) {
+        bg[0] = bg[1] = bg[2] = 1.f;
+      }
+    }
+    // expected depth = dsum / (acc + eps):  d/d dsum = g/(acc+eps),  d/d acc = -g * depth / (acc+eps)
+    float g_dsum = 0.f, g_acc = a.g_acc ? a.g_acc[r] : 0.f;
+    if (a.g_depth) {
+      float g = a.g_depth[r], den = acc + 1e-10f;
+      g_dsum = g / den;
+      g_acc += -g * a.depth_raw[r] / den;
+    }
+    // pass A: gradient w.r.t. each weight
+    float Q = 0.f;
+    for (int s = lane; s < S; s += 32) {
+      float w = a.weights[base + s];
+      float g = g_acc + (a.g_weights ? a.g_weights[base + s] : 0.f);
+      if (a.g_rgb) {
+        const float* c = a.rgb + (base + s) * 3;
+        g += gr[0] * (c[0] - bg[0]) + gr[1] * (c[1] - bg[1]) + gr[2] * (c[2] - bg[2]);
+      }
+      if (a.g_depth) g += g_dsum * ((a.starts[base + s] + a.ends[base + s]) / 2.f);
+      if (a.g_sem && a.sem_weight_grad) {
+        const float* q = a.sem + (base + s) * a.C;
+        const float* gq = a.g_sem + r * a.C;
+        float d = 0.f;
+        for (int c = 0; c < a.C; ++c) d += gq[c] * q[c];
+        g += d;
+      }
+      sw[s] = w;
+      sg[s] = g;
+      Q += g * w;
+      if (a.d_weights) a.d_weights[base + s] = g;
+      if (a.d_rgb) {
+        float* o = a.d_rgb + (base + s) * 3;
+        float extra = (a.bg_mode == 0 && s == S - 1) ? (1.f - acc) : 0.f;
+        o[0] = gr[0] * (w + extra);
+        o[1] = gr[1] * (w + extra);
+        o[2] = gr[2] * (w + extra);
+      }
+    }
+    Q = warp_sum(Q);
+    __syncwarp();
+    if (a.d_sem) {
+      float* o = a.d_sem + base * a.C;
+      for (int c0 = 0; c0 < a.C; c0 += 32) {
+        int c = c0 + lane;
+        if (c < a.C) {
+          float g = a.g_sem ? a.g_sem[r * a.C + c] : 0.f;
+          for (int s = 0; s < S; ++s) o[(int64_t)s * a.C + c] = sw[s] * g;
+        }
+      }
+    }
+    if (a.d_density) {
+      // w_i = (1-exp(-x_i)) exp(-sum_{j<i} x_j):  dL/dx_i = g_i exp(-incl_i) - sum_{j>i} g_j w_j
+      float carry_x = 0.f, carry_q = 0.f;
+      for (int s0 = 0; s0 < S; s0 += 32) {
+        int s = s0 + lane;
+        bool live = s < S;
+        float delta = live ? a.ends[base + s] - a.starts[base + s] : 0.f;
+        float x = live ? delta * a.density[base + s] : 0.f;
+        float g = live ? sg[s] : 0.f;
+        float q = live ? g * sw[s] : 0.f;
+        float ix = warp_incl_scan(x, lane);
+        float iq = warp_incl_scan(q, lane);
+        float dx = g * expf(-(carry_x + ix)) - (Q - (carry_q + iq));
+        if (live) a.d_density[base + s] = delta * dx;
+        carry_x += __shfl_sync(0xffffffffu, ix, 31);
+        carry_q += __shfl_sync(0xffffffffu, iq, 31);
+      }
+    }
+    __syncwarp();
+  }
+}
+
+int comp_grid(int64_t R) {
+  int64_t blocks = (R + kWarpsPerCta - 1) / kWarpsPerCta;
+  int64_t cap = (int64_t)nkbs_num_sms() * 8;
+  if (blocks < 1) blocks = 1;
+  return (int)(blocks < cap ? blocks : cap);
+}
+
+}  // namespace
+
+extern "C" int nkbs_composite_fwd(int64_t R, int32_t S, const float* density, const float* weights_in,
+                                  const float* starts, const float* ends, const float* rgb, const float* sem,
+                                  int32_t C, int32_t bg_mode, int32_t eval_mode, float* weights, float* rgb_out,
+                                  float* acc_out, float* depth_exp_raw, float* depth_exp, float* depth_mask,
+                                  float* depth_med, float* sem_out, int32_t* minmax_ws, void* stream) {
+  NKBS_CHECK_ARG(R >= 0 && S >= 1 && S <= kMaxS, "nkbs_composite_fwd: S=%d outside 1..%d", S, kMaxS);
+  if (R == 0) return 0;
+  NKBS_CHECK_ARG((density != nullptr) != (weights_in != nullptr), "nkbs_composite_fwd: give exactly one of density / weights");
+  NKBS_CHECK_ARG(!density || (starts && ends), "nkbs_composite_fwd: density needs starts/ends");
+  NKBS_CHECK_ARG(!(depth_exp_raw || depth_med) || (starts && ends), "nkbs_composite_fwd: depth needs starts/ends");
+  NKBS_CHECK_ARG(!rgb_out || rgb, "nkbs_composite_fwd: rgb_out without rgb");
+  NKBS_CHECK_ARG(!sem_out || (sem && C >= 1), "nkbs_composite_fwd: sem_out without sem");
+  NKBS_CHECK_ARG(!depth_exp || (depth_exp_raw && minmax_ws), "nkbs_composite_fwd: clipped depth needs raw + workspace");
+  NKBS_CHECK_ARG(bg_mode >= 0 && bg_mode <= 2, "nkbs_composite_fwd: unknown background mode %d", bg_mode);
+  if (R == 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  CompArgs a{R, S, density, weights_in, starts, ends, rgb, sem, C, bg_mode, eval_mode,
+             weights, rgb_out, acc_out, depth_exp_raw, depth_med, sem_out, depth_exp ? minmax_ws : nullptr};
+  if (depth_exp) minmax_init_kernel<<<1, 1, 0, st>>>(minmax_ws);
+  size_t smem = (size_t)kWarpsPerCta * S * sizeof(float);
+  composite_fwd_kernel<<<comp_grid(R), kThreads, smem, st>>>(a);
+  NKBS_CHECK_LAUNCH("nkbs_composite_fwd");
+  if (depth_exp) {
+    clip_depth_kernel<<<(int)((R + 255) / 256), 256, 0, st>>>(depth_exp_raw, minmax_ws, R, depth_exp, depth_mask);
+    NKBS_CHECK_LAUNCH("nkbs_composite_fwd(clip)");
+  }
+  return 0;
+}
+
+extern "C" int nkbs_composite_bwd(int64_t R, int32_t S, const float* density, const float* weights,
+                                  const float* starts, const float* ends, const float* rgb, const float* sem,
+                                  int32_t C, int32_t bg_mode, int32_t sem_weight_grad, const float* acc,
+                                  const float* depth_raw, const float* g_weights, const float* g_rgb,
+                                  const float* g_acc, const float* g_depth, const float* g_sem, float* d_density,
+                                  float* d_weights, float* d_rgb, float* d_sem, void* stream) {
+  NKBS_CHECK_ARG(R >= 0 && S >= 1 && S <= kMaxS, "nkbs_composite_bwd: S=%d outside 1..%d", S, kMaxS);
+  if (R == 0) return 0;
+  NKBS_CHECK_ARG(weights, "nkbs_composite_bwd: null weights");
+  NKBS_CHECK_ARG(!d_density || (density && starts && ends), "nkbs_composite_bwd: d_density needs density/starts/ends");
+  NKBS_CHECK_ARG(!g_rgb || (rgb && acc), "nkbs_composite_bwd: g_rgb needs rgb and accumulation");
+  NKBS_CHECK_ARG(!g_depth || (depth_raw && acc && starts && ends), "nkbs_composite_bwd: g_depth needs depth_raw/acc/starts/ends");
+  NKBS_CHECK_ARG(!(g_sem && sem_weight_grad) || sem, "nkbs_composite_bwd: semantic weight gradient needs sem");
+  NKBS_CHECK_ARG(!d_rgb || acc || bg_mode != 0, "nkbs_composite_bwd: d_rgb with last_sample background needs accumulation");
+  if (R == 0) return 0;
+  CompBwdArgs a{R, S, density, weights, starts, ends, rgb, sem, C, bg_mode, sem_weight_grad, acc, depth_raw,
+                g_weights, g_rgb, g_acc, g_depth, g_sem, d_density, d_weights, d_rgb, d_sem};
+  size_t smem = (size_t)kWarpsPerCta * 2 * S * sizeof(float);
+  composite_bwd_kernel<<<comp_grid(R), kThreads, smem, (cudaStream_t)stream>>>(a);
+  NKBS_CHECK_LAUNCH("nkbs_composite_bwd");
+  return 0;
+}

@@ -1,0 +1,238 @@
+// K1/K2: position front end + multiresolution hash-grid encoding, forward and backward.
+// Replaces nerfstudio HashEncoding.pytorch_fwd and its autograd, reached from
+// ref:nerfacto.py:275-311 and ref:semantic_nerfw.py:102-126.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kEncThreads = 256;
+
+struct EncodeArgs {
+  int mode;  // 0: x normalised, 1: x raw positions, 2: frustum
+  const float* x;
+  const float* origins;
+  const float* directions;
+  const float* starts;
+  const float* ends;
+  int64_t N;
+  int S;
+  NormParams norm;
+  LevelParams lv;
+  const float2* table;
+  float* xn;
+  float* selector;
+  float* features;
+  int64_t* indices;
+};
+
+__device__ __forceinline__ float3 load_sample_position(const EncodeArgs& a, int64_t n, float& sel) {
+  float3 p;
+  if (a.mode == 2) {
+    int64_t r = n / a.S;
+    float3 o = make_float3(a.origins[3 * r], a.origins[3 * r + 1], a.origins[3 * r + 2]);
+    float3 d = make_float3(a.directions[3 * r], a.directions[3 * r + 1], a.directions[3 * r + 2]);
+    p = nkbs_frustum_position(o, d, a.starts[n], a.ends[n]);
+  } else {
+    p = make_float3(a.x[3 * n], a.x[3 * n + 1], a.x[3 * n + 2]);
+  }
+  if (a.mode == 0) {
+    sel = 1.f;
+    return p;
+  }
+  return nkbs_normalise(p, a.norm, sel);
+}
+
+// One thread per sample; the level loop keeps 8 independent 8-byte gathers in flight per level and
+// the compiler overlaps two levels (unroll 2).  Level scales live in shared memory.
+template <bool kWriteIdx>
+__global__ void __launch_bounds__(kEncThreads) encode_fwd_kernel(const EncodeArgs a) {
+  __shared__ float s_scale[NKBS_MAX_LEVELS];
+  if (threadIdx.x < NKBS_MAX_LEVELS) s_scale[threadIdx.x] = a.lv.scale[threadIdx.x];
+  __syncthreads();
+  const int L = a.lv.num_levels;
+  const uint32_t mask = a.lv.table_mask;
+  for (int64_t n = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; n < a.N; n += (int64_t)gridDim.x * blockDim.x) {
+    float sel;
+    float3 x = load_sample_position(a, n, sel);
+    if (a.xn) {
+      a.xn[3 * n] = x.x;
+      a.xn[3 * n + 1] = x.y;
+      a.xn[3 * n + 2] = x.z;
+    }
+    if (a.selector) a.selector[n] = sel;
+    float2* out = reinterpret_cast<float2*>(a.features + n * (2 * L));
+#pragma unroll 2
+    for (int l = 0; l < L; ++l) {
+      Cell cl = nkbs_cell(x, s_scale[l]);
+      uint32_t h[8];
+      nkbs_corner_hashes(cl, mask, h);
+      const float2* tl = a.table + ((size_t)l << a.lv.log2_T);
+      float2 v[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = __ldg(tl + h[k]);
+      float v0[8], v1[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        v0[k] = v[k].x;
+        v1[k] = v[k].y;
+      }
+      out[l] = make_float2(nkbs_trilerp(v0, cl.o[0], cl.o[1], cl.o[2]), nkbs_trilerp(v1, cl.o[0], cl.o[1], cl.o[2]));
+      if (kWriteIdx) {
+        int64_t* ip = a.indices + (n * L + l) * 8;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) ip[k] = (int64_t)h[k] + ((int64_t)l << a.lv.log2_T);
+      }
+    }
+  }
+}
+
+struct EncodeBwdArgs {
+  const float* xn;        // [N,3] normalised positions (selector already applied)
+  const float* dfeat;     // [N,2L]
+  int64_t N;
+  LevelParams lv;
+  float* dtable;          // [L*T,2], accumulated into
+  int dedup_levels;       // levels below this index use warp-level duplicate merging
+};
+
+// Scatter of one corner: lanes of the warp that hit the same table row first merge their
+// contributions through shuffles (match.any) so that one 8-byte vector reduction leaves the warp per
+// distinct row.  Adjacent lanes are adjacent samples of one ray, so coarse levels collapse to 1-4
+// reductions per warp instead of 32.
+__device__ __forceinline__ void scatter_corner_dedup(float* base, uint32_t idx, float gx, float gy, int lane) {
+  unsigned peers = __match_any_sync(0xffffffffu, idx);
+  int leader = __ffs(peers) - 1;
+  unsigned rem = peers & ~(1u << leader);
+  // every lane walks its own peer list; only the leader's sum is used
+  float sx = gx, sy = gy;
+  unsigned any_rem = __ballot_sync(0xffffffffu, rem != 0 && lane == leader);
+  if (any_rem) {
+    // iterate as long as some leader still has peers to fold in
+    unsigned mine = (lane == leader) ? rem : 0u;
+    while (__any_sync(0xffffffffu, mine != 0)) {
+      int src = mine ? (__ffs(mine) - 1) : lane;
+      float ox = __shfl_sync(0xffffffffu, gx, src);
+      float oy = __shfl_sync(0xffffffffu, gy, src);
+      if (mine) {
+        sx += ox;
+        sy += oy;
+        mine &= mine - 1;
+      }
+    }
+  }
+  if (lane == leader && (sx != 0.f || sy != 0.f)) nkbs_red_add_v2(base + 2 * (size_t)idx, sx, sy);
+}
+
+__global__ void __launch_bounds__(kEncThreads) encode_bwd_kernel(const EncodeBwdArgs a) {
+  __shared__ float s_scale[NKBS_MAX_LEVELS];
+  if (threadIdx.x < NKBS_MAX_LEVELS) s_scale[threadIdx.x] = a.lv.scale[threadIdx.x];
+  __syncthreads();
+  const int L = a.lv.num_levels;
+  const uint32_t mask = a.lv.table_mask;
+  const int lane = threadIdx.x & 31;
+  // grid-stride over whole warps so that every lane of a warp reaches the collectives
+  const int64_t n_round = (a.N + 31) / 32 * 32;
+  for (int64_t n = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; n < n_round; n += (int64_t)gridDim.x * blockDim.x) {
+    const bool live = n < a.N;
+    float3 x = make_float3(0.f, 0.f, 0.f);
+    if (live) x = make_float3(a.xn[3 * n], a.xn[3 * n + 1], a.xn[3 * n + 2]);
+    const float2* g = reinterpret_cast<const float2*>(a.dfeat + (live ? n : 0) * (2 * L));
+    for (int l = 0; l < L; ++l) {
+      Cell cl = nkbs_cell(x, s_scale[l]);
+      uint32_t h[8];
+      nkbs_corner_hashes(cl, mask, h);
+      float w[8];
+      nkbs_corner_weights(cl.o[0], cl.o[1], cl.o[2], w);
+      float2 gl = live ? __ldg(g + l) : make_float2(0.f, 0.f);
+      float* base = a.dtable + ((size_t)l << (a.lv.log2_T + 1));
+      if (l < a.dedup_levels) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) scatter_corner_dedup(base, h[k], w[k] * gl.x, w[k] * gl.y, lane);
+      } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          float gx = w[k] * gl.x, gy = w[k] * gl.y;
+          if (gx != 0.f || gy != 0.f) nkbs_red_add_v2(base + 2 * (size_t)h[k], gx, gy);
+        }
+      }
+    }
+  }
+}
+
+int fill_levels(LevelParams& lv, const float* scalings, int L, int log2_T) {
+  if (L < 1 || L > NKBS_MAX_LEVELS) return -1;
+  if (log2_T < 1 || log2_T > 30) return -1;
+  for (int i = 0; i < NKBS_MAX_LEVELS; ++i) lv.scale[i] = i < L ? scalings[i] : 0.f;
+  lv.num_levels = L;
+  lv.log2_T = (uint32_t)log2_T;
+  lv.table_mask = (1u << log2_T) - 1u;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int nkbs_encode_fwd(int mode, const float* x, const float* origins, const float* directions,
+                               const float* starts, const float* ends, int64_t R, int32_t S, int contraction,
+                               const float* aabb, const float* table, const float* scalings, int32_t L,
+                               int32_t log2_T, int32_t F, float* xn, float* selector, float* features,
+                               int64_t* indices, void* stream) {
+  NKBS_CHECK_ARG(mode >= 0 && mode <= 2, "nkbs_encode_fwd: mode must be 0, 1 or 2 (got %d)", mode);
+  NKBS_CHECK_ARG(F == 2, "nkbs_encode_fwd: features_per_level must be 2 (got %d)", F);
+  NKBS_CHECK_ARG(R >= 0 && S >= 1, "nkbs_encode_fwd: bad sizes R=%lld S=%d", (long long)R, S);
+  NKBS_CHECK_ARG(table && features && scalings, "nkbs_encode_fwd: null table/features/scalings");
+  if (mode == 2)
+    NKBS_CHECK_ARG(origins && directions && starts && ends, "nkbs_encode_fwd: frustum mode needs origins/directions/starts/ends");
+  else
+    NKBS_CHECK_ARG(x != nullptr || R == 0, "nkbs_encode_fwd: null positions");
+  EncodeArgs a;
+  a.mode = mode;
+  a.x = x;
+  a.origins = origins;
+  a.directions = directions;
+  a.starts = starts;
+  a.ends = ends;
+  a.N = R * (int64_t)S;
+  a.S = S;
+  a.norm.contraction = contraction;
+  for (int i = 0; i < 3; ++i) {
+    a.norm.aabb_min[i] = aabb ? aabb[i] : 0.f;
+    a.norm.aabb_len[i] = aabb ? aabb[3 + i] - aabb[i] : 1.f;
+  }
+  NKBS_CHECK_ARG(fill_levels(a.lv, scalings, L, log2_T) == 0, "nkbs_encode_fwd: unsupported grid L=%d log2_T=%d", L, log2_T);
+  a.table = reinterpret_cast<const float2*>(table);
+  a.xn = xn;
+  a.selector = selector;
+  a.features = features;
+  a.indices = indices;
+  if (a.N == 0) return 0;
+  int64_t blocks = (a.N + kEncThreads - 1) / kEncThreads;
+  int64_t cap = (int64_t)nkbs_num_sms() * 32;
+  int grid = (int)(blocks < cap ? blocks : cap);
+  if (indices)
+    encode_fwd_kernel<true><<<grid, kEncThreads, 0, (cudaStream_t)stream>>>(a);
+  else
+    encode_fwd_kernel<false><<<grid, kEncThreads, 0, (cudaStream_t)stream>>>(a);
+  NKBS_CHECK_LAUNCH("nkbs_encode_fwd");
+  return 0;
+}
+
+extern "C" int nkbs_encode_bwd(const float* xn, const float* dfeat, int64_t N, const float* scalings, int32_t L,
+                               int32_t log2_T, int32_t F, int32_t dedup_levels, float* dtable, void* stream) {
+  NKBS_CHECK_ARG(F == 2, "nkbs_encode_bwd: features_per_level must be 2 (got %d)", F);
+  NKBS_CHECK_ARG(N >= 0 && dtable && scalings, "nkbs_encode_bwd: bad arguments");
+  EncodeBwdArgs a;
+  a.xn = xn;
+  a.dfeat = dfeat;
+  a.N = N;
+  NKBS_CHECK_ARG(fill_levels(a.lv, scalings, L, log2_T) == 0, "nkbs_encode_bwd: unsupported grid L=%d log2_T=%d", L, log2_T);
+  a.dtable = dtable;
+  a.dedup_levels = dedup_levels < 0 ? L : dedup_levels;
+  if (N == 0) return 0;
+  NKBS_CHECK_ARG(xn && dfeat, "nkbs_encode_bwd: null xn/dfeat");
+  int64_t blocks = (N + kEncThreads - 1) / kEncThreads;
+  int64_t cap = (int64_t)nkbs_num_sms() * 32;
+  int grid = (int)(blocks < cap ? blocks : cap);
+  encode_bwd_kernel<<<grid, kEncThreads, 0, (cudaStream_t)stream>>>(a);
+  NKBS_CHECK_LAUNCH("nkbs_encode_bwd");
+  return 0;
+}

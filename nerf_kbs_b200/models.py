@@ -1,0 +1,251 @@
+"""The two ``get_outputs`` orchestrations of the reference, over the nkbs operators.
+
+``NerfactoModel.get_outputs``      follows ref:nerfacto.py:396-453       (modules: :265-357)
+``SemanticNerfWModel.get_outputs`` follows ref:semantic_nerfw.py:186-234 (modules: :92-154)
+
+Weights + every renderer of the final level run as ONE ray-major compositing launch (ops.composite)
+instead of get_weights + five renderer calls; results are the same tensors under the same keys."""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, Tuple
+
+import numpy as np
+import torch
+from torch import nn
+
+from . import ops
+from .fields import FieldHeadNames, HashMLPDensityField, NerfactoField, SceneContraction
+from .losses import distortion_loss, interlevel_loss
+from .rays import RayBundle
+from .renderers import NearFarCollider
+from .samplers import ProposalNetworkSampler
+
+
+@dataclass
+class ModelConfig:
+    """Constants of ref:nerfacto.py:148-221 and ref:semantic_nerfw.py:59-72."""
+    near_plane: float = 0.001
+    far_plane: float = 1000.0
+    background_color: str = "last_sample"
+    hidden_dim: int = 64
+    hidden_dim_color: int = 64
+    hidden_dim_transient: int = 64
+    num_levels: int = 16
+    max_res: int = 2048
+    log2_hashmap_size: int = 19
+    num_proposal_samples_per_ray: Tuple[int, ...] = (256, 96)
+    num_nerf_samples_per_ray: int = 48
+    proposal_update_every: int = 5
+    proposal_warmup: int = 5000
+    num_proposal_iterations: int = 2
+    proposal_net_args_list: Tuple[Dict, ...] = (
+        {"hidden_dim": 16, "log2_hashmap_size": 17, "num_levels": 5, "max_res": 128, "use_linear": False},
+        {"hidden_dim": 16, "log2_hashmap_size": 17, "num_levels": 5, "max_res": 256, "use_linear": False},
+    )
+    interlevel_loss_mult: float = 1.0
+    distortion_loss_mult: float = 0.002
+    use_proposal_weight_anneal: bool = True
+    use_average_appearance_embedding: bool = True
+    proposal_weights_anneal_slope: float = 10.0
+    proposal_weights_anneal_max_num_iters: int = 1000
+    use_single_jitter: bool = True
+    pass_semantic_gradients: bool = False
+    use_semantic: bool = False
+    num_semantic_classes: int = 19
+    use_transient_embedding: bool = False
+    semantic_loss_weight: float = 0.05
+    num_images: int = 115
+
+
+def anneal_value(step: int, max_iters: int, slope: float) -> float:
+    """ref:nerfacto.py:373-379 (mip-NeRF-360 eq. 18 bias schedule)."""
+    train_frac = np.clip(step / max_iters, 0, 1)
+    return float((slope * train_frac) / ((slope - 1) * train_frac + 1))
+
+
+class _ModelBase(nn.Module):
+    config: ModelConfig
+
+    def set_step(self, step: int) -> None:
+        """BEFORE_TRAIN_ITERATION callback (ref:nerfacto.py:373-386; semantic_nerfw.py:170-183)."""
+        c = self.config
+        if c.use_proposal_weight_anneal:
+            self.proposal_sampler.set_anneal(
+                anneal_value(step, c.proposal_weights_anneal_max_num_iters, c.proposal_weights_anneal_slope))
+
+    def get_param_groups(self):
+        return {"proposal_networks": list(self.proposal_networks.parameters()),
+                "fields": list(self.field.parameters())}
+
+    def forward(self, ray_bundle: RayBundle, jitter=None):
+        return self.get_outputs(self.collider(ray_bundle), jitter=jitter)
+
+    def _prop_depths(self, outputs, weights_list, ray_samples_list):
+        for i in range(self.config.num_proposal_iterations):
+            rs = ray_samples_list[i]
+            outputs[f"prop_depth_{i}"] = ops.composite(
+                weights=weights_list[i].detach(), starts=rs.frustums.starts, ends=rs.frustums.ends,
+                want=("depth_med",))["depth"]
+
+
+class NerfactoModel(_ModelBase):
+    """ref:nerfacto.py:226."""
+
+    def __init__(self, config: ModelConfig, aabb=None):
+        super().__init__()
+        self.config = c = config
+        aabb = torch.tensor([[-1.0, -1.0, -1.0], [1.0, 1.0, 1.0]]) if aabb is None else aabb
+        sc = SceneContraction(order=float("inf"))
+        self.field = NerfactoField(
+            aabb, hidden_dim=c.hidden_dim, num_levels=c.num_levels, max_res=c.max_res,
+            log2_hashmap_size=c.log2_hashmap_size, hidden_dim_color=c.hidden_dim_color,
+            hidden_dim_transient=c.hidden_dim_transient, spatial_distortion=sc, num_images=c.num_images,
+            use_average_appearance_embedding=c.use_average_appearance_embedding, use_semantics=c.use_semantic,
+            num_semantic_classes=c.num_semantic_classes, pass_semantic_gradients=c.pass_semantic_gradients)
+        self.proposal_networks = nn.ModuleList()
+        for i in range(c.num_proposal_iterations):
+            args = c.proposal_net_args_list[min(i, len(c.proposal_net_args_list) - 1)]
+            self.proposal_networks.append(HashMLPDensityField(aabb, spatial_distortion=sc, **args))
+        self.density_fns = [n.density_fn for n in self.proposal_networks]
+        sched = lambda step: np.clip(np.interp(step, [0, c.proposal_warmup], [0, c.proposal_update_every]),
+                                     1, c.proposal_update_every)
+        self.proposal_sampler = ProposalNetworkSampler(
+            num_nerf_samples_per_ray=c.num_nerf_samples_per_ray,
+            num_proposal_samples_per_ray=c.num_proposal_samples_per_ray,
+            num_proposal_network_iterations=c.num_proposal_iterations, single_jitter=c.use_single_jitter,
+            update_sched=sched)
+        self.collider = NearFarCollider(near_plane=c.near_plane, far_plane=c.far_plane)
+
+    def after_step(self, step: int) -> None:
+        """AFTER_TRAIN_ITERATION callback (ref:nerfacto.py:387-393)."""
+        self.proposal_sampler.step_cb(step)
+
+    def get_outputs(self, ray_bundle: RayBundle, jitter=None):
+        c = self.config
+        ray_samples, weights_list, ray_samples_list = self.proposal_sampler(
+            ray_bundle, density_fns=self.density_fns, jitter=jitter)
+        field_outputs = self.field(ray_samples)
+        sem = field_outputs.get(FieldHeadNames.SEMANTICS) if c.use_semantic else None
+        want = ("rgb", "acc", "depth_exp", "depth_med") + (("sem",) if sem is not None else ())
+        comp = ops.composite(density=field_outputs[FieldHeadNames.DENSITY], rgb=field_outputs[FieldHeadNames.RGB],
+                             sem=sem, starts=ray_samples.frustums.starts, ends=ray_samples.frustums.ends,
+                             background=c.background_color, eval_mode=not self.training,
+                             sem_weight_grad=c.pass_semantic_gradients, want=want)
+        weights = comp["weights"]
+        weights_list.append(weights)
+        ray_samples_list.append(ray_samples)
+        outputs = {"rgb": comp["rgb"], "accumulation": comp["accumulation"], "depth": comp["depth"],
+                   "expected_depth": comp["expected_depth"], "directions": ray_bundle.directions,
+                   "origins": ray_bundle.origins}
+        if sem is not None:
+            outputs["semantics"] = comp["semantics"]
+        if self.training:
+            outputs["weights_list"] = weights_list
+            outputs["ray_samples_list"] = ray_samples_list
+        self._prop_depths(outputs, weights_list, ray_samples_list)
+        if ray_bundle.metadata is not None and "directions_norm" in ray_bundle.metadata:
+            outputs["directions_norm"] = ray_bundle.metadata["directions_norm"]
+        return outputs
+
+    def get_loss_dict(self, outputs, batch):
+        """ref:nerfacto.py:465-515."""
+        c = self.config
+        loss = {"rgb_loss": nn.functional.mse_loss(batch["image"], outputs["rgb"])}
+        if self.training:
+            loss["interlevel_loss"] = c.interlevel_loss_mult * interlevel_loss(
+                outputs["weights_list"], outputs["ray_samples_list"])
+            loss["distortion_loss"] = c.distortion_loss_mult * distortion_loss(
+                outputs["weights_list"], outputs["ray_samples_list"])
+        if c.use_semantic:
+            loss["semantics_loss"] = c.semantic_loss_weight * nn.functional.cross_entropy(
+                outputs["semantics"], batch["semantics_label"], ignore_index=c.num_semantic_classes)
+        return loss
+
+
+class SemanticNerfWModel(_ModelBase):
+    """ref:semantic_nerfw.py:75.  The reference ctor rejects ``use_transient_embedding`` (:98-99) but
+    BASELINE config 3 asks for the transient heads, so the flag is accepted here and the (dead) transient
+    branch of get_outputs (:190-198, :217-221) is followed literally."""
+
+    def __init__(self, config: ModelConfig, aabb=None):
+        super().__init__()
+        self.config = c = config
+        aabb = torch.tensor([[-1.0, -1.0, -1.0], [1.0, 1.0, 1.0]]) if aabb is None else aabb
+        sc = SceneContraction(order=float("inf"))
+        self.field = NerfactoField(
+            aabb, num_levels=c.num_levels, max_res=c.max_res, log2_hashmap_size=c.log2_hashmap_size,
+            spatial_distortion=sc, num_images=c.num_images,
+            use_average_appearance_embedding=c.use_average_appearance_embedding,
+            use_transient_embedding=c.use_transient_embedding, use_semantics=True,
+            num_semantic_classes=c.num_semantic_classes, pass_semantic_gradients=c.pass_semantic_gradients)
+        self.proposal_networks = nn.ModuleList(
+            [HashMLPDensityField(aabb, spatial_distortion=sc) for _ in range(c.num_proposal_iterations)])
+        self.density_fns = [n.density_fn for n in self.proposal_networks]
+        self.collider = NearFarCollider(near_plane=c.near_plane, far_plane=c.far_plane)
+        self.proposal_sampler = ProposalNetworkSampler(
+            num_nerf_samples_per_ray=c.num_nerf_samples_per_ray,
+            num_proposal_samples_per_ray=c.num_proposal_samples_per_ray,
+            num_proposal_network_iterations=c.num_proposal_iterations, single_jitter=c.use_single_jitter)
+
+    def after_step(self, step: int) -> None:
+        pass  # no step_cb is registered by the reference (semantic_nerfw.py:162-184)
+
+    def get_outputs(self, ray_bundle: RayBundle, jitter=None):
+        c = self.config
+        ray_samples, weights_list, ray_samples_list = self.proposal_sampler(
+            ray_bundle, density_fns=self.density_fns, jitter=jitter)
+        fo = self.field(ray_samples)
+        st, en = ray_samples.frustums.starts, ray_samples.frustums.ends
+        kw = dict(starts=st, ends=en, background=c.background_color, eval_mode=not self.training)
+        transient = self.training and c.use_transient_embedding
+        if transient:
+            stat = ops.composite(density=fo[FieldHeadNames.DENSITY], sem=fo[FieldHeadNames.SEMANTICS],
+                                 sem_weight_grad=c.pass_semantic_gradients, want=("acc", "depth_med", "sem"), **kw)
+            density = fo[FieldHeadNames.DENSITY] + fo[FieldHeadNames.TRANSIENT_DENSITY]
+            both = ops.composite(density=density, rgb=fo[FieldHeadNames.RGB], want=("rgb",), **kw)
+            rgb_t = ops.composite(weights=both["weights"], rgb=fo[FieldHeadNames.TRANSIENT_RGB], want=("rgb",),
+                                  background=c.background_color, eval_mode=False)
+            rgb = both["rgb"] + rgb_t["rgb"]
+        else:
+            stat = ops.composite(density=fo[FieldHeadNames.DENSITY], rgb=fo[FieldHeadNames.RGB],
+                                 sem=fo[FieldHeadNames.SEMANTICS], sem_weight_grad=c.pass_semantic_gradients,
+                                 want=("rgb", "acc", "depth_med", "sem"), **kw)
+            rgb = stat["rgb"]
+        weights_static = stat["weights"]
+        weights_list.append(weights_static)
+        ray_samples_list.append(ray_samples)
+        outputs = {"rgb": rgb, "accumulation": stat["accumulation"], "depth": stat["depth"]}
+        outputs["weights_list"] = weights_list
+        outputs["ray_samples_list"] = ray_samples_list
+        self._prop_depths(outputs, weights_list, ray_samples_list)
+        if transient:
+            unc = ops.composite(density=fo[FieldHeadNames.TRANSIENT_DENSITY], sem=fo[FieldHeadNames.UNCERTAINTY],
+                                sem_weight_grad=True, want=("sem",), starts=st, ends=en)
+            outputs["uncertainty"] = unc["semantics"] + 0.03
+            outputs["density_transient"] = fo[FieldHeadNames.TRANSIENT_DENSITY]
+        outputs["semantics"] = stat["semantics"]
+        if ray_bundle.metadata is not None and "directions_norm" in ray_bundle.metadata:
+            outputs["directions_norm"] = ray_bundle.metadata["directions_norm"]
+        return outputs
+
+    def get_loss_dict(self, outputs, batch):
+        """ref:semantic_nerfw.py:249-279."""
+        c = self.config
+        image = batch["image"]
+        loss = {}
+        if self.training:
+            loss["interlevel_loss"] = c.interlevel_loss_mult * interlevel_loss(
+                outputs["weights_list"], outputs["ray_samples_list"])
+            loss["distortion_loss"] = c.distortion_loss_mult * distortion_loss(
+                outputs["weights_list"], outputs["ray_samples_list"])
+        if self.training and c.use_transient_embedding:
+            betas = outputs["uncertainty"]
+            loss["uncertainty_loss"] = 3 + torch.log(betas).mean()
+            loss["density_loss"] = 0.01 * outputs["density_transient"].mean()
+            loss["rgb_loss"] = (((image - outputs["rgb"]) ** 2).sum(-1) / (betas[..., 0] ** 2)).mean()
+        else:
+            loss["rgb_loss"] = nn.functional.mse_loss(image, outputs["rgb"])
+        loss["semantics_loss"] = c.semantic_loss_weight * nn.functional.cross_entropy(
+            outputs["semantics"], batch["semantics_label"])
+        return loss

@@ -1,0 +1,349 @@
+"""torch.autograd bindings of the nkbs C-ABI kernels (include/nkbs.h).
+
+Every function here launches hand-written sm_100a kernels on the current CUDA stream.  PyTorch only
+owns the buffers.  There is no CPU path: CPU tensors raise.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import call, host_floats, host_i32, host_ptrs, ptr, require_cuda, stream
+
+ACT_NONE, ACT_SIGMOID, ACT_DENSITY, ACT_TRANSIENT = 0, 1, 2, 3
+BG_MODES = {"last_sample": 0, "black": 1, "white": 2}
+
+
+def _c(t: Optional[torch.Tensor], dtype=torch.float32) -> Optional[torch.Tensor]:
+    if t is None:
+        return None
+    if t.dtype != dtype:
+        t = t.to(dtype)
+    return t.contiguous()
+
+
+# ----------------------------------------------------------------------------------------------
+# K1/K2 hash-grid encoding
+# ----------------------------------------------------------------------------------------------
+@dataclass(frozen=True)
+class GridSpec:
+    scalings: Tuple[float, ...]
+    log2_T: int
+    features_per_level: int = 2
+
+    @property
+    def L(self) -> int:
+        return len(self.scalings)
+
+    @property
+    def out_dim(self) -> int:
+        return self.L * self.features_per_level
+
+
+@dataclass(frozen=True)
+class NormSpec:
+    contraction: bool
+    aabb: Tuple[float, ...]  # 6 floats
+
+
+def encode_raw(mode: int, grid: GridSpec, norm: Optional[NormSpec], table, x=None, origins=None, directions=None,
+               starts=None, ends=None, want_indices=False):
+    """Launch K1.  Returns (features [N,2L], selector [N], xn [N,3], indices or None)."""
+    require_cuda(table, x, origins, starts)
+    if mode == 2:
+        R, S = starts.shape[0], starts.shape[1]
+        dev = starts.device
+    else:
+        R, S = x.shape[0], 1
+        dev = x.device
+    N = R * S
+    feats = torch.empty((N, grid.out_dim), device=dev, dtype=torch.float32)
+    sel = torch.empty((N,), device=dev, dtype=torch.float32)
+    xn = torch.empty((N, 3), device=dev, dtype=torch.float32)
+    idx = torch.empty((N, grid.L, 8), device=dev, dtype=torch.int64) if want_indices else None
+    aabb = host_floats(norm.aabb) if norm is not None else None
+    call("nkbs_encode_fwd", mode, ptr(x), ptr(origins), ptr(directions), ptr(starts), ptr(ends), R, S,
+         int(norm.contraction) if norm is not None else 0, aabb, ptr(table), host_floats(grid.scalings), grid.L,
+         grid.log2_T, grid.features_per_level, ptr(xn), ptr(sel), ptr(feats), ptr(idx), stream())
+    return feats, sel, xn, idx
+
+
+class _HashEncode(torch.autograd.Function):
+    """features = HashEncoding(normalise(positions)); gradient w.r.t. the table only (sample positions
+    are detached in the reference path: PDF bins are detached)."""
+
+    @staticmethod
+    def forward(ctx, table, mode, grid, norm, dedup_levels, x, origins, directions, starts, ends):
+        feats, sel, xn, _ = encode_raw(mode, grid, norm, table, x, origins, directions, starts, ends)
+        ctx.grid = grid
+        ctx.dedup = dedup_levels
+        ctx.table_shape = table.shape
+        ctx.save_for_backward(xn)
+        ctx.mark_non_differentiable(sel, xn)
+        return feats, sel, xn
+
+    @staticmethod
+    def backward(ctx, dfeat, _dsel, _dxn):
+        (xn,) = ctx.saved_tensors
+        g = ctx.grid
+        dtable = torch.zeros(ctx.table_shape, device=xn.device, dtype=torch.float32)
+        dfeat = _c(dfeat)
+        call("nkbs_encode_bwd", ptr(xn), ptr(dfeat), xn.shape[0], host_floats(g.scalings), g.L, g.log2_T,
+             g.features_per_level, ctx.dedup, ptr(dtable), stream())
+        return (dtable,) + (None,) * 9
+
+
+def hash_encode(table, grid: GridSpec, x_normalised):
+    """HashEncoding.forward on positions already in [0,1] (mode 0)."""
+    x = _c(x_normalised).reshape(-1, 3)
+    feats, _, _ = _HashEncode.apply(table, 0, grid, None, -1, x, None, None, None, None)
+    return feats
+
+
+def contract_encode(table, grid: GridSpec, norm: NormSpec, positions=None, origins=None, directions=None,
+                    starts=None, ends=None, dedup_levels=-1):
+    """Front end + encoding.  Either raw ``positions`` [N,3] or per-ray ``origins/directions`` [R,3] with
+    per-sample ``starts/ends`` [R,S].  Returns (features [N,2L], selector [N])."""
+    if positions is not None:
+        feats, sel, _ = _HashEncode.apply(table, 1, grid, norm, dedup_levels, _c(positions).reshape(-1, 3), None,
+                                          None, None, None)
+    else:
+        feats, sel, _ = _HashEncode.apply(table, 2, grid, norm, dedup_levels, None, _c(origins), _c(directions),
+                                          _c(starts), _c(ends))
+    return feats, sel
+
+
+# ----------------------------------------------------------------------------------------------
+# K3 fused MLP (fp32 CUDA-core path)
+# ----------------------------------------------------------------------------------------------
+class _Mlp(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, selector, relu_mask, out_act, *params):
+        nl = len(params) // 2
+        Ws = [_c(p) for p in params[0::2]]
+        bs = [_c(p) for p in params[1::2]]
+        x = _c(x)
+        require_cuda(x, *Ws)
+        dims = [Ws[0].shape[1]] + [w.shape[0] for w in Ws]
+        N = x.shape[0]
+        y = torch.empty((N, dims[-1]), device=x.device, dtype=torch.float32)
+        call("nkbs_mlp_fwd", ptr(x), N, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask, out_act,
+             ptr(selector), ptr(y), stream())
+        ctx.cfg = (nl, dims, relu_mask, out_act)
+        ctx.save_for_backward(x, selector, *Ws, *bs)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        nl, dims, relu_mask, out_act = ctx.cfg
+        saved = ctx.saved_tensors
+        x, selector = saved[0], saved[1]
+        Ws, bs = list(saved[2:2 + nl]), list(saved[2 + nl:2 + 2 * nl])
+        dy = _c(dy)
+        N = x.shape[0]
+        dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        dWs = [torch.zeros_like(w) for w in Ws]
+        dbs = [torch.zeros_like(b) for b in bs]
+        call("nkbs_mlp_bwd", ptr(x), ptr(dy), N, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask,
+             out_act, ptr(selector), ptr(dx), host_ptrs(dWs), host_ptrs(dbs), stream())
+        grads = []
+        for w, b in zip(dWs, dbs):
+            grads += [w, b]
+        return (dx, None, None, None, *grads)
+
+
+def mlp(x, weights: Sequence[torch.Tensor], biases: Sequence[torch.Tensor], relu_mask: int, out_act: int = ACT_NONE,
+        selector: Optional[torch.Tensor] = None):
+    """y = MLP(x) with up to three nn.Linear layers; x [N,K0] -> y [N,Kn]."""
+    params = []
+    for w, b in zip(weights, biases):
+        params += [w, b]
+    return _Mlp.apply(x, selector, relu_mask, out_act, *params)
+
+
+# ----------------------------------------------------------------------------------------------
+# K4 head-input assembly
+# ----------------------------------------------------------------------------------------------
+class _Assemble(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, geo, emb, emb_const, directions, cam, S, sh_dim, dir_per_ray, cam_per_ray):
+        geo = _c(geo)
+        N, geo_dim = geo.shape
+        emb_dim = emb.shape[1] if emb is not None else emb_const.shape[0]
+        h = torch.empty((N, sh_dim + geo_dim + emb_dim), device=geo.device, dtype=torch.float32)
+        use_cam = cam is not None and emb_const is None
+        call("nkbs_assemble_fwd", N, S, sh_dim, geo_dim, emb_dim, ptr(directions), int(dir_per_ray), ptr(geo),
+             ptr(cam) if use_cam else None, int(cam_per_ray), ptr(emb) if use_cam else None, ptr(emb_const),
+             emb.shape[0] if emb is not None else 0, ptr(h), stream())
+        ctx.cfg = (N, S, sh_dim, geo_dim, emb_dim, cam_per_ray, use_cam, emb.shape if emb is not None else None)
+        ctx.save_for_backward(cam if use_cam else None)
+        return h
+
+    @staticmethod
+    def backward(ctx, dh):
+        N, S, sh_dim, geo_dim, emb_dim, cam_per_ray, use_cam, emb_shape = ctx.cfg
+        (cam,) = ctx.saved_tensors
+        dh = _c(dh)
+        dgeo = torch.empty((N, geo_dim), device=dh.device, dtype=torch.float32) if ctx.needs_input_grad[0] else None
+        demb = None
+        if use_cam and ctx.needs_input_grad[1]:
+            demb = torch.zeros(emb_shape, device=dh.device, dtype=torch.float32)
+        call("nkbs_assemble_bwd", N, S, sh_dim, geo_dim, emb_dim, ptr(dh), ptr(dgeo), ptr(cam) if demb is not None else None,
+             int(cam_per_ray), ptr(demb), stream())
+        return dgeo, demb, None, None, None, None, None, None, None
+
+
+def assemble(geo, emb_table, emb_const, directions, cam, S: int, sh_dim: int, dir_per_ray: bool, cam_per_ray: bool):
+    """h = [SH16((d+1)/2) | geo | embedding[cam] or emb_const]; see nkbs_assemble_fwd."""
+    return _Assemble.apply(geo, emb_table, emb_const, _c(directions), _c(cam, torch.int64), S, sh_dim, dir_per_ray,
+                           cam_per_ray)
+
+
+# ----------------------------------------------------------------------------------------------
+# K5 samplers (no gradient: the reference detaches the bins)
+# ----------------------------------------------------------------------------------------------
+_LIN_CACHE = {}
+
+
+def _lin_table(kind: str, n: int, device) -> torch.Tensor:
+    """torch.linspace evaluated on the CPU (the oracle's rounding), cached per device."""
+    key = (kind, n, str(device))
+    t = _LIN_CACHE.get(key)
+    if t is None:
+        if kind == "bins":  # linspace(0, 1, S+1)
+            t = torch.linspace(0.0, 1.0, n + 1)
+        else:  # "u": linspace(0, 1 - 1/nb, nb)
+            t = torch.linspace(0.0, 1.0 - (1.0 / n), steps=n)
+        t = t.to(device)
+        _LIN_CACHE[key] = t
+    return t
+
+
+@torch.no_grad()
+def initial_sampler(nears, fars, num_samples: int, t_rand=None):
+    """UniformLinDispPiecewiseSampler bins.  Returns (spacing bins [R,S+1], euclidean bins [R,S+1])."""
+    nears, fars = _c(nears).reshape(-1), _c(fars).reshape(-1)
+    require_cuda(nears, fars, t_rand)
+    R = nears.shape[0]
+    lin = _lin_table("bins", num_samples, nears.device)
+    sb = torch.empty((R, num_samples + 1), device=nears.device, dtype=torch.float32)
+    eb = torch.empty_like(sb)
+    per_bin = 0
+    if t_rand is not None:
+        t_rand = _c(t_rand)
+        per_bin = int(t_rand.numel() != R)
+    call("nkbs_initial_sampler", R, num_samples, ptr(lin), ptr(t_rand), per_bin, ptr(nears), ptr(fars), ptr(sb),
+         ptr(eb), stream())
+    return sb, eb
+
+
+@torch.no_grad()
+def pdf_sample(weights, spacing_bins, nears, fars, num_samples: int, anneal: float = 1.0, rand=None,
+               histogram_padding: float = 0.01, eps: float = 1e-5, anneal_dev=None, want_indices=False):
+    """PDFSampler: weights [R,S] (pre-anneal), spacing_bins [R,S+1] -> new (spacing, euclid) bins [R,ns+1]."""
+    weights = _c(weights.detach())
+    R, S = weights.shape
+    nb = num_samples + 1
+    sbins = _c(spacing_bins)
+    nears, fars = _c(nears).reshape(-1), _c(fars).reshape(-1)
+    require_cuda(weights, sbins, nears)
+    u = _lin_table("u", nb, weights.device)
+    ob = torch.empty((R, nb), device=weights.device, dtype=torch.float32)
+    oe = torch.empty_like(ob)
+    inds = torch.empty((R, nb), device=weights.device, dtype=torch.int64) if want_indices else None
+    per_bin = 0
+    if rand is not None:
+        rand = _c(rand)
+        per_bin = int(rand.numel() != R)
+    call("nkbs_pdf_sample", R, S, nb, ptr(weights), float(anneal), ptr(anneal_dev), float(histogram_padding),
+         float(eps), ptr(sbins), ptr(u), ptr(rand), per_bin, ptr(nears), ptr(fars), ptr(ob), ptr(oe), ptr(inds),
+         stream())
+    return (ob, oe, inds) if want_indices else (ob, oe)
+
+
+# ----------------------------------------------------------------------------------------------
+# K6/K7 compositing
+# ----------------------------------------------------------------------------------------------
+class _Composite(torch.autograd.Function):
+    """One ray-major pass: weights (from density) and every requested render."""
+
+    @staticmethod
+    def forward(ctx, density, weights_in, rgb, sem, starts, ends, bg_mode, eval_mode, sem_weight_grad, want):
+        ctx.set_materialize_grads(False)
+        src = density if density is not None else weights_in
+        R, S = src.shape[0], src.shape[1]
+        dev = src.device
+        density, weights_in, rgb, sem = _c(density), _c(weights_in), _c(rgb), _c(sem)
+        starts, ends = _c(starts), _c(ends)
+        require_cuda(src, rgb, sem, starts)
+        C = sem.shape[-1] if sem is not None else 0
+        f32 = dict(device=dev, dtype=torch.float32)
+        weights = torch.empty((R, S), **f32) if density is not None else None
+        rgb_out = torch.empty((R, 3), **f32) if (rgb is not None and "rgb" in want) else None
+        acc = torch.empty((R,), **f32) if ("acc" in want or rgb_out is not None or "depth_exp" in want) else None
+        d_raw = torch.empty((R,), **f32) if "depth_exp" in want else None
+        d_exp = torch.empty((R,), **f32) if d_raw is not None else None
+        d_mask = torch.empty((R,), **f32) if d_raw is not None else None
+        d_med = torch.empty((R,), **f32) if "depth_med" in want else None
+        sem_out = torch.empty((R, C), **f32) if (sem is not None and "sem" in want) else None
+        mm = torch.empty((2,), device=dev, dtype=torch.int32) if d_raw is not None else None
+        call("nkbs_composite_fwd", R, S, ptr(density), ptr(weights_in), ptr(starts), ptr(ends), ptr(rgb), ptr(sem),
+             C, bg_mode, int(eval_mode), ptr(weights), ptr(rgb_out), ptr(acc), ptr(d_raw), ptr(d_exp), ptr(d_mask),
+             ptr(d_med), ptr(sem_out), ptr(mm), stream())
+        w_saved = weights if density is not None else weights_in
+        ctx.cfg = (R, S, C, bg_mode, sem_weight_grad, density is not None)
+        ctx.save_for_backward(density, w_saved, starts, ends, rgb, sem, acc, d_raw, d_mask)
+        if d_med is not None:
+            ctx.mark_non_differentiable(d_med)
+        outs = (weights, rgb_out, acc, d_exp, d_med, sem_out)
+        return outs
+
+    @staticmethod
+    def backward(ctx, g_w, g_rgb, g_acc, g_dexp, _g_dmed, g_sem):
+        R, S, C, bg_mode, sem_weight_grad, from_density = ctx.cfg
+        density, w, starts, ends, rgb, sem, acc, d_raw, d_mask = ctx.saved_tensors
+        dev = w.device
+        f32 = dict(device=dev, dtype=torch.float32)
+        g_w, g_rgb, g_acc, g_sem = _c(g_w), _c(g_rgb), _c(g_acc), _c(g_sem)
+        g_depth = None
+        if g_dexp is not None and d_raw is not None:
+            g_depth = (_c(g_dexp) * d_mask).contiguous()
+        need_src = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
+        d_density = torch.empty((R, S), **f32) if (from_density and need_src) else None
+        d_weights = torch.empty((R, S), **f32) if (not from_density and need_src) else None
+        d_rgb = torch.empty((R, S, 3), **f32) if (rgb is not None and ctx.needs_input_grad[2] and g_rgb is not None) else None
+        d_sem = torch.empty((R, S, C), **f32) if (sem is not None and ctx.needs_input_grad[3] and g_sem is not None) else None
+        call("nkbs_composite_bwd", R, S, ptr(density), ptr(w), ptr(starts), ptr(ends), ptr(rgb), ptr(sem), C, bg_mode,
+             int(sem_weight_grad), ptr(acc), ptr(d_raw), ptr(g_w), ptr(g_rgb) if rgb is not None else None,
+             ptr(g_acc), ptr(g_depth), ptr(g_sem) if sem is not None else None, ptr(d_density), ptr(d_weights),
+             ptr(d_rgb), ptr(d_sem), stream())
+        return d_density, d_weights, d_rgb, d_sem, None, None, None, None, None, None
+
+
+def composite(density=None, weights=None, rgb=None, sem=None, starts=None, ends=None, background="last_sample",
+              eval_mode=False, sem_weight_grad=False, want=("rgb", "acc", "depth_exp", "depth_med", "sem")):
+    """Fused get_weights + renderers.  [R,S(,C)] inputs (a trailing singleton dim on density / weights /
+    starts / ends is accepted).  Returns dict with weights [R,S,1], rgb [R,3], accumulation [R,1],
+    expected_depth [R,1], depth [R,1] (median), semantics [R,C] — those requested and possible."""
+    def sq(t):
+        return t[..., 0] if (t is not None and t.dim() == 3 and t.shape[-1] == 1) else t
+    density, weights, starts, ends = sq(density), sq(weights), sq(starts), sq(ends)
+    w, rgb_o, acc, dexp, dmed, sem_o = _Composite.apply(density, weights, rgb, sem, starts, ends, BG_MODES[background],
+                                                        eval_mode, sem_weight_grad, frozenset(want))
+    out = {}
+    if w is not None:
+        out["weights"] = w[..., None]
+    if rgb_o is not None:
+        out["rgb"] = rgb_o
+    if acc is not None and "acc" in want:
+        out["accumulation"] = acc[..., None]
+    if dexp is not None:
+        out["expected_depth"] = dexp[..., None]
+    if dmed is not None:
+        out["depth"] = dmed[..., None]
+    if sem_o is not None:
+        out["semantics"] = sem_o
+    return out

@@ -1,0 +1,167 @@
+"""Drop-in samplers (nerfstudio model_components/ray_samplers.py) built at ref:nerfacto.py:325-332 and
+ref:semantic_nerfw.py:132-137, called at ref:nerfacto.py:397 / ref:semantic_nerfw.py:187."""
+from __future__ import annotations
+
+from typing import Callable, List, Optional, Tuple
+
+import torch
+from torch import nn
+
+from . import ops
+from .rays import RayBundle, RaySamples
+
+
+def _spacing_fn(x):
+    return torch.where(x < 1, x / 2, 1 - 1 / (2 * x))
+
+
+def _spacing_fn_inv(x):
+    return torch.where(x < 0.5, 2 * x, 1 / (2 - 2 * x))
+
+
+def _make_s2e(nears, fars):
+    """spacing -> euclidean map handed to RaySamples (only evaluated by foreign callers; the kernels
+    compute it in-line)."""
+    def fn(x):
+        s_near, s_far = _spacing_fn(nears), _spacing_fn(fars)
+        return _spacing_fn_inv(x * s_far + (1 - x) * s_near)
+    return fn
+
+
+class UniformLinDispPiecewiseSampler(nn.Module):
+    """Initial sampler: uniform in distance up to 1, uniform in disparity beyond."""
+
+    def __init__(self, num_samples: Optional[int] = None, train_stratified: bool = True, single_jitter: bool = False):
+        super().__init__()
+        self.num_samples = num_samples
+        self.train_stratified = train_stratified
+        self.single_jitter = single_jitter
+
+    def generate_ray_samples(self, ray_bundle: RayBundle, num_samples: Optional[int] = None, t_rand=None) -> RaySamples:
+        assert ray_bundle.nears is not None and ray_bundle.fars is not None
+        num_samples = num_samples or self.num_samples
+        R = ray_bundle.origins.shape[0]
+        if self.train_stratified and self.training:
+            if t_rand is None:
+                n = 1 if self.single_jitter else num_samples + 1
+                t_rand = torch.rand((R, n), dtype=torch.float32, device=ray_bundle.origins.device)
+        else:
+            t_rand = None
+        sb, eb = ops.initial_sampler(ray_bundle.nears, ray_bundle.fars, num_samples, t_rand)
+        return ray_bundle.samples_from_bins(sb, eb, _make_s2e(ray_bundle.nears, ray_bundle.fars))
+
+    def forward(self, *args, **kwargs):
+        return self.generate_ray_samples(*args, **kwargs)
+
+
+class PDFSampler(nn.Module):
+    """Inverse-CDF resampling along a weight histogram."""
+
+    def __init__(self, num_samples: Optional[int] = None, train_stratified: bool = True, single_jitter: bool = False,
+                 include_original: bool = True, histogram_padding: float = 0.01):
+        super().__init__()
+        if include_original:
+            raise NotImplementedError("include_original=True is not on the reference path (ProposalNetworkSampler "
+                                      "builds PDFSampler(include_original=False))")
+        self.num_samples = num_samples
+        self.train_stratified = train_stratified
+        self.single_jitter = single_jitter
+        self.histogram_padding = histogram_padding
+        self.anneal_dev = None  # optional device scalar (CUDA-graph replay)
+
+    def generate_ray_samples(self, ray_bundle: RayBundle, ray_samples: RaySamples, weights: torch.Tensor,
+                             num_samples: Optional[int] = None, eps: float = 1e-5, rand=None,
+                             anneal: float = 1.0) -> RaySamples:
+        """``weights`` are the pre-anneal weights; ``anneal`` is applied inside the kernel
+        (pow(weights, anneal), ref ProposalNetworkSampler)."""
+        num_samples = num_samples or self.num_samples
+        S = weights.shape[-2]
+        w = weights.reshape(-1, S)
+        R = w.shape[0]
+        if ray_samples.spacing_bins is not None:
+            sb = ray_samples.spacing_bins
+        else:
+            sb = torch.cat([ray_samples.spacing_starts[..., 0], ray_samples.spacing_ends[..., -1:, 0]], dim=-1)
+        if self.train_stratified and self.training:
+            if rand is None:
+                n = 1 if self.single_jitter else num_samples + 1
+                rand = torch.rand((R, n), device=w.device)
+        else:
+            rand = None
+        nsb, neb = ops.pdf_sample(w, sb, ray_bundle.nears, ray_bundle.fars, num_samples, anneal=anneal, rand=rand,
+                                  histogram_padding=self.histogram_padding, eps=eps, anneal_dev=self.anneal_dev)
+        return ray_bundle.samples_from_bins(nsb, neb, ray_samples.spacing_to_euclidean_fn)
+
+    def forward(self, *args, **kwargs):
+        return self.generate_ray_samples(*args, **kwargs)
+
+
+class ProposalNetworkSampler(nn.Module):
+    """Hierarchical proposal sampling with the reference's update gating and weight annealing
+    (ref:nerfacto.py:314-332,365-394)."""
+
+    def __init__(self, num_nerf_samples_per_ray: int = 32, num_proposal_samples_per_ray: Tuple[int, ...] = (64,),
+                 num_proposal_network_iterations: int = 2, single_jitter: bool = False,
+                 update_sched: Callable = lambda x: 1, initial_sampler=None):
+        super().__init__()
+        self.num_nerf_samples_per_ray = num_nerf_samples_per_ray
+        self.num_proposal_samples_per_ray = num_proposal_samples_per_ray
+        self.num_proposal_network_iterations = num_proposal_network_iterations
+        self.update_sched = update_sched
+        if self.num_proposal_network_iterations < 1:
+            raise ValueError("num_proposal_network_iterations must be >= 1")
+        if initial_sampler is None:
+            self.initial_sampler = UniformLinDispPiecewiseSampler(single_jitter=single_jitter)
+        else:
+            self.initial_sampler = initial_sampler
+        self.pdf_sampler = PDFSampler(include_original=False, single_jitter=single_jitter)
+        self._anneal = 1.0
+        self._steps_since_update = 0
+        self._step = 0
+
+    def set_anneal(self, anneal: float) -> None:
+        self._anneal = anneal
+
+    def step_cb(self, step):
+        self._step = step
+        self._steps_since_update += 1
+
+    def will_update(self) -> bool:
+        return self._steps_since_update > self.update_sched(self._step) or self._step < 10
+
+    def generate_ray_samples(self, ray_bundle: Optional[RayBundle] = None, density_fns: Optional[List[Callable]] = None,
+                             jitter=None) -> Tuple[RaySamples, List, List]:
+        """``jitter`` (optional [t_rand0, rand1, rand2]) injects the random draws, for parity tests."""
+        assert ray_bundle is not None and density_fns is not None
+        weights_list, ray_samples_list = [], []
+        n = self.num_proposal_network_iterations
+        weights, ray_samples = None, None
+        updated = self.will_update()
+        for i_level in range(n + 1):
+            is_prop = i_level < n
+            num_samples = self.num_proposal_samples_per_ray[i_level] if is_prop else self.num_nerf_samples_per_ray
+            j = None if jitter is None else jitter[i_level]
+            if i_level == 0:
+                ray_samples = self.initial_sampler(ray_bundle, num_samples=num_samples, t_rand=j)
+            else:
+                # pow(weights, anneal) happens inside the PDF kernel
+                ray_samples = self.pdf_sampler(ray_bundle, ray_samples, weights, num_samples=num_samples, rand=j,
+                                               anneal=float(self._anneal))
+            if is_prop:
+                fn = density_fns[i_level]
+                owner = getattr(fn, "__self__", None)
+                with torch.set_grad_enabled(updated and torch.is_grad_enabled()):
+                    if owner is not None and hasattr(owner, "get_density") and getattr(owner, "_norm", None) is not None:
+                        density, _ = owner.get_density(ray_samples)  # per-ray frustum path, no [R,S,3] tensor
+                    else:
+                        density = fn(ray_samples.frustums.get_positions())
+                    weights = ray_samples.get_weights(density)
+                weights_list.append(weights)
+                ray_samples_list.append(ray_samples)
+        if updated:
+            self._steps_since_update = 0
+        assert ray_samples is not None
+        return ray_samples, weights_list, ray_samples_list
+
+    def forward(self, *args, **kwargs):
+        return self.generate_ray_samples(*args, **kwargs)
