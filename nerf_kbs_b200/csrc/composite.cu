@@ -9,7 +9,7 @@ namespace {
 
 constexpr int kWarpsPerCta = 8;
 constexpr int kThreads = kWarpsPerCta * 32;
-constexpr int kMaxS = 512;   // samples per ray held in a warp's shared-memory strip
+constexpr int kMaxS = 512;  // samples per ray held in a warp's shared-memory strip
 
 struct CompArgs {
   int64_t R;
@@ -104,13 +104,14 @@ __global__ void __launch_bounds__(kThreads) composite_fwd_kernel(const CompArgs 
     if (a.acc_out && lane == 0) a.acc_out[r] = acc;
     if (a.depth_exp && lane == 0) a.depth_exp[r] = dsum / (acc + 1e-10f);
     if (a.depth_med) {
-      // inclusive cumsum in sample order (torch.cumsum on the CPU), first index with cum >= 0.5
+      // inclusive cumsum in sample order, double accumulator rounded to float per element (what
+      // torch.cumsum does on the CPU); first index with cum >= 0.5
       if (lane == 0) {
-        float cum = 0.f;
+        double cum = 0.0;
         int idx = S;
         for (int s = 0; s < S; ++s) {
-          cum += sw[s];
-          if (cum >= 0.5f) {
+          cum += (double)sw[s];
+          if ((float)cum >= 0.5f) {
             idx = s;
             break;
           }
@@ -221,11 +222,12 @@ struct CompBwdArgs {
 };
 
 __global__ void __launch_bounds__(kThreads) composite_bwd_kernel(const CompBwdArgs a) {
-  extern __shared__ float s_buf[];  // [kWarpsPerCta][2][S]
+  extern __shared__ float s_buf[];  // [kWarpsPerCta][3][S]: weights, dL/dw, exp(-incl)
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int S = a.S;
-  float* sw = s_buf + wid * 2 * S;
+  float* sw = s_buf + wid * 3 * S;
   float* sg = sw + S;
+  float* sE = sg + S;
   for (int64_t r = blockIdx.x * (int64_t)kWarpsPerCta + wid; r < a.R; r += (int64_t)gridDim.x * kWarpsPerCta) {
     const int64_t base = r * S;
     const float acc = a.acc ? a.acc[r] : 0.f;
@@ -250,7 +252,6 @@ __global__ void __launch_bounds__(kThreads) composite_bwd_kernel(const CompBwdAr
       g_acc += -g * a.depth_raw[r] / den;
     }
     // pass A: gradient w.r.t. each weight
-    float Q = 0.f;
     for (int s = lane; s < S; s += 32) {
       float w = a.weights[base + s];
       float g = g_acc + (a.g_weights ? a.g_weights[base + s] : 0.f);
@@ -268,7 +269,6 @@ __global__ void __launch_bounds__(kThreads) composite_bwd_kernel(const CompBwdAr
       }
       sw[s] = w;
       sg[s] = g;
-      Q += g * w;
       if (a.d_weights) a.d_weights[base + s] = g;
       if (a.d_rgb) {
         float* o = a.d_rgb + (base + s) * 3;
@@ -278,7 +278,6 @@ __global__ void __launch_bounds__(kThreads) composite_bwd_kernel(const CompBwdAr
         o[2] = gr[2] * (w + extra);
       }
     }
-    Q = warp_sum(Q);
     __syncwarp();
     if (a.d_sem) {
       float* o = a.d_sem + base * a.C;
@@ -292,20 +291,35 @@ __global__ void __launch_bounds__(kThreads) composite_bwd_kernel(const CompBwdAr
     }
     if (a.d_density) {
       // w_i = (1-exp(-x_i)) exp(-sum_{j<i} x_j):  dL/dx_i = g_i exp(-incl_i) - sum_{j>i} g_j w_j
-      float carry_x = 0.f, carry_q = 0.f;
+      // forward sweep: E_i = exp(-inclusive prefix of x); reverse sweep: exclusive suffix sum of g_j w_j
+      float carry_x = 0.f;
       for (int s0 = 0; s0 < S; s0 += 32) {
         int s = s0 + lane;
         bool live = s < S;
-        float delta = live ? a.ends[base + s] - a.starts[base + s] : 0.f;
-        float x = live ? delta * a.density[base + s] : 0.f;
-        float g = live ? sg[s] : 0.f;
-        float q = live ? g * sw[s] : 0.f;
+        float x = live ? (a.ends[base + s] - a.starts[base + s]) * a.density[base + s] : 0.f;
         float ix = warp_incl_scan(x, lane);
-        float iq = warp_incl_scan(q, lane);
-        float dx = g * expf(-(carry_x + ix)) - (Q - (carry_q + iq));
-        if (live) a.d_density[base + s] = delta * dx;
+        if (live) sE[s] = expf(-(carry_x + ix));
         carry_x += __shfl_sync(0xffffffffu, ix, 31);
-        carry_q += __shfl_sync(0xffffffffu, iq, 31);
+      }
+      __syncwarp();
+      float carry_q = 0.f;  // sum of g_j w_j over all later chunks
+      for (int s0 = ((S - 1) / 32) * 32; s0 >= 0; s0 -= 32) {
+        int s = s0 + lane;
+        bool live = s < S;
+        float q = live ? sg[s] * sw[s] : 0.f;
+        // inclusive suffix scan inside the chunk
+        float sq = q;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          float n = __shfl_down_sync(0xffffffffu, sq, o);
+          if (lane + o < 32) sq += n;
+        }
+        float suffix_excl = carry_q + (sq - q);
+        if (live) {
+          float delta = a.ends[base + s] - a.starts[base + s];
+          a.d_density[base + s] = delta * (sg[s] * sE[s] - suffix_excl);
+        }
+        carry_q += __shfl_sync(0xffffffffu, sq, 0);
       }
     }
     __syncwarp();
@@ -367,7 +381,7 @@ extern "C" int nkbs_composite_bwd(int64_t R, int32_t S, const float* density, co
   if (R == 0) return 0;
   CompBwdArgs a{R, S, density, weights, starts, ends, rgb, sem, C, bg_mode, sem_weight_grad, acc, depth_raw,
                 g_weights, g_rgb, g_acc, g_depth, g_sem, d_density, d_weights, d_rgb, d_sem};
-  size_t smem = (size_t)kWarpsPerCta * 2 * S * sizeof(float);
+  size_t smem = (size_t)kWarpsPerCta * 3 * S * sizeof(float);
   composite_bwd_kernel<<<comp_grid(R), kThreads, smem, (cudaStream_t)stream>>>(a);
   NKBS_CHECK_LAUNCH("nkbs_composite_bwd");
   return 0;

@@ -3,7 +3,9 @@
 // reached from ref:nerfacto.py:325-332,397 and ref:semantic_nerfw.py:132-137,187.
 //
 // Bit-exactness: every op is an explicit round-to-nearest IEEE op in the torch path's order; sums and
-// the cumulative distribution are accumulated in sample order (torch.cumsum's order on the CPU).  The
+// the cumulative distribution are accumulated in sample order; the cdf uses a double accumulator rounded
+// to float per entry, which is what torch.cumsum does on the CPU (the normaliser torch.sum uses a
+// vectorised float order that no kernel can reproduce: there the kernel sums floats in sample order).  The
 // linspace tables come from the host (torch.linspace on the CPU) so their rounding is the oracle's.
 #include <float.h>
 #include "common.cuh"
@@ -89,19 +91,22 @@ __global__ void __launch_bounds__(kThreads) pdf_sample_kernel(const PdfArgs a) {
     const float* eb = a.sbins + r * (S + 1);
     const bool do_pow = anneal != 1.0f;
     // pass 1: weights_sum = sum(pow(w, anneal) + histogram_padding)
-    float sum = 0.f;
+    // The normaliser is accumulated in double and rounded once: torch.sum's vectorised float order on the
+    // CPU is machine dependent, the correctly rounded sum is the closest well-defined stand-in.
+    double dsum = 0.0;
     for (int s = 0; s < S; ++s) {
       float v = w[s];
       if (do_pow) v = powf(v, anneal);
-      sum = __fadd_rn(sum, __fadd_rn(v, a.hist_pad));
+      dsum += (double)__fadd_rn(v, a.hist_pad);
     }
+    float sum = (float)dsum;
     float padding = fmaxf(__fsub_rn(a.eps, sum), 0.f);
     float pad_each = __fdiv_rn(padding, fS);
     sum = __fadd_rn(sum, padding);
     float s_near = spacing_fn(a.nears[r]), s_far = spacing_fn(a.fars[r]);
     // merge walk state: idx = number of cdf entries known to be <= u so far
     int idx = 0;            // candidate searchsorted result
-    float run = 0.f;        // unclipped cumsum of pdf up to entry idx
+    double run = 0.0;       // unclipped cumsum of pdf up to entry idx (double accumulator, as torch.cumsum on the CPU)
     float c_cur = 0.f;      // cdf[idx]   (cdf[0] = 0)
     float c_prev = 0.f;     // cdf[idx-1] (unused while idx == 0)
     float rj = 0.f;
@@ -122,8 +127,8 @@ __global__ void __launch_bounds__(kThreads) pdf_sample_kernel(const PdfArgs a) {
           float v = w[idx - 1];
           if (do_pow) v = powf(v, anneal);
           v = __fadd_rn(__fadd_rn(v, a.hist_pad), pad_each);
-          run = __fadd_rn(run, __fdiv_rn(v, sum));
-          c_cur = fminf(1.f, run);
+          run += (double)__fdiv_rn(v, sum);
+          c_cur = fminf(1.f, (float)run);
         }
       }
       int below = idx - 1 < 0 ? 0 : (idx - 1 > S ? S : idx - 1);
