@@ -95,6 +95,18 @@ int nkbs_composite_bwd(int64_t R, int32_t S, const float* density, const float* 
                        const float* g_sem, float* d_density, float* d_weights, float* d_rgb, float* d_sem,
                        void* stream);
 
+/* N2 — multi-tensor Adam (torch.optim.Adam semantics, amsgrad off).
+ * replaces: the Adam(lr=1e-3, eps=1e-15) optimizers the reference configures for the "fields" and
+ *           "proposal_networks" groups (train.py:85-98; groups nerfacto.py:359-363).
+ * params/grads/exp_avg/exp_avg_sq: HOST arrays of num_tensors DEVICE pointers; numel: HOST.
+ * step_dev: device scalar, the step count t >= 1 as float (bias corrections 1-beta^t are computed on the
+ * device so a captured CUDA graph sees a new t every replay).  inv_scale_dev: optional device scalar
+ * multiplied into every gradient (GradScaler unscale). */
+int nkbs_adam_step(int32_t num_tensors, float* const* params, const float* const* grads,
+                   float* const* exp_avg, float* const* exp_avg_sq, const int64_t* numel, float lr,
+                   float beta1, float beta2, float eps, float weight_decay, const float* step_dev,
+                   const float* inv_scale_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

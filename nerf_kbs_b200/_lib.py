@@ -26,6 +26,7 @@ SIGNATURES = {
     "nkbs_initial_sampler": [_i64, _i32, _p, _p, _i32, _p, _p, _p, _p, _p],
     "nkbs_pdf_sample": [_i64, _i32, _i32, _p, _f, _p, _f, _f, _p, _p, _p, _i32, _p, _p, _p, _p, _p, _p],
     "nkbs_composite_fwd": [_i64, _i32, _p, _p, _p, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
+    "nkbs_adam_step": [_i32, _p, _p, _p, _p, _p, _f, _f, _f, _f, _f, _p, _p, _p],
     "nkbs_composite_bwd": [_i64, _i32, _p, _p, _p, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
 }
 
@@ -64,9 +65,20 @@ def stream() -> int:
     return torch.cuda.current_stream().cuda_stream
 
 
+# optional per-launch observer (bench.py's kernel timing pass): callable(name, args) -> context manager
+launch_observer = None
+# every entry point counts its calls here (bench.py reports the launches of a step from it)
+call_counts = {}
+
+
 def call(name: str, *args) -> None:
     lib = load()
-    rc = getattr(lib, name)(*args)
+    call_counts[name] = call_counts.get(name, 0) + 1
+    if launch_observer is not None:
+        with launch_observer(name, args):
+            rc = getattr(lib, name)(*args)
+    else:
+        rc = getattr(lib, name)(*args)
     if rc != 0:
         raise RuntimeError(f"{name} failed ({rc}): {lib.nkbs_last_error().decode()}")
 

@@ -118,6 +118,7 @@ class ProposalNetworkSampler(nn.Module):
         self._anneal = 1.0
         self._steps_since_update = 0
         self._step = 0
+        self.force_updated = None  # Trainer sets this while it captures the two CUDA-graph variants
 
     def set_anneal(self, anneal: float) -> None:
         self._anneal = anneal
@@ -127,6 +128,8 @@ class ProposalNetworkSampler(nn.Module):
         self._steps_since_update += 1
 
     def will_update(self) -> bool:
+        if self.force_updated is not None:
+            return bool(self.force_updated)
         return self._steps_since_update > self.update_sched(self._step) or self._step < 10
 
     def generate_ray_samples(self, ray_bundle: Optional[RayBundle] = None, density_fns: Optional[List[Callable]] = None,

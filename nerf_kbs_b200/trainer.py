@@ -1,0 +1,240 @@
+"""Training-step driver of the ray-batch hot path: what nerfstudio's ``Trainer.train_iteration`` does
+around ``model.get_outputs`` for the reference's configs (ref:train.py:42-101 — 4096 rays per step,
+Adam lr 1e-3 eps 1e-15 on the "proposal_networks" and "fields" groups, no scheduler), as one CUDA
+graph per step:
+
+    zero_grad -> model(ray_bundle) -> get_loss_dict -> backward -> [gradient allreduce] -> Adam
+
+The callbacks of ref:nerfacto.py:365-394 (weight-anneal before the step, ``step_cb`` after it) stay on
+the host: the anneal value reaches the captured kernels through a device scalar, and the proposal
+"updated" gating selects between two captured graphs (with / without proposal gradients).
+
+Data parallelism: one process per GPU, every rank steps its own ray batch, and one
+sum-allreduce (NCCL over NVLink; gloo on the CPU for tests) of the gradients precedes Adam — large hash
+tables in place, everything else through one flat bucket.  No other collective is on the path."""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from .optim import Adam
+from .rays import RayBundle
+
+BIG_TENSOR = 1 << 18  # elements; gradients at least this large are all-reduced in place, the rest bucketed
+
+
+# ----------------------------------------------------------------------------------------------
+# gradient exchange (device-agnostic: exercised with gloo on CPU tensors by the tests)
+# ----------------------------------------------------------------------------------------------
+def allreduce_mean_(tensors: Sequence[torch.Tensor], group=None, world_size: Optional[int] = None) -> None:
+    """In-place mean over ranks of every tensor in ``tensors`` (DDP gradient semantics)."""
+    if not dist.is_available() or not dist.is_initialized():
+        return
+    ws = world_size if world_size is not None else dist.get_world_size(group)
+    if ws == 1:
+        return
+    small = [t for t in tensors if t.numel() < BIG_TENSOR]
+    big = [t for t in tensors if t.numel() >= BIG_TENSOR]
+    inv = 1.0 / ws
+    for t in big:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+        t.mul_(inv)
+    if small:
+        flat = torch.cat([t.reshape(-1) for t in small])
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+        flat.mul_(inv)
+        off = 0
+        for t in small:
+            n = t.numel()
+            t.copy_(flat[off:off + n].view_as(t))
+            off += n
+
+
+def shard_rays(num_rays_total: int, rank: int, world_size: int) -> range:
+    """Strong-scaling split used by the reference's datamanager: ``train_num_rays_per_batch // world_size``
+    rays per rank (ref:dataparser/datamanager_z.py:225-231)."""
+    per = num_rays_total // world_size
+    return range(rank * per, (rank + 1) * per)
+
+
+# ----------------------------------------------------------------------------------------------
+class Trainer:
+    """One training step of ``model`` (NerfactoModel / SemanticNerfWModel) per call."""
+
+    def __init__(self, model, num_rays: int, lr: float = 1e-3, eps: float = 1e-15, betas=(0.9, 0.999),
+                 use_graph: bool = True, process_group=None, graph_warmup: int = 3, seed: Optional[int] = None):
+        self.model = model
+        p0 = next(model.parameters())
+        if p0.device.type != "cuda":
+            raise RuntimeError("nkbs Trainer needs the model on a CUDA device (no CPU fallback)")
+        self.device = p0.device
+        self.R = int(num_rays)
+        groups = model.get_param_groups()
+        # one Adam per group, as nerfstudio's Optimizers does (same hyper-parameters in the reference)
+        self.optimizers: Dict[str, Adam] = {k: Adam(v, lr=lr, betas=betas, eps=eps) for k, v in groups.items()}
+        self.group = process_group
+        self.world_size = dist.get_world_size(process_group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.use_graph = use_graph
+        self.graph_warmup = graph_warmup
+        self.step = 0
+        self._graphs: Dict[bool, torch.cuda.CUDAGraph] = {}
+        self._graph_loss: Dict[bool, Dict[str, torch.Tensor]] = {}
+        self._pool = None
+        self._eager_steps = 0
+        self._calls_per_graph: Dict[bool, int] = {}
+        self.nkbs_calls = 0  # nkbs entry-point launches issued so far (graph replays count what they captured)
+        self._h2d_done: Optional[torch.cuda.Event] = None
+        dev = self.device
+        C = getattr(model.config, "num_semantic_classes", 0)
+        self.needs_labels = bool(getattr(model.config, "use_semantic", False)) or model.__class__.__name__ == "SemanticNerfWModel"
+        # static device-side inputs of the step (CUDA-graph replay reads these addresses)
+        self.buf = {
+            "origins": torch.zeros(self.R, 3, device=dev), "directions": torch.zeros(self.R, 3, device=dev),
+            "camera_indices": torch.zeros(self.R, 1, device=dev, dtype=torch.int64),
+            "pixel_area": torch.zeros(self.R, 1, device=dev), "image": torch.zeros(self.R, 3, device=dev),
+        }
+        if self.needs_labels:
+            self.buf["semantics_label"] = torch.zeros(self.R, device=dev, dtype=torch.int64)
+        self.pinned = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True) for k, v in self.buf.items()}
+        self.anneal_t = torch.ones((), device=dev)
+        model.proposal_sampler.pdf_sampler.anneal_dev = self.anneal_t
+        self._loss_host = torch.zeros((), pin_memory=True)
+        self.loss_dict: Dict[str, torch.Tensor] = {}
+        if seed is not None:
+            torch.cuda.manual_seed(seed)
+
+    # -- inputs ------------------------------------------------------------------------------------
+    def h2d_bytes(self) -> int:
+        return sum(v.numel() * v.element_size() for v in self.buf.values())
+
+    def load_batch(self, ray_bundle: RayBundle, batch: Dict[str, torch.Tensor]) -> None:
+        """Copy one ray batch (host or device tensors) into the step's static input buffers.  Host tensors go
+        through pinned staging memory unless they already are pinned."""
+        src = {"origins": ray_bundle.origins, "directions": ray_bundle.directions,
+               "camera_indices": ray_bundle.camera_indices, "pixel_area": ray_bundle.pixel_area,
+               "image": batch["image"]}
+        if self.needs_labels:
+            src["semantics_label"] = batch["semantics_label"]
+        staged = False
+        for k, t in src.items():
+            dst = self.buf[k]
+            if t is None:
+                continue
+            if t.shape != dst.shape:
+                raise ValueError(f"{k}: expected shape {tuple(dst.shape)}, got {tuple(t.shape)}")
+            if t.device.type == "cpu" and not t.is_pinned():
+                if self._h2d_done is not None:  # the staging buffer may still feed the previous step's copy
+                    self._h2d_done.synchronize()
+                    self._h2d_done = None
+                self.pinned[k].copy_(t)
+                t = self.pinned[k]
+                staged = True
+            dst.copy_(t, non_blocking=True)
+        if staged:
+            self._h2d_done = torch.cuda.Event()
+            self._h2d_done.record()
+
+    def _bundle(self) -> RayBundle:
+        b = self.buf
+        return RayBundle(origins=b["origins"], directions=b["directions"], pixel_area=b["pixel_area"],
+                         camera_indices=b["camera_indices"], metadata={})
+
+    # -- the step ----------------------------------------------------------------------------------
+    def _grads(self) -> List[torch.Tensor]:
+        return [p.grad for o in self.optimizers.values() for p in o.params if p.grad is not None]
+
+    def _step_body(self) -> Dict[str, torch.Tensor]:
+        for o in self.optimizers.values():
+            o.zero_grad(set_to_none=True)
+        outputs = self.model(self._bundle())
+        batch = {"image": self.buf["image"]}
+        if self.needs_labels:
+            batch["semantics_label"] = self.buf["semantics_label"]
+        loss_dict = self.model.get_loss_dict(outputs, batch)
+        loss = sum(loss_dict.values())
+        loss.backward()
+        if self.world_size > 1:
+            allreduce_mean_(self._grads(), self.group, self.world_size)
+        for o in self.optimizers.values():
+            o.step()
+        out = {k: v.detach() for k, v in loss_dict.items()}
+        out["loss"] = loss.detach()
+        return out
+
+    def _capture(self, key: bool) -> None:
+        g = torch.cuda.CUDAGraph()
+        if self._pool is None:
+            self._pool = torch.cuda.graph_pool_handle()
+        for o in self.optimizers.values():
+            o.zero_grad(set_to_none=True)
+        torch.cuda.synchronize(self.device)
+        c0 = sum(_lib.call_counts.values())
+        with torch.cuda.graph(g, pool=self._pool):
+            out = self._step_body()
+        self._calls_per_graph[key] = sum(_lib.call_counts.values()) - c0
+        self._graphs[key] = g
+        self._graph_loss[key] = out
+
+    def prepare(self) -> None:
+        """Run the eager warm-up steps and capture every CUDA-graph variant up front (these are real
+        training steps on whatever the static buffers hold), so that no later step pays for a capture."""
+        if not self.use_graph:
+            return
+        sampler = self.model.proposal_sampler
+        while self._eager_steps < self.graph_warmup:
+            self.train_step()
+        gated = self.model.__class__.__name__ != "SemanticNerfWModel"  # no step_cb there: always updated
+        for key in ((True, False) if gated else (True,)):
+            if key not in self._graphs:
+                sampler.force_updated = key
+                try:
+                    self.train_step()
+                finally:
+                    sampler.force_updated = None
+
+    def train_step(self, ray_bundle: Optional[RayBundle] = None, batch: Optional[Dict[str, torch.Tensor]] = None
+                   ) -> torch.Tensor:
+        """Run one step on the given batch (or on whatever the static buffers hold).  Returns the total loss
+        as a device scalar; ``self.loss_dict`` holds the individual terms."""
+        if ray_bundle is not None:
+            self.load_batch(ray_bundle, batch)
+        m = self.model
+        m.set_step(self.step)
+        self.anneal_t.fill_(float(m.proposal_sampler._anneal))  # scalar travels as a kernel argument
+        updated = bool(m.proposal_sampler.will_update())
+        if self.use_graph and self._eager_steps >= self.graph_warmup:
+            if updated not in self._graphs:
+                self._capture(updated)
+            self._graphs[updated].replay()
+            self.nkbs_calls += self._calls_per_graph[updated]
+            out = self._graph_loss[updated]
+            if updated:  # the eager path resets this inside the sampler; the replay has no host side
+                m.proposal_sampler._steps_since_update = 0
+        else:
+            c0 = sum(_lib.call_counts.values())
+            if self.use_graph:
+                # warm-up iterations run on a side stream, as CUDA-graph capture requires
+                s = torch.cuda.Stream(self.device)
+                s.wait_stream(torch.cuda.current_stream(self.device))
+                with torch.cuda.stream(s):
+                    out = self._step_body()
+                torch.cuda.current_stream(self.device).wait_stream(s)
+            else:
+                out = self._step_body()
+            self._eager_steps += 1
+            self.nkbs_calls += sum(_lib.call_counts.values()) - c0
+        m.after_step(self.step)
+        self.step += 1
+        self.loss_dict = out
+        return out["loss"]
+
+    def train_step_host(self, ray_bundle: RayBundle, batch: Dict[str, torch.Tensor]) -> float:
+        """Host in, host out: H2D of the batch, the step, D2H of the loss (what a datamanager-driven loop
+        sees per iteration)."""
+        loss = self.train_step(ray_bundle, batch)
+        self._loss_host.copy_(loss, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return float(self._loss_host)
