@@ -54,6 +54,18 @@ int nkbs_mlp_bwd(const float* x, const float* dy, int64_t N, int32_t nl, const i
                  const float* const* W, const float* const* b, int32_t relu_mask, int32_t out_act,
                  const float* selector, float* dx, float* const* dW, float* const* db, void* stream);
 
+/* K3 (tensor cores) — the same fused MLP on tcgen05 tensor cores: 16-bit operands (fmt 0 = fp16, 1 = bf16),
+ * fp32 accumulation in TMEM, weights resident in shared memory, bias folded into the GEMM.  Same argument
+ * meaning as nkbs_mlp_fwd/bwd.  This is the mixed-precision path (the reference trains under autocast,
+ * train.py:50); parity bar 1e-2 relative. */
+int nkbs_mlp_tc_fwd(const float* x, int64_t N, int32_t nl, const int32_t* dims, const float* const* W,
+                    const float* const* b, int32_t relu_mask, int32_t out_act, int32_t fmt,
+                    const float* selector, float* y, void* stream);
+int nkbs_mlp_tc_bwd(const float* x, const float* dy, int64_t N, int32_t nl, const int32_t* dims,
+                    const float* const* W, const float* const* b, int32_t relu_mask, int32_t out_act,
+                    int32_t fmt, const float* selector, float* dx, float* const* dW, float* const* db,
+                    void* stream);
+
 /* K4 — head-MLP input assembly  h = [SH16((d+1)/2) | geo | embedding row]  and its backward.
  * replaces: SHEncoding + Embedding + torch.cat in NerfactoField.get_outputs (nerfacto.py:398;
  *           semantic_nerfw.py:188).  cam NULL -> emb_const [emb_dim] is used (eval). */

@@ -1,0 +1,571 @@
+// K3 (tensor-core path): fused small MLP, forward and backward, on tcgen05 tensor cores.
+//
+// One CTA (128 threads, thread t <-> sample row t <-> TMEM lane t) walks over 128-sample tiles.  Weights of
+// every layer stay in shared memory for the whole kernel as 16-bit UMMA operand tiles; activations bounce
+// TMEM -> registers (bias is folded into the GEMM through a constant-one input column, ReLU and the 16-bit
+// conversion happen in registers) -> shared memory, where they are the A operand of the next layer.
+// The backward kernel recomputes the forward, then per layer issues
+//     dX_l  = dY_l   . W_l        (A = dY_l K-major,            B = W_l viewed MN-major)
+//     dW_l += dY_l^T . [X_l | 1]  (A = dY_l viewed MN-major, M=64, B = X_l viewed MN-major; K = 128 samples)
+// with the weight/bias gradient accumulated in TMEM across all tiles of the CTA and flushed once.
+// Operand tiles use the chunk-major no-swizzle canonical layout of umma.cuh, so no transposed copies exist.
+// fmt 0 = fp16 operands, 1 = bf16 operands; accumulation is always fp32.
+// Replaces nerfstudio field_components.mlp.MLP (+ the field-head activations) reached from
+// ref:nerfacto.py:275-311,398 and ref:semantic_nerfw.py:102-126,188 (under autocast these linears run in
+// 16-bit on the reference side too, ref:train.py:50).
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include "common.cuh"
+#include "umma.cuh"
+
+namespace {
+
+using namespace umma;
+
+constexpr int kTile = 128;
+constexpr int kThreads = 128;
+constexpr int kMaxLayers = 3;
+constexpr int kMaxWidth = 64;
+constexpr int kActCs = kTile * 16 + 16;  // chunk stride (bytes) of a 128-row activation tile
+
+enum OutAct { ACT_NONE = 0, ACT_SIGMOID = 1, ACT_DENSITY = 2, ACT_TRANSIENT = 3 };
+
+struct TcLayer {
+  const float* W;  // [N,K] torch nn.Linear layout
+  const float* b;  // [N]
+  float* dW;
+  float* db;
+  int K, N;
+  int relu;   // ReLU after this layer
+  int Ka;     // K + 1 (bias column) rounded up to 16
+  int Np;     // N rounded up to 16
+  int w_off;  // byte offset of the weight tile in shared memory
+  int w_cs;   // chunk stride (bytes) of the weight tile = Np*16 + 16
+  int x_off;  // byte offset of this layer's input tile X_l
+  int dw_col; // first TMEM column of this layer's dW accumulator (backward)
+};
+
+struct TcArgs {
+  int nl;
+  TcLayer layer[kMaxLayers];
+  const float* x;         // [N,K0]
+  const float* selector;  // [N] or null
+  float* y;               // [N,Kn]   (forward)
+  const float* dy;        // [N,Kn]   (backward)
+  float* dx;              // [N,K0] or null (backward)
+  int out_act;
+  int fmt;                // 0 fp16, 1 bf16
+  int64_t N;
+  int x_off1;             // forward: second ping-pong activation buffer
+  int g_off;              // backward: gradient tile (64 features wide)
+  int tmem_cols;          // power of two >= 32
+  int smem_bytes;
+};
+
+template <int FMT>
+__device__ __forceinline__ uint16_t cvt16(float v) {
+  if (FMT == 1) {
+    __nv_bfloat16 h = __float2bfloat16_rn(v);
+    return *reinterpret_cast<uint16_t*>(&h);
+  } else {
+    __half h = __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f));
+    return *reinterpret_cast<uint16_t*>(&h);
+  }
+}
+template <int FMT>
+__device__ __forceinline__ uint32_t pack2(float a, float b) {
+  return (uint32_t)cvt16<FMT>(a) | ((uint32_t)cvt16<FMT>(b) << 16);
+}
+
+// byte offset of element (row, k) inside a tile with chunk stride cs
+__device__ __forceinline__ int tile_off(int row, int k, int cs) { return (k >> 3) * cs + row * 16 + (k & 7) * 2; }
+
+// weights of every layer -> 16-bit operand tiles: rows n < Np (zero padded), columns k < Ka with column K = bias
+template <int FMT>
+__device__ void stage_weights(const TcArgs& a, unsigned char* smem) {
+  for (int l = 0; l < a.nl; ++l) {
+    const TcLayer& ly = a.layer[l];
+    unsigned char* wt = smem + ly.w_off;
+    const int total = ly.Np * ly.Ka;
+    for (int e = threadIdx.x; e < total; e += kThreads) {
+      int n = e / ly.Ka, k = e - n * ly.Ka;
+      float v = 0.f;
+      if (n < ly.N) {
+        if (k < ly.K) v = __ldg(ly.W + (size_t)n * ly.K + k);
+        else if (k == ly.K) v = __ldg(ly.b + n);
+      }
+      *reinterpret_cast<uint16_t*>(wt + tile_off(n, k, ly.w_cs)) = cvt16<FMT>(v);
+    }
+  }
+}
+
+// global x[row0 .. row0+127, 0..K) fp32 -> X0 tile (16-bit), column K = 1, columns K+1..Ka-1 = 0
+template <int FMT>
+__device__ void load_input_tile(const float* __restrict__ x, int64_t row0, int64_t rows_total, int K, int Ka,
+                                unsigned char* tile) {
+  int64_t rows = rows_total - row0;
+  if (rows > kTile) rows = kTile;
+  const float* src = x + row0 * K;
+  const int valid = (int)rows * K;
+  const int total = kTile * K;
+  if ((K & 3) == 0 && ((reinterpret_cast<uintptr_t>(src) & 15) == 0)) {
+    for (int e = threadIdx.x * 4; e < total; e += kThreads * 4) {
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (e < valid) v = __ldg(reinterpret_cast<const float4*>(src + e));
+      int r = e / K, k = e - r * K;
+      uint2 p = make_uint2(pack2<FMT>(v.x, v.y), pack2<FMT>(v.z, v.w));
+      *reinterpret_cast<uint2*>(tile + tile_off(r, k, kActCs)) = p;
+    }
+  } else {
+    for (int e = threadIdx.x; e < total; e += kThreads) {
+      float v = e < valid ? __ldg(src + e) : 0.f;
+      int r = e / K, k = e - r * K;
+      *reinterpret_cast<uint16_t*>(tile + tile_off(r, k, kActCs)) = cvt16<FMT>(v);
+    }
+  }
+  const int r = threadIdx.x;
+  for (int k = K; k < Ka; ++k)
+    *reinterpret_cast<uint16_t*>(tile + tile_off(r, k, kActCs)) = cvt16<FMT>(k == K ? 1.f : 0.f);
+}
+
+__device__ __forceinline__ float apply_out_act(int act, int n, float raw, float sel) {
+  switch (act) {
+    case ACT_SIGMOID: return nkbs_sigmoid(raw);
+    case ACT_DENSITY: return n == 0 ? expf(raw) * sel : raw;
+    case ACT_TRANSIENT: return (n >= 1 && n <= 3) ? nkbs_sigmoid(raw) : nkbs_softplus(raw);
+    default: return raw;
+  }
+}
+
+__device__ __forceinline__ float out_act_grad(int act, int n, float raw, float sel, float dy) {
+  switch (act) {
+    case ACT_SIGMOID: {
+      float s = nkbs_sigmoid(raw);
+      return dy * s * (1.f - s);
+    }
+    case ACT_DENSITY: return n == 0 ? dy * sel * expf(fminf(fmaxf(raw, -15.f), 15.f)) : dy;
+    case ACT_TRANSIENT:
+      if (n >= 1 && n <= 3) {
+        float s = nkbs_sigmoid(raw);
+        return dy * s * (1.f - s);
+      }
+      return raw > 20.f ? dy : dy * nkbs_sigmoid(raw);
+    default: return dy;
+  }
+}
+
+// D[128 x Np] (TMEM col 0) = X_l [128 x Ka] . W_l^T      (both K-major)
+__device__ __forceinline__ void issue_forward(const TcArgs& a, int l, uint32_t smem_base, uint32_t tmem, uint32_t x_off) {
+  const TcLayer& ly = a.layer[l];
+  const uint32_t idesc = make_idesc_f16(128, ly.Np, 0, 0, a.fmt, a.fmt);
+  const uint32_t xa = smem_base + x_off, wa = smem_base + ly.w_off;
+  for (int k = 0; k < ly.Ka / 16; ++k)
+    mma_f16(tmem, make_desc(xa + k * 2 * kActCs, kActCs, 128), make_desc(wa + k * 2 * ly.w_cs, ly.w_cs, 128), idesc, k > 0);
+}
+
+// hidden-layer epilogue: TMEM accumulator -> ReLU -> 16-bit -> next layer's input tile (+ bias column)
+template <int FMT>
+__device__ __forceinline__ void hidden_epilogue(uint32_t tmem_row, int Np, int N, int relu, int Ka_next,
+                                                unsigned char* dst) {
+  const int r = threadIdx.x;
+  for (int c0 = 0; c0 < Ka_next; c0 += 16) {
+    float v[16];
+    if (c0 < Np) {
+      tmem_ld16(tmem_row + c0, v);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) v[j] = 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      int n = c0 + j;
+      v[j] = n < N ? (relu ? fmaxf(v[j], 0.f) : v[j]) : (n == N ? 1.f : 0.f);
+    }
+    uint4 lo = make_uint4(pack2<FMT>(v[0], v[1]), pack2<FMT>(v[2], v[3]), pack2<FMT>(v[4], v[5]), pack2<FMT>(v[6], v[7]));
+    uint4 hi = make_uint4(pack2<FMT>(v[8], v[9]), pack2<FMT>(v[10], v[11]), pack2<FMT>(v[12], v[13]), pack2<FMT>(v[14], v[15]));
+    *reinterpret_cast<uint4*>(dst + (c0 >> 3) * kActCs + r * 16) = lo;
+    *reinterpret_cast<uint4*>(dst + ((c0 >> 3) + 1) * kActCs + r * 16) = hi;
+  }
+}
+
+struct Ctx {
+  uint64_t bar;
+  uint32_t tmem_base;
+};
+
+template <int FMT>
+__global__ void __launch_bounds__(kThreads) mlp_tc_fwd_kernel(const TcArgs a) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  __shared__ Ctx ctx;
+  stage_weights<FMT>(a, smem);
+  if (threadIdx.x == 0) {
+    mbar_init(&ctx.bar, 1);
+    mbar_fence_init();
+  }
+  if (threadIdx.x < 32) tmem_alloc(&ctx.tmem_base, a.tmem_cols);
+  fence_proxy_async();
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = ctx.tmem_base;
+  const uint32_t tmem_row = tmem + ((uint32_t)(threadIdx.x & ~31) << 16);
+  const uint32_t smem_base = smem_u32(smem);
+  uint32_t phase = 0;
+  const int64_t ntiles = (a.N + kTile - 1) / kTile;
+  const TcLayer& last = a.layer[a.nl - 1];
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int64_t row0 = tile * kTile;
+    uint32_t cur = a.layer[0].x_off, nxt = a.x_off1;
+    load_input_tile<FMT>(a.x, row0, a.N, a.layer[0].K, a.layer[0].Ka, smem + cur);
+    for (int l = 0; l < a.nl; ++l) {
+      fence_proxy_async();
+      fence_before_sync();
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        fence_after_sync();
+        issue_forward(a, l, smem_base, tmem, cur);
+        commit(&ctx.bar);
+      }
+      mbar_wait(&ctx.bar, phase);
+      phase ^= 1;
+      fence_after_sync();
+      if (l + 1 < a.nl) {
+        hidden_epilogue<FMT>(tmem_row, a.layer[l].Np, a.layer[l].N, a.layer[l].relu, a.layer[l + 1].Ka, smem + nxt);
+        uint32_t t = cur;
+        cur = nxt;
+        nxt = t;
+      }
+    }
+    // output layer: activation and store, one row per thread
+    const int64_t row = row0 + threadIdx.x;
+    const bool live = row < a.N;
+    float sel = 1.f;
+    if (a.selector && live) sel = a.selector[row];
+    float* yo = a.y + row * last.N;
+    for (int c0 = 0; c0 < last.Np; c0 += 16) {
+      float v[16];
+      tmem_ld16(tmem_row + c0, v);
+      if (live) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          if (c0 + j < last.N) yo[c0 + j] = apply_out_act(a.out_act, c0 + j, v[j], sel);
+      }
+    }
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (threadIdx.x < 32) tmem_dealloc(tmem, a.tmem_cols);
+}
+
+template <int FMT>
+__global__ void __launch_bounds__(kThreads) mlp_tc_bwd_kernel(const TcArgs a) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  __shared__ Ctx ctx;
+  stage_weights<FMT>(a, smem);
+  if (threadIdx.x == 0) {
+    mbar_init(&ctx.bar, 1);
+    mbar_fence_init();
+  }
+  if (threadIdx.x < 32) tmem_alloc(&ctx.tmem_base, a.tmem_cols);
+  fence_proxy_async();
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = ctx.tmem_base;
+  const uint32_t tmem_row = tmem + ((uint32_t)(threadIdx.x & ~31) << 16);
+  const uint32_t smem_base = smem_u32(smem);
+  const int r = threadIdx.x;
+  uint32_t phase = 0;
+  const int64_t ntiles = (a.N + kTile - 1) / kTile;
+  const TcLayer& last = a.layer[a.nl - 1];
+  bool first_tile = true;
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int64_t row0 = tile * kTile;
+    load_input_tile<FMT>(a.x, row0, a.N, a.layer[0].K, a.layer[0].Ka, smem + a.layer[0].x_off);
+    // ---- forward recompute, every layer input kept ----
+    for (int l = 0; l < a.nl; ++l) {
+      fence_proxy_async();
+      fence_before_sync();
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        fence_after_sync();
+        issue_forward(a, l, smem_base, tmem, a.layer[l].x_off);
+        commit(&ctx.bar);
+      }
+      mbar_wait(&ctx.bar, phase);
+      phase ^= 1;
+      fence_after_sync();
+      if (l + 1 < a.nl) hidden_epilogue<FMT>(tmem_row, a.layer[l].Np, a.layer[l].N, a.layer[l].relu, a.layer[l + 1].Ka,
+                                              smem + a.layer[l + 1].x_off);
+    }
+    // ---- gradient w.r.t. the raw outputs -> G tile (64 features wide, zero padded) ----
+    {
+      const int64_t row = row0 + r;
+      const bool live = row < a.N;
+      float sel = 1.f;
+      if (a.selector && live) sel = a.selector[row];
+      const float* dyr = a.dy + row * last.N;
+      unsigned char* g = smem + a.g_off;
+      for (int c0 = 0; c0 < kMaxWidth; c0 += 16) {
+        float v[16];
+        if (c0 < last.Np) {
+          tmem_ld16(tmem_row + c0, v);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          int n = c0 + j;
+          float d = 0.f;
+          if (live && n < last.N) d = out_act_grad(a.out_act, n, v[j], sel, __ldg(dyr + n));
+          v[j] = d;
+        }
+        uint4 lo = make_uint4(pack2<FMT>(v[0], v[1]), pack2<FMT>(v[2], v[3]), pack2<FMT>(v[4], v[5]), pack2<FMT>(v[6], v[7]));
+        uint4 hi = make_uint4(pack2<FMT>(v[8], v[9]), pack2<FMT>(v[10], v[11]), pack2<FMT>(v[12], v[13]), pack2<FMT>(v[14], v[15]));
+        *reinterpret_cast<uint4*>(g + (c0 >> 3) * kActCs + r * 16) = lo;
+        *reinterpret_cast<uint4*>(g + ((c0 >> 3) + 1) * kActCs + r * 16) = hi;
+      }
+    }
+    // ---- backward sweep ----
+    uint32_t g_off = a.g_off;
+    for (int l = a.nl - 1; l >= 0; --l) {
+      const TcLayer& ly = a.layer[l];
+      const bool need_dx = (l > 0) || (a.dx != nullptr);
+      const int Nx = (ly.K + 15) & ~15;  // columns of dX computed
+      fence_proxy_async();
+      fence_before_sync();
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        fence_after_sync();
+        const uint32_t ga = smem_base + g_off, xa = smem_base + ly.x_off, wa = smem_base + ly.w_off;
+        // dW_l (M=64 features of dY) += G^T . [X_l | 1]   : contraction over the 128 samples
+        const uint32_t id_w = make_idesc_f16(64, ly.Ka, 1, 1, a.fmt, a.fmt);
+        for (int k = 0; k < kTile / 16; ++k)
+          mma_f16(tmem + ly.dw_col, make_desc(ga + k * 256, 128, kActCs), make_desc(xa + k * 256, 128, kActCs), id_w,
+                  (!first_tile) || k > 0);
+        if (need_dx) {
+          // dX_l [128 x Nx] = G [128 x Np] . W_l   (W_l viewed MN-major: contraction over its rows)
+          const uint32_t id_x = make_idesc_f16(128, Nx, 0, 1, a.fmt, a.fmt);
+          for (int k = 0; k < ly.Np / 16; ++k)
+            mma_f16(tmem, make_desc(ga + k * 2 * kActCs, kActCs, 128), make_desc(wa + k * 256, 128, ly.w_cs), id_x, k > 0);
+        }
+        commit(&ctx.bar);
+      }
+      mbar_wait(&ctx.bar, phase);
+      phase ^= 1;
+      fence_after_sync();
+      if (l > 0) {
+        // dY_{l-1} = dX_l * relu'(X_l), written in place over X_l (its MMAs have completed); 64 columns wide
+        unsigned char* xt = smem + ly.x_off;
+        const bool masked = a.layer[l - 1].relu != 0;
+        for (int c0 = 0; c0 < kMaxWidth; c0 += 16) {
+          float v[16];
+          if (c0 < Nx) {
+            tmem_ld16(tmem_row + c0, v);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = 0.f;
+          }
+          uint4* p0 = reinterpret_cast<uint4*>(xt + (c0 >> 3) * kActCs + r * 16);
+          uint4* p1 = reinterpret_cast<uint4*>(xt + ((c0 >> 3) + 1) * kActCs + r * 16);
+          uint4 m0 = make_uint4(0, 0, 0, 0), m1 = make_uint4(0, 0, 0, 0);
+          if (c0 < ly.Ka) {
+            m0 = *p0;
+            m1 = *p1;
+          }
+          const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            // stored activation > 0  <=>  16-bit pattern is positive and non-zero (sign bit clear, magnitude != 0)
+            uint32_t h = (mw[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
+            bool pos = !masked || ((h != 0u) && ((h & 0x8000u) == 0u));
+            if (!(pos && (c0 + j) < ly.K)) v[j] = 0.f;
+          }
+          *p0 = make_uint4(pack2<FMT>(v[0], v[1]), pack2<FMT>(v[2], v[3]), pack2<FMT>(v[4], v[5]), pack2<FMT>(v[6], v[7]));
+          *p1 = make_uint4(pack2<FMT>(v[8], v[9]), pack2<FMT>(v[10], v[11]), pack2<FMT>(v[12], v[13]), pack2<FMT>(v[14], v[15]));
+        }
+        g_off = ly.x_off;
+      } else if (a.dx) {
+        const int64_t row = row0 + r;
+        float* dxr = a.dx + row * ly.K;
+        for (int c0 = 0; c0 < Nx; c0 += 16) {
+          float v[16];
+          tmem_ld16(tmem_row + c0, v);
+          if (row < a.N) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (c0 + j < ly.K) dxr[c0 + j] = v[j];
+          }
+        }
+      }
+    }
+    first_tile = false;
+  }
+  // ---- flush the weight / bias gradients: M=64 accumulator rows live in lanes 0..15 of every warp ----
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  if (!first_tile) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int n = 16 * w + lane;
+    for (int l = 0; l < a.nl; ++l) {
+      const TcLayer& ly = a.layer[l];
+      for (int c0 = 0; c0 < ly.Ka; c0 += 16) {
+        float v[16];
+        tmem_ld16(tmem_row + ly.dw_col + c0, v);
+        if (lane < 16 && n < ly.N) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            int k = c0 + j;
+            if (k < ly.K) atomicAdd(ly.dW + (size_t)n * ly.K + k, v[j]);
+            else if (k == ly.K) atomicAdd(ly.db + n, v[j]);
+          }
+        }
+      }
+    }
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (threadIdx.x < 32) tmem_dealloc(tmem, a.tmem_cols);
+}
+
+int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+int build_args(TcArgs& a, bool backward, int nl, const int32_t* dims, const float* const* W, const float* const* b,
+               int relu_mask, int out_act, int fmt, const char* who) {
+  NKBS_CHECK_ARG(nl >= 1 && nl <= kMaxLayers, "%s: 1..%d linear layers supported (got %d)", who, kMaxLayers, nl);
+  NKBS_CHECK_ARG(out_act >= 0 && out_act <= 3, "%s: unknown output activation %d", who, out_act);
+  NKBS_CHECK_ARG(fmt == 0 || fmt == 1, "%s: fmt must be 0 (fp16) or 1 (bf16)", who);
+  for (int l = 0; l <= nl; ++l)
+    NKBS_CHECK_ARG(dims[l] >= 1 && dims[l] <= kMaxWidth, "%s: layer width %d outside 1..%d", who, dims[l], kMaxWidth);
+  int off = 0, max_ka = 0;
+  for (int l = 0; l < nl; ++l) {
+    TcLayer& ly = a.layer[l];
+    NKBS_CHECK_ARG(W[l] && b[l], "%s: null weight/bias for layer %d", who, l);
+    ly.W = W[l];
+    ly.b = b[l];
+    ly.dW = nullptr;
+    ly.db = nullptr;
+    ly.K = dims[l];
+    ly.N = dims[l + 1];
+    ly.relu = (relu_mask >> l) & 1;
+    ly.Ka = round_up(ly.K + 1, 16);
+    ly.Np = round_up(ly.N, 16);
+    ly.w_cs = ly.Np * 16 + 16;
+    ly.w_off = off;
+    off += (ly.Ka / 8) * ly.w_cs;
+    off = round_up(off, 128);
+    if (ly.Ka > max_ka) max_ka = ly.Ka;
+  }
+  a.nl = nl;
+  a.out_act = out_act;
+  a.fmt = fmt;
+  int cols = kMaxWidth;  // work accumulator (forward outputs / dX)
+  if (!backward) {
+    int tile_bytes = round_up((max_ka / 8) * kActCs, 128);
+    a.layer[0].x_off = off;
+    a.x_off1 = off + tile_bytes;
+    off += 2 * tile_bytes;
+    a.g_off = 0;
+  } else {
+    for (int l = 0; l < nl; ++l) {
+      TcLayer& ly = a.layer[l];
+      int width = ly.Ka > kMaxWidth ? ly.Ka : kMaxWidth;  // later reused as a 64-wide gradient tile
+      ly.x_off = off;
+      off += round_up((width / 8) * kActCs, 128);
+      ly.dw_col = cols;
+      cols += ly.Ka;
+    }
+    a.g_off = off;
+    off += round_up((kMaxWidth / 8) * kActCs, 128);
+    a.x_off1 = 0;
+  }
+  int tc = 32;
+  while (tc < cols) tc <<= 1;
+  NKBS_CHECK_ARG(tc <= 512, "%s: needs %d TMEM columns", who, cols);
+  a.tmem_cols = tc;
+  a.smem_bytes = off;
+  NKBS_CHECK_ARG(off <= 227 * 1024, "%s: needs %d bytes of shared memory", who, off);
+  return 0;
+}
+
+template <typename K>
+int set_smem(K kernel, int bytes, const char* who) {
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  NKBS_CHECK_ARG(e == cudaSuccess, "%s: %d bytes of shared memory refused: %s", who, bytes, cudaGetErrorString(e));
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int nkbs_mlp_tc_fwd(const float* x, int64_t N, int32_t nl, const int32_t* dims, const float* const* W,
+                               const float* const* b, int32_t relu_mask, int32_t out_act, int32_t fmt,
+                               const float* selector, float* y, void* stream) {
+  TcArgs a;
+  if (build_args(a, false, nl, dims, W, b, relu_mask, out_act, fmt, "nkbs_mlp_tc_fwd")) return -1;
+  NKBS_CHECK_ARG(N >= 0, "nkbs_mlp_tc_fwd: negative N");
+  if (N == 0) return 0;
+  NKBS_CHECK_ARG(x && y, "nkbs_mlp_tc_fwd: null x/y");
+  a.x = x;
+  a.y = y;
+  a.selector = selector;
+  a.dy = nullptr;
+  a.dx = nullptr;
+  a.N = N;
+  int64_t ntiles = (N + kTile - 1) / kTile;
+  int per_sm = 227 * 1024 / (a.smem_bytes + 1024);
+  int by_tmem = 512 / a.tmem_cols;
+  if (per_sm > by_tmem) per_sm = by_tmem;
+  if (per_sm < 1) per_sm = 1;
+  if (per_sm > 4) per_sm = 4;
+  int64_t cap = (int64_t)nkbs_num_sms() * per_sm;
+  int grid = (int)(ntiles < cap ? ntiles : cap);
+  if (fmt == 0) {
+    if (set_smem(mlp_tc_fwd_kernel<0>, a.smem_bytes, "nkbs_mlp_tc_fwd")) return -1;
+    mlp_tc_fwd_kernel<0><<<grid, kThreads, a.smem_bytes, (cudaStream_t)stream>>>(a);
+  } else {
+    if (set_smem(mlp_tc_fwd_kernel<1>, a.smem_bytes, "nkbs_mlp_tc_fwd")) return -1;
+    mlp_tc_fwd_kernel<1><<<grid, kThreads, a.smem_bytes, (cudaStream_t)stream>>>(a);
+  }
+  NKBS_CHECK_LAUNCH("nkbs_mlp_tc_fwd");
+  return 0;
+}
+
+extern "C" int nkbs_mlp_tc_bwd(const float* x, const float* dy, int64_t N, int32_t nl, const int32_t* dims,
+                               const float* const* W, const float* const* b, int32_t relu_mask, int32_t out_act,
+                               int32_t fmt, const float* selector, float* dx, float* const* dW, float* const* db, void* stream) {
+  TcArgs a;
+  if (build_args(a, true, nl, dims, W, b, relu_mask, out_act, fmt, "nkbs_mlp_tc_bwd")) return -1;
+  NKBS_CHECK_ARG(N >= 0, "nkbs_mlp_tc_bwd: negative N");
+  if (N == 0) return 0;
+  NKBS_CHECK_ARG(x && dy, "nkbs_mlp_tc_bwd: null x/dy");
+  for (int l = 0; l < nl; ++l) {
+    NKBS_CHECK_ARG(dW[l] && db[l], "nkbs_mlp_tc_bwd: null dW/db for layer %d", l);
+    a.layer[l].dW = dW[l];
+    a.layer[l].db = db[l];
+  }
+  a.x = x;
+  a.y = nullptr;
+  a.selector = selector;
+  a.dy = dy;
+  a.dx = dx;
+  a.N = N;
+  int64_t ntiles = (N + kTile - 1) / kTile;
+  int per_sm = 227 * 1024 / (a.smem_bytes + 1024);
+  int by_tmem = 512 / a.tmem_cols;
+  if (per_sm > by_tmem) per_sm = by_tmem;
+  if (per_sm < 1) per_sm = 1;
+  if (per_sm > 4) per_sm = 4;
+  int64_t cap = (int64_t)nkbs_num_sms() * per_sm;
+  int grid = (int)(ntiles < cap ? ntiles : cap);
+  if (fmt == 0) {
+    if (set_smem(mlp_tc_bwd_kernel<0>, a.smem_bytes, "nkbs_mlp_tc_bwd")) return -1;
+    mlp_tc_bwd_kernel<0><<<grid, kThreads, a.smem_bytes, (cudaStream_t)stream>>>(a);
+  } else {
+    if (set_smem(mlp_tc_bwd_kernel<1>, a.smem_bytes, "nkbs_mlp_tc_bwd")) return -1;
+    mlp_tc_bwd_kernel<1><<<grid, kThreads, a.smem_bytes, (cudaStream_t)stream>>>(a);
+  }
+  NKBS_CHECK_LAUNCH("nkbs_mlp_tc_bwd");
+  return 0;
+}

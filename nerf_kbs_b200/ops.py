@@ -119,6 +119,23 @@ def contract_encode(table, grid: GridSpec, norm: NormSpec, positions=None, origi
 # ----------------------------------------------------------------------------------------------
 # K3 fused MLP (fp32 CUDA-core path)
 # ----------------------------------------------------------------------------------------------
+# "fp32": CUDA-core kernels (parity 1e-4).  "tc": tcgen05 tensor cores, 16-bit operands, fp32 accumulate
+# (parity 1e-2; what the reference's autocast training does, ref:train.py:50).
+FMT_FP16, FMT_BF16 = 0, 1
+_MLP_CFG = {"precision": "tc", "fwd_fmt": FMT_FP16, "bwd_fmt": FMT_BF16}
+
+
+def set_mlp_precision(precision: str, fwd_fmt: int = FMT_FP16, bwd_fmt: int = FMT_BF16) -> None:
+    """Select the MLP kernels: ``"fp32"`` (CUDA cores) or ``"tc"`` (tensor cores; operand formats per pass)."""
+    if precision not in ("fp32", "tc"):
+        raise ValueError("precision must be 'fp32' or 'tc'")
+    _MLP_CFG.update(precision=precision, fwd_fmt=int(fwd_fmt), bwd_fmt=int(bwd_fmt))
+
+
+def get_mlp_precision() -> str:
+    return _MLP_CFG["precision"]
+
+
 class _Mlp(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, selector, relu_mask, out_act, *params):
@@ -130,15 +147,20 @@ class _Mlp(torch.autograd.Function):
         dims = [Ws[0].shape[1]] + [w.shape[0] for w in Ws]
         N = x.shape[0]
         y = torch.empty((N, dims[-1]), device=x.device, dtype=torch.float32)
-        call("nkbs_mlp_fwd", ptr(x), N, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask, out_act,
-             ptr(selector), ptr(y), stream())
-        ctx.cfg = (nl, dims, relu_mask, out_act)
+        tc = _MLP_CFG["precision"] == "tc"
+        if tc:
+            call("nkbs_mlp_tc_fwd", ptr(x), N, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask, out_act,
+                 _MLP_CFG["fwd_fmt"], ptr(selector), ptr(y), stream())
+        else:
+            call("nkbs_mlp_fwd", ptr(x), N, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask, out_act,
+                 ptr(selector), ptr(y), stream())
+        ctx.cfg = (nl, dims, relu_mask, out_act, tc, _MLP_CFG["bwd_fmt"])
         ctx.save_for_backward(x, selector, *Ws, *bs)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        nl, dims, relu_mask, out_act = ctx.cfg
+        nl, dims, relu_mask, out_act, tc, bwd_fmt = ctx.cfg
         saved = ctx.saved_tensors
         x, selector = saved[0], saved[1]
         Ws, bs = list(saved[2:2 + nl]), list(saved[2 + nl:2 + 2 * nl])
@@ -147,8 +169,12 @@ class _Mlp(torch.autograd.Function):
         dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
         dWs = [torch.zeros_like(w) for w in Ws]
         dbs = [torch.zeros_like(b) for b in bs]
-        call("nkbs_mlp_bwd", ptr(x), ptr(dy), N, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask,
-             out_act, ptr(selector), ptr(dx), host_ptrs(dWs), host_ptrs(dbs), stream())
+        if tc:
+            call("nkbs_mlp_tc_bwd", ptr(x), ptr(dy), N, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask,
+                 out_act, bwd_fmt, ptr(selector), ptr(dx), host_ptrs(dWs), host_ptrs(dbs), stream())
+        else:
+            call("nkbs_mlp_bwd", ptr(x), ptr(dy), N, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask,
+                 out_act, ptr(selector), ptr(dx), host_ptrs(dWs), host_ptrs(dbs), stream())
         grads = []
         for w, b in zip(dWs, dbs):
             grads += [w, b]

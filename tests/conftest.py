@@ -20,3 +20,12 @@ def pytest_collection_modifyitems(config, items):
     for item in items:
         if "gpu" in item.keywords:
             item.add_marker(skip)
+
+
+@pytest.fixture(autouse=True)
+def _fp32_mlp_by_default():
+    """Parity tests at the 1e-4 bar run the fp32 CUDA-core MLP; tensor-core tests opt in explicitly."""
+    from nerf_kbs_b200 import ops
+    ops.set_mlp_precision("fp32")
+    yield
+    ops.set_mlp_precision("tc")

