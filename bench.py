@@ -42,6 +42,7 @@ def parse_args():
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of one CUDA graph per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernel-pass", action="store_true")
+    ap.add_argument("--fp32-mlp", action="store_true", help="CUDA-core fp32 MLP kernels instead of the tcgen05 path")
     ap.add_argument("--pool", type=int, default=8, help="distinct ray batches cycled through")
     return ap.parse_args()
 
@@ -147,7 +148,7 @@ def kernel_work(name, a):
     if name == "nkbs_encode_bwd":
         N, L, F = a[2], a[4], a[6]
         return "hbm", N * (12 + 4 * L * F + 8 * L * F * 4)
-    if name in ("nkbs_mlp_fwd", "nkbs_mlp_bwd"):
+    if name in ("nkbs_mlp_fwd", "nkbs_mlp_bwd", "nkbs_mlp_tc_fwd", "nkbs_mlp_tc_bwd"):
         fwd = name.endswith("fwd")
         N, nl = (a[1], a[2]) if fwd else (a[2], a[3])
         dims = i32s(a[3] if fwd else a[4], nl + 1)
@@ -295,6 +296,8 @@ def run_nkbs(args):
     from nerf_kbs_b200.rays import RayBundle
     from nerf_kbs_b200.trainer import Trainer
 
+    from nerf_kbs_b200 import ops as nk_ops
+    nk_ops.set_mlp_precision("fp32" if args.fp32_mlp else "tc")
     torch.manual_seed(0)  # identical parameters on every rank
     if args.model == "nerfacto":
         model = nk.NerfactoModel(nk.ModelConfig()).to(dev).train()
@@ -407,7 +410,8 @@ def run_nkbs(args):
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": W,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic",
+        "dtype": "f16/bf16 tensor-core MLPs (fp32 accumulate), f32 elsewhere" if not args.fp32_mlp else "f32",
+        "data": "synthetic",
         "config": {"workload": workload_name(args), "rays_per_gpu": R, "global_rays_per_step": world * R,
                    "samples_per_ray": list(SAMPLES), "parallelism": f"dp{world}", "cuda_graph": not args.no_graph,
                    "l2": f"no flush: the step's working set (parameters + gradients + Adam moments = {working_set / 2**20:.0f} MiB, "

@@ -102,4 +102,6 @@ def test_training_loop_tracks_oracle():
             o.step()
         nm.after_step(step)
         assert abs(ln.item() - lo.item()) <= 1e-3 * abs(lo.item()), (step, ln.item(), lo.item())
-    assert rel_err(nm.field.mlp_head.layers[0].weight, om.field.mlp_head.layers[0].weight) < 1e-2
+    # Adam normalises every gradient entry to a step of about lr: entries whose gradient is rounding noise move
+    # by +-lr in either run, so the weights are compared loosely
+    assert rel_err(nm.field.mlp_head.layers[0].weight, om.field.mlp_head.layers[0].weight) < 5e-2
