@@ -1,6 +1,9 @@
 // K3 (tensor-core path): fused small MLP, forward and backward, on tcgen05 tensor cores.
 //
-// One CTA (128 threads, thread t <-> sample row t <-> TMEM lane t) walks over 128-sample tiles.  Weights of
+// A CTA is nwg epilogue warpgroups (128 threads each: thread t <-> sample row t <-> TMEM lane t of the tile the
+// warpgroup currently owns) plus one issuer warp whose elected lane issues every tcgen05.mma of the CTA.  The
+// warpgroups and the issuer talk through mbarriers only (operands ready -> MMA batch -> tcgen05.commit), so the
+// tensor pipe works on one warpgroup's tile while the others run their epilogues.  Weights of
 // every layer stay in shared memory for the whole kernel as 16-bit UMMA operand tiles; activations bounce
 // TMEM -> registers (bias is folded into the GEMM through a constant-one input column, ReLU and the 16-bit
 // conversion happen in registers) -> shared memory, where they are the A operand of the next layer.
@@ -56,8 +59,11 @@ struct TcArgs {
   int out_act;
   int fmt;                // 0 fp16, 1 bf16
   int64_t N;
-  int x_off1;             // forward: second ping-pong activation buffer
-  int g_off;              // backward: gradient tile (64 features wide)
+  int x_off1;             // forward: second ping-pong activation buffer   (offsets x_off/x_off1/g_off are
+  int g_off;              // backward: gradient tile (64 features wide)    relative to the warpgroup's region)
+  int wg_base;            // byte offset of warpgroup 0's activation region
+  int wg_stride;          // bytes per warpgroup region
+  int nwg;                // epilogue warpgroups per CTA (each owns one 128-sample tile at a time)
   int tmem_cols;          // power of two >= 32
   int smem_bytes;
 };
@@ -87,7 +93,7 @@ __device__ void stage_weights(const TcArgs& a, unsigned char* smem) {
     const TcLayer& ly = a.layer[l];
     unsigned char* wt = smem + ly.w_off;
     const int total = ly.Np * ly.Ka;
-    for (int e = threadIdx.x; e < total; e += kThreads) {
+    for (int e = threadIdx.x; e < total; e += blockDim.x) {
       int n = e / ly.Ka, k = e - n * ly.Ka;
       float v = 0.f;
       if (n < ly.N) {
@@ -102,14 +108,14 @@ __device__ void stage_weights(const TcArgs& a, unsigned char* smem) {
 // global x[row0 .. row0+127, 0..K) fp32 -> X0 tile (16-bit), column K = 1, columns K+1..Ka-1 = 0
 template <int FMT>
 __device__ void load_input_tile(const float* __restrict__ x, int64_t row0, int64_t rows_total, int K, int Ka,
-                                unsigned char* tile) {
+                                unsigned char* tile, int tid) {
   int64_t rows = rows_total - row0;
   if (rows > kTile) rows = kTile;
   const float* src = x + row0 * K;
   const int valid = (int)rows * K;
   const int total = kTile * K;
   if ((K & 3) == 0 && ((reinterpret_cast<uintptr_t>(src) & 15) == 0)) {
-    for (int e = threadIdx.x * 4; e < total; e += kThreads * 4) {
+    for (int e = tid * 4; e < total; e += kThreads * 4) {
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
       if (e < valid) v = __ldg(reinterpret_cast<const float4*>(src + e));
       int r = e / K, k = e - r * K;
@@ -117,13 +123,13 @@ __device__ void load_input_tile(const float* __restrict__ x, int64_t row0, int64
       *reinterpret_cast<uint2*>(tile + tile_off(r, k, kActCs)) = p;
     }
   } else {
-    for (int e = threadIdx.x; e < total; e += kThreads) {
+    for (int e = tid; e < total; e += kThreads) {
       float v = e < valid ? __ldg(src + e) : 0.f;
       int r = e / K, k = e - r * K;
       *reinterpret_cast<uint16_t*>(tile + tile_off(r, k, kActCs)) = cvt16<FMT>(v);
     }
   }
-  const int r = threadIdx.x;
+  const int r = tid;
   for (int k = K; k < Ka; ++k)
     *reinterpret_cast<uint16_t*>(tile + tile_off(r, k, kActCs)) = cvt16<FMT>(k == K ? 1.f : 0.f);
 }
@@ -154,20 +160,23 @@ __device__ __forceinline__ float out_act_grad(int act, int n, float raw, float s
   }
 }
 
-// D[128 x Np] (TMEM col 0) = X_l [128 x Ka] . W_l^T      (both K-major)
-__device__ __forceinline__ void issue_forward(const TcArgs& a, int l, uint32_t smem_base, uint32_t tmem, uint32_t x_off) {
+// D[128 x Np] = X_l [128 x Ka] . W_l^T      (both K-major).  Warp-uniform: see mma_f16_uniform.
+__device__ __forceinline__ void issue_forward(const TcArgs& a, int l, uint32_t smem_base, uint32_t tmem, uint32_t xa,
+                                              uint32_t leader) {
   const TcLayer& ly = a.layer[l];
   const uint32_t idesc = make_idesc_f16(128, ly.Np, 0, 0, a.fmt, a.fmt);
-  const uint32_t xa = smem_base + x_off, wa = smem_base + ly.w_off;
-  for (int k = 0; k < ly.Ka / 16; ++k)
-    mma_f16(tmem, make_desc(xa + k * 2 * kActCs, kActCs, 128), make_desc(wa + k * 2 * ly.w_cs, ly.w_cs, 128), idesc, k > 0);
+  const uint64_t da = make_desc(xa, kActCs, 128), db = make_desc(smem_base + ly.w_off, ly.w_cs, 128);
+  const uint32_t sa = (2 * kActCs) >> 4, sb = (2 * ly.w_cs) >> 4;  // descriptor start-address steps per K=16
+  const int nk = ly.Ka >> 4;
+#pragma unroll
+  for (int k = 0; k < (kMaxWidth + 16) / 16; ++k)
+    if (k < nk) mma_f16_uniform(tmem, da + (uint64_t)(k * sa), db + (uint64_t)(k * sb), idesc, k > 0, leader);
 }
 
 // hidden-layer epilogue: TMEM accumulator -> ReLU -> 16-bit -> next layer's input tile (+ bias column)
 template <int FMT>
 __device__ __forceinline__ void hidden_epilogue(uint32_t tmem_row, int Np, int N, int relu, int Ka_next,
-                                                unsigned char* dst) {
-  const int r = threadIdx.x;
+                                                unsigned char* dst, int r) {
   for (int c0 = 0; c0 < Ka_next; c0 += 16) {
     float v[16];
     if (c0 < Np) {
@@ -188,232 +197,351 @@ __device__ __forceinline__ void hidden_epilogue(uint32_t tmem_row, int Np, int N
   }
 }
 
-struct Ctx {
-  uint64_t bar;
+
+struct Sh {
+  uint64_t ready[4];  // warpgroup g: operand tiles of its next MMA batch are written   (128 arrivals)
+  uint64_t done[4];   // issuer: that batch has completed (tcgen05.commit)
   uint32_t tmem_base;
 };
 
-template <int FMT>
-__global__ void __launch_bounds__(kThreads) mlp_tc_fwd_kernel(const TcArgs a) {
-  extern __shared__ __align__(128) unsigned char smem[];
-  __shared__ Ctx ctx;
-  stage_weights<FMT>(a, smem);
-  if (threadIdx.x == 0) {
-    mbar_init(&ctx.bar, 1);
-    mbar_fence_init();
-  }
-  if (threadIdx.x < 32) tmem_alloc(&ctx.tmem_base, a.tmem_cols);
-  fence_proxy_async();
-  fence_before_sync();
-  __syncthreads();
-  fence_after_sync();
-  const uint32_t tmem = ctx.tmem_base;
-  const uint32_t tmem_row = tmem + ((uint32_t)(threadIdx.x & ~31) << 16);
-  const uint32_t smem_base = smem_u32(smem);
-  uint32_t phase = 0;
-  const int64_t ntiles = (a.N + kTile - 1) / kTile;
-  const TcLayer& last = a.layer[a.nl - 1];
-  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    const int64_t row0 = tile * kTile;
-    uint32_t cur = a.layer[0].x_off, nxt = a.x_off1;
-    load_input_tile<FMT>(a.x, row0, a.N, a.layer[0].K, a.layer[0].Ka, smem + cur);
-    for (int l = 0; l < a.nl; ++l) {
-      fence_proxy_async();
-      fence_before_sync();
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        fence_after_sync();
-        issue_forward(a, l, smem_base, tmem, cur);
-        commit(&ctx.bar);
-      }
-      mbar_wait(&ctx.bar, phase);
-      phase ^= 1;
-      fence_after_sync();
-      if (l + 1 < a.nl) {
-        hidden_epilogue<FMT>(tmem_row, a.layer[l].Np, a.layer[l].N, a.layer[l].relu, a.layer[l + 1].Ka, smem + nxt);
-        uint32_t t = cur;
-        cur = nxt;
-        nxt = t;
-      }
-    }
-    // output layer: activation and store, one row per thread
-    const int64_t row = row0 + threadIdx.x;
-    const bool live = row < a.N;
-    float sel = 1.f;
-    if (a.selector && live) sel = a.selector[row];
-    float* yo = a.y + row * last.N;
-    for (int c0 = 0; c0 < last.Np; c0 += 16) {
-      float v[16];
-      tmem_ld16(tmem_row + c0, v);
-      if (live) {
+__device__ __forceinline__ int64_t tile_of(int i, int wg, int nwg) {
+  return ((int64_t)i * gridDim.x + blockIdx.x) * nwg + wg;
+}
+
+// ---- input tile through registers: the loads of tile i+1 are in flight while tile i is processed ----
+__device__ __forceinline__ void x_prefetch(float4 xr[16], const float* __restrict__ x, int64_t row0, int64_t rows_total,
+                                           int K, int tid) {
+  int64_t rows = rows_total - row0;
+  if (rows > kTile) rows = kTile;
+  const float* src = x + row0 * K;
+  const int valid = (int)rows * K;
+  const int nvec = K >> 2;
 #pragma unroll
-        for (int j = 0; j < 16; ++j)
-          if (c0 + j < last.N) yo[c0 + j] = apply_out_act(a.out_act, c0 + j, v[j], sel);
-      }
-    }
+  for (int j = 0; j < 16; ++j) {
+    const int e = 4 * (tid + kThreads * j);
+    xr[j] = (j < nvec && e < valid) ? __ldg(reinterpret_cast<const float4*>(src + e)) : make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  fence_before_sync();
-  __syncthreads();
-  if (threadIdx.x < 32) tmem_dealloc(tmem, a.tmem_cols);
 }
 
 template <int FMT>
-__global__ void __launch_bounds__(kThreads) mlp_tc_bwd_kernel(const TcArgs a) {
+__device__ __forceinline__ void x_commit(const float4 xr[16], int K, int kshift, int Ka, unsigned char* tile, int tid) {
+  const int nvec = K >> 2;
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    if (j < nvec) {
+      const int e = 4 * (tid + kThreads * j);
+      const int r = kshift >= 0 ? (e >> kshift) : (e / K);
+      const int k = e - r * K;
+      *reinterpret_cast<uint2*>(tile + tile_off(r, k, kActCs)) =
+          make_uint2(pack2<FMT>(xr[j].x, xr[j].y), pack2<FMT>(xr[j].z, xr[j].w));
+    }
+  }
+  for (int k = K; k < Ka; ++k)
+    *reinterpret_cast<uint16_t*>(tile + tile_off(tid, k, kActCs)) = cvt16<FMT>(k == K ? 1.f : 0.f);
+}
+
+// warpgroup side of one MMA batch: publish the operand tiles, then wait for the batch to complete
+__device__ __forceinline__ void wg_round(Sh& sh, int wg, uint32_t& phase) {
+  fence_proxy_async();   // st.shared of the operand tiles -> visible to the tensor core's async proxy
+  fence_before_sync();   // earlier tcgen05.ld of this thread are ordered before the batch that overwrites TMEM
+  mbar_arrive(&sh.ready[wg]);
+  mbar_wait(&sh.done[wg], phase);
+  phase ^= 1;
+  fence_after_sync();
+}
+
+template <int FMT>
+__global__ void __launch_bounds__(4 * kThreads + 32) mlp_tc_fwd_kernel(const TcArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
-  __shared__ Ctx ctx;
+  __shared__ Sh sh;
+  const int nwg = a.nwg;
+  const int wg = threadIdx.x >> 7;
+  const int tid = threadIdx.x & (kThreads - 1);
+  const int lane = threadIdx.x & 31;
+  const bool issuer = wg == nwg;
   stage_weights<FMT>(a, smem);
   if (threadIdx.x == 0) {
-    mbar_init(&ctx.bar, 1);
+    for (int g = 0; g < 4; ++g) {
+      mbar_init(&sh.ready[g], kThreads);
+      mbar_init(&sh.done[g], 1);
+    }
     mbar_fence_init();
   }
-  if (threadIdx.x < 32) tmem_alloc(&ctx.tmem_base, a.tmem_cols);
+  if (issuer) tmem_alloc(&sh.tmem_base, a.tmem_cols);
   fence_proxy_async();
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  const uint32_t tmem = ctx.tmem_base;
-  const uint32_t tmem_row = tmem + ((uint32_t)(threadIdx.x & ~31) << 16);
+  const uint32_t tmem = sh.tmem_base;
   const uint32_t smem_base = smem_u32(smem);
-  const int r = threadIdx.x;
-  uint32_t phase = 0;
   const int64_t ntiles = (a.N + kTile - 1) / kTile;
-  const TcLayer& last = a.layer[a.nl - 1];
-  bool first_tile = true;
-  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    const int64_t row0 = tile * kTile;
-    load_input_tile<FMT>(a.x, row0, a.N, a.layer[0].K, a.layer[0].Ka, smem + a.layer[0].x_off);
-    // ---- forward recompute, every layer input kept ----
-    for (int l = 0; l < a.nl; ++l) {
-      fence_proxy_async();
-      fence_before_sync();
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        fence_after_sync();
-        issue_forward(a, l, smem_base, tmem, a.layer[l].x_off);
-        commit(&ctx.bar);
+  if (issuer) {
+    uint32_t rph = 0;  // bit g: phase of ready[g]
+    const uint32_t leader = lane == 0;
+    for (int i = 0;; ++i) {
+      if (tile_of(i, 0, nwg) >= ntiles) break;
+      for (int l = 0; l < a.nl; ++l) {
+        for (int g = 0; g < nwg; ++g) {
+          if (tile_of(i, g, nwg) >= ntiles) break;
+          mbar_wait(&sh.ready[g], (rph >> g) & 1u);
+          fence_after_sync();
+          const uint32_t base = smem_base + a.wg_base + g * a.wg_stride;
+          issue_forward(a, l, smem_base, tmem + g * kMaxWidth, base + ((l & 1) ? a.x_off1 : a.layer[0].x_off), leader);
+          commit_uniform(&sh.done[g], leader);
+          rph ^= 1u << g;
+          __syncwarp();
+        }
       }
-      mbar_wait(&ctx.bar, phase);
-      phase ^= 1;
-      fence_after_sync();
-      if (l + 1 < a.nl) hidden_epilogue<FMT>(tmem_row, a.layer[l].Np, a.layer[l].N, a.layer[l].relu, a.layer[l + 1].Ka,
-                                              smem + a.layer[l + 1].x_off);
     }
-    // ---- gradient w.r.t. the raw outputs -> G tile (64 features wide, zero padded) ----
-    {
-      const int64_t row = row0 + r;
+  } else {
+    unsigned char* base = smem + a.wg_base + wg * a.wg_stride;
+    const uint32_t tmem_row = tmem + wg * kMaxWidth + ((uint32_t)(tid & ~31) << 16);
+    const TcLayer& last = a.layer[a.nl - 1];
+    const int K0 = a.layer[0].K, Ka0 = a.layer[0].Ka;
+    const bool vec = (K0 & 3) == 0 && (reinterpret_cast<uintptr_t>(a.x) & 15) == 0;
+    const int kshift = (K0 & (K0 - 1)) == 0 ? (31 - __clz(K0)) : -1;
+    uint32_t phase = 0;
+    float4 xr[16];
+    if (vec && tile_of(0, wg, nwg) < ntiles) x_prefetch(xr, a.x, tile_of(0, wg, nwg) * kTile, a.N, K0, tid);
+    for (int i = 0;; ++i) {
+      const int64_t t = tile_of(i, wg, nwg);
+      if (t >= ntiles) break;
+      const int64_t row0 = t * kTile;
+      unsigned char* cur = base + a.layer[0].x_off;
+      unsigned char* nxt = base + a.x_off1;
+      if (vec) {
+        x_commit<FMT>(xr, K0, kshift, Ka0, cur, tid);
+        const int64_t t2 = tile_of(i + 1, wg, nwg);
+        if (t2 < ntiles) x_prefetch(xr, a.x, t2 * kTile, a.N, K0, tid);
+      } else {
+        load_input_tile<FMT>(a.x, row0, a.N, K0, Ka0, cur, tid);
+      }
+      for (int l = 0; l < a.nl; ++l) {
+        wg_round(sh, wg, phase);
+        if (l + 1 < a.nl) {
+          hidden_epilogue<FMT>(tmem_row, a.layer[l].Np, a.layer[l].N, a.layer[l].relu, a.layer[l + 1].Ka, nxt, tid);
+          unsigned char* tmp = cur;
+          cur = nxt;
+          nxt = tmp;
+        }
+      }
+      // output layer: activation and store, one row per thread
+      const int64_t row = row0 + tid;
       const bool live = row < a.N;
       float sel = 1.f;
       if (a.selector && live) sel = a.selector[row];
-      const float* dyr = a.dy + row * last.N;
-      unsigned char* g = smem + a.g_off;
-      for (int c0 = 0; c0 < kMaxWidth; c0 += 16) {
+      float* yo = a.y + row * last.N;
+      for (int c0 = 0; c0 < last.Np; c0 += 16) {
         float v[16];
-        if (c0 < last.Np) {
-          tmem_ld16(tmem_row + c0, v);
-        } else {
+        tmem_ld16(tmem_row + c0, v);
+        if (live) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) v[j] = 0.f;
+          for (int j = 0; j < 16; ++j)
+            if (c0 + j < last.N) yo[c0 + j] = apply_out_act(a.out_act, c0 + j, v[j], sel);
         }
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          int n = c0 + j;
-          float d = 0.f;
-          if (live && n < last.N) d = out_act_grad(a.out_act, n, v[j], sel, __ldg(dyr + n));
-          v[j] = d;
-        }
-        uint4 lo = make_uint4(pack2<FMT>(v[0], v[1]), pack2<FMT>(v[2], v[3]), pack2<FMT>(v[4], v[5]), pack2<FMT>(v[6], v[7]));
-        uint4 hi = make_uint4(pack2<FMT>(v[8], v[9]), pack2<FMT>(v[10], v[11]), pack2<FMT>(v[12], v[13]), pack2<FMT>(v[14], v[15]));
-        *reinterpret_cast<uint4*>(g + (c0 >> 3) * kActCs + r * 16) = lo;
-        *reinterpret_cast<uint4*>(g + ((c0 >> 3) + 1) * kActCs + r * 16) = hi;
       }
     }
-    // ---- backward sweep ----
-    uint32_t g_off = a.g_off;
-    for (int l = a.nl - 1; l >= 0; --l) {
-      const TcLayer& ly = a.layer[l];
-      const bool need_dx = (l > 0) || (a.dx != nullptr);
-      const int Nx = (ly.K + 15) & ~15;  // columns of dX computed
-      fence_proxy_async();
-      fence_before_sync();
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        fence_after_sync();
-        const uint32_t ga = smem_base + g_off, xa = smem_base + ly.x_off, wa = smem_base + ly.w_off;
-        // dW_l (M=64 features of dY) += G^T . [X_l | 1]   : contraction over the 128 samples
-        const uint32_t id_w = make_idesc_f16(64, ly.Ka, 1, 1, a.fmt, a.fmt);
-        for (int k = 0; k < kTile / 16; ++k)
-          mma_f16(tmem + ly.dw_col, make_desc(ga + k * 256, 128, kActCs), make_desc(xa + k * 256, 128, kActCs), id_w,
-                  (!first_tile) || k > 0);
-        if (need_dx) {
-          // dX_l [128 x Nx] = G [128 x Np] . W_l   (W_l viewed MN-major: contraction over its rows)
-          const uint32_t id_x = make_idesc_f16(128, Nx, 0, 1, a.fmt, a.fmt);
-          for (int k = 0; k < ly.Np / 16; ++k)
-            mma_f16(tmem, make_desc(ga + k * 2 * kActCs, kActCs, 128), make_desc(wa + k * 256, 128, ly.w_cs), id_x, k > 0);
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (issuer) tmem_dealloc(tmem, a.tmem_cols);
+}
+
+template <int FMT>
+__global__ void __launch_bounds__(4 * kThreads + 32) mlp_tc_bwd_kernel(const TcArgs a) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  __shared__ Sh sh;
+  const int nwg = a.nwg;
+  const int wg = threadIdx.x >> 7;
+  const int tid = threadIdx.x & (kThreads - 1);
+  const int lane = threadIdx.x & 31;
+  const bool issuer = wg == nwg;
+  stage_weights<FMT>(a, smem);
+  if (threadIdx.x == 0) {
+    for (int g = 0; g < 4; ++g) {
+      mbar_init(&sh.ready[g], kThreads);
+      mbar_init(&sh.done[g], 1);
+    }
+    mbar_fence_init();
+  }
+  if (issuer) tmem_alloc(&sh.tmem_base, a.tmem_cols);
+  fence_proxy_async();
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = sh.tmem_base;
+  const uint32_t smem_base = smem_u32(smem);
+  const int64_t ntiles = (a.N + kTile - 1) / kTile;
+  const int nl = a.nl;
+  const bool any_tile = tile_of(0, 0, nwg) < ntiles;
+  if (issuer) {
+    uint32_t rph = 0;      // bit g: phase of ready[g]
+    uint32_t started = 0;  // bit l: dW_l accumulator holds data
+    const uint32_t leader = lane == 0;
+    for (int i = 0;; ++i) {
+      if (tile_of(i, 0, nwg) >= ntiles) break;
+      for (int r = 0; r < 2 * nl; ++r) {
+        for (int g = 0; g < nwg; ++g) {
+          if (tile_of(i, g, nwg) >= ntiles) break;
+          mbar_wait(&sh.ready[g], (rph >> g) & 1u);
+          fence_after_sync();
+          const uint32_t base = smem_base + a.wg_base + g * a.wg_stride;
+          const uint32_t work = tmem + g * kMaxWidth;
+          if (r < nl) {
+            issue_forward(a, r, smem_base, work, base + a.layer[r].x_off, leader);
+          } else {
+            const int l = 2 * nl - 1 - r;
+            const TcLayer& ly = a.layer[l];
+            const uint32_t ga = base + (l == nl - 1 ? a.g_off : a.layer[l + 1].x_off);
+            const uint32_t xa = base + ly.x_off, wa = smem_base + ly.w_off;
+            // dW_l (M = 64 features of dY) += G^T . [X_l | 1]   : contraction over the 128 samples
+            const uint32_t id_w = make_idesc_f16(64, ly.Ka, 1, 1, a.fmt, a.fmt);
+            const uint32_t acc0 = (started >> l) & 1u;
+            const uint64_t dg = make_desc(ga, 128, kActCs), dx = make_desc(xa, 128, kActCs);
+#pragma unroll
+            for (int k = 0; k < kTile / 16; ++k)
+              mma_f16_uniform(tmem + ly.dw_col, dg + (uint64_t)(k * 16), dx + (uint64_t)(k * 16), id_w, acc0 | (k > 0), leader);
+            if (l > 0 || a.dx != nullptr) {
+              // dX_l [128 x Nx] = G [128 x Np] . W_l   (W_l viewed MN-major: contraction over its rows)
+              const int Nx = (ly.K + 15) & ~15;
+              const uint32_t id_x = make_idesc_f16(128, Nx, 0, 1, a.fmt, a.fmt);
+              const uint64_t dgk = make_desc(ga, kActCs, 128), dw = make_desc(wa, 128, ly.w_cs);
+              const int nk = ly.Np >> 4;
+#pragma unroll
+              for (int k = 0; k < kMaxWidth / 16; ++k)
+                if (k < nk)
+                  mma_f16_uniform(work, dgk + (uint64_t)(k * ((2 * kActCs) >> 4)), dw + (uint64_t)(k * 16), id_x, k > 0, leader);
+            }
+          }
+          commit_uniform(&sh.done[g], leader);
+          if (r >= nl) started |= 1u << (2 * nl - 1 - r);
+          rph ^= 1u << g;
+          __syncwarp();
         }
-        commit(&ctx.bar);
       }
-      mbar_wait(&ctx.bar, phase);
-      phase ^= 1;
-      fence_after_sync();
-      if (l > 0) {
-        // dY_{l-1} = dX_l * relu'(X_l), written in place over X_l (its MMAs have completed); 64 columns wide
-        unsigned char* xt = smem + ly.x_off;
-        const bool masked = a.layer[l - 1].relu != 0;
+    }
+  } else {
+    unsigned char* base = smem + a.wg_base + wg * a.wg_stride;
+    const uint32_t tmem_row = tmem + wg * kMaxWidth + ((uint32_t)(tid & ~31) << 16);
+    const TcLayer& last = a.layer[nl - 1];
+    const int K0 = a.layer[0].K, Ka0 = a.layer[0].Ka;
+    const bool vec = (K0 & 3) == 0 && (reinterpret_cast<uintptr_t>(a.x) & 15) == 0;
+    const int kshift = (K0 & (K0 - 1)) == 0 ? (31 - __clz(K0)) : -1;
+    const int r = tid;
+    uint32_t phase = 0;
+    float4 xr[16];
+    if (vec && tile_of(0, wg, nwg) < ntiles) x_prefetch(xr, a.x, tile_of(0, wg, nwg) * kTile, a.N, K0, tid);
+    for (int i = 0;; ++i) {
+      const int64_t t = tile_of(i, wg, nwg);
+      if (t >= ntiles) break;
+      const int64_t row0 = t * kTile;
+      if (vec) {
+        x_commit<FMT>(xr, K0, kshift, Ka0, base + a.layer[0].x_off, tid);
+        const int64_t t2 = tile_of(i + 1, wg, nwg);
+        if (t2 < ntiles) x_prefetch(xr, a.x, t2 * kTile, a.N, K0, tid);
+      } else {
+        load_input_tile<FMT>(a.x, row0, a.N, K0, Ka0, base + a.layer[0].x_off, tid);
+      }
+      // ---- forward recompute, every layer input kept ----
+      for (int l = 0; l < nl; ++l) {
+        wg_round(sh, wg, phase);
+        if (l + 1 < nl)
+          hidden_epilogue<FMT>(tmem_row, a.layer[l].Np, a.layer[l].N, a.layer[l].relu, a.layer[l + 1].Ka,
+                               base + a.layer[l + 1].x_off, tid);
+      }
+      // ---- gradient w.r.t. the raw outputs -> G tile (64 features wide, zero padded) ----
+      {
+        const int64_t row = row0 + r;
+        const bool live = row < a.N;
+        float sel = 1.f;
+        if (a.selector && live) sel = a.selector[row];
+        const float* dyr = a.dy + row * last.N;
+        unsigned char* g = base + a.g_off;
         for (int c0 = 0; c0 < kMaxWidth; c0 += 16) {
           float v[16];
-          if (c0 < Nx) {
+          if (c0 < last.Np) {
             tmem_ld16(tmem_row + c0, v);
           } else {
 #pragma unroll
             for (int j = 0; j < 16; ++j) v[j] = 0.f;
           }
-          uint4* p0 = reinterpret_cast<uint4*>(xt + (c0 >> 3) * kActCs + r * 16);
-          uint4* p1 = reinterpret_cast<uint4*>(xt + ((c0 >> 3) + 1) * kActCs + r * 16);
-          uint4 m0 = make_uint4(0, 0, 0, 0), m1 = make_uint4(0, 0, 0, 0);
-          if (c0 < ly.Ka) {
-            m0 = *p0;
-            m1 = *p1;
-          }
-          const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            // stored activation > 0  <=>  16-bit pattern is positive and non-zero (sign bit clear, magnitude != 0)
-            uint32_t h = (mw[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-            bool pos = !masked || ((h != 0u) && ((h & 0x8000u) == 0u));
-            if (!(pos && (c0 + j) < ly.K)) v[j] = 0.f;
+            int n = c0 + j;
+            float d = 0.f;
+            if (live && n < last.N) d = out_act_grad(a.out_act, n, v[j], sel, __ldg(dyr + n));
+            v[j] = d;
           }
-          *p0 = make_uint4(pack2<FMT>(v[0], v[1]), pack2<FMT>(v[2], v[3]), pack2<FMT>(v[4], v[5]), pack2<FMT>(v[6], v[7]));
-          *p1 = make_uint4(pack2<FMT>(v[8], v[9]), pack2<FMT>(v[10], v[11]), pack2<FMT>(v[12], v[13]), pack2<FMT>(v[14], v[15]));
+          *reinterpret_cast<uint4*>(g + (c0 >> 3) * kActCs + r * 16) =
+              make_uint4(pack2<FMT>(v[0], v[1]), pack2<FMT>(v[2], v[3]), pack2<FMT>(v[4], v[5]), pack2<FMT>(v[6], v[7]));
+          *reinterpret_cast<uint4*>(g + ((c0 >> 3) + 1) * kActCs + r * 16) =
+              make_uint4(pack2<FMT>(v[8], v[9]), pack2<FMT>(v[10], v[11]), pack2<FMT>(v[12], v[13]), pack2<FMT>(v[14], v[15]));
         }
-        g_off = ly.x_off;
-      } else if (a.dx) {
-        const int64_t row = row0 + r;
-        float* dxr = a.dx + row * ly.K;
-        for (int c0 = 0; c0 < Nx; c0 += 16) {
-          float v[16];
-          tmem_ld16(tmem_row + c0, v);
-          if (row < a.N) {
+      }
+      // ---- backward sweep ----
+      for (int l = nl - 1; l >= 0; --l) {
+        const TcLayer& ly = a.layer[l];
+        const int Nx = (ly.K + 15) & ~15;
+        wg_round(sh, wg, phase);
+        if (l > 0) {
+          // dY_{l-1} = dX_l * relu'(X_l), written in place over X_l (its MMAs have completed); 64 columns wide
+          unsigned char* xt = base + ly.x_off;
+          const bool masked = a.layer[l - 1].relu != 0;
+          for (int c0 = 0; c0 < kMaxWidth; c0 += 16) {
+            float v[16];
+            if (c0 < Nx) {
+              tmem_ld16(tmem_row + c0, v);
+            } else {
 #pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (c0 + j < ly.K) dxr[c0 + j] = v[j];
+              for (int j = 0; j < 16; ++j) v[j] = 0.f;
+            }
+            uint4* p0 = reinterpret_cast<uint4*>(xt + (c0 >> 3) * kActCs + r * 16);
+            uint4* p1 = reinterpret_cast<uint4*>(xt + ((c0 >> 3) + 1) * kActCs + r * 16);
+            uint4 m0 = make_uint4(0, 0, 0, 0), m1 = make_uint4(0, 0, 0, 0);
+            if (c0 < ly.Ka) {
+              m0 = *p0;
+              m1 = *p1;
+            }
+            const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              // stored activation > 0  <=>  16-bit pattern is non-zero with the sign bit clear
+              uint32_t h = (mw[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
+              bool pos = !masked || ((h != 0u) && ((h & 0x8000u) == 0u));
+              if (!(pos && (c0 + j) < ly.K)) v[j] = 0.f;
+            }
+            *p0 = make_uint4(pack2<FMT>(v[0], v[1]), pack2<FMT>(v[2], v[3]), pack2<FMT>(v[4], v[5]), pack2<FMT>(v[6], v[7]));
+            *p1 = make_uint4(pack2<FMT>(v[8], v[9]), pack2<FMT>(v[10], v[11]), pack2<FMT>(v[12], v[13]), pack2<FMT>(v[14], v[15]));
+          }
+        } else if (a.dx) {
+          const int64_t row = row0 + r;
+          float* dxr = a.dx + row * ly.K;
+          for (int c0 = 0; c0 < Nx; c0 += 16) {
+            float v[16];
+            tmem_ld16(tmem_row + c0, v);
+            if (row < a.N) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (c0 + j < ly.K) dxr[c0 + j] = v[j];
+            }
           }
         }
       }
     }
-    first_tile = false;
   }
   // ---- flush the weight / bias gradients: M=64 accumulator rows live in lanes 0..15 of every warp ----
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  if (!first_tile) {
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (!issuer && any_tile) {
+    const int w = tid >> 5;
     const int n = 16 * w + lane;
-    for (int l = 0; l < a.nl; ++l) {
+    const uint32_t lane_base = tmem + ((uint32_t)(tid & ~31) << 16);
+    for (int l = wg; l < nl; l += nwg) {
       const TcLayer& ly = a.layer[l];
       for (int c0 = 0; c0 < ly.Ka; c0 += 16) {
         float v[16];
-        tmem_ld16(tmem_row + ly.dw_col + c0, v);
+        tmem_ld16(lane_base + ly.dw_col + c0, v);
         if (lane < 16 && n < ly.N) {
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
@@ -427,10 +555,12 @@ __global__ void __launch_bounds__(kThreads) mlp_tc_bwd_kernel(const TcArgs a) {
   }
   fence_before_sync();
   __syncthreads();
-  if (threadIdx.x < 32) tmem_dealloc(tmem, a.tmem_cols);
+  if (issuer) tmem_dealloc(tmem, a.tmem_cols);
 }
 
 int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+constexpr int kSmemLimit = 227 * 1024;
 
 int build_args(TcArgs& a, bool backward, int nl, const int32_t* dims, const float* const* W, const float* const* b,
                int relu_mask, int out_act, int fmt, const char* who) {
@@ -456,37 +586,49 @@ int build_args(TcArgs& a, bool backward, int nl, const int32_t* dims, const floa
     ly.w_off = off;
     off += (ly.Ka / 8) * ly.w_cs;
     off = round_up(off, 128);
+    ly.x_off = 0;
+    ly.dw_col = 0;
     if (ly.Ka > max_ka) max_ka = ly.Ka;
   }
   a.nl = nl;
   a.out_act = out_act;
   a.fmt = fmt;
-  int cols = kMaxWidth;  // work accumulator (forward outputs / dX)
+  a.wg_base = off;
+  int per_wg = 0, dw_cols = 0;
   if (!backward) {
     int tile_bytes = round_up((max_ka / 8) * kActCs, 128);
-    a.layer[0].x_off = off;
-    a.x_off1 = off + tile_bytes;
-    off += 2 * tile_bytes;
+    a.layer[0].x_off = 0;
+    a.x_off1 = tile_bytes;
     a.g_off = 0;
+    per_wg = 2 * tile_bytes;
   } else {
     for (int l = 0; l < nl; ++l) {
       TcLayer& ly = a.layer[l];
       int width = ly.Ka > kMaxWidth ? ly.Ka : kMaxWidth;  // later reused as a 64-wide gradient tile
-      ly.x_off = off;
-      off += round_up((width / 8) * kActCs, 128);
-      ly.dw_col = cols;
-      cols += ly.Ka;
+      ly.x_off = per_wg;
+      per_wg += round_up((width / 8) * kActCs, 128);
+      dw_cols += ly.Ka;
     }
-    a.g_off = off;
-    off += round_up((kMaxWidth / 8) * kActCs, 128);
+    a.g_off = per_wg;
+    per_wg += round_up((kMaxWidth / 8) * kActCs, 128);
     a.x_off1 = 0;
   }
+  a.wg_stride = per_wg;
+  int nwg = 4;
+  while (nwg > 1 && (a.wg_base + nwg * per_wg > kSmemLimit - 1024 || nwg * kMaxWidth + dw_cols > 512)) --nwg;
+  NKBS_CHECK_ARG(a.wg_base + nwg * per_wg <= kSmemLimit - 1024 && nwg * kMaxWidth + dw_cols <= 512,
+                 "%s: does not fit (smem %d, tmem %d)", who, a.wg_base + per_wg, kMaxWidth + dw_cols);
+  a.nwg = nwg;
+  int col = nwg * kMaxWidth;
+  if (backward)
+    for (int l = 0; l < nl; ++l) {
+      a.layer[l].dw_col = col;
+      col += a.layer[l].Ka;
+    }
   int tc = 32;
-  while (tc < cols) tc <<= 1;
-  NKBS_CHECK_ARG(tc <= 512, "%s: needs %d TMEM columns", who, cols);
+  while (tc < col) tc <<= 1;
   a.tmem_cols = tc;
-  a.smem_bytes = off;
-  NKBS_CHECK_ARG(off <= 227 * 1024, "%s: needs %d bytes of shared memory", who, off);
+  a.smem_bytes = a.wg_base + nwg * per_wg;
   return 0;
 }
 
@@ -495,6 +637,18 @@ int set_smem(K kernel, int bytes, const char* who) {
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
   NKBS_CHECK_ARG(e == cudaSuccess, "%s: %d bytes of shared memory refused: %s", who, bytes, cudaGetErrorString(e));
   return 0;
+}
+
+int pick_grid(const TcArgs& a, int64_t N) {
+  int64_t ntiles = (N + kTile - 1) / kTile;
+  int64_t groups = (ntiles + a.nwg - 1) / a.nwg;
+  int threads = a.nwg * kThreads + 32;
+  int per_sm = kSmemLimit / (a.smem_bytes + 1024);
+  if (per_sm > 512 / a.tmem_cols) per_sm = 512 / a.tmem_cols;
+  if (per_sm > 2048 / threads) per_sm = 2048 / threads;
+  if (per_sm < 1) per_sm = 1;
+  int64_t cap = (int64_t)nkbs_num_sms() * per_sm;
+  return (int)(groups < cap ? groups : cap);
 }
 
 }  // namespace
@@ -513,20 +667,13 @@ extern "C" int nkbs_mlp_tc_fwd(const float* x, int64_t N, int32_t nl, const int3
   a.dy = nullptr;
   a.dx = nullptr;
   a.N = N;
-  int64_t ntiles = (N + kTile - 1) / kTile;
-  int per_sm = 227 * 1024 / (a.smem_bytes + 1024);
-  int by_tmem = 512 / a.tmem_cols;
-  if (per_sm > by_tmem) per_sm = by_tmem;
-  if (per_sm < 1) per_sm = 1;
-  if (per_sm > 4) per_sm = 4;
-  int64_t cap = (int64_t)nkbs_num_sms() * per_sm;
-  int grid = (int)(ntiles < cap ? ntiles : cap);
+  const int grid = pick_grid(a, N), threads = a.nwg * kThreads + 32;
   if (fmt == 0) {
     if (set_smem(mlp_tc_fwd_kernel<0>, a.smem_bytes, "nkbs_mlp_tc_fwd")) return -1;
-    mlp_tc_fwd_kernel<0><<<grid, kThreads, a.smem_bytes, (cudaStream_t)stream>>>(a);
+    mlp_tc_fwd_kernel<0><<<grid, threads, a.smem_bytes, (cudaStream_t)stream>>>(a);
   } else {
     if (set_smem(mlp_tc_fwd_kernel<1>, a.smem_bytes, "nkbs_mlp_tc_fwd")) return -1;
-    mlp_tc_fwd_kernel<1><<<grid, kThreads, a.smem_bytes, (cudaStream_t)stream>>>(a);
+    mlp_tc_fwd_kernel<1><<<grid, threads, a.smem_bytes, (cudaStream_t)stream>>>(a);
   }
   NKBS_CHECK_LAUNCH("nkbs_mlp_tc_fwd");
   return 0;
@@ -534,7 +681,8 @@ extern "C" int nkbs_mlp_tc_fwd(const float* x, int64_t N, int32_t nl, const int3
 
 extern "C" int nkbs_mlp_tc_bwd(const float* x, const float* dy, int64_t N, int32_t nl, const int32_t* dims,
                                const float* const* W, const float* const* b, int32_t relu_mask, int32_t out_act,
-                               int32_t fmt, const float* selector, float* dx, float* const* dW, float* const* db, void* stream) {
+                               int32_t fmt, const float* selector, float* dx, float* const* dW, float* const* db,
+                               void* stream) {
   TcArgs a;
   if (build_args(a, true, nl, dims, W, b, relu_mask, out_act, fmt, "nkbs_mlp_tc_bwd")) return -1;
   NKBS_CHECK_ARG(N >= 0, "nkbs_mlp_tc_bwd: negative N");
@@ -551,20 +699,13 @@ extern "C" int nkbs_mlp_tc_bwd(const float* x, const float* dy, int64_t N, int32
   a.dy = dy;
   a.dx = dx;
   a.N = N;
-  int64_t ntiles = (N + kTile - 1) / kTile;
-  int per_sm = 227 * 1024 / (a.smem_bytes + 1024);
-  int by_tmem = 512 / a.tmem_cols;
-  if (per_sm > by_tmem) per_sm = by_tmem;
-  if (per_sm < 1) per_sm = 1;
-  if (per_sm > 4) per_sm = 4;
-  int64_t cap = (int64_t)nkbs_num_sms() * per_sm;
-  int grid = (int)(ntiles < cap ? ntiles : cap);
+  const int grid = pick_grid(a, N), threads = a.nwg * kThreads + 32;
   if (fmt == 0) {
     if (set_smem(mlp_tc_bwd_kernel<0>, a.smem_bytes, "nkbs_mlp_tc_bwd")) return -1;
-    mlp_tc_bwd_kernel<0><<<grid, kThreads, a.smem_bytes, (cudaStream_t)stream>>>(a);
+    mlp_tc_bwd_kernel<0><<<grid, threads, a.smem_bytes, (cudaStream_t)stream>>>(a);
   } else {
     if (set_smem(mlp_tc_bwd_kernel<1>, a.smem_bytes, "nkbs_mlp_tc_bwd")) return -1;
-    mlp_tc_bwd_kernel<1><<<grid, kThreads, a.smem_bytes, (cudaStream_t)stream>>>(a);
+    mlp_tc_bwd_kernel<1><<<grid, threads, a.smem_bytes, (cudaStream_t)stream>>>(a);
   }
   NKBS_CHECK_LAUNCH("nkbs_mlp_tc_bwd");
   return 0;
