@@ -3,12 +3,13 @@ library is missing or an entry point fails, the caller gets an exception."""
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 import torch
 
 _HERE = Path(__file__).resolve().parent
-_LIB_PATH = _HERE / "libnkbs.so"
+_LIB_PATH = Path(os.environ["NKBS_LIB"]) if os.environ.get("NKBS_LIB") else _HERE / "libnkbs.so"  # NKBS_LIB: debug builds
 
 _p = C.c_void_p
 _i32 = C.c_int32

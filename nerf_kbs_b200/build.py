@@ -13,7 +13,7 @@ CSRC = HERE / "csrc"
 LIB = HERE / "libnkbs.so"
 OBJ = HERE / "build"
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-              "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
+              "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "--extended-lambda"]
 
 
 def _nvcc() -> str:

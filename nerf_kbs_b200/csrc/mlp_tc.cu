@@ -61,6 +61,9 @@ struct TcArgs {
   int64_t N;
   int x_off1;             // forward: second ping-pong activation buffer   (offsets x_off/x_off1/g_off are
   int g_off;              // backward: gradient tile (64 features wide)    relative to the warpgroup's region)
+  int dy_off;             // backward: fp32 staging of the upstream-gradient tile [128 x Kn] (cp.async target)
+  int stage_off;          // backward: fp32 staging used to write dx coalesced (aliases dead activation tiles)
+  int stage_ok;           // 1 if the dx staging fits
   int wg_base;            // byte offset of warpgroup 0's activation region
   int wg_stride;          // bytes per warpgroup region
   int nwg;                // epilogue warpgroups per CTA (each owns one 128-sample tile at a time)
@@ -79,8 +82,14 @@ __device__ __forceinline__ uint16_t cvt16(float v) {
   }
 }
 template <int FMT>
-__device__ __forceinline__ uint32_t pack2(float a, float b) {
-  return (uint32_t)cvt16<FMT>(a) | ((uint32_t)cvt16<FMT>(b) << 16);
+__device__ __forceinline__ uint32_t pack2(float a, float b) {  // one F2FP: two floats -> packed 16-bit pair (a low)
+  if (FMT == 1) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+  } else {
+    __half2 h = __floats2half2_rn(fminf(fmaxf(a, -65504.f), 65504.f), fminf(fmaxf(b, -65504.f), 65504.f));
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
 }
 
 // byte offset of element (row, k) inside a tile with chunk stride cs
@@ -173,30 +182,77 @@ __device__ __forceinline__ void issue_forward(const TcArgs& a, int l, uint32_t s
     if (k < nk) mma_f16_uniform(tmem, da + (uint64_t)(k * sa), db + (uint64_t)(k * sb), idesc, k > 0, leader);
 }
 
+
+// Walk this thread's accumulator row in groups of 16 columns: f(c0, v[16]) for c0 = 0, 16, .. < ncols_total.
+// Columns >= ncols_tmem are zeros.  Two tcgen05.ld (32 columns) are in flight per wait.
+template <int kMaxGroups, typename F>
+__device__ __forceinline__ void tmem_foreach16(uint32_t taddr, int ncols_tmem, int ncols_total, F f) {
+#pragma unroll 1
+  for (int c0 = 0; c0 < ncols_total; c0 += 32) {
+    uint32_t b0[16], b1[16];
+    const bool h0 = c0 < ncols_tmem, h1 = c0 + 16 < ncols_tmem;
+    if (h0) tmem_ld16_issue(taddr + c0, b0);
+    if (h1) tmem_ld16_issue(taddr + c0 + 16, b1);
+    if (h0) tmem_ld_wait();
+    float v[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] = h0 ? __uint_as_float(b0[j]) : 0.f;
+    f(c0, v);
+    if (c0 + 16 < ncols_total) {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) v[j] = h1 ? __uint_as_float(b1[j]) : 0.f;
+      f(c0 + 16, v);
+    }
+  }
+}
+
+template <int FMT>
+__device__ __forceinline__ void store16(unsigned char* tile, int c0, int r, const float v[16]) {
+  *reinterpret_cast<uint4*>(tile + (c0 >> 3) * kActCs + r * 16) =
+      make_uint4(pack2<FMT>(v[0], v[1]), pack2<FMT>(v[2], v[3]), pack2<FMT>(v[4], v[5]), pack2<FMT>(v[6], v[7]));
+  *reinterpret_cast<uint4*>(tile + ((c0 >> 3) + 1) * kActCs + r * 16) =
+      make_uint4(pack2<FMT>(v[8], v[9]), pack2<FMT>(v[10], v[11]), pack2<FMT>(v[12], v[13]), pack2<FMT>(v[14], v[15]));
+}
+
 // hidden-layer epilogue: TMEM accumulator -> ReLU -> 16-bit -> next layer's input tile (+ bias column)
 template <int FMT>
 __device__ __forceinline__ void hidden_epilogue(uint32_t tmem_row, int Np, int N, int relu, int Ka_next,
                                                 unsigned char* dst, int r) {
-  for (int c0 = 0; c0 < Ka_next; c0 += 16) {
-    float v[16];
-    if (c0 < Np) {
-      tmem_ld16(tmem_row + c0, v);
-    } else {
+  tmem_foreach16<(kMaxWidth + 16) / 16>(tmem_row, Np, Ka_next, [&](int c0, float v[16]) {
+    if (c0 + 16 <= N) {  // interior group: no per-column bookkeeping
+      if (relu) {
 #pragma unroll
-      for (int j = 0; j < 16; ++j) v[j] = 0.f;
-    }
+        for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
+      }
+    } else {  // group holding the bias column and the zero padding
 #pragma unroll
-    for (int j = 0; j < 16; ++j) {
-      int n = c0 + j;
-      v[j] = n < N ? (relu ? fmaxf(v[j], 0.f) : v[j]) : (n == N ? 1.f : 0.f);
+      for (int j = 0; j < 16; ++j) {
+        const int n = c0 + j;
+        v[j] = n < N ? (relu ? fmaxf(v[j], 0.f) : v[j]) : (n == N ? 1.f : 0.f);
+      }
     }
-    uint4 lo = make_uint4(pack2<FMT>(v[0], v[1]), pack2<FMT>(v[2], v[3]), pack2<FMT>(v[4], v[5]), pack2<FMT>(v[6], v[7]));
-    uint4 hi = make_uint4(pack2<FMT>(v[8], v[9]), pack2<FMT>(v[10], v[11]), pack2<FMT>(v[12], v[13]), pack2<FMT>(v[14], v[15]));
-    *reinterpret_cast<uint4*>(dst + (c0 >> 3) * kActCs + r * 16) = lo;
-    *reinterpret_cast<uint4*>(dst + ((c0 >> 3) + 1) * kActCs + r * 16) = hi;
-  }
+    store16<FMT>(dst, c0, r, v);
+  });
 }
 
+#ifdef NKBS_TRACE
+__device__ long long g_trace[2][4096];
+__device__ int g_trace_n[2];
+__device__ __forceinline__ void trace(int role, int tag) {
+  if (blockIdx.x != 0) return;
+  int i = g_trace_n[role];
+  if (i < 2047) {
+    g_trace[role][2 * i] = tag;
+    g_trace[role][2 * i + 1] = clock64();
+    g_trace_n[role] = i + 1;
+  }
+}
+#define TRACE_WG(tag) do { if (wg == 0 && tid == 0) trace(0, tag); } while (0)
+#define TRACE_IS(tag) do { if (lane == 0) trace(1, tag); } while (0)
+#else
+#define TRACE_WG(tag)
+#define TRACE_IS(tag)
+#endif
 
 struct Sh {
   uint64_t ready[4];  // warpgroup g: operand tiles of its next MMA batch are written   (128 arrivals)
@@ -209,7 +265,8 @@ __device__ __forceinline__ int64_t tile_of(int i, int wg, int nwg) {
 }
 
 // ---- input tile through registers: the loads of tile i+1 are in flight while tile i is processed ----
-__device__ __forceinline__ void x_prefetch(float4 xr[16], const float* __restrict__ x, int64_t row0, int64_t rows_total,
+template <int NV>
+__device__ __forceinline__ void x_prefetch(float4 (&xr)[NV], const float* __restrict__ x, int64_t row0, int64_t rows_total,
                                            int K, int tid) {
   int64_t rows = rows_total - row0;
   if (rows > kTile) rows = kTile;
@@ -217,17 +274,18 @@ __device__ __forceinline__ void x_prefetch(float4 xr[16], const float* __restric
   const int valid = (int)rows * K;
   const int nvec = K >> 2;
 #pragma unroll
-  for (int j = 0; j < 16; ++j) {
+  for (int j = 0; j < NV; ++j) {
     const int e = 4 * (tid + kThreads * j);
-    xr[j] = (j < nvec && e < valid) ? __ldg(reinterpret_cast<const float4*>(src + e)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    if (j < nvec && e < valid) xr[j] = ldg_nc_v4(src + e);
+    else xr[j] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
 }
 
-template <int FMT>
-__device__ __forceinline__ void x_commit(const float4 xr[16], int K, int kshift, int Ka, unsigned char* tile, int tid) {
+template <int FMT, int NV>
+__device__ __forceinline__ void x_commit(const float4 (&xr)[NV], int K, int kshift, int Ka, unsigned char* tile, int tid) {
   const int nvec = K >> 2;
 #pragma unroll
-  for (int j = 0; j < 16; ++j) {
+  for (int j = 0; j < NV; ++j) {
     if (j < nvec) {
       const int e = 4 * (tid + kThreads * j);
       const int r = kshift >= 0 ? (e >> kshift) : (e / K);
@@ -250,16 +308,7 @@ __device__ __forceinline__ void wg_round(Sh& sh, int wg, uint32_t& phase) {
   fence_after_sync();
 }
 
-template <int FMT>
-__global__ void __launch_bounds__(4 * kThreads + 32) mlp_tc_fwd_kernel(const TcArgs a) {
-  extern __shared__ __align__(128) unsigned char smem[];
-  __shared__ Sh sh;
-  const int nwg = a.nwg;
-  const int wg = threadIdx.x >> 7;
-  const int tid = threadIdx.x & (kThreads - 1);
-  const int lane = threadIdx.x & 31;
-  const bool issuer = wg == nwg;
-  stage_weights<FMT>(a, smem);
+__device__ __forceinline__ void kernel_prologue(Sh& sh, bool issuer, int tmem_cols) {
   if (threadIdx.x == 0) {
     for (int g = 0; g < 4; ++g) {
       mbar_init(&sh.ready[g], kThreads);
@@ -267,29 +316,42 @@ __global__ void __launch_bounds__(4 * kThreads + 32) mlp_tc_fwd_kernel(const TcA
     }
     mbar_fence_init();
   }
-  if (issuer) tmem_alloc(&sh.tmem_base, a.tmem_cols);
+  if (issuer) tmem_alloc(&sh.tmem_base, tmem_cols);
   fence_proxy_async();
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
+}
+
+template <int FMT, int NWG>
+__global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_fwd_kernel(const TcArgs a) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  __shared__ Sh sh;
+  constexpr int nwg = NWG;
+  const int wg = threadIdx.x >> 7;
+  const int tid = threadIdx.x & (kThreads - 1);
+  const bool issuer = wg == nwg;
+  stage_weights<FMT>(a, smem);
+  kernel_prologue(sh, issuer, a.tmem_cols);
   const uint32_t tmem = sh.tmem_base;
   const uint32_t smem_base = smem_u32(smem);
   const int64_t ntiles = (a.N + kTile - 1) / kTile;
   if (issuer) {
     uint32_t rph = 0;  // bit g: phase of ready[g]
-    const uint32_t leader = lane == 0;
+    const uint32_t leader = elect_one();
     for (int i = 0;; ++i) {
       if (tile_of(i, 0, nwg) >= ntiles) break;
       for (int l = 0; l < a.nl; ++l) {
+#pragma unroll
         for (int g = 0; g < nwg; ++g) {
-          if (tile_of(i, g, nwg) >= ntiles) break;
-          mbar_wait(&sh.ready[g], (rph >> g) & 1u);
-          fence_after_sync();
-          const uint32_t base = smem_base + a.wg_base + g * a.wg_stride;
-          issue_forward(a, l, smem_base, tmem + g * kMaxWidth, base + ((l & 1) ? a.x_off1 : a.layer[0].x_off), leader);
-          commit_uniform(&sh.done[g], leader);
-          rph ^= 1u << g;
-          __syncwarp();
+          if (tile_of(i, g, nwg) < ntiles) {
+            mbar_wait(&sh.ready[g], (rph >> g) & 1u);
+            fence_after_sync();
+            const uint32_t base = smem_base + a.wg_base + g * a.wg_stride;
+            issue_forward(a, l, smem_base, tmem + g * kMaxWidth, base + ((l & 1) ? a.x_off1 : a.layer[0].x_off), leader);
+            commit_uniform(&sh.done[g], leader);
+            rph ^= 1u << g;
+          }
         }
       }
     }
@@ -298,21 +360,24 @@ __global__ void __launch_bounds__(4 * kThreads + 32) mlp_tc_fwd_kernel(const TcA
     const uint32_t tmem_row = tmem + wg * kMaxWidth + ((uint32_t)(tid & ~31) << 16);
     const TcLayer& last = a.layer[a.nl - 1];
     const int K0 = a.layer[0].K, Ka0 = a.layer[0].Ka;
-    const bool vec = (K0 & 3) == 0 && (reinterpret_cast<uintptr_t>(a.x) & 15) == 0;
+    const bool vec = (K0 & 3) == 0 && (K0 >> 2) <= (NWG >= 4 ? 8 : 16) && (reinterpret_cast<uintptr_t>(a.x) & 15) == 0;
     const int kshift = (K0 & (K0 - 1)) == 0 ? (31 - __clz(K0)) : -1;
     uint32_t phase = 0;
-    float4 xr[16];
-    if (vec && tile_of(0, wg, nwg) < ntiles) x_prefetch(xr, a.x, tile_of(0, wg, nwg) * kTile, a.N, K0, tid);
+    constexpr int NV = NWG >= 4 ? 8 : 16;  // register budget: 120 registers per thread with four warpgroups
     for (int i = 0;; ++i) {
       const int64_t t = tile_of(i, wg, nwg);
       if (t >= ntiles) break;
       const int64_t row0 = t * kTile;
+      const int64_t row = row0 + tid;
+      const bool live = row < a.N;
+      float sel = 1.f;
+      if (a.selector && live) sel = __ldg(a.selector + row);
       unsigned char* cur = base + a.layer[0].x_off;
       unsigned char* nxt = base + a.x_off1;
       if (vec) {
+        float4 xr[NV];
+        x_prefetch(xr, a.x, row0, a.N, K0, tid);
         x_commit<FMT>(xr, K0, kshift, Ka0, cur, tid);
-        const int64_t t2 = tile_of(i + 1, wg, nwg);
-        if (t2 < ntiles) x_prefetch(xr, a.x, t2 * kTile, a.N, K0, tid);
       } else {
         load_input_tile<FMT>(a.x, row0, a.N, K0, Ka0, cur, tid);
       }
@@ -326,20 +391,14 @@ __global__ void __launch_bounds__(4 * kThreads + 32) mlp_tc_fwd_kernel(const TcA
         }
       }
       // output layer: activation and store, one row per thread
-      const int64_t row = row0 + tid;
-      const bool live = row < a.N;
-      float sel = 1.f;
-      if (a.selector && live) sel = a.selector[row];
       float* yo = a.y + row * last.N;
-      for (int c0 = 0; c0 < last.Np; c0 += 16) {
-        float v[16];
-        tmem_ld16(tmem_row + c0, v);
+      tmem_foreach16<kMaxWidth / 16>(tmem_row, last.Np, last.Np, [&](int c0, float v[16]) {
         if (live) {
 #pragma unroll
           for (int j = 0; j < 16; ++j)
             if (c0 + j < last.N) yo[c0 + j] = apply_out_act(a.out_act, c0 + j, v[j], sel);
         }
-      }
+      });
     }
   }
   fence_before_sync();
@@ -347,28 +406,17 @@ __global__ void __launch_bounds__(4 * kThreads + 32) mlp_tc_fwd_kernel(const TcA
   if (issuer) tmem_dealloc(tmem, a.tmem_cols);
 }
 
-template <int FMT>
-__global__ void __launch_bounds__(4 * kThreads + 32) mlp_tc_bwd_kernel(const TcArgs a) {
+template <int FMT, int NWG>
+__global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(const TcArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ Sh sh;
-  const int nwg = a.nwg;
+  constexpr int nwg = NWG;
   const int wg = threadIdx.x >> 7;
   const int tid = threadIdx.x & (kThreads - 1);
   const int lane = threadIdx.x & 31;
   const bool issuer = wg == nwg;
   stage_weights<FMT>(a, smem);
-  if (threadIdx.x == 0) {
-    for (int g = 0; g < 4; ++g) {
-      mbar_init(&sh.ready[g], kThreads);
-      mbar_init(&sh.done[g], 1);
-    }
-    mbar_fence_init();
-  }
-  if (issuer) tmem_alloc(&sh.tmem_base, a.tmem_cols);
-  fence_proxy_async();
-  fence_before_sync();
-  __syncthreads();
-  fence_after_sync();
+  kernel_prologue(sh, issuer, a.tmem_cols);
   const uint32_t tmem = sh.tmem_base;
   const uint32_t smem_base = smem_u32(smem);
   const int64_t ntiles = (a.N + kTile - 1) / kTile;
@@ -377,46 +425,50 @@ __global__ void __launch_bounds__(4 * kThreads + 32) mlp_tc_bwd_kernel(const TcA
   if (issuer) {
     uint32_t rph = 0;      // bit g: phase of ready[g]
     uint32_t started = 0;  // bit l: dW_l accumulator holds data
-    const uint32_t leader = lane == 0;
+    const uint32_t leader = elect_one();
     for (int i = 0;; ++i) {
       if (tile_of(i, 0, nwg) >= ntiles) break;
       for (int r = 0; r < 2 * nl; ++r) {
+#pragma unroll
         for (int g = 0; g < nwg; ++g) {
-          if (tile_of(i, g, nwg) >= ntiles) break;
-          mbar_wait(&sh.ready[g], (rph >> g) & 1u);
-          fence_after_sync();
-          const uint32_t base = smem_base + a.wg_base + g * a.wg_stride;
-          const uint32_t work = tmem + g * kMaxWidth;
-          if (r < nl) {
-            issue_forward(a, r, smem_base, work, base + a.layer[r].x_off, leader);
-          } else {
-            const int l = 2 * nl - 1 - r;
-            const TcLayer& ly = a.layer[l];
-            const uint32_t ga = base + (l == nl - 1 ? a.g_off : a.layer[l + 1].x_off);
-            const uint32_t xa = base + ly.x_off, wa = smem_base + ly.w_off;
-            // dW_l (M = 64 features of dY) += G^T . [X_l | 1]   : contraction over the 128 samples
-            const uint32_t id_w = make_idesc_f16(64, ly.Ka, 1, 1, a.fmt, a.fmt);
-            const uint32_t acc0 = (started >> l) & 1u;
-            const uint64_t dg = make_desc(ga, 128, kActCs), dx = make_desc(xa, 128, kActCs);
+          if (tile_of(i, g, nwg) < ntiles) {
+            mbar_wait(&sh.ready[g], (rph >> g) & 1u);
+            fence_after_sync();
+            TRACE_IS(100 + r * 4 + g);
+            const uint32_t base = smem_base + a.wg_base + g * a.wg_stride;
+            const uint32_t work = tmem + g * kMaxWidth;
+            if (r < nl) {
+              issue_forward(a, r, smem_base, work, base + a.layer[r].x_off, leader);
+            } else {
+              const int l = 2 * nl - 1 - r;
+              const TcLayer& ly = a.layer[l];
+              const uint32_t ga = base + (l == nl - 1 ? a.g_off : a.layer[l + 1].x_off);
+              const uint32_t xa = base + ly.x_off, wa = smem_base + ly.w_off;
+              if (l > 0 || a.dx != nullptr) {
+                // dX_l [128 x Nx] = G [128 x Np] . W_l   (W_l viewed MN-major: contraction over its rows); issued
+                // first and committed on its own so the warpgroup's epilogue does not wait for the dW GEMM
+                const int Nx = (ly.K + 15) & ~15;
+                const uint32_t id_x = make_idesc_f16(128, Nx, 0, 1, a.fmt, a.fmt);
+                const uint64_t dgk = make_desc(ga, kActCs, 128), dw = make_desc(wa, 128, ly.w_cs);
+                const int nk = ly.Np >> 4;
 #pragma unroll
-            for (int k = 0; k < kTile / 16; ++k)
-              mma_f16_uniform(tmem + ly.dw_col, dg + (uint64_t)(k * 16), dx + (uint64_t)(k * 16), id_w, acc0 | (k > 0), leader);
-            if (l > 0 || a.dx != nullptr) {
-              // dX_l [128 x Nx] = G [128 x Np] . W_l   (W_l viewed MN-major: contraction over its rows)
-              const int Nx = (ly.K + 15) & ~15;
-              const uint32_t id_x = make_idesc_f16(128, Nx, 0, 1, a.fmt, a.fmt);
-              const uint64_t dgk = make_desc(ga, kActCs, 128), dw = make_desc(wa, 128, ly.w_cs);
-              const int nk = ly.Np >> 4;
+                for (int k = 0; k < kMaxWidth / 16; ++k)
+                  if (k < nk)
+                    mma_f16_uniform(work, dgk + (uint64_t)(k * ((2 * kActCs) >> 4)), dw + (uint64_t)(k * 16), id_x, k > 0, leader);
+              }
+              // dW_l (M = 64 features of dY) += G^T . [X_l | 1]   : contraction over the 128 samples
+              const uint32_t id_w = make_idesc_f16(64, ly.Ka, 1, 1, a.fmt, a.fmt);
+              const uint32_t acc0 = (started >> l) & 1u;
+              const uint64_t dg = make_desc(ga, 128, kActCs), dxd = make_desc(xa, 128, kActCs);
 #pragma unroll
-              for (int k = 0; k < kMaxWidth / 16; ++k)
-                if (k < nk)
-                  mma_f16_uniform(work, dgk + (uint64_t)(k * ((2 * kActCs) >> 4)), dw + (uint64_t)(k * 16), id_x, k > 0, leader);
+              for (int k = 0; k < kTile / 16; ++k)
+                mma_f16_uniform(tmem + ly.dw_col, dg + (uint64_t)(k * 16), dxd + (uint64_t)(k * 16), id_w, acc0 | (k > 0), leader);
+              started |= 1u << l;
             }
+            commit_uniform(&sh.done[g], leader);
+            TRACE_IS(200 + r * 4 + g);
+            rph ^= 1u << g;
           }
-          commit_uniform(&sh.done[g], leader);
-          if (r >= nl) started |= 1u << (2 * nl - 1 - r);
-          rph ^= 1u << g;
-          __syncwarp();
         }
       }
     }
@@ -424,106 +476,155 @@ __global__ void __launch_bounds__(4 * kThreads + 32) mlp_tc_bwd_kernel(const TcA
     unsigned char* base = smem + a.wg_base + wg * a.wg_stride;
     const uint32_t tmem_row = tmem + wg * kMaxWidth + ((uint32_t)(tid & ~31) << 16);
     const TcLayer& last = a.layer[nl - 1];
-    const int K0 = a.layer[0].K, Ka0 = a.layer[0].Ka;
-    const bool vec = (K0 & 3) == 0 && (reinterpret_cast<uintptr_t>(a.x) & 15) == 0;
+    const int K0 = a.layer[0].K, Ka0 = a.layer[0].Ka, Kn = last.N;
+    const bool vec = (K0 & 3) == 0 && (K0 >> 2) <= (NWG >= 4 ? 8 : 16) && (reinterpret_cast<uintptr_t>(a.x) & 15) == 0;
+    const bool vec_dx = a.dx && (K0 & 3) == 0 && (reinterpret_cast<uintptr_t>(a.dx) & 15) == 0;
     const int kshift = (K0 & (K0 - 1)) == 0 ? (31 - __clz(K0)) : -1;
     const int r = tid;
+    float* dys = reinterpret_cast<float*>(base + a.dy_off);
     uint32_t phase = 0;
-    float4 xr[16];
-    if (vec && tile_of(0, wg, nwg) < ntiles) x_prefetch(xr, a.x, tile_of(0, wg, nwg) * kTile, a.N, K0, tid);
+    constexpr int NV = NWG >= 4 ? 8 : 16;  // register budget: 120 registers per thread with four warpgroups
     for (int i = 0;; ++i) {
       const int64_t t = tile_of(i, wg, nwg);
       if (t >= ntiles) break;
       const int64_t row0 = t * kTile;
+      const int64_t row = row0 + r;
+      const bool live = row < a.N;
+      TRACE_WG(1);
+      // upstream gradient tile: asynchronous copy, consumed after the forward recompute
+      {
+        const int64_t total = a.N * Kn, e0 = row0 * Kn;
+        for (int j = 0; j < Kn; ++j) {
+          const int e = tid + kThreads * j;
+          const bool ok = e0 + e < total;
+          cp_async4(dys + e, a.dy + (ok ? e0 + e : 0), ok ? 4u : 0u);
+        }
+        cp_async_commit();
+      }
+      TRACE_WG(5);
+      float sel = 1.f;
+      if (a.selector && live) sel = __ldg(a.selector + row);
       if (vec) {
+        float4 xr[NV];
+        x_prefetch(xr, a.x, row0, a.N, K0, tid);
+        TRACE_WG(6);
         x_commit<FMT>(xr, K0, kshift, Ka0, base + a.layer[0].x_off, tid);
-        const int64_t t2 = tile_of(i + 1, wg, nwg);
-        if (t2 < ntiles) x_prefetch(xr, a.x, t2 * kTile, a.N, K0, tid);
       } else {
         load_input_tile<FMT>(a.x, row0, a.N, K0, Ka0, base + a.layer[0].x_off, tid);
       }
+      TRACE_WG(2);
       // ---- forward recompute, every layer input kept ----
       for (int l = 0; l < nl; ++l) {
         wg_round(sh, wg, phase);
+        TRACE_WG(10 + l);
         if (l + 1 < nl)
           hidden_epilogue<FMT>(tmem_row, a.layer[l].Np, a.layer[l].N, a.layer[l].relu, a.layer[l + 1].Ka,
                                base + a.layer[l + 1].x_off, tid);
       }
+      TRACE_WG(3);
       // ---- gradient w.r.t. the raw outputs -> G tile (64 features wide, zero padded) ----
       {
-        const int64_t row = row0 + r;
-        const bool live = row < a.N;
-        float sel = 1.f;
-        if (a.selector && live) sel = a.selector[row];
-        const float* dyr = a.dy + row * last.N;
+        cp_async_wait_all();
+        wg_sync(wg);  // every thread's part of the dy tile has landed
+        const float* dyr = dys + r * Kn;
         unsigned char* g = base + a.g_off;
-        for (int c0 = 0; c0 < kMaxWidth; c0 += 16) {
-          float v[16];
-          if (c0 < last.Np) {
-            tmem_ld16(tmem_row + c0, v);
+        tmem_foreach16<kMaxWidth / 16>(tmem_row, last.Np, kMaxWidth, [&](int c0, float v[16]) {
+          if (c0 < Kn && live) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int n = c0 + j;
+              v[j] = n < Kn ? out_act_grad(a.out_act, n, v[j], sel, dyr[n]) : 0.f;
+            }
           } else {
 #pragma unroll
             for (int j = 0; j < 16; ++j) v[j] = 0.f;
           }
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            int n = c0 + j;
-            float d = 0.f;
-            if (live && n < last.N) d = out_act_grad(a.out_act, n, v[j], sel, __ldg(dyr + n));
-            v[j] = d;
-          }
-          *reinterpret_cast<uint4*>(g + (c0 >> 3) * kActCs + r * 16) =
-              make_uint4(pack2<FMT>(v[0], v[1]), pack2<FMT>(v[2], v[3]), pack2<FMT>(v[4], v[5]), pack2<FMT>(v[6], v[7]));
-          *reinterpret_cast<uint4*>(g + ((c0 >> 3) + 1) * kActCs + r * 16) =
-              make_uint4(pack2<FMT>(v[8], v[9]), pack2<FMT>(v[10], v[11]), pack2<FMT>(v[12], v[13]), pack2<FMT>(v[14], v[15]));
-        }
+          store16<FMT>(g, c0, r, v);
+        });
       }
+      TRACE_WG(4);
       // ---- backward sweep ----
       for (int l = nl - 1; l >= 0; --l) {
         const TcLayer& ly = a.layer[l];
         const int Nx = (ly.K + 15) & ~15;
+        TRACE_WG(30 + l);
         wg_round(sh, wg, phase);
+        TRACE_WG(20 + l);
         if (l > 0) {
           // dY_{l-1} = dX_l * relu'(X_l), written in place over X_l (its MMAs have completed); 64 columns wide
           unsigned char* xt = base + ly.x_off;
           const bool masked = a.layer[l - 1].relu != 0;
-          for (int c0 = 0; c0 < kMaxWidth; c0 += 16) {
-            float v[16];
-            if (c0 < Nx) {
-              tmem_ld16(tmem_row + c0, v);
-            } else {
-#pragma unroll
-              for (int j = 0; j < 16; ++j) v[j] = 0.f;
-            }
-            uint4* p0 = reinterpret_cast<uint4*>(xt + (c0 >> 3) * kActCs + r * 16);
-            uint4* p1 = reinterpret_cast<uint4*>(xt + ((c0 >> 3) + 1) * kActCs + r * 16);
+          const int K = ly.K, Ka = ly.Ka;
+          tmem_foreach16<kMaxWidth / 16>(tmem_row, Nx, kMaxWidth, [&](int c0, float v[16]) {
             uint4 m0 = make_uint4(0, 0, 0, 0), m1 = make_uint4(0, 0, 0, 0);
-            if (c0 < ly.Ka) {
-              m0 = *p0;
-              m1 = *p1;
+            if (c0 < Ka) {
+              m0 = *reinterpret_cast<const uint4*>(xt + (c0 >> 3) * kActCs + r * 16);
+              m1 = *reinterpret_cast<const uint4*>(xt + ((c0 >> 3) + 1) * kActCs + r * 16);
             }
             const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+            if (c0 + 16 <= K) {
+              if (masked) {
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              // stored activation > 0  <=>  16-bit pattern is non-zero with the sign bit clear
-              uint32_t h = (mw[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-              bool pos = !masked || ((h != 0u) && ((h & 0x8000u) == 0u));
-              if (!(pos && (c0 + j) < ly.K)) v[j] = 0.f;
+                for (int j = 0; j < 16; ++j) {
+                  // stored activation > 0  <=>  16-bit pattern, as a signed 16-bit integer, is > 0
+                  const int h = (int)(mw[j >> 1] << ((j & 1) ? 0 : 16)) >> 16;
+                  if (h <= 0) v[j] = 0.f;
+                }
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const int h = (int)(mw[j >> 1] << ((j & 1) ? 0 : 16)) >> 16;
+                const bool pos = !masked || h > 0;
+                if (!(pos && (c0 + j) < K)) v[j] = 0.f;
+              }
             }
-            *p0 = make_uint4(pack2<FMT>(v[0], v[1]), pack2<FMT>(v[2], v[3]), pack2<FMT>(v[4], v[5]), pack2<FMT>(v[6], v[7]));
-            *p1 = make_uint4(pack2<FMT>(v[8], v[9]), pack2<FMT>(v[10], v[11]), pack2<FMT>(v[12], v[13]), pack2<FMT>(v[14], v[15]));
-          }
+            store16<FMT>(xt, c0, r, v);
+          });
         } else if (a.dx) {
-          const int64_t row = row0 + r;
-          float* dxr = a.dx + row * ly.K;
-          for (int c0 = 0; c0 < Nx; c0 += 16) {
-            float v[16];
-            tmem_ld16(tmem_row + c0, v);
-            if (row < a.N) {
-#pragma unroll
-              for (int j = 0; j < 16; ++j)
-                if (c0 + j < ly.K) dxr[c0 + j] = v[j];
+          if (a.stage_ok) {
+            // dX_0 rows -> fp32 staging (row stride Nx+4 floats: conflict-free 16-byte stores) -> coalesced global
+            float* st = reinterpret_cast<float*>(base + a.stage_off);
+            const int stride = Nx + 4;
+            tmem_foreach16<kMaxWidth / 16>(tmem_row, Nx, Nx, [&](int c0, float v[16]) {
+              float4* p = reinterpret_cast<float4*>(st + r * stride + c0);
+              p[0] = make_float4(v[0], v[1], v[2], v[3]);
+              p[1] = make_float4(v[4], v[5], v[6], v[7]);
+              p[2] = make_float4(v[8], v[9], v[10], v[11]);
+              p[3] = make_float4(v[12], v[13], v[14], v[15]);
+            });
+            wg_sync(wg);
+            int64_t rows = a.N - row0;
+            if (rows > kTile) rows = kTile;
+            float* dst = a.dx + row0 * K0;
+            if (vec_dx && kshift >= 2) {
+              // K0 a power of two: thread -> (row, 16-byte column) by shifts, rows advance by 128 / (K0/4)
+              const int sh = kshift - 2, nv = 1 << sh;
+              const int c4 = tid & (nv - 1), step = kThreads >> sh;
+              for (int rr = tid >> sh; rr < (int)rows; rr += step)
+                reinterpret_cast<float4*>(dst)[rr * nv + c4] = *reinterpret_cast<const float4*>(st + rr * stride + c4 * 4);
+            } else if (vec_dx) {
+              const int nv = K0 >> 2, total = (int)rows * nv;
+              for (int e = tid; e < total; e += kThreads) {
+                const int rr = e / nv, c4 = e - rr * nv;
+                reinterpret_cast<float4*>(dst)[e] = *reinterpret_cast<const float4*>(st + rr * stride + c4 * 4);
+              }
+            } else {
+              const int total = (int)rows * K0;
+              for (int e = tid; e < total; e += kThreads) {
+                const int rr = e / K0, c = e - rr * K0;
+                dst[e] = st[rr * stride + c];
+              }
             }
+          } else {
+            float* dxr = a.dx + row * K0;
+            tmem_foreach16<kMaxWidth / 16>(tmem_row, Nx, Nx, [&](int c0, float v[16]) {
+              if (live) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                  if (c0 + j < K0) dxr[c0 + j] = v[j];
+              }
+            });
           }
         }
       }
@@ -600,6 +701,9 @@ int build_args(TcArgs& a, bool backward, int nl, const int32_t* dims, const floa
     a.layer[0].x_off = 0;
     a.x_off1 = tile_bytes;
     a.g_off = 0;
+    a.dy_off = 0;
+    a.stage_off = 0;
+    a.stage_ok = 0;
     per_wg = 2 * tile_bytes;
   } else {
     for (int l = 0; l < nl; ++l) {
@@ -611,11 +715,17 @@ int build_args(TcArgs& a, bool backward, int nl, const int32_t* dims, const floa
     }
     a.g_off = per_wg;
     per_wg += round_up((kMaxWidth / 8) * kActCs, 128);
+    a.dy_off = per_wg;
+    per_wg += round_up(kTile * a.layer[nl - 1].N * 4, 128);
     a.x_off1 = 0;
+    // dx staging aliases everything after X_0 (dead once the last batch of the tile has completed)
+    const int nx0 = round_up(a.layer[0].K, 16);
+    a.stage_off = nl >= 2 ? a.layer[1].x_off : 0;
+    a.stage_ok = nl >= 2 && kTile * (nx0 + 4) * 4 <= per_wg - a.stage_off;
   }
   a.wg_stride = per_wg;
   int nwg = 4;
-  while (nwg > 1 && (a.wg_base + nwg * per_wg > kSmemLimit - 1024 || nwg * kMaxWidth + dw_cols > 512)) --nwg;
+  while (nwg > 1 && (a.wg_base + nwg * per_wg > kSmemLimit - 1024 || nwg * kMaxWidth + dw_cols > 512)) nwg >>= 1;
   NKBS_CHECK_ARG(a.wg_base + nwg * per_wg <= kSmemLimit - 1024 && nwg * kMaxWidth + dw_cols <= 512,
                  "%s: does not fit (smem %d, tmem %d)", who, a.wg_base + per_wg, kMaxWidth + dw_cols);
   a.nwg = nwg;
@@ -651,7 +761,46 @@ int pick_grid(const TcArgs& a, int64_t N) {
   return (int)(groups < cap ? groups : cap);
 }
 
+template <bool BWD, int FMT, int NWG>
+int launch_one(const TcArgs& a, int64_t N, cudaStream_t st, const char* who) {
+  const int grid = pick_grid(a, N), threads = NWG * kThreads + 32;
+  if (BWD) {
+    if (set_smem(mlp_tc_bwd_kernel<FMT, NWG>, a.smem_bytes, who)) return -1;
+    mlp_tc_bwd_kernel<FMT, NWG><<<grid, threads, a.smem_bytes, st>>>(a);
+  } else {
+    if (set_smem(mlp_tc_fwd_kernel<FMT, NWG>, a.smem_bytes, who)) return -1;
+    mlp_tc_fwd_kernel<FMT, NWG><<<grid, threads, a.smem_bytes, st>>>(a);
+  }
+  return 0;
+}
+
+template <bool BWD>
+int launch_tc(const TcArgs& a, int64_t N, cudaStream_t st, const char* who) {
+  const int key = a.fmt * 8 + a.nwg;
+  switch (key) {
+    case 1: return launch_one<BWD, 0, 1>(a, N, st, who);
+    case 2: return launch_one<BWD, 0, 2>(a, N, st, who);
+    case 4: return launch_one<BWD, 0, 4>(a, N, st, who);
+    case 9: return launch_one<BWD, 1, 1>(a, N, st, who);
+    case 10: return launch_one<BWD, 1, 2>(a, N, st, who);
+    case 12: return launch_one<BWD, 1, 4>(a, N, st, who);
+  }
+  nkbs_set_error("%s: unsupported warpgroup count %d", who, a.nwg);
+  return -1;
+}
+
 }  // namespace
+
+#ifdef NKBS_TRACE
+extern "C" int nkbs_debug_trace(long long* host, int* n) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(host, g_trace, sizeof(long long) * 2 * 4096);
+  cudaMemcpyFromSymbol(n, g_trace_n, sizeof(int) * 2);
+  int z[2] = {0, 0};
+  cudaMemcpyToSymbol(g_trace_n, z, sizeof(z));
+  return 0;
+}
+#endif
 
 extern "C" int nkbs_mlp_tc_fwd(const float* x, int64_t N, int32_t nl, const int32_t* dims, const float* const* W,
                                const float* const* b, int32_t relu_mask, int32_t out_act, int32_t fmt,
@@ -667,14 +816,7 @@ extern "C" int nkbs_mlp_tc_fwd(const float* x, int64_t N, int32_t nl, const int3
   a.dy = nullptr;
   a.dx = nullptr;
   a.N = N;
-  const int grid = pick_grid(a, N), threads = a.nwg * kThreads + 32;
-  if (fmt == 0) {
-    if (set_smem(mlp_tc_fwd_kernel<0>, a.smem_bytes, "nkbs_mlp_tc_fwd")) return -1;
-    mlp_tc_fwd_kernel<0><<<grid, threads, a.smem_bytes, (cudaStream_t)stream>>>(a);
-  } else {
-    if (set_smem(mlp_tc_fwd_kernel<1>, a.smem_bytes, "nkbs_mlp_tc_fwd")) return -1;
-    mlp_tc_fwd_kernel<1><<<grid, threads, a.smem_bytes, (cudaStream_t)stream>>>(a);
-  }
+  if (launch_tc<false>(a, N, (cudaStream_t)stream, "nkbs_mlp_tc_fwd")) return -1;
   NKBS_CHECK_LAUNCH("nkbs_mlp_tc_fwd");
   return 0;
 }
@@ -699,14 +841,7 @@ extern "C" int nkbs_mlp_tc_bwd(const float* x, const float* dy, int64_t N, int32
   a.dy = dy;
   a.dx = dx;
   a.N = N;
-  const int grid = pick_grid(a, N), threads = a.nwg * kThreads + 32;
-  if (fmt == 0) {
-    if (set_smem(mlp_tc_bwd_kernel<0>, a.smem_bytes, "nkbs_mlp_tc_bwd")) return -1;
-    mlp_tc_bwd_kernel<0><<<grid, threads, a.smem_bytes, (cudaStream_t)stream>>>(a);
-  } else {
-    if (set_smem(mlp_tc_bwd_kernel<1>, a.smem_bytes, "nkbs_mlp_tc_bwd")) return -1;
-    mlp_tc_bwd_kernel<1><<<grid, threads, a.smem_bytes, (cudaStream_t)stream>>>(a);
-  }
+  if (launch_tc<true>(a, N, (cudaStream_t)stream, "nkbs_mlp_tc_bwd")) return -1;
   NKBS_CHECK_LAUNCH("nkbs_mlp_tc_bwd");
   return 0;
 }

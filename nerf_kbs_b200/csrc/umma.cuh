@@ -54,6 +54,19 @@ __device__ __forceinline__ void mma_f16(uint32_t d_tmem, uint64_t a_desc, uint64
       : "memory");
 }
 
+// one lane of the converged warp is elected (cute::elect_one_sync idiom); returns non-zero on that lane
+__device__ __forceinline__ uint32_t elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P;\n\t"
+      "elect.sync _|P, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, P;\n\t"
+      "}\n"
+      : "=r"(pred));
+  return pred;
+}
+
 // Warp-uniform issue: every lane of the (converged) issuer warp executes this with identical operands, only the
 // lane whose `leader` is non-zero issues.  Keeping the surrounding code convergent lets the compiler hold the
 // descriptors in uniform registers instead of electing a lane per instruction.
@@ -158,6 +171,39 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, float v[8]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
   for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// split form: issue the load, wait later (lets the load of the next column group overlap the current one's math)
+__device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t r[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// ---- misc memory helpers ----
+__device__ __forceinline__ float4 ldg_nc_v4(const float* p) {  // volatile: stays where it is written (prefetch)
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+// 4-byte asynchronous global -> shared copy; src_bytes = 0 writes zeros without reading
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc, uint32_t src_bytes) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+// barrier among the 128 threads of one warpgroup (ids 1..4; id 0 is __syncthreads)
+__device__ __forceinline__ void wg_sync(int wg) {
+  switch (wg) {  // immediate ids: a register id would make the compiler reserve all 16 hardware barriers
+    case 0: asm volatile("bar.sync 1, 128;" ::: "memory"); break;
+    case 1: asm volatile("bar.sync 2, 128;" ::: "memory"); break;
+    case 2: asm volatile("bar.sync 3, 128;" ::: "memory"); break;
+    default: asm volatile("bar.sync 4, 128;" ::: "memory"); break;
+  }
 }
 
 // round-to-nearest fp32 -> tf32 (the tensor core would otherwise truncate the low 13 mantissa bits)
