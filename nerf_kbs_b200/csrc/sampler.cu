@@ -158,6 +158,99 @@ __global__ void __launch_bounds__(kThreads) pdf_sample_kernel(const PdfArgs a) {
   }
 }
 
+// One warp per ray (S <= kWarpPdfMaxS).  Same arithmetic as pdf_sample_kernel: the normaliser and the running cdf
+// are sums of float terms held in double, which are exact for these magnitudes (terms >= histogram_padding / sum,
+// totals < 2^9: fewer than 53 significant bits), so the warp-parallel reduction / scan produce the very bits of the
+// sequential accumulation.  searchsorted(cdf, u, right) becomes a binary search in the warp's shared-memory cdf.
+constexpr int kWarpPdfMaxS = 1024;
+constexpr int kPdfWarps = 8;
+
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__global__ void __launch_bounds__(kPdfWarps * 32) pdf_sample_warp_kernel(const PdfArgs a) {
+  extern __shared__ float s_pdf[];  // per warp: v[S] then cdf[S+1]
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int S = a.S, nb = a.nb;
+  float* sv = s_pdf + wid * (2 * S + 1);
+  float* scdf = sv + S;
+  const float anneal = a.anneal_dev ? *a.anneal_dev : a.anneal;
+  const bool do_pow = anneal != 1.0f;
+  const float fS = (float)S, fnb = (float)nb;
+  const float eval_off = (float)(1.0 / (2.0 * (double)nb));
+  for (int64_t r = blockIdx.x * (int64_t)kPdfWarps + wid; r < a.R; r += (int64_t)gridDim.x * kPdfWarps) {
+    const float* w = a.weights + r * S;
+    const float* eb = a.sbins + r * (S + 1);
+    // pass 1: v = pow(w, anneal); weights_sum = sum(v + histogram_padding)
+    double dsum = 0.0;
+    for (int s = lane; s < S; s += 32) {
+      float v = w[s];
+      if (do_pow) v = powf(v, anneal);
+      sv[s] = v;
+      dsum += (double)__fadd_rn(v, a.hist_pad);
+    }
+    dsum = warp_sum_d(dsum);
+    float sum = (float)dsum;
+    const float padding = fmaxf(__fsub_rn(a.eps, sum), 0.f);
+    const float pad_each = __fdiv_rn(padding, fS);
+    sum = __fadd_rn(sum, padding);
+    // pass 2: cdf[k] = min(1, float(sum_{s<k} pdf_s)), running sum in double, 32 samples per round
+    double carry = 0.0;
+    if (lane == 0) scdf[0] = 0.f;
+    for (int s0 = 0; s0 < S; s0 += 32) {
+      const int s = s0 + lane;
+      double x = 0.0;
+      if (s < S) x = (double)__fdiv_rn(__fadd_rn(__fadd_rn(sv[s], a.hist_pad), pad_each), sum);
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        double n = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += n;
+      }
+      x += carry;
+      if (s < S) scdf[s + 1] = fminf(1.f, (float)x);
+      carry = __shfl_sync(0xffffffffu, x, 31);
+    }
+    __syncwarp();
+    const float s_near = spacing_fn(a.nears[r]), s_far = spacing_fn(a.fars[r]);
+    float rj = 0.f;
+    if (a.rand && !a.rand_per_bin) rj = __fdiv_rn(a.rand[r], fnb);
+    for (int i = lane; i < nb; i += 32) {
+      float u = a.u_base[i];
+      if (a.rand) {
+        if (a.rand_per_bin) rj = __fdiv_rn(a.rand[r * nb + i], fnb);
+        u = __fadd_rn(u, rj);
+      } else {
+        u = __fadd_rn(u, eval_off);
+      }
+      // idx = number of entries of cdf[0..S] that are <= u  (side="right")
+      int lo = 0, hi = S + 1;
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (scdf[mid] <= u) lo = mid + 1;
+        else hi = mid;
+      }
+      const int idx = lo;
+      const int below = idx - 1 < 0 ? 0 : (idx - 1 > S ? S : idx - 1);
+      const int above = idx > S ? S : idx;
+      const float g0 = scdf[below], g1 = scdf[above];
+      const float b0 = eb[below], b1 = eb[above];
+      float t = __fdiv_rn(__fsub_rn(u, g0), __fsub_rn(g1, g0));
+      if (t != t) t = 0.f;
+      else if (t > FLT_MAX) t = FLT_MAX;
+      else if (t < -FLT_MAX) t = -FLT_MAX;
+      t = fminf(fmaxf(t, 0.f), 1.f);
+      const float b = __fadd_rn(b0, __fmul_rn(t, __fsub_rn(b1, b0)));
+      a.out_sbins[r * nb + i] = b;
+      a.out_ebins[r * nb + i] = to_euclid(b, s_near, s_far);
+      if (a.out_inds) a.out_inds[r * nb + i] = idx;
+    }
+    __syncwarp();
+  }
+}
+
 }  // namespace
 
 extern "C" int nkbs_initial_sampler(int64_t R, int32_t S, const float* lin, const float* t_rand,
@@ -185,8 +278,20 @@ extern "C" int nkbs_pdf_sample(int64_t R, int32_t S, int32_t num_bins, const flo
   NKBS_CHECK_ARG(weights && sbins && u_base && nears && fars && out_sbins && out_ebins, "nkbs_pdf_sample: null argument");
   PdfArgs a{R, S, num_bins, weights, anneal, anneal_dev, histogram_padding, eps, sbins, u_base, rand, rand_per_bin,
             nears, fars, out_sbins, out_ebins, out_inds};
-  int64_t blocks = (R + kThreads - 1) / kThreads;
-  pdf_sample_kernel<<<(int)blocks, kThreads, 0, (cudaStream_t)stream>>>(a);
+  if (S <= kWarpPdfMaxS) {
+    int64_t blocks = (R + kPdfWarps - 1) / kPdfWarps;
+    int64_t cap = (int64_t)nkbs_num_sms() * 8;
+    size_t smem = (size_t)kPdfWarps * (2 * S + 1) * sizeof(float);
+    static thread_local size_t configured = 48 * 1024;
+    if (smem > configured) {
+      cudaFuncSetAttribute(pdf_sample_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      configured = smem;
+    }
+    pdf_sample_warp_kernel<<<(int)(blocks < cap ? blocks : cap), kPdfWarps * 32, smem, (cudaStream_t)stream>>>(a);
+  } else {
+    int64_t blocks = (R + kThreads - 1) / kThreads;
+    pdf_sample_kernel<<<(int)blocks, kThreads, 0, (cudaStream_t)stream>>>(a);
+  }
   NKBS_CHECK_LAUNCH("nkbs_pdf_sample");
   return 0;
 }
