@@ -277,6 +277,17 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def _finish(dist):
+    """Leave a multi-rank run: final barrier, then exit without tearing NCCL down (destroy_process_group was seen
+    to hang on a communicator that captured CUDA graphs still reference)."""
+    import torch
+    dist.barrier()
+    torch.cuda.synchronize()
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(0)
+
+
 # ------------------------------------------------------------------------------------------------
 def run_nkbs(args):
     import torch
@@ -288,8 +299,13 @@ def run_nkbs(args):
         raise SystemExit("bench.py: no CUDA device (the nkbs path has no CPU fallback)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    saved_stdout = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # NCCL prints its version banner on stdout: keep stdout clean for the one JSON line
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
     import nerf_kbs_b200 as nk
     from nerf_kbs_b200 import _lib
@@ -365,8 +381,7 @@ def run_nkbs(args):
 
     if rank != 0:
         if world > 1:
-            dist.barrier()
-            dist.destroy_process_group()
+            _finish(dist)
         return
 
     peaks = {}
@@ -420,10 +435,12 @@ def run_nkbs(args):
         "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks.summary(), "kernels": kernels,
         "final_loss": final_loss,
     }
+    if saved_stdout is not None:
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
     print(json.dumps(line))
     if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+        _finish(dist)
 
 
 if __name__ == "__main__":
