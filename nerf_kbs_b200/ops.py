@@ -79,7 +79,9 @@ class _HashEncode(torch.autograd.Function):
     def forward(ctx, table, mode, grid, norm, dedup_levels, x, origins, directions, starts, ends):
         feats, sel, xn, _ = encode_raw(mode, grid, norm, table, x, origins, directions, starts, ends)
         ctx.grid = grid
-        ctx.dedup = dedup_levels
+        # warp-level duplicate merging pays only where adjacent samples of a ray share cells: measured on B200
+        # (scripts/encode_bench.py) the best cut is the levels of resolution <= 32; -1 keeps that default
+        ctx.dedup = dedup_levels if dedup_levels >= 0 else sum(1 for sc in grid.scalings if sc <= 32.0)
         ctx.table_shape = table.shape
         ctx.save_for_backward(xn)
         ctx.mark_non_differentiable(sel, xn)
