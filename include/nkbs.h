@@ -66,6 +66,25 @@ int nkbs_mlp_tc_bwd(const float* x, const float* dy, int64_t N, int32_t nl, cons
                     int32_t fmt, const float* selector, float* dx, float* const* dW, float* const* db,
                     void* stream);
 
+/* K8 — the proposal density field fused: ray point -> contraction -> HashEncoding -> MLP(2L -> H -> 1, ReLU) ->
+ * trunc_exp * selector in one kernel per direction; only the density [N] is written.  fp32 throughout.
+ * replaces: HashMLPDensityField.get_density / density_fn (nerfacto.py:299-311,325-332; semantic_nerfw.py:119-137).
+ * mode 1: x = raw positions [N,3] (R = N, S = 1); mode 2: per-ray origins/directions + per-sample starts/ends.
+ * Supported shapes: (L=5,H=16) nerfacto proposals, (L=8,H=64) HashMLPDensityField defaults; others return an
+ * error (callers use K1 + K3).  W1 [H,2L], b1 [H], W2 [1,H], b2 [1] in torch nn.Linear layout.
+ * bwd recomputes the forward and ACCUMULATES into dtable [L*T,2], dW1, db1, dW2, db2. */
+int nkbs_density_fwd(int32_t mode, const float* x, const float* origins, const float* directions,
+                     const float* starts, const float* ends, int64_t R, int32_t S, int32_t contraction,
+                     const float* aabb, const float* table, const float* scalings, int32_t L, int32_t log2_T,
+                     const float* W1, const float* b1, const float* W2, const float* b2, int32_t H,
+                     float* density, void* stream);
+int nkbs_density_bwd(int32_t mode, const float* x, const float* origins, const float* directions,
+                     const float* starts, const float* ends, int64_t R, int32_t S, int32_t contraction,
+                     const float* aabb, const float* table, const float* scalings, int32_t L, int32_t log2_T,
+                     const float* W1, const float* b1, const float* W2, const float* b2, int32_t H,
+                     const float* ddensity, int32_t dedup_levels, float* dtable, float* dW1, float* db1,
+                     float* dW2, float* db2, void* stream);
+
 /* K4 — head-MLP input assembly  h = [SH16((d+1)/2) | geo | embedding row]  and its backward.
  * replaces: SHEncoding + Embedding + torch.cat in NerfactoField.get_outputs (nerfacto.py:398;
  *           semantic_nerfw.py:188).  cam NULL -> emb_const [emb_dim] is used (eval). */

@@ -24,6 +24,9 @@ SIGNATURES = {
     "nkbs_mlp_bwd": [_p, _p, _i64, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _p],
     "nkbs_mlp_tc_fwd": [_p, _i64, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p],
     "nkbs_mlp_tc_bwd": [_p, _p, _i64, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p],
+    "nkbs_density_fwd": [_i32, _p, _p, _p, _p, _p, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _i32, _p, _p],
+    "nkbs_density_bwd": [_i32, _p, _p, _p, _p, _p, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _i32, _p, _i32,
+                         _p, _p, _p, _p, _p, _p],
     "nkbs_assemble_fwd": [_i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32, _p, _p, _i64, _p, _p],
     "nkbs_assemble_bwd": [_i64, _i32, _i32, _i32, _i32, _p, _p, _p, _i32, _p, _p],
     "nkbs_initial_sampler": [_i64, _i32, _p, _p, _i32, _p, _p, _p, _p, _p],

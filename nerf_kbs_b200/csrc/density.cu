@@ -1,0 +1,354 @@
+// K8: the proposal density field in ONE pass per direction: ray point -> L-inf contraction -> hash-grid
+// encoding -> MLP (2L -> H -> 1, ReLU) -> trunc_exp * selector, with nothing but the density leaving the SM.
+// The unfused route (K1 + K3) writes and re-reads 2L+4 floats per sample; at the proposal levels that is 23 M
+// samples per 65 536-ray step.  H is 16 (nerfacto) or 64 (semantic-NeRF-W defaults): an MMA of N = 16 would use a
+// sixteenth of a tcgen05 tile, so these two layers run on the CUDA cores, weights broadcast from shared memory,
+// one thread per sample (adjacent lanes = adjacent samples of one ray, as in encode.cu).
+// Backward recomputes the forward, scatters the feature gradient straight into the table gradient (warp-merged
+// on the coarse levels) and reduces the weight gradients warp -> CTA -> global with a transposed shared-memory
+// sum (no shuffles: 32 rows x 32 lanes per pass).
+// Replaces HashMLPDensityField.get_density / density_fn reached from ref:nerfacto.py:299-311,325-332 and
+// ref:semantic_nerfw.py:119-137.
+#include "common.cuh"
+#include "encode.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+constexpr int kRedStride = 36;  // floats per row of the transposed-sum scratch: 16-byte rows, conflict-free both ways
+
+struct DensityArgs : SampleSource {
+  int64_t N;
+  LevelParams lv;
+  const float2* table;
+  const float* W1;  // [H, 2L]
+  const float* b1;  // [H]
+  const float* W2;  // [1, H]
+  const float* b2;  // [1]
+  float* density;   // [N]            (forward)
+  const float* ddensity;  // [N]      (backward)
+  float* dtable;    // [L*T, 2]
+  float* dW1;
+  float* db1;
+  float* dW2;
+  float* db2;
+  int dedup_levels;
+};
+
+// shared weights: W1 rows padded to KP floats (16-byte rows -> LDS.128 broadcasts), then b1, W2, b2
+template <int H, int L>
+struct Smem {
+  static constexpr int K = 2 * L;
+  static constexpr int KP = (K + 3) & ~3;
+  float w1[H * KP];
+  float b1[H];
+  float w2[H];
+  float b2;
+};
+
+template <int H, int L>
+__device__ __forceinline__ void stage(const DensityArgs& a, Smem<H, L>& s) {
+  constexpr int K = 2 * L, KP = Smem<H, L>::KP;
+  for (int e = threadIdx.x; e < H * KP; e += kThreads) {
+    int j = e / KP, i = e - j * KP;
+    s.w1[e] = i < K ? __ldg(a.W1 + j * K + i) : 0.f;
+  }
+  for (int j = threadIdx.x; j < H; j += kThreads) {
+    s.b1[j] = __ldg(a.b1 + j);
+    s.w2[j] = __ldg(a.W2 + j);
+  }
+  if (threadIdx.x == 0) s.b2 = __ldg(a.b2);
+}
+
+template <int L>
+__device__ __forceinline__ void encode_sample(const DensityArgs& a, const float* s_scale, float3 x, float (&f)[2 * L]) {
+  const uint32_t mask = a.lv.table_mask;
+#pragma unroll
+  for (int l = 0; l < L; ++l) {
+    Cell cl = nkbs_cell(x, s_scale[l]);
+    uint32_t h[8];
+    nkbs_corner_hashes(cl, mask, h);
+    const float2* tl = a.table + ((size_t)l << a.lv.log2_T);
+    float2 v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = __ldg(tl + h[k]);
+    float v0[8], v1[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      v0[k] = v[k].x;
+      v1[k] = v[k].y;
+    }
+    f[2 * l] = nkbs_trilerp(v0, cl.o[0], cl.o[1], cl.o[2]);
+    f[2 * l + 1] = nkbs_trilerp(v1, cl.o[0], cl.o[1], cl.o[2]);
+  }
+}
+
+// z_j = b1_j + sum_i W1[j][i] f_i  (i ascending, fused multiply-adds), hidden unit j of the first layer
+template <int H, int L>
+__device__ __forceinline__ float hidden_pre(const Smem<H, L>& s, const float (&f)[2 * L], int j) {
+  constexpr int K = 2 * L, KP = Smem<H, L>::KP;
+  float z = s.b1[j];
+  const float4* w = reinterpret_cast<const float4*>(s.w1 + j * KP);
+#pragma unroll
+  for (int q = 0; q < KP / 4; ++q) {
+    float4 wv = w[q];
+    if (4 * q + 0 < K) z = fmaf(wv.x, f[4 * q + 0 < K ? 4 * q + 0 : 0], z);
+    if (4 * q + 1 < K) z = fmaf(wv.y, f[4 * q + 1 < K ? 4 * q + 1 : 0], z);
+    if (4 * q + 2 < K) z = fmaf(wv.z, f[4 * q + 2 < K ? 4 * q + 2 : 0], z);
+    if (4 * q + 3 < K) z = fmaf(wv.w, f[4 * q + 3 < K ? 4 * q + 3 : 0], z);
+  }
+  return z;
+}
+
+template <int H, int L>
+__global__ void __launch_bounds__(kThreads) density_fwd_kernel(const DensityArgs a) {
+  __shared__ float s_scale[NKBS_MAX_LEVELS];
+  __shared__ __align__(16) Smem<H, L> s;
+  if (threadIdx.x < NKBS_MAX_LEVELS) s_scale[threadIdx.x] = a.lv.scale[threadIdx.x];
+  stage<H, L>(a, s);
+  __syncthreads();
+  for (int64_t n = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; n < a.N; n += (int64_t)gridDim.x * blockDim.x) {
+    float sel;
+    float3 x = load_sample_position(a, n, sel);
+    float f[2 * L];
+    encode_sample<L>(a, s_scale, x, f);
+    float out = s.b2;
+#pragma unroll
+    for (int j = 0; j < H; ++j) out = fmaf(s.w2[j], fmaxf(hidden_pre<H, L>(s, f, j), 0.f), out);
+    a.density[n] = expf(out) * sel;
+  }
+}
+
+// One pass of the transposed sum: every lane contributes `v` for 32 consecutive gradient rows (row r of the pass
+// is written by the caller through put(r, value)); afterwards lane i holds the warp total of row i.
+__device__ __forceinline__ float row_total(const float* scratch, int lane) {
+  const float4* p = reinterpret_cast<const float4*>(scratch + lane * kRedStride);
+  float t = 0.f;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    float4 v = p[q];
+    t += (v.x + v.y) + (v.z + v.w);
+  }
+  return t;
+}
+
+template <int H, int L>
+__global__ void __launch_bounds__(kThreads) density_bwd_kernel(const DensityArgs a) {
+  constexpr int K = 2 * L, KP = Smem<H, L>::KP;
+  // gradient rows, in this order: for each hidden unit j: dW1[j][0..K), db1[j], dW2[j]; then db2
+  constexpr int kPerJ = K + 2;
+  constexpr int kRows = H * kPerJ + 1;
+  constexpr int kPasses = (kRows + 31) / 32;
+  __shared__ float s_scale[NKBS_MAX_LEVELS];
+  __shared__ __align__(16) Smem<H, L> s;
+  __shared__ __align__(16) float s_red[kWarps][32 * kRedStride];
+  __shared__ float s_tot[kPasses * 32];
+  if (threadIdx.x < NKBS_MAX_LEVELS) s_scale[threadIdx.x] = a.lv.scale[threadIdx.x];
+  for (int e = threadIdx.x; e < kPasses * 32; e += kThreads) s_tot[e] = 0.f;
+  stage<H, L>(a, s);
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  float* red = s_red[wid];
+  const uint32_t mask = a.lv.table_mask;
+  float acc[kPasses];
+#pragma unroll
+  for (int p = 0; p < kPasses; ++p) acc[p] = 0.f;
+  const int64_t n_round = (a.N + 31) / 32 * 32;  // whole warps reach the collectives
+  for (int64_t n = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; n < n_round; n += (int64_t)gridDim.x * blockDim.x) {
+    const bool live = n < a.N;
+    float sel = 0.f;
+    float3 x = make_float3(0.f, 0.f, 0.f);
+    float g_up = 0.f;
+    if (live) {
+      x = load_sample_position(a, n, sel);
+      g_up = a.ddensity[n] * sel;
+    }
+    // a warp whose samples all lie outside the grid (or carry no gradient) has nothing to add
+    if (!__any_sync(0xffffffffu, g_up != 0.f)) continue;
+    float f[K];
+    encode_sample<L>(a, s_scale, x, f);
+    float z[H];
+    float out = s.b2;
+#pragma unroll
+    for (int j = 0; j < H; ++j) {
+      z[j] = hidden_pre<H, L>(s, f, j);
+      out = fmaf(s.w2[j], fmaxf(z[j], 0.f), out);
+    }
+    // trunc_exp backward (A.4): g * exp(clamp(raw, -15, 15))
+    const float g_out = g_up * expf(fminf(fmaxf(out, -15.f), 15.f));
+    float df[K];
+#pragma unroll
+    for (int i = 0; i < K; ++i) df[i] = 0.f;
+    // ---- weight gradients: rows are produced unit by unit and summed 32 rows at a time ----
+    int row = 0;  // compile-time after unrolling
+    int pass = 0;
+#pragma unroll
+    for (int j = 0; j < H; ++j) {
+      const float gh = z[j] > 0.f ? g_out * s.w2[j] : 0.f;
+      const float4* w = reinterpret_cast<const float4*>(s.w1 + j * KP);
+#pragma unroll
+      for (int q = 0; q < KP / 4; ++q) {
+        float4 wv = w[q];
+        if (4 * q + 0 < K) df[4 * q + 0 < K ? 4 * q + 0 : 0] = fmaf(gh, wv.x, df[4 * q + 0 < K ? 4 * q + 0 : 0]);
+        if (4 * q + 1 < K) df[4 * q + 1 < K ? 4 * q + 1 : 0] = fmaf(gh, wv.y, df[4 * q + 1 < K ? 4 * q + 1 : 0]);
+        if (4 * q + 2 < K) df[4 * q + 2 < K ? 4 * q + 2 : 0] = fmaf(gh, wv.z, df[4 * q + 2 < K ? 4 * q + 2 : 0]);
+        if (4 * q + 3 < K) df[4 * q + 3 < K ? 4 * q + 3 : 0] = fmaf(gh, wv.w, df[4 * q + 3 < K ? 4 * q + 3 : 0]);
+      }
+#pragma unroll
+      for (int c = 0; c < kPerJ; ++c) {
+        const float v = c < K ? gh * f[c < K ? c : 0] : (c == K ? gh : g_out * fmaxf(z[j], 0.f));
+        red[(row & 31) * kRedStride + lane] = v;
+        ++row;
+        if ((row & 31) == 0) {
+          __syncwarp();
+          acc[pass] += row_total(red, lane);
+          ++pass;
+          __syncwarp();
+        }
+      }
+    }
+    red[(row & 31) * kRedStride + lane] = g_out;  // db2
+    ++row;
+#pragma unroll
+    for (int r = row & 31; r < 32 && (row & 31) != 0; ++r) red[r * kRedStride + lane] = 0.f;
+    __syncwarp();
+    acc[kPasses - 1] += row_total(red, lane);
+    __syncwarp();
+    // ---- feature gradient -> table gradient ----
+#pragma unroll
+    for (int l = 0; l < L; ++l) {
+      Cell cl = nkbs_cell(x, s_scale[l]);
+      uint32_t h[8];
+      nkbs_corner_hashes(cl, mask, h);
+      float w[8];
+      nkbs_corner_weights(cl.o[0], cl.o[1], cl.o[2], w);
+      float* base = a.dtable + ((size_t)l << (a.lv.log2_T + 1));
+      if (l < a.dedup_levels) {
+        scatter_level_runs(base, cl, h, w, df[2 * l], df[2 * l + 1], lane);
+      } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          float gx = w[k] * df[2 * l], gy = w[k] * df[2 * l + 1];
+          if (gx != 0.f || gy != 0.f) nkbs_red_add_v2(base + 2 * (size_t)h[k], gx, gy);
+        }
+      }
+    }
+  }
+  // ---- warp totals -> CTA totals -> global ----
+#pragma unroll
+  for (int p = 0; p < kPasses; ++p)
+    if (acc[p] != 0.f) atomicAdd(&s_tot[p * 32 + lane], acc[p]);
+  __syncthreads();
+  for (int r = threadIdx.x; r < kRows; r += kThreads) {
+    const float v = s_tot[r];
+    if (v == 0.f) continue;
+    if (r == kRows - 1) {
+      atomicAdd(a.db2, v);
+    } else {
+      const int j = r / kPerJ, c = r - j * kPerJ;
+      if (c < K) atomicAdd(a.dW1 + j * K + c, v);
+      else if (c == K) atomicAdd(a.db1 + j, v);
+      else atomicAdd(a.dW2 + j, v);
+    }
+  }
+}
+
+template <typename Kern>
+int grid_for(Kern kern, int64_t N) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+  int64_t blocks = (N + kThreads - 1) / kThreads;
+  int64_t cap = (int64_t)nkbs_num_sms() * per_sm;
+  return (int)(blocks < cap ? blocks : cap);
+}
+
+int fill(DensityArgs& a, const char* who, int mode, const float* x, const float* origins, const float* directions,
+         const float* starts, const float* ends, int64_t R, int32_t S, int contraction, const float* aabb,
+         const float* table, const float* scalings, int L, int log2_T, const float* W1, const float* b1,
+         const float* W2, const float* b2, int H) {
+  NKBS_CHECK_ARG(mode == 1 || mode == 2, "%s: mode must be 1 (positions) or 2 (frustums), got %d", who, mode);
+  NKBS_CHECK_ARG(R >= 0 && S >= 1, "%s: bad sizes R=%lld S=%d", who, (long long)R, S);
+  NKBS_CHECK_ARG((H == 16 && L == 5) || (H == 64 && L == 8),
+                 "%s: fused shapes are (L=5,H=16) and (L=8,H=64); got L=%d H=%d (use encode + mlp)", who, L, H);
+  NKBS_CHECK_ARG(table && scalings && W1 && b1 && W2 && b2, "%s: null table/scalings/weights", who);
+  if (mode == 2)
+    NKBS_CHECK_ARG(origins && directions && starts && ends, "%s: frustum mode needs origins/directions/starts/ends", who);
+  else
+    NKBS_CHECK_ARG(x != nullptr || R == 0, "%s: null positions", who);
+  a.mode = mode;
+  a.x = x;
+  a.origins = origins;
+  a.directions = directions;
+  a.starts = starts;
+  a.ends = ends;
+  a.S = S;
+  a.N = R * (int64_t)S;
+  a.norm.contraction = contraction;
+  for (int i = 0; i < 3; ++i) {
+    a.norm.aabb_min[i] = aabb ? aabb[i] : 0.f;
+    a.norm.aabb_len[i] = aabb ? aabb[3 + i] - aabb[i] : 1.f;
+  }
+  NKBS_CHECK_ARG(fill_levels(a.lv, scalings, L, log2_T) == 0, "%s: unsupported grid L=%d log2_T=%d", who, L, log2_T);
+  a.table = reinterpret_cast<const float2*>(table);
+  a.W1 = W1;
+  a.b1 = b1;
+  a.W2 = W2;
+  a.b2 = b2;
+  a.density = nullptr;
+  a.ddensity = nullptr;
+  a.dtable = a.dW1 = a.db1 = a.dW2 = a.db2 = nullptr;
+  a.dedup_levels = 0;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int nkbs_density_fwd(int32_t mode, const float* x, const float* origins, const float* directions,
+                                const float* starts, const float* ends, int64_t R, int32_t S, int32_t contraction,
+                                const float* aabb, const float* table, const float* scalings, int32_t L,
+                                int32_t log2_T, const float* W1, const float* b1, const float* W2, const float* b2,
+                                int32_t H, float* density, void* stream) {
+  DensityArgs a;
+  if (fill(a, "nkbs_density_fwd", mode, x, origins, directions, starts, ends, R, S, contraction, aabb, table, scalings,
+           L, log2_T, W1, b1, W2, b2, H))
+    return -1;
+  if (a.N == 0) return 0;
+  NKBS_CHECK_ARG(density, "nkbs_density_fwd: null output");
+  a.density = density;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (H == 16)
+    density_fwd_kernel<16, 5><<<grid_for(density_fwd_kernel<16, 5>, a.N), kThreads, 0, st>>>(a);
+  else
+    density_fwd_kernel<64, 8><<<grid_for(density_fwd_kernel<64, 8>, a.N), kThreads, 0, st>>>(a);
+  NKBS_CHECK_LAUNCH("nkbs_density_fwd");
+  return 0;
+}
+
+extern "C" int nkbs_density_bwd(int32_t mode, const float* x, const float* origins, const float* directions,
+                                const float* starts, const float* ends, int64_t R, int32_t S, int32_t contraction,
+                                const float* aabb, const float* table, const float* scalings, int32_t L,
+                                int32_t log2_T, const float* W1, const float* b1, const float* W2, const float* b2,
+                                int32_t H, const float* ddensity, int32_t dedup_levels, float* dtable, float* dW1,
+                                float* db1, float* dW2, float* db2, void* stream) {
+  DensityArgs a;
+  if (fill(a, "nkbs_density_bwd", mode, x, origins, directions, starts, ends, R, S, contraction, aabb, table, scalings,
+           L, log2_T, W1, b1, W2, b2, H))
+    return -1;
+  if (a.N == 0) return 0;
+  NKBS_CHECK_ARG(ddensity && dtable && dW1 && db1 && dW2 && db2, "nkbs_density_bwd: null gradient buffers");
+  a.ddensity = ddensity;
+  a.dtable = dtable;
+  a.dW1 = dW1;
+  a.db1 = db1;
+  a.dW2 = dW2;
+  a.db2 = db2;
+  a.dedup_levels = dedup_levels < 0 ? L : dedup_levels;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (H == 16)
+    density_bwd_kernel<16, 5><<<grid_for(density_bwd_kernel<16, 5>, a.N), kThreads, 0, st>>>(a);
+  else
+    density_bwd_kernel<64, 8><<<grid_for(density_bwd_kernel<64, 8>, a.N), kThreads, 0, st>>>(a);
+  NKBS_CHECK_LAUNCH("nkbs_density_bwd");
+  return 0;
+}

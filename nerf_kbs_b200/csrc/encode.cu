@@ -2,21 +2,14 @@
 // Replaces nerfstudio HashEncoding.pytorch_fwd and its autograd, reached from
 // ref:nerfacto.py:275-311 and ref:semantic_nerfw.py:102-126.
 #include "common.cuh"
+#include "encode.cuh"
 
 namespace {
 
 constexpr int kEncThreads = 256;
 
-struct EncodeArgs {
-  int mode;  // 0: x normalised, 1: x raw positions, 2: frustum
-  const float* x;
-  const float* origins;
-  const float* directions;
-  const float* starts;
-  const float* ends;
+struct EncodeArgs : SampleSource {
   int64_t N;
-  int S;
-  NormParams norm;
   LevelParams lv;
   const float2* table;
   float* xn;
@@ -24,23 +17,6 @@ struct EncodeArgs {
   float* features;
   int64_t* indices;
 };
-
-__device__ __forceinline__ float3 load_sample_position(const EncodeArgs& a, int64_t n, float& sel) {
-  float3 p;
-  if (a.mode == 2) {
-    int64_t r = n / a.S;
-    float3 o = make_float3(a.origins[3 * r], a.origins[3 * r + 1], a.origins[3 * r + 2]);
-    float3 d = make_float3(a.directions[3 * r], a.directions[3 * r + 1], a.directions[3 * r + 2]);
-    p = nkbs_frustum_position(o, d, a.starts[n], a.ends[n]);
-  } else {
-    p = make_float3(a.x[3 * n], a.x[3 * n + 1], a.x[3 * n + 2]);
-  }
-  if (a.mode == 0) {
-    sel = 1.f;
-    return p;
-  }
-  return nkbs_normalise(p, a.norm, sel);
-}
 
 // One thread per sample; the level loop keeps 8 independent 8-byte gathers in flight per level and
 // the compiler overlaps two levels (unroll 2).  Level scales live in shared memory.
@@ -95,34 +71,6 @@ struct EncodeBwdArgs {
   int dedup_levels;       // levels below this index use warp-level duplicate merging
 };
 
-// Scatter of one corner: lanes of the warp that hit the same table row first merge their
-// contributions through shuffles (match.any) so that one 8-byte vector reduction leaves the warp per
-// distinct row.  Adjacent lanes are adjacent samples of one ray, so coarse levels collapse to 1-4
-// reductions per warp instead of 32.
-__device__ __forceinline__ void scatter_corner_dedup(float* base, uint32_t idx, float gx, float gy, int lane) {
-  unsigned peers = __match_any_sync(0xffffffffu, idx);
-  int leader = __ffs(peers) - 1;
-  unsigned rem = peers & ~(1u << leader);
-  // every lane walks its own peer list; only the leader's sum is used
-  float sx = gx, sy = gy;
-  unsigned any_rem = __ballot_sync(0xffffffffu, rem != 0 && lane == leader);
-  if (any_rem) {
-    // iterate as long as some leader still has peers to fold in
-    unsigned mine = (lane == leader) ? rem : 0u;
-    while (__any_sync(0xffffffffu, mine != 0)) {
-      int src = mine ? (__ffs(mine) - 1) : lane;
-      float ox = __shfl_sync(0xffffffffu, gx, src);
-      float oy = __shfl_sync(0xffffffffu, gy, src);
-      if (mine) {
-        sx += ox;
-        sy += oy;
-        mine &= mine - 1;
-      }
-    }
-  }
-  if (lane == leader && (sx != 0.f || sy != 0.f)) nkbs_red_add_v2(base + 2 * (size_t)idx, sx, sy);
-}
-
 __global__ void __launch_bounds__(kEncThreads) encode_bwd_kernel(const EncodeBwdArgs a) {
   __shared__ float s_scale[NKBS_MAX_LEVELS];
   if (threadIdx.x < NKBS_MAX_LEVELS) s_scale[threadIdx.x] = a.lv.scale[threadIdx.x];
@@ -146,8 +94,7 @@ __global__ void __launch_bounds__(kEncThreads) encode_bwd_kernel(const EncodeBwd
       float2 gl = live ? __ldg(g + l) : make_float2(0.f, 0.f);
       float* base = a.dtable + ((size_t)l << (a.lv.log2_T + 1));
       if (l < a.dedup_levels) {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) scatter_corner_dedup(base, h[k], w[k] * gl.x, w[k] * gl.y, lane);
+        scatter_level_runs(base, cl, h, w, gl.x, gl.y, lane);
       } else {
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
@@ -157,16 +104,6 @@ __global__ void __launch_bounds__(kEncThreads) encode_bwd_kernel(const EncodeBwd
       }
     }
   }
-}
-
-int fill_levels(LevelParams& lv, const float* scalings, int L, int log2_T) {
-  if (L < 1 || L > NKBS_MAX_LEVELS) return -1;
-  if (log2_T < 1 || log2_T > 30) return -1;
-  for (int i = 0; i < NKBS_MAX_LEVELS; ++i) lv.scale[i] = i < L ? scalings[i] : 0.f;
-  lv.num_levels = L;
-  lv.log2_T = (uint32_t)log2_T;
-  lv.table_mask = (1u << log2_T) - 1u;
-  return 0;
 }
 
 }  // namespace

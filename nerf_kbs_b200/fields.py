@@ -201,7 +201,28 @@ class HashMLPDensityField(_Field):
             self.linear = nn.Linear(self.encoding.get_out_dim(), 1)
         self._norm = _norm_spec(self.aabb, spatial_distortion)
 
+    def _fused_ok(self) -> bool:
+        if self.use_linear or not ops.fused_density_enabled():
+            return False
+        net = self.mlp_base[1]
+        return len(net.layers) == 2 and (self.encoding.grid.L, net.layers[0].out_features) in ops.FUSED_DENSITY_SHAPES
+
     def get_density(self, ray_samples: RaySamples) -> Tuple[torch.Tensor, None]:
+        if self._fused_ok():
+            # one kernel: ray point -> contraction -> hash grid -> MLP -> trunc_exp * selector (csrc/density.cu)
+            (W1, W2), (b1, b2) = self.mlp_base[1].weights_biases()
+            enc = self.encoding
+            pos = getattr(ray_samples, "_positions", None)
+            fi = _frustum_inputs(ray_samples) if pos is None else None
+            if fi is not None:
+                o, d, st, en = fi
+                density = ops.fused_density(enc.hash_table, enc.grid, self._norm, W1, b1, W2, b2, origins=o,
+                                            directions=d, starts=st, ends=en)
+            else:
+                if pos is None:
+                    pos = ray_samples.frustums.get_positions()
+                density = ops.fused_density(enc.hash_table, enc.grid, self._norm, W1, b1, W2, b2, positions=pos)
+            return density.reshape(*ray_samples.frustums.shape, 1), None
         feats, sel = self._encode(ray_samples, self.encoding, self._norm)
         if not self.use_linear:
             W, b = self.mlp_base[1].weights_biases()

@@ -79,9 +79,9 @@ class _HashEncode(torch.autograd.Function):
     def forward(ctx, table, mode, grid, norm, dedup_levels, x, origins, directions, starts, ends):
         feats, sel, xn, _ = encode_raw(mode, grid, norm, table, x, origins, directions, starts, ends)
         ctx.grid = grid
-        # warp-level duplicate merging pays only where adjacent samples of a ray share cells: measured on B200
-        # (scripts/encode_bench.py) the best cut is the levels of resolution <= 32; -1 keeps that default
-        ctx.dedup = dedup_levels if dedup_levels >= 0 else sum(1 for sc in grid.scalings if sc <= 32.0)
+        # run merging (segmented shuffle reduction, csrc/encode.cuh) costs a ballot on levels without duplicates and
+        # never loses on B200 (scripts/encode_bench.py sweep): -1 = every level
+        ctx.dedup = dedup_levels if dedup_levels >= 0 else grid.L
         ctx.table_shape = table.shape
         ctx.save_for_backward(xn)
         ctx.mark_non_differentiable(sel, xn)
@@ -116,6 +116,70 @@ def contract_encode(table, grid: GridSpec, norm: NormSpec, positions=None, origi
         feats, sel, _ = _HashEncode.apply(table, 2, grid, norm, dedup_levels, None, _c(origins), _c(directions),
                                           _c(starts), _c(ends))
     return feats, sel
+
+
+# ----------------------------------------------------------------------------------------------
+# K8 fused proposal density field (encode + two-layer MLP + trunc_exp * selector)
+# ----------------------------------------------------------------------------------------------
+FUSED_DENSITY_SHAPES = ((5, 16), (8, 64))  # (levels, hidden width) instantiated in csrc/density.cu
+_FUSED_DENSITY = {"enabled": True}
+
+
+def set_fused_density(enabled: bool) -> None:
+    """Route HashMLPDensityField through the one-kernel path (default) or through encode + mlp."""
+    _FUSED_DENSITY["enabled"] = bool(enabled)
+
+
+def fused_density_enabled() -> bool:
+    return _FUSED_DENSITY["enabled"]
+
+
+class _FusedDensity(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, table, W1, b1, W2, b2, grid, norm, dedup_levels, x, origins, directions, starts, ends):
+        table, W1, b1, W2, b2 = _c(table), _c(W1), _c(b1), _c(W2), _c(b2)
+        require_cuda(table, W1, x, origins, starts)
+        if x is not None:
+            mode, R, S, dev = 1, x.shape[0], 1, x.device
+        else:
+            mode, R, S, dev = 2, starts.shape[0], starts.shape[1], starts.device
+        H = W1.shape[0]
+        density = torch.empty((R * S,), device=dev, dtype=torch.float32)
+        aabb = host_floats(norm.aabb)
+        call("nkbs_density_fwd", mode, ptr(x), ptr(origins), ptr(directions), ptr(starts), ptr(ends), R, S,
+             int(norm.contraction), aabb, ptr(table), host_floats(grid.scalings), grid.L, grid.log2_T, ptr(W1), ptr(b1),
+             ptr(W2), ptr(b2), H, ptr(density), stream())
+        # proposal rays carry 96-256 samples: neighbouring samples share cells on every level of these grids
+        ctx.cfg = (mode, R, S, H, grid, norm, dedup_levels if dedup_levels >= 0 else grid.L)
+        ctx.save_for_backward(table, W1, b1, W2, b2, x, origins, directions, starts, ends)
+        return density
+
+    @staticmethod
+    def backward(ctx, ddensity):
+        mode, R, S, H, grid, norm, dedup = ctx.cfg
+        table, W1, b1, W2, b2, x, origins, directions, starts, ends = ctx.saved_tensors
+        ddensity = _c(ddensity)
+        dtable = torch.zeros_like(table)
+        dW1, db1, dW2, db2 = (torch.zeros_like(t) for t in (W1, b1, W2, b2))
+        call("nkbs_density_bwd", mode, ptr(x), ptr(origins), ptr(directions), ptr(starts), ptr(ends), R, S,
+             int(norm.contraction), host_floats(norm.aabb), ptr(table), host_floats(grid.scalings), grid.L, grid.log2_T,
+             ptr(W1), ptr(b1), ptr(W2), ptr(b2), H, ptr(ddensity), dedup, ptr(dtable), ptr(dW1), ptr(db1), ptr(dW2),
+             ptr(db2), stream())
+        return (dtable, dW1, db1, dW2, db2) + (None,) * 8
+
+
+def fused_density(table, grid: GridSpec, norm: NormSpec, W1, b1, W2, b2, positions=None, origins=None, directions=None,
+                  starts=None, ends=None, dedup_levels=-1):
+    """density [N] of the proposal field.  Either raw ``positions`` [N,3] or per-ray ``origins/directions`` [R,3]
+    with per-sample ``starts/ends`` [R,S].  Gradients: table and the four MLP tensors (sample positions are
+    detached in the reference path)."""
+    if (grid.L, W1.shape[0]) not in FUSED_DENSITY_SHAPES or W1.shape[1] != grid.out_dim or W2.shape[0] != 1:
+        raise ValueError(f"no fused density kernel for L={grid.L}, MLP {tuple(W1.shape)} -> {tuple(W2.shape)}")
+    if positions is not None:
+        return _FusedDensity.apply(table, W1, b1, W2, b2, grid, norm, dedup_levels, _c(positions).reshape(-1, 3), None,
+                                   None, None, None)
+    return _FusedDensity.apply(table, W1, b1, W2, b2, grid, norm, dedup_levels, None, _c(origins), _c(directions),
+                               _c(starts), _c(ends))
 
 
 # ----------------------------------------------------------------------------------------------
