@@ -85,6 +85,21 @@ int nkbs_density_bwd(int32_t mode, const float* x, const float* origins, const f
                      const float* ddensity, int32_t dedup_levels, float* dtable, float* dW1, float* db1,
                      float* dW2, float* db2, void* stream);
 
+/* N1 — per-ray training losses and their gradients in one ray-major pass (one warp per ray).
+ * replaces: losses.interlevel_loss / distortion_loss, MSELoss and CrossEntropyLoss as called at
+ *           nerfacto.py:468,483-489,505-515 and semantic_nerfw.py:253-279.
+ * final level: sdist [R,S+1] spacing-space bin edges, w [R,S]; dw [R,S] receives d(distortion)/dw (NULL skips it).
+ * proposal levels (HOST arrays of n_prop entries): S_prop, sdist_prop [R,Sp+1], w_prop [R,Sp], dw_prop [R,Sp]
+ * receives d(interlevel)/dw_prop.  rgb/image/drgb [R,3] (rgb NULL skips the MSE); logits/dlogits [R,C], labels [R]
+ * int64 (logits NULL skips the cross-entropy; dlogits = softmax - onehot, zero rows for ignore_index: the caller
+ * divides by the count).  out [5], ACCUMULATED into: mean squared colour error, interlevel loss (sum over levels
+ * of the [R,S] means), distortion loss (mean over rays), cross-entropy SUM, number of counted labels. */
+int nkbs_ray_losses(int64_t R, int32_t S, const float* sdist, const float* w, float* dw, int32_t n_prop,
+                    const int32_t* S_prop, const float* const* sdist_prop, const float* const* w_prop,
+                    float* const* dw_prop, const float* rgb, const float* image, float* drgb, const float* logits,
+                    const int64_t* labels, int32_t C, int64_t ignore_index, float* dlogits, float* out,
+                    void* stream);
+
 /* K4 — head-MLP input assembly  h = [SH16((d+1)/2) | geo | embedding row]  and its backward.
  * replaces: SHEncoding + Embedding + torch.cat in NerfactoField.get_outputs (nerfacto.py:398;
  *           semantic_nerfw.py:188).  cam NULL -> emb_const [emb_dim] is used (eval). */

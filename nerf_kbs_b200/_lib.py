@@ -27,6 +27,7 @@ SIGNATURES = {
     "nkbs_density_fwd": [_i32, _p, _p, _p, _p, _p, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _i32, _p, _p],
     "nkbs_density_bwd": [_i32, _p, _p, _p, _p, _p, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _i32, _p, _i32,
                          _p, _p, _p, _p, _p, _p],
+    "nkbs_ray_losses": [_i64, _i32, _p, _p, _p, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _i64, _p, _p, _p],
     "nkbs_assemble_fwd": [_i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32, _p, _p, _i64, _p, _p],
     "nkbs_assemble_bwd": [_i64, _i32, _i32, _i32, _i32, _p, _p, _p, _i32, _p, _p],
     "nkbs_initial_sampler": [_i64, _i32, _p, _p, _i32, _p, _p, _p, _p, _p],

@@ -1,9 +1,11 @@
-"""Losses adjacent to the hot path: interlevel (proposal) loss and distortion loss as
-called at ref:nerfacto.py:483-489 and ref:semantic_nerfw.py:253-257.  Round-1 status: expressed with
-torch CUDA ops (library kernels); a fused ray-major kernel is the N1 follow-up."""
+"""Losses adjacent to the hot path: interlevel (proposal) loss, distortion loss, colour MSE
+and semantic cross-entropy as called at ref:nerfacto.py:468,483-515 and ref:semantic_nerfw.py:253-279.  All of them
+run in one ray-major CUDA kernel (csrc/losses.cu, ``ops.ray_losses``) that also writes the gradients."""
 from __future__ import annotations
 
 import torch
+
+from . import ops
 
 
 def ray_samples_to_sdist(ray_samples):
@@ -12,42 +14,34 @@ def ray_samples_to_sdist(ray_samples):
     return torch.cat([ray_samples.spacing_starts[..., 0], ray_samples.spacing_ends[..., -1:, 0]], dim=-1)
 
 
-def outer(t0_starts, t0_ends, t1_starts, t1_ends, y1):
-    cy1 = torch.cat([torch.zeros_like(y1[..., :1]), torch.cumsum(y1, dim=-1)], dim=-1)
-    idx_lo = torch.searchsorted(t1_starts.contiguous(), t0_starts.contiguous(), side="right") - 1
-    idx_lo = torch.clamp(idx_lo, min=0, max=y1.shape[-1] - 1)
-    idx_hi = torch.searchsorted(t1_ends.contiguous(), t0_ends.contiguous(), side="right")
-    idx_hi = torch.clamp(idx_hi, min=0, max=y1.shape[-1] - 1)
-    cy1_lo = torch.take_along_dim(cy1[..., :-1], idx_lo, dim=-1)
-    cy1_hi = torch.take_along_dim(cy1[..., 1:], idx_hi, dim=-1)
-    return cy1_hi - cy1_lo
-
-
-def lossfun_outer(t, w, t_env, w_env):
-    w_outer = outer(t[..., :-1], t[..., 1:], t_env[..., :-1], t_env[..., 1:], w_env)
-    return torch.clip(w - w_outer, min=0) ** 2 / (w + 1e-7)
+def _w(weights):
+    return weights[..., 0] if weights.dim() == 3 else weights
 
 
 def interlevel_loss(weights_list, ray_samples_list):
-    c = ray_samples_to_sdist(ray_samples_list[-1]).detach()
-    w = weights_list[-1][..., 0].detach()
-    loss = 0.0
-    for ray_samples, weights in zip(ray_samples_list[:-1], weights_list[:-1]):
-        cp = ray_samples_to_sdist(ray_samples)
-        wp = weights[..., 0]
-        loss = loss + torch.mean(lossfun_outer(c, w, cp, wp))
-    return loss
-
-
-def lossfun_distortion(t, w):
-    ut = (t[..., 1:] + t[..., :-1]) / 2
-    dut = torch.abs(ut[..., :, None] - ut[..., None, :])
-    loss_inter = torch.sum(w * torch.sum(w[..., None, :] * dut, dim=-1), dim=-1)
-    loss_intra = torch.sum(w**2 * (t[..., 1:] - t[..., :-1]), dim=-1) / 3
-    return loss_inter + loss_intra
+    """Sum over proposal levels of mean(lossfun_outer(final histogram, proposal histogram))."""
+    _, inter, _, _ = ops.ray_losses(
+        w_final=_w(weights_list[-1]).detach(), sdist_final=ray_samples_to_sdist(ray_samples_list[-1]).detach(),
+        w_props=[_w(w) for w in weights_list[:-1]], sdist_props=[ray_samples_to_sdist(rs) for rs in ray_samples_list[:-1]],
+        want_distortion=False)
+    return inter
 
 
 def distortion_loss(weights_list, ray_samples_list):
-    c = ray_samples_to_sdist(ray_samples_list[-1])
-    w = weights_list[-1][..., 0]
-    return torch.mean(lossfun_distortion(c, w))
+    """mean over rays of lossfun_distortion(final bins, final weights)."""
+    _, _, dist, _ = ops.ray_losses(w_final=_w(weights_list[-1]), sdist_final=ray_samples_to_sdist(ray_samples_list[-1]))
+    return dist
+
+
+def training_losses(weights_list, ray_samples_list, rgb=None, image=None, logits=None, labels=None, ignore_index=-100):
+    """Every per-ray term of a training step in ONE launch: (rgb_mse, interlevel, distortion, cross_entropy)."""
+    return ops.ray_losses(
+        w_final=_w(weights_list[-1]), sdist_final=ray_samples_to_sdist(ray_samples_list[-1]),
+        w_props=[_w(w) for w in weights_list[:-1]], sdist_props=[ray_samples_to_sdist(rs) for rs in ray_samples_list[:-1]],
+        rgb=rgb, image=image, logits=logits, labels=labels, ignore_index=ignore_index)
+
+
+def pixel_losses(rgb=None, image=None, logits=None, labels=None, ignore_index=-100):
+    """Colour MSE and semantic cross-entropy only (evaluation: no weights lists)."""
+    mse, _, _, ce = ops.ray_losses(rgb=rgb, image=image, logits=logits, labels=labels, ignore_index=ignore_index)
+    return mse, ce

@@ -16,7 +16,7 @@ from torch import nn
 
 from . import ops
 from .fields import FieldHeadNames, HashMLPDensityField, NerfactoField, SceneContraction
-from .losses import distortion_loss, interlevel_loss
+from .losses import pixel_losses, training_losses
 from .rays import RayBundle
 from .renderers import NearFarCollider
 from .samplers import ProposalNetworkSampler
@@ -149,17 +149,20 @@ class NerfactoModel(_ModelBase):
         return outputs
 
     def get_loss_dict(self, outputs, batch):
-        """ref:nerfacto.py:465-515."""
+        """ref:nerfacto.py:465-515.  One kernel launch computes every term and its gradient (csrc/losses.cu)."""
         c = self.config
-        loss = {"rgb_loss": nn.functional.mse_loss(batch["image"], outputs["rgb"])}
+        sem = dict(logits=outputs["semantics"], labels=batch["semantics_label"],
+                   ignore_index=c.num_semantic_classes) if c.use_semantic else {}
         if self.training:
-            loss["interlevel_loss"] = c.interlevel_loss_mult * interlevel_loss(
-                outputs["weights_list"], outputs["ray_samples_list"])
-            loss["distortion_loss"] = c.distortion_loss_mult * distortion_loss(
-                outputs["weights_list"], outputs["ray_samples_list"])
+            mse, inter, dist, ce = training_losses(outputs["weights_list"], outputs["ray_samples_list"],
+                                                   rgb=outputs["rgb"], image=batch["image"], **sem)
+            loss = {"rgb_loss": mse, "interlevel_loss": c.interlevel_loss_mult * inter,
+                    "distortion_loss": c.distortion_loss_mult * dist}
+        else:
+            mse, ce = pixel_losses(rgb=outputs["rgb"], image=batch["image"], **sem)
+            loss = {"rgb_loss": mse}
         if c.use_semantic:
-            loss["semantics_loss"] = c.semantic_loss_weight * nn.functional.cross_entropy(
-                outputs["semantics"], batch["semantics_label"], ignore_index=c.num_semantic_classes)
+            loss["semantics_loss"] = c.semantic_loss_weight * ce
         return loss
 
 
@@ -230,22 +233,27 @@ class SemanticNerfWModel(_ModelBase):
         return outputs
 
     def get_loss_dict(self, outputs, batch):
-        """ref:semantic_nerfw.py:249-279."""
+        """ref:semantic_nerfw.py:249-279.  One kernel launch for the per-ray terms (csrc/losses.cu); the
+        uncertainty-weighted colour loss of the transient branch stays a few torch ops on [R] tensors."""
         c = self.config
         image = batch["image"]
+        transient = self.training and c.use_transient_embedding
+        pix = dict(logits=outputs["semantics"], labels=batch["semantics_label"])
+        if not transient:
+            pix.update(rgb=outputs["rgb"], image=image)
         loss = {}
         if self.training:
-            loss["interlevel_loss"] = c.interlevel_loss_mult * interlevel_loss(
-                outputs["weights_list"], outputs["ray_samples_list"])
-            loss["distortion_loss"] = c.distortion_loss_mult * distortion_loss(
-                outputs["weights_list"], outputs["ray_samples_list"])
-        if self.training and c.use_transient_embedding:
+            mse, inter, dist, ce = training_losses(outputs["weights_list"], outputs["ray_samples_list"], **pix)
+            loss["interlevel_loss"] = c.interlevel_loss_mult * inter
+            loss["distortion_loss"] = c.distortion_loss_mult * dist
+        else:
+            mse, ce = pixel_losses(**pix)
+        if transient:
             betas = outputs["uncertainty"]
             loss["uncertainty_loss"] = 3 + torch.log(betas).mean()
             loss["density_loss"] = 0.01 * outputs["density_transient"].mean()
             loss["rgb_loss"] = (((image - outputs["rgb"]) ** 2).sum(-1) / (betas[..., 0] ** 2)).mean()
         else:
-            loss["rgb_loss"] = nn.functional.mse_loss(image, outputs["rgb"])
-        loss["semantics_loss"] = c.semantic_loss_weight * nn.functional.cross_entropy(
-            outputs["semantics"], batch["semantics_label"])
+            loss["rgb_loss"] = mse
+        loss["semantics_loss"] = c.semantic_loss_weight * ce
         return loss

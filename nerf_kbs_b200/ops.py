@@ -439,3 +439,64 @@ def composite(density=None, weights=None, rgb=None, sem=None, starts=None, ends=
     if sem_o is not None:
         out["semantics"] = sem_o
     return out
+
+
+# ----------------------------------------------------------------------------------------------
+# N1 per-ray losses (interlevel, distortion, colour MSE, semantic cross-entropy) in one launch
+# ----------------------------------------------------------------------------------------------
+class _RayLosses(torch.autograd.Function):
+    """Returns (rgb_mse, interlevel, distortion, cross_entropy) as 0-dim tensors; terms whose inputs are absent
+    come back as zeros.  Differentiable inputs: final weights (distortion), proposal weights (interlevel), rgb,
+    logits.  The final weights enter the interlevel term detached, as in the reference."""
+
+    @staticmethod
+    def forward(ctx, meta, w_final, rgb, logits, *w_props):
+        sdist, sdist_props, image, labels, ignore_index, want_dist = meta
+        dev = (w_final if w_final is not None else (rgb if rgb is not None else logits)).device
+        require_cuda(w_final, rgb, logits, *w_props)
+        out = torch.zeros(5, device=dev, dtype=torch.float32)
+        hist = w_final is not None
+        R = (w_final if hist else (rgb if rgb is not None else logits)).shape[0]
+        S = w_final.shape[1] if hist else 1
+        w_final = _c(w_final)
+        dw = torch.empty_like(w_final) if (hist and want_dist) else None
+        w_props = [_c(t) for t in w_props]
+        sdist_props = [_c(t) for t in sdist_props]
+        dw_props = [torch.empty_like(t) for t in w_props]
+        rgb, image = _c(rgb), _c(image)
+        drgb = torch.empty_like(rgb) if rgb is not None else None
+        logits = _c(logits)
+        dlogits = torch.empty_like(logits) if logits is not None else None
+        C = logits.shape[1] if logits is not None else 0
+        call("nkbs_ray_losses", R, S, ptr(_c(sdist)), ptr(w_final), ptr(dw), len(w_props),
+             host_i32([t.shape[1] for t in w_props]), host_ptrs(sdist_props), host_ptrs(w_props), host_ptrs(dw_props),
+             ptr(rgb), ptr(image), ptr(drgb), ptr(logits), ptr(_c(labels, torch.int64)), C, int(ignore_index),
+             ptr(dlogits), ptr(out), stream())
+        ctx.n_prop = len(w_props)
+        ctx.has = (dw is not None, drgb is not None, dlogits is not None)
+        ctx.save_for_backward(*[t for t in (dw, drgb, dlogits, out) if t is not None], *dw_props)
+        ce = out[3] / torch.clamp(out[4], min=1.0) if logits is not None else out[3]
+        return out[0], out[1], out[2], ce
+
+    @staticmethod
+    def backward(ctx, g_rgb, g_inter, g_dist, g_ce):
+        saved = list(ctx.saved_tensors)
+        has_dw, has_rgb, has_log = ctx.has
+        dw = saved.pop(0) if has_dw else None
+        drgb = saved.pop(0) if has_rgb else None
+        dlogits = saved.pop(0) if has_log else None
+        out = saved.pop(0)
+        dw_props = saved
+        g_w = dw * g_dist if (dw is not None and g_dist is not None) else None
+        g_c = drgb * g_rgb if (drgb is not None and g_rgb is not None) else None
+        g_l = dlogits * (g_ce / torch.clamp(out[4], min=1.0)) if (dlogits is not None and g_ce is not None) else None
+        g_p = [t * g_inter if g_inter is not None else None for t in dw_props]
+        return (None, g_w, g_c, g_l, *g_p)
+
+
+def ray_losses(w_final=None, sdist_final=None, w_props=(), sdist_props=(), rgb=None, image=None, logits=None,
+               labels=None, ignore_index=-100, want_distortion=True):
+    """One launch for every per-ray loss term.  ``w_*`` are [R,S] weights, ``sdist_*`` [R,S+1] spacing-space bin
+    edges; returns (rgb_mse, interlevel, distortion, cross_entropy)."""
+    meta = (sdist_final, list(sdist_props), image, labels, ignore_index, want_distortion)
+    return _RayLosses.apply(meta, w_final, rgb, logits, *w_props)

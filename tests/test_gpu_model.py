@@ -115,8 +115,10 @@ def test_proposal_update_gating():
         jit = make_jitter(R, seed=step)
         sum(nm.get_loss_dict(nm(to_nk_bundle(rb), jitter=[j.to(DEV) for j in jit]), {k: v.to(DEV) for k, v in batch.items()}).values()).backward()
         sum(om.get_loss_dict(om(rb, jitter=jit), batch).values()).backward()
-        g_n = nm.proposal_networks[0].encoding.hash_table.grad
-        g_o = om.proposal_networks[0].encoding.hash_table.grad
+        # level 1: at the first steps the level-0 envelope already covers the final histogram up to rounding noise,
+        # so whether its gradient is exactly zero depends on the summation order
+        g_n = nm.proposal_networks[1].encoding.hash_table.grad
+        g_o = om.proposal_networks[1].encoding.hash_table.grad
         pattern.append((g_n is not None and g_n.abs().sum().item() > 0, g_o is not None and g_o.abs().sum().item() > 0))
         nm.after_step(step), om.after_step(step)
     assert all(a == b for a, b in pattern), pattern
