@@ -100,6 +100,32 @@ int nkbs_ray_losses(int64_t R, int32_t S, const float* sdist, const float* w, fl
                     const int64_t* labels, int32_t C, int64_t ignore_index, float* dlogits, float* out,
                     void* stream);
 
+/* N3 — pinhole ray generation: ray_indices [N,3] int64 (camera, row, col), c2w [num_cameras,3,4], intrinsics
+ * [num_cameras,4] = fx, fy, cx, cy.  Pixel centres at +0.5; camera looks down -z with +y up; directions are unit
+ * vectors, directions_norm their length before normalisation, pixel_area the product of the distances to the rays
+ * one pixel right and one pixel down (all three optional outputs may be NULL).
+ * replaces: nerfstudio RayGenerator / Cameras.generate_rays as driven by dataparser/datamanager_z.py:96,252-278. */
+int nkbs_generate_rays(int64_t N, const int64_t* ray_indices, const float* c2w, const float* intrinsics,
+                       int64_t num_cameras, float* origins, float* directions, float* directions_norm,
+                       float* pixel_area, int64_t* camera_indices, void* stream);
+
+/* N3 — masked pixel sampling: keeps, in order, the candidates (image_indices[m], pixel_indices[m]) whose byte in
+ * masks [num_images, pixels_per_image] is non-zero, up to R of them; if fewer survive they repeat cyclically.
+ * *n_kept (device int32) receives the number of survivors.  replaces: dataparser/dataset_z.py:180-191. */
+int nkbs_compact_masked(int64_t M, const int64_t* image_indices, const int64_t* pixel_indices, const uint8_t* masks,
+                        int64_t pixels_per_image, int64_t R, int64_t* out_image, int64_t* out_pixel, int32_t* n_kept,
+                        void* stream);
+
+/* N3/N4 — semantic palette.  palette: device int32 [1 + 256] = {n, r|g<<8|b<<16 per class}.
+ * color_to_label: rgb uint8 [N,3] -> labels int64 [N] (default_label when the colour is not in the palette);
+ * replaces the per-pixel color2label loop of nerfacto.py:508-512.
+ * semantic_colormap: logits [N,C] -> argmax labels (int64, may be NULL) and palette colours uint8 [N,3] (may be
+ * NULL); replaces argmax(softmax) + colormap lookup of nerfacto.py:574-578 / semantic_nerfw.py:346-351. */
+int nkbs_color_to_label(int64_t N, const uint8_t* rgb, const void* palette, int64_t default_label, int64_t* labels,
+                        void* stream);
+int nkbs_semantic_colormap(int64_t N, int32_t C, const float* logits, const void* palette, int64_t* labels,
+                           uint8_t* rgb, void* stream);
+
 /* K4 — head-MLP input assembly  h = [SH16((d+1)/2) | geo | embedding row]  and its backward.
  * replaces: SHEncoding + Embedding + torch.cat in NerfactoField.get_outputs (nerfacto.py:398;
  *           semantic_nerfw.py:188).  cam NULL -> emb_const [emb_dim] is used (eval). */

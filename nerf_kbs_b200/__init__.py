@@ -2,8 +2,10 @@
 (see DESIGN.md).  Importing the package does not need a GPU; calling an operator does."""
 from .fields import (FieldHeadNames, HashEncoding, HashMLPDensityField, MLP, NerfactoField,  # noqa: F401
                      SceneContraction)
+from .data import Cameras, RayGenerator, SemanticPalette, image_ray_indices, sample_masked_pixels  # noqa: F401
 from .models import ModelConfig, NerfactoModel, SemanticNerfWModel  # noqa: F401
 from .rays import Frustums, RayBundle, RaySamples  # noqa: F401
+from .render import get_outputs_for_camera_ray_bundle, render_camera  # noqa: F401
 from .renderers import (AccumulationRenderer, DepthRenderer, NearFarCollider, RGBRenderer,  # noqa: F401
                         SemanticRenderer, UncertaintyRenderer)
 from .samplers import PDFSampler, ProposalNetworkSampler, UniformLinDispPiecewiseSampler  # noqa: F401

@@ -1,0 +1,220 @@
+// N3/N4: the data-side and image-side neighbours of the ray-batch path, on the device:
+//   nkbs_generate_rays      pinhole rays (origins, unit directions, directions_norm, pixel_area) from (camera,row,col)
+//   nkbs_compact_masked     stable compaction of candidate pixels whose motion mask is non-zero to exactly R rays
+//   nkbs_color_to_label     RGB semantic colour -> class label through a palette (replaces a per-pixel Python loop)
+//   nkbs_semantic_colormap  argmax over class logits -> palette colour (the rendered semantic image)
+// Replaces nerfstudio RayGenerator / Cameras.generate_rays as driven by ref:dataparser/datamanager_z.py:96,252-278,
+// the masked sampling of ref:dataparser/dataset_z.py:180-191, the color2label loop of ref:nerfacto.py:508-512 and
+// the argmax + colormap of ref:nerfacto.py:574-578 / ref:semantic_nerfw.py:346-351.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+
+struct RayGenArgs {
+  int64_t N;
+  const int64_t* idx;     // [N,3] camera, row, col
+  const float* c2w;       // [num_cameras,3,4]
+  const float* intr;      // [num_cameras,4] fx, fy, cx, cy
+  int64_t num_cameras;
+  float* origins;         // [N,3]
+  float* directions;      // [N,3] unit
+  float* dnorm;           // [N] or null
+  float* pixel_area;      // [N] or null
+  int64_t* cam_out;       // [N] or null
+};
+
+__device__ __forceinline__ float3 rotate(const float* R, float x, float y, float z) {
+  // sum(dir[None, :] * R[3x3 of the 3x4], -1): row i = R[i,0] x + R[i,1] y + R[i,2] z, left to right
+  float3 o;
+  o.x = __fadd_rn(__fadd_rn(__fmul_rn(x, R[0]), __fmul_rn(y, R[1])), __fmul_rn(z, R[2]));
+  o.y = __fadd_rn(__fadd_rn(__fmul_rn(x, R[4]), __fmul_rn(y, R[5])), __fmul_rn(z, R[6]));
+  o.z = __fadd_rn(__fadd_rn(__fmul_rn(x, R[8]), __fmul_rn(y, R[9])), __fmul_rn(z, R[10]));
+  return o;
+}
+__device__ __forceinline__ float norm3(float3 v) {
+  return sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(v.x, v.x), __fmul_rn(v.y, v.y)), __fmul_rn(v.z, v.z)));
+}
+
+__global__ void __launch_bounds__(kThreads) generate_rays_kernel(const RayGenArgs a) {
+  for (int64_t n = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; n < a.N; n += (int64_t)gridDim.x * blockDim.x) {
+    int64_t cam = a.idx[3 * n];
+    cam = cam < 0 ? 0 : (cam >= a.num_cameras ? a.num_cameras - 1 : cam);
+    const float py = (float)a.idx[3 * n + 1] + 0.5f, px = (float)a.idx[3 * n + 2] + 0.5f;
+    const float fx = a.intr[4 * cam], fy = a.intr[4 * cam + 1], cx = a.intr[4 * cam + 2], cy = a.intr[4 * cam + 3];
+    const float* M = a.c2w + 12 * cam;
+    // camera looks down -z, y up (nerfstudio / OpenGL convention); neighbours one pixel right and one pixel down
+    const float x0 = (px - cx) / fx, y0 = (py - cy) / fy;
+    const float x1 = (px + 1.f - cx) / fx, y1 = (py + 1.f - cy) / fy;
+    float3 d = rotate(M, x0, -y0, -1.f);
+    float3 dx = rotate(M, x1, -y0, -1.f);
+    float3 dy = rotate(M, x0, -y1, -1.f);
+    const float n0 = norm3(d), n1 = norm3(dx), n2 = norm3(dy);
+    d = make_float3(d.x / n0, d.y / n0, d.z / n0);
+    dx = make_float3(dx.x / n1, dx.y / n1, dx.z / n1);
+    dy = make_float3(dy.x / n2, dy.y / n2, dy.z / n2);
+    a.origins[3 * n] = M[3];
+    a.origins[3 * n + 1] = M[7];
+    a.origins[3 * n + 2] = M[11];
+    a.directions[3 * n] = d.x;
+    a.directions[3 * n + 1] = d.y;
+    a.directions[3 * n + 2] = d.z;
+    if (a.dnorm) a.dnorm[n] = n0;
+    if (a.pixel_area) {
+      const float ax = norm3(make_float3(dx.x - d.x, dx.y - d.y, dx.z - d.z));
+      const float ay = norm3(make_float3(dy.x - d.x, dy.y - d.y, dy.z - d.z));
+      a.pixel_area[n] = ax * ay;
+    }
+    if (a.cam_out) a.cam_out[n] = cam;
+  }
+}
+
+// Stable compaction by ONE CTA (candidate lists are ~R long, a few thousand): out[k] = k-th candidate whose mask
+// byte is non-zero; if fewer than R survive the survivors repeat cyclically (count returned in *n_kept).
+__global__ void __launch_bounds__(1024) compact_masked_kernel(int64_t M, const int64_t* img, const int64_t* pix,
+                                                              const uint8_t* mask, int64_t pixels_per_image, int64_t R,
+                                                              int64_t* out_img, int64_t* out_pix, int32_t* n_kept) {
+  __shared__ int s_warp[32];
+  __shared__ int s_base, s_total;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (threadIdx.x == 0) s_base = 0;
+  __syncthreads();
+  for (int64_t m0 = 0; m0 < M; m0 += blockDim.x) {
+    const int64_t m = m0 + threadIdx.x;
+    bool keep = false;
+    if (m < M) keep = mask[img[m] * pixels_per_image + pix[m]] != 0;
+    const unsigned b = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) s_warp[wid] = __popc(b);
+    __syncthreads();
+    if (wid == 0) {  // exclusive scan of the 32 warp counts
+      const int v = s_warp[lane];
+      int incl = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+      }
+      s_warp[lane] = incl - v;
+      if (lane == 31) s_total = incl;
+    }
+    __syncthreads();
+    const int base = s_base;
+    const int pos = base + s_warp[wid] + __popc(b & ((1u << lane) - 1u));
+    if (keep && pos < R) {
+      out_img[pos] = img[m];
+      out_pix[pos] = pix[m];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) s_base = base + s_total;
+    __syncthreads();
+  }
+  const int kept = s_base < R ? s_base : (int)R;
+  if (threadIdx.x == 0) *n_kept = s_base;
+  __syncthreads();  // the survivors are in global memory before they are repeated
+  if (kept > 0 && kept < R) {
+    for (int64_t k = kept + threadIdx.x; k < R; k += blockDim.x) {
+      out_img[k] = out_img[k % kept];
+      out_pix[k] = out_pix[k % kept];
+    }
+  }
+}
+
+constexpr int kMaxPalette = 256;
+struct Palette {
+  int n;
+  uint32_t key[kMaxPalette];  // r | g<<8 | b<<16
+};
+
+__global__ void __launch_bounds__(kThreads) color_to_label_kernel(int64_t N, const uint8_t* rgb, const Palette* pal,
+                                                                  int64_t default_label, int64_t* labels) {
+  __shared__ uint32_t s_key[kMaxPalette];
+  const int n = pal->n;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) s_key[i] = pal->key[i];
+  __syncthreads();
+  for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < N; p += (int64_t)gridDim.x * blockDim.x) {
+    const uint32_t k = rgb[3 * p] | ((uint32_t)rgb[3 * p + 1] << 8) | ((uint32_t)rgb[3 * p + 2] << 16);
+    int64_t lab = default_label;
+    for (int i = 0; i < n; ++i)
+      if (s_key[i] == k) {
+        lab = i;
+        break;
+      }
+    labels[p] = lab;
+  }
+}
+
+__global__ void __launch_bounds__(kThreads) semantic_colormap_kernel(int64_t N, int C, const float* logits,
+                                                                     const Palette* pal, int64_t* labels, uint8_t* rgb) {
+  for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < N; p += (int64_t)gridDim.x * blockDim.x) {
+    const float* x = logits + p * C;
+    int best = 0;
+    float bv = x[0];
+    for (int c = 1; c < C; ++c) {  // first maximum wins, as torch.argmax
+      const float v = x[c];
+      if (v > bv || (v != v && !(bv != bv))) {
+        bv = v;
+        best = c;
+      }
+    }
+    if (labels) labels[p] = best;
+    if (rgb) {
+      const uint32_t k = best < pal->n ? pal->key[best] : 0u;
+      rgb[3 * p] = k & 0xff;
+      rgb[3 * p + 1] = (k >> 8) & 0xff;
+      rgb[3 * p + 2] = (k >> 16) & 0xff;
+    }
+  }
+}
+
+int grid_for(int64_t n) {
+  int64_t blocks = (n + kThreads - 1) / kThreads;
+  int64_t cap = (int64_t)nkbs_num_sms() * 8;
+  if (blocks < 1) blocks = 1;
+  return (int)(blocks < cap ? blocks : cap);
+}
+
+}  // namespace
+
+extern "C" int nkbs_generate_rays(int64_t N, const int64_t* ray_indices, const float* c2w, const float* intrinsics,
+                                  int64_t num_cameras, float* origins, float* directions, float* directions_norm,
+                                  float* pixel_area, int64_t* camera_indices, void* stream) {
+  NKBS_CHECK_ARG(N >= 0 && num_cameras >= 1, "nkbs_generate_rays: bad sizes");
+  if (N == 0) return 0;
+  NKBS_CHECK_ARG(ray_indices && c2w && intrinsics && origins && directions, "nkbs_generate_rays: null pointers");
+  RayGenArgs a{N, ray_indices, c2w, intrinsics, num_cameras, origins, directions, directions_norm, pixel_area, camera_indices};
+  generate_rays_kernel<<<grid_for(N), kThreads, 0, (cudaStream_t)stream>>>(a);
+  NKBS_CHECK_LAUNCH("nkbs_generate_rays");
+  return 0;
+}
+
+extern "C" int nkbs_compact_masked(int64_t M, const int64_t* image_indices, const int64_t* pixel_indices,
+                                   const uint8_t* masks, int64_t pixels_per_image, int64_t R, int64_t* out_image,
+                                   int64_t* out_pixel, int32_t* n_kept, void* stream) {
+  NKBS_CHECK_ARG(M >= 0 && R >= 0 && pixels_per_image >= 1, "nkbs_compact_masked: bad sizes");
+  NKBS_CHECK_ARG(image_indices && pixel_indices && masks && out_image && out_pixel && n_kept, "nkbs_compact_masked: null pointers");
+  compact_masked_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(M, image_indices, pixel_indices, masks, pixels_per_image, R,
+                                                             out_image, out_pixel, n_kept);
+  NKBS_CHECK_LAUNCH("nkbs_compact_masked");
+  return 0;
+}
+
+extern "C" int nkbs_color_to_label(int64_t N, const uint8_t* rgb, const void* palette, int64_t default_label,
+                                   int64_t* labels, void* stream) {
+  NKBS_CHECK_ARG(N >= 0, "nkbs_color_to_label: negative N");
+  if (N == 0) return 0;
+  NKBS_CHECK_ARG(rgb && palette && labels, "nkbs_color_to_label: null pointers");
+  color_to_label_kernel<<<grid_for(N), kThreads, 0, (cudaStream_t)stream>>>(N, rgb, (const Palette*)palette, default_label, labels);
+  NKBS_CHECK_LAUNCH("nkbs_color_to_label");
+  return 0;
+}
+
+extern "C" int nkbs_semantic_colormap(int64_t N, int32_t C, const float* logits, const void* palette, int64_t* labels,
+                                      uint8_t* rgb, void* stream) {
+  NKBS_CHECK_ARG(N >= 0 && C >= 1, "nkbs_semantic_colormap: bad sizes");
+  if (N == 0) return 0;
+  NKBS_CHECK_ARG(logits && (labels || rgb) && (!rgb || palette), "nkbs_semantic_colormap: null pointers");
+  semantic_colormap_kernel<<<grid_for(N), kThreads, 0, (cudaStream_t)stream>>>(N, C, logits, (const Palette*)palette, labels, rgb);
+  NKBS_CHECK_LAUNCH("nkbs_semantic_colormap");
+  return 0;
+}

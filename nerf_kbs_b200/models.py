@@ -81,6 +81,11 @@ class _ModelBase(nn.Module):
     def forward(self, ray_bundle: RayBundle, jitter=None):
         return self.get_outputs(self.collider(ray_bundle), jitter=jitter)
 
+    def get_outputs_for_camera_ray_bundle(self, camera_ray_bundle: RayBundle, num_rays_per_chunk: int = 1 << 16):
+        """nerfstudio Model API: chunked eval forward (ref:train.py:77 sets the chunk to 1 << 16)."""
+        from .render import get_outputs_for_camera_ray_bundle
+        return get_outputs_for_camera_ray_bundle(self, camera_ray_bundle, num_rays_per_chunk)
+
     def _prop_depths(self, outputs, weights_list, ray_samples_list):
         for i in range(self.config.num_proposal_iterations):
             rs = ray_samples_list[i]

@@ -997,3 +997,54 @@ def synthetic_ray_bundle(num_rays: int, num_images: int = 115, seed: int = 0) ->
     cam = torch.randint(0, num_images, (num_rays, 1), generator=g)
     return RayBundle(origins=origins, directions=d, pixel_area=torch.ones(num_rays, 1) * 1e-6,
                      camera_indices=cam, metadata={"directions_norm": torch.ones(num_rays, 1)})
+
+
+# ------------------------------------------------------------------------------------------------
+# N3 / N4 neighbours of the ray-batch path: ray generation, masked sampling, semantic palette
+# ------------------------------------------------------------------------------------------------
+def generate_rays(ray_indices: torch.Tensor, c2w: torch.Tensor, intrinsics: torch.Tensor) -> RayBundle:
+    """nerfstudio Cameras._generate_rays_from_coords for undistorted PERSPECTIVE cameras [NS-recalled], as
+    driven by RayGenerator at ref:dataparser/datamanager_z.py:96,252-278.  ``ray_indices`` [N,3] = (camera, row,
+    col); ``c2w`` [num_cameras,3,4]; ``intrinsics`` [num_cameras,4] = fx, fy, cx, cy."""
+    cam = ray_indices[:, 0]
+    y = ray_indices[:, 1].float() + 0.5
+    x = ray_indices[:, 2].float() + 0.5
+    fx, fy, cx, cy = (intrinsics[cam, i] for i in range(4))
+    coord = torch.stack([(x - cx) / fx, -(y - cy) / fy], -1)
+    coord_x = torch.stack([(x + 1 - cx) / fx, -(y - cy) / fy], -1)
+    coord_y = torch.stack([(x - cx) / fx, -(y + 1 - cy) / fy], -1)
+    stack = torch.stack([coord, coord_x, coord_y], 0)                          # [3,N,2]
+    dirs = torch.cat([stack, -torch.ones_like(stack[..., :1])], -1)            # [3,N,3]
+    rot = c2w[cam][:, :3, :3]                                                  # [N,3,3]
+    dirs = torch.sum(dirs[..., None, :] * rot[None], dim=-1)                   # [3,N,3]
+    norms = torch.linalg.vector_norm(dirs, dim=-1, keepdim=True)
+    dirs = dirs / norms
+    dx = torch.sqrt(torch.sum((dirs[0] - dirs[1]) ** 2, dim=-1))
+    dy = torch.sqrt(torch.sum((dirs[0] - dirs[2]) ** 2, dim=-1))
+    return RayBundle(origins=c2w[cam][:, :3, 3], directions=dirs[0], pixel_area=(dx * dy)[:, None],
+                     camera_indices=cam[:, None], metadata={"directions_norm": norms[0]})
+
+
+def compact_masked(image_indices, pixel_indices, masks, num_rays):
+    """ref:dataparser/dataset_z.py:180-191: candidates whose mask is non-zero, in order; cut / cyclically padded to
+    ``num_rays`` (the reference draws a fixed-size chunk and batches from it)."""
+    keep = masks[image_indices, pixel_indices] > 0
+    img, pix = image_indices[keep], pixel_indices[keep]
+    n = int(keep.sum())
+    if n >= num_rays or n == 0:
+        return img[:num_rays], pix[:num_rays], n
+    idx = torch.arange(num_rays) % n
+    return img[idx], pix[idx], n
+
+
+def color_to_label(rgb_u8: torch.Tensor, palette, default_label: int) -> torch.Tensor:
+    """ref:nerfacto.py:508-512 (color2label.get(tuple(pixel), semantic_num) per pixel)."""
+    table = {tuple(int(v) for v in c): i for i, c in reversed(list(enumerate(palette)))}
+    return torch.tensor([table.get(tuple(int(v) for v in p), default_label) for p in rgb_u8.tolist()], dtype=torch.long)
+
+
+def semantic_colormap(logits: torch.Tensor, palette) -> Tuple[torch.Tensor, torch.Tensor]:
+    """ref:nerfacto.py:574-578 / semantic_nerfw.py:346-351: argmax(softmax(logits)) -> palette colour."""
+    labels = torch.argmax(torch.nn.functional.softmax(logits, dim=-1), dim=-1)
+    pal = torch.tensor(palette, dtype=torch.uint8)
+    return labels, pal[labels]

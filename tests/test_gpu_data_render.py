@@ -1,0 +1,110 @@
+"""GPU parity of ray generation, masked sampling, the semantic palette kernels and the chunked full-frame render
+driver against the oracle restatements."""
+import pytest
+import torch
+
+from oracle import nerfstudio_torch as O
+import nerf_kbs_b200 as nk
+from nerf_kbs_b200 import data as D
+from tests.util import assert_close, copy_model
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+PALETTE = [(128, 64, 128), (244, 35, 232), (70, 70, 70), (102, 102, 156), (190, 153, 153), (153, 153, 153),
+           (250, 170, 30), (220, 220, 0), (107, 142, 35), (152, 251, 152), (70, 130, 180), (220, 20, 60), (255, 0, 0),
+           (0, 0, 142), (0, 0, 70), (0, 60, 100), (0, 80, 100), (0, 0, 230), (119, 11, 32)]
+
+
+def _cameras(n=5, H=375, W=1242, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    q, _ = torch.linalg.qr(torch.randn(n, 3, 3, generator=g))
+    t = torch.rand(n, 3, 1, generator=g) - 0.5
+    c2w = torch.cat([q, t], -1)
+    f = torch.full((n,), 721.5)
+    return nk.Cameras(c2w, f, f.clone(), torch.full((n,), W / 2.0), torch.full((n,), H / 2.0), H, W)
+
+
+def test_generate_rays_matches_oracle():
+    cams = _cameras()
+    g = torch.Generator().manual_seed(1)
+    N = 20000
+    idx = torch.stack([torch.randint(0, len(cams), (N,), generator=g), torch.randint(0, cams.height, (N,), generator=g),
+                       torch.randint(0, cams.width, (N,), generator=g)], -1)
+    want = O.generate_rays(idx, cams.camera_to_worlds, cams.intrinsics)
+    got = nk.RayGenerator(cams).to(DEV)(idx.to(DEV))
+    assert torch.equal(got.origins.cpu(), want.origins)
+    assert torch.equal(got.camera_indices.cpu(), want.camera_indices)
+    assert_close(got.directions, want.directions, 1e-6, "directions")
+    assert_close(got.metadata["directions_norm"], want.metadata["directions_norm"], 1e-6, "directions_norm")
+    assert_close(got.pixel_area, want.pixel_area, 1e-4, "pixel_area")
+    assert float((got.directions.norm(dim=-1) - 1).abs().max()) < 1e-6
+
+
+def test_full_image_indices_are_row_major():
+    idx = D.image_ray_indices(3, 4, 5, DEV)
+    assert idx.shape == (20, 3) and idx[:, 0].eq(3).all()
+    assert idx[:, 1].tolist() == [r for r in range(4) for _ in range(5)]
+    assert idx[:, 2].tolist() == list(range(5)) * 4
+
+
+@pytest.mark.parametrize("keep,R", [(0.8, 8192), (0.3, 4096), (0.0, 64), (1.0, 1000)])
+def test_masked_compaction_matches_oracle(keep, R):
+    g = torch.Generator().manual_seed(R)
+    n_img, n_pix = 7, 1242 * 375
+    masks = (torch.rand(n_img, n_pix, generator=g) < keep).to(torch.uint8) * 255
+    M = int(R * 1.5) + 32
+    img = torch.randint(0, n_img, (M,), generator=g)
+    pix = torch.randint(0, n_pix, (M,), generator=g)
+    wi, wp, wn = O.compact_masked(img, pix, masks, R)
+    gi, gp, gn = D.compact_masked(img.to(DEV), pix.to(DEV), masks.to(DEV), R)
+    assert int(gn) == wn
+    if wn > 0:
+        assert torch.equal(gi.cpu(), wi) and torch.equal(gp.cpu(), wp)
+        assert masks[gi.cpu(), gp.cpu()].ne(0).all()
+
+
+def test_palette_round_trip_and_colormap():
+    pal = nk.SemanticPalette(PALETTE, DEV)
+    g = torch.Generator().manual_seed(2)
+    labels = torch.randint(0, len(PALETTE), (5000,), generator=g)
+    rgb = torch.tensor(PALETTE, dtype=torch.uint8)[labels]
+    rgb[::11] = torch.tensor([1, 2, 3], dtype=torch.uint8)  # colours outside the palette -> default label
+    want = O.color_to_label(rgb, PALETTE, len(PALETTE))
+    got = pal.color_to_label(rgb.to(DEV))
+    assert torch.equal(got.cpu(), want)
+    logits = torch.randn(5000, len(PALETTE), generator=g)
+    logits[5, 3] = logits[5, 9] = 10.0  # tie: the first maximum wins
+    wl, wc = O.semantic_colormap(logits, PALETTE)
+    gl, gc = pal.colormap(logits.to(DEV))
+    assert torch.equal(gl.cpu(), wl) and torch.equal(gc.cpu(), wc)
+
+
+def test_render_camera_matches_oracle_chunks():
+    """A small frame rendered in uneven chunks equals the oracle's eval forward on the same rays."""
+    torch.manual_seed(0)
+    cfg = dict(use_semantic=True)
+    om, nm = O.NerfactoModel(O.ModelConfig(**cfg)), nk.NerfactoModel(nk.ModelConfig(**cfg)).to(DEV)
+    with torch.no_grad():
+        for p in om.parameters():
+            if p.dim() == 2 and p.shape[1] == 2:
+                p.mul_(300.0)
+    copy_model(nm, om)
+    om.eval(), nm.eval()
+    cams = _cameras(n=3, H=12, W=20)
+    gen = nk.RayGenerator(cams).to(DEV)
+    pal = nk.SemanticPalette(PALETTE, DEV)
+    prev = nk.ops.get_mlp_precision()
+    nk.ops.set_mlp_precision("fp32")
+    try:
+        out = nk.render_camera(nm, gen, 1, num_rays_per_chunk=64, palette=pal)
+    finally:
+        nk.ops.set_mlp_precision(prev)
+    idx = D.image_ray_indices(1, 12, 20, "cpu")
+    with torch.no_grad():
+        want = om(O.generate_rays(idx, cams.camera_to_worlds, cams.intrinsics))
+    assert out["rgb"].shape == (12, 20, 3) and out["semantics_colormap"].dtype == torch.uint8
+    assert_close(out["rgb"].reshape(-1, 3), want["rgb"], 1e-4, "rgb")
+    assert_close(out["accumulation"].reshape(-1, 1), want["accumulation"], 1e-4, "accumulation")
+    assert_close(out["depth"].reshape(-1, 1), want["depth"], 1e-3, "median depth")
+    assert_close(out["semantics"].reshape(-1, 19), want["semantics"], 1e-4, "semantics")
+    assert float(out["rgb"].min()) >= 0.0 and float(out["rgb"].max()) <= 1.0
