@@ -44,6 +44,8 @@ def parse_args():
     ap.add_argument("--no-kernel-pass", action="store_true")
     ap.add_argument("--fp32-mlp", action="store_true", help="CUDA-core fp32 MLP kernels instead of the tcgen05 path")
     ap.add_argument("--pool", type=int, default=8, help="distinct ray batches cycled through")
+    ap.add_argument("--no-render", action="store_true", help="skip the full-frame render leg (BASELINE configs[3])")
+    ap.add_argument("--render-frames", type=int, default=10)
     return ap.parse_args()
 
 
@@ -173,6 +175,17 @@ def kernel_work(name, a):
         return "hbm", N * 4 * (w + a[3])
     if name == "nkbs_adam_step":
         return "hbm", 7 * 4 * sum(list(a[5])[:a[0]])
+    if name in ("nkbs_density_fwd", "nkbs_density_bwd"):
+        # fused proposal field: bin edges in, 8 corner rows of F=2 floats per level gathered, density out;
+        # bwd additionally reads d(density) and scatters the same 8*L rows once each
+        N, L = a[6] * a[7], a[12]
+        gathers = 8 * L * 2 * 4
+        return "hbm", N * ((8 + gathers + 4) if name.endswith("fwd") else (8 + 4 + 2 * gathers))
+    if name == "nkbs_ray_losses":
+        R, S, n_prop = a[0], a[1], a[5]
+        sp = list(a[6])[:n_prop]
+        per = 4 * (S + 1) + 8 * S + sum(4 * (x + 1) + 8 * x for x in sp) + 36 * (a[10] is not None)
+        return "hbm", R * per
     return "hbm", 0
 
 
@@ -277,6 +290,66 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+KITTI_H, KITTI_W = 375, 1242
+
+
+def render_run(dev, frames, warmup, rank=0, world=1, chunk=1 << 16):
+    """BASELINE configs[3]: full-frame 1242x375 inference (rgb, depth, semantics) from synthetic poses on a straight
+    KITTI-like trajectory, rays generated on the device, 65 536-ray chunks, eval mode.  Returns rays/s over all ranks
+    (chunks are dealt round-robin) and the end-to-end figure that includes the D2H copy of the three images."""
+    import torch
+    import torch.distributed as dist
+    import nerf_kbs_b200 as nk
+    torch.manual_seed(0)
+    model = nk.NerfactoModel(nk.ModelConfig(use_semantic=True)).to(dev).eval()
+    n_cam = 8
+    c2w = torch.eye(4)[:3].repeat(n_cam, 1, 1)
+    c2w[:, 2, 3] = torch.linspace(-0.4, 0.4, n_cam)  # drive along the optical axis
+    f = torch.full((n_cam,), 721.5)
+    cams = nk.Cameras(c2w, f, f.clone(), torch.full((n_cam,), 621.0), torch.full((n_cam,), 187.5), KITTI_H, KITTI_W)
+    gen = nk.RayGenerator(cams).to(dev)
+    palette = nk.SemanticPalette([((37 * i) % 256, (91 * i) % 256, (173 * i) % 256) for i in range(19)], dev)
+    n_rays = KITTI_H * KITTI_W
+    host = {k: torch.empty(s, dtype=t, pin_memory=True) for k, s, t in
+            (("rgb", (KITTI_H, KITTI_W, 3), torch.float32), ("depth", (KITTI_H, KITTI_W, 1), torch.float32),
+             ("semantics_colormap", (KITTI_H, KITTI_W, 3), torch.uint8))}
+
+    def frame(i, to_host):
+        out = nk.render_camera(model, gen, i % n_cam, num_rays_per_chunk=chunk, palette=palette, rank=rank, world_size=world)
+        if to_host:
+            for k, h in host.items():
+                h.copy_(out[k], non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        return out
+
+    def timed(to_host):
+        for i in range(warmup):
+            frame(i, to_host)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(frames):
+            frame(i, to_host)
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    ms = timed(False)
+    ms_e2e = timed(True)
+    d2h = sum(h.numel() * h.element_size() for h in host.values())
+    return {"metric": "render_rays_per_sec", "value": n_rays * frames / (ms * 1e-3), "unit": UNIT,
+            "ms_per_frame": ms / frames, "frames": frames, "rays_per_frame": n_rays, "chunk": chunk,
+            "workload": "nerfacto + semantic head, 1242x375 frame, eval mode, rays generated on device, "
+                        "outputs rgb + median depth + semantic logits/argmax colour map",
+            "e2e": {"value": n_rays * frames / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_frame": ms_e2e / frames,
+                    "h2d_bytes_per_step": 0, "d2h_bytes_per_step": d2h}}
+
+
 def _finish(dist):
     """Leave a multi-rank run: final barrier, then exit without tearing NCCL down (destroy_process_group was seen
     to hang on a communicator that captured CUDA graphs still reference)."""
@@ -379,6 +452,13 @@ def run_nkbs(args):
     e2e = {"value": world * R * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
            "h2d_bytes_per_step": tr.h2d_bytes() + 4, "d2h_bytes_per_step": 4}
 
+    # (2b) render rays/s (BASELINE configs[3]); every rank takes part (chunks are dealt round-robin)
+    render = None
+    if not args.no_render:
+        del devb
+        render = render_run(dev, args.render_frames, 2, rank, world)
+        devb = [{k: v.to(dev) for k, v in b.items()} for b in host]
+
     if rank != 0:
         if world > 1:
             _finish(dist)
@@ -432,7 +512,7 @@ def run_nkbs(args):
                    "l2": f"no flush: the step's working set (parameters + gradients + Adam moments = {working_set / 2**20:.0f} MiB, "
                          f"all streamed every step) exceeds the {L2_BYTES // 2**20} MiB L2; {args.pool} distinct ray batches rotate"},
         "e2e": e2e, "gpu_launches": nk_launches, "nkbs_entry_calls_per_step": launches_per_step,
-        "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks.summary(), "kernels": kernels,
+        "roofline": roofline, "cpu_baseline": cpu, "render": render, "clocks": clocks.summary(), "kernels": kernels,
         "final_loss": final_loss,
     }
     if saved_stdout is not None:
