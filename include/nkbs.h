@@ -126,6 +126,26 @@ int nkbs_color_to_label(int64_t N, const uint8_t* rgb, const void* palette, int6
 int nkbs_semantic_colormap(int64_t N, int32_t C, const float* logits, const void* palette, int64_t* labels,
                            uint8_t* rgb, void* stream);
 
+/* K3+K4 — head MLPs on the tensor cores with their input assembled inside the kernel: the row
+ * [SH16((d+1)/2) | geo15 | appearance32] (colour head) or [geo15 | transient16] (transient head) is built per
+ * 128-sample tile straight into the first layer's operand tile, and the backward splits dX_0 into the geometry
+ * gradient rows (dgeo, row stride dgeo_stride floats; may be NULL) and the per-image embedding gradient (demb
+ * [num_images, emb_dim], accumulated; may be NULL), so neither the assembled [N,63] tensor nor its gradient ever
+ * exists in HBM.  geo rows may be strided (geo_stride floats): the base MLP's [N,16] output is read in place.
+ * replaces: nkbs_assemble_fwd/bwd + nkbs_mlp_tc_fwd/bwd for NerfactoField.get_outputs (nerfacto.py:398;
+ *           semantic_nerfw.py:188).  Other arguments as nkbs_assemble_fwd and nkbs_mlp_tc_fwd/bwd. */
+int nkbs_head_tc_fwd(int32_t sh_dim, int32_t geo_dim, int32_t emb_dim, const float* geo, int32_t geo_stride,
+                     const float* directions, int32_t dir_per_ray, const int64_t* cam, int32_t cam_per_ray,
+                     const float* emb, const float* emb_const, int32_t S, int64_t N, int32_t nl, const int32_t* dims,
+                     const float* const* W, const float* const* b, int32_t relu_mask, int32_t out_act, int32_t fmt,
+                     float* y, void* stream);
+int nkbs_head_tc_bwd(int32_t sh_dim, int32_t geo_dim, int32_t emb_dim, const float* geo, int32_t geo_stride,
+                     const float* directions, int32_t dir_per_ray, const int64_t* cam, int32_t cam_per_ray,
+                     const float* emb, const float* emb_const, int32_t S, const float* dy, int64_t N, int32_t nl,
+                     const int32_t* dims, const float* const* W, const float* const* b, int32_t relu_mask,
+                     int32_t out_act, int32_t fmt, float* dgeo, int32_t dgeo_stride, float* demb, float* const* dW,
+                     float* const* db, void* stream);
+
 /* K4 — head-MLP input assembly  h = [SH16((d+1)/2) | geo | embedding row]  and its backward.
  * replaces: SHEncoding + Embedding + torch.cat in NerfactoField.get_outputs (nerfacto.py:398;
  *           semantic_nerfw.py:188).  cam NULL -> emb_const [emb_dim] is used (eval). */

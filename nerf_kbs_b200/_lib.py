@@ -32,6 +32,10 @@ SIGNATURES = {
     "nkbs_compact_masked": [_i64, _p, _p, _p, _i64, _i64, _p, _p, _p, _p],
     "nkbs_color_to_label": [_i64, _p, _p, _i64, _p, _p],
     "nkbs_semantic_colormap": [_i64, _i32, _p, _p, _p, _p, _p],
+    "nkbs_head_tc_fwd": [_i32, _i32, _i32, _p, _i32, _p, _i32, _p, _i32, _p, _p, _i32, _i64, _i32, _p, _p, _p, _i32, _i32, _i32,
+                         _p, _p],
+    "nkbs_head_tc_bwd": [_i32, _i32, _i32, _p, _i32, _p, _i32, _p, _i32, _p, _p, _i32, _p, _i64, _i32, _p, _p, _p, _i32, _i32,
+                         _i32, _p, _i32, _p, _p, _p, _p],
     "nkbs_assemble_fwd": [_i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32, _p, _p, _i64, _p, _p],
     "nkbs_assemble_bwd": [_i64, _i32, _i32, _i32, _i32, _p, _p, _p, _i32, _p, _p],
     "nkbs_initial_sampler": [_i64, _i32, _p, _p, _i32, _p, _p, _p, _p, _p],

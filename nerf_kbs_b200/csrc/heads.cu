@@ -4,33 +4,11 @@
 // Replaces the cat([...]) + SHEncoding + Embedding lookups of NerfactoField.get_outputs reached from
 // ref:nerfacto.py:398 and ref:semantic_nerfw.py:188.
 #include "common.cuh"
+#include "sh.cuh"
 
 namespace {
 
 constexpr int kThreads = 256;
-
-// SH component c of degree<=3 evaluated on d' = (d+1)/2, the torch path's convention
-__device__ __forceinline__ float sh_component(int c, float x, float y, float z) {
-  float xx = x * x, yy = y * y, zz = z * z;
-  switch (c) {
-    case 0: return 0.28209479177387814f;
-    case 1: return 0.4886025119029199f * y;
-    case 2: return 0.4886025119029199f * z;
-    case 3: return 0.4886025119029199f * x;
-    case 4: return 1.0925484305920792f * x * y;
-    case 5: return 1.0925484305920792f * y * z;
-    case 6: return 0.9461746957575601f * zz - 0.31539156525251999f;
-    case 7: return 1.0925484305920792f * x * z;
-    case 8: return 0.5462742152960396f * (xx - yy);
-    case 9: return 0.5900435899266435f * y * (3.f * xx - yy);
-    case 10: return 2.890611442640554f * x * y * z;
-    case 11: return 0.4570457994644658f * y * (5.f * zz - 1.f);
-    case 12: return 0.3731763325901154f * z * (5.f * zz - 3.f);
-    case 13: return 0.4570457994644658f * x * (5.f * zz - 1.f);
-    case 14: return 1.445305721320277f * z * (xx - yy);
-    default: return 0.5900435899266435f * x * (xx - 3.f * yy);
-  }
-}
 
 struct AssembleArgs {
   int64_t N;

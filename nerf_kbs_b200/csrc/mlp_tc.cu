@@ -19,6 +19,7 @@
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include "common.cuh"
+#include "sh.cuh"
 #include "umma.cuh"
 
 namespace {
@@ -48,7 +49,27 @@ struct TcLayer {
   int dw_col; // first TMEM column of this layer's dW accumulator (backward)
 };
 
+// Input built in the kernel instead of read as rows (IN = 1, 2): X0 = [SH16((d+1)/2) | geo15 | embedding row | 1],
+// the colour head's input (IN = 1: SH 16, appearance 32), or [geo15 | embedding row | 1], the transient head's
+// (IN = 2: no SH, transient embedding 16).  Replaces K4 (heads.cu) on the tensor-core path: the [N,63] tensor and
+// its gradient never exist in HBM.
+struct HeadIn {
+  const float* geo;        // row n at geo + n * geo_stride (15 floats)
+  int geo_stride;
+  const float* dirs;       // [R,3] if dir_per_ray else [N,3]
+  int dir_per_ray;
+  const int64_t* cam;      // [R] if cam_per_ray else [N]; null -> emb_const
+  int cam_per_ray;
+  const float* emb;        // [num_images, emb_dim]
+  const float* emb_const;  // [emb_dim]
+  int S;                   // samples per ray
+  float* dgeo;             // backward: row n at dgeo + n * dgeo_stride, or null
+  int dgeo_stride;
+  float* demb;             // backward: [num_images, emb_dim], accumulated into, or null
+};
+
 struct TcArgs {
+  HeadIn hin;
   int nl;
   TcLayer layer[kMaxLayers];
   const float* x;         // [N,K0]
@@ -141,6 +162,52 @@ __device__ void load_input_tile(const float* __restrict__ x, int64_t row0, int64
   const int r = tid;
   for (int k = K; k < Ka; ++k)
     *reinterpret_cast<uint16_t*>(tile + tile_off(r, k, kActCs)) = cvt16<FMT>(k == K ? 1.f : 0.f);
+}
+
+// X0 tile of the head MLPs, one row per thread (IN = 1: SHD = 16, EMBD = 32; IN = 2: SHD = 0, EMBD = 16).
+// Values are produced in fp32 exactly as nkbs_assemble_fwd writes them, then rounded to the operand format.
+template <int FMT, int SHD, int EMBD>
+__device__ __forceinline__ void build_head_tile(const TcArgs& a, int64_t row0, unsigned char* tile, int tid) {
+  constexpr int GEO = 15, K0 = SHD + GEO + EMBD, Ka = (K0 + 1 + 15) & ~15;
+  const HeadIn& h = a.hin;
+  const int64_t row = row0 + tid;
+  const bool live = row < a.N;
+  const int64_t ray = live ? row / h.S : 0;
+  float sh[16];
+  if (SHD > 0) {
+    const int64_t di = h.dir_per_ray ? ray : (live ? row : 0);
+    const float x = (__ldg(h.dirs + 3 * di) + 1.0f) / 2.0f;
+    const float y = (__ldg(h.dirs + 3 * di + 1) + 1.0f) / 2.0f;
+    const float z = (__ldg(h.dirs + 3 * di + 2) + 1.0f) / 2.0f;
+    sh16(x, y, z, sh);
+  }
+  // geometry and embedding values are fetched chunk by chunk (L1-resident rows), which keeps the live registers
+  // of this stage near one chunk instead of the whole 64-wide row
+  const float* gp = h.geo + (live ? row : 0) * (int64_t)h.geo_stride;
+  const float* ep = h.emb_const;
+  if (h.cam) ep = h.emb + __ldg(h.cam + (h.cam_per_ray ? ray : (live ? row : 0))) * EMBD;
+#pragma unroll
+  for (int c = 0; c < Ka / 8; ++c) {
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int k = 8 * c + j;  // compile-time column
+      float x;
+      if (k < SHD) x = sh[k < 16 ? k : 0];
+      else if (k < SHD + GEO) x = __ldg(gp + (k - SHD));
+      else if (k < K0) x = __ldg(ep + (k - SHD - GEO));
+      else x = k == K0 ? 1.f : 0.f;
+      v[j] = (live || k == K0) ? x : 0.f;
+    }
+    *reinterpret_cast<uint4*>(tile + c * kActCs + tid * 16) =
+        make_uint4(pack2<FMT>(v[0], v[1]), pack2<FMT>(v[2], v[3]), pack2<FMT>(v[4], v[5]), pack2<FMT>(v[6], v[7]));
+  }
+}
+
+template <int FMT, int IN>
+__device__ __forceinline__ void build_head_tile_in(const TcArgs& a, int64_t row0, unsigned char* tile, int tid) {
+  if (IN == 1) build_head_tile<FMT, 16, 32>(a, row0, tile, tid);
+  else build_head_tile<FMT, 0, 16>(a, row0, tile, tid);
 }
 
 __device__ __forceinline__ float apply_out_act(int act, int n, float raw, float sel) {
@@ -323,7 +390,7 @@ __device__ __forceinline__ void kernel_prologue(Sh& sh, bool issuer, int tmem_co
   fence_after_sync();
 }
 
-template <int FMT, int NWG>
+template <int FMT, int NWG, int IN>
 __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_fwd_kernel(const TcArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ Sh sh;
@@ -374,7 +441,9 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_fwd_kernel(cons
       if (a.selector && live) sel = __ldg(a.selector + row);
       unsigned char* cur = base + a.layer[0].x_off;
       unsigned char* nxt = base + a.x_off1;
-      if (vec) {
+      if (IN != 0) {
+        build_head_tile_in<FMT, IN>(a, row0, cur, tid);
+      } else if (vec) {
         float4 xr[NV];
         x_prefetch(xr, a.x, row0, a.N, K0, tid);
         x_commit<FMT>(xr, K0, kshift, Ka0, cur, tid);
@@ -406,7 +475,7 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_fwd_kernel(cons
   if (issuer) tmem_dealloc(tmem, a.tmem_cols);
 }
 
-template <int FMT, int NWG>
+template <int FMT, int NWG, int IN>
 __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(const TcArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ Sh sh;
@@ -422,6 +491,8 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(cons
   const int64_t ntiles = (a.N + kTile - 1) / kTile;
   const int nl = a.nl;
   const bool any_tile = tile_of(0, 0, nwg) < ntiles;
+  // gradient w.r.t. the first layer's input is wanted: as rows (dx) or split into geo / embedding parts (IN != 0)
+  const bool want_dx0 = a.dx != nullptr || (IN != 0 && (a.hin.dgeo != nullptr || a.hin.demb != nullptr));
   if (issuer) {
     uint32_t rph = 0;      // bit g: phase of ready[g]
     uint32_t started = 0;  // bit l: dW_l accumulator holds data
@@ -444,7 +515,7 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(cons
               const TcLayer& ly = a.layer[l];
               const uint32_t ga = base + (l == nl - 1 ? a.g_off : a.layer[l + 1].x_off);
               const uint32_t xa = base + ly.x_off, wa = smem_base + ly.w_off;
-              if (l > 0 || a.dx != nullptr) {
+              if (l > 0 || want_dx0) {
                 // dX_l [128 x Nx] = G [128 x Np] . W_l   (W_l viewed MN-major: contraction over its rows); issued
                 // first and committed on its own so the warpgroup's epilogue does not wait for the dW GEMM
                 const int Nx = (ly.K + 15) & ~15;
@@ -484,6 +555,11 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(cons
     float* dys = reinterpret_cast<float*>(base + a.dy_off);
     uint32_t phase = 0;
     constexpr int NV = NWG >= 4 ? 8 : 16;  // register budget: 120 registers per thread with four warpgroups
+    // The output-gradient tile G is read 64 features wide (dW of the last layer, M = 64) but only its first Np
+    // columns carry data: the padding is zeroed once here, nothing else ever writes this region (the dx staging
+    // ends before it, see build_args).
+    for (int c = last.Np >> 3; c < kMaxWidth / 8; ++c)
+      *reinterpret_cast<uint4*>(base + a.g_off + c * kActCs + r * 16) = make_uint4(0u, 0u, 0u, 0u);
     for (int i = 0;; ++i) {
       const int64_t t = tile_of(i, wg, nwg);
       if (t >= ntiles) break;
@@ -504,7 +580,9 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(cons
       TRACE_WG(5);
       float sel = 1.f;
       if (a.selector && live) sel = __ldg(a.selector + row);
-      if (vec) {
+      if (IN != 0) {
+        build_head_tile_in<FMT, IN>(a, row0, base + a.layer[0].x_off, tid);
+      } else if (vec) {
         float4 xr[NV];
         x_prefetch(xr, a.x, row0, a.N, K0, tid);
         TRACE_WG(6);
@@ -528,7 +606,7 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(cons
         wg_sync(wg);  // every thread's part of the dy tile has landed
         const float* dyr = dys + r * Kn;
         unsigned char* g = base + a.g_off;
-        tmem_foreach16<kMaxWidth / 16>(tmem_row, last.Np, kMaxWidth, [&](int c0, float v[16]) {
+        tmem_foreach16<kMaxWidth / 16>(tmem_row, last.Np, last.Np, [&](int c0, float v[16]) {
           if (c0 < Kn && live) {
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
@@ -581,6 +659,42 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(cons
             }
             store16<FMT>(xt, c0, r, v);
           });
+        } else if (IN != 0 && want_dx0) {
+          // dX_0 rows -> fp32 staging; the geometry columns go out as rows of dgeo, the embedding columns are summed
+          // over the samples of each ray (they share the embedding row) and added to that row's gradient
+          constexpr int SHD = IN == 1 ? 16 : 0, GEO = 15, EMBD = IN == 1 ? 32 : 16;
+          float* st = reinterpret_cast<float*>(base + a.stage_off);
+          const int stride = Nx + 4;
+          tmem_foreach16<kMaxWidth / 16>(tmem_row, Nx, Nx, [&](int c0, float v[16]) {
+            float4* p = reinterpret_cast<float4*>(st + r * stride + c0);
+            p[0] = make_float4(v[0], v[1], v[2], v[3]);
+            p[1] = make_float4(v[4], v[5], v[6], v[7]);
+            p[2] = make_float4(v[8], v[9], v[10], v[11]);
+            p[3] = make_float4(v[12], v[13], v[14], v[15]);
+          });
+          wg_sync(wg);
+          int64_t rows = a.N - row0;
+          if (rows > kTile) rows = kTile;
+          if (a.hin.dgeo) {
+            const int total = (int)rows * GEO;
+            for (int e = tid; e < total; e += kThreads) {
+              const int rr = e / GEO, c = e - rr * GEO;
+              a.hin.dgeo[(row0 + rr) * (int64_t)a.hin.dgeo_stride + c] = st[rr * stride + SHD + c];
+            }
+          }
+          if (a.hin.demb && a.hin.cam) {
+            const int G = a.hin.cam_per_ray ? a.hin.S : 1;
+            const int64_t g0 = row0 / G, g1 = (row0 + rows - 1) / G;
+            const int lane_ = tid & 31, warp_ = tid >> 5;
+            for (int64_t g = g0 + warp_; g <= g1; g += kThreads / 32) {
+              const int lo = (int)max(g * G - row0, (int64_t)0), hi = (int)min((g + 1) * G - row0, rows);
+              if (lane_ < EMBD) {
+                float sum = 0.f;
+                for (int rr = lo; rr < hi; ++rr) sum += st[rr * stride + SHD + GEO + lane_];
+                if (sum != 0.f) atomicAdd(a.hin.demb + __ldg(a.hin.cam + g) * EMBD + lane_, sum);
+              }
+            }
+          }
         } else if (a.dx) {
           if (a.stage_ok) {
             // dX_0 rows -> fp32 staging (row stride Nx+4 floats: conflict-free 16-byte stores) -> coalesced global
@@ -721,7 +835,8 @@ int build_args(TcArgs& a, bool backward, int nl, const int32_t* dims, const floa
     // dx staging aliases everything after X_0 (dead once the last batch of the tile has completed)
     const int nx0 = round_up(a.layer[0].K, 16);
     a.stage_off = nl >= 2 ? a.layer[1].x_off : 0;
-    a.stage_ok = nl >= 2 && kTile * (nx0 + 4) * 4 <= per_wg - a.stage_off;
+    // the staging must end before the G tile, whose zero padding is written once per kernel
+    a.stage_ok = nl >= 2 && kTile * (nx0 + 4) * 4 <= a.g_off - a.stage_off;
   }
   a.wg_stride = per_wg;
   int nwg = 4;
@@ -761,32 +876,59 @@ int pick_grid(const TcArgs& a, int64_t N) {
   return (int)(groups < cap ? groups : cap);
 }
 
-template <bool BWD, int FMT, int NWG>
+template <bool BWD, int FMT, int NWG, int IN>
 int launch_one(const TcArgs& a, int64_t N, cudaStream_t st, const char* who) {
   const int grid = pick_grid(a, N), threads = NWG * kThreads + 32;
   if (BWD) {
-    if (set_smem(mlp_tc_bwd_kernel<FMT, NWG>, a.smem_bytes, who)) return -1;
-    mlp_tc_bwd_kernel<FMT, NWG><<<grid, threads, a.smem_bytes, st>>>(a);
+    if (set_smem(mlp_tc_bwd_kernel<FMT, NWG, IN>, a.smem_bytes, who)) return -1;
+    mlp_tc_bwd_kernel<FMT, NWG, IN><<<grid, threads, a.smem_bytes, st>>>(a);
   } else {
-    if (set_smem(mlp_tc_fwd_kernel<FMT, NWG>, a.smem_bytes, who)) return -1;
-    mlp_tc_fwd_kernel<FMT, NWG><<<grid, threads, a.smem_bytes, st>>>(a);
+    if (set_smem(mlp_tc_fwd_kernel<FMT, NWG, IN>, a.smem_bytes, who)) return -1;
+    mlp_tc_fwd_kernel<FMT, NWG, IN><<<grid, threads, a.smem_bytes, st>>>(a);
   }
   return 0;
 }
 
-template <bool BWD>
+template <bool BWD, int IN>
 int launch_tc(const TcArgs& a, int64_t N, cudaStream_t st, const char* who) {
   const int key = a.fmt * 8 + a.nwg;
   switch (key) {
-    case 1: return launch_one<BWD, 0, 1>(a, N, st, who);
-    case 2: return launch_one<BWD, 0, 2>(a, N, st, who);
-    case 4: return launch_one<BWD, 0, 4>(a, N, st, who);
-    case 9: return launch_one<BWD, 1, 1>(a, N, st, who);
-    case 10: return launch_one<BWD, 1, 2>(a, N, st, who);
-    case 12: return launch_one<BWD, 1, 4>(a, N, st, who);
+    case 1: return launch_one<BWD, 0, 1, IN>(a, N, st, who);
+    case 2: return launch_one<BWD, 0, 2, IN>(a, N, st, who);
+    case 4: return launch_one<BWD, 0, 4, IN>(a, N, st, who);
+    case 9: return launch_one<BWD, 1, 1, IN>(a, N, st, who);
+    case 10: return launch_one<BWD, 1, 2, IN>(a, N, st, who);
+    case 12: return launch_one<BWD, 1, 4, IN>(a, N, st, who);
   }
   nkbs_set_error("%s: unsupported warpgroup count %d", who, a.nwg);
   return -1;
+}
+
+int fill_head(TcArgs& a, const char* who, int sh_dim, int geo_dim, int emb_dim, const float* geo, int geo_stride,
+              const float* dirs, int dir_per_ray, const int64_t* cam, int cam_per_ray, const float* emb,
+              const float* emb_const, int S, int64_t N, int& in_mode) {
+  NKBS_CHECK_ARG(geo_dim == 15 && ((sh_dim == 16 && emb_dim == 32) || (sh_dim == 0 && emb_dim == 16)),
+                 "%s: head inputs are [SH16|geo15|emb32] or [geo15|emb16] (got %d/%d/%d)", who, sh_dim, geo_dim, emb_dim);
+  in_mode = sh_dim == 16 ? 1 : 2;
+  NKBS_CHECK_ARG(a.layer[0].K == sh_dim + geo_dim + emb_dim, "%s: first layer takes %d inputs, the assembled row has %d",
+                 who, a.layer[0].K, sh_dim + geo_dim + emb_dim);
+  NKBS_CHECK_ARG(geo && geo_stride >= geo_dim && S >= 1, "%s: bad geo / S", who);
+  NKBS_CHECK_ARG(sh_dim == 0 || dirs, "%s: null directions", who);
+  NKBS_CHECK_ARG((cam && emb) || emb_const, "%s: need camera indices + table, or a constant row", who);
+  NKBS_CHECK_ARG(!(dir_per_ray || cam_per_ray) || N % S == 0, "%s: N not a multiple of S", who);
+  a.hin.geo = geo;
+  a.hin.geo_stride = geo_stride;
+  a.hin.dirs = dirs;
+  a.hin.dir_per_ray = dir_per_ray;
+  a.hin.cam = emb_const ? nullptr : cam;
+  a.hin.cam_per_ray = cam_per_ray;
+  a.hin.emb = emb;
+  a.hin.emb_const = emb_const;
+  a.hin.S = S;
+  a.hin.dgeo = nullptr;
+  a.hin.dgeo_stride = 0;
+  a.hin.demb = nullptr;
+  return 0;
 }
 
 }  // namespace
@@ -810,13 +952,14 @@ extern "C" int nkbs_mlp_tc_fwd(const float* x, int64_t N, int32_t nl, const int3
   NKBS_CHECK_ARG(N >= 0, "nkbs_mlp_tc_fwd: negative N");
   if (N == 0) return 0;
   NKBS_CHECK_ARG(x && y, "nkbs_mlp_tc_fwd: null x/y");
+  a.hin = HeadIn{};
   a.x = x;
   a.y = y;
   a.selector = selector;
   a.dy = nullptr;
   a.dx = nullptr;
   a.N = N;
-  if (launch_tc<false>(a, N, (cudaStream_t)stream, "nkbs_mlp_tc_fwd")) return -1;
+  if (launch_tc<false, 0>(a, N, (cudaStream_t)stream, "nkbs_mlp_tc_fwd")) return -1;
   NKBS_CHECK_LAUNCH("nkbs_mlp_tc_fwd");
   return 0;
 }
@@ -835,13 +978,80 @@ extern "C" int nkbs_mlp_tc_bwd(const float* x, const float* dy, int64_t N, int32
     a.layer[l].dW = dW[l];
     a.layer[l].db = db[l];
   }
+  a.hin = HeadIn{};
   a.x = x;
   a.y = nullptr;
   a.selector = selector;
   a.dy = dy;
   a.dx = dx;
   a.N = N;
-  if (launch_tc<true>(a, N, (cudaStream_t)stream, "nkbs_mlp_tc_bwd")) return -1;
+  if (launch_tc<true, 0>(a, N, (cudaStream_t)stream, "nkbs_mlp_tc_bwd")) return -1;
   NKBS_CHECK_LAUNCH("nkbs_mlp_tc_bwd");
+  return 0;
+}
+
+// ---- head MLPs with the input assembled in the kernel (K4 folded into K3) ----
+extern "C" int nkbs_head_tc_fwd(int32_t sh_dim, int32_t geo_dim, int32_t emb_dim, const float* geo, int32_t geo_stride,
+                                const float* directions, int32_t dir_per_ray, const int64_t* cam, int32_t cam_per_ray,
+                                const float* emb, const float* emb_const, int32_t S, int64_t N, int32_t nl,
+                                const int32_t* dims, const float* const* W, const float* const* b, int32_t relu_mask,
+                                int32_t out_act, int32_t fmt, float* y, void* stream) {
+  TcArgs a;
+  if (build_args(a, false, nl, dims, W, b, relu_mask, out_act, fmt, "nkbs_head_tc_fwd")) return -1;
+  NKBS_CHECK_ARG(N >= 0, "nkbs_head_tc_fwd: negative N");
+  if (N == 0) return 0;
+  int in_mode = 0;
+  if (fill_head(a, "nkbs_head_tc_fwd", sh_dim, geo_dim, emb_dim, geo, geo_stride, directions, dir_per_ray, cam,
+                cam_per_ray, emb, emb_const, S, N, in_mode))
+    return -1;
+  NKBS_CHECK_ARG(y, "nkbs_head_tc_fwd: null y");
+  a.x = nullptr;
+  a.y = y;
+  a.selector = nullptr;
+  a.dy = nullptr;
+  a.dx = nullptr;
+  a.N = N;
+  const int rc = in_mode == 1 ? launch_tc<false, 1>(a, N, (cudaStream_t)stream, "nkbs_head_tc_fwd")
+                              : launch_tc<false, 2>(a, N, (cudaStream_t)stream, "nkbs_head_tc_fwd");
+  if (rc) return -1;
+  NKBS_CHECK_LAUNCH("nkbs_head_tc_fwd");
+  return 0;
+}
+
+extern "C" int nkbs_head_tc_bwd(int32_t sh_dim, int32_t geo_dim, int32_t emb_dim, const float* geo, int32_t geo_stride,
+                                const float* directions, int32_t dir_per_ray, const int64_t* cam, int32_t cam_per_ray,
+                                const float* emb, const float* emb_const, int32_t S, const float* dy, int64_t N,
+                                int32_t nl, const int32_t* dims, const float* const* W, const float* const* b,
+                                int32_t relu_mask, int32_t out_act, int32_t fmt, float* dgeo, int32_t dgeo_stride,
+                                float* demb, float* const* dW, float* const* db, void* stream) {
+  TcArgs a;
+  if (build_args(a, true, nl, dims, W, b, relu_mask, out_act, fmt, "nkbs_head_tc_bwd")) return -1;
+  NKBS_CHECK_ARG(N >= 0, "nkbs_head_tc_bwd: negative N");
+  if (N == 0) return 0;
+  int in_mode = 0;
+  if (fill_head(a, "nkbs_head_tc_bwd", sh_dim, geo_dim, emb_dim, geo, geo_stride, directions, dir_per_ray, cam,
+                cam_per_ray, emb, emb_const, S, N, in_mode))
+    return -1;
+  NKBS_CHECK_ARG(dy, "nkbs_head_tc_bwd: null dy");
+  NKBS_CHECK_ARG(a.stage_ok, "nkbs_head_tc_bwd: staging does not fit for this MLP shape");
+  NKBS_CHECK_ARG(!dgeo || dgeo_stride >= geo_dim, "nkbs_head_tc_bwd: bad dgeo stride");
+  for (int l = 0; l < nl; ++l) {
+    NKBS_CHECK_ARG(dW[l] && db[l], "nkbs_head_tc_bwd: null dW/db for layer %d", l);
+    a.layer[l].dW = dW[l];
+    a.layer[l].db = db[l];
+  }
+  a.hin.dgeo = dgeo;
+  a.hin.dgeo_stride = dgeo_stride;
+  a.hin.demb = a.hin.cam ? demb : nullptr;
+  a.x = nullptr;
+  a.y = nullptr;
+  a.selector = nullptr;
+  a.dy = dy;
+  a.dx = nullptr;
+  a.N = N;
+  const int rc = in_mode == 1 ? launch_tc<true, 1>(a, N, (cudaStream_t)stream, "nkbs_head_tc_bwd")
+                              : launch_tc<true, 2>(a, N, (cudaStream_t)stream, "nkbs_head_tc_bwd");
+  if (rc) return -1;
+  NKBS_CHECK_LAUNCH("nkbs_head_tc_bwd");
   return 0;
 }

@@ -290,8 +290,10 @@ class NerfactoField(_Field):
         feats, sel = self._encode(ray_samples, self.mlp_base_grid, self._norm)
         W, b = self.mlp_base_mlp.weights_biases()
         h = ops.mlp(feats, W, b, self.mlp_base_mlp.relu_mask, ops.ACT_DENSITY, selector=sel)
-        h = h.reshape(*ray_samples.frustums.shape, -1)
-        density, base_mlp_out = torch.split(h, [1, self.geo_feat_dim], dim=-1)
+        h3 = h.reshape(*ray_samples.frustums.shape, -1)
+        density, base_mlp_out = torch.split(h3, [1, self.geo_feat_dim], dim=-1)
+        # the head kernels read the geometry columns of the base MLP's output in place (no slice copy)
+        base_mlp_out._nkbs_src = (h, 1)
         return density, base_mlp_out
 
     # -- heads ---------------------------------------------------------------------------------
@@ -329,15 +331,27 @@ class NerfactoField(_Field):
             else:
                 emb_const = torch.zeros(self.appearance_embedding_dim, device=geo.device)
 
+        # tensor-core path: the head kernels assemble their input rows themselves (csrc/mlp_tc.cu, IN = 1 / 2)
+        src, col = getattr(density_embedding, "_nkbs_src", (None, 0))
+        fused_in = (ops.get_mlp_precision() == "tc" and ops.fused_head_enabled() and self.geo_feat_dim == 15
+                    and cam is not None)
+        if fused_in and src is None:
+            src, col = geo.contiguous(), 0
+
         if self.use_transient_embedding and self.training:
-            t_in = ops.assemble(geo, self.embedding_transient.embedding.weight, None, None, cam, S, 0, False, cpr)
             W, b = self.mlp_transient.weights_biases()
             heads = (self.field_head_transient_uncertainty, self.field_head_transient_rgb,
                      self.field_head_transient_density)
             W = W + [torch.cat([h.net.weight for h in heads], dim=0)]
             b = b + [torch.cat([h.net.bias for h in heads], dim=0)]
             relu = self.mlp_transient.relu_mask  # no activation between mlp_transient's output and the heads
-            x = ops.mlp(t_in, W, b, relu, ops.ACT_TRANSIENT).reshape(*outputs_shape, 5)
+            if fused_in and self.transient_embedding_dim == 16 and len(W) == 3:
+                x = ops.head_mlp(src, col, self.embedding_transient.embedding.weight, None, None, cam, S, 0, False, cpr,
+                                 W, b, relu, ops.ACT_TRANSIENT)
+            else:
+                t_in = ops.assemble(geo, self.embedding_transient.embedding.weight, None, None, cam, S, 0, False, cpr)
+                x = ops.mlp(t_in, W, b, relu, ops.ACT_TRANSIENT)
+            x = x.reshape(*outputs_shape, 5)
             outputs[FieldHeadNames.UNCERTAINTY] = x[..., 0:1]
             outputs[FieldHeadNames.TRANSIENT_RGB] = x[..., 1:4]
             outputs[FieldHeadNames.TRANSIENT_DENSITY] = x[..., 4:5]
@@ -350,9 +364,13 @@ class NerfactoField(_Field):
             x = ops.mlp(sem_in, W, b, self.mlp_semantics.relu_mask, ops.ACT_NONE)
             outputs[FieldHeadNames.SEMANTICS] = x.reshape(*outputs_shape, -1)
 
-        h = ops.assemble(geo, self.embedding_appearance.embedding.weight, emb_const, dirs, cam, S, 16, dpr, cpr)
         W, b = self.mlp_head.weights_biases()
-        rgb = ops.mlp(h, W, b, self.mlp_head.relu_mask, ops.ACT_SIGMOID)
+        if fused_in and self.appearance_embedding_dim == 32 and len(W) == 3:
+            rgb = ops.head_mlp(src, col, self.embedding_appearance.embedding.weight, emb_const, dirs, cam, S, 16, dpr,
+                               cpr, W, b, self.mlp_head.relu_mask, ops.ACT_SIGMOID)
+        else:
+            h = ops.assemble(geo, self.embedding_appearance.embedding.weight, emb_const, dirs, cam, S, 16, dpr, cpr)
+            rgb = ops.mlp(h, W, b, self.mlp_head.relu_mask, ops.ACT_SIGMOID)
         outputs[FieldHeadNames.RGB] = rgb.reshape(*outputs_shape, -1)
         return outputs
 

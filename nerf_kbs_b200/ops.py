@@ -295,6 +295,81 @@ def assemble(geo, emb_table, emb_const, directions, cam, S: int, sh_dim: int, di
 
 
 # ----------------------------------------------------------------------------------------------
+# K3+K4 head MLP with in-kernel input assembly (tensor-core path only)
+# ----------------------------------------------------------------------------------------------
+_FUSED_HEAD = {"enabled": True}
+
+
+def set_fused_head(enabled: bool) -> None:
+    """Head MLPs build their input inside the tensor-core kernel (default) or go through nkbs_assemble + nkbs_mlp_tc."""
+    _FUSED_HEAD["enabled"] = bool(enabled)
+
+
+def fused_head_enabled() -> bool:
+    return _FUSED_HEAD["enabled"]
+
+
+class _HeadMlp(torch.autograd.Function):
+    """y = MLP([SH16 | geo | emb[cam]]) with the input row built inside the tensor-core kernel.  ``src`` holds the
+    geometry features in columns [col, col+15) of its rows (the base MLP's output is passed whole: no slice copy)."""
+
+    @staticmethod
+    def forward(ctx, src, col, emb, emb_const, directions, cam, S, sh_dim, dir_per_ray, cam_per_ray, relu_mask, out_act,
+                *params):
+        nl = len(params) // 2
+        Ws = [_c(p) for p in params[0::2]]
+        bs = [_c(p) for p in params[1::2]]
+        src = _c(src)
+        require_cuda(src, *Ws)
+        N, stride = src.shape
+        emb_dim = emb.shape[1] if emb is not None else emb_const.shape[0]
+        dims = [Ws[0].shape[1]] + [w.shape[0] for w in Ws]
+        use_cam = cam is not None and emb_const is None
+        y = torch.empty((N, dims[-1]), device=src.device, dtype=torch.float32)
+        geo = src.reshape(-1)[col:]  # element offset of the first geometry column
+        call("nkbs_head_tc_fwd", sh_dim, 15, emb_dim, ptr(geo), stride, ptr(directions), int(dir_per_ray),
+             ptr(cam) if use_cam else None, int(cam_per_ray), ptr(emb) if use_cam else None, ptr(emb_const), S, N, nl,
+             host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask, out_act, _MLP_CFG["fwd_fmt"], ptr(y), stream())
+        ctx.cfg = (col, S, sh_dim, emb_dim, dir_per_ray, cam_per_ray, relu_mask, out_act, nl, dims, use_cam,
+                   _MLP_CFG["bwd_fmt"], emb.shape if emb is not None else None)
+        ctx.save_for_backward(src, emb, emb_const, directions, cam, *Ws, *bs)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        col, S, sh_dim, emb_dim, dpr, cpr, relu_mask, out_act, nl, dims, use_cam, bwd_fmt, emb_shape = ctx.cfg
+        saved = ctx.saved_tensors
+        src, emb, emb_const, directions, cam = saved[:5]
+        Ws, bs = list(saved[5:5 + nl]), list(saved[5 + nl:5 + 2 * nl])
+        dy = _c(dy)
+        N, stride = src.shape
+        dsrc = torch.zeros_like(src) if ctx.needs_input_grad[0] else None
+        demb = torch.zeros(emb_shape, device=src.device, dtype=torch.float32) if (use_cam and ctx.needs_input_grad[2]) else None
+        dWs = [torch.zeros_like(w) for w in Ws]
+        dbs = [torch.zeros_like(b) for b in bs]
+        geo = src.reshape(-1)[col:]
+        dgeo = dsrc.reshape(-1)[col:] if dsrc is not None else None
+        call("nkbs_head_tc_bwd", sh_dim, 15, emb_dim, ptr(geo), stride, ptr(directions), int(dpr),
+             ptr(cam) if use_cam else None, int(cpr), ptr(emb) if use_cam else None, ptr(emb_const), S, ptr(dy), N, nl,
+             host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask, out_act, bwd_fmt, ptr(dgeo), stride, ptr(demb),
+             host_ptrs(dWs), host_ptrs(dbs), stream())
+        grads = []
+        for w, b in zip(dWs, dbs):
+            grads += [w, b]
+        return (dsrc, None, demb, None, None, None, None, None, None, None, None, None, *grads)
+
+
+def head_mlp(src, col: int, emb_table, emb_const, directions, cam, S: int, sh_dim: int, dir_per_ray: bool,
+             cam_per_ray: bool, weights, biases, relu_mask: int, out_act: int):
+    """Head MLP over rows [SH(sh_dim) | src[:, col:col+15] | embedding row]; tensor-core path (nkbs_head_tc_*)."""
+    params = []
+    for w, b in zip(weights, biases):
+        params += [w, b]
+    return _HeadMlp.apply(src, col, emb_table, emb_const, _c(directions), _c(cam, torch.int64), S, sh_dim, dir_per_ray,
+                          cam_per_ray, relu_mask, out_act, *params)
+
+
+# ----------------------------------------------------------------------------------------------
 # K5 samplers (no gradient: the reference detaches the bins)
 # ----------------------------------------------------------------------------------------------
 _LIN_CACHE = {}

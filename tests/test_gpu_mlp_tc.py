@@ -106,3 +106,67 @@ def test_tc_backward(name, N, fmt):
         ref = [x.grad] + [w.grad for w in Ws] + [b.grad for b in bs]
         for n_, a, b in zip(names, mine, ref):
             assert metric(a, b) <= tol, f"{name} N={N} {n_} vs {'rounded' if ref_fmt is not None else 'fp32'} reference: {metric(a, b):.3e}"
+
+
+# ---- head MLPs with the input row assembled inside the kernel (nkbs_head_tc_fwd/bwd) ----
+@pytest.mark.parametrize("kind,R,S", [("colour", 70, 48), ("colour", 3, 48), ("transient", 70, 48), ("colour", 9, 7)])
+def test_head_mlp_fused_input_matches_assemble_route(kind, R, S):
+    """Same layers, same samples: input built in the kernel from (directions, geo columns of a [N,16] tensor,
+    embedding rows) vs nkbs_assemble + nkbs_mlp_tc.  Both multiply the same 16-bit operands."""
+    g = torch.Generator().manual_seed(R * 100 + S)
+    N = R * S
+    sh_dim, emb_dim, out_dim, act = (16, 32, 3, ops.ACT_SIGMOID) if kind == "colour" else (0, 16, 5, ops.ACT_TRANSIENT)
+    relu = 0b11 if kind == "colour" else 0b01
+    dims = [sh_dim + 15 + emb_dim, 64, 64, out_dim]
+    Ws = [(torch.randn(dims[i + 1], dims[i], generator=g) / dims[i] ** 0.5).to(DEV).requires_grad_() for i in range(3)]
+    bs = [(torch.randn(dims[i + 1], generator=g) * 0.1).to(DEV).requires_grad_() for i in range(3)]
+    base = torch.randn(N, 16, generator=g).to(DEV).requires_grad_()
+    emb = torch.randn(115, emb_dim, generator=g).to(DEV).requires_grad_()
+    dirs = torch.nn.functional.normalize(torch.randn(R, 3, generator=g), dim=-1).to(DEV)
+    cam = torch.randint(0, 115, (R,), generator=g).to(DEV)
+    dy = torch.randn(N, out_dim, generator=g).to(DEV)
+    prev = ops.get_mlp_precision()
+    ops.set_mlp_precision("tc")
+    try:
+        res = {}
+        for fused in (True, False):
+            for t in Ws + bs + [base, emb]:
+                t.grad = None
+            if fused:
+                y = ops.head_mlp(base, 1, emb, None, dirs if sh_dim else None, cam, S, sh_dim, True, True, Ws, bs, relu, act)
+            else:
+                h = ops.assemble(base[:, 1:], emb, None, dirs if sh_dim else None, cam, S, sh_dim, True, True)
+                y = ops.mlp(h, Ws, bs, relu, act)
+            y.backward(dy)
+            res[fused] = (y.detach().clone(), base.grad.clone(), emb.grad.clone(), [t.grad.clone() for t in Ws + bs])
+    finally:
+        ops.set_mlp_precision(prev)
+    assert_close = lambda a, b, tol, name: (_ for _ in ()).throw(AssertionError(f"{name}: {rel_err(a, b):.3e}")) if rel_err(a, b) > tol else None
+    assert_close(res[True][0], res[False][0], 1e-5, "y")
+    assert float(res[True][1][:, 0].abs().max()) == 0.0, "column 0 of the base output receives no gradient from the head"
+    assert_close(res[True][1], res[False][1], 2e-3, "d base")
+    assert_close(res[True][2], res[False][2], 2e-3, "d embedding")
+    for i, (a, b) in enumerate(zip(res[True][3], res[False][3])):
+        assert_close(a, b, 2e-3, f"param grad {i}")
+
+
+def test_head_mlp_fused_eval_constant_embedding():
+    """Eval: the appearance row is a constant (mean embedding), no embedding gradient path."""
+    g = torch.Generator().manual_seed(5)
+    R, S = 20, 48
+    dims = [63, 64, 64, 3]
+    Ws = [(torch.randn(dims[i + 1], dims[i], generator=g) / dims[i] ** 0.5).to(DEV) for i in range(3)]
+    bs = [(torch.randn(dims[i + 1], generator=g) * 0.1).to(DEV) for i in range(3)]
+    geo = torch.randn(R * S, 15, generator=g).to(DEV)
+    const = torch.randn(32, generator=g).to(DEV)
+    dirs = torch.nn.functional.normalize(torch.randn(R, 3, generator=g), dim=-1).to(DEV)
+    cam = torch.zeros(R, dtype=torch.long, device=DEV)
+    prev = ops.get_mlp_precision()
+    ops.set_mlp_precision("tc")
+    try:
+        y = ops.head_mlp(geo, 0, None, const, dirs, cam, S, 16, True, True, Ws, bs, 0b11, ops.ACT_SIGMOID)
+        h = ops.assemble(geo, None, const, dirs, cam, S, 16, True, True)
+        want = ops.mlp(h, Ws, bs, 0b11, ops.ACT_SIGMOID)
+    finally:
+        ops.set_mlp_precision(prev)
+    assert rel_err(y, want) <= 1e-5
