@@ -145,7 +145,7 @@ def kernel_work(name, a):
     def i32s(arr, n):
         return list(arr)[:n]
     if name == "nkbs_encode_fwd":
-        N, L, F = a[6] * a[7], a[12], a[14]
+        N, L, F = a[7] * a[8], a[13], a[15]
         return "hbm", N * (12 + 8 * L * F * 4 + 4 * L * F)
     if name == "nkbs_encode_bwd":
         N, L, F = a[2], a[4], a[6]
@@ -156,14 +156,20 @@ def kernel_work(name, a):
         dims = i32s(a[3] if fwd else a[4], nl + 1)
         mac = sum(dims[i] * dims[i + 1] for i in range(nl))
         return "tensor", N * mac * (2 if fwd else 4)  # bwd: data-gradient + weight-gradient contractions
+    if name in ("nkbs_head_tc_fwd", "nkbs_head_tc_bwd"):
+        fwd = name.endswith("fwd")
+        N, nl = (a[12], a[13]) if fwd else (a[13], a[14])
+        dims = i32s(a[14] if fwd else a[15], nl + 1)
+        mac = sum(dims[i] * dims[i + 1] for i in range(nl))
+        return "tensor", N * mac * (2 if fwd else 4)
     if name == "nkbs_composite_fwd":
-        R, S, C_ = a[0], a[1], a[8]
-        per = S * (4 * (a[2] is not None or a[3] is not None) + 8 * (a[4] is not None) + 12 * (a[6] is not None and a[12] is not None)
-                   + 4 * C_ * (a[7] is not None and a[18] is not None)) + 4 * S * (a[11] is not None) + 4 * (3 + 1 + 1 + 1 + C_)
+        R, S, C_ = a[0], a[1], a[9]
+        per = S * (4 * (a[2] is not None or a[3] is not None) + 8 * (a[4] is not None) + 12 * (a[7] is not None and a[13] is not None)
+                   + 4 * C_ * (a[8] is not None and a[19] is not None)) + 4 * S * (a[12] is not None) + 4 * (3 + 1 + 1 + 1 + C_)
         return "hbm", R * per
     if name == "nkbs_composite_bwd":
-        R, S, C_ = a[0], a[1], a[8]
-        per = S * (4 + 4 + 8 + 12 * (a[6] is not None) + 4 * C_ * (a[7] is not None)) + S * (4 + 12 * (a[20] is not None) + 4 * C_ * (a[21] is not None))
+        R, S, C_ = a[0], a[1], a[9]
+        per = S * (4 + 4 + 8 + 12 * (a[7] is not None) + 4 * C_ * (a[8] is not None)) + S * (4 + 12 * (a[21] is not None) + 4 * C_ * (a[22] is not None))
         return "hbm", R * per
     if name == "nkbs_pdf_sample":
         R, S, nb = a[0], a[1], a[2]
@@ -178,7 +184,7 @@ def kernel_work(name, a):
     if name in ("nkbs_density_fwd", "nkbs_density_bwd"):
         # fused proposal field: bin edges in, 8 corner rows of F=2 floats per level gathered, density out;
         # bwd additionally reads d(density) and scatters the same 8*L rows once each
-        N, L = a[6] * a[7], a[12]
+        N, L = a[7] * a[8], a[13]
         gathers = 8 * L * 2 * 4
         return "hbm", N * ((8 + gathers + 4) if name.endswith("fwd") else (8 + 4 + 2 * gathers))
     if name == "nkbs_ray_losses":

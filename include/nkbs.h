@@ -26,10 +26,12 @@ const char* nkbs_last_error(void);
  * mode 0: x = normalised positions in [0,1]            (HashEncoding.forward itself)
  * mode 1: x = raw positions [N,3] -> contraction/aabb -> (x+2)/4 -> selector
  * mode 2: positions = origins[r] + directions[r]*(starts+ends)/2 from per-ray data, then as mode 1
+ * bin_stride: floats between consecutive rays in starts / ends (0 = S; S+1 when both are views of one [R,S+1]
+ * bin-edge array, starts = bins, ends = bins + 1).  The same convention holds for K6/K7/K8.
  * aabb, scalings: HOST pointers ([6] and [L]).  xn/selector/indices may be NULL.
  * indices: int64 [N,L,8] table rows in the torch path's corner order (parity checks). */
 int nkbs_encode_fwd(int32_t mode, const float* x, const float* origins, const float* directions,
-                    const float* starts, const float* ends, int64_t R, int32_t S, int32_t contraction,
+                    const float* starts, const float* ends, int32_t bin_stride, int64_t R, int32_t S, int32_t contraction,
                     const float* aabb, const float* table, const float* scalings, int32_t L, int32_t log2_T,
                     int32_t F, float* xn, float* selector, float* features, int64_t* indices, void* stream);
 
@@ -74,12 +76,12 @@ int nkbs_mlp_tc_bwd(const float* x, const float* dy, int64_t N, int32_t nl, cons
  * error (callers use K1 + K3).  W1 [H,2L], b1 [H], W2 [1,H], b2 [1] in torch nn.Linear layout.
  * bwd recomputes the forward and ACCUMULATES into dtable [L*T,2], dW1, db1, dW2, db2. */
 int nkbs_density_fwd(int32_t mode, const float* x, const float* origins, const float* directions,
-                     const float* starts, const float* ends, int64_t R, int32_t S, int32_t contraction,
+                     const float* starts, const float* ends, int32_t bin_stride, int64_t R, int32_t S, int32_t contraction,
                      const float* aabb, const float* table, const float* scalings, int32_t L, int32_t log2_T,
                      const float* W1, const float* b1, const float* W2, const float* b2, int32_t H,
                      float* density, void* stream);
 int nkbs_density_bwd(int32_t mode, const float* x, const float* origins, const float* directions,
-                     const float* starts, const float* ends, int64_t R, int32_t S, int32_t contraction,
+                     const float* starts, const float* ends, int32_t bin_stride, int64_t R, int32_t S, int32_t contraction,
                      const float* aabb, const float* table, const float* scalings, int32_t L, int32_t log2_T,
                      const float* W1, const float* b1, const float* W2, const float* b2, int32_t H,
                      const float* ddensity, int32_t dedup_levels, float* dtable, float* dW1, float* db1,
@@ -176,12 +178,12 @@ int nkbs_pdf_sample(int64_t R, int32_t S, int32_t num_bins, const float* weights
  * 2 white.  depth_exp = clip(depth_exp_raw, steps.min(), steps.max()) over the whole batch;
  * depth_mask = 1 where the clip is the identity; minmax_ws = int32[2] workspace. */
 int nkbs_composite_fwd(int64_t R, int32_t S, const float* density, const float* weights_in,
-                       const float* starts, const float* ends, const float* rgb, const float* sem, int32_t C,
+                       const float* starts, const float* ends, int32_t bin_stride, const float* rgb, const float* sem, int32_t C,
                        int32_t bg_mode, int32_t eval_mode, float* weights, float* rgb_out, float* acc_out,
                        float* depth_exp_raw, float* depth_exp, float* depth_mask, float* depth_med,
                        float* sem_out, int32_t* minmax_ws, void* stream);
 int nkbs_composite_bwd(int64_t R, int32_t S, const float* density, const float* weights, const float* starts,
-                       const float* ends, const float* rgb, const float* sem, int32_t C, int32_t bg_mode,
+                       const float* ends, int32_t bin_stride, const float* rgb, const float* sem, int32_t C, int32_t bg_mode,
                        int32_t sem_weight_grad, const float* acc, const float* depth_raw,
                        const float* g_weights, const float* g_rgb, const float* g_acc, const float* g_depth,
                        const float* g_sem, float* d_density, float* d_weights, float* d_rgb, float* d_sem,

@@ -18,14 +18,14 @@ _f = C.c_float
 
 # name -> argtypes, in the order of include/nkbs.h
 SIGNATURES = {
-    "nkbs_encode_fwd": [_i32, _p, _p, _p, _p, _p, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p],
+    "nkbs_encode_fwd": [_i32, _p, _p, _p, _p, _p, _i32, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p],
     "nkbs_encode_bwd": [_p, _p, _i64, _p, _i32, _i32, _i32, _i32, _p, _p],
     "nkbs_mlp_fwd": [_p, _i64, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p],
     "nkbs_mlp_bwd": [_p, _p, _i64, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _p],
     "nkbs_mlp_tc_fwd": [_p, _i64, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p],
     "nkbs_mlp_tc_bwd": [_p, _p, _i64, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p],
-    "nkbs_density_fwd": [_i32, _p, _p, _p, _p, _p, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _i32, _p, _p],
-    "nkbs_density_bwd": [_i32, _p, _p, _p, _p, _p, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _i32, _p, _i32,
+    "nkbs_density_fwd": [_i32, _p, _p, _p, _p, _p, _i32, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _i32, _p, _p],
+    "nkbs_density_bwd": [_i32, _p, _p, _p, _p, _p, _i32, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _i32, _p, _i32,
                          _p, _p, _p, _p, _p, _p],
     "nkbs_ray_losses": [_i64, _i32, _p, _p, _p, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _i64, _p, _p, _p],
     "nkbs_generate_rays": [_i64, _p, _p, _p, _i64, _p, _p, _p, _p, _p, _p],
@@ -40,9 +40,9 @@ SIGNATURES = {
     "nkbs_assemble_bwd": [_i64, _i32, _i32, _i32, _i32, _p, _p, _p, _i32, _p, _p],
     "nkbs_initial_sampler": [_i64, _i32, _p, _p, _i32, _p, _p, _p, _p, _p],
     "nkbs_pdf_sample": [_i64, _i32, _i32, _p, _f, _p, _f, _f, _p, _p, _p, _i32, _p, _p, _p, _p, _p, _p],
-    "nkbs_composite_fwd": [_i64, _i32, _p, _p, _p, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
+    "nkbs_composite_fwd": [_i64, _i32, _p, _p, _p, _p, _i32, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
     "nkbs_adam_step": [_i32, _p, _p, _p, _p, _p, _f, _f, _f, _f, _f, _p, _p, _p],
-    "nkbs_composite_bwd": [_i64, _i32, _p, _p, _p, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
+    "nkbs_composite_bwd": [_i64, _i32, _p, _p, _p, _p, _i32, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
 }
 
 _lib = None
@@ -74,6 +74,18 @@ def ptr(t):
         return None
     assert t.is_contiguous(), "nkbs kernels take contiguous tensors"
     return t.data_ptr()
+
+
+def rows(starts, ends):
+    """[R,S] starts / ends with unit inner stride and a common row stride (e.g. the two views bins[:, :-1] and
+    bins[:, 1:] of one [R,S+1] bin-edge array) -> (starts pointer, ends pointer, row stride) without a copy;
+    anything else is made contiguous first.  (None, None, 0) when absent."""
+    if starts is None:
+        return None, None, 0, ()
+    if not (starts.dim() == 2 and starts.stride(1) == 1 and ends.stride(1) == 1 and starts.stride(0) == ends.stride(0)
+            and starts.stride(0) >= starts.shape[1]):
+        starts, ends = starts.contiguous(), ends.contiguous()
+    return starts.data_ptr(), ends.data_ptr(), starts.stride(0) if starts.shape[0] > 1 else max(starts.stride(0), starts.shape[1]), (starts, ends)
 
 
 def stream() -> int:

@@ -17,8 +17,9 @@ struct CompArgs {
   // weights source: density (compute alpha/transmittance) or precomputed weights
   const float* density;   // [R,S] or null
   const float* weights_in;// [R,S] or null
-  const float* starts;    // [R,S] euclidean bin starts (needed for density and depth)
+  const float* starts;    // [R,S] euclidean bin starts (needed for density and depth), row stride bstride
   const float* ends;      // [R,S]
+  int bstride;            // floats between consecutive rays in starts / ends (S, or S+1 for views of bin edges)
   const float* rgb;       // [R,S,3] or null
   const float* sem;       // [R,S,C] or null
   int C;
@@ -68,6 +69,7 @@ __global__ void __launch_bounds__(kThreads) composite_fwd_kernel(const CompArgs 
   float lmin = FLT_MAX, lmax = -FLT_MAX;
   for (int64_t r = blockIdx.x * (int64_t)kWarpsPerCta + wid; r < a.R; r += (int64_t)gridDim.x * kWarpsPerCta) {
     const int64_t base = r * S;
+    const int64_t bb = r * a.bstride;
     float carry = 0.f;  // exclusive prefix of delta*sigma entering this 32-sample chunk
     float acc = 0.f, dsum = 0.f;
     for (int s0 = 0; s0 < S; s0 += 32) {
@@ -75,8 +77,8 @@ __global__ void __launch_bounds__(kThreads) composite_fwd_kernel(const CompArgs 
       bool live = s < S;
       float st = 0.f, en = 0.f, w = 0.f;
       if (live && a.starts) {
-        st = a.starts[base + s];
-        en = a.ends[base + s];
+        st = a.starts[bb + s];
+        en = a.ends[bb + s];
       }
       if (a.density) {
         float x = live ? (en - st) * a.density[base + s] : 0.f;
@@ -104,21 +106,31 @@ __global__ void __launch_bounds__(kThreads) composite_fwd_kernel(const CompArgs 
     if (a.acc_out && lane == 0) a.acc_out[r] = acc;
     if (a.depth_exp && lane == 0) a.depth_exp[r] = dsum / (acc + 1e-10f);
     if (a.depth_med) {
-      // inclusive cumsum in sample order, double accumulator rounded to float per element (what
-      // torch.cumsum does on the CPU); first index with cum >= 0.5
-      if (lane == 0) {
-        double cum = 0.0;
-        int idx = S;
-        for (int s = 0; s < S; ++s) {
-          cum += (double)sw[s];
-          if ((float)cum >= 0.5f) {
-            idx = s;
-            break;
-          }
-        }
-        if (idx > S - 1) idx = S - 1;
-        a.depth_med[r] = (a.starts[base + idx] + a.ends[base + idx]) / 2.f;
+      // first index whose inclusive cumulative weight (double accumulator rounded to float per element, what
+      // torch.cumsum does on the CPU) reaches 0.5.  Every lane owns a contiguous run of samples: run totals are
+      // scanned across the warp in double, then each lane walks its own run.
+      const int per = (S + 31) >> 5;
+      const int s0 = min(lane * per, S), s1 = min(s0 + per, S);
+      double local = 0.0;
+      for (int s = s0; s < s1; ++s) local += (double)sw[s];
+      double incl = local;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const double t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
       }
+      double cum = incl - local;
+      int idx = S;
+      for (int s = s0; s < s1; ++s) {
+        cum += (double)sw[s];
+        if ((float)cum >= 0.5f) {
+          idx = s;
+          break;
+        }
+      }
+      const unsigned hit = __ballot_sync(0xffffffffu, idx < S);
+      idx = hit ? __shfl_sync(0xffffffffu, idx, __ffs(hit) - 1) : S - 1;
+      if (lane == 0) a.depth_med[r] = (a.starts[bb + idx] + a.ends[bb + idx]) / 2.f;
     }
     if (a.rgb_out) {
       // lanes 0..2 = colour channel accumulators would idle 29 lanes; instead stride the flat [S*3] strip
@@ -201,6 +213,7 @@ struct CompBwdArgs {
   const float* weights;    // [R,S] saved forward weights
   const float* starts;
   const float* ends;
+  int bstride;
   const float* rgb;        // [R,S,3] or null
   const float* sem;        // [R,S,C] or null
   int C;
@@ -230,6 +243,7 @@ __global__ void __launch_bounds__(kThreads) composite_bwd_kernel(const CompBwdAr
   float* sE = sg + S;
   for (int64_t r = blockIdx.x * (int64_t)kWarpsPerCta + wid; r < a.R; r += (int64_t)gridDim.x * kWarpsPerCta) {
     const int64_t base = r * S;
+    const int64_t bb = r * a.bstride;
     const float acc = a.acc ? a.acc[r] : 0.f;
     float gr[3] = {0.f, 0.f, 0.f}, bg[3] = {0.f, 0.f, 0.f};
     if (a.g_rgb) {
@@ -259,7 +273,7 @@ __global__ void __launch_bounds__(kThreads) composite_bwd_kernel(const CompBwdAr
         const float* c = a.rgb + (base + s) * 3;
         g += gr[0] * (c[0] - bg[0]) + gr[1] * (c[1] - bg[1]) + gr[2] * (c[2] - bg[2]);
       }
-      if (a.g_depth) g += g_dsum * ((a.starts[base + s] + a.ends[base + s]) / 2.f);
+      if (a.g_depth) g += g_dsum * ((a.starts[bb + s] + a.ends[bb + s]) / 2.f);
       if (a.g_sem && a.sem_weight_grad) {
         const float* q = a.sem + (base + s) * a.C;
         const float* gq = a.g_sem + r * a.C;
@@ -296,7 +310,7 @@ __global__ void __launch_bounds__(kThreads) composite_bwd_kernel(const CompBwdAr
       for (int s0 = 0; s0 < S; s0 += 32) {
         int s = s0 + lane;
         bool live = s < S;
-        float x = live ? (a.ends[base + s] - a.starts[base + s]) * a.density[base + s] : 0.f;
+        float x = live ? (a.ends[bb + s] - a.starts[bb + s]) * a.density[base + s] : 0.f;
         float ix = warp_incl_scan(x, lane);
         if (live) sE[s] = expf(-(carry_x + ix));
         carry_x += __shfl_sync(0xffffffffu, ix, 31);
@@ -316,7 +330,7 @@ __global__ void __launch_bounds__(kThreads) composite_bwd_kernel(const CompBwdAr
         }
         float suffix_excl = carry_q + (sq - q);
         if (live) {
-          float delta = a.ends[base + s] - a.starts[base + s];
+          float delta = a.ends[bb + s] - a.starts[bb + s];
           a.d_density[base + s] = delta * (sg[s] * sE[s] - suffix_excl);
         }
         carry_q += __shfl_sync(0xffffffffu, sq, 0);
@@ -336,8 +350,8 @@ int comp_grid(int64_t R) {
 }  // namespace
 
 extern "C" int nkbs_composite_fwd(int64_t R, int32_t S, const float* density, const float* weights_in,
-                                  const float* starts, const float* ends, const float* rgb, const float* sem,
-                                  int32_t C, int32_t bg_mode, int32_t eval_mode, float* weights, float* rgb_out,
+                                  const float* starts, const float* ends, int32_t bin_stride, const float* rgb,
+                                  const float* sem, int32_t C, int32_t bg_mode, int32_t eval_mode, float* weights, float* rgb_out,
                                   float* acc_out, float* depth_exp_raw, float* depth_exp, float* depth_mask,
                                   float* depth_med, float* sem_out, int32_t* minmax_ws, void* stream) {
   NKBS_CHECK_ARG(R >= 0 && S >= 1 && S <= kMaxS, "nkbs_composite_fwd: S=%d outside 1..%d", S, kMaxS);
@@ -351,7 +365,8 @@ extern "C" int nkbs_composite_fwd(int64_t R, int32_t S, const float* density, co
   NKBS_CHECK_ARG(bg_mode >= 0 && bg_mode <= 2, "nkbs_composite_fwd: unknown background mode %d", bg_mode);
   if (R == 0) return 0;
   cudaStream_t st = (cudaStream_t)stream;
-  CompArgs a{R, S, density, weights_in, starts, ends, rgb, sem, C, bg_mode, eval_mode,
+  NKBS_CHECK_ARG(bin_stride == 0 || bin_stride >= S, "nkbs_composite_fwd: bin_stride %d < S", bin_stride);
+  CompArgs a{R, S, density, weights_in, starts, ends, bin_stride ? bin_stride : S, rgb, sem, C, bg_mode, eval_mode,
              weights, rgb_out, acc_out, depth_exp_raw, depth_med, sem_out, depth_exp ? minmax_ws : nullptr};
   if (depth_exp) minmax_init_kernel<<<1, 1, 0, st>>>(minmax_ws);
   size_t smem = (size_t)kWarpsPerCta * S * sizeof(float);
@@ -365,8 +380,8 @@ extern "C" int nkbs_composite_fwd(int64_t R, int32_t S, const float* density, co
 }
 
 extern "C" int nkbs_composite_bwd(int64_t R, int32_t S, const float* density, const float* weights,
-                                  const float* starts, const float* ends, const float* rgb, const float* sem,
-                                  int32_t C, int32_t bg_mode, int32_t sem_weight_grad, const float* acc,
+                                  const float* starts, const float* ends, int32_t bin_stride, const float* rgb,
+                                  const float* sem, int32_t C, int32_t bg_mode, int32_t sem_weight_grad, const float* acc,
                                   const float* depth_raw, const float* g_weights, const float* g_rgb,
                                   const float* g_acc, const float* g_depth, const float* g_sem, float* d_density,
                                   float* d_weights, float* d_rgb, float* d_sem, void* stream) {
@@ -379,7 +394,8 @@ extern "C" int nkbs_composite_bwd(int64_t R, int32_t S, const float* density, co
   NKBS_CHECK_ARG(!(g_sem && sem_weight_grad) || sem, "nkbs_composite_bwd: semantic weight gradient needs sem");
   NKBS_CHECK_ARG(!d_rgb || acc || bg_mode != 0, "nkbs_composite_bwd: d_rgb with last_sample background needs accumulation");
   if (R == 0) return 0;
-  CompBwdArgs a{R, S, density, weights, starts, ends, rgb, sem, C, bg_mode, sem_weight_grad, acc, depth_raw,
+  NKBS_CHECK_ARG(bin_stride == 0 || bin_stride >= S, "nkbs_composite_bwd: bin_stride %d < S", bin_stride);
+  CompBwdArgs a{R, S, density, weights, starts, ends, bin_stride ? bin_stride : S, rgb, sem, C, bg_mode, sem_weight_grad, acc, depth_raw,
                 g_weights, g_rgb, g_acc, g_depth, g_sem, d_density, d_weights, d_rgb, d_sem};
   size_t smem = (size_t)kWarpsPerCta * 3 * S * sizeof(float);
   composite_bwd_kernel<<<comp_grid(R), kThreads, smem, (cudaStream_t)stream>>>(a);

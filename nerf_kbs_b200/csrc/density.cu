@@ -264,7 +264,7 @@ int grid_for(Kern kern, int64_t N) {
 }
 
 int fill(DensityArgs& a, const char* who, int mode, const float* x, const float* origins, const float* directions,
-         const float* starts, const float* ends, int64_t R, int32_t S, int contraction, const float* aabb,
+         const float* starts, const float* ends, int bin_stride, int64_t R, int32_t S, int contraction, const float* aabb,
          const float* table, const float* scalings, int L, int log2_T, const float* W1, const float* b1,
          const float* W2, const float* b2, int H) {
   NKBS_CHECK_ARG(mode == 1 || mode == 2, "%s: mode must be 1 (positions) or 2 (frustums), got %d", who, mode);
@@ -283,6 +283,8 @@ int fill(DensityArgs& a, const char* who, int mode, const float* x, const float*
   a.starts = starts;
   a.ends = ends;
   a.S = S;
+  NKBS_CHECK_ARG(bin_stride == 0 || bin_stride >= S, "%s: bin_stride %d < S", who, bin_stride);
+  a.bstride = bin_stride ? bin_stride : S;
   a.N = R * (int64_t)S;
   a.norm.contraction = contraction;
   for (int i = 0; i < 3; ++i) {
@@ -305,12 +307,13 @@ int fill(DensityArgs& a, const char* who, int mode, const float* x, const float*
 }  // namespace
 
 extern "C" int nkbs_density_fwd(int32_t mode, const float* x, const float* origins, const float* directions,
-                                const float* starts, const float* ends, int64_t R, int32_t S, int32_t contraction,
+                                const float* starts, const float* ends, int32_t bin_stride, int64_t R, int32_t S,
+                                int32_t contraction,
                                 const float* aabb, const float* table, const float* scalings, int32_t L,
                                 int32_t log2_T, const float* W1, const float* b1, const float* W2, const float* b2,
                                 int32_t H, float* density, void* stream) {
   DensityArgs a;
-  if (fill(a, "nkbs_density_fwd", mode, x, origins, directions, starts, ends, R, S, contraction, aabb, table, scalings,
+  if (fill(a, "nkbs_density_fwd", mode, x, origins, directions, starts, ends, bin_stride, R, S, contraction, aabb, table, scalings,
            L, log2_T, W1, b1, W2, b2, H))
     return -1;
   if (a.N == 0) return 0;
@@ -326,13 +329,14 @@ extern "C" int nkbs_density_fwd(int32_t mode, const float* x, const float* origi
 }
 
 extern "C" int nkbs_density_bwd(int32_t mode, const float* x, const float* origins, const float* directions,
-                                const float* starts, const float* ends, int64_t R, int32_t S, int32_t contraction,
+                                const float* starts, const float* ends, int32_t bin_stride, int64_t R, int32_t S,
+                                int32_t contraction,
                                 const float* aabb, const float* table, const float* scalings, int32_t L,
                                 int32_t log2_T, const float* W1, const float* b1, const float* W2, const float* b2,
                                 int32_t H, const float* ddensity, int32_t dedup_levels, float* dtable, float* dW1,
                                 float* db1, float* dW2, float* db2, void* stream) {
   DensityArgs a;
-  if (fill(a, "nkbs_density_bwd", mode, x, origins, directions, starts, ends, R, S, contraction, aabb, table, scalings,
+  if (fill(a, "nkbs_density_bwd", mode, x, origins, directions, starts, ends, bin_stride, R, S, contraction, aabb, table, scalings,
            L, log2_T, W1, b1, W2, b2, H))
     return -1;
   if (a.N == 0) return 0;

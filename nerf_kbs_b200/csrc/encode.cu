@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(kEncThreads) encode_bwd_kernel(const EncodeBwd
 }  // namespace
 
 extern "C" int nkbs_encode_fwd(int mode, const float* x, const float* origins, const float* directions,
-                               const float* starts, const float* ends, int64_t R, int32_t S, int contraction,
+                               const float* starts, const float* ends, int32_t bin_stride, int64_t R, int32_t S, int contraction,
                                const float* aabb, const float* table, const float* scalings, int32_t L,
                                int32_t log2_T, int32_t F, float* xn, float* selector, float* features,
                                int64_t* indices, void* stream) {
@@ -130,6 +130,8 @@ extern "C" int nkbs_encode_fwd(int mode, const float* x, const float* origins, c
   a.ends = ends;
   a.N = R * (int64_t)S;
   a.S = S;
+  NKBS_CHECK_ARG(bin_stride == 0 || bin_stride >= S, "nkbs_encode_fwd: bin_stride %d < S", bin_stride);
+  a.bstride = bin_stride ? bin_stride : S;
   a.norm.contraction = contraction;
   for (int i = 0; i < 3; ++i) {
     a.norm.aabb_min[i] = aabb ? aabb[i] : 0.f;

@@ -11,6 +11,7 @@ struct SampleSource {
   const float* starts;
   const float* ends;
   int S;
+  int bstride;  // floats between consecutive rays in starts / ends (S, or S+1 for views of an [R,S+1] bin array)
   NormParams norm;
 };
 
@@ -20,7 +21,8 @@ __device__ __forceinline__ float3 load_sample_position(const SampleSource& a, in
     int64_t r = n / a.S;
     float3 o = make_float3(a.origins[3 * r], a.origins[3 * r + 1], a.origins[3 * r + 2]);
     float3 d = make_float3(a.directions[3 * r], a.directions[3 * r + 1], a.directions[3 * r + 2]);
-    p = nkbs_frustum_position(o, d, a.starts[n], a.ends[n]);
+    const int64_t b = r * a.bstride + (n - r * a.S);
+    p = nkbs_frustum_position(o, d, a.starts[b], a.ends[b]);
   } else {
     p = make_float3(a.x[3 * n], a.x[3 * n + 1], a.x[3 * n + 2]);
   }

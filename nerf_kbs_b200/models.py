@@ -89,6 +89,10 @@ class _ModelBase(nn.Module):
     def _prop_depths(self, outputs, weights_list, ray_samples_list):
         for i in range(self.config.num_proposal_iterations):
             rs = ray_samples_list[i]
+            cached = getattr(weights_list[i], "_nkbs_depth_med", None)
+            if cached is not None:  # computed by the launch that produced the level's weights (RaySamples.get_weights)
+                outputs[f"prop_depth_{i}"] = cached
+                continue
             outputs[f"prop_depth_{i}"] = ops.composite(
                 weights=weights_list[i].detach(), starts=rs.frustums.starts, ends=rs.frustums.ends,
                 want=("depth_med",))["depth"]

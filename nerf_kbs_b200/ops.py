@@ -11,7 +11,7 @@ from typing import List, Optional, Sequence, Tuple
 import torch
 
 from . import _lib
-from ._lib import call, host_floats, host_i32, host_ptrs, ptr, require_cuda, stream
+from ._lib import call, host_floats, host_i32, host_ptrs, ptr, require_cuda, rows, stream
 
 ACT_NONE, ACT_SIGMOID, ACT_DENSITY, ACT_TRANSIENT = 0, 1, 2, 3
 BG_MODES = {"last_sample": 0, "black": 1, "white": 2}
@@ -65,7 +65,8 @@ def encode_raw(mode: int, grid: GridSpec, norm: Optional[NormSpec], table, x=Non
     xn = torch.empty((N, 3), device=dev, dtype=torch.float32)
     idx = torch.empty((N, grid.L, 8), device=dev, dtype=torch.int64) if want_indices else None
     aabb = host_floats(norm.aabb) if norm is not None else None
-    call("nkbs_encode_fwd", mode, ptr(x), ptr(origins), ptr(directions), ptr(starts), ptr(ends), R, S,
+    p_st, p_en, bstride, _keep = rows(starts, ends)
+    call("nkbs_encode_fwd", mode, ptr(x), ptr(origins), ptr(directions), p_st, p_en, bstride, R, S,
          int(norm.contraction) if norm is not None else 0, aabb, ptr(table), host_floats(grid.scalings), grid.L,
          grid.log2_T, grid.features_per_level, ptr(xn), ptr(sel), ptr(feats), ptr(idx), stream())
     return feats, sel, xn, idx
@@ -114,7 +115,7 @@ def contract_encode(table, grid: GridSpec, norm: NormSpec, positions=None, origi
                                           None, None, None)
     else:
         feats, sel, _ = _HashEncode.apply(table, 2, grid, norm, dedup_levels, None, _c(origins), _c(directions),
-                                          _c(starts), _c(ends))
+                                          starts.float(), ends.float())
     return feats, sel
 
 
@@ -146,7 +147,8 @@ class _FusedDensity(torch.autograd.Function):
         H = W1.shape[0]
         density = torch.empty((R * S,), device=dev, dtype=torch.float32)
         aabb = host_floats(norm.aabb)
-        call("nkbs_density_fwd", mode, ptr(x), ptr(origins), ptr(directions), ptr(starts), ptr(ends), R, S,
+        p_st, p_en, bstride, _keep = rows(starts, ends)
+        call("nkbs_density_fwd", mode, ptr(x), ptr(origins), ptr(directions), p_st, p_en, bstride, R, S,
              int(norm.contraction), aabb, ptr(table), host_floats(grid.scalings), grid.L, grid.log2_T, ptr(W1), ptr(b1),
              ptr(W2), ptr(b2), H, ptr(density), stream())
         # proposal rays carry 96-256 samples: neighbouring samples share cells on every level of these grids
@@ -161,7 +163,8 @@ class _FusedDensity(torch.autograd.Function):
         ddensity = _c(ddensity)
         dtable = torch.zeros_like(table)
         dW1, db1, dW2, db2 = (torch.zeros_like(t) for t in (W1, b1, W2, b2))
-        call("nkbs_density_bwd", mode, ptr(x), ptr(origins), ptr(directions), ptr(starts), ptr(ends), R, S,
+        p_st, p_en, bstride, _keep = rows(starts, ends)
+        call("nkbs_density_bwd", mode, ptr(x), ptr(origins), ptr(directions), p_st, p_en, bstride, R, S,
              int(norm.contraction), host_floats(norm.aabb), ptr(table), host_floats(grid.scalings), grid.L, grid.log2_T,
              ptr(W1), ptr(b1), ptr(W2), ptr(b2), H, ptr(ddensity), dedup, ptr(dtable), ptr(dW1), ptr(db1), ptr(dW2),
              ptr(db2), stream())
@@ -179,7 +182,7 @@ def fused_density(table, grid: GridSpec, norm: NormSpec, W1, b1, W2, b2, positio
         return _FusedDensity.apply(table, W1, b1, W2, b2, grid, norm, dedup_levels, _c(positions).reshape(-1, 3), None,
                                    None, None, None)
     return _FusedDensity.apply(table, W1, b1, W2, b2, grid, norm, dedup_levels, None, _c(origins), _c(directions),
-                               _c(starts), _c(ends))
+                               starts.float(), ends.float())
 
 
 # ----------------------------------------------------------------------------------------------
@@ -444,8 +447,10 @@ class _Composite(torch.autograd.Function):
         R, S = src.shape[0], src.shape[1]
         dev = src.device
         density, weights_in, rgb, sem = _c(density), _c(weights_in), _c(rgb), _c(sem)
-        starts, ends = _c(starts), _c(ends)
         require_cuda(src, rgb, sem, starts)
+        p_st, p_en, bstride, keep = rows(starts, ends)
+        if keep:
+            starts, ends = keep
         C = sem.shape[-1] if sem is not None else 0
         f32 = dict(device=dev, dtype=torch.float32)
         weights = torch.empty((R, S), **f32) if density is not None else None
@@ -457,7 +462,7 @@ class _Composite(torch.autograd.Function):
         d_med = torch.empty((R,), **f32) if "depth_med" in want else None
         sem_out = torch.empty((R, C), **f32) if (sem is not None and "sem" in want) else None
         mm = torch.empty((2,), device=dev, dtype=torch.int32) if d_raw is not None else None
-        call("nkbs_composite_fwd", R, S, ptr(density), ptr(weights_in), ptr(starts), ptr(ends), ptr(rgb), ptr(sem),
+        call("nkbs_composite_fwd", R, S, ptr(density), ptr(weights_in), p_st, p_en, bstride, ptr(rgb), ptr(sem),
              C, bg_mode, int(eval_mode), ptr(weights), ptr(rgb_out), ptr(acc), ptr(d_raw), ptr(d_exp), ptr(d_mask),
              ptr(d_med), ptr(sem_out), ptr(mm), stream())
         w_saved = weights if density is not None else weights_in
@@ -483,7 +488,8 @@ class _Composite(torch.autograd.Function):
         d_weights = torch.empty((R, S), **f32) if (not from_density and need_src) else None
         d_rgb = torch.empty((R, S, 3), **f32) if (rgb is not None and ctx.needs_input_grad[2] and g_rgb is not None) else None
         d_sem = torch.empty((R, S, C), **f32) if (sem is not None and ctx.needs_input_grad[3] and g_sem is not None) else None
-        call("nkbs_composite_bwd", R, S, ptr(density), ptr(w), ptr(starts), ptr(ends), ptr(rgb), ptr(sem), C, bg_mode,
+        p_st, p_en, bstride, _keep = rows(starts, ends)
+        call("nkbs_composite_bwd", R, S, ptr(density), ptr(w), p_st, p_en, bstride, ptr(rgb), ptr(sem), C, bg_mode,
              int(sem_weight_grad), ptr(acc), ptr(d_raw), ptr(g_w), ptr(g_rgb) if rgb is not None else None,
              ptr(g_acc), ptr(g_depth), ptr(g_sem) if sem is not None else None, ptr(d_density), ptr(d_weights),
              ptr(d_rgb), ptr(d_sem), stream())

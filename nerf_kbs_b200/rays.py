@@ -59,8 +59,11 @@ class RaySamples:
         d = densities.reshape(-1, S)
         st = self.frustums.starts.reshape(-1, S)
         en = self.frustums.ends.reshape(-1, S)
-        out = ops.composite(density=d, starts=st, ends=en, want=())
-        return out["weights"].reshape(densities.shape)
+        # the median depth of the level comes out of the same launch (the models ask for it as prop_depth_i)
+        out = ops.composite(density=d, starts=st, ends=en, want=("depth_med",))
+        w = out["weights"].reshape(densities.shape)
+        w._nkbs_depth_med = out["depth"]
+        return w
 
 
 @dataclass

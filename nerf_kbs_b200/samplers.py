@@ -2,6 +2,9 @@
 ref:semantic_nerfw.py:132-137, called at ref:nerfacto.py:397 / ref:semantic_nerfw.py:187."""
 from __future__ import annotations
 
+import contextlib
+import os
+
 from typing import Callable, List, Optional, Tuple
 
 import torch
@@ -119,6 +122,15 @@ class ProposalNetworkSampler(nn.Module):
         self._steps_since_update = 0
         self._step = 0
         self.force_updated = None  # Trainer sets this while it captures the two CUDA-graph variants
+        # training proposal levels run on their own CUDA streams (see generate_ray_samples); NKBS_SIDE_STREAMS=0 disables
+        self.side_streams = os.environ.get("NKBS_SIDE_STREAMS", "1") != "0"
+        self._streams = {}
+
+    def _side_stream(self, level: int, device) -> "torch.cuda.Stream":
+        key = (level, device.index)
+        if key not in self._streams:
+            self._streams[key] = torch.cuda.Stream(device)
+        return self._streams[key]
 
     def set_anneal(self, anneal: float) -> None:
         self._anneal = anneal
@@ -153,12 +165,26 @@ class ProposalNetworkSampler(nn.Module):
             if is_prop:
                 fn = density_fns[i_level]
                 owner = getattr(fn, "__self__", None)
-                with torch.set_grad_enabled(updated and torch.is_grad_enabled()):
+                train_level = updated and torch.is_grad_enabled()
+                # A level that trains runs on its own CUDA stream.  The forward gains nothing (the next level waits
+                # for these weights) but autograd replays each node on the stream of its forward, so the backward of
+                # the proposal fields (atomics-bound table scatters) overlaps the main field's backward (tensor-core
+                # MLPs + its own scatter) instead of queueing behind it.  Works the same under CUDA-graph capture.
+                side = self._side_stream(i_level, ray_bundle.origins.device) if (train_level and self.side_streams) else None
+                cur = torch.cuda.current_stream() if side is not None else None
+                if side is not None:
+                    side.wait_stream(cur)
+                with torch.set_grad_enabled(train_level), (torch.cuda.stream(side) if side is not None else contextlib.nullcontext()):
                     if owner is not None and hasattr(owner, "get_density") and getattr(owner, "_norm", None) is not None:
                         density, _ = owner.get_density(ray_samples)  # per-ray frustum path, no [R,S,3] tensor
                     else:
                         density = fn(ray_samples.frustums.get_positions())
                     weights = ray_samples.get_weights(density)
+                if side is not None:
+                    cur.wait_stream(side)
+                    for t in (weights, getattr(weights, "_nkbs_depth_med", None)):
+                        if t is not None:
+                            t.record_stream(cur)
                 weights_list.append(weights)
                 ray_samples_list.append(ray_samples)
         if updated:
