@@ -15,6 +15,9 @@
 namespace {
 
 constexpr int kThreads = 256;
+#ifndef NKBS_DENSITY_BWD_CTAS
+#define NKBS_DENSITY_BWD_CTAS 2
+#endif
 constexpr int kWarps = kThreads / 32;
 constexpr int kRedStride = 36;  // floats per row of the transposed-sum scratch: 16-byte rows, conflict-free both ways
 
@@ -133,8 +136,12 @@ __device__ __forceinline__ float row_total(const float* scratch, int lane) {
   return t;
 }
 
+// resident CTAs per SM the backward is compiled for: the H = 16 field fits three (85 registers per thread)
+template <int H>
+constexpr int bwd_ctas() { return H <= 16 ? NKBS_DENSITY_BWD_CTAS : 1; }
+
 template <int H, int L>
-__global__ void __launch_bounds__(kThreads) density_bwd_kernel(const DensityArgs a) {
+__global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(const DensityArgs a) {
   constexpr int K = 2 * L, KP = Smem<H, L>::KP;
   // gradient rows, in this order: for each hidden unit j: dW1[j][0..K), db1[j], dW2[j]; then db2
   constexpr int kPerJ = K + 2;

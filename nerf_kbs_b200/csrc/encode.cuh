@@ -56,8 +56,13 @@ __device__ __forceinline__ void scatter_level_runs(float* base, const Cell& cl, 
     vy[k] = w[k] * gy;
   }
   if (heads != 0xffffffffu) {  // some run is longer than one lane
+    // start of this lane's run = highest head at or below the lane; the longest run of the warp bounds the
+    // number of reduction steps (fine levels hold runs of 2-4 samples: 1-2 steps instead of 5)
+    const int start = 31 - __clz(heads & ((2u << lane) - 1u));
+    const int longest = __reduce_max_sync(0xffffffffu, end - start + 1);
 #pragma unroll
     for (int off = 1; off < 32; off <<= 1) {
+      if (off >= longest) break;
       const bool take = lane + off <= end;
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
