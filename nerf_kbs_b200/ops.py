@@ -17,6 +17,18 @@ ACT_NONE, ACT_SIGMOID, ACT_DENSITY, ACT_TRANSIENT = 0, 1, 2, 3
 BG_MODES = {"last_sample": 0, "black": 1, "white": 2}
 
 
+def _zeros_like_many(tensors):
+    """One zero-filled flat buffer carved into views shaped like ``tensors`` (one fill launch instead of one per
+    tensor; the kernels accumulate into these gradient buffers)."""
+    sizes = [(t.numel() + 3) // 4 * 4 for t in tensors]  # 16-byte aligned pieces
+    flat = torch.zeros(sum(sizes), device=tensors[0].device, dtype=torch.float32)
+    out, o = [], 0
+    for t, n in zip(tensors, sizes):
+        out.append(flat[o:o + t.numel()].view(t.shape))
+        o += n
+    return out
+
+
 def _c(t: Optional[torch.Tensor], dtype=torch.float32) -> Optional[torch.Tensor]:
     if t is None:
         return None
@@ -161,8 +173,7 @@ class _FusedDensity(torch.autograd.Function):
         mode, R, S, H, grid, norm, dedup = ctx.cfg
         table, W1, b1, W2, b2, x, origins, directions, starts, ends = ctx.saved_tensors
         ddensity = _c(ddensity)
-        dtable = torch.zeros_like(table)
-        dW1, db1, dW2, db2 = (torch.zeros_like(t) for t in (W1, b1, W2, b2))
+        dtable, dW1, db1, dW2, db2 = _zeros_like_many([table, W1, b1, W2, b2])
         p_st, p_en, bstride, _keep = rows(starts, ends)
         call("nkbs_density_bwd", mode, ptr(x), ptr(origins), ptr(directions), p_st, p_en, bstride, R, S,
              int(norm.contraction), host_floats(norm.aabb), ptr(table), host_floats(grid.scalings), grid.L, grid.log2_T,
@@ -236,8 +247,8 @@ class _Mlp(torch.autograd.Function):
         dy = _c(dy)
         N = x.shape[0]
         dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
-        dWs = [torch.zeros_like(w) for w in Ws]
-        dbs = [torch.zeros_like(b) for b in bs]
+        zs = _zeros_like_many(Ws + bs)
+        dWs, dbs = zs[:nl], zs[nl:]
         if tc:
             call("nkbs_mlp_tc_bwd", ptr(x), ptr(dy), N, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask,
                  out_act, bwd_fmt, ptr(selector), ptr(dx), host_ptrs(dWs), host_ptrs(dbs), stream())
@@ -348,8 +359,8 @@ class _HeadMlp(torch.autograd.Function):
         N, stride = src.shape
         dsrc = torch.zeros_like(src) if ctx.needs_input_grad[0] else None
         demb = torch.zeros(emb_shape, device=src.device, dtype=torch.float32) if (use_cam and ctx.needs_input_grad[2]) else None
-        dWs = [torch.zeros_like(w) for w in Ws]
-        dbs = [torch.zeros_like(b) for b in bs]
+        zs = _zeros_like_many(Ws + bs)
+        dWs, dbs = zs[:nl], zs[nl:]
         geo = src.reshape(-1)[col:]
         dgeo = dsrc.reshape(-1)[col:] if dsrc is not None else None
         call("nkbs_head_tc_bwd", sh_dim, 15, emb_dim, ptr(geo), stride, ptr(directions), int(dpr),
