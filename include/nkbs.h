@@ -201,6 +201,16 @@ int nkbs_adam_step(int32_t num_tensors, float* const* params, const float* const
                    float beta1, float beta2, float eps, float weight_decay, const float* step_dev,
                    const float* inv_scale_dev, void* stream);
 
+/* N2 (data parallel) — reduce-scatter + Adam + all-gather in one kernel over NVLink peer memory.  grad_peers /
+ * param_peers: HOST arrays of `world` DEVICE pointers to the flat gradient / parameter buffer of every rank
+ * (symmetric memory: same layout on every GPU, peer-mapped).  This rank owns elements [lo, lo+n): it averages the
+ * peers' gradients of that slice, updates its own shard of the moments (exp_avg, exp_avg_sq: [n]) and stores the new
+ * parameters into every rank's buffer.  The caller orders it between two cross-rank barriers.
+ * replaces: NCCL allreduce of the gradients + nkbs_adam_step (datamanager_z.py:225-231 DDP setup; train.py:85-98). */
+int nkbs_dp_adam_step(int32_t world, int32_t rank, const float* const* grad_peers, float* const* param_peers,
+                      int64_t lo, int64_t n, float* exp_avg, float* exp_avg_sq, float lr, float beta1, float beta2,
+                      float eps, float weight_decay, const float* step_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -78,6 +78,57 @@ __global__ void __launch_bounds__(kThreads) adam_kernel(const AdamArgs a) {
   }
 }
 
+// ---- data-parallel step over NVLink peer memory: reduce-scatter + Adam + all-gather in ONE kernel ----
+// Every rank owns the slice [lo, lo+n) of a flat parameter buffer that exists at the same offsets on every GPU
+// (symmetric memory).  For its slice a rank reads the gradient from all peers (P2P loads), averages, applies Adam
+// with moments it alone keeps (a 1/world shard), and stores the new parameters into every peer's buffer (P2P
+// stores).  Link traffic equals an allreduce's (reduce-scatter + all-gather) but the separate Adam pass, its
+// 7 words/parameter of HBM traffic on every GPU and the gradient scaling pass are gone.
+constexpr int kMaxPeers = 16;
+struct DpAdamArgs {
+  const float* g[kMaxPeers];  // flat gradient buffer of every rank
+  float* p[kMaxPeers];        // flat parameter buffer of every rank
+  int world, rank;
+  int64_t lo, n;              // this rank's slice (elements; lo and n are multiples of 4)
+  float* m;                   // [n] first moments of the slice
+  float* v;                   // [n]
+  float lr, beta1, beta2, eps, weight_decay;
+  const float* step_dev;
+};
+
+__global__ void __launch_bounds__(kThreads) dp_adam_kernel(const DpAdamArgs a) {
+  const float t = *a.step_dev;
+  const float bc1 = 1.f - powf(a.beta1, t);
+  const float bc2 = 1.f - powf(a.beta2, t);
+  const float step_size = a.lr / bc1;
+  const float sqrt_bc2 = sqrtf(bc2);
+  const float inv_world = 1.f / (float)a.world;
+  const int64_t nvec = a.n >> 2;
+  for (int64_t q = blockIdx.x * (int64_t)kThreads + threadIdx.x; q < nvec; q += (int64_t)gridDim.x * kThreads) {
+    const int64_t i = a.lo + 4 * q;
+    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+    for (int r = 0; r < a.world; ++r) {  // own rank first would not change the sum order across ranks: keep rank order
+      const float4 x = *reinterpret_cast<const float4*>(a.g[r] + i);
+      g.x += x.x;
+      g.y += x.y;
+      g.z += x.z;
+      g.w += x.w;
+    }
+    float4 p = *reinterpret_cast<const float4*>(a.p[a.rank] + i);
+    float4 m = *reinterpret_cast<const float4*>(a.m + 4 * q);
+    float4 v = *reinterpret_cast<const float4*>(a.v + 4 * q);
+    adam_one(p.x, g.x * inv_world, m.x, v.x, a.beta1, a.beta2, a.eps, step_size, sqrt_bc2, a.weight_decay);
+    adam_one(p.y, g.y * inv_world, m.y, v.y, a.beta1, a.beta2, a.eps, step_size, sqrt_bc2, a.weight_decay);
+    adam_one(p.z, g.z * inv_world, m.z, v.z, a.beta1, a.beta2, a.eps, step_size, sqrt_bc2, a.weight_decay);
+    adam_one(p.w, g.w * inv_world, m.w, v.w, a.beta1, a.beta2, a.eps, step_size, sqrt_bc2, a.weight_decay);
+    *reinterpret_cast<float4*>(a.m + 4 * q) = m;
+    *reinterpret_cast<float4*>(a.v + 4 * q) = v;
+#pragma unroll 1
+    for (int r = 0; r < a.world; ++r) *reinterpret_cast<float4*>(a.p[r] + i) = p;
+  }
+}
+
 }  // namespace
 
 extern "C" int nkbs_adam_step(int32_t num_tensors, float* const* params, const float* const* grads,
@@ -114,5 +165,39 @@ extern "C" int nkbs_adam_step(int32_t num_tensors, float* const* params, const f
     adam_kernel<<<blocks, kThreads, 0, (cudaStream_t)stream>>>(a);
     NKBS_CHECK_LAUNCH("nkbs_adam_step");
   }
+  return 0;
+}
+
+extern "C" int nkbs_dp_adam_step(int32_t world, int32_t rank, const float* const* grad_peers, float* const* param_peers,
+                                 int64_t lo, int64_t n, float* exp_avg, float* exp_avg_sq, float lr, float beta1,
+                                 float beta2, float eps, float weight_decay, const float* step_dev, void* stream) {
+  NKBS_CHECK_ARG(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world, "nkbs_dp_adam_step: bad world/rank %d/%d", world, rank);
+  NKBS_CHECK_ARG(lo >= 0 && n >= 0 && (lo & 3) == 0 && (n & 3) == 0, "nkbs_dp_adam_step: slice must be 4-element aligned");
+  if (n == 0) return 0;
+  NKBS_CHECK_ARG(grad_peers && param_peers && exp_avg && exp_avg_sq && step_dev, "nkbs_dp_adam_step: null pointers");
+  DpAdamArgs a;
+  for (int r = 0; r < world; ++r) {
+    NKBS_CHECK_ARG(grad_peers[r] && param_peers[r], "nkbs_dp_adam_step: null peer buffer %d", r);
+    NKBS_CHECK_ARG(((reinterpret_cast<uintptr_t>(grad_peers[r]) | reinterpret_cast<uintptr_t>(param_peers[r])) & 15) == 0,
+                   "nkbs_dp_adam_step: peer buffers must be 16-byte aligned");
+    a.g[r] = grad_peers[r];
+    a.p[r] = param_peers[r];
+  }
+  a.world = world;
+  a.rank = rank;
+  a.lo = lo;
+  a.n = n;
+  a.m = exp_avg;
+  a.v = exp_avg_sq;
+  a.lr = lr;
+  a.beta1 = beta1;
+  a.beta2 = beta2;
+  a.eps = eps;
+  a.weight_decay = weight_decay;
+  a.step_dev = step_dev;
+  int64_t blocks = ((n >> 2) + kThreads - 1) / kThreads;
+  int64_t cap = (int64_t)nkbs_num_sms() * 8;
+  dp_adam_kernel<<<(int)(blocks < cap ? blocks : cap), kThreads, 0, (cudaStream_t)stream>>>(a);
+  NKBS_CHECK_LAUNCH("nkbs_dp_adam_step");
   return 0;
 }

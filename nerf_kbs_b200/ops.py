@@ -89,8 +89,9 @@ class _HashEncode(torch.autograd.Function):
     are detached in the reference path: PDF bins are detached)."""
 
     @staticmethod
-    def forward(ctx, table, mode, grid, norm, dedup_levels, x, origins, directions, starts, ends):
+    def forward(ctx, table, mode, grid, norm, dedup_levels, x, origins, directions, starts, ends, sink=None):
         feats, sel, xn, _ = encode_raw(mode, grid, norm, table, x, origins, directions, starts, ends)
+        ctx.sink = sink  # optional pre-registered gradient buffer (dp_optim.ShardedAdam: symmetric memory)
         ctx.grid = grid
         # run merging (segmented shuffle reduction, csrc/encode.cuh) costs a ballot on levels without duplicates and
         # never loses on B200 (scripts/encode_bench.py sweep): -1 = every level
@@ -104,11 +105,15 @@ class _HashEncode(torch.autograd.Function):
     def backward(ctx, dfeat, _dsel, _dxn):
         (xn,) = ctx.saved_tensors
         g = ctx.grid
-        dtable = torch.zeros(ctx.table_shape, device=xn.device, dtype=torch.float32)
+        if ctx.sink is not None:
+            dtable = ctx.sink.detach()
+            dtable.zero_()
+        else:
+            dtable = torch.zeros(ctx.table_shape, device=xn.device, dtype=torch.float32)
         dfeat = _c(dfeat)
         call("nkbs_encode_bwd", ptr(xn), ptr(dfeat), xn.shape[0], host_floats(g.scalings), g.L, g.log2_T,
              g.features_per_level, ctx.dedup, ptr(dtable), stream())
-        return (dtable,) + (None,) * 9
+        return (dtable,) + (None,) * 10
 
 
 def hash_encode(table, grid: GridSpec, x_normalised):
@@ -122,12 +127,13 @@ def contract_encode(table, grid: GridSpec, norm: NormSpec, positions=None, origi
                     starts=None, ends=None, dedup_levels=-1):
     """Front end + encoding.  Either raw ``positions`` [N,3] or per-ray ``origins/directions`` [R,3] with
     per-sample ``starts/ends`` [R,S].  Returns (features [N,2L], selector [N])."""
+    sink = getattr(table, "_nkbs_grad_sink", None)
     if positions is not None:
         feats, sel, _ = _HashEncode.apply(table, 1, grid, norm, dedup_levels, _c(positions).reshape(-1, 3), None,
-                                          None, None, None)
+                                          None, None, None, sink)
     else:
         feats, sel, _ = _HashEncode.apply(table, 2, grid, norm, dedup_levels, None, _c(origins), _c(directions),
-                                          starts.float(), ends.float())
+                                          starts.float(), ends.float(), sink)
     return feats, sel
 
 

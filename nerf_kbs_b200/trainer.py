@@ -14,6 +14,8 @@ sum-allreduce (NCCL over NVLink; gloo on the CPU for tests) of the gradients pre
 tables in place, everything else through one flat bucket.  No other collective is on the path."""
 from __future__ import annotations
 
+import os
+
 from typing import Dict, List, Optional, Sequence
 
 import torch
@@ -74,9 +76,16 @@ class Trainer:
         self.R = int(num_rays)
         groups = model.get_param_groups()
         # one Adam per group, as nerfstudio's Optimizers does (same hyper-parameters in the reference)
-        self.optimizers: Dict[str, Adam] = {k: Adam(v, lr=lr, betas=betas, eps=eps) for k, v in groups.items()}
         self.group = process_group
         self.world_size = dist.get_world_size(process_group) if (dist.is_available() and dist.is_initialized()) else 1
+        # several GPUs: reduce-scatter + Adam + all-gather fused over NVLink peer memory (dp_optim.py);
+        # NKBS_DP_FUSED=0 keeps the NCCL allreduce + per-rank Adam route
+        self.sharded = None
+        if self.world_size > 1 and os.environ.get("NKBS_DP_FUSED", "1") != "0":
+            from .dp_optim import ShardedAdam
+            self.sharded = ShardedAdam(groups, lr=lr, betas=betas, eps=eps, process_group=process_group)
+        self.optimizers: Dict[str, Adam] = {} if self.sharded is not None else {
+            k: Adam(v, lr=lr, betas=betas, eps=eps) for k, v in groups.items()}
         self.use_graph = use_graph
         self.graph_warmup = graph_warmup
         self.step = 0
@@ -143,12 +152,17 @@ class Trainer:
                          camera_indices=b["camera_indices"], metadata={})
 
     # -- the step ----------------------------------------------------------------------------------
+    def _zero_grad(self) -> None:
+        if self.sharded is not None:
+            self.sharded.zero_grad()
+        for o in self.optimizers.values():
+            o.zero_grad(set_to_none=True)
+
     def _grads(self) -> List[torch.Tensor]:
         return [p.grad for o in self.optimizers.values() for p in o.params if p.grad is not None]
 
     def _step_body(self) -> Dict[str, torch.Tensor]:
-        for o in self.optimizers.values():
-            o.zero_grad(set_to_none=True)
+        self._zero_grad()
         outputs = self.model(self._bundle())
         batch = {"image": self.buf["image"]}
         if self.needs_labels:
@@ -156,10 +170,13 @@ class Trainer:
         loss_dict = self.model.get_loss_dict(outputs, batch)
         loss = sum(loss_dict.values())
         loss.backward()
-        if self.world_size > 1:
-            allreduce_mean_(self._grads(), self.group, self.world_size)
-        for o in self.optimizers.values():
-            o.step()
+        if self.sharded is not None:
+            self.sharded.step()
+        else:
+            if self.world_size > 1:
+                allreduce_mean_(self._grads(), self.group, self.world_size)
+            for o in self.optimizers.values():
+                o.step()
         out = {k: v.detach() for k, v in loss_dict.items()}
         out["loss"] = loss.detach()
         return out
@@ -168,8 +185,7 @@ class Trainer:
         g = torch.cuda.CUDAGraph()
         if self._pool is None:
             self._pool = torch.cuda.graph_pool_handle()
-        for o in self.optimizers.values():
-            o.zero_grad(set_to_none=True)
+        self._zero_grad()
         torch.cuda.synchronize(self.device)
         c0 = sum(_lib.call_counts.values())
         with torch.cuda.graph(g, pool=self._pool):

@@ -55,3 +55,23 @@ def test_shard_rays_covers_batch():
     for ws in (1, 2, 4, 8):
         idx = [i for r in range(ws) for i in shard_rays(4096, r, ws)]
         assert idx == list(range(4096))
+
+
+def test_sharded_adam_flat_layout():
+    """Slices of the fused NVLink optimizer step: aligned, disjoint, and covering every group on every world size."""
+    from nerf_kbs_b200.dp_optim import flat_layout
+    groups = {"proposal_networks": [1310720 * 2, 160, 16, 16, 1] * 2, "fields": [16777216, 2048, 64, 1024, 16, 3680, 4032, 64, 4096, 64, 192, 3]}
+    for world in (1, 2, 4, 8):
+        slices = {}
+        for rank in range(world):
+            lay = flat_layout(groups, world, rank)
+            total = lay.pop("__total__")
+            for name, g in lay.items():
+                assert g["lo"] % 4 == 0 and g["n"] % 4 == 0 and g["len"] == g["n"] * world
+                assert all(o % 4 == 0 for o in g["offs"]) and g["offs"][0] == g["start"]
+                assert g["offs"][-1] + groups[name][-1] <= g["start"] + g["len"] <= total
+                slices.setdefault(name, []).append((g["lo"], g["lo"] + g["n"]))
+        for name, sl in slices.items():
+            sl.sort()
+            assert sl[0][0] == lay[name]["start"] and sl[-1][1] == lay[name]["start"] + lay[name]["len"]
+            assert all(a[1] == b[0] for a, b in zip(sl, sl[1:]))

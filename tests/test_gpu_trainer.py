@@ -105,3 +105,18 @@ def test_training_loop_tracks_oracle():
     # Adam normalises every gradient entry to a step of about lr: entries whose gradient is rounding noise move
     # by +-lr in either run, so the weights are compared loosely
     assert rel_err(nm.field.mlp_head.layers[0].weight, om.field.mlp_head.layers[0].weight) < 5e-2
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_fused_dp_step_equals_nccl_route():
+    """torchrun over 2 GPUs: reduce-Adam-broadcast over NVLink peer memory vs NCCL allreduce + Adam (scripts/dp_check.py)."""
+    import os, re, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29577", os.path.join(root, "scripts", "dp_check.py")],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = re.findall(r"max\|dp\| = ([0-9.e+-]+) .*rank spread ([0-9.e+-]+)", r.stdout)
+    assert len(lines) == 2
+    for d, spread in lines:
+        assert float(d) < 2e-3 and float(spread) == 0.0
