@@ -16,6 +16,7 @@
 // Replaces nerfstudio field_components.mlp.MLP (+ the field-head activations) reached from
 // ref:nerfacto.py:275-311,398 and ref:semantic_nerfw.py:102-126,188 (under autocast these linears run in
 // 16-bit on the reference side too, ref:train.py:50).
+#include <stdlib.h>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include "common.cuh"
@@ -85,6 +86,7 @@ struct TcArgs {
   int dy_off;             // backward: fp32 staging of the upstream-gradient tile [128 x Kn] (cp.async target)
   int stage_off;          // backward: fp32 staging used to write dx coalesced (aliases dead activation tiles)
   int stage_ok;           // 1 if the dx staging fits
+  int recycle;            // backward, three layers: X_2 lives where X_0 was and X_0 is rebuilt before the last batch
   int wg_base;            // byte offset of warpgroup 0's activation region
   int wg_stride;          // bytes per warpgroup region
   int nwg;                // epilogue warpgroups per CTA (each owns one 128-sample tile at a time)
@@ -427,10 +429,10 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_fwd_kernel(cons
     const uint32_t tmem_row = tmem + wg * kMaxWidth + ((uint32_t)(tid & ~31) << 16);
     const TcLayer& last = a.layer[a.nl - 1];
     const int K0 = a.layer[0].K, Ka0 = a.layer[0].Ka;
-    const bool vec = (K0 & 3) == 0 && (K0 >> 2) <= (NWG >= 4 ? 8 : 16) && (reinterpret_cast<uintptr_t>(a.x) & 15) == 0;
+    const bool vec = (K0 & 3) == 0 && (K0 >> 2) <= (NWG >= 3 ? 8 : 16) && (reinterpret_cast<uintptr_t>(a.x) & 15) == 0;
     const int kshift = (K0 & (K0 - 1)) == 0 ? (31 - __clz(K0)) : -1;
     uint32_t phase = 0;
-    constexpr int NV = NWG >= 4 ? 8 : 16;  // register budget: 120 registers per thread with four warpgroups
+    constexpr int NV = NWG >= 3 ? 8 : 16;  // register budget: 120-128 registers per thread with three or four warpgroups
     for (int i = 0;; ++i) {
       const int64_t t = tile_of(i, wg, nwg);
       if (t >= ntiles) break;
@@ -548,13 +550,13 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(cons
     const uint32_t tmem_row = tmem + wg * kMaxWidth + ((uint32_t)(tid & ~31) << 16);
     const TcLayer& last = a.layer[nl - 1];
     const int K0 = a.layer[0].K, Ka0 = a.layer[0].Ka, Kn = last.N;
-    const bool vec = (K0 & 3) == 0 && (K0 >> 2) <= (NWG >= 4 ? 8 : 16) && (reinterpret_cast<uintptr_t>(a.x) & 15) == 0;
+    const bool vec = (K0 & 3) == 0 && (K0 >> 2) <= (NWG >= 3 ? 8 : 16) && (reinterpret_cast<uintptr_t>(a.x) & 15) == 0;
     const bool vec_dx = a.dx && (K0 & 3) == 0 && (reinterpret_cast<uintptr_t>(a.dx) & 15) == 0;
     const int kshift = (K0 & (K0 - 1)) == 0 ? (31 - __clz(K0)) : -1;
     const int r = tid;
     float* dys = reinterpret_cast<float*>(base + a.dy_off);
     uint32_t phase = 0;
-    constexpr int NV = NWG >= 4 ? 8 : 16;  // register budget: 120 registers per thread with four warpgroups
+    constexpr int NV = NWG >= 3 ? 8 : 16;  // register budget: 120-128 registers per thread with three or four warpgroups
     // The output-gradient tile G is read 64 features wide (dW of the last layer, M = 64) but only its first Np
     // columns carry data: the padding is zeroed once here, nothing else ever writes this region (the dx staging
     // ends before it, see build_args).
@@ -580,16 +582,18 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(cons
       TRACE_WG(5);
       float sel = 1.f;
       if (a.selector && live) sel = __ldg(a.selector + row);
-      if (IN != 0) {
-        build_head_tile_in<FMT, IN>(a, row0, base + a.layer[0].x_off, tid);
-      } else if (vec) {
-        float4 xr[NV];
-        x_prefetch(xr, a.x, row0, a.N, K0, tid);
-        TRACE_WG(6);
-        x_commit<FMT>(xr, K0, kshift, Ka0, base + a.layer[0].x_off, tid);
-      } else {
-        load_input_tile<FMT>(a.x, row0, a.N, K0, Ka0, base + a.layer[0].x_off, tid);
-      }
+      auto stage_x0 = [&]() {
+        if (IN != 0) {
+          build_head_tile_in<FMT, IN>(a, row0, base + a.layer[0].x_off, tid);
+        } else if (vec) {
+          float4 xr[NV];
+          x_prefetch(xr, a.x, row0, a.N, K0, tid);
+          x_commit<FMT>(xr, K0, kshift, Ka0, base + a.layer[0].x_off, tid);
+        } else {
+          load_input_tile<FMT>(a.x, row0, a.N, K0, Ka0, base + a.layer[0].x_off, tid);
+        }
+      };
+      stage_x0();
       TRACE_WG(2);
       // ---- forward recompute, every layer input kept ----
       for (int l = 0; l < nl; ++l) {
@@ -626,6 +630,8 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(cons
         const TcLayer& ly = a.layer[l];
         const int Nx = (ly.K + 15) & ~15;
         TRACE_WG(30 + l);
+        // recycled layout: X_2 / dY_1 occupied X_0's place; dW_0 needs X_0 again (all earlier batches have completed)
+        if (l == 0 && a.recycle) stage_x0();
         wg_round(sh, wg, phase);
         TRACE_WG(20 + l);
         if (l > 0) {
@@ -742,6 +748,8 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(cons
           }
         }
       }
+      // recycled layout: the dx staging covers X_0's place, which the next tile's input is written into right away
+      if (a.recycle) wg_sync(wg);
     }
   }
   // ---- flush the weight / bias gradients: M=64 accumulator rows live in lanes 0..15 of every warp ----
@@ -818,29 +826,64 @@ int build_args(TcArgs& a, bool backward, int nl, const int32_t* dims, const floa
     a.dy_off = 0;
     a.stage_off = 0;
     a.stage_ok = 0;
+    a.recycle = 0;
     per_wg = 2 * tile_bytes;
   } else {
-    for (int l = 0; l < nl; ++l) {
-      TcLayer& ly = a.layer[l];
-      int width = ly.Ka > kMaxWidth ? ly.Ka : kMaxWidth;  // later reused as a 64-wide gradient tile
-      ly.x_off = per_wg;
-      per_wg += round_up((width / 8) * kActCs, 128);
-      dw_cols += ly.Ka;
-    }
-    a.g_off = per_wg;
-    per_wg += round_up((kMaxWidth / 8) * kActCs, 128);
-    a.dy_off = per_wg;
-    per_wg += round_up(kTile * a.layer[nl - 1].N * 4, 128);
+    // Two layouts.  Plain: X_0 .. X_{nl-1} | G | dy.  Recycled (three layers): X_2 is written where X_0 was (X_0 is
+    // dead between the first forward batch and the last backward batch, before which it is rebuilt), which frees one
+    // tile per warpgroup and lets a third warpgroup fit.  The recycled layout is used only when it adds a warpgroup.
+    for (int l = 0; l < nl; ++l) dw_cols += a.layer[l].Ka;
+    auto tile_of_layer = [&](int l) {
+      const int width = a.layer[l].Ka > kMaxWidth ? a.layer[l].Ka : kMaxWidth;  // later reused as a 64-wide gradient tile
+      return round_up((width / 8) * kActCs, 128);
+    };
+    auto lay = [&](bool recycle) {
+      int off = 0;
+      if (recycle) {
+        a.layer[0].x_off = a.layer[2].x_off = 0;
+        off += tile_of_layer(0) > tile_of_layer(2) ? tile_of_layer(0) : tile_of_layer(2);
+        a.layer[1].x_off = off;
+        off += tile_of_layer(1);
+      } else {
+        for (int l = 0; l < nl; ++l) {
+          a.layer[l].x_off = off;
+          off += tile_of_layer(l);
+        }
+      }
+      a.g_off = off;
+      off += round_up((kMaxWidth / 8) * kActCs, 128);
+      a.dy_off = off;
+      off += round_up(kTile * a.layer[nl - 1].N * 4, 128);
+      // dx staging: after X_0 in the plain layout; over both activation regions in the recycled one (every tile is dead
+      // once the last batch has completed).  It must end before the G tile, whose zero padding is written once.
+      const int nx0 = round_up(a.layer[0].K, 16);
+      a.stage_off = recycle ? 0 : (nl >= 2 ? a.layer[1].x_off : 0);
+      a.stage_ok = nl >= 2 && kTile * (nx0 + 4) * 4 <= a.g_off - a.stage_off;
+      a.recycle = recycle ? 1 : 0;
+      return off;
+    };
+    auto fit = [&](int bytes) {
+      int n = 4;
+      while (n > 1 && (a.wg_base + n * bytes > kSmemLimit - 1024 || n * kMaxWidth + dw_cols > 512)) --n;
+      return n;
+    };
     a.x_off1 = 0;
-    // dx staging aliases everything after X_0 (dead once the last batch of the tile has completed)
-    const int nx0 = round_up(a.layer[0].K, 16);
-    a.stage_off = nl >= 2 ? a.layer[1].x_off : 0;
-    // the staging must end before the G tile, whose zero padding is written once per kernel
-    a.stage_ok = nl >= 2 && kTile * (nx0 + 4) * 4 <= a.g_off - a.stage_off;
+    per_wg = lay(false);
+    // Measured on B200 (round 1): a third warpgroup makes the CTA 13 warps, which the register file allocates as 16
+    // (128 registers per thread); the three-layer backward then spills ~0.5 KB per thread and loses more than the
+    // extra tile in flight gains (colour head 1.56 -> 1.81 ms at 3.1 M samples).  The recycled layout therefore stays
+    // off unless NKBS_TC_RECYCLE=1 asks for it (experiments); two-layer nets fit three warpgroups in the plain layout.
+    static const bool want_recycle = [] { const char* e = getenv("NKBS_TC_RECYCLE"); return e && e[0] == '1'; }();
+    if (nl == 3 && want_recycle) {
+      const int plain = fit(per_wg);
+      const int rec_bytes = lay(true);
+      if (fit(rec_bytes) > plain && a.stage_ok) per_wg = rec_bytes;
+      else per_wg = lay(false);
+    }
   }
   a.wg_stride = per_wg;
   int nwg = 4;
-  while (nwg > 1 && (a.wg_base + nwg * per_wg > kSmemLimit - 1024 || nwg * kMaxWidth + dw_cols > 512)) nwg >>= 1;
+  while (nwg > 1 && (a.wg_base + nwg * per_wg > kSmemLimit - 1024 || nwg * kMaxWidth + dw_cols > 512)) --nwg;
   NKBS_CHECK_ARG(a.wg_base + nwg * per_wg <= kSmemLimit - 1024 && nwg * kMaxWidth + dw_cols <= 512,
                  "%s: does not fit (smem %d, tmem %d)", who, a.wg_base + per_wg, kMaxWidth + dw_cols);
   a.nwg = nwg;
@@ -895,9 +938,11 @@ int launch_tc(const TcArgs& a, int64_t N, cudaStream_t st, const char* who) {
   switch (key) {
     case 1: return launch_one<BWD, 0, 1, IN>(a, N, st, who);
     case 2: return launch_one<BWD, 0, 2, IN>(a, N, st, who);
+    case 3: return launch_one<BWD, 0, 3, IN>(a, N, st, who);
     case 4: return launch_one<BWD, 0, 4, IN>(a, N, st, who);
     case 9: return launch_one<BWD, 1, 1, IN>(a, N, st, who);
     case 10: return launch_one<BWD, 1, 2, IN>(a, N, st, who);
+    case 11: return launch_one<BWD, 1, 3, IN>(a, N, st, who);
     case 12: return launch_one<BWD, 1, 4, IN>(a, N, st, who);
   }
   nkbs_set_error("%s: unsupported warpgroup count %d", who, a.nwg);
