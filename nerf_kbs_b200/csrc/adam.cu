@@ -96,24 +96,41 @@ struct DpAdamArgs {
   const float* step_dev;
 };
 
+// WORLD > 0: number of ranks known at compile time, the peer loads of one element are all in flight together
+// (NVLink round trips are ~2 us: the loop over ranks must not serialise them); WORLD = 0: any rank count.
+template <int WORLD>
 __global__ void __launch_bounds__(kThreads) dp_adam_kernel(const DpAdamArgs a) {
   const float t = *a.step_dev;
   const float bc1 = 1.f - powf(a.beta1, t);
   const float bc2 = 1.f - powf(a.beta2, t);
   const float step_size = a.lr / bc1;
   const float sqrt_bc2 = sqrtf(bc2);
-  const float inv_world = 1.f / (float)a.world;
+  const int world = WORLD > 0 ? WORLD : a.world;
+  const float inv_world = 1.f / (float)world;
   const int64_t nvec = a.n >> 2;
   for (int64_t q = blockIdx.x * (int64_t)kThreads + threadIdx.x; q < nvec; q += (int64_t)gridDim.x * kThreads) {
     const int64_t i = a.lo + 4 * q;
     float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (WORLD > 0) {
+      float4 x[WORLD > 0 ? WORLD : 1];
+#pragma unroll
+      for (int r = 0; r < WORLD; ++r) x[r] = *reinterpret_cast<const float4*>(a.g[r] + i);
+#pragma unroll
+      for (int r = 0; r < WORLD; ++r) {  // rank order on every rank: all ranks compute the same sum
+        g.x += x[r].x;
+        g.y += x[r].y;
+        g.z += x[r].z;
+        g.w += x[r].w;
+      }
+    } else {
 #pragma unroll 1
-    for (int r = 0; r < a.world; ++r) {  // own rank first would not change the sum order across ranks: keep rank order
-      const float4 x = *reinterpret_cast<const float4*>(a.g[r] + i);
-      g.x += x.x;
-      g.y += x.y;
-      g.z += x.z;
-      g.w += x.w;
+      for (int r = 0; r < world; ++r) {
+        const float4 x = *reinterpret_cast<const float4*>(a.g[r] + i);
+        g.x += x.x;
+        g.y += x.y;
+        g.z += x.z;
+        g.w += x.w;
+      }
     }
     float4 p = *reinterpret_cast<const float4*>(a.p[a.rank] + i);
     float4 m = *reinterpret_cast<const float4*>(a.m + 4 * q);
@@ -124,8 +141,13 @@ __global__ void __launch_bounds__(kThreads) dp_adam_kernel(const DpAdamArgs a) {
     adam_one(p.w, g.w * inv_world, m.w, v.w, a.beta1, a.beta2, a.eps, step_size, sqrt_bc2, a.weight_decay);
     *reinterpret_cast<float4*>(a.m + 4 * q) = m;
     *reinterpret_cast<float4*>(a.v + 4 * q) = v;
+    if (WORLD > 0) {
+#pragma unroll
+      for (int r = 0; r < WORLD; ++r) *reinterpret_cast<float4*>(a.p[r] + i) = p;
+    } else {
 #pragma unroll 1
-    for (int r = 0; r < a.world; ++r) *reinterpret_cast<float4*>(a.p[r] + i) = p;
+      for (int r = 0; r < world; ++r) *reinterpret_cast<float4*>(a.p[r] + i) = p;
+    }
   }
 }
 
@@ -197,7 +219,14 @@ extern "C" int nkbs_dp_adam_step(int32_t world, int32_t rank, const float* const
   a.step_dev = step_dev;
   int64_t blocks = ((n >> 2) + kThreads - 1) / kThreads;
   int64_t cap = (int64_t)nkbs_num_sms() * 8;
-  dp_adam_kernel<<<(int)(blocks < cap ? blocks : cap), kThreads, 0, (cudaStream_t)stream>>>(a);
+  const int grid = (int)(blocks < cap ? blocks : cap);
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (world) {
+    case 2: dp_adam_kernel<2><<<grid, kThreads, 0, st>>>(a); break;
+    case 4: dp_adam_kernel<4><<<grid, kThreads, 0, st>>>(a); break;
+    case 8: dp_adam_kernel<8><<<grid, kThreads, 0, st>>>(a); break;
+    default: dp_adam_kernel<0><<<grid, kThreads, 0, st>>>(a); break;
+  }
   NKBS_CHECK_LAUNCH("nkbs_dp_adam_step");
   return 0;
 }
