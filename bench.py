@@ -212,6 +212,10 @@ def kernel_pass(trainer, batches, steps):
 
     was = trainer.use_graph
     trainer.use_graph = False
+    # per-kernel times are taken with the proposal levels on the main stream: on their side streams they overlap the
+    # main field's backward and an event pair around one launch would also time its neighbours
+    sampler = trainer.model.proposal_sampler
+    was_side, sampler.side_streams = sampler.side_streams, False
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     _lib.launch_observer = observer
     try:
@@ -224,6 +228,7 @@ def kernel_pass(trainer, batches, steps):
     finally:
         _lib.launch_observer = None
         trainer.use_graph = was
+        sampler.side_streams = was_side
     agg = {}
     for name, (kind, amount), s, e in rec:
         d = agg.setdefault(name, {"ms": 0.0, "launches": 0, "work": 0.0, "kind": kind})

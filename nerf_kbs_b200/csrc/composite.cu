@@ -11,6 +11,11 @@ constexpr int kWarpsPerCta = 8;
 constexpr int kThreads = kWarpsPerCta * 32;
 constexpr int kMaxS = 512;  // samples per ray held in a warp's shared-memory strip
 
+// Per-warp strips are indexed through PI: one pad word per 32 samples, so that lanes walking contiguous runs of
+// 2, 4, 8 or 16 samples (stride = run length) and lanes striding by 32 both hit distinct banks.
+#define PI(s) ((s) + ((s) >> 5))
+__host__ __device__ constexpr int strip_len(int S) { return S + (S >> 5) + 1; }
+
 struct CompArgs {
   int64_t R;
   int S;
@@ -64,41 +69,50 @@ __device__ __forceinline__ float nan_to_num(float w) {
 __global__ void __launch_bounds__(kThreads) composite_fwd_kernel(const CompArgs a) {
   extern __shared__ float s_w[];  // [kWarpsPerCta][S]
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  float* sw = s_w + wid * a.S;
+  float* sw = s_w + wid * strip_len(a.S);
   const int S = a.S;
   float lmin = FLT_MAX, lmax = -FLT_MAX;
   for (int64_t r = blockIdx.x * (int64_t)kWarpsPerCta + wid; r < a.R; r += (int64_t)gridDim.x * kWarpsPerCta) {
     const int64_t base = r * S;
     const int64_t bb = r * a.bstride;
-    float carry = 0.f;  // exclusive prefix of delta*sigma entering this 32-sample chunk
+    // Three passes.  (A) coalesced, independent loads: delta*sigma of every sample into the strip.  (B) every lane
+    // owns a contiguous run of `per` samples: serial prefix inside the run plus ONE warp scan of the run totals
+    // (instead of a scan per 32-sample chunk).  (C) coalesced stores and the per-ray sums.
+    const int per = (S + 31) >> 5;
+    const int r0 = min(lane * per, S), r1 = min(r0 + per, S);
     float acc = 0.f, dsum = 0.f;
-    for (int s0 = 0; s0 < S; s0 += 32) {
-      int s = s0 + lane;
-      bool live = s < S;
-      float st = 0.f, en = 0.f, w = 0.f;
-      if (live && a.starts) {
+    if (a.density) {
+      for (int s = lane; s < S; s += 32) sw[PI(s)] = (a.ends[bb + s] - a.starts[bb + s]) * a.density[base + s];
+      __syncwarp();
+      float tot = 0.f;
+      for (int s = r0; s < r1; ++s) tot += sw[PI(s)];
+      float run = warp_incl_scan(tot, lane) - tot;  // delta*sigma accumulated before this lane's run
+      for (int s = r0; s < r1; ++s) {
+        const float x = sw[PI(s)];
+        // alphas * transmittance, nan_to_num as in get_weights
+        sw[PI(s)] = nan_to_num((1.f - expf(-x)) * expf(-run));
+        run += x;
+      }
+      __syncwarp();
+    }
+    for (int s = lane; s < S; s += 32) {
+      float st = 0.f, en = 0.f, w;
+      if (a.starts) {
         st = a.starts[bb + s];
         en = a.ends[bb + s];
       }
       if (a.density) {
-        float x = live ? (en - st) * a.density[base + s] : 0.f;
-        float incl = warp_incl_scan(x, lane);
-        float excl = carry + (incl - x);
-        // alphas * transmittance, nan_to_num as in get_weights
-        w = live ? nan_to_num((1.f - expf(-x)) * expf(-excl)) : 0.f;
-        carry += __shfl_sync(0xffffffffu, incl, 31);
-      } else if (live) {
+        w = sw[PI(s)];
+      } else {
         w = a.weights_in[base + s];
+        sw[PI(s)] = w;
       }
-      if (live) {
-        sw[s] = w;
-        if (a.weights) a.weights[base + s] = w;
-        float step = (st + en) / 2.f;
-        acc += w;
-        dsum += w * step;
-        lmin = fminf(lmin, step);
-        lmax = fmaxf(lmax, step);
-      }
+      if (a.weights) a.weights[base + s] = w;
+      const float step = (st + en) / 2.f;
+      acc += w;
+      dsum += w * step;
+      lmin = fminf(lmin, step);
+      lmax = fmaxf(lmax, step);
     }
     acc = warp_sum(acc);
     dsum = warp_sum(dsum);
@@ -112,7 +126,7 @@ __global__ void __launch_bounds__(kThreads) composite_fwd_kernel(const CompArgs 
       const int per = (S + 31) >> 5;
       const int s0 = min(lane * per, S), s1 = min(s0 + per, S);
       double local = 0.0;
-      for (int s = s0; s < s1; ++s) local += (double)sw[s];
+      for (int s = s0; s < s1; ++s) local += (double)sw[PI(s)];
       double incl = local;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
@@ -122,7 +136,7 @@ __global__ void __launch_bounds__(kThreads) composite_fwd_kernel(const CompArgs 
       double cum = incl - local;
       int idx = S;
       for (int s = s0; s < s1; ++s) {
-        cum += (double)sw[s];
+        cum += (double)sw[PI(s)];
         if ((float)cum >= 0.5f) {
           idx = s;
           break;
@@ -137,7 +151,7 @@ __global__ void __launch_bounds__(kThreads) composite_fwd_kernel(const CompArgs 
       float c0 = 0.f, c1 = 0.f, c2 = 0.f;
       const float* rgb = a.rgb + base * 3;
       for (int s = lane; s < S; s += 32) {
-        float w = sw[s];
+        float w = sw[PI(s)];
         float r0 = rgb[3 * s], g0 = rgb[3 * s + 1], b0 = rgb[3 * s + 2];
         if (a.eval_mode) {
           r0 = nan_to_num(r0);
@@ -172,7 +186,7 @@ __global__ void __launch_bounds__(kThreads) composite_fwd_kernel(const CompArgs 
         int c = c0 + lane;
         float v = 0.f;
         if (c < a.C)
-          for (int s = 0; s < S; ++s) v += sw[s] * sem[(int64_t)s * a.C + c];
+          for (int s = 0; s < S; ++s) v += sw[PI(s)] * sem[(int64_t)s * a.C + c];
         if (c < a.C) a.sem_out[r * a.C + c] = v;
       }
     }
@@ -238,9 +252,9 @@ __global__ void __launch_bounds__(kThreads) composite_bwd_kernel(const CompBwdAr
   extern __shared__ float s_buf[];  // [kWarpsPerCta][3][S]: weights, dL/dw, exp(-incl)
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int S = a.S;
-  float* sw = s_buf + wid * 3 * S;
-  float* sg = sw + S;
-  float* sE = sg + S;
+  float* sw = s_buf + wid * 3 * strip_len(S);
+  float* sg = sw + strip_len(S);
+  float* sE = sg + strip_len(S);
   for (int64_t r = blockIdx.x * (int64_t)kWarpsPerCta + wid; r < a.R; r += (int64_t)gridDim.x * kWarpsPerCta) {
     const int64_t base = r * S;
     const int64_t bb = r * a.bstride;
@@ -281,8 +295,8 @@ __global__ void __launch_bounds__(kThreads) composite_bwd_kernel(const CompBwdAr
         for (int c = 0; c < a.C; ++c) d += gq[c] * q[c];
         g += d;
       }
-      sw[s] = w;
-      sg[s] = g;
+      sw[PI(s)] = w;
+      sg[PI(s)] = g;
       if (a.d_weights) a.d_weights[base + s] = g;
       if (a.d_rgb) {
         float* o = a.d_rgb + (base + s) * 3;
@@ -299,42 +313,42 @@ __global__ void __launch_bounds__(kThreads) composite_bwd_kernel(const CompBwdAr
         int c = c0 + lane;
         if (c < a.C) {
           float g = a.g_sem ? a.g_sem[r * a.C + c] : 0.f;
-          for (int s = 0; s < S; ++s) o[(int64_t)s * a.C + c] = sw[s] * g;
+          for (int s = 0; s < S; ++s) o[(int64_t)s * a.C + c] = sw[PI(s)] * g;
         }
       }
     }
     if (a.d_density) {
       // w_i = (1-exp(-x_i)) exp(-sum_{j<i} x_j):  dL/dx_i = g_i exp(-incl_i) - sum_{j>i} g_j w_j
       // forward sweep: E_i = exp(-inclusive prefix of x); reverse sweep: exclusive suffix sum of g_j w_j
-      float carry_x = 0.f;
-      for (int s0 = 0; s0 < S; s0 += 32) {
-        int s = s0 + lane;
-        bool live = s < S;
-        float x = live ? (a.ends[bb + s] - a.starts[bb + s]) * a.density[base + s] : 0.f;
-        float ix = warp_incl_scan(x, lane);
-        if (live) sE[s] = expf(-(carry_x + ix));
-        carry_x += __shfl_sync(0xffffffffu, ix, 31);
+      // same three passes as the forward: coalesced loads, lane-contiguous runs with one scan, coalesced stores
+      const int per = (S + 31) >> 5;
+      const int r0 = min(lane * per, S), r1 = min(r0 + per, S);
+      for (int s = lane; s < S; s += 32) sE[PI(s)] = (a.ends[bb + s] - a.starts[bb + s]) * a.density[base + s];
+      __syncwarp();
+      float tot = 0.f;
+      for (int s = r0; s < r1; ++s) tot += sE[PI(s)];
+      float run = warp_incl_scan(tot, lane) - tot;
+      float qtot = 0.f;
+      for (int s = r0; s < r1; ++s) {
+        run += sE[PI(s)];
+        sE[PI(s)] = expf(-run);
+        qtot += sg[PI(s)] * sw[PI(s)];
+      }
+      // exclusive suffix of the run totals of g_j w_j (runs of the lanes above this one)
+      float suf = qtot;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const float n = __shfl_down_sync(0xffffffffu, suf, o);
+        if (lane + o < 32) suf += n;
+      }
+      float after = suf - qtot;  // sum of g_j w_j over all later samples
+      for (int s = r1 - 1; s >= r0; --s) {
+        const float q = sg[PI(s)] * sw[PI(s)];
+        sE[PI(s)] = sg[PI(s)] * sE[PI(s)] - after;
+        after += q;
       }
       __syncwarp();
-      float carry_q = 0.f;  // sum of g_j w_j over all later chunks
-      for (int s0 = ((S - 1) / 32) * 32; s0 >= 0; s0 -= 32) {
-        int s = s0 + lane;
-        bool live = s < S;
-        float q = live ? sg[s] * sw[s] : 0.f;
-        // inclusive suffix scan inside the chunk
-        float sq = q;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          float n = __shfl_down_sync(0xffffffffu, sq, o);
-          if (lane + o < 32) sq += n;
-        }
-        float suffix_excl = carry_q + (sq - q);
-        if (live) {
-          float delta = a.ends[bb + s] - a.starts[bb + s];
-          a.d_density[base + s] = delta * (sg[s] * sE[s] - suffix_excl);
-        }
-        carry_q += __shfl_sync(0xffffffffu, sq, 0);
-      }
+      for (int s = lane; s < S; s += 32) a.d_density[base + s] = (a.ends[bb + s] - a.starts[bb + s]) * sE[PI(s)];
     }
     __syncwarp();
   }
@@ -369,7 +383,7 @@ extern "C" int nkbs_composite_fwd(int64_t R, int32_t S, const float* density, co
   CompArgs a{R, S, density, weights_in, starts, ends, bin_stride ? bin_stride : S, rgb, sem, C, bg_mode, eval_mode,
              weights, rgb_out, acc_out, depth_exp_raw, depth_med, sem_out, depth_exp ? minmax_ws : nullptr};
   if (depth_exp) minmax_init_kernel<<<1, 1, 0, st>>>(minmax_ws);
-  size_t smem = (size_t)kWarpsPerCta * S * sizeof(float);
+  size_t smem = (size_t)kWarpsPerCta * strip_len(S) * sizeof(float);
   composite_fwd_kernel<<<comp_grid(R), kThreads, smem, st>>>(a);
   NKBS_CHECK_LAUNCH("nkbs_composite_fwd");
   if (depth_exp) {
@@ -397,7 +411,7 @@ extern "C" int nkbs_composite_bwd(int64_t R, int32_t S, const float* density, co
   NKBS_CHECK_ARG(bin_stride == 0 || bin_stride >= S, "nkbs_composite_bwd: bin_stride %d < S", bin_stride);
   CompBwdArgs a{R, S, density, weights, starts, ends, bin_stride ? bin_stride : S, rgb, sem, C, bg_mode, sem_weight_grad, acc, depth_raw,
                 g_weights, g_rgb, g_acc, g_depth, g_sem, d_density, d_weights, d_rgb, d_sem};
-  size_t smem = (size_t)kWarpsPerCta * 3 * S * sizeof(float);
+  size_t smem = (size_t)kWarpsPerCta * 3 * strip_len(S) * sizeof(float);
   composite_bwd_kernel<<<comp_grid(R), kThreads, smem, (cudaStream_t)stream>>>(a);
   NKBS_CHECK_LAUNCH("nkbs_composite_bwd");
   return 0;
