@@ -195,6 +195,37 @@ def kernel_work(name, a):
     return "hbm", 0
 
 
+NCU_NAMES = {"nkbs_density_bwd": "density_bwd_kernel", "nkbs_density_fwd": "density_fwd_kernel", "nkbs_encode_bwd": "encode_bwd_kernel",
+             "nkbs_encode_fwd": "encode_fwd_kernel", "nkbs_mlp_tc_bwd": "mlp_tc_bwd_kernel", "nkbs_mlp_tc_fwd": "mlp_tc_fwd_kernel",
+             "nkbs_head_tc_bwd": "mlp_tc_bwd_kernel", "nkbs_head_tc_fwd": "mlp_tc_fwd_kernel", "nkbs_adam_step": "adam_kernel",
+             "nkbs_composite_fwd": "composite_fwd_kernel", "nkbs_composite_bwd": "composite_bwd_kernel",
+             "nkbs_ray_losses": "ray_losses_kernel", "nkbs_pdf_sample": "pdf_sample"}
+UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+
+
+def ncu_traffic(entry, rays):
+    """DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of `entry`'s kernel, from the committed
+    `ncu --set full` capture of the 4096-ray step (profiles/*_top_kernels_ncu_full.csv); None for other workloads."""
+    import csv
+    import glob
+    if rays != 4096 or entry not in NCU_NAMES:
+        return None
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_top_kernels_ncu_full.csv")))
+    if not files:
+        return None
+    rows = list(csv.reader(open(files[-1])))
+    if len(rows) < 3:
+        return None
+    h, units = rows[0], rows[1]
+    try:
+        ik, ir, iw = h.index("Kernel Name"), h.index("dram__bytes_read.sum"), h.index("dram__bytes_write.sum")
+    except ValueError:
+        return None
+    vals = [float(r[ir]) * UNIT.get(units[ir], 1.0) + float(r[iw]) * UNIT.get(units[iw], 1.0)
+            for r in rows[2:] if len(r) == len(h) and NCU_NAMES[entry] in r[ik]]
+    return round(sum(vals) / len(vals)) if vals else None
+
+
 def kernel_pass(trainer, batches, steps):
     """Eager (graph-less) steps with a CUDA-event pair around every nkbs launch, on the launching stream."""
     import torch
@@ -502,7 +533,9 @@ def run_nkbs(args):
         k = kernels[top]
         peak = hbm_peak if k["bound"] == "hbm" else tc_peak
         roofline = {"kernel": top, "bound": k["bound"], "achieved": k["achieved"], "peak": peak, "unit": k["unit"],
-                    "frac": round(k["achieved"] / peak, 4), "traffic": None, "peak_source": peak_src,
+                    "frac": round(k["achieved"] / peak, 4), "traffic": ncu_traffic(top, R),
+                    "traffic_note": "DRAM bytes per launch from profiles/*_top_kernels_ncu_full.csv (ncu --set full, same step)",
+                    "peak_source": peak_src,
                     "launch_ms": round(k["ms_per_step"] / k["launches_per_step"], 4),
                     "share_of_nkbs_kernel_time": k["share"], "eager_ms_per_step": round(eager_ms, 3)}
 
