@@ -82,6 +82,51 @@ def build():
         o = m(O.synthetic_ray_bundle(48, seed=32))
     for k in ("rgb", "accumulation", "depth", "expected_depth", "semantics"):
         out[f"model_{k}"] = o[k].numpy()
+    # --- proposal losses (N1): interlevel + distortion over three histogram levels, values and d/dw ---
+    g = torch.Generator().manual_seed(41)
+    edges, ws = [], []
+    for S in (64, 24, 12):
+        e = torch.sort(torch.rand(40, S + 1, generator=g), dim=-1).values
+        w = torch.rand(40, S, generator=g) + 0.05
+        w = (w / w.sum(-1, keepdim=True) * torch.rand(40, 1, generator=g)).requires_grad_()
+        edges.append(e)
+        ws.append(w)
+
+    class _RS:  # the losses read only the spacing-space bin edges
+        def __init__(self, sd):
+            self.spacing_starts, self.spacing_ends = sd[..., :-1, None], sd[..., 1:, None]
+
+    rsl = [_RS(e) for e in edges]
+    inter = O.interlevel_loss([w[..., None] for w in ws], rsl)
+    dist = O.distortion_loss([w[..., None] for w in ws], rsl)
+    (inter + 0.5 * dist).backward()
+    out["loss_interlevel"], out["loss_distortion"] = inter.detach().numpy(), dist.detach().numpy()
+    for i, (e, w) in enumerate(zip(edges, ws)):
+        out[f"loss_sdist{i}"], out[f"loss_w{i}"], out[f"loss_dw{i}"] = e.numpy(), w.detach().numpy(), w.grad.numpy()
+    # --- ray generation, masked compaction, label palette (N3 / N4) ---
+    g = torch.Generator().manual_seed(51)
+    q, _ = torch.linalg.qr(torch.randn(3, 3, 3, generator=g))
+    c2w = torch.cat([q, torch.rand(3, 3, 1, generator=g) - 0.5], -1)
+    intr = torch.tensor([[721.5, 721.5, 621.0, 187.5]]).repeat(3, 1)
+    idx = torch.stack([torch.randint(0, 3, (300,), generator=g), torch.randint(0, 375, (300,), generator=g),
+                       torch.randint(0, 1242, (300,), generator=g)], -1)
+    rbg = O.generate_rays(idx, c2w, intr)
+    out["ray_c2w"], out["ray_intrinsics"], out["ray_idx"] = c2w.numpy(), intr.numpy(), idx.numpy()
+    out["ray_origins"], out["ray_directions"] = rbg.origins.numpy(), rbg.directions.numpy()
+    out["ray_pixel_area"], out["ray_dnorm"] = rbg.pixel_area.numpy(), rbg.metadata["directions_norm"].numpy()
+    masks = (torch.rand(3, 500, generator=g) < 0.6).to(torch.uint8) * 255
+    ci, cp = torch.randint(0, 3, (200,), generator=g), torch.randint(0, 500, (200,), generator=g)
+    wi, wp, wn = O.compact_masked(ci, cp, masks, 150)
+    out["msk_masks"], out["msk_img"], out["msk_pix"] = masks.numpy(), ci.numpy(), cp.numpy()
+    out["msk_out_img"], out["msk_out_pix"], out["msk_count"] = wi.numpy(), wp.numpy(), np.array(wn)
+    palette = [(128, 64, 128), (244, 35, 232), (70, 70, 70), (102, 102, 156), (190, 153, 153), (0, 0, 142)]
+    pix = torch.tensor(palette, dtype=torch.uint8)[torch.randint(0, 6, (400,), generator=g)]
+    pix[::9] = torch.randint(0, 256, (len(pix[::9]), 3), generator=g).to(torch.uint8)
+    logits = torch.randn(400, 6, generator=g)
+    lab, col = O.semantic_colormap(logits, palette)
+    out["pal_palette"], out["pal_pixels"] = np.array(palette, dtype=np.uint8), pix.numpy()
+    out["pal_labels"] = O.color_to_label(pix, palette, 6).numpy()
+    out["pal_logits"], out["pal_argmax"], out["pal_colours"] = logits.numpy(), lab.numpy(), col.numpy()
     return out
 
 

@@ -21,7 +21,8 @@ def _t(name):
 def test_oracle_reproduces_golden_vectors():
     import make_golden
     now = make_golden.build()
-    exact = [k for k in GOLD.files if k.endswith(("_idx", "_rows", "_inds1", "_sbins0", "_ebins0", "_scalings"))]
+    exact = [k for k in GOLD.files if k.endswith(("_idx", "_rows", "_inds1", "_sbins0", "_ebins0", "_scalings", "_out_img", "_out_pix",
+                                                  "_count", "_labels", "_argmax", "_colours", "ray_origins"))]
     for k in GOLD.files:
         if k.endswith("_version"):
             continue
@@ -85,3 +86,38 @@ def test_kernels_reproduce_golden_compositing():
         assert (out[k].cpu() - want).abs().max() <= 1e-4 * want.abs().max() + 1e-7, k
     med, want = out["depth"].cpu(), _t("cmp_depth_med")
     assert ((med - want).abs() <= 1e-5 * want.abs()).float().mean() > 0.98
+
+
+@pytest.mark.gpu
+def test_kernels_reproduce_golden_losses():
+    from nerf_kbs_b200 import ops
+    ws = [_t(f"loss_w{i}").cuda().requires_grad_() for i in range(3)]
+    sd = [_t(f"loss_sdist{i}").cuda() for i in range(3)]
+    _, inter, dist, _ = ops.ray_losses(w_final=ws[-1], sdist_final=sd[-1], w_props=ws[:-1], sdist_props=sd[:-1])
+    assert abs(inter.item() - float(GOLD["loss_interlevel"])) <= 1e-4 * abs(float(GOLD["loss_interlevel"]))
+    assert abs(dist.item() - float(GOLD["loss_distortion"])) <= 1e-4 * abs(float(GOLD["loss_distortion"]))
+    (inter + 0.5 * dist).backward()
+    for i, w in enumerate(ws):
+        want = _t(f"loss_dw{i}")
+        assert (w.grad.cpu() - want).abs().max() <= 1e-4 * want.abs().max(), f"d/dw level {i}"
+
+
+@pytest.mark.gpu
+def test_kernels_reproduce_golden_rays_masks_and_palette():
+    import nerf_kbs_b200 as nk
+    from nerf_kbs_b200 import data as D
+    intr = _t("ray_intrinsics")
+    cams = nk.Cameras(_t("ray_c2w"), intr[:, 0], intr[:, 1], intr[:, 2], intr[:, 3], 375, 1242)
+    rb = nk.RayGenerator(cams).to("cuda")(_t("ray_idx").cuda())
+    assert torch.equal(rb.origins.cpu(), _t("ray_origins"))
+    assert (rb.directions.cpu() - _t("ray_directions")).abs().max() <= 1e-6
+    assert (rb.metadata["directions_norm"].cpu() - _t("ray_dnorm")).abs().max() <= 1e-6 * _t("ray_dnorm").abs().max()
+    want = _t("ray_pixel_area")
+    assert (rb.pixel_area.cpu() - want).abs().max() <= 1e-4 * want.abs().max()
+    gi, gp, gn = D.compact_masked(_t("msk_img").cuda(), _t("msk_pix").cuda(), _t("msk_masks").cuda(), 150)
+    assert int(gn) == int(GOLD["msk_count"])
+    assert torch.equal(gi.cpu(), _t("msk_out_img")) and torch.equal(gp.cpu(), _t("msk_out_pix"))
+    pal = D.SemanticPalette([tuple(int(v) for v in c) for c in GOLD["pal_palette"]], "cuda")
+    assert torch.equal(pal.color_to_label(_t("pal_pixels").cuda()).cpu(), _t("pal_labels"))
+    lab, col = pal.colormap(_t("pal_logits").cuda())
+    assert torch.equal(lab.cpu(), _t("pal_argmax")) and torch.equal(col.cpu(), _t("pal_colours"))
