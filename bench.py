@@ -200,7 +200,7 @@ NCU_NAMES = {"nkbs_density_bwd": "density_bwd_kernel", "nkbs_density_fwd": "dens
              "nkbs_head_tc_bwd": "mlp_tc_bwd_kernel", "nkbs_head_tc_fwd": "mlp_tc_fwd_kernel", "nkbs_adam_step": "adam_kernel",
              "nkbs_composite_fwd": "composite_fwd_kernel", "nkbs_composite_bwd": "composite_bwd_kernel",
              "nkbs_ray_losses": "ray_losses_kernel", "nkbs_pdf_sample": "pdf_sample"}
-UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+_NCU_BYTES = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 
 
 def ncu_traffic(entry, rays):
@@ -221,7 +221,7 @@ def ncu_traffic(entry, rays):
         ik, ir, iw = h.index("Kernel Name"), h.index("dram__bytes_read.sum"), h.index("dram__bytes_write.sum")
     except ValueError:
         return None
-    vals = [float(r[ir]) * UNIT.get(units[ir], 1.0) + float(r[iw]) * UNIT.get(units[iw], 1.0)
+    vals = [float(r[ir]) * _NCU_BYTES.get(units[ir], 1.0) + float(r[iw]) * _NCU_BYTES.get(units[iw], 1.0)
             for r in rows[2:] if len(r) == len(h) and NCU_NAMES[entry] in r[ik]]
     return round(sum(vals) / len(vals)) if vals else None
 
