@@ -53,7 +53,7 @@ struct TcLayer {
 // Input built in the kernel instead of read as rows (IN = 1, 2): X0 = [SH16((d+1)/2) | geo15 | embedding row | 1],
 // the colour head's input (IN = 1: SH 16, appearance 32), or [geo15 | embedding row | 1], the transient head's
 // (IN = 2: no SH, transient embedding 16).  Replaces K4 (heads.cu) on the tensor-core path: the [N,63] tensor and
-// its gradient never exist in HBM.
+// its gradient never exist in HBM.  IN = 3: [geo15 | 1], the semantics head's input (no embedding).
 struct HeadIn {
   const float* geo;        // row n at geo + n * geo_stride (15 floats)
   int geo_stride;
@@ -86,6 +86,7 @@ struct TcArgs {
   int dy_off;             // backward: fp32 staging of the upstream-gradient tile [128 x Kn] (cp.async target)
   int stage_off;          // backward: fp32 staging used to write dx coalesced (aliases dead activation tiles)
   int stage_ok;           // 1 if the dx staging fits
+  int ystage_ok;          // forward: the output tile is staged in shared memory and stored coalesced
   int recycle;            // backward, three layers: X_2 lives where X_0 was and X_0 is rebuilt before the last batch
   int wg_base;            // byte offset of warpgroup 0's activation region
   int wg_stride;          // bytes per warpgroup region
@@ -105,14 +106,24 @@ __device__ __forceinline__ uint16_t cvt16(float v) {
   }
 }
 template <int FMT>
-__device__ __forceinline__ uint32_t pack2(float a, float b) {  // one F2FP: two floats -> packed 16-bit pair (a low)
-  if (FMT == 1) {
-    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-    return *reinterpret_cast<uint32_t*>(&h);
-  } else {
-    __half2 h = __floats2half2_rn(fminf(fmaxf(a, -65504.f), 65504.f), fminf(fmaxf(b, -65504.f), 65504.f));
-    return *reinterpret_cast<uint32_t*>(&h);
-  }
+__device__ __forceinline__ uint32_t pack2(float a, float b) {  // one F2FP: two floats -> packed 16-bit pair (a low),
+  uint32_t d;                                                  // saturating at the format's largest finite value
+  if (FMT == 1) asm("cvt.rn.satfinite.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(b), "f"(a));
+  else asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(b), "f"(a));
+  return d;
+}
+template <int FMT>
+__device__ __forceinline__ uint32_t pack2_relu(float a, float b) {  // max(., 0) folded into the conversion
+  uint32_t d;
+  if (FMT == 1) asm("cvt.rn.relu.satfinite.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(b), "f"(a));
+  else asm("cvt.rn.relu.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(b), "f"(a));
+  return d;
+}
+// packed pair with the halves whose partner in `h` (same format) is not > 0 cleared: dX * relu'(X)
+template <int FMT>
+__device__ __forceinline__ uint32_t mask_pos2(uint32_t v, uint32_t h) {
+  if (FMT == 1) return v & __hgt2_mask(*reinterpret_cast<const __nv_bfloat162*>(&h), __float2bfloat162_rn(0.f));
+  return v & __hgt2_mask(*reinterpret_cast<const __half2*>(&h), __float2half2_rn(0.f));
 }
 
 // byte offset of element (row, k) inside a tile with chunk stride cs
@@ -187,7 +198,7 @@ __device__ __forceinline__ void build_head_tile(const TcArgs& a, int64_t row0, u
   // of this stage near one chunk instead of the whole 64-wide row
   const float* gp = h.geo + (live ? row : 0) * (int64_t)h.geo_stride;
   const float* ep = h.emb_const;
-  if (h.cam) ep = h.emb + __ldg(h.cam + (h.cam_per_ray ? ray : (live ? row : 0))) * EMBD;
+  if (EMBD > 0 && h.cam) ep = h.emb + __ldg(h.cam + (h.cam_per_ray ? ray : (live ? row : 0))) * EMBD;
 #pragma unroll
   for (int c = 0; c < Ka / 8; ++c) {
     float v[8];
@@ -209,15 +220,32 @@ __device__ __forceinline__ void build_head_tile(const TcArgs& a, int64_t row0, u
 template <int FMT, int IN>
 __device__ __forceinline__ void build_head_tile_in(const TcArgs& a, int64_t row0, unsigned char* tile, int tid) {
   if (IN == 1) build_head_tile<FMT, 16, 32>(a, row0, tile, tid);
-  else build_head_tile<FMT, 0, 16>(a, row0, tile, tid);
+  else if (IN == 2) build_head_tile<FMT, 0, 16>(a, row0, tile, tid);
+  else build_head_tile<FMT, 0, 0>(a, row0, tile, tid);
 }
 
-__device__ __forceinline__ float apply_out_act(int act, int n, float raw, float sel) {
-  switch (act) {
-    case ACT_SIGMOID: return nkbs_sigmoid(raw);
-    case ACT_DENSITY: return n == 0 ? expf(raw) * sel : raw;
-    case ACT_TRANSIENT: return (n >= 1 && n <= 3) ? nkbs_sigmoid(raw) : nkbs_softplus(raw);
-    default: return raw;
+// Output activation on a group of 16 accumulator columns starting at c0: one warp-uniform branch per group, and only
+// the columns an activation actually touches are computed (density: column 0; sigmoid: columns < N).
+__device__ __forceinline__ void apply_out_act16(int act, int c0, int N, float* v, float sel) {
+  if (act == ACT_SIGMOID) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (c0 + 4 * q < N) {
+#pragma unroll
+        for (int j = 4 * q; j < 4 * q + 4; ++j) v[j] = nkbs_sigmoid(v[j]);
+      }
+  } else if (act == ACT_DENSITY) {
+    if (c0 == 0) v[0] = expf(v[0]) * sel;
+  } else if (act == ACT_TRANSIENT) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (c0 + 4 * q < N) {
+#pragma unroll
+        for (int j = 4 * q; j < 4 * q + 4; ++j) {
+          const float sg = nkbs_sigmoid(v[j]), sp = nkbs_softplus(v[j]);
+          v[j] = (c0 + j >= 1 && c0 + j <= 3) ? sg : sp;
+        }
+      }
   }
 }
 
@@ -238,6 +266,43 @@ __device__ __forceinline__ float out_act_grad(int act, int n, float raw, float s
   }
 }
 
+// The same on a group of 16 columns: v[j] (raw output) -> dL/d raw, zero for columns >= Kn.  One warp-uniform branch
+// on the activation per group, work only for the 4-column pieces that hold outputs.
+template <typename G>
+__device__ __forceinline__ void grad_loop16(int c0, int Kn, float* v, const float* dyr, G g) {
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    if (c0 + 4 * q < Kn) {
+#pragma unroll
+      for (int j = 4 * q; j < 4 * q + 4; ++j) {
+        const int n = c0 + j;
+        const bool in = n < Kn;
+        const float r = g(n, v[j], in ? dyr[n] : 0.f);
+        v[j] = in ? r : 0.f;
+      }
+    } else {
+#pragma unroll
+      for (int j = 4 * q; j < 4 * q + 4; ++j) v[j] = 0.f;
+    }
+  }
+}
+__device__ __forceinline__ void out_act_grad16(int act, int c0, int Kn, float* v, float sel, const float* dyr) {
+  if (act == ACT_SIGMOID) {
+    grad_loop16(c0, Kn, v, dyr, [](int, float raw, float dy) {
+      const float s = nkbs_sigmoid(raw);
+      return dy * s * (1.f - s);
+    });
+  } else if (act == ACT_DENSITY) {
+    grad_loop16(c0, Kn, v, dyr, [sel](int n, float raw, float dy) {
+      return n == 0 ? dy * sel * expf(fminf(fmaxf(raw, -15.f), 15.f)) : dy;
+    });
+  } else if (act == ACT_TRANSIENT) {
+    grad_loop16(c0, Kn, v, dyr, [act, sel](int n, float raw, float dy) { return out_act_grad(act, n, raw, sel, dy); });
+  } else {
+    grad_loop16(c0, Kn, v, dyr, [](int, float, float dy) { return dy; });
+  }
+}
+
 // D[128 x Np] = X_l [128 x Ka] . W_l^T      (both K-major).  Warp-uniform: see mma_f16_uniform.
 __device__ __forceinline__ void issue_forward(const TcArgs& a, int l, uint32_t smem_base, uint32_t tmem, uint32_t xa,
                                               uint32_t leader) {
@@ -252,14 +317,21 @@ __device__ __forceinline__ void issue_forward(const TcArgs& a, int l, uint32_t s
 }
 
 
+#ifdef NKBS_TRACE
+__constant__ int c_dbg;  // experiments (NKBS_TC_DBG): bit 0 skips the TMEM loads, bit 1 the operand-tile stores
+#define DBG(bit) (c_dbg & (bit))
+#else
+#define DBG(bit) 0
+#endif
+
 // Walk this thread's accumulator row in groups of 16 columns: f(c0, v[16]) for c0 = 0, 16, .. < ncols_total.
 // Columns >= ncols_tmem are zeros.  Two tcgen05.ld (32 columns) are in flight per wait.
 template <int kMaxGroups, typename F>
-__device__ __forceinline__ void tmem_foreach16(uint32_t taddr, int ncols_tmem, int ncols_total, F f) {
+__device__ __forceinline__ void tmem_foreach16(uint32_t taddr, int ncols_tmem, int ncols_total, F f, int c_begin = 0) {
 #pragma unroll 1
-  for (int c0 = 0; c0 < ncols_total; c0 += 32) {
+  for (int c0 = c_begin; c0 < ncols_total; c0 += 32) {
     uint32_t b0[16], b1[16];
-    const bool h0 = c0 < ncols_tmem, h1 = c0 + 16 < ncols_tmem;
+    const bool h0 = c0 < ncols_tmem && !DBG(1), h1 = c0 + 16 < ncols_tmem && !DBG(1);
     if (h0) tmem_ld16_issue(taddr + c0, b0);
     if (h1) tmem_ld16_issue(taddr + c0 + 16, b1);
     if (h0) tmem_ld_wait();
@@ -277,31 +349,58 @@ __device__ __forceinline__ void tmem_foreach16(uint32_t taddr, int ncols_tmem, i
 
 template <int FMT>
 __device__ __forceinline__ void store16(unsigned char* tile, int c0, int r, const float v[16]) {
+  if (DBG(2)) return;
   *reinterpret_cast<uint4*>(tile + (c0 >> 3) * kActCs + r * 16) =
       make_uint4(pack2<FMT>(v[0], v[1]), pack2<FMT>(v[2], v[3]), pack2<FMT>(v[4], v[5]), pack2<FMT>(v[6], v[7]));
   *reinterpret_cast<uint4*>(tile + ((c0 >> 3) + 1) * kActCs + r * 16) =
       make_uint4(pack2<FMT>(v[8], v[9]), pack2<FMT>(v[10], v[11]), pack2<FMT>(v[12], v[13]), pack2<FMT>(v[14], v[15]));
 }
 
-// hidden-layer epilogue: TMEM accumulator -> ReLU -> 16-bit -> next layer's input tile (+ bias column)
+// 16 accumulator columns (raw TMEM words) -> two 16-byte chunks of an operand tile, ReLU folded into the conversion
+template <int FMT>
+__device__ __forceinline__ void store16_act(unsigned char* tile, int c0, int r, const uint32_t (&b)[16], bool relu) {
+  uint32_t p[8];
+  if (relu) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) p[j] = pack2_relu<FMT>(__uint_as_float(b[2 * j]), __uint_as_float(b[2 * j + 1]));
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) p[j] = pack2<FMT>(__uint_as_float(b[2 * j]), __uint_as_float(b[2 * j + 1]));
+  }
+  if (DBG(2)) return;
+  *reinterpret_cast<uint4*>(tile + (c0 >> 3) * kActCs + r * 16) = make_uint4(p[0], p[1], p[2], p[3]);
+  *reinterpret_cast<uint4*>(tile + ((c0 >> 3) + 1) * kActCs + r * 16) = make_uint4(p[4], p[5], p[6], p[7]);
+}
+
+// hidden-layer epilogue: TMEM accumulator -> ReLU -> 16-bit -> next layer's input tile (+ bias column).
+// Interior columns go 32 at a time through one conversion per pair; the groups that hold the tail of the outputs,
+// the constant-one column and the zero padding take the per-column path.
 template <int FMT>
 __device__ __forceinline__ void hidden_epilogue(uint32_t tmem_row, int Np, int N, int relu, int Ka_next,
                                                 unsigned char* dst, int r) {
+  int c0 = 0;
+#pragma unroll 1
+  for (; c0 + 32 <= N; c0 += 32) {
+    uint32_t b0[16], b1[16];
+    tmem_ld16_issue(tmem_row + c0, b0);
+    tmem_ld16_issue(tmem_row + c0 + 16, b1);
+    tmem_ld_wait();
+    store16_act<FMT>(dst, c0, r, b0, relu != 0);
+    store16_act<FMT>(dst, c0 + 16, r, b1, relu != 0);
+  }
+  if ((N & 15) == 0 && c0 == N) {  // nothing but [1 0 0 0 0 0 0 0] and zero chunks left
+    for (int c = N >> 3; c < (Ka_next >> 3); ++c)
+      *reinterpret_cast<uint4*>(dst + c * kActCs + r * 16) = make_uint4(c == (N >> 3) ? cvt16<FMT>(1.f) : 0u, 0u, 0u, 0u);
+    return;
+  }
   tmem_foreach16<(kMaxWidth + 16) / 16>(tmem_row, Np, Ka_next, [&](int c0, float v[16]) {
-    if (c0 + 16 <= N) {  // interior group: no per-column bookkeeping
-      if (relu) {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
-      }
-    } else {  // group holding the bias column and the zero padding
-#pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const int n = c0 + j;
-        v[j] = n < N ? (relu ? fmaxf(v[j], 0.f) : v[j]) : (n == N ? 1.f : 0.f);
-      }
+    for (int j = 0; j < 16; ++j) {
+      const int n = c0 + j;
+      v[j] = n < N ? (relu ? fmaxf(v[j], 0.f) : v[j]) : (n == N ? 1.f : 0.f);
     }
     store16<FMT>(dst, c0, r, v);
-  });
+  }, c0);
 }
 
 #ifdef NKBS_TRACE
@@ -350,6 +449,17 @@ __device__ __forceinline__ void x_prefetch(float4 (&xr)[NV], const float* __rest
   }
 }
 
+// next tile's input rows -> L2 (one 128-byte line per thread and pass): the tile after this one then loads from L2
+// instead of HBM, without holding registers or shared memory for it
+__device__ __forceinline__ void x_prefetch_l2(const float* __restrict__ x, int64_t row0, int64_t rows_total, int K, int tid) {
+  if (row0 >= rows_total) return;
+  int64_t rows = rows_total - row0;
+  if (rows > kTile) rows = kTile;
+  const char* src = reinterpret_cast<const char*>(x + row0 * K);
+  const int bytes = (int)rows * K * 4;
+  for (int o = tid * 128; o < bytes; o += kThreads * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(src + o));
+}
+
 template <int FMT, int NV>
 __device__ __forceinline__ void x_commit(const float4 (&xr)[NV], int K, int kshift, int Ka, unsigned char* tile, int tid) {
   const int nvec = K >> 2;
@@ -363,8 +473,13 @@ __device__ __forceinline__ void x_commit(const float4 (&xr)[NV], int K, int kshi
           make_uint2(pack2<FMT>(xr[j].x, xr[j].y), pack2<FMT>(xr[j].z, xr[j].w));
     }
   }
-  for (int k = K; k < Ka; ++k)
-    *reinterpret_cast<uint16_t*>(tile + tile_off(tid, k, kActCs)) = cvt16<FMT>(k == K ? 1.f : 0.f);
+  if ((K & 7) == 0) {  // the constant-one column opens a 16-byte chunk: [1 0 0 0 0 0 0 0], then zero chunks
+    for (int c = K >> 3; c < (Ka >> 3); ++c)
+      *reinterpret_cast<uint4*>(tile + c * kActCs + tid * 16) = make_uint4(c == (K >> 3) ? cvt16<FMT>(1.f) : 0u, 0u, 0u, 0u);
+  } else {
+    for (int k = K; k < Ka; ++k)
+      *reinterpret_cast<uint16_t*>(tile + tile_off(tid, k, kActCs)) = cvt16<FMT>(k == K ? 1.f : 0.f);
+  }
 }
 
 // warpgroup side of one MMA batch: publish the operand tiles, then wait for the batch to complete
@@ -443,33 +558,100 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_fwd_kernel(cons
       if (a.selector && live) sel = __ldg(a.selector + row);
       unsigned char* cur = base + a.layer[0].x_off;
       unsigned char* nxt = base + a.x_off1;
+      TRACE_WG(1);
       if (IN != 0) {
         build_head_tile_in<FMT, IN>(a, row0, cur, tid);
       } else if (vec) {
         float4 xr[NV];
         x_prefetch(xr, a.x, row0, a.N, K0, tid);
+        x_prefetch_l2(a.x, tile_of(i + 1, wg, nwg) * kTile, a.N, K0, tid);
         x_commit<FMT>(xr, K0, kshift, Ka0, cur, tid);
       } else {
         load_input_tile<FMT>(a.x, row0, a.N, K0, Ka0, cur, tid);
       }
+      TRACE_WG(2);
       for (int l = 0; l < a.nl; ++l) {
         wg_round(sh, wg, phase);
+        TRACE_WG(10 + l);
         if (l + 1 < a.nl) {
           hidden_epilogue<FMT>(tmem_row, a.layer[l].Np, a.layer[l].N, a.layer[l].relu, a.layer[l + 1].Ka, nxt, tid);
+          TRACE_WG(20 + l);
           unsigned char* tmp = cur;
           cur = nxt;
           nxt = tmp;
         }
       }
-      // output layer: activation and store, one row per thread
-      float* yo = a.y + row * last.N;
-      tmem_foreach16<kMaxWidth / 16>(tmem_row, last.Np, last.Np, [&](int c0, float v[16]) {
-        if (live) {
+      // output layer: activation, then rows -> fp32 staging (odd row stride: conflict-free) -> coalesced global stores.
+      // The staging lives in the second activation buffer: the last MMA that read it has completed, and its next
+      // writer is the next tile's first hidden epilogue, a warpgroup round away.
+      if (a.ystage_ok) {
+        float* st = reinterpret_cast<float*>(base + a.x_off1);
+        const int NO = last.N;
+        int64_t rows = a.N - row0;
+        if (rows > kTile) rows = kTile;
+        float* dst = a.y + row0 * NO;
+        if ((NO & 3) == 0) {
+          // rows of 16-byte pieces: stride NO + 4 floats keeps both the row-wise stores and the linear reads aligned
+          const int stride = NO + 4;
+          tmem_foreach16<kMaxWidth / 16>(tmem_row, last.Np, last.Np, [&](int c0, float v[16]) {
+            apply_out_act16(a.out_act, c0, NO, v, sel);
+            float4* p = reinterpret_cast<float4*>(st + tid * stride + c0);
 #pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (c0 + j < last.N) yo[c0 + j] = apply_out_act(a.out_act, c0 + j, v[j], sel);
+            for (int q = 0; q < 4; ++q)
+              if (c0 + 4 * q < NO) p[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+          });
+          TRACE_WG(31);
+          wg_sync(wg);
+          TRACE_WG(32);
+          const int nv = NO >> 2, total = (int)rows * nv;
+          int rr = tid / nv, c4 = tid - rr * nv;
+          const int dr = kThreads / nv, dc = kThreads - dr * nv;
+          for (int e = tid; e < total; e += kThreads) {
+            reinterpret_cast<float4*>(dst)[e] = *reinterpret_cast<const float4*>(st + rr * stride + 4 * c4);
+            rr += dr;
+            c4 += dc;
+            if (c4 >= nv) {
+              c4 -= nv;
+              ++rr;
+            }
+          }
+        } else {
+          const int stride = NO | 1, pad = stride - NO;
+          float* srow = st + tid * stride;
+          tmem_foreach16<kMaxWidth / 16>(tmem_row, last.Np, last.Np, [&](int c0, float v[16]) {
+            apply_out_act16(a.out_act, c0, NO, v, sel);
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (c0 + j < NO) srow[c0 + j] = v[j];
+          });
+          TRACE_WG(31);
+          wg_sync(wg);
+          TRACE_WG(32);
+          const int total = (int)rows * NO;
+          int rr = tid / NO, c = tid - rr * NO;
+          const int dr = kThreads / NO, dc = kThreads - dr * NO;
+          for (int e = tid; e < total; e += kThreads) {
+            dst[e] = st[e + rr * pad];
+            rr += dr;
+            c += dc;
+            if (c >= NO) {
+              c -= NO;
+              ++rr;
+            }
+          }
         }
-      });
+      } else {
+        float* yo = a.y + row * last.N;
+        tmem_foreach16<kMaxWidth / 16>(tmem_row, last.Np, last.Np, [&](int c0, float v[16]) {
+          apply_out_act16(a.out_act, c0, last.N, v, sel);
+          if (live) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (c0 + j < last.N) yo[c0 + j] = v[j];
+          }
+        });
+      }
+      TRACE_WG(30);
     }
   }
   fence_before_sync();
@@ -588,6 +770,7 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(cons
         } else if (vec) {
           float4 xr[NV];
           x_prefetch(xr, a.x, row0, a.N, K0, tid);
+          x_prefetch_l2(a.x, tile_of(i + 1, wg, nwg) * kTile, a.N, K0, tid);
           x_commit<FMT>(xr, K0, kshift, Ka0, base + a.layer[0].x_off, tid);
         } else {
           load_input_tile<FMT>(a.x, row0, a.N, K0, Ka0, base + a.layer[0].x_off, tid);
@@ -612,11 +795,7 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(cons
         unsigned char* g = base + a.g_off;
         tmem_foreach16<kMaxWidth / 16>(tmem_row, last.Np, last.Np, [&](int c0, float v[16]) {
           if (c0 < Kn && live) {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const int n = c0 + j;
-              v[j] = n < Kn ? out_act_grad(a.out_act, n, v[j], sel, dyr[n]) : 0.f;
-            }
+            out_act_grad16(a.out_act, c0, Kn, v, sel, dyr);
           } else {
 #pragma unroll
             for (int j = 0; j < 16; ++j) v[j] = 0.f;
@@ -639,6 +818,36 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(cons
           unsigned char* xt = base + ly.x_off;
           const bool masked = a.layer[l - 1].relu != 0;
           const int K = ly.K, Ka = ly.Ka;
+          // interior columns, 32 at a time: one conversion per pair, ReLU mask applied on the packed pair
+          int cb = 0;
+#pragma unroll 1
+          for (; cb + 32 <= K; cb += 32) {
+            uint32_t b0[16], b1[16];
+            tmem_ld16_issue(tmem_row + cb, b0);
+            tmem_ld16_issue(tmem_row + cb + 16, b1);
+            uint4 m[4];
+            if (masked) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q) m[q] = *reinterpret_cast<const uint4*>(xt + ((cb >> 3) + q) * kActCs + r * 16);
+            }
+            tmem_ld_wait();
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const uint32_t* b = q < 2 ? b0 : b1;
+              const int o = (q & 1) * 8;
+              uint32_t p0 = pack2<FMT>(__uint_as_float(b[o]), __uint_as_float(b[o + 1]));
+              uint32_t p1 = pack2<FMT>(__uint_as_float(b[o + 2]), __uint_as_float(b[o + 3]));
+              uint32_t p2 = pack2<FMT>(__uint_as_float(b[o + 4]), __uint_as_float(b[o + 5]));
+              uint32_t p3 = pack2<FMT>(__uint_as_float(b[o + 6]), __uint_as_float(b[o + 7]));
+              if (masked) {
+                p0 = mask_pos2<FMT>(p0, m[q].x);
+                p1 = mask_pos2<FMT>(p1, m[q].y);
+                p2 = mask_pos2<FMT>(p2, m[q].z);
+                p3 = mask_pos2<FMT>(p3, m[q].w);
+              }
+              *reinterpret_cast<uint4*>(xt + ((cb >> 3) + q) * kActCs + r * 16) = make_uint4(p0, p1, p2, p3);
+            }
+          }
           tmem_foreach16<kMaxWidth / 16>(tmem_row, Nx, kMaxWidth, [&](int c0, float v[16]) {
             uint4 m0 = make_uint4(0, 0, 0, 0), m1 = make_uint4(0, 0, 0, 0);
             if (c0 < Ka) {
@@ -664,11 +873,11 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(cons
               }
             }
             store16<FMT>(xt, c0, r, v);
-          });
+          }, cb);
         } else if (IN != 0 && want_dx0) {
           // dX_0 rows -> fp32 staging; the geometry columns go out as rows of dgeo, the embedding columns are summed
           // over the samples of each ray (they share the embedding row) and added to that row's gradient
-          constexpr int SHD = IN == 1 ? 16 : 0, GEO = 15, EMBD = IN == 1 ? 32 : 16;
+          constexpr int SHD = IN == 1 ? 16 : 0, GEO = 15, EMBD = IN == 1 ? 32 : (IN == 2 ? 16 : 0);
           float* st = reinterpret_cast<float*>(base + a.stage_off);
           const int stride = Nx + 4;
           tmem_foreach16<kMaxWidth / 16>(tmem_row, Nx, Nx, [&](int c0, float v[16]) {
@@ -828,6 +1037,7 @@ int build_args(TcArgs& a, bool backward, int nl, const int32_t* dims, const floa
     a.stage_ok = 0;
     a.recycle = 0;
     per_wg = 2 * tile_bytes;
+    a.ystage_ok = nl >= 2 && a.layer[nl - 1].N >= 4 && kTile * (a.layer[nl - 1].N + 4) * 4 <= tile_bytes;
   } else {
     // Two layouts.  Plain: X_0 .. X_{nl-1} | G | dy.  Recycled (three layers): X_2 is written where X_0 was (X_0 is
     // dead between the first forward batch and the last backward batch, before which it is rebuilt), which frees one
@@ -868,6 +1078,7 @@ int build_args(TcArgs& a, bool backward, int nl, const int32_t* dims, const floa
       return n;
     };
     a.x_off1 = 0;
+    a.ystage_ok = 0;
     per_wg = lay(false);
     // Measured on B200 (round 1): a third warpgroup makes the CTA 13 warps, which the register file allocates as 16
     // (128 registers per thread); the three-layer backward then spills ~0.5 KB per thread and loses more than the
@@ -881,8 +1092,20 @@ int build_args(TcArgs& a, bool backward, int nl, const int32_t* dims, const floa
       else per_wg = lay(false);
     }
   }
+#ifdef NKBS_TRACE
+  {
+    const char* e = getenv("NKBS_TC_DBG");
+    int d = e ? atoi(e) : 0;
+    cudaMemcpyToSymbol(c_dbg, &d, sizeof(int));
+  }
+#endif
   a.wg_stride = per_wg;
-  int nwg = 4;
+  // NKBS_TC_NWG=1..4 caps the warpgroups per CTA (experiments: scripts/tc_trace.py)
+  static const int nwg_cap = [] { const char* e = getenv("NKBS_TC_NWG"); return (e && e[0] >= '1' && e[0] <= '4') ? e[0] - '0' : 4; }();
+  // Forward: three warpgroups.  A fourth makes the CTA 17 warps, which caps the kernel at 96 registers per thread; the
+  // spill traffic that follows costs more than the extra tile in flight brings (measured on B200, full-frame render:
+  // colour + semantics heads 9.8 -> 6.5 ms, base MLP 3.9 -> 2.2 ms per frame with three).
+  int nwg = backward ? nwg_cap : (nwg_cap < 3 ? nwg_cap : 3);
   while (nwg > 1 && (a.wg_base + nwg * per_wg > kSmemLimit - 1024 || nwg * kMaxWidth + dw_cols > 512)) --nwg;
   NKBS_CHECK_ARG(a.wg_base + nwg * per_wg <= kSmemLimit - 1024 && nwg * kMaxWidth + dw_cols <= 512,
                  "%s: does not fit (smem %d, tmem %d)", who, a.wg_base + per_wg, kMaxWidth + dw_cols);
@@ -952,20 +1175,20 @@ int launch_tc(const TcArgs& a, int64_t N, cudaStream_t st, const char* who) {
 int fill_head(TcArgs& a, const char* who, int sh_dim, int geo_dim, int emb_dim, const float* geo, int geo_stride,
               const float* dirs, int dir_per_ray, const int64_t* cam, int cam_per_ray, const float* emb,
               const float* emb_const, int S, int64_t N, int& in_mode) {
-  NKBS_CHECK_ARG(geo_dim == 15 && ((sh_dim == 16 && emb_dim == 32) || (sh_dim == 0 && emb_dim == 16)),
-                 "%s: head inputs are [SH16|geo15|emb32] or [geo15|emb16] (got %d/%d/%d)", who, sh_dim, geo_dim, emb_dim);
-  in_mode = sh_dim == 16 ? 1 : 2;
+  NKBS_CHECK_ARG(geo_dim == 15 && ((sh_dim == 16 && emb_dim == 32) || (sh_dim == 0 && (emb_dim == 16 || emb_dim == 0))),
+                 "%s: head inputs are [SH16|geo15|emb32], [geo15|emb16] or [geo15] (got %d/%d/%d)", who, sh_dim, geo_dim, emb_dim);
+  in_mode = sh_dim == 16 ? 1 : (emb_dim == 16 ? 2 : 3);
   NKBS_CHECK_ARG(a.layer[0].K == sh_dim + geo_dim + emb_dim, "%s: first layer takes %d inputs, the assembled row has %d",
                  who, a.layer[0].K, sh_dim + geo_dim + emb_dim);
   NKBS_CHECK_ARG(geo && geo_stride >= geo_dim && S >= 1, "%s: bad geo / S", who);
   NKBS_CHECK_ARG(sh_dim == 0 || dirs, "%s: null directions", who);
-  NKBS_CHECK_ARG((cam && emb) || emb_const, "%s: need camera indices + table, or a constant row", who);
+  NKBS_CHECK_ARG(emb_dim == 0 || (cam && emb) || emb_const, "%s: need camera indices + table, or a constant row", who);
   NKBS_CHECK_ARG(!(dir_per_ray || cam_per_ray) || N % S == 0, "%s: N not a multiple of S", who);
   a.hin.geo = geo;
   a.hin.geo_stride = geo_stride;
   a.hin.dirs = dirs;
   a.hin.dir_per_ray = dir_per_ray;
-  a.hin.cam = emb_const ? nullptr : cam;
+  a.hin.cam = (emb_const || emb_dim == 0) ? nullptr : cam;
   a.hin.cam_per_ray = cam_per_ray;
   a.hin.emb = emb;
   a.hin.emb_const = emb_const;
@@ -1056,8 +1279,9 @@ extern "C" int nkbs_head_tc_fwd(int32_t sh_dim, int32_t geo_dim, int32_t emb_dim
   a.dy = nullptr;
   a.dx = nullptr;
   a.N = N;
-  const int rc = in_mode == 1 ? launch_tc<false, 1>(a, N, (cudaStream_t)stream, "nkbs_head_tc_fwd")
-                              : launch_tc<false, 2>(a, N, (cudaStream_t)stream, "nkbs_head_tc_fwd");
+  const int rc = in_mode == 1   ? launch_tc<false, 1>(a, N, (cudaStream_t)stream, "nkbs_head_tc_fwd")
+                 : in_mode == 2 ? launch_tc<false, 2>(a, N, (cudaStream_t)stream, "nkbs_head_tc_fwd")
+                                : launch_tc<false, 3>(a, N, (cudaStream_t)stream, "nkbs_head_tc_fwd");
   if (rc) return -1;
   NKBS_CHECK_LAUNCH("nkbs_head_tc_fwd");
   return 0;
@@ -1094,8 +1318,9 @@ extern "C" int nkbs_head_tc_bwd(int32_t sh_dim, int32_t geo_dim, int32_t emb_dim
   a.dy = dy;
   a.dx = nullptr;
   a.N = N;
-  const int rc = in_mode == 1 ? launch_tc<true, 1>(a, N, (cudaStream_t)stream, "nkbs_head_tc_bwd")
-                              : launch_tc<true, 2>(a, N, (cudaStream_t)stream, "nkbs_head_tc_bwd");
+  const int rc = in_mode == 1   ? launch_tc<true, 1>(a, N, (cudaStream_t)stream, "nkbs_head_tc_bwd")
+                 : in_mode == 2 ? launch_tc<true, 2>(a, N, (cudaStream_t)stream, "nkbs_head_tc_bwd")
+                                : launch_tc<true, 3>(a, N, (cudaStream_t)stream, "nkbs_head_tc_bwd");
   if (rc) return -1;
   NKBS_CHECK_LAUNCH("nkbs_head_tc_bwd");
   return 0;

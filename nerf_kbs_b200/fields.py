@@ -361,7 +361,13 @@ class NerfactoField(_Field):
             W, b = self.mlp_semantics.weights_biases()
             W = W + [self.field_head_semantics.net.weight]
             b = b + [self.field_head_semantics.net.bias]
-            x = ops.mlp(sem_in, W, b, self.mlp_semantics.relu_mask, ops.ACT_NONE)
+            if fused_in and len(W) == 3:
+                # geometry columns read in place from the base MLP's output (no slice copy), rows stored coalesced
+                sem_src = src if self.pass_semantic_gradients else src.detach()
+                x = ops.head_mlp(sem_src, col, None, None, None, None, S, 0, False, False, W, b,
+                                 self.mlp_semantics.relu_mask, ops.ACT_NONE)
+            else:
+                x = ops.mlp(sem_in, W, b, self.mlp_semantics.relu_mask, ops.ACT_NONE)
             outputs[FieldHeadNames.SEMANTICS] = x.reshape(*outputs_shape, -1)
 
         W, b = self.mlp_head.weights_biases()

@@ -342,7 +342,7 @@ class _HeadMlp(torch.autograd.Function):
         src = _c(src)
         require_cuda(src, *Ws)
         N, stride = src.shape
-        emb_dim = emb.shape[1] if emb is not None else emb_const.shape[0]
+        emb_dim = emb.shape[1] if emb is not None else (emb_const.shape[0] if emb_const is not None else 0)
         dims = [Ws[0].shape[1]] + [w.shape[0] for w in Ws]
         use_cam = cam is not None and emb_const is None
         y = torch.empty((N, dims[-1]), device=src.device, dtype=torch.float32)
@@ -381,7 +381,8 @@ class _HeadMlp(torch.autograd.Function):
 
 def head_mlp(src, col: int, emb_table, emb_const, directions, cam, S: int, sh_dim: int, dir_per_ray: bool,
              cam_per_ray: bool, weights, biases, relu_mask: int, out_act: int):
-    """Head MLP over rows [SH(sh_dim) | src[:, col:col+15] | embedding row]; tensor-core path (nkbs_head_tc_*)."""
+    """Head MLP over rows [SH(sh_dim) | src[:, col:col+15] | embedding row]; tensor-core path (nkbs_head_tc_*).
+    Without an embedding (``emb_table`` and ``emb_const`` both None) the row is the geometry feature alone."""
     params = []
     for w, b in zip(weights, biases):
         params += [w, b]

@@ -170,3 +170,37 @@ def test_head_mlp_fused_eval_constant_embedding():
     finally:
         ops.set_mlp_precision(prev)
     assert rel_err(y, want) <= 1e-5
+
+
+@pytest.mark.parametrize("R,S,with_grad", [(70, 48, True), (70, 48, False), (3, 5, True), (683, 48, False)])
+def test_semantics_head_reads_geometry_in_place(R, S, with_grad):
+    """Semantics head (15 -> 64 -> 64 -> 19): input rows read from columns 1..15 of the base MLP's [N,16] output inside
+    the kernel (no slice copy) vs nkbs_mlp_tc on the contiguous slice; output rows are stored through shared memory."""
+    g = torch.Generator().manual_seed(R + S)
+    N = R * S
+    dims = [15, 64, 64, 19]
+    Ws = [(torch.randn(dims[i + 1], dims[i], generator=g) / dims[i] ** 0.5).to(DEV).requires_grad_() for i in range(3)]
+    bs = [(torch.randn(dims[i + 1], generator=g) * 0.1).to(DEV).requires_grad_() for i in range(3)]
+    base = torch.randn(N, 16, generator=g).to(DEV).requires_grad_(with_grad)
+    dy = torch.randn(N, 19, generator=g).to(DEV)
+    prev = ops.get_mlp_precision()
+    ops.set_mlp_precision("tc")
+    try:
+        res = {}
+        for fused in (True, False):
+            for t in Ws + bs + [base]:
+                t.grad = None
+            if fused:
+                y = ops.head_mlp(base, 1, None, None, None, None, S, 0, False, False, Ws, bs, 0b01, ops.ACT_NONE)
+            else:
+                y = ops.mlp(base[:, 1:], Ws, bs, 0b01, ops.ACT_NONE)
+            y.backward(dy)
+            res[fused] = (y.detach().clone(), base.grad.clone() if with_grad else None, [t.grad.clone() for t in Ws + bs])
+    finally:
+        ops.set_mlp_precision(prev)
+    assert rel_err(res[True][0], res[False][0]) <= 1e-5, "y"
+    if with_grad:
+        assert float(res[True][1][:, 0].abs().max()) == 0.0
+        assert rel_err(res[True][1], res[False][1]) <= 2e-3, "d base"
+    for i, (a, b) in enumerate(zip(res[True][2], res[False][2])):
+        assert rel_err(a, b) <= 2e-3, f"param grad {i}"
