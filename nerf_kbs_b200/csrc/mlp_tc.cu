@@ -507,19 +507,38 @@ __device__ __forceinline__ void kernel_prologue(Sh& sh, bool issuer, int tmem_co
   fence_after_sync();
 }
 
+// Register rebalancing (setmaxnreg): the CTA is NWG epilogue warpgroups plus one warpgroup of which only the first warp
+// works (the MMA issuer).  At launch every warp gets the same 512 / (NWG + 1) registers per lane of its SM
+// sub-partition; the issuer warpgroup shrinks to 56 and the epilogue warpgroups grow into what that frees
+// (pool = the CTA's launch allocation: 2 x 224 + 56 = 3 x 168, 3 x 152 + 56 = 4 x 128, 4 x 104 + 56 <= 5 x 96), which is what keeps their tile-wide register arrays out of local memory.
+template <int NWG>
+__device__ __forceinline__ void rebalance_registers(bool issuer_wg) {
+  if (NWG < 2) return;
+  if (issuer_wg) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+  } else {
+    if (NWG == 2) asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
+    else if (NWG == 3) asm volatile("setmaxnreg.inc.sync.aligned.u32 152;");
+    else asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");
+  }
+}
+
 template <int FMT, int NWG, int IN>
-__global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_fwd_kernel(const TcArgs a) {
+__global__ void __launch_bounds__((NWG + 1) * kThreads, 1) mlp_tc_fwd_kernel(const TcArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ Sh sh;
   constexpr int nwg = NWG;
   const int wg = threadIdx.x >> 7;
   const int tid = threadIdx.x & (kThreads - 1);
-  const bool issuer = wg == nwg;
+  const bool issuer = threadIdx.x >> 5 == nwg * 4;  // first warp of the last warpgroup; its other warps only idle
   stage_weights<FMT>(a, smem);
   kernel_prologue(sh, issuer, a.tmem_cols);
   const uint32_t tmem = sh.tmem_base;
   const uint32_t smem_base = smem_u32(smem);
   const int64_t ntiles = (a.N + kTile - 1) / kTile;
+  if (wg == nwg) {
+    rebalance_registers<NWG>(true);
+  }
   if (issuer) {
     uint32_t rph = 0;  // bit g: phase of ready[g]
     const uint32_t leader = elect_one();
@@ -539,7 +558,8 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_fwd_kernel(cons
         }
       }
     }
-  } else {
+  } else if (wg < nwg) {
+    rebalance_registers<NWG>(false);
     unsigned char* base = smem + a.wg_base + wg * a.wg_stride;
     const uint32_t tmem_row = tmem + wg * kMaxWidth + ((uint32_t)(tid & ~31) << 16);
     const TcLayer& last = a.layer[a.nl - 1];
@@ -660,14 +680,14 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_fwd_kernel(cons
 }
 
 template <int FMT, int NWG, int IN>
-__global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(const TcArgs a) {
+__global__ void __launch_bounds__((NWG + 1) * kThreads, 1) mlp_tc_bwd_kernel(const TcArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ Sh sh;
   constexpr int nwg = NWG;
   const int wg = threadIdx.x >> 7;
   const int tid = threadIdx.x & (kThreads - 1);
   const int lane = threadIdx.x & 31;
-  const bool issuer = wg == nwg;
+  const bool issuer = threadIdx.x >> 5 == nwg * 4;  // first warp of the last warpgroup; its other warps only idle
   stage_weights<FMT>(a, smem);
   kernel_prologue(sh, issuer, a.tmem_cols);
   const uint32_t tmem = sh.tmem_base;
@@ -677,6 +697,9 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(cons
   const bool any_tile = tile_of(0, 0, nwg) < ntiles;
   // gradient w.r.t. the first layer's input is wanted: as rows (dx) or split into geo / embedding parts (IN != 0)
   const bool want_dx0 = a.dx != nullptr || (IN != 0 && (a.hin.dgeo != nullptr || a.hin.demb != nullptr));
+  if (wg == nwg) {
+    rebalance_registers<NWG>(true);
+  }
   if (issuer) {
     uint32_t rph = 0;      // bit g: phase of ready[g]
     uint32_t started = 0;  // bit l: dW_l accumulator holds data
@@ -727,7 +750,8 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(cons
         }
       }
     }
-  } else {
+  } else if (wg < nwg) {
+    rebalance_registers<NWG>(false);
     unsigned char* base = smem + a.wg_base + wg * a.wg_stride;
     const uint32_t tmem_row = tmem + wg * kMaxWidth + ((uint32_t)(tid & ~31) << 16);
     const TcLayer& last = a.layer[nl - 1];
@@ -825,27 +849,24 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(cons
             uint32_t b0[16], b1[16];
             tmem_ld16_issue(tmem_row + cb, b0);
             tmem_ld16_issue(tmem_row + cb + 16, b1);
-            uint4 m[4];
-            if (masked) {
-#pragma unroll
-              for (int q = 0; q < 4; ++q) m[q] = *reinterpret_cast<const uint4*>(xt + ((cb >> 3) + q) * kActCs + r * 16);
-            }
             tmem_ld_wait();
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
               const uint32_t* b = q < 2 ? b0 : b1;
               const int o = (q & 1) * 8;
+              uint4* slot = reinterpret_cast<uint4*>(xt + ((cb >> 3) + q) * kActCs + r * 16);
               uint32_t p0 = pack2<FMT>(__uint_as_float(b[o]), __uint_as_float(b[o + 1]));
               uint32_t p1 = pack2<FMT>(__uint_as_float(b[o + 2]), __uint_as_float(b[o + 3]));
               uint32_t p2 = pack2<FMT>(__uint_as_float(b[o + 4]), __uint_as_float(b[o + 5]));
               uint32_t p3 = pack2<FMT>(__uint_as_float(b[o + 6]), __uint_as_float(b[o + 7]));
-              if (masked) {
-                p0 = mask_pos2<FMT>(p0, m[q].x);
-                p1 = mask_pos2<FMT>(p1, m[q].y);
-                p2 = mask_pos2<FMT>(p2, m[q].z);
-                p3 = mask_pos2<FMT>(p3, m[q].w);
+              if (masked) {  // the stored activation chunk is read right where it is needed (four live registers)
+                const uint4 m = *slot;
+                p0 = mask_pos2<FMT>(p0, m.x);
+                p1 = mask_pos2<FMT>(p1, m.y);
+                p2 = mask_pos2<FMT>(p2, m.z);
+                p3 = mask_pos2<FMT>(p3, m.w);
               }
-              *reinterpret_cast<uint4*>(xt + ((cb >> 3) + q) * kActCs + r * 16) = make_uint4(p0, p1, p2, p3);
+              *slot = make_uint4(p0, p1, p2, p3);
             }
           }
           tmem_foreach16<kMaxWidth / 16>(tmem_row, Nx, kMaxWidth, [&](int c0, float v[16]) {
@@ -960,26 +981,27 @@ __global__ void __launch_bounds__(NWG * kThreads + 32, 1) mlp_tc_bwd_kernel(cons
       // recycled layout: the dx staging covers X_0's place, which the next tile's input is written into right away
       if (a.recycle) wg_sync(wg);
     }
-  }
-  // ---- flush the weight / bias gradients: M=64 accumulator rows live in lanes 0..15 of every warp ----
-  fence_before_sync();
-  __syncthreads();
-  fence_after_sync();
-  if (!issuer && any_tile) {
-    const int w = tid >> 5;
-    const int n = 16 * w + lane;
-    const uint32_t lane_base = tmem + ((uint32_t)(tid & ~31) << 16);
-    for (int l = wg; l < nl; l += nwg) {
-      const TcLayer& ly = a.layer[l];
-      for (int c0 = 0; c0 < ly.Ka; c0 += 16) {
-        float v[16];
-        tmem_ld16(lane_base + ly.dw_col + c0, v);
-        if (lane < 16 && n < ly.N) {
+    // ---- flush the weight / bias gradients: M=64 accumulator rows live in lanes 0..15 of every warp.  Every
+    // warpgroup has waited for its own last batch; the barrier among them covers the others' dW accumulations. ----
+    fence_before_sync();
+    epilogue_sync<NWG>();
+    fence_after_sync();
+    if (any_tile) {
+      const int w = tid >> 5;
+      const int n = 16 * w + lane;
+      const uint32_t lane_base = tmem + ((uint32_t)(tid & ~31) << 16);
+      for (int l = wg; l < nl; l += nwg) {
+        const TcLayer& ly = a.layer[l];
+        for (int c0 = 0; c0 < ly.Ka; c0 += 16) {
+          float v[16];
+          tmem_ld16(lane_base + ly.dw_col + c0, v);
+          if (lane < 16 && n < ly.N) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            int k = c0 + j;
-            if (k < ly.K) atomicAdd(ly.dW + (size_t)n * ly.K + k, v[j]);
-            else if (k == ly.K) atomicAdd(ly.db + n, v[j]);
+            for (int j = 0; j < 16; ++j) {
+              int k = c0 + j;
+              if (k < ly.K) atomicAdd(ly.dW + (size_t)n * ly.K + k, v[j]);
+              else if (k == ly.K) atomicAdd(ly.db + n, v[j]);
+            }
           }
         }
       }
@@ -1133,7 +1155,7 @@ int set_smem(K kernel, int bytes, const char* who) {
 int pick_grid(const TcArgs& a, int64_t N) {
   int64_t ntiles = (N + kTile - 1) / kTile;
   int64_t groups = (ntiles + a.nwg - 1) / a.nwg;
-  int threads = a.nwg * kThreads + 32;
+  int threads = (a.nwg + 1) * kThreads;
   int per_sm = kSmemLimit / (a.smem_bytes + 1024);
   if (per_sm > 512 / a.tmem_cols) per_sm = 512 / a.tmem_cols;
   if (per_sm > 2048 / threads) per_sm = 2048 / threads;
@@ -1142,13 +1164,32 @@ int pick_grid(const TcArgs& a, int64_t N) {
   return (int)(groups < cap ? groups : cap);
 }
 
+// registers per lane the rebalancing hands out (rebalance_registers) vs. what the kernel was launched with: the
+// growth blocks until the pool has room, so a kernel that was allocated less than assumed must not be launched
+template <typename K>
+int check_register_pool(K kernel, int nwg, const char* who) {
+  if (nwg < 2) return 0;
+  cudaFuncAttributes fa;
+  cudaError_t e = cudaFuncGetAttributes(&fa, kernel);
+  NKBS_CHECK_ARG(e == cudaSuccess, "%s: cudaFuncGetAttributes: %s", who, cudaGetErrorString(e));
+  const int grown = nwg == 2 ? 224 : (nwg == 3 ? 152 : 104);
+  NKBS_CHECK_ARG(fa.numRegs * (nwg + 1) >= nwg * grown + 56,
+                 "%s: kernel launched with %d registers per thread, the register rebalancing needs %d", who, fa.numRegs,
+                 (nwg * grown + 56 + nwg) / (nwg + 1));
+  return 0;
+}
+
 template <bool BWD, int FMT, int NWG, int IN>
 int launch_one(const TcArgs& a, int64_t N, cudaStream_t st, const char* who) {
-  const int grid = pick_grid(a, N), threads = NWG * kThreads + 32;
+  const int grid = pick_grid(a, N), threads = (NWG + 1) * kThreads;
   if (BWD) {
+    static const int ok = check_register_pool(mlp_tc_bwd_kernel<FMT, NWG, IN>, NWG, who);
+    if (ok) return -1;
     if (set_smem(mlp_tc_bwd_kernel<FMT, NWG, IN>, a.smem_bytes, who)) return -1;
     mlp_tc_bwd_kernel<FMT, NWG, IN><<<grid, threads, a.smem_bytes, st>>>(a);
   } else {
+    static const int ok = check_register_pool(mlp_tc_fwd_kernel<FMT, NWG, IN>, NWG, who);
+    if (ok) return -1;
     if (set_smem(mlp_tc_fwd_kernel<FMT, NWG, IN>, a.smem_bytes, who)) return -1;
     mlp_tc_fwd_kernel<FMT, NWG, IN><<<grid, threads, a.smem_bytes, st>>>(a);
   }

@@ -211,6 +211,14 @@ __device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc, uint
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+// barrier among all epilogue warpgroups of the CTA (id 5), NWG * 128 threads
+template <int NWG>
+__device__ __forceinline__ void epilogue_sync() {
+  if (NWG == 1) asm volatile("bar.sync 5, 128;" ::: "memory");
+  else if (NWG == 2) asm volatile("bar.sync 5, 256;" ::: "memory");
+  else if (NWG == 3) asm volatile("bar.sync 5, 384;" ::: "memory");
+  else asm volatile("bar.sync 5, 512;" ::: "memory");
+}
 // barrier among the 128 threads of one warpgroup (ids 1..4; id 0 is __syncthreads)
 __device__ __forceinline__ void wg_sync(int wg) {
   switch (wg) {  // immediate ids: a register id would make the compiler reserve all 16 hardware barriers
