@@ -39,7 +39,8 @@ want = ["Kernel Name", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__
         "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
         "l1tex__throughput.avg.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active",
         "smsp__issue_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread", "launch__grid_size",
-        "launch__block_size", "smsp__inst_executed.sum"]
+        "launch__block_size", "smsp__inst_executed.sum", "l1tex__t_requests_pipe_lsu_mem_local_op_ld.sum",
+        "l1tex__t_requests_pipe_lsu_mem_local_op_st.sum"]
 cols = [h.index(w) for w in want if w in h]
 with open(os.path.join(dst, f"{tag}_top_kernels_ncu_full.csv"), "w", newline="") as f:
     w = csv.writer(f)
