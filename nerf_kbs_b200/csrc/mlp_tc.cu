@@ -64,6 +64,8 @@ struct HeadIn {
   const float* emb;        // [num_images, emb_dim]
   const float* emb_const;  // [emb_dim]
   int S;                   // samples per ray
+  int geo_vec;             // rows can be fetched as four aligned 16-byte loads starting one float before geo
+  int emb_vec;             // embedding rows (and the constant row) are 16-byte aligned
   float* dgeo;             // backward: row n at dgeo + n * dgeo_stride, or null
   int dgeo_stride;
   float* demb;             // backward: [num_images, emb_dim], accumulated into, or null
@@ -184,33 +186,70 @@ __device__ __forceinline__ void build_head_tile(const TcArgs& a, int64_t row0, u
   constexpr int GEO = 15, K0 = SHD + GEO + EMBD, Ka = (K0 + 1 + 15) & ~15;
   const HeadIn& h = a.hin;
   const int64_t row = row0 + tid;
-  const bool live = row < a.N;
-  const int64_t ray = live ? row / h.S : 0;
+  if (row >= a.N) {  // rows past the end (last tile only): zeros and the constant-one column
+#pragma unroll
+    for (int c = 0; c < Ka / 8; ++c) {
+      uint4 z = make_uint4(0u, 0u, 0u, 0u);
+      if (c == K0 / 8) {
+        const uint32_t one = (uint32_t)cvt16<FMT>(1.f) << ((K0 & 1) * 16);
+        if (((K0 & 7) >> 1) == 0) z.x = one;
+        else if (((K0 & 7) >> 1) == 1) z.y = one;
+        else if (((K0 & 7) >> 1) == 2) z.z = one;
+        else z.w = one;
+      }
+      *reinterpret_cast<uint4*>(tile + c * kActCs + tid * 16) = z;
+    }
+    return;
+  }
+  const int64_t ray = row / h.S;
   float sh[16];
   if (SHD > 0) {
-    const int64_t di = h.dir_per_ray ? ray : (live ? row : 0);
+    const int64_t di = h.dir_per_ray ? ray : row;
     const float x = (__ldg(h.dirs + 3 * di) + 1.0f) / 2.0f;
     const float y = (__ldg(h.dirs + 3 * di + 1) + 1.0f) / 2.0f;
     const float z = (__ldg(h.dirs + 3 * di + 2) + 1.0f) / 2.0f;
     sh16(x, y, z, sh);
   }
-  // geometry and embedding values are fetched chunk by chunk (L1-resident rows), which keeps the live registers
-  // of this stage near one chunk instead of the whole 64-wide row
-  const float* gp = h.geo + (live ? row : 0) * (int64_t)h.geo_stride;
-  const float* ep = h.emb_const;
-  if (EMBD > 0 && h.cam) ep = h.emb + __ldg(h.cam + (h.cam_per_ray ? ray : (live ? row : 0))) * EMBD;
+  // geometry: g[1..15].  When the features are columns 1..15 of 16-float rows (the base MLP's output, the usual
+  // caller) the row is fetched with four 16-byte loads; element 0 (the density column) rides along unused.
+  float g[16];
+  const float* gp = h.geo + row * (int64_t)h.geo_stride;
+  if (h.geo_vec) {
+    const float4* q = reinterpret_cast<const float4*>(gp - 1);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float4 t = __ldg(q + i);
+      g[4 * i] = t.x, g[4 * i + 1] = t.y, g[4 * i + 2] = t.z, g[4 * i + 3] = t.w;
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < GEO; ++k) g[k + 1] = __ldg(gp + k);
+  }
+  float e[EMBD > 0 ? EMBD : 1];
+  if (EMBD > 0) {
+    const float* ep = h.emb_const;
+    if (h.cam) ep = h.emb + __ldg(h.cam + (h.cam_per_ray ? ray : row)) * EMBD;
+    if (h.emb_vec) {
+#pragma unroll
+      for (int i = 0; i < EMBD / 4; ++i) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(ep) + i);
+        e[4 * i] = t.x, e[4 * i + 1] = t.y, e[4 * i + 2] = t.z, e[4 * i + 3] = t.w;
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < EMBD; ++k) e[k] = __ldg(ep + k);
+    }
+  }
 #pragma unroll
   for (int c = 0; c < Ka / 8; ++c) {
     float v[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int k = 8 * c + j;  // compile-time column
-      float x;
-      if (k < SHD) x = sh[k < 16 ? k : 0];
-      else if (k < SHD + GEO) x = __ldg(gp + (k - SHD));
-      else if (k < K0) x = __ldg(ep + (k - SHD - GEO));
-      else x = k == K0 ? 1.f : 0.f;
-      v[j] = (live || k == K0) ? x : 0.f;
+      if (k < SHD) v[j] = sh[k < 16 ? k : 0];
+      else if (k < SHD + GEO) v[j] = g[k - SHD + 1];
+      else if (k < K0) v[j] = e[EMBD > 0 ? k - SHD - GEO : 0];
+      else v[j] = k == K0 ? 1.f : 0.f;
     }
     *reinterpret_cast<uint4*>(tile + c * kActCs + tid * 16) =
         make_uint4(pack2<FMT>(v[0], v[1]), pack2<FMT>(v[2], v[3]), pack2<FMT>(v[4], v[5]), pack2<FMT>(v[6], v[7]));
@@ -1234,6 +1273,10 @@ int fill_head(TcArgs& a, const char* who, int sh_dim, int geo_dim, int emb_dim, 
   a.hin.emb = emb;
   a.hin.emb_const = emb_const;
   a.hin.S = S;
+  // a pointer 4 bytes past a 16-byte boundary is never the start of an allocation: the float before it is readable
+  a.hin.geo_vec = (geo_stride % 4 == 0) && (reinterpret_cast<uintptr_t>(geo) & 15) == 4;
+  a.hin.emb_vec = emb_dim % 4 == 0 && emb_dim > 0 &&
+                  (reinterpret_cast<uintptr_t>(a.hin.cam ? (const void*)emb : (const void*)emb_const) & 15) == 0;
   a.hin.dgeo = nullptr;
   a.hin.dgeo_stride = 0;
   a.hin.demb = nullptr;
