@@ -32,7 +32,10 @@ def test_oracle_reproduces_golden_vectors():
             assert np.array_equal(a, b), f"{k}: not bit-identical to the golden vector"
         else:
             scale = np.abs(b).max() + 1e-12
-            assert np.abs(a - b).max() <= 1e-6 * scale, f"{k}: drifted by {np.abs(a - b).max() / scale:.2e}"
+            # pixel area = product of differences of neighbouring unit directions (cancellation: one fp32 ulp of a
+            # direction is ~1e-4 of the area), so it moves with the host's vector ISA; same 1e-4 bar as the GPU test
+            tol = 1e-4 if k == "ray_pixel_area" else 1e-6
+            assert np.abs(a - b).max() <= tol * scale, f"{k}: drifted by {np.abs(a - b).max() / scale:.2e}"
 
 
 def test_fp32_scaling_artefact_is_pinned():
