@@ -187,7 +187,7 @@ def kernel_work(name, a):
         N, L = a[7] * a[8], a[13]
         gathers = 8 * L * 2 * 4
         return "hbm", N * ((8 + gathers + 4) if name.endswith("fwd") else (8 + 4 + 2 * gathers))
-    if name == "nkbs_ray_losses":
+    if name in ("nkbs_ray_losses", "nkbs_ray_losses_weighted"):
         R, S, n_prop = a[0], a[1], a[5]
         sp = list(a[6])[:n_prop]
         per = 4 * (S + 1) + 8 * S + sum(4 * (x + 1) + 8 * x for x in sp) + 36 * (a[10] is not None)
@@ -199,7 +199,7 @@ NCU_NAMES = {"nkbs_density_bwd": "density_bwd_kernel", "nkbs_density_fwd": "dens
              "nkbs_encode_fwd": "encode_fwd_kernel", "nkbs_mlp_tc_bwd": "mlp_tc_bwd_kernel", "nkbs_mlp_tc_fwd": "mlp_tc_fwd_kernel",
              "nkbs_head_tc_bwd": "mlp_tc_bwd_kernel", "nkbs_head_tc_fwd": "mlp_tc_fwd_kernel", "nkbs_adam_step": "adam_kernel",
              "nkbs_composite_fwd": "composite_fwd_kernel", "nkbs_composite_bwd": "composite_bwd_kernel",
-             "nkbs_ray_losses": "ray_losses_kernel", "nkbs_pdf_sample": "pdf_sample"}
+             "nkbs_ray_losses": "ray_losses_kernel", "nkbs_ray_losses_weighted": "ray_losses_kernel", "nkbs_pdf_sample": "pdf_sample"}
 _NCU_BYTES = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 
 

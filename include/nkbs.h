@@ -102,6 +102,17 @@ int nkbs_ray_losses(int64_t R, int32_t S, const float* sdist, const float* w, fl
                     const int64_t* labels, int32_t C, int64_t ignore_index, float* dlogits, float* out,
                     void* stream);
 
+/* N1' — the same pass for a caller that owns the total loss (the step driver): term_weights = HOST [3] multipliers of
+ * (colour MSE, interlevel, distortion) as in the loss dict of nerfacto.py:483-489 (1, interlevel_loss_mult,
+ * distortion_loss_mult).  The gradients dw / dw_prop / drgb come out already multiplied by their term's weight, so they
+ * seed the backward pass as they are; out [5] still receives the UNWEIGHTED terms; total [1] (optional, accumulated
+ * into) receives the weighted sum of the three terms.  The cross-entropy outputs are as in nkbs_ray_losses. */
+int nkbs_ray_losses_weighted(int64_t R, int32_t S, const float* sdist, const float* w, float* dw, int32_t n_prop,
+                             const int32_t* S_prop, const float* const* sdist_prop, const float* const* w_prop,
+                             float* const* dw_prop, const float* rgb, const float* image, float* drgb,
+                             const float* logits, const int64_t* labels, int32_t C, int64_t ignore_index,
+                             float* dlogits, float* out, const float* term_weights, float* total, void* stream);
+
 /* N3 — pinhole ray generation: ray_indices [N,3] int64 (camera, row, col), c2w [num_cameras,3,4], intrinsics
  * [num_cameras,4] = fx, fy, cx, cy.  Pixel centres at +0.5; camera looks down -z with +y up; directions are unit
  * vectors, directions_norm their length before normalisation, pixel_area the product of the distances to the rays

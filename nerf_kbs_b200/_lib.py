@@ -28,6 +28,8 @@ SIGNATURES = {
     "nkbs_density_bwd": [_i32, _p, _p, _p, _p, _p, _i32, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _i32, _p, _i32,
                          _p, _p, _p, _p, _p, _p],
     "nkbs_ray_losses": [_i64, _i32, _p, _p, _p, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _i64, _p, _p, _p],
+    "nkbs_ray_losses_weighted": [_i64, _i32, _p, _p, _p, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _i64, _p, _p, _p, _p,
+                                 _p],
     "nkbs_generate_rays": [_i64, _p, _p, _p, _i64, _p, _p, _p, _p, _p, _p],
     "nkbs_compact_masked": [_i64, _p, _p, _p, _i64, _i64, _p, _p, _p, _p],
     "nkbs_color_to_label": [_i64, _p, _p, _i64, _p, _p],

@@ -7,6 +7,9 @@
 namespace {
 
 constexpr int kEncThreads = 256;
+// x edges of a cell as (ceil-x corner, floor-x corner) in the corner order of nkbs_corner_hashes
+__device__ constexpr int kEdgeC[4] = {0, 1, 4, 5};
+__device__ constexpr int kEdgeF[4] = {3, 2, 7, 6};
 
 struct EncodeArgs : SampleSource {
   int64_t N;
@@ -18,7 +21,7 @@ struct EncodeArgs : SampleSource {
   int64_t* indices;
 };
 
-// One thread per sample; the level loop keeps 8 independent 8-byte gathers in flight per level and
+// One thread per sample; the level loop keeps 4 16-byte (+ up to 4 8-byte) independent gathers in flight per level and
 // the compiler overlaps two levels (unroll 2).  Level scales live in shared memory.
 template <bool kWriteIdx>
 __global__ void __launch_bounds__(kEncThreads) encode_fwd_kernel(const EncodeArgs a) {
@@ -43,9 +46,27 @@ __global__ void __launch_bounds__(kEncThreads) encode_fwd_kernel(const EncodeArg
       uint32_t h[8];
       nkbs_corner_hashes(cl, mask, h);
       const float2* tl = a.table + ((size_t)l << a.lv.log2_T);
+      // The x prime of the hash is 1, so the two corners of an x edge are rows h and h ^ 1 of one 16-byte pair whenever
+      // floor(x) is even (or ceil == floor): one 16-byte gather at the pair base returns both, and the second gather of
+      // the edge is issued only when floor(x) is odd.  Same rows and values as eight 8-byte gathers, a quarter fewer
+      // sector requests on the levels whose gathers do not coalesce.
+      const bool same = cl.c[0] == cl.f[0];
+      const bool in_pair = same || !(cl.f[0] & 1u);
+      float4 q[4];
+      float2 vc[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) q[j] = __ldg(reinterpret_cast<const float4*>(tl + (h[kEdgeF[j]] & ~1u)));
+#pragma unroll
+      for (int j = 0; j < 4; ++j) vc[j] = in_pair ? make_float2(0.f, 0.f) : __ldg(tl + h[kEdgeC[j]]);
       float2 v[8];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) v[k] = __ldg(tl + h[k]);
+      for (int j = 0; j < 4; ++j) {
+        const bool hi = h[kEdgeF[j]] & 1u;
+        const float2 lo2 = make_float2(q[j].x, q[j].y), hi2 = make_float2(q[j].z, q[j].w);
+        const float2 vf = hi ? hi2 : lo2, other = hi ? lo2 : hi2;
+        v[kEdgeF[j]] = vf;
+        v[kEdgeC[j]] = same ? vf : (in_pair ? other : vc[j]);
+      }
       float v0[8], v1[8];
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
@@ -117,6 +138,7 @@ extern "C" int nkbs_encode_fwd(int mode, const float* x, const float* origins, c
   NKBS_CHECK_ARG(F == 2, "nkbs_encode_fwd: features_per_level must be 2 (got %d)", F);
   NKBS_CHECK_ARG(R >= 0 && S >= 1, "nkbs_encode_fwd: bad sizes R=%lld S=%d", (long long)R, S);
   NKBS_CHECK_ARG(table && features && scalings, "nkbs_encode_fwd: null table/features/scalings");
+  NKBS_CHECK_ARG((reinterpret_cast<uintptr_t>(table) & 15u) == 0, "nkbs_encode_fwd: table must be 16-byte aligned");
   if (mode == 2)
     NKBS_CHECK_ARG(origins && directions && starts && ends, "nkbs_encode_fwd: frustum mode needs origins/directions/starts/ends");
   else

@@ -37,7 +37,10 @@ struct LossArgs {
   int64_t ignore_index;
   float* dlogits;               // [R,C]  softmax - onehot, zero rows for ignored labels (caller divides by the count)
   float* out;                   // [5] rgb mse, interlevel, distortion, CE sum, CE count  (accumulated: caller zeroes)
-  float inv_R, inv_RS, inv_R3;
+  float inv_R, inv_RS, inv_R3;  // normalisers of the reported terms
+  float g_R, g_RS, g_R3;        // normalisers x term weights, applied to the gradients (weighted entry point)
+  float tw[3];                  // term weights (rgb, interlevel, distortion)
+  float* total;                 // optional [1]: weighted sum of the three terms, accumulated
 };
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -104,7 +107,7 @@ __global__ void __launch_bounds__(kThreads) ray_losses_kernel(const LossArgs a, 
         for (int j = 0; j < S; ++j) inner += sw[j] * fabsf(ui - sut[j]);
         const float delta = sc[i + 1] - sc[i];
         t_dist += wi * inner + wi * wi * delta / 3.f;
-        a.dw[r * S + i] = (2.f * inner + 2.f * wi * delta / 3.f) * a.inv_R;
+        a.dw[r * S + i] = (2.f * inner + 2.f * wi * delta / 3.f) * a.g_R;
       }
     }
     // ---- interlevel: for every proposal level, the final histogram must lie under the proposal's envelope ----
@@ -137,7 +140,7 @@ __global__ void __launch_bounds__(kThreads) ray_losses_kernel(const LossArgs a, 
         const float d = fmaxf(ws - w_outer, 0.f);
         const float den = ws + 1e-7f;
         t_inter += d * d / den;
-        const float g = -2.f * d / den * a.inv_RS;  // d loss / d w_outer
+        const float g = -2.f * d / den * a.g_RS;  // d loss / d w_outer
         if (g != 0.f) {
           atomicAdd(&sD[lo], g);
           atomicAdd(&sD[hi + 1], -g);
@@ -160,7 +163,7 @@ __global__ void __launch_bounds__(kThreads) ray_losses_kernel(const LossArgs a, 
     if (a.rgb && lane < 3) {
       const float e = a.rgb[r * 3 + lane] - a.image[r * 3 + lane];
       t_rgb += e * e;
-      a.drgb[r * 3 + lane] = 2.f * e * a.inv_R3;
+      a.drgb[r * 3 + lane] = 2.f * e * a.g_R3;
     }
     // ---- semantic cross-entropy ----
     if (a.logits) {
@@ -203,15 +206,19 @@ __global__ void __launch_bounds__(kThreads) ray_losses_kernel(const LossArgs a, 
     const float v = s_out[threadIdx.x] * scale;
     if (v != 0.f) atomicAdd(a.out + threadIdx.x, v);
   }
+  if (a.total && threadIdx.x == 0) {
+    const float v = a.tw[0] * (s_out[0] * a.inv_R3) + a.tw[1] * (s_out[1] * a.inv_RS) + a.tw[2] * (s_out[2] * a.inv_R);
+    if (v != 0.f) atomicAdd(a.total, v);
+  }
 }
 
 }  // namespace
 
-extern "C" int nkbs_ray_losses(int64_t R, int32_t S, const float* sdist, const float* w, float* dw, int32_t n_prop,
-                               const int32_t* S_prop, const float* const* sdist_prop, const float* const* w_prop,
-                               float* const* dw_prop, const float* rgb, const float* image, float* drgb,
-                               const float* logits, const int64_t* labels, int32_t C, int64_t ignore_index,
-                               float* dlogits, float* out, void* stream) {
+static int ray_losses_launch(int64_t R, int32_t S, const float* sdist, const float* w, float* dw, int32_t n_prop,
+                             const int32_t* S_prop, const float* const* sdist_prop, const float* const* w_prop,
+                             float* const* dw_prop, const float* rgb, const float* image, float* drgb,
+                             const float* logits, const int64_t* labels, int32_t C, int64_t ignore_index,
+                             float* dlogits, float* out, const float* term_weights, float* total, void* stream) {
   NKBS_CHECK_ARG(R >= 0 && out, "nkbs_ray_losses: bad arguments");
   NKBS_CHECK_ARG(n_prop >= 0 && n_prop <= kMaxProp, "nkbs_ray_losses: at most %d proposal levels (got %d)", kMaxProp, n_prop);
   const bool hist = dw != nullptr || n_prop > 0;
@@ -248,6 +255,11 @@ extern "C" int nkbs_ray_losses(int64_t R, int32_t S, const float* sdist, const f
   a.inv_R = 1.f / (float)R;
   a.inv_RS = 1.f / ((float)R * (float)a.S);
   a.inv_R3 = 1.f / ((float)R * 3.f);
+  for (int i = 0; i < 3; ++i) a.tw[i] = term_weights ? term_weights[i] : 1.f;
+  a.g_R3 = a.inv_R3 * a.tw[0];
+  a.g_RS = a.inv_RS * a.tw[1];
+  a.g_R = a.inv_R * a.tw[2];
+  a.total = total;
   const size_t smem = (size_t)kWarpsPerCta * ((a.S + 1) + 2 * a.S + 3 * (smax + 2)) * sizeof(float);
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(ray_losses_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -259,4 +271,24 @@ extern "C" int nkbs_ray_losses(int64_t R, int32_t S, const float* sdist, const f
   ray_losses_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(a, smax);
   NKBS_CHECK_LAUNCH("nkbs_ray_losses");
   return 0;
+}
+
+extern "C" int nkbs_ray_losses(int64_t R, int32_t S, const float* sdist, const float* w, float* dw, int32_t n_prop,
+                               const int32_t* S_prop, const float* const* sdist_prop, const float* const* w_prop,
+                               float* const* dw_prop, const float* rgb, const float* image, float* drgb,
+                               const float* logits, const int64_t* labels, int32_t C, int64_t ignore_index,
+                               float* dlogits, float* out, void* stream) {
+  return ray_losses_launch(R, S, sdist, w, dw, n_prop, S_prop, sdist_prop, w_prop, dw_prop, rgb, image, drgb, logits,
+                           labels, C, ignore_index, dlogits, out, nullptr, nullptr, stream);
+}
+
+extern "C" int nkbs_ray_losses_weighted(int64_t R, int32_t S, const float* sdist, const float* w, float* dw,
+                                        int32_t n_prop, const int32_t* S_prop, const float* const* sdist_prop,
+                                        const float* const* w_prop, float* const* dw_prop, const float* rgb,
+                                        const float* image, float* drgb, const float* logits, const int64_t* labels,
+                                        int32_t C, int64_t ignore_index, float* dlogits, float* out,
+                                        const float* term_weights, float* total, void* stream) {
+  NKBS_CHECK_ARG(term_weights != nullptr, "nkbs_ray_losses_weighted: null term_weights");
+  return ray_losses_launch(R, S, sdist, w, dw, n_prop, S_prop, sdist_prop, w_prop, dw_prop, rgb, image, drgb, logits,
+                           labels, C, ignore_index, dlogits, out, term_weights, total, stream);
 }

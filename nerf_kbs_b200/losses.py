@@ -41,6 +41,15 @@ def training_losses(weights_list, ray_samples_list, rgb=None, image=None, logits
         rgb=rgb, image=image, logits=logits, labels=labels, ignore_index=ignore_index)
 
 
+def training_loss_total(weights_list, ray_samples_list, rgb, image, term_weights, unit_seed=True):
+    """(total, (mse, interlevel, distortion)): the weighted total as the root of the backward pass, gradients weighted
+    inside the kernel (``ops.ray_loss_total``).  Used by the step driver; the loss dict route stays ``training_losses``."""
+    return ops.ray_loss_total(
+        _w(weights_list[-1]), ray_samples_to_sdist(ray_samples_list[-1]),
+        [_w(w) for w in weights_list[:-1]], [ray_samples_to_sdist(rs) for rs in ray_samples_list[:-1]],
+        rgb, image, term_weights, unit_seed=unit_seed)
+
+
 def pixel_losses(rgb=None, image=None, logits=None, labels=None, ignore_index=-100):
     """Colour MSE and semantic cross-entropy only (evaluation: no weights lists)."""
     mse, _, _, ce = ops.ray_losses(rgb=rgb, image=image, logits=logits, labels=labels, ignore_index=ignore_index)

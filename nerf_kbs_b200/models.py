@@ -16,7 +16,7 @@ from torch import nn
 
 from . import ops
 from .fields import FieldHeadNames, HashMLPDensityField, NerfactoField, SceneContraction
-from .losses import pixel_losses, training_losses
+from .losses import pixel_losses, training_loss_total, training_losses
 from .rays import RayBundle
 from .renderers import NearFarCollider
 from .samplers import ProposalNetworkSampler
@@ -173,6 +173,24 @@ class NerfactoModel(_ModelBase):
         if c.use_semantic:
             loss["semantics_loss"] = c.semantic_loss_weight * ce
         return loss
+
+
+    def get_loss_total(self, outputs, batch):
+        """Step-driver route: (total, loss_dict) with the same terms and multipliers as ``get_loss_dict``
+        (ref:nerfacto.py:483-489) but weighted inside the loss kernel, ``total`` being the root ``backward()`` is
+        called on.  None when the configuration has terms the fused route does not carry (semantics, evaluation)."""
+        c = self.config
+        if not self.training or c.use_semantic:
+            return None
+        total, terms = training_loss_total(outputs["weights_list"], outputs["ray_samples_list"], outputs["rgb"],
+                                           batch["image"], (1.0, c.interlevel_loss_mult, c.distortion_loss_mult))
+        # the dict holds the weighted terms like get_loss_dict does (one launch, for whoever logs them)
+        wv = getattr(self, "_term_weights_dev", None)
+        if wv is None or wv.device != terms.device:
+            wv = self._term_weights_dev = torch.tensor([1.0, c.interlevel_loss_mult, c.distortion_loss_mult],
+                                                       device=terms.device)
+        weighted = terms * wv
+        return total, {"rgb_loss": weighted[0], "interlevel_loss": weighted[1], "distortion_loss": weighted[2]}
 
 
 class SemanticNerfWModel(_ModelBase):

@@ -599,3 +599,47 @@ def ray_losses(w_final=None, sdist_final=None, w_props=(), sdist_props=(), rgb=N
     edges; returns (rgb_mse, interlevel, distortion, cross_entropy)."""
     meta = (sdist_final, list(sdist_props), image, labels, ignore_index, want_distortion)
     return _RayLosses.apply(meta, w_final, rgb, logits, *w_props)
+
+
+class _RayLossTotal(torch.autograd.Function):
+    """Weighted total of the colour / interlevel / distortion terms as the ROOT of the backward pass (step driver).
+
+    The kernel writes every gradient already multiplied by its term's weight (``nkbs_ray_losses_weighted``), so
+    ``total.backward()`` hands them on as they are: no weighting, summing or rescaling launches around the loss.
+    ``unit_seed=True`` is the caller's promise that the incoming gradient of ``total`` is 1 (what ``backward()`` on the
+    scalar itself seeds); with ``unit_seed=False`` the saved gradients are multiplied by whatever arrives."""
+
+    @staticmethod
+    def forward(ctx, meta, w_final, rgb, *w_props):
+        sdist, sdist_props, image, term_weights, unit_seed = meta
+        require_cuda(w_final, rgb, *w_props)
+        R, S = w_final.shape
+        out = torch.zeros(6, device=w_final.device, dtype=torch.float32)  # five terms of the kernel + the total
+        w_final, rgb, image = _c(w_final), _c(rgb), _c(image)
+        w_props = [_c(t) for t in w_props]
+        sdist_props = [_c(t) for t in sdist_props]
+        dw, drgb = torch.empty_like(w_final), torch.empty_like(rgb)
+        dw_props = [torch.empty_like(t) for t in w_props]
+        call("nkbs_ray_losses_weighted", R, S, ptr(_c(sdist)), ptr(w_final), ptr(dw), len(w_props),
+             host_i32([t.shape[1] for t in w_props]), host_ptrs(sdist_props), host_ptrs(w_props), host_ptrs(dw_props),
+             ptr(rgb), ptr(image), ptr(drgb), None, None, 0, 0, None, ptr(out), host_floats(term_weights),
+             out.data_ptr() + 5 * 4, stream())
+        ctx.unit_seed = bool(unit_seed)
+        ctx.save_for_backward(dw, drgb, *dw_props)
+        terms = out[:3]
+        ctx.mark_non_differentiable(terms)
+        return out[5], terms
+
+    @staticmethod
+    def backward(ctx, g_total, _g_terms):
+        dw, drgb, *dw_props = ctx.saved_tensors
+        if not ctx.unit_seed:
+            dw, drgb, dw_props = dw * g_total, drgb * g_total, [t * g_total for t in dw_props]
+        return (None, dw, drgb, *dw_props)
+
+
+def ray_loss_total(w_final, sdist_final, w_props, sdist_props, rgb, image, term_weights, unit_seed=True):
+    """(total, terms[3]) with total = w_rgb * mse + w_inter * interlevel + w_dist * distortion; ``terms`` are the
+    unweighted (mse, interlevel, distortion), not differentiable.  See ``_RayLossTotal`` for ``unit_seed``."""
+    meta = (sdist_final, list(sdist_props), image, tuple(float(v) for v in term_weights), unit_seed)
+    return _RayLossTotal.apply(meta, w_final, rgb, *w_props)

@@ -37,7 +37,7 @@ class Frustums:
 class RaySamples:
     frustums: Frustums
     camera_indices: Optional[torch.Tensor] = None
-    deltas: Optional[torch.Tensor] = None
+    deltas_: Optional[torch.Tensor] = None  # see ``deltas``: materialised on first use (no kernel reads it)
     spacing_starts: Optional[torch.Tensor] = None
     spacing_ends: Optional[torch.Tensor] = None
     spacing_to_euclidean_fn: Optional[Callable] = None
@@ -52,6 +52,18 @@ class RaySamples:
     @property
     def shape(self):
         return self.frustums.shape
+
+    @property
+    def deltas(self) -> Optional[torch.Tensor]:
+        """``ends - starts`` [..., S, 1].  The compositing kernels read the bin edges themselves, so the tensor is only
+        built when somebody asks for it (one launch per level saved on the training step)."""
+        if self.deltas_ is None and self.frustums is not None and self.frustums.starts is not None:
+            self.deltas_ = self.frustums.ends - self.frustums.starts
+        return self.deltas_
+
+    @deltas.setter
+    def deltas(self, value: Optional[torch.Tensor]) -> None:
+        self.deltas_ = value
 
     def get_weights(self, densities: torch.Tensor) -> torch.Tensor:
         """alpha-compositing weights [..., S, 1] (ref:nerfacto.py:399; semantic_nerfw.py:192-193)."""
@@ -94,7 +106,7 @@ class RayBundle:
                       directions=self.directions[:, None, :].expand(R, S, 3),
                       starts=bin_starts, ends=bin_ends, pixel_area=pa,
                       ray_origins=self.origins, ray_directions=self.directions)
-        return RaySamples(frustums=fr, camera_indices=cam, deltas=bin_ends - bin_starts,
+        return RaySamples(frustums=fr, camera_indices=cam, deltas_=None,
                           spacing_starts=spacing_starts, spacing_ends=spacing_ends,
                           spacing_to_euclidean_fn=spacing_to_euclidean_fn, metadata=self.metadata,
                           ray_camera_indices=self.camera_indices[:, 0] if self.camera_indices is not None else None,

@@ -14,11 +14,20 @@ class NearFarCollider(nn.Module):
     def __init__(self, near_plane: float, far_plane: float, **kwargs):
         super().__init__()
         self.near_plane, self.far_plane = near_plane, far_plane
+        self._planes = {}
 
     def set_nears_and_fars(self, ray_bundle: RayBundle) -> RayBundle:
-        ones = torch.ones_like(ray_bundle.origins[..., 0:1])
-        ray_bundle.nears = ones * self.near_plane
-        ray_bundle.fars = ones * self.far_plane
+        # the two [R,1] constants are built once per (rays, device) and handed out read-only afterwards: four launches
+        # fewer on every step (the sampler kernels only read them)
+        o = ray_bundle.origins
+        key = (tuple(o.shape[:-1]), o.device, o.dtype, float(self.near_plane), float(self.far_plane))
+        planes = self._planes.get(key)
+        if planes is None:
+            if len(self._planes) > 8:
+                self._planes.clear()
+            planes = (torch.full_like(o[..., 0:1], self.near_plane), torch.full_like(o[..., 0:1], self.far_plane))
+            self._planes[key] = planes
+        ray_bundle.nears, ray_bundle.fars = planes
         return ray_bundle
 
     def forward(self, ray_bundle: RayBundle) -> RayBundle:

@@ -152,6 +152,12 @@ class ProposalNetworkSampler(nn.Module):
         n = self.num_proposal_network_iterations
         weights, ray_samples = None, None
         updated = self.will_update()
+        if jitter is None and self.training and getattr(self.initial_sampler, "single_jitter", False) \
+                and self.pdf_sampler.single_jitter and getattr(self.initial_sampler, "train_stratified", False) \
+                and self.pdf_sampler.train_stratified:
+            # one launch draws the per-ray jitter of every level (the samplers would draw [R,1] each)
+            dev = ray_bundle.origins.device
+            jitter = torch.rand((n + 1, ray_bundle.origins.shape[0], 1), dtype=torch.float32, device=dev).unbind(0)
         for i_level in range(n + 1):
             is_prop = i_level < n
             num_samples = self.num_proposal_samples_per_ray[i_level] if is_prop else self.num_nerf_samples_per_ray

@@ -67,8 +67,11 @@ class Trainer:
     """One training step of ``model`` (NerfactoModel / SemanticNerfWModel) per call."""
 
     def __init__(self, model, num_rays: int, lr: float = 1e-3, eps: float = 1e-15, betas=(0.9, 0.999),
-                 use_graph: bool = True, process_group=None, graph_warmup: int = 3, seed: Optional[int] = None):
+                 use_graph: bool = True, process_group=None, graph_warmup: int = 3, seed: Optional[int] = None,
+                 fused_loss: Optional[bool] = None):
         self.model = model
+        # weighted total straight out of the loss kernel (models.get_loss_total); NKBS_FUSED_LOSS=0 keeps the loss-dict route
+        self.fused_loss = (os.environ.get("NKBS_FUSED_LOSS", "1") != "0") if fused_loss is None else bool(fused_loss)
         p0 = next(model.parameters())
         if p0.device.type != "cuda":
             raise RuntimeError("nkbs Trainer needs the model on a CUDA device (no CPU fallback)")
@@ -167,8 +170,14 @@ class Trainer:
         batch = {"image": self.buf["image"]}
         if self.needs_labels:
             batch["semantics_label"] = self.buf["semantics_label"]
-        loss_dict = self.model.get_loss_dict(outputs, batch)
-        loss = sum(loss_dict.values())
+        fused = self.model.get_loss_total(outputs, batch) if (self.fused_loss and hasattr(self.model, "get_loss_total")) else None
+        if fused is not None:
+            # the loss kernel weights its own gradients and the total is the root of the backward pass: nothing is
+            # launched between the loss kernel and the first backward kernel except the unit seed
+            loss, loss_dict = fused
+        else:
+            loss_dict = self.model.get_loss_dict(outputs, batch)
+            loss = sum(loss_dict.values())
         loss.backward()
         if self.sharded is not None:
             self.sharded.step()

@@ -75,6 +75,65 @@ def test_graph_step_equals_eager_step():
         assert abs(a - b) <= 2e-4 * abs(a), (losses[False], losses[True])
 
 
+def test_fused_loss_route_equals_loss_dict_route():
+    """The step driver's route (gradients weighted inside the loss kernel, total as the backward root) against the
+    loss-dict route (torch weights, sums and rescales): same losses, same terms, same parameters after the steps."""
+    R = 512
+    rb = O.synthetic_ray_bundle(R, seed=5)
+    batch = {"image": torch.rand(R, 3, generator=torch.Generator().manual_seed(6)).to(DEV)}
+    runs = {}
+    for fused in (False, True):
+        _, nm = _train_pair(R, 0, False)
+        tr = Trainer(nm, R, use_graph=False, fused_loss=fused)
+        torch.cuda.manual_seed(11)
+        ls = []
+        for _ in range(6):
+            ls.append(tr.train_step(to_nk_bundle(rb, DEV), batch).item())
+        runs[fused] = (ls, {k: v.item() for k, v in tr.loss_dict.items()}, nm)
+    for a, b in zip(runs[False][0], runs[True][0]):
+        assert abs(a - b) <= 1e-5 * abs(a), (runs[False][0], runs[True][0])
+    for k in ("rgb_loss", "interlevel_loss", "distortion_loss"):
+        assert abs(runs[False][1][k] - runs[True][1][k]) <= 1e-5 * abs(runs[False][1][k]) + 1e-9, k
+    pa, pb = runs[False][2], runs[True][2]
+    # Adam (eps 1e-15) turns every gradient entry into a step of about lr, so rows whose gradient is rounding noise of
+    # the atomics order move by +-lr in either run (as in test_training_loop_tracks_oracle): loose bar on parameters
+    assert rel_err(pb.field.mlp_base_grid.hash_table, pa.field.mlp_base_grid.hash_table) < 2e-2
+    assert rel_err(pb.proposal_networks[0].encoding.hash_table, pa.proposal_networks[0].encoding.hash_table) < 2e-2
+
+
+def test_weighted_loss_kernel_scales_its_gradients():
+    """nkbs_ray_losses_weighted: gradients = weight x the unweighted kernel's, terms unweighted, total = weighted sum."""
+    from nerf_kbs_b200 import ops
+    g = torch.Generator().manual_seed(0)
+    R, S, Sp = 64, 48, 96
+    def hist(n):
+        e = torch.sort(torch.rand(R, n + 1, generator=g), dim=-1).values
+        w = torch.rand(R, n, generator=g)
+        return (w / w.sum(-1, keepdim=True)).to(DEV).requires_grad_(True), e.to(DEV)
+    w, sd = hist(S)
+    wp, sdp = hist(Sp)
+    rgb = torch.rand(R, 3, generator=g).to(DEV).requires_grad_(True)
+    img = torch.rand(R, 3, generator=g).to(DEV)
+    tw = (1.0, 0.7, 0.002)
+    mse, inter, dist, _ = ops.ray_losses(w_final=w, sdist_final=sd, w_props=[wp], sdist_props=[sdp], rgb=rgb, image=img)
+    (tw[0] * mse + tw[1] * inter + tw[2] * dist).backward()
+    want = [t.grad.clone() for t in (w, wp, rgb)]
+    for t in (w, wp, rgb):
+        t.grad = None
+    total, terms = ops.ray_loss_total(w, sd, [wp], [sdp], rgb, img, tw)
+    total.backward()
+    assert abs(total.item() - (tw[0] * mse + tw[1] * inter + tw[2] * dist).item()) <= 1e-6 * abs(total.item())
+    assert torch.allclose(terms, torch.stack([mse, inter, dist]).detach(), rtol=1e-6, atol=0)
+    for got, ref in zip((w.grad, wp.grad, rgb.grad), want):
+        assert rel_err(got, ref) < 1e-6
+    # a non-unit seed is honoured when the caller says so
+    for t in (w, wp, rgb):
+        t.grad = None
+    total, _ = ops.ray_loss_total(w, sd, [wp], [sdp], rgb, img, tw, unit_seed=False)
+    (3.0 * total).backward()
+    assert rel_err(rgb.grad, 3.0 * want[2]) < 1e-6
+
+
 def test_training_loop_tracks_oracle():
     """Five optimisation steps with injected jitter: losses follow the CPU oracle's Adam loop."""
     R = 256
