@@ -136,6 +136,55 @@ __device__ __forceinline__ float row_total(const float* scratch, int lane) {
   return t;
 }
 
+
+// ---- weight gradients of the H = 16 field on the tensor cores (mma.sync m16n8k8, 3xTF32) ----------------------
+// The weight gradients are sums over samples of outer products, i.e. GEMMs that contract over the 32 samples of a
+// warp: dW1|db1 = GH^T [16 x 32] . [F | 1] [32 x 16]  and  dW2 = RZ^T [16 x 32] . g_out [32 x 1].  Every lane owns one
+// sample (one row of GH, F, RZ), so the operands cross lanes through a per-warp shared-memory tile (row = sample, 20
+// floats: 16-byte rows, conflict-free 128-bit stores) and come back as MMA fragments; the accumulators stay in
+// registers over the whole grid-stride loop.  Each product is split into tf32 high and low parts (hi*hi + hi*lo +
+// lo*hi) so the result keeps fp32 accuracy.  Against the transposed shared-memory sum this moves a quarter of the
+// shared-memory wavefronts per sample.
+#ifndef NKBS_DENSITY_BWD_MMA
+#define NKBS_DENSITY_BWD_MMA 1
+#endif
+constexpr int kTileStride = 20;
+
+__device__ __forceinline__ void split_tf32(float v, uint32_t& hi, uint32_t& lo) {
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(v));
+  const float r = v - __uint_as_float(hi);
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(r));
+}
+
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+// d += A . B with both operands split (three MMAs)
+__device__ __forceinline__ void mma_3xtf32(float (&d)[4], const float (&a)[4], const float (&b)[2]) {
+  uint32_t ah[4], al[4], bh[2], bl[2];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) split_tf32(a[i], ah[i], al[i]);
+#pragma unroll
+  for (int i = 0; i < 2; ++i) split_tf32(b[i], bh[i], bl[i]);
+  mma_tf32(d, al, bh);
+  mma_tf32(d, ah, bl);
+  mma_tf32(d, ah, bh);
+}
+
+// A fragment of the k-step `ks` (samples 8ks .. 8ks+7) from a [32 samples][16] tile read TRANSPOSED (row = column
+// of the tile, contraction index = sample): a0 (g, t), a1 (g+8, t), a2 (g, t+4), a3 (g+8, t+4), g = lane/4, t = lane%4
+__device__ __forceinline__ void load_a_transposed(const float* tile, int ks, int g, int t, float (&a)[4]) {
+  const float* r0 = tile + (8 * ks + t) * kTileStride;
+  const float* r1 = r0 + 4 * kTileStride;
+  a[0] = r0[g];
+  a[1] = r0[g + 8];
+  a[2] = r1[g];
+  a[3] = r1[g + 8];
+}
+
 // resident CTAs per SM the backward is compiled for: the H = 16 field fits three (85 registers per thread)
 template <int H>
 constexpr int bwd_ctas() { return H <= 16 ? NKBS_DENSITY_BWD_CTAS : 1; }
@@ -149,7 +198,10 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
   constexpr int kPasses = (kRows + 31) / 32;
   __shared__ float s_scale[NKBS_MAX_LEVELS];
   __shared__ __align__(16) Smem<H, L> s;
-  __shared__ __align__(16) float s_red[kWarps][32 * kRedStride];
+  constexpr bool kMma = NKBS_DENSITY_BWD_MMA && H == 16 && K + 1 <= 16;
+  // transposed-sum scratch, or (tensor-core route) two [32][kTileStride] operand tiles per warp
+  constexpr int kScratch = kMma ? 2 * 32 * kTileStride : 32 * kRedStride;
+  __shared__ __align__(16) float s_red[kWarps][kScratch];
   __shared__ float s_tot[kPasses * 32];
   if (threadIdx.x < NKBS_MAX_LEVELS) s_scale[threadIdx.x] = a.lv.scale[threadIdx.x];
   for (int e = threadIdx.x; e < kPasses * 32; e += kThreads) s_tot[e] = 0.f;
@@ -161,6 +213,11 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
   float acc[kPasses];
 #pragma unroll
   for (int p = 0; p < kPasses; ++p) acc[p] = 0.f;
+  // tensor-core route: D1 = dW1|db1 as two 16x8 tiles (hidden unit x input column), D2 = dW2 in column 0 of one tile
+  float d1[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+  float d2[4] = {0.f, 0.f, 0.f, 0.f};
+  float db2_acc = 0.f;
+  const int fg = lane >> 2, ft = lane & 3;
   const int64_t n_round = (a.N + 31) / 32 * 32;  // whole warps reach the collectives
   for (int64_t n = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; n < n_round; n += (int64_t)gridDim.x * blockDim.x) {
     const bool live = n < a.N;
@@ -175,18 +232,96 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
     if (!__any_sync(0xffffffffu, g_up != 0.f)) continue;
     float f[K];
     encode_sample<L>(a, s_scale, x, f);
-    float z[H];
+    float z[kMma ? 1 : H];
     float out = s.b2;
-#pragma unroll
-    for (int j = 0; j < H; ++j) {
-      z[j] = hidden_pre<H, L>(s, f, j);
-      out = fmaf(s.w2[j], fmaxf(z[j], 0.f), out);
-    }
-    // trunc_exp backward (A.4): g * exp(clamp(raw, -15, 15))
-    const float g_out = g_up * expf(fminf(fmaxf(out, -15.f), 15.f));
     float df[K];
 #pragma unroll
     for (int i = 0; i < K; ++i) df[i] = 0.f;
+    float g_out;
+    if constexpr (kMma) {
+      // ---- weight gradients on the tensor cores (see mma_3xtf32 above) ----
+      float* tA = red;                       // [32][kTileStride]: relu(z), then GH
+      float* tB = red + 32 * kTileStride;    // [32][kTileStride]: F | 1 | 0
+      float4* rowA = reinterpret_cast<float4*>(tA + lane * kTileStride);
+      float4* rowB = reinterpret_cast<float4*>(tB + lane * kTileStride);
+      uint32_t positive = 0u;  // bit j: hidden unit j is active for this sample
+#pragma unroll
+      for (int q = 0; q < H / 4; ++q) {
+        float r[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int j = 4 * q + i;
+          const float zj = hidden_pre<H, L>(s, f, j);
+          r[i] = fmaxf(zj, 0.f);
+          if (zj > 0.f) positive |= 1u << j;
+          out = fmaf(s.w2[j], r[i], out);
+        }
+        rowA[q] = make_float4(r[0], r[1], r[2], r[3]);
+      }
+      // trunc_exp backward (A.4): g * exp(clamp(raw, -15, 15))
+      g_out = g_up * expf(fminf(fmaxf(out, -15.f), 15.f));
+      __syncwarp();
+      // dW2 = RZ^T . g_out: B carries g_out in column 0 (k = sample), i.e. on the lanes with g == 0
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {
+        float af[4];
+        load_a_transposed(tA, ks, fg, ft, af);
+        const float g0 = __shfl_sync(0xffffffffu, g_out, 8 * ks + ft), g1 = __shfl_sync(0xffffffffu, g_out, 8 * ks + ft + 4);
+        float bf[2] = {fg == 0 ? g0 : 0.f, fg == 0 ? g1 : 0.f};
+        mma_3xtf32(d2, af, bf);
+      }
+      __syncwarp();
+#pragma unroll
+      for (int q = 0; q < H / 4; ++q) {
+        float gq[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int j = 4 * q + i;
+          gq[i] = (positive >> j) & 1u ? g_out * s.w2[j] : 0.f;
+          const float4* w = reinterpret_cast<const float4*>(s.w1 + j * KP);
+#pragma unroll
+          for (int qq = 0; qq < KP / 4; ++qq) {
+            float4 wv = w[qq];
+            if (4 * qq + 0 < K) df[4 * qq + 0 < K ? 4 * qq + 0 : 0] = fmaf(gq[i], wv.x, df[4 * qq + 0 < K ? 4 * qq + 0 : 0]);
+            if (4 * qq + 1 < K) df[4 * qq + 1 < K ? 4 * qq + 1 : 0] = fmaf(gq[i], wv.y, df[4 * qq + 1 < K ? 4 * qq + 1 : 0]);
+            if (4 * qq + 2 < K) df[4 * qq + 2 < K ? 4 * qq + 2 : 0] = fmaf(gq[i], wv.z, df[4 * qq + 2 < K ? 4 * qq + 2 : 0]);
+            if (4 * qq + 3 < K) df[4 * qq + 3 < K ? 4 * qq + 3 : 0] = fmaf(gq[i], wv.w, df[4 * qq + 3 < K ? 4 * qq + 3 : 0]);
+          }
+        }
+        rowA[q] = make_float4(gq[0], gq[1], gq[2], gq[3]);
+        float e[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int c = 4 * q + i;
+          e[i] = c < K ? f[c < K ? c : 0] : (c == K ? 1.f : 0.f);
+        }
+        rowB[q] = make_float4(e[0], e[1], e[2], e[3]);
+      }
+      __syncwarp();
+      // dW1 | db1 = GH^T . [F | 1]
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {
+        float af[4];
+        load_a_transposed(tA, ks, fg, ft, af);
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+          // B (k = sample, n = input column): b0 (t, g), b1 (t+4, g)
+          float bf[2];
+          bf[0] = tB[(8 * ks + ft) * kTileStride + 8 * nt + fg];
+          bf[1] = tB[(8 * ks + ft + 4) * kTileStride + 8 * nt + fg];
+          mma_3xtf32(d1[nt], af, bf);
+        }
+      }
+      __syncwarp();
+      db2_acc += g_out;
+    } else {
+#pragma unroll
+      for (int j = 0; j < H; ++j) {
+        z[j] = hidden_pre<H, L>(s, f, j);
+        out = fmaf(s.w2[j], fmaxf(z[j], 0.f), out);
+      }
+      // trunc_exp backward (A.4): g * exp(clamp(raw, -15, 15))
+      g_out = g_up * expf(fminf(fmaxf(out, -15.f), 15.f));
     // ---- weight gradients: rows are produced unit by unit and summed 32 rows at a time ----
     int row = 0;  // compile-time after unrolling
     int pass = 0;
@@ -222,6 +357,7 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
     __syncwarp();
     acc[kPasses - 1] += row_total(red, lane);
     __syncwarp();
+    }
     // ---- feature gradient -> table gradient ----
 #pragma unroll
     for (int l = 0; l < L; ++l) {
@@ -243,6 +379,24 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
     }
   }
   // ---- warp totals -> CTA totals -> global ----
+  if constexpr (kMma) {
+    // D1 tile nt: d0 (j = g, c = 8nt + 2t), d1 (g, c + 1), d2 (g + 8, c), d3 (g + 8, c + 1); columns c <= K are real
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int j = fg + (i >= 2 ? 8 : 0), c = 8 * nt + 2 * ft + (i & 1);
+        if (c <= K && d1[nt][i] != 0.f) atomicAdd(&s_tot[j * kPerJ + c], d1[nt][i]);
+      }
+    }
+    if (ft == 0) {  // column 0 of D2: dW2[g], dW2[g + 8]
+      if (d2[0] != 0.f) atomicAdd(&s_tot[fg * kPerJ + K + 1], d2[0]);
+      if (d2[2] != 0.f) atomicAdd(&s_tot[(fg + 8) * kPerJ + K + 1], d2[2]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) db2_acc += __shfl_xor_sync(0xffffffffu, db2_acc, o);
+    if (lane == 0 && db2_acc != 0.f) atomicAdd(&s_tot[kRows - 1], db2_acc);
+  }
 #pragma unroll
   for (int p = 0; p < kPasses; ++p)
     if (acc[p] != 0.f) atomicAdd(&s_tot[p * 32 + lane], acc[p]);
