@@ -175,7 +175,12 @@ def test_fused_dp_step_equals_nccl_route():
                         "127.0.0.1", "--master-port", "29577", os.path.join(root, "scripts", "dp_check.py")],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
-    lines = re.findall(r"max\|dp\| = ([0-9.e+-]+) .*rank spread ([0-9.e+-]+)", r.stdout)
+    lines = re.findall(r"max\|dp\| = ([0-9.e+-]+) .*rank spread ([0-9.e+-]+); losses ([0-9.e+-]+) vs ([0-9.e+-]+)", r.stdout)
     assert len(lines) == 2
-    for d, spread in lines:
-        assert float(d) < 2e-3 and float(spread) == 0.0
+    for d, spread, l_fused, l_nccl in lines:
+        # ranks hold bit-identical parameters; the two routes reach the same loss.  Parameters are compared loosely:
+        # Adam (eps 1e-15) moves an entry whose gradient is summation-order noise by about lr per step in either
+        # direction, so after the 8 steps of the script two correct runs differ by up to 8 lr on such entries
+        assert float(spread) == 0.0
+        assert abs(float(l_fused) - float(l_nccl)) <= 1e-5 * abs(float(l_nccl))
+        assert float(d) < 8e-3
