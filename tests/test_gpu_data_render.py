@@ -36,7 +36,10 @@ def test_generate_rays_matches_oracle():
     assert torch.equal(got.camera_indices.cpu(), want.camera_indices)
     assert_close(got.directions, want.directions, 1e-6, "directions")
     assert_close(got.metadata["directions_norm"], want.metadata["directions_norm"], 1e-6, "directions_norm")
-    assert_close(got.pixel_area, want.pixel_area, 1e-4, "pixel_area")
+    # a product of two differences of unit vectors 1/721 apart: one fp32 ulp of a direction component is 6e-8 * 721 =
+    # 4e-5 of a difference, so two correct fp32 evaluations (the host's vector ISA decides the oracle's rounding) differ
+    # by a few 1e-4 of the area; the bar sits above that noise, and the directions themselves are held to 1e-6 above
+    assert_close(got.pixel_area, want.pixel_area, 1e-3, "pixel_area")
     assert float((got.directions.norm(dim=-1) - 1).abs().max()) < 1e-6
 
 
