@@ -1,6 +1,8 @@
 // K1/K2: position front end + multiresolution hash-grid encoding, forward and backward.
 // Replaces nerfstudio HashEncoding.pytorch_fwd and its autograd, reached from
 // ref:nerfacto.py:275-311 and ref:semantic_nerfw.py:102-126.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "encode.cuh"
 
@@ -30,18 +32,20 @@ __global__ void __launch_bounds__(kEncThreads) encode_fwd_kernel(const EncodeArg
   __syncthreads();
   const int L = a.lv.num_levels;
   const uint32_t mask = a.lv.table_mask;
+  // gridDim.y slices of the level range (small batches: more CTAs than one per 256 samples, see level_slices)
+  const int l_begin = (int)((blockIdx.y * L) / gridDim.y), l_end = (int)(((blockIdx.y + 1) * L) / gridDim.y);
   for (int64_t n = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; n < a.N; n += (int64_t)gridDim.x * blockDim.x) {
     float sel;
     float3 x = load_sample_position(a, n, sel);
-    if (a.xn) {
+    if (a.xn && blockIdx.y == 0) {
       a.xn[3 * n] = x.x;
       a.xn[3 * n + 1] = x.y;
       a.xn[3 * n + 2] = x.z;
     }
-    if (a.selector) a.selector[n] = sel;
+    if (a.selector && blockIdx.y == 0) a.selector[n] = sel;
     float2* out = reinterpret_cast<float2*>(a.features + n * (2 * L));
 #pragma unroll 2
-    for (int l = 0; l < L; ++l) {
+    for (int l = l_begin; l < l_end; ++l) {
       Cell cl = nkbs_cell(x, s_scale[l]);
       uint32_t h[8];
       nkbs_corner_hashes(cl, mask, h);
@@ -99,6 +103,7 @@ __global__ void __launch_bounds__(kEncThreads) encode_bwd_kernel(const EncodeBwd
   const int L = a.lv.num_levels;
   const uint32_t mask = a.lv.table_mask;
   const int lane = threadIdx.x & 31;
+  const int l_begin = (int)((blockIdx.y * L) / gridDim.y), l_end = (int)(((blockIdx.y + 1) * L) / gridDim.y);
   // grid-stride over whole warps so that every lane of a warp reaches the collectives
   const int64_t n_round = (a.N + 31) / 32 * 32;
   for (int64_t n = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; n < n_round; n += (int64_t)gridDim.x * blockDim.x) {
@@ -106,7 +111,7 @@ __global__ void __launch_bounds__(kEncThreads) encode_bwd_kernel(const EncodeBwd
     float3 x = make_float3(0.f, 0.f, 0.f);
     if (live) x = make_float3(a.xn[3 * n], a.xn[3 * n + 1], a.xn[3 * n + 2]);
     const float2* g = reinterpret_cast<const float2*>(a.dfeat + (live ? n : 0) * (2 * L));
-    for (int l = 0; l < L; ++l) {
+    for (int l = l_begin; l < l_end; ++l) {
       Cell cl = nkbs_cell(x, s_scale[l]);
       uint32_t h[8];
       nkbs_corner_hashes(cl, mask, h);
@@ -125,6 +130,20 @@ __global__ void __launch_bounds__(kEncThreads) encode_bwd_kernel(const EncodeBwd
       }
     }
   }
+}
+
+// A batch of fewer CTAs than two waves (148 SMs x 8 resident CTAs) leaves SMs idle or unevenly loaded: the level range
+// is then cut into slices along gridDim.y, each CTA looping over L / slices levels of its 256 samples, so that coarse
+// (shuffle-merged) and fine (L2-bound) levels also run side by side.  NKBS_ENCODE_SLICES overrides (1, 2 or 4).
+int level_slices(int64_t blocks, int L) {
+  static const int forced = [] {
+    const char* e = getenv("NKBS_ENCODE_SLICES");
+    return e ? atoi(e) : 0;
+  }();
+  int s = forced > 0 ? forced : (blocks < (int64_t)nkbs_num_sms() * 16 ? 2 : 1);
+  if (s > 4) s = 4;
+  while (s > 1 && L % s != 0) --s;
+  return s;
 }
 
 }  // namespace
@@ -169,10 +188,11 @@ extern "C" int nkbs_encode_fwd(int mode, const float* x, const float* origins, c
   int64_t blocks = (a.N + kEncThreads - 1) / kEncThreads;
   int64_t cap = (int64_t)nkbs_num_sms() * 32;
   int grid = (int)(blocks < cap ? blocks : cap);
+  const dim3 grid2(grid, level_slices(blocks, L));
   if (indices)
-    encode_fwd_kernel<true><<<grid, kEncThreads, 0, (cudaStream_t)stream>>>(a);
+    encode_fwd_kernel<true><<<grid2, kEncThreads, 0, (cudaStream_t)stream>>>(a);
   else
-    encode_fwd_kernel<false><<<grid, kEncThreads, 0, (cudaStream_t)stream>>>(a);
+    encode_fwd_kernel<false><<<grid2, kEncThreads, 0, (cudaStream_t)stream>>>(a);
   NKBS_CHECK_LAUNCH("nkbs_encode_fwd");
   return 0;
 }
@@ -193,7 +213,7 @@ extern "C" int nkbs_encode_bwd(const float* xn, const float* dfeat, int64_t N, c
   int64_t blocks = (N + kEncThreads - 1) / kEncThreads;
   int64_t cap = (int64_t)nkbs_num_sms() * 32;
   int grid = (int)(blocks < cap ? blocks : cap);
-  encode_bwd_kernel<<<grid, kEncThreads, 0, (cudaStream_t)stream>>>(a);
+  encode_bwd_kernel<<<dim3(grid, level_slices(blocks, L)), kEncThreads, 0, (cudaStream_t)stream>>>(a);
   NKBS_CHECK_LAUNCH("nkbs_encode_bwd");
   return 0;
 }
