@@ -134,14 +134,14 @@ __global__ void __launch_bounds__(kEncThreads) encode_bwd_kernel(const EncodeBwd
 
 // A batch of fewer CTAs than two waves (148 SMs x 8 resident CTAs) leaves SMs idle or unevenly loaded: the level range
 // is then cut into slices along gridDim.y, each CTA looping over L / slices levels of its 256 samples, so that coarse
-// (shuffle-merged) and fine (L2-bound) levels also run side by side.  NKBS_ENCODE_SLICES overrides (1, 2 or 4).
+// (shuffle-merged) and fine (L2-bound) levels also run side by side.  NKBS_ENCODE_SLICES overrides (a divisor of L).
 int level_slices(int64_t blocks, int L) {
   static const int forced = [] {
     const char* e = getenv("NKBS_ENCODE_SLICES");
     return e ? atoi(e) : 0;
   }();
-  int s = forced > 0 ? forced : (blocks < (int64_t)nkbs_num_sms() * 16 ? 2 : 1);
-  if (s > 4) s = 4;
+  int s = forced > 0 ? forced : (blocks < (int64_t)nkbs_num_sms() * 16 ? 4 : 1);
+  if (s > L) s = L;
   while (s > 1 && L % s != 0) --s;
   return s;
 }
