@@ -15,7 +15,9 @@ def ray_samples_to_sdist(ray_samples):
 
 
 def _w(weights):
-    return weights[..., 0] if weights.dim() == 3 else weights
+    # squeeze, not [..., 0]: the backward of a select builds a zero tensor and copies the gradient into it (two
+    # launches per level), the backward of a squeeze is a view
+    return weights.squeeze(-1) if (weights.dim() == 3 and weights.shape[-1] == 1) else (weights[..., 0] if weights.dim() == 3 else weights)
 
 
 def interlevel_loss(weights_list, ray_samples_list):

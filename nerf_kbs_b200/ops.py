@@ -520,7 +520,8 @@ def composite(density=None, weights=None, rgb=None, sem=None, starts=None, ends=
     starts / ends is accepted).  Returns dict with weights [R,S,1], rgb [R,3], accumulation [R,1],
     expected_depth [R,1], depth [R,1] (median), semantics [R,C] — those requested and possible."""
     def sq(t):
-        return t[..., 0] if (t is not None and t.dim() == 3 and t.shape[-1] == 1) else t
+        # squeeze (a view in the backward pass too), not a select (zero fill + copy in its backward)
+        return t.squeeze(-1) if (t is not None and t.dim() == 3 and t.shape[-1] == 1) else t
     density, weights, starts, ends = sq(density), sq(weights), sq(starts), sq(ends)
     w, rgb_o, acc, dexp, dmed, sem_o = _Composite.apply(density, weights, rgb, sem, starts, ends, BG_MODES[background],
                                                         eval_mode, sem_weight_grad, frozenset(want))
