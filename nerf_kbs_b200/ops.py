@@ -91,6 +91,8 @@ class _HashEncode(torch.autograd.Function):
     @staticmethod
     def forward(ctx, table, mode, grid, norm, dedup_levels, x, origins, directions, starts, ends, sink=None):
         feats, sel, xn, _ = encode_raw(mode, grid, norm, table, x, origins, directions, starts, ends)
+        # the non-differentiable outputs would otherwise receive materialised zero gradients ([N] and [N,3] fills)
+        ctx.set_materialize_grads(False)
         ctx.sink = sink  # optional pre-registered gradient buffer (dp_optim.ShardedAdam: symmetric memory)
         ctx.grid = grid
         # run merging (segmented shuffle reduction, csrc/encode.cuh) costs a ballot on levels without duplicates and
@@ -105,6 +107,8 @@ class _HashEncode(torch.autograd.Function):
     def backward(ctx, dfeat, _dsel, _dxn):
         (xn,) = ctx.saved_tensors
         g = ctx.grid
+        if dfeat is None:
+            return (None,) * 11
         if ctx.sink is not None:
             dtable = ctx.sink.detach()
             dtable.zero_()
@@ -626,6 +630,7 @@ class _RayLossTotal(torch.autograd.Function):
              ptr(rgb), ptr(image), ptr(drgb), None, None, 0, 0, None, ptr(out), host_floats(term_weights),
              out.data_ptr() + 5 * 4, stream())
         ctx.unit_seed = bool(unit_seed)
+        ctx.set_materialize_grads(False)
         ctx.save_for_backward(dw, drgb, *dw_props)
         terms = out[:3]
         ctx.mark_non_differentiable(terms)
@@ -634,6 +639,8 @@ class _RayLossTotal(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_total, _g_terms):
         dw, drgb, *dw_props = ctx.saved_tensors
+        if g_total is None:
+            return (None,) * (3 + len(dw_props))
         if not ctx.unit_seed:
             dw, drgb, dw_props = dw * g_total, drgb * g_total, [t * g_total for t in dw_props]
         return (None, dw, drgb, *dw_props)
