@@ -298,3 +298,25 @@ def test_c_abi_refuses_bad_arguments_without_a_gpu():
     assert lib.nkbs_version() > 0
     err = lib.nkbs_last_error()
     assert err is None or isinstance(err, (bytes, str))
+
+
+def test_host_ray_containers_keep_the_reference_attributes():
+    """RaySamples.deltas is ends - starts although it is only built on demand; the collider's cached planes carry the
+    configured near / far values for every bundle of the same size (ref: NearFarCollider at nerfacto.py:335)."""
+    import nerf_kbs_b200 as nk
+    R, S = 6, 4
+    edges = torch.linspace(1.0, 3.0, S + 1).repeat(R, 1)
+    rb = nk.RayBundle(torch.zeros(R, 3), torch.ones(R, 3), torch.ones(R, 1), torch.zeros(R, 1, dtype=torch.long))
+    col = nk.NearFarCollider(near_plane=0.001, far_plane=1000.0)
+    rb = col(rb)
+    assert rb.nears.shape == (R, 1) and float(rb.nears[0, 0]) == pytest.approx(0.001) and float(rb.fars[-1, 0]) == 1000.0
+    rb2 = col(nk.RayBundle(torch.ones(R, 3), torch.ones(R, 3), torch.ones(R, 1), torch.zeros(R, 1, dtype=torch.long)))
+    assert torch.equal(rb2.nears, rb.nears) and torch.equal(rb2.fars, rb.fars)
+    rb3 = col(nk.RayBundle(torch.ones(2 * R, 3), torch.ones(2 * R, 3)))
+    assert rb3.nears.shape == (2 * R, 1)
+    rs = rb.samples_from_bins(edges / 3.0, edges)
+    assert rs.deltas_ is None                                   # nothing built yet
+    assert rs.deltas.shape == (R, S, 1) and torch.allclose(rs.deltas, torch.full((R, S, 1), 0.5))
+    assert rs.frustums.starts.shape == (R, S, 1) and rs.spacing_bins.shape == (R, S + 1)
+    rs.deltas = torch.zeros(R, S, 1)
+    assert float(rs.deltas.abs().sum()) == 0.0
