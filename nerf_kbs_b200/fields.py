@@ -289,9 +289,11 @@ class NerfactoField(_Field):
     def get_density(self, ray_samples: RaySamples):
         feats, sel = self._encode(ray_samples, self.mlp_base_grid, self._norm)
         W, b = self.mlp_base_mlp.weights_biases()
-        h = ops.mlp(feats, W, b, self.mlp_base_mlp.relu_mask, ops.ACT_DENSITY, selector=sel)
+        h, d0 = ops.mlp(feats, W, b, self.mlp_base_mlp.relu_mask, ops.ACT_DENSITY, selector=sel, col0=True)
         h3 = h.reshape(*ray_samples.frustums.shape, -1)
-        density, base_mlp_out = torch.split(h3, [1, self.geo_feat_dim], dim=-1)
+        # torch.split(h3, [1, geo]) of the reference, without a split node in the backward pass (ops._Mlp, col0)
+        density = d0.reshape(*ray_samples.frustums.shape, 1)
+        base_mlp_out = h3[..., 1:]
         # the head kernels read the geometry columns of the base MLP's output in place (no slice copy)
         base_mlp_out._nkbs_src = (h, 1)
         return density, base_mlp_out

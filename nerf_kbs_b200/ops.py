@@ -228,12 +228,13 @@ def get_mlp_precision() -> str:
 
 class _Mlp(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, selector, relu_mask, out_act, *params):
+    def forward(ctx, x, selector, relu_mask, out_act, col0, *params):
         nl = len(params) // 2
         Ws = [_c(p) for p in params[0::2]]
         bs = [_c(p) for p in params[1::2]]
         x = _c(x)
         require_cuda(x, *Ws)
+        ctx.set_materialize_grads(False)
         dims = [Ws[0].shape[1]] + [w.shape[0] for w in Ws]
         N = x.shape[0]
         y = torch.empty((N, dims[-1]), device=x.device, dtype=torch.float32)
@@ -246,15 +247,28 @@ class _Mlp(torch.autograd.Function):
                  ptr(selector), ptr(y), stream())
         ctx.cfg = (nl, dims, relu_mask, out_act, tc, _MLP_CFG["bwd_fmt"])
         ctx.save_for_backward(x, selector, *Ws, *bs)
+        if col0:
+            # column 0 also leaves as its own contiguous output (the density of the base MLP): its gradient comes back
+            # to THIS node and is added into column 0 of dy, instead of a split node that zero-fills, concatenates and
+            # adds three [N,16] tensors
+            return y, y[:, 0].contiguous()
         return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, dy0=None):
         nl, dims, relu_mask, out_act, tc, bwd_fmt = ctx.cfg
         saved = ctx.saved_tensors
         x, selector = saved[0], saved[1]
         Ws, bs = list(saved[2:2 + nl]), list(saved[2 + nl:2 + 2 * nl])
+        if dy is None and dy0 is None:
+            return (None,) * (5 + 2 * nl)
+        if dy is None:
+            dy = torch.zeros((x.shape[0], dims[-1]), device=x.device, dtype=torch.float32)
         dy = _c(dy)
+        if dy0 is not None:
+            if dy._base is not None:  # never write into somebody else's storage
+                dy = dy.clone()
+            dy[:, 0] += dy0.reshape(-1)
         N = x.shape[0]
         dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
         zs = _zeros_like_many(Ws + bs)
@@ -268,16 +282,17 @@ class _Mlp(torch.autograd.Function):
         grads = []
         for w, b in zip(dWs, dbs):
             grads += [w, b]
-        return (dx, None, None, None, *grads)
+        return (dx, None, None, None, None, *grads)
 
 
 def mlp(x, weights: Sequence[torch.Tensor], biases: Sequence[torch.Tensor], relu_mask: int, out_act: int = ACT_NONE,
-        selector: Optional[torch.Tensor] = None):
-    """y = MLP(x) with up to three nn.Linear layers; x [N,K0] -> y [N,Kn]."""
+        selector: Optional[torch.Tensor] = None, col0: bool = False):
+    """y = MLP(x) with up to three nn.Linear layers; x [N,K0] -> y [N,Kn].  ``col0=True`` returns (y, y[:, 0] as a
+    contiguous [N] tensor) from one autograd node."""
     params = []
     for w, b in zip(weights, biases):
         params += [w, b]
-    return _Mlp.apply(x, selector, relu_mask, out_act, *params)
+    return _Mlp.apply(x, selector, relu_mask, out_act, bool(col0), *params)
 
 
 # ----------------------------------------------------------------------------------------------
