@@ -7,7 +7,15 @@
 A step = one training iteration over one synthetic ray batch: proposal sampling (256/96) + 48 final
 samples, field, compositing, losses, backward, Adam (ref:train.py:42-101).  Prints ONE JSON line.
 For N > 1 launch under torchrun: one rank per GPU, every rank steps its own batch of the same size
-(weak scaling), gradients are all-reduced over NCCL before Adam.
+(weak scaling); the gradient exchange is fused with Adam in one kernel over NVLink peer (symmetric)
+memory (reduce-scatter + Adam + all-gather, nkbs_dp_adam_step) and NCCL only carries barriers and the
+timing reduce (NKBS_DP_FUSED=0 selects an NCCL allreduce + local Adam instead).
+
+The headline `value` stays on BASELINE.json configs[1] (4096 rays per GPU).  The same JSON line carries
+sub-legs for the other configurations: `cfg3` (configs[2]: semantic-NeRF-W, 8192 motion-masked rays with ray
+generation and mask compaction inside the timed region), `render` (configs[3]: full 1242x375 frame),
+`cfg5` (configs[4]: the nerfacto step at 65 536 rays per GPU at this run's N), and for N > 1 `dp_check`
+(fused exchange vs the NCCL route, outside the timed regions).
 """
 from __future__ import annotations
 
@@ -29,6 +37,20 @@ METRIC = "train_rays_per_sec"
 UNIT = "rays/s"
 SAMPLES = (256, 96, 48)
 L2_BYTES = 126 * 2**20
+L2_BYTES_PER_CYCLE = 6300  # whole-chip L2 (LTS) throughput cap, /opt/skills/guides/B300_MICROARCH.md
+# Kernels whose tables are cache-resident are reported against L2 throughput, not HBM: the proposal grids are 5-16 MiB
+# (L1/L2 hits, ncu: DRAM 2 %), and the gradient scatter of the main table is bound by L2 reductions (ncu:
+# lts__throughput 67 %, DRAM 10 %).  The main-grid gather (64 MiB table evicted by the 540 MB optimizer stream of
+# every step) and everything ray-major stay HBM kernels.
+L2_BOUND = {"nkbs_density_fwd", "nkbs_density_bwd", "nkbs_encode_bwd"}
+BOUND_NOTE = {"l2": "table traffic of this kernel is served by L1/L2 (tables of 5-64 MiB against a 126 MiB L2): achieved = "
+                    "algorithmic gather/scatter bytes per second against the L2 throughput cap, not HBM",
+              "hbm": "achieved = algorithmic bytes per second against the measured HBM copy bandwidth",
+              "tensor": "achieved = 2 (fwd) or 4 (bwd) x MAC flops per second against the sustained cuBLAS bf16 rate"}
+
+
+def kernel_bound(name, kind):
+    return "l2" if name in L2_BOUND else kind
 
 
 def parse_args():
@@ -46,6 +68,8 @@ def parse_args():
     ap.add_argument("--pool", type=int, default=8, help="distinct ray batches cycled through")
     ap.add_argument("--no-render", action="store_true", help="skip the full-frame render leg (BASELINE configs[3])")
     ap.add_argument("--render-frames", type=int, default=10)
+    ap.add_argument("--no-legs", action="store_true", help="skip the cfg3 / cfg5 sub-legs and the dp_check")
+    ap.add_argument("--leg-steps", type=int, default=0, help="timed steps of the cfg3 / cfg5 legs (default: min(--steps, 30))")
     return ap.parse_args()
 
 
@@ -55,6 +79,19 @@ def workload_name(args):
                 "MSE+interlevel+distortion losses, Adam lr 1e-3 eps 1e-15")
     return (f"semantic_nerfw training step (semantic + transient heads), {args.rays} rays/GPU, 8-level 2^18 proposal "
             "grids, proposal 256/96 + 48 samples, Adam lr 1e-3 eps 1e-15")
+
+
+PARAM_WORDS = 16 * (1 << 19) * 2 + 2 * 5 * (1 << 17) * 2 + 21000  # nerfacto defaults: tables + MLPs + embedding
+
+
+def bench_config(args, world):
+    """The `config` object of the JSON line — the same for this repo's arm and for `--impl reference` (the driver
+    compares them): what one step is, not how an arm executes it."""
+    ws = PARAM_WORDS * 4 * 4 / 2**20  # parameters + gradients + two Adam moments
+    return {"workload": workload_name(args), "rays_per_gpu": args.rays, "global_rays_per_step": world * args.rays,
+            "samples_per_ray": list(SAMPLES), "parallelism": f"dp{world}", "collective": _collective(world),
+            "l2": f"no flush: the step's working set (parameters + gradients + Adam moments = {ws:.0f} MiB, all streamed "
+                  f"every step) exceeds the {L2_BYTES // 2**20} MiB L2; {args.pool} distinct ray batches rotate"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -180,7 +217,8 @@ def kernel_work(name, a):
         N, w = a[0], a[2] + a[3] + a[4]
         return "hbm", N * 4 * (w + a[3])
     if name == "nkbs_adam_step":
-        return "hbm", 7 * 4 * sum(list(a[5])[:a[0]])
+        # p, g, m, v read; p, m, v written; + g re-zeroed when the step driver asks for it
+        return "hbm", (7 + (1 if a[13] else 0)) * 4 * sum(list(a[5])[:a[0]])
     if name in ("nkbs_density_fwd", "nkbs_density_bwd"):
         # fused proposal field: bin edges in, 8 corner rows of F=2 floats per level gathered, density out;
         # bwd additionally reads d(density) and scatters the same 8*L rows once each
@@ -325,8 +363,9 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(args), "rays_per_step_sampled": r["rays_per_step"]},
-            "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+            "config": bench_config(args, int(os.environ.get("WORLD_SIZE", "1"))),
+            "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"],
+                             "rays_per_step_sampled": r["rays_per_step"]},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
@@ -393,14 +432,175 @@ def render_run(dev, frames, warmup, rank=0, world=1, chunk=1 << 16):
 
 
 def _finish(dist):
-    """Leave a multi-rank run: final barrier, then exit without tearing NCCL down (destroy_process_group was seen
-    to hang on a communicator that captured CUDA graphs still reference)."""
+    """Leave a multi-rank run: every Trainer has dropped its captured graphs (Trainer.close: a graph that captured a
+    collective keeps the communicator busy and destroy_process_group then waits forever), final barrier, NCCL torn
+    down properly.  A watchdog turns a teardown that still does not return within 30 s into a plain exit, so a hung
+    destroy can never cost the run its (already printed) result."""
+    import gc
+    import threading
     import torch
+    gc.collect()
     dist.barrier()
     torch.cuda.synchronize()
     sys.stdout.flush()
     sys.stderr.flush()
-    os._exit(0)
+    dog = threading.Timer(30.0, lambda: os._exit(0))
+    dog.daemon = True
+    dog.start()
+    dist.destroy_process_group()
+    dog.cancel()
+
+
+
+COLLECTIVE = ("symmetric-memory reduce-scatter + Adam + all-gather in one kernel over NVLink peer memory "
+              "(nkbs_dp_adam_step); NCCL: barriers and the timing reduce only")
+
+
+def _collective(world):
+    if world == 1:
+        return "none (1 GPU)"
+    if os.environ.get("NKBS_DP_FUSED", "1") == "0":
+        return "NCCL sum-allreduce of the flat gradient slice per parameter group, then local Adam (NKBS_DP_FUSED=0)"
+    return COLLECTIVE
+
+
+def _max_over_ranks(ms, dev, world):
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t.item()
+
+
+def _barrier(world):
+    import torch
+    import torch.distributed as dist
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def timed_steps(step_fn, steps, dev, world):
+    """K calls of step_fn(i) between two CUDA events, barrier + synchronize on both sides, max over ranks (ms)."""
+    import torch
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    _barrier(world)
+    e0.record()
+    for i in range(steps):
+        step_fn(i)
+    e1.record()
+    _barrier(world)
+    return _max_over_ranks(e0.elapsed_time(e1), dev, world)
+
+
+def cfg5_leg(args, dev, rank, world, steps, warmup, n1_value=None):
+    """BASELINE configs[4]: the nerfacto training step at 65 536 rays per GPU, data parallel over this run's N GPUs."""
+    import torch
+    import nerf_kbs_b200 as nk
+    from nerf_kbs_b200.rays import RayBundle
+    from nerf_kbs_b200.trainer import Trainer
+    R = 65536
+    torch.manual_seed(0)
+    model = nk.NerfactoModel(nk.ModelConfig()).to(dev).train()
+    torch.cuda.manual_seed(4321 + rank)
+    host = make_batches(4, R, 300 + rank, False, pin=True)
+    devb = [{k: v.to(dev) for k, v in b.items()} for b in host]
+    tr = Trainer(model, R)
+    bundle = lambda b: RayBundle(b["origins"], b["directions"], b["pixel_area"], b["camera_indices"])
+    tr.load_batch(bundle(devb[0]), devb[0])
+    tr.prepare()
+    for i in range(max(warmup, 3)):
+        tr.train_step(bundle(devb[i % 4]), devb[i % 4])
+    c0 = tr.nkbs_calls
+    ms = timed_steps(lambda i: tr.train_step(bundle(devb[i % 4]), devb[i % 4]), steps, dev, world)
+    launches = tr.nkbs_calls - c0
+    for i in range(3):
+        tr.train_step_host(bundle(host[i % 4]), host[i % 4])
+    ms_e2e = timed_steps(lambda i: tr.train_step_host(bundle(host[i % 4]), host[i % 4]), steps, dev, world)
+    final_loss = float(tr.loss_dict["loss"])
+    tr.close()
+    return {"metric": METRIC, "unit": UNIT, "workload": "nerfacto training step, 65536 rays/GPU (BASELINE configs[4])",
+            "rays_per_gpu": R, "n_gpus": world, "steps": steps, "value": world * R * steps / (ms * 1e-3),
+            "ms_per_step": ms / steps, "scaling": "weak", "collective": _collective(world), "gpu_launches": launches,
+            "e2e": {"value": world * R * steps / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e / steps,
+                    "h2d_bytes_per_step": tr.h2d_bytes() + 4, "d2h_bytes_per_step": 4},
+            "final_loss": final_loss}
+
+
+def cfg3_leg(args, dev, rank, world, steps, warmup):
+    """BASELINE configs[2]: semantic-NeRF-W training step with semantic + transient heads on 8192 MOTION-MASKED rays.
+    Every step draws candidate pixels, keeps those whose motion mask is non-zero (Bernoulli keep 0.8; nonzero = keep,
+    ref:dataparser/dataset_z.py:186-191,226-232), compacts them to exactly 8192 (nkbs_compact_masked), generates the
+    pinhole rays on the device (nkbs_generate_rays), gathers colour and label targets and runs the step — all inside
+    the timed region.  e2e: the candidate list comes from pinned host memory, the loss goes back."""
+    import torch
+    import nerf_kbs_b200 as nk
+    from nerf_kbs_b200 import data as D
+    from nerf_kbs_b200.trainer import Trainer
+    R, n_img, H, W = 8192, 8, KITTI_H, KITTI_W
+    M = int(R * 1.5)
+    torch.manual_seed(0)
+    model = nk.SemanticNerfWModel(nk.ModelConfig(use_semantic=True, use_transient_embedding=True, num_images=n_img)).to(dev).train()
+    torch.cuda.manual_seed(999 + rank)
+    g = torch.Generator().manual_seed(500 + rank)
+    c2w = torch.eye(4)[:3].repeat(n_img, 1, 1)
+    c2w[:, 2, 3] = torch.linspace(-0.4, 0.4, n_img)
+    f = torch.full((n_img,), 721.5)
+    cams = nk.Cameras(c2w, f, f.clone(), torch.full((n_img,), 621.0), torch.full((n_img,), 187.5), H, W)
+    gen = nk.RayGenerator(cams).to(dev)
+    images = torch.rand(n_img, H * W, 3, generator=g).to(dev)
+    labels = torch.randint(0, 19, (n_img, H * W), generator=g).to(dev)
+    masks = (torch.rand(n_img, H * W, generator=g) < 0.8).to(torch.uint8).to(dev)
+    pool = 8
+    cand_host = [torch.stack([torch.randint(0, n_img, (M,), generator=g), torch.randint(0, H * W, (M,), generator=g)], 0).pin_memory()
+                 for _ in range(pool)]
+    cand_dev = [c.to(dev) for c in cand_host]
+    stage = torch.empty(2, M, dtype=torch.int64, device=dev)
+    tr = Trainer(model, R)
+    kept_min = torch.full((1,), 1 << 30, device=dev, dtype=torch.int32)
+
+    def step(cand):
+        img_i, pix_i, kept = D.compact_masked(cand[0], cand[1], masks, R)
+        torch.minimum(kept_min, kept, out=kept_min)
+        idx = torch.stack([img_i, pix_i // W, pix_i % W], dim=-1)
+        rb = gen(idx)
+        batch = {"image": images[img_i, pix_i], "semantics_label": labels[img_i, pix_i]}
+        return tr.train_step(rb, batch)
+
+    step(cand_dev[0])
+    tr.prepare()
+    for i in range(max(warmup, 3)):
+        step(cand_dev[i % pool])
+    c0 = tr.nkbs_calls
+    d0 = sum(nk._lib.call_counts.get(k, 0) for k in ("nkbs_compact_masked", "nkbs_generate_rays"))
+    ms = timed_steps(lambda i: step(cand_dev[i % pool]), steps, dev, world)
+    launches = tr.nkbs_calls - c0 + sum(nk._lib.call_counts.get(k, 0) for k in ("nkbs_compact_masked", "nkbs_generate_rays")) - d0
+
+    loss_host = torch.zeros((), pin_memory=True)
+
+    def step_host(i):
+        stage.copy_(cand_host[i % pool], non_blocking=True)
+        loss = step(stage)
+        loss_host.copy_(loss, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    for i in range(3):
+        step_host(i)
+    ms_e2e = timed_steps(step_host, steps, dev, world)
+    final_loss = float(tr.loss_dict["loss"])
+    kept = int(kept_min.item())
+    tr.close()
+    return {"metric": METRIC, "unit": UNIT,
+            "workload": "semantic_nerfw training step (semantic + transient heads), 8192 motion-masked rays/GPU "
+                        "(Bernoulli keep 0.8, candidates compacted and rays generated on the device inside the timed "
+                        "region), 8-level 2^18 hidden-64 proposal fields (BASELINE configs[2])",
+            "rays_per_gpu": R, "candidates_per_step": M, "min_kept_candidates": kept, "n_gpus": world, "steps": steps,
+            "value": world * R * steps / (ms * 1e-3), "ms_per_step": ms / steps, "scaling": "weak",
+            "collective": _collective(world), "gpu_launches": launches,
+            "e2e": {"value": world * R * steps / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e / steps,
+                    "h2d_bytes_per_step": stage.numel() * 8, "d2h_bytes_per_step": 4},
+            "final_loss": final_loss}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -501,11 +701,6 @@ def run_nkbs(args):
         render = render_run(dev, args.render_frames, 2, rank, world)
         devb = [{k: v.to(dev) for k, v in b.items()} for b in host]
 
-    if rank != 0:
-        if world > 1:
-            _finish(dist)
-        return
-
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -514,6 +709,10 @@ def run_nkbs(args):
         peak_src = "fallback (B200_PROFILING.md)"
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     tc_peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
+    clk = clocks.summary()
+    # L2: ~6300 B/cycle over the whole chip (B300_MICROARCH.md "LTS throughput cap") at the SM clock seen in this run
+    l2_peak = L2_BYTES_PER_CYCLE * float(clk.get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)) * 1e6 / 1e9
+    PEAK = {"hbm": hbm_peak, "l2": l2_peak, "tensor": tc_peak}
 
     # (3) per-kernel device time (eager pass, CUDA events on the launching stream) -> dominant kernel roofline
     roofline, kernels, launches_per_step = None, {}, None
@@ -525,19 +724,54 @@ def run_nkbs(args):
         tot = sum(d["ms"] for d in agg.values())
         for name, d in sorted(agg.items(), key=lambda kv: -kv[1]["ms"]):
             per = d["ms"] / d["launches"]
-            ach = d["work"] / d["launches"] / (per * 1e-3) / (1e9 if d["kind"] == "hbm" else 1e12)
+            bound = kernel_bound(name, d["kind"])
+            ach = d["work"] / d["launches"] / (per * 1e-3) / (1e12 if bound == "tensor" else 1e9)
             kernels[name] = {"ms_per_step": round(d["ms"] / nsteps, 4), "launches_per_step": d["launches"] / nsteps,
-                             "share": round(d["ms"] / tot, 4), "bound": d["kind"],
-                             "achieved": round(ach, 2), "unit": "GB/s" if d["kind"] == "hbm" else "TFLOP/s"}
+                             "launch_ms": round(per, 4), "share": round(d["ms"] / tot, 4), "bound": bound,
+                             "achieved": round(ach, 2), "unit": "TFLOP/s" if bound == "tensor" else "GB/s",
+                             "peak": round(PEAK[bound], 1), "frac": round(ach / PEAK[bound], 4)}
         top = next(iter(kernels))
         k = kernels[top]
-        peak = hbm_peak if k["bound"] == "hbm" else tc_peak
-        roofline = {"kernel": top, "bound": k["bound"], "achieved": k["achieved"], "peak": peak, "unit": k["unit"],
-                    "frac": round(k["achieved"] / peak, 4), "traffic": ncu_traffic(top, R),
+        roofline = {"kernel": top, "bound": k["bound"], "achieved": k["achieved"], "peak": k["peak"], "unit": k["unit"],
+                    "frac": k["frac"], "traffic": ncu_traffic(top, R),
                     "traffic_note": "DRAM bytes per launch from profiles/*_top_kernels_ncu_full.csv (ncu --set full, same step)",
-                    "peak_source": peak_src,
-                    "launch_ms": round(k["ms_per_step"] / k["launches_per_step"], 4),
-                    "share_of_nkbs_kernel_time": k["share"], "eager_ms_per_step": round(eager_ms, 3)}
+                    "peak_source": peak_src if k["bound"] != "l2" else
+                    f"L2: {L2_BYTES_PER_CYCLE} B/cycle (B300_MICROARCH.md) x {l2_peak / L2_BYTES_PER_CYCLE * 1e3:.0f} MHz SM clock of this run",
+                    "bound_note": BOUND_NOTE.get(k["bound"], ""),
+                    "launch_ms": k["launch_ms"], "share_of_nkbs_kernel_time": k["share"],
+                    "eager_ms_per_step": round(eager_ms, 3)}
+    if render is not None:
+        # forward-only traffic of a rendered ray: hash-grid gathers 161 792 B + PDF 3408 B + compositing
+        # 5092 B; the proposal tables stay in L1/L2, the 64 MiB main table is re-read from HBM by every 65 536-ray chunk
+        per_ray = 161792 + 2440 + 968 + 5092
+        ach = per_ray * render["value"] / 1e9
+        render["roofline"] = {"bound": "hbm", "achieved": round(ach, 1), "peak": hbm_peak, "unit": "GB/s",
+                              "frac": round(ach / hbm_peak, 4), "traffic": None,
+                              "note": "whole render leg (all kernels of a frame), algorithmic gather + sampler + compositing "
+                                      "bytes per ray x rays/s; the MLPs' tensor work (1.22 MFLOP/ray) is not counted"}
+
+    # (2c) the other BASELINE configurations as sub-legs, and the data-parallel correctness check (every rank)
+    legs = {}
+    if not args.no_legs and args.model == "nerfacto" and R == 4096:
+        tr.close()
+        del devb
+        tr = None
+        torch.cuda.empty_cache()
+        leg_steps = args.leg_steps or min(args.steps, 30)
+        legs["cfg3"] = cfg3_leg(args, dev, rank, world, leg_steps, 5)
+        torch.cuda.empty_cache()
+        legs["cfg5"] = cfg5_leg(args, dev, rank, world, leg_steps, 5)
+        torch.cuda.empty_cache()
+        if world > 1:
+            from nerf_kbs_b200.dp_check import run_dp_check
+            legs["dp_check"] = run_dp_check(dev, rank, world, rays=1024, steps=8, graph=True)
+
+    if tr is not None:
+        tr.close()
+    if rank != 0:
+        if world > 1:
+            _finish(dist)
+        return
 
     # (4) the CPU torch path on this box's host cores, bounded sample
     cpu = None
@@ -545,20 +779,19 @@ def run_nkbs(args):
         r = cpu_reference_run(args, steps=2, warmup=1, budget_s=45.0)
         cpu = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]}
 
-    working_set = sum(p.numel() * 4 for p in model.parameters()) * 4  # params + grads + 2 Adam moments
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": W,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f16/bf16 tensor-core MLPs (fp32 accumulate), f32 elsewhere" if not args.fp32_mlp else "f32",
         "data": "synthetic",
-        "config": {"workload": workload_name(args), "rays_per_gpu": R, "global_rays_per_step": world * R,
-                   "samples_per_ray": list(SAMPLES), "parallelism": f"dp{world}", "cuda_graph": not args.no_graph,
-                   "l2": f"no flush: the step's working set (parameters + gradients + Adam moments = {working_set / 2**20:.0f} MiB, "
-                         f"all streamed every step) exceeds the {L2_BYTES // 2**20} MiB L2; {args.pool} distinct ray batches rotate"},
+        "config": bench_config(args, world),
+        "execution": {"cuda_graph": not args.no_graph, "collective": _collective(world),
+                      "mlp": "fp32 CUDA cores" if args.fp32_mlp else "tcgen05 (fp16 forward / bf16 backward operands, fp32 accumulate)"},
         "e2e": e2e, "gpu_launches": nk_launches, "nkbs_entry_calls_per_step": launches_per_step,
-        "roofline": roofline, "cpu_baseline": cpu, "render": render, "clocks": clocks.summary(), "kernels": kernels,
+        "roofline": roofline, "cpu_baseline": cpu, "render": render, "clocks": clk, "kernels": kernels,
         "final_loss": final_loss,
     }
+    line.update(legs)
     if saved_stdout is not None:
         sys.stdout.flush()
         os.dup2(saved_stdout, 1)

@@ -206,11 +206,13 @@ int nkbs_composite_bwd(int64_t R, int32_t S, const float* density, const float* 
  * params/grads/exp_avg/exp_avg_sq: HOST arrays of num_tensors DEVICE pointers; numel: HOST.
  * step_dev: device scalar, the step count t >= 1 as float (bias corrections 1-beta^t are computed on the
  * device so a captured CUDA graph sees a new t every replay).  inv_scale_dev: optional device scalar
- * multiplied into every gradient (GradScaler unscale). */
-int nkbs_adam_step(int32_t num_tensors, float* const* params, const float* const* grads,
+ * multiplied into every gradient (1/world after a sum-allreduce; a GradScaler's unscale).  zero_grads != 0: every
+ * gradient element is overwritten with 0 after it has been read, so the backward kernels of the next step can
+ * accumulate into the same buffers without a separate fill pass. */
+int nkbs_adam_step(int32_t num_tensors, float* const* params, float* const* grads,
                    float* const* exp_avg, float* const* exp_avg_sq, const int64_t* numel, float lr,
                    float beta1, float beta2, float eps, float weight_decay, const float* step_dev,
-                   const float* inv_scale_dev, void* stream);
+                   const float* inv_scale_dev, int32_t zero_grads, void* stream);
 
 /* N2 (data parallel) — reduce-scatter + Adam + all-gather in one kernel over NVLink peer memory.  grad_peers /
  * param_peers: HOST arrays of `world` DEVICE pointers to the flat gradient / parameter buffer of every rank
@@ -221,6 +223,25 @@ int nkbs_adam_step(int32_t num_tensors, float* const* params, const float* const
 int nkbs_dp_adam_step(int32_t world, int32_t rank, const float* const* grad_peers, float* const* param_peers,
                       int64_t lo, int64_t n, float* exp_avg, float* exp_avg_sq, float lr, float beta1, float beta2,
                       float eps, float weight_decay, const float* step_dev, void* stream);
+
+/* N4 — scalar colour maps of the rendered frame.  lut: DEVICE float [256,3] colour table (the caller's data:
+ * matplotlib's "viridis" / "turbo" tables in nerfstudio).  apply_colormap: image [N] in [0,1] -> rgb [N,3] =
+ * lut[(long)(image * 255)].  apply_depth_colormap: depth [N] normalised by (near, far) — each either given
+ * (have_* != 0) or the minimum / maximum of `depth` itself, reduced on the device into minmax_ws (2 x int32) —
+ * as clip((d - near) / (far - near + 1e-10), 0, 1), mapped through lut, and with accumulation [N] (may be NULL)
+ * blended over white: colour * acc + (1 - acc).
+ * replaces: nerfstudio utils.colormaps.apply_colormap / apply_depth_colormap (nerfacto.py:574-578,608-613;
+ *           semantic_nerfw.py:305). */
+int nkbs_apply_colormap(int64_t N, const float* image, const float* lut, float* rgb, void* stream);
+int nkbs_apply_depth_colormap(int64_t N, const float* depth, const float* accumulation, const float* lut,
+                              int32_t have_near, float near_plane, int32_t have_far, float far_plane,
+                              int32_t* minmax_ws, float* rgb, void* stream);
+
+/* Zero `bytes` bytes of device memory on `stream` (cudaMemsetAsync: a memset node inside a captured CUDA graph).
+ * Used for gradient buffers that cannot be re-zeroed by the optimizer kernel that reads them (peers still read
+ * them over NVLink until the closing barrier of nkbs_dp_adam_step).
+ * replaces: optimizer.zero_grad() of the nerfstudio Trainer loop (train.py:85-98 optimizers). */
+int nkbs_zero_async(void* dev_ptr, int64_t bytes, void* stream);
 
 #ifdef __cplusplus
 }

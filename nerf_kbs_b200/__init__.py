@@ -2,6 +2,7 @@
 (see DESIGN.md).  Importing the package does not need a GPU; calling an operator does."""
 from .fields import (FieldHeadNames, HashEncoding, HashMLPDensityField, MLP, NerfactoField,  # noqa: F401
                      SceneContraction)
+from .colormaps import apply_colormap, apply_depth_colormap, colormap_table  # noqa: F401
 from .data import Cameras, RayGenerator, SemanticPalette, image_ray_indices, sample_masked_pixels  # noqa: F401
 from .models import ModelConfig, NerfactoModel, SemanticNerfWModel  # noqa: F401
 from .rays import Frustums, RayBundle, RaySamples  # noqa: F401

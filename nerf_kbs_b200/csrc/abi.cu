@@ -3,7 +3,7 @@
 #include <string.h>
 #include "common.cuh"
 
-#define NKBS_VERSION 100
+#define NKBS_VERSION 200
 
 static thread_local char g_err[512] = "";
 
@@ -30,3 +30,12 @@ int nkbs_num_sms() {
 
 extern "C" int nkbs_version(void) { return NKBS_VERSION; }
 extern "C" const char* nkbs_last_error(void) { return g_err; }
+
+// memset node on the caller's stream (a CUDA-graph memset node when captured, not a kernel launch)
+extern "C" int nkbs_zero_async(void* dev_ptr, int64_t bytes, void* stream) {
+  NKBS_CHECK_ARG(bytes >= 0 && (dev_ptr || bytes == 0), "nkbs_zero_async: bad arguments");
+  if (bytes == 0) return 0;
+  cudaError_t e = cudaMemsetAsync(dev_ptr, 0, (size_t)bytes, (cudaStream_t)stream);
+  NKBS_CHECK_ARG(e == cudaSuccess, "nkbs_zero_async: %s", cudaGetErrorString(e));
+  return 0;
+}

@@ -12,7 +12,7 @@ constexpr int kPerBlock = kThreads * 16;  // floats per CTA
 
 struct AdamSeg {
   float* p;
-  const float* g;
+  float* g;
   float* m;
   float* v;
   int64_t n;
@@ -24,7 +24,8 @@ struct AdamArgs {
   int nseg;
   float lr, beta1, beta2, eps, weight_decay;
   const float* step_dev;   // device scalar: step count t >= 1 (float), read by every thread
-  const float* inv_scale;  // optional device scalar multiplied into the gradient (GradScaler unscale)
+  const float* inv_scale;  // optional device scalar multiplied into the gradient (GradScaler unscale / 1/world)
+  int zero_grads;          // write 0 back over every gradient read: the buffer is ready for the next backward pass
 };
 
 __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, float b1, float b2, float eps,
@@ -65,6 +66,7 @@ __global__ void __launch_bounds__(kThreads) adam_kernel(const AdamArgs a) {
       *reinterpret_cast<float4*>(sg.p + i) = p;
       *reinterpret_cast<float4*>(sg.m + i) = m;
       *reinterpret_cast<float4*>(sg.v + i) = v;
+      if (a.zero_grads) __stcs(reinterpret_cast<float4*>(sg.g + i), make_float4(0.f, 0.f, 0.f, 0.f));
     }
   } else {
     int64_t end = base + kPerBlock < sg.n ? base + kPerBlock : sg.n;
@@ -74,6 +76,7 @@ __global__ void __launch_bounds__(kThreads) adam_kernel(const AdamArgs a) {
       sg.p[i] = p;
       sg.m[i] = m;
       sg.v[i] = v;
+      if (a.zero_grads) sg.g[i] = 0.f;
     }
   }
 }
@@ -153,10 +156,10 @@ __global__ void __launch_bounds__(kThreads) dp_adam_kernel(const DpAdamArgs a) {
 
 }  // namespace
 
-extern "C" int nkbs_adam_step(int32_t num_tensors, float* const* params, const float* const* grads,
+extern "C" int nkbs_adam_step(int32_t num_tensors, float* const* params, float* const* grads,
                               float* const* exp_avg, float* const* exp_avg_sq, const int64_t* numel, float lr,
                               float beta1, float beta2, float eps, float weight_decay, const float* step_dev,
-                              const float* inv_scale_dev, void* stream) {
+                              const float* inv_scale_dev, int32_t zero_grads, void* stream) {
   NKBS_CHECK_ARG(num_tensors >= 0 && step_dev, "nkbs_adam_step: bad arguments");
   int i = 0;
   while (i < num_tensors) {
@@ -184,6 +187,7 @@ extern "C" int nkbs_adam_step(int32_t num_tensors, float* const* params, const f
     a.weight_decay = weight_decay;
     a.step_dev = step_dev;
     a.inv_scale = inv_scale_dev;
+    a.zero_grads = zero_grads;
     adam_kernel<<<blocks, kThreads, 0, (cudaStream_t)stream>>>(a);
     NKBS_CHECK_LAUNCH("nkbs_adam_step");
   }

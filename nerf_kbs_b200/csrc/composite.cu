@@ -412,6 +412,10 @@ extern "C" int nkbs_composite_bwd(int64_t R, int32_t S, const float* density, co
   CompBwdArgs a{R, S, density, weights, starts, ends, bin_stride ? bin_stride : S, rgb, sem, C, bg_mode, sem_weight_grad, acc, depth_raw,
                 g_weights, g_rgb, g_acc, g_depth, g_sem, d_density, d_weights, d_rgb, d_sem};
   size_t smem = (size_t)kWarpsPerCta * 3 * strip_len(S) * sizeof(float);
+  if (smem > 48 * 1024) {  // S >= 496: opt in to more than the default 48 KB of dynamic shared memory
+    cudaError_t e = cudaFuncSetAttribute(composite_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    NKBS_CHECK_ARG(e == cudaSuccess, "nkbs_composite_bwd: %zu bytes of shared memory refused (%s)", smem, cudaGetErrorString(e));
+  }
   composite_bwd_kernel<<<comp_grid(R), kThreads, smem, (cudaStream_t)stream>>>(a);
   NKBS_CHECK_LAUNCH("nkbs_composite_bwd");
   return 0;

@@ -3,9 +3,14 @@
 //   nkbs_compact_masked     stable compaction of candidate pixels whose motion mask is non-zero to exactly R rays
 //   nkbs_color_to_label     RGB semantic colour -> class label through a palette (replaces a per-pixel Python loop)
 //   nkbs_semantic_colormap  argmax over class logits -> palette colour (the rendered semantic image)
+//   nkbs_apply_colormap     scalar image in [0,1] -> 256-entry colour table (accumulation image)
+//   nkbs_apply_depth_colormap  depth normalised by its own (or given) range -> colour table, blended over white by accumulation
 // Replaces nerfstudio RayGenerator / Cameras.generate_rays as driven by ref:dataparser/datamanager_z.py:96,252-278,
 // the masked sampling of ref:dataparser/dataset_z.py:180-191, the color2label loop of ref:nerfacto.py:508-512 and
-// the argmax + colormap of ref:nerfacto.py:574-578 / ref:semantic_nerfw.py:346-351.
+// the argmax + colormap of ref:nerfacto.py:574-578 / ref:semantic_nerfw.py:346-351, and nerfstudio
+// utils.colormaps.apply_colormap / apply_depth_colormap as called at ref:nerfacto.py:574-578,608-613 and
+// ref:semantic_nerfw.py:305.
+#include <float.h>
 #include "common.cuh"
 
 namespace {
@@ -167,6 +172,73 @@ __global__ void __launch_bounds__(kThreads) semantic_colormap_kernel(int64_t N, 
   }
 }
 
+// ---- scalar colour maps (nerfstudio utils/colormaps.py) ----
+__device__ __forceinline__ int cm_float_key(float f) {
+  int i = __float_as_int(f);
+  return i >= 0 ? i : i ^ 0x7fffffff;
+}
+__device__ __forceinline__ float cm_key_float(int k) { return __int_as_float(k >= 0 ? k : k ^ 0x7fffffff); }
+
+__global__ void cm_minmax_init_kernel(int* mm) {
+  mm[0] = cm_float_key(FLT_MAX);
+  mm[1] = cm_float_key(-FLT_MAX);
+}
+
+__global__ void __launch_bounds__(kThreads) cm_minmax_kernel(int64_t N, const float* x, int* mm) {
+  float lo = FLT_MAX, hi = -FLT_MAX;
+  for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < N; p += (int64_t)gridDim.x * blockDim.x) {
+    const float v = x[p];
+    lo = fminf(lo, v);
+    hi = fmaxf(hi, v);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+  }
+  if ((threadIdx.x & 31) == 0 && lo <= hi) {
+    atomicMin(mm, cm_float_key(lo));
+    atomicMax(mm + 1, cm_float_key(hi));
+  }
+}
+
+// colour = lut[(long)(v * 255)]   (torch: (image * 255).long() truncates toward zero; nerfstudio asserts the index
+// range 0..255, here it is clamped).  depth mode: v = clip((d - near) / (far - near + 1e-10), 0, 1) with near / far
+// python floats in the reference: the subtraction runs in fp32 against fp32(near), the divisor is
+// fp32(double(far) - double(near) + 1e-10), the division is a true fp32 division (CPU torch semantics); then
+// colour * acc + (1 - acc).
+__global__ void __launch_bounds__(kThreads) colormap_kernel(int64_t N, const float* x, const float* acc, const float* lut,
+                                                            int depth_mode, const int* mm, float near_in, float far_in,
+                                                            int have_near, int have_far, float* out) {
+  float near = 0.f, den = 1.f;
+  if (depth_mode) {
+    near = have_near ? near_in : cm_key_float(mm[0]);
+    const float far = have_far ? far_in : cm_key_float(mm[1]);
+    den = (float)((double)far - (double)near + 1e-10);
+  }
+  for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < N; p += (int64_t)gridDim.x * blockDim.x) {
+    float v = x[p];
+    if (depth_mode) {
+      v = __fdiv_rn(__fsub_rn(v, near), den);
+      v = fminf(fmaxf(v, 0.f), 1.f);  // torch.clip: NaN propagates
+      if (v != v) v = 0.f;
+    }
+    long long idx = (long long)__fmul_rn(v, 255.f);
+    idx = idx < 0 ? 0 : (idx > 255 ? 255 : idx);
+    float r = lut[3 * idx], g = lut[3 * idx + 1], b = lut[3 * idx + 2];
+    if (acc) {
+      const float a = acc[p];
+      const float w = __fsub_rn(1.f, a);
+      r = __fadd_rn(__fmul_rn(r, a), w);
+      g = __fadd_rn(__fmul_rn(g, a), w);
+      b = __fadd_rn(__fmul_rn(b, a), w);
+    }
+    out[3 * p] = r;
+    out[3 * p + 1] = g;
+    out[3 * p + 2] = b;
+  }
+}
+
 int grid_for(int64_t n) {
   int64_t blocks = (n + kThreads - 1) / kThreads;
   int64_t cap = (int64_t)nkbs_num_sms() * 8;
@@ -216,5 +288,33 @@ extern "C" int nkbs_semantic_colormap(int64_t N, int32_t C, const float* logits,
   NKBS_CHECK_ARG(logits && (labels || rgb) && (!rgb || palette), "nkbs_semantic_colormap: null pointers");
   semantic_colormap_kernel<<<grid_for(N), kThreads, 0, (cudaStream_t)stream>>>(N, C, logits, (const Palette*)palette, labels, rgb);
   NKBS_CHECK_LAUNCH("nkbs_semantic_colormap");
+  return 0;
+}
+
+extern "C" int nkbs_apply_colormap(int64_t N, const float* image, const float* lut, float* rgb, void* stream) {
+  NKBS_CHECK_ARG(N >= 0, "nkbs_apply_colormap: negative N");
+  if (N == 0) return 0;
+  NKBS_CHECK_ARG(image && lut && rgb, "nkbs_apply_colormap: null pointers");
+  colormap_kernel<<<grid_for(N), kThreads, 0, (cudaStream_t)stream>>>(N, image, nullptr, lut, 0, nullptr, 0.f, 0.f, 0, 0, rgb);
+  NKBS_CHECK_LAUNCH("nkbs_apply_colormap");
+  return 0;
+}
+
+extern "C" int nkbs_apply_depth_colormap(int64_t N, const float* depth, const float* accumulation, const float* lut,
+                                         int32_t have_near, float near_plane, int32_t have_far, float far_plane,
+                                         int32_t* minmax_ws, float* rgb, void* stream) {
+  NKBS_CHECK_ARG(N >= 0, "nkbs_apply_depth_colormap: negative N");
+  if (N == 0) return 0;
+  NKBS_CHECK_ARG(depth && lut && rgb, "nkbs_apply_depth_colormap: null pointers");
+  NKBS_CHECK_ARG((have_near && have_far) || minmax_ws, "nkbs_apply_depth_colormap: the depth range needs a workspace");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!(have_near && have_far)) {
+    cm_minmax_init_kernel<<<1, 1, 0, st>>>(minmax_ws);
+    cm_minmax_kernel<<<grid_for(N), kThreads, 0, st>>>(N, depth, minmax_ws);
+    NKBS_CHECK_LAUNCH("nkbs_apply_depth_colormap(range)");
+  }
+  colormap_kernel<<<grid_for(N), kThreads, 0, st>>>(N, depth, accumulation, lut, 1, minmax_ws, near_plane, far_plane,
+                                                    have_near, have_far, rgb);
+  NKBS_CHECK_LAUNCH("nkbs_apply_depth_colormap");
   return 0;
 }

@@ -29,6 +29,24 @@ def _zeros_like_many(tensors):
     return out
 
 
+def _sinks(params):
+    """Gradient sinks of ``params`` (``p._nkbs_grad_sink``: the parameter's view of a step driver's flat gradient
+    buffer, optim.ParamArena) if EVERY one has one, else None.  Collected outside ``Function.apply`` from the caller's
+    own Parameter objects."""
+    sinks = [getattr(p, "_nkbs_grad_sink", None) for p in params]
+    return sinks if sinks and all(s is not None for s in sinks) else None
+
+
+def _grad_buffers(sinks, like):
+    """(buffers the backward kernel accumulates the parameter gradients into, what ``backward`` returns for them).
+    With sinks the kernel adds into the step driver's buffer and autograd sees no gradient for the parameter (no
+    fill launch, no AccumulateGrad); without, fresh zero-filled tensors are handed to autograd."""
+    if sinks is not None:
+        return list(sinks), [None] * len(sinks)
+    zs = _zeros_like_many(like)
+    return zs, zs
+
+
 def _c(t: Optional[torch.Tensor], dtype=torch.float32) -> Optional[torch.Tensor]:
     if t is None:
         return None
@@ -93,7 +111,7 @@ class _HashEncode(torch.autograd.Function):
         feats, sel, xn, _ = encode_raw(mode, grid, norm, table, x, origins, directions, starts, ends)
         # the non-differentiable outputs would otherwise receive materialised zero gradients ([N] and [N,3] fills)
         ctx.set_materialize_grads(False)
-        ctx.sink = sink  # optional pre-registered gradient buffer (dp_optim.ShardedAdam: symmetric memory)
+        ctx.sink = sink  # optional gradient sink (optim.ParamArena): the scatter accumulates into it
         ctx.grid = grid
         # run merging (segmented shuffle reduction, csrc/encode.cuh) costs a ballot on levels without duplicates and
         # never loses on B200 (scripts/encode_bench.py sweep): -1 = every level
@@ -109,15 +127,11 @@ class _HashEncode(torch.autograd.Function):
         g = ctx.grid
         if dfeat is None:
             return (None,) * 11
-        if ctx.sink is not None:
-            dtable = ctx.sink.detach()
-            dtable.zero_()
-        else:
-            dtable = torch.zeros(ctx.table_shape, device=xn.device, dtype=torch.float32)
+        (dtable,), (ret,) = _grad_buffers([ctx.sink] if ctx.sink is not None else None, [xn.new_empty(ctx.table_shape)])
         dfeat = _c(dfeat)
         call("nkbs_encode_bwd", ptr(xn), ptr(dfeat), xn.shape[0], host_floats(g.scalings), g.L, g.log2_T,
              g.features_per_level, ctx.dedup, ptr(dtable), stream())
-        return (dtable,) + (None,) * 10
+        return (ret,) + (None,) * 10
 
 
 def hash_encode(table, grid: GridSpec, x_normalised):
@@ -159,7 +173,8 @@ def fused_density_enabled() -> bool:
 
 class _FusedDensity(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, table, W1, b1, W2, b2, grid, norm, dedup_levels, x, origins, directions, starts, ends):
+    def forward(ctx, table, W1, b1, W2, b2, grid, norm, dedup_levels, x, origins, directions, starts, ends, sinks=None):
+        ctx.sinks = sinks
         table, W1, b1, W2, b2 = _c(table), _c(W1), _c(b1), _c(W2), _c(b2)
         require_cuda(table, W1, x, origins, starts)
         if x is not None:
@@ -183,13 +198,13 @@ class _FusedDensity(torch.autograd.Function):
         mode, R, S, H, grid, norm, dedup = ctx.cfg
         table, W1, b1, W2, b2, x, origins, directions, starts, ends = ctx.saved_tensors
         ddensity = _c(ddensity)
-        dtable, dW1, db1, dW2, db2 = _zeros_like_many([table, W1, b1, W2, b2])
+        (dtable, dW1, db1, dW2, db2), ret = _grad_buffers(ctx.sinks, [table, W1, b1, W2, b2])
         p_st, p_en, bstride, _keep = rows(starts, ends)
         call("nkbs_density_bwd", mode, ptr(x), ptr(origins), ptr(directions), p_st, p_en, bstride, R, S,
              int(norm.contraction), host_floats(norm.aabb), ptr(table), host_floats(grid.scalings), grid.L, grid.log2_T,
              ptr(W1), ptr(b1), ptr(W2), ptr(b2), H, ptr(ddensity), dedup, ptr(dtable), ptr(dW1), ptr(db1), ptr(dW2),
              ptr(db2), stream())
-        return (dtable, dW1, db1, dW2, db2) + (None,) * 8
+        return (*ret,) + (None,) * 9
 
 
 def fused_density(table, grid: GridSpec, norm: NormSpec, W1, b1, W2, b2, positions=None, origins=None, directions=None,
@@ -199,11 +214,12 @@ def fused_density(table, grid: GridSpec, norm: NormSpec, W1, b1, W2, b2, positio
     detached in the reference path)."""
     if (grid.L, W1.shape[0]) not in FUSED_DENSITY_SHAPES or W1.shape[1] != grid.out_dim or W2.shape[0] != 1:
         raise ValueError(f"no fused density kernel for L={grid.L}, MLP {tuple(W1.shape)} -> {tuple(W2.shape)}")
+    sinks = _sinks([table, W1, b1, W2, b2])
     if positions is not None:
         return _FusedDensity.apply(table, W1, b1, W2, b2, grid, norm, dedup_levels, _c(positions).reshape(-1, 3), None,
-                                   None, None, None)
+                                   None, None, None, sinks)
     return _FusedDensity.apply(table, W1, b1, W2, b2, grid, norm, dedup_levels, None, _c(origins), _c(directions),
-                               starts.float(), ends.float())
+                               starts.float(), ends.float(), sinks)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -228,7 +244,8 @@ def get_mlp_precision() -> str:
 
 class _Mlp(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, selector, relu_mask, out_act, col0, *params):
+    def forward(ctx, x, selector, relu_mask, out_act, col0, sinks, *params):
+        ctx.sinks = sinks  # gradient sinks in the order W_0..W_{n-1}, b_0..b_{n-1}, or None
         nl = len(params) // 2
         Ws = [_c(p) for p in params[0::2]]
         bs = [_c(p) for p in params[1::2]]
@@ -261,7 +278,7 @@ class _Mlp(torch.autograd.Function):
         x, selector = saved[0], saved[1]
         Ws, bs = list(saved[2:2 + nl]), list(saved[2 + nl:2 + 2 * nl])
         if dy is None and dy0 is None:
-            return (None,) * (5 + 2 * nl)
+            return (None,) * (6 + 2 * nl)
         if dy is None:
             dy = torch.zeros((x.shape[0], dims[-1]), device=x.device, dtype=torch.float32)
         dy = _c(dy)
@@ -271,7 +288,7 @@ class _Mlp(torch.autograd.Function):
             dy[:, 0] += dy0.reshape(-1)
         N = x.shape[0]
         dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
-        zs = _zeros_like_many(Ws + bs)
+        zs, ret = _grad_buffers(ctx.sinks, Ws + bs)
         dWs, dbs = zs[:nl], zs[nl:]
         if tc:
             call("nkbs_mlp_tc_bwd", ptr(x), ptr(dy), N, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask,
@@ -280,9 +297,9 @@ class _Mlp(torch.autograd.Function):
             call("nkbs_mlp_bwd", ptr(x), ptr(dy), N, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask,
                  out_act, ptr(selector), ptr(dx), host_ptrs(dWs), host_ptrs(dbs), stream())
         grads = []
-        for w, b in zip(dWs, dbs):
+        for w, b in zip(ret[:nl], ret[nl:]):
             grads += [w, b]
-        return (dx, None, None, None, None, *grads)
+        return (dx, None, None, None, None, None, *grads)
 
 
 def mlp(x, weights: Sequence[torch.Tensor], biases: Sequence[torch.Tensor], relu_mask: int, out_act: int = ACT_NONE,
@@ -292,7 +309,7 @@ def mlp(x, weights: Sequence[torch.Tensor], biases: Sequence[torch.Tensor], relu
     params = []
     for w, b in zip(weights, biases):
         params += [w, b]
-    return _Mlp.apply(x, selector, relu_mask, out_act, bool(col0), *params)
+    return _Mlp.apply(x, selector, relu_mask, out_act, bool(col0), _sinks(list(weights) + list(biases)), *params)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -354,7 +371,8 @@ class _HeadMlp(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, src, col, emb, emb_const, directions, cam, S, sh_dim, dir_per_ray, cam_per_ray, relu_mask, out_act,
-                *params):
+                sinks, *params):
+        ctx.sinks, ctx.emb_sink = sinks  # (W.., b.. sinks or None, embedding-table sink or None)
         nl = len(params) // 2
         Ws = [_c(p) for p in params[0::2]]
         bs = [_c(p) for p in params[1::2]]
@@ -383,8 +401,13 @@ class _HeadMlp(torch.autograd.Function):
         dy = _c(dy)
         N, stride = src.shape
         dsrc = torch.zeros_like(src) if ctx.needs_input_grad[0] else None
-        demb = torch.zeros(emb_shape, device=src.device, dtype=torch.float32) if (use_cam and ctx.needs_input_grad[2]) else None
-        zs = _zeros_like_many(Ws + bs)
+        demb, demb_ret = None, None
+        if use_cam and ctx.needs_input_grad[2]:
+            if ctx.emb_sink is not None:
+                demb = ctx.emb_sink
+            else:
+                demb = demb_ret = torch.zeros(emb_shape, device=src.device, dtype=torch.float32)
+        zs, ret = _grad_buffers(ctx.sinks, Ws + bs)
         dWs, dbs = zs[:nl], zs[nl:]
         geo = src.reshape(-1)[col:]
         dgeo = dsrc.reshape(-1)[col:] if dsrc is not None else None
@@ -393,9 +416,9 @@ class _HeadMlp(torch.autograd.Function):
              host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask, out_act, bwd_fmt, ptr(dgeo), stride, ptr(demb),
              host_ptrs(dWs), host_ptrs(dbs), stream())
         grads = []
-        for w, b in zip(dWs, dbs):
+        for w, b in zip(ret[:nl], ret[nl:]):
             grads += [w, b]
-        return (dsrc, None, demb, None, None, None, None, None, None, None, None, None, *grads)
+        return (dsrc, None, demb_ret, None, None, None, None, None, None, None, None, None, None, *grads)
 
 
 def head_mlp(src, col: int, emb_table, emb_const, directions, cam, S: int, sh_dim: int, dir_per_ray: bool,
@@ -405,8 +428,9 @@ def head_mlp(src, col: int, emb_table, emb_const, directions, cam, S: int, sh_di
     params = []
     for w, b in zip(weights, biases):
         params += [w, b]
+    sinks = (_sinks(list(weights) + list(biases)), getattr(emb_table, "_nkbs_grad_sink", None))
     return _HeadMlp.apply(src, col, emb_table, emb_const, _c(directions), _c(cam, torch.int64), S, sh_dim, dir_per_ray,
-                          cam_per_ray, relu_mask, out_act, *params)
+                          cam_per_ray, relu_mask, out_act, sinks, *params)
 
 
 # ----------------------------------------------------------------------------------------------

@@ -7,7 +7,7 @@ device so that a captured CUDA graph advances it on every replay."""
 from __future__ import annotations
 
 import ctypes as C
-from typing import Iterable, Optional
+from typing import Dict, Iterable, List, Optional, Sequence
 
 import torch
 
@@ -40,9 +40,10 @@ class Adam:
                     p.grad.zero_()
 
     @torch.no_grad()
-    def step(self, inv_scale: Optional[torch.Tensor] = None) -> None:
-        """One update of every parameter that has a gradient."""
-        self.step_t.add_(1.0)
+    def step(self, inv_scale: Optional[torch.Tensor] = None, zero_grads: bool = False) -> None:
+        """One update of every parameter that has a gradient.  A call in which no parameter has one (the proposal
+        group on a gated step) is a no-op and does NOT advance the step count — torch.optim.Adam keeps
+        the count per parameter and skips parameters whose ``grad`` is None."""
         ps, gs, ms, vs, ns, keep = [], [], [], [], [], []
         for p, m, v in zip(self.params, self.exp_avg, self.exp_avg_sq):
             g = p.grad
@@ -56,10 +57,11 @@ class Adam:
         n = len(ps)
         if n == 0:
             return
+        self.step_t.add_(1.0)
         arr = lambda xs: (C.c_void_p * n)(*xs)
         call("nkbs_adam_step", n, arr(ps), arr(gs), arr(ms), arr(vs), (C.c_int64 * n)(*ns), float(self.lr),
              float(self.betas[0]), float(self.betas[1]), float(self.eps), float(self.weight_decay),
-             self.step_t.data_ptr(), inv_scale.data_ptr() if inv_scale is not None else None, stream())
+             self.step_t.data_ptr(), inv_scale.data_ptr() if inv_scale is not None else None, int(zero_grads), stream())
 
     def state_dict(self):
         return {"step": self.step_t.clone(), "exp_avg": [m.clone() for m in self.exp_avg],
@@ -71,3 +73,118 @@ class Adam:
             a.copy_(b)
         for a, b in zip(self.exp_avg_sq, sd["exp_avg_sq"]):
             a.copy_(b)
+
+
+# ----------------------------------------------------------------------------------------------
+# flat parameter / gradient arena of the step driver
+# ----------------------------------------------------------------------------------------------
+def _round_up(n: int, m: int) -> int:
+    return (n + m - 1) // m * m
+
+
+def flat_layout(group_numels: Dict[str, Sequence[int]], world: int, rank: int) -> Dict[str, Dict]:
+    """Offsets of every tensor in the flat buffers and this rank's slice of every group: tensors are 4-element
+    aligned, every group is padded to a multiple of 4 * world elements and cut into ``world`` equal slices."""
+    layout, off = {}, 0
+    for name, numels in group_numels.items():
+        start, offs = off, []
+        for n in numels:
+            offs.append(off)
+            off += _round_up(n, 4)
+        off = start + _round_up(off - start, 4 * world)
+        shard = (off - start) // world
+        layout[name] = {"start": start, "len": off - start, "offs": offs, "lo": start + rank * shard, "n": shard}
+    layout["__total__"] = off
+    return layout
+
+
+class ParamArena:
+    """Parameters and gradients of all groups in two flat fp32 buffers ``P`` and ``G`` (group after group, every
+    tensor 16-byte aligned).  The Parameter objects stay; their storage moves into ``P``, ``p.grad`` becomes the
+    matching view of ``G`` for good, and ``p._nkbs_grad_sink`` tells the nkbs backward kernels to ACCUMULATE their
+    parameter gradients straight into ``G`` (ops.py) instead of returning fresh zero-filled tensors to autograd: no
+    fill launches, no AccumulateGrad copies, and the optimizer is one launch per group that re-zeroes ``G`` as it
+    reads it.  ``alloc(numel)`` lets the data-parallel step place the buffers in symmetric (peer-mapped) memory."""
+
+    def __init__(self, groups: Dict[str, Sequence[torch.nn.Parameter]], world: int = 1, rank: int = 0, alloc=None):
+        self.groups: Dict[str, List[torch.nn.Parameter]] = {k: [p for p in v if p.requires_grad] for k, v in groups.items()}
+        first = next(p for ps in self.groups.values() for p in ps)
+        dev = first.device
+        if dev.type != "cuda":
+            raise RuntimeError("nkbs optimizers run on CUDA parameters only (no CPU fallback)")
+        for ps in self.groups.values():
+            for p in ps:
+                if p.dtype != torch.float32 or not p.is_contiguous():
+                    raise ValueError("nkbs optimizers take contiguous fp32 parameters")
+        self.device = dev
+        self.layout = flat_layout({k: [p.numel() for p in ps] for k, ps in self.groups.items()}, world, rank)
+        self.total = self.layout.pop("__total__")
+        alloc = alloc if alloc is not None else (lambda n: torch.empty(n, dtype=torch.float32, device=dev))
+        self.P, self.G = alloc(self.total), alloc(self.total)
+        self.P.zero_()
+        self.G.zero_()
+        self.grad_view: Dict[int, torch.Tensor] = {}
+        with torch.no_grad():
+            for name, ps in self.groups.items():
+                for p, o in zip(ps, self.layout[name]["offs"]):
+                    view = self.P[o:o + p.numel()].view(p.shape)
+                    view.copy_(p.data)
+                    p.data = view
+                    gv = self.G[o:o + p.numel()].view(p.shape)
+                    self.grad_view[id(p)] = gv
+                    p._nkbs_grad_sink = gv
+                    p.grad = gv
+
+    def group_slice(self, name: str, buf: torch.Tensor) -> torch.Tensor:
+        lay = self.layout[name]
+        return buf[lay["start"]:lay["start"] + lay["len"]]
+
+    def release(self) -> None:
+        """Detach the parameters from the arena's gradient buffer (they keep their storage in ``P``)."""
+        for ps in self.groups.values():
+            for p in ps:
+                if hasattr(p, "_nkbs_grad_sink"):
+                    del p._nkbs_grad_sink
+                p.grad = None
+
+
+class ArenaAdam:
+    """torch.optim.Adam semantics per parameter group over a ``ParamArena``: one ``nkbs_adam_step`` launch per
+    active group over the group's flat slice; the kernel writes zeros back over the gradients it has read.  A group
+    that is not active in a step (the proposal networks on a gated step) is skipped and its step count
+    does not advance, like torch.optim.Adam skips parameters whose ``grad`` is None."""
+
+    def __init__(self, arena: ParamArena, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-15,
+                 weight_decay: float = 0.0):
+        self.arena = arena
+        self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
+        dev = arena.device
+        self.exp_avg = {k: torch.zeros(v["len"], device=dev) for k, v in arena.layout.items()}
+        self.exp_avg_sq = {k: torch.zeros(v["len"], device=dev) for k, v in arena.layout.items()}
+        self.step_t = {k: torch.zeros((), device=dev, dtype=torch.float32) for k in arena.layout}
+
+    @torch.no_grad()
+    def step(self, active: Optional[Sequence[str]] = None, inv_scale: Optional[torch.Tensor] = None,
+             zero_grads: bool = True) -> None:
+        a = self.arena
+        for name in (active if active is not None else list(a.layout)):
+            lay = a.layout[name]
+            self.step_t[name].add_(1.0)
+            one = lambda x: (C.c_void_p * 1)(x)
+            off = lay["start"] * 4
+            call("nkbs_adam_step", 1, one(a.P.data_ptr() + off), one(a.G.data_ptr() + off),
+                 one(self.exp_avg[name].data_ptr()), one(self.exp_avg_sq[name].data_ptr()), (C.c_int64 * 1)(lay["len"]),
+                 float(self.lr), float(self.betas[0]), float(self.betas[1]), float(self.eps), float(self.weight_decay),
+                 self.step_t[name].data_ptr(), inv_scale.data_ptr() if inv_scale is not None else None, int(zero_grads),
+                 stream())
+
+    def moments_of(self, p: torch.nn.Parameter):
+        """(exp_avg, exp_avg_sq) views shaped like ``p`` (checkpointing, tests)."""
+        a = self.arena
+        for name, ps in a.groups.items():
+            for q, o in zip(ps, a.layout[name]["offs"]):
+                if q is p:
+                    lo = o - a.layout[name]["start"]
+                    return (self.exp_avg[name][lo:lo + p.numel()].view(p.shape),
+                            self.exp_avg_sq[name][lo:lo + p.numel()].view(p.shape))
+        raise KeyError("parameter is not in the arena")

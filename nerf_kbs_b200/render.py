@@ -52,10 +52,11 @@ def get_outputs_for_camera_ray_bundle(model, ray_bundle: RayBundle, num_rays_per
 
 @torch.no_grad()
 def render_camera(model, ray_generator: RayGenerator, camera_index: int, num_rays_per_chunk: int = 1 << 16,
-                  palette: Optional[SemanticPalette] = None, rank: int = 0, world_size: int = 1, group=None
-                  ) -> Dict[str, torch.Tensor]:
-    """Render one full frame: rgb [H,W,3], depth / accumulation [H,W,1], semantics logits [H,W,C] and, with a
-    palette, ``semantics_label`` [H,W] int64 and ``semantics_colormap`` [H,W,3] uint8."""
+                  palette: Optional[SemanticPalette] = None, rank: int = 0, world_size: int = 1, group=None,
+                  colormaps: bool = True) -> Dict[str, torch.Tensor]:
+    """Render one full frame: rgb [H,W,3], depth / accumulation [H,W,1], semantics logits [H,W,C]; with a palette,
+    ``semantics_label`` [H,W] int64 and ``semantics_colormap`` [H,W,3] uint8; with ``colormaps``, the colour-mapped
+    ``accumulation_colormap`` and ``depth_colormap`` / ``prop_depth_i_colormap`` [H,W,3] float images."""
     cams = ray_generator.cameras
     H, W = cams.height, cams.width
     idx = image_ray_indices(camera_index, H, W, ray_generator.c2w.device)
@@ -64,4 +65,11 @@ def render_camera(model, ray_generator: RayGenerator, camera_index: int, num_ray
     out = {k: v.reshape(H, W, *v.shape[1:]) for k, v in flat.items()}
     if palette is not None and "semantics" in out:
         out["semantics_label"], out["semantics_colormap"] = palette.colormap(out["semantics"])
+    if colormaps:
+        # the images of get_image_metrics_and_images (ref:nerfacto.py:574-578,608-613), on the device
+        from .colormaps import apply_colormap, apply_depth_colormap
+        out["accumulation_colormap"] = apply_colormap(out["accumulation"])
+        for k in ("depth", "prop_depth_0", "prop_depth_1"):
+            if k in out:
+                out[k + "_colormap"] = apply_depth_colormap(out[k], accumulation=out["accumulation"])
     return out

@@ -18,13 +18,18 @@ class NearFarCollider(nn.Module):
 
     def set_nears_and_fars(self, ray_bundle: RayBundle) -> RayBundle:
         # the two [R,1] constants are built once per (rays, device) and handed out read-only afterwards: four launches
-        # fewer on every step (the sampler kernels only read them)
+        # fewer on every step (the sampler kernels only read them).  Entries are never evicted while somebody else
+        # still holds them (a captured CUDA graph would keep reading the freed memory); the step driver owns its
+        # planes itself (trainer.Trainer._planes) and does not come through here.
         o = ray_bundle.origins
         key = (tuple(o.shape[:-1]), o.device, o.dtype, float(self.near_plane), float(self.far_plane))
         planes = self._planes.get(key)
         if planes is None:
             if len(self._planes) > 8:
-                self._planes.clear()
+                import sys
+                # getrefcount: the dict's tuple + the argument = 2 when nobody else holds the pair
+                for k in [k for k, v in self._planes.items() if sys.getrefcount(v[0]) <= 2 and sys.getrefcount(v[1]) <= 2]:
+                    del self._planes[k]
             planes = (torch.full_like(o[..., 0:1], self.near_plane), torch.full_like(o[..., 0:1], self.far_plane))
             self._planes[key] = planes
         ray_bundle.nears, ray_bundle.fars = planes

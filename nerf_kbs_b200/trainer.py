@@ -3,15 +3,20 @@ around ``model.get_outputs`` for the reference's configs (ref:train.py:42-101 â€
 Adam lr 1e-3 eps 1e-15 on the "proposal_networks" and "fields" groups, no scheduler), as one CUDA
 graph per step:
 
-    zero_grad -> model(ray_bundle) -> get_loss_dict -> backward -> [gradient allreduce] -> Adam
+    model(ray_bundle) -> losses -> backward -> [gradient exchange] -> Adam (which re-zeroes the gradients)
+
+Parameters and gradients live in one flat arena (optim.ParamArena): the backward kernels accumulate parameter
+gradients straight into it, so the step has no zero_grad pass, no fill launches and no AccumulateGrad copies.
 
 The callbacks of ref:nerfacto.py:365-394 (weight-anneal before the step, ``step_cb`` after it) stay on
 the host: the anneal value reaches the captured kernels through a device scalar, and the proposal
 "updated" gating selects between two captured graphs (with / without proposal gradients).
 
-Data parallelism (SURVEY Â§8e): one process per GPU, every rank steps its own ray batch, and one
-sum-allreduce (NCCL over NVLink; gloo on the CPU for tests) of the gradients precedes Adam â€” large hash
-tables in place, everything else through one flat bucket.  No other collective is on the path."""
+Data parallelism (SURVEY Â§8e): one process per GPU, every rank steps its own ray batch; the one exchange of
+the path is the gradient mean before Adam.  Default on several GPUs: reduce-scatter + Adam + all-gather fused
+in one kernel over NVLink peer (symmetric) memory (dp_optim.ShardedAdam -> nkbs_dp_adam_step), NCCL carrying
+only barriers.  ``NKBS_DP_FUSED=0``: one NCCL sum-allreduce per parameter group over the arena's flat gradient
+slice, then the local Adam with 1/world folded in (the checker route; gloo on the CPU for the host-logic tests)."""
 from __future__ import annotations
 
 import os
@@ -22,7 +27,7 @@ import torch
 import torch.distributed as dist
 
 from . import _lib
-from .optim import Adam
+from .optim import ArenaAdam, ParamArena
 from .rays import RayBundle
 
 BIG_TENSOR = 1 << 18  # elements; gradients at least this large are all-reduced in place, the rest bucketed
@@ -68,7 +73,11 @@ class Trainer:
 
     def __init__(self, model, num_rays: int, lr: float = 1e-3, eps: float = 1e-15, betas=(0.9, 0.999),
                  use_graph: bool = True, process_group=None, graph_warmup: int = 3, seed: Optional[int] = None,
-                 fused_loss: Optional[bool] = None):
+                 fused_loss: Optional[bool] = None, inject_jitter: bool = False, keep_grads: bool = False):
+        """``inject_jitter``: the per-ray jitter of the three sampling levels is an input of the step
+        (``train_step(..., jitter=[t0, t1, t2])``, each [R,1]) instead of being drawn on the device â€” parity tests feed
+        the oracle the same draws.  ``keep_grads``: debugging / tests â€” the optimizer leaves the gradients in the arena
+        (``p.grad`` readable after the step) and the step starts with a fill instead."""
         self.model = model
         # weighted total straight out of the loss kernel (models.get_loss_total); NKBS_FUSED_LOSS=0 keeps the loss-dict route
         self.fused_loss = (os.environ.get("NKBS_FUSED_LOSS", "1") != "0") if fused_loss is None else bool(fused_loss)
@@ -83,17 +92,23 @@ class Trainer:
         self.world_size = dist.get_world_size(process_group) if (dist.is_available() and dist.is_initialized()) else 1
         # several GPUs: reduce-scatter + Adam + all-gather fused over NVLink peer memory (dp_optim.py);
         # NKBS_DP_FUSED=0 keeps the NCCL allreduce + per-rank Adam route
-        self.sharded = None
+        self.sharded, self.opt = None, None
         if self.world_size > 1 and os.environ.get("NKBS_DP_FUSED", "1") != "0":
             from .dp_optim import ShardedAdam
-            self.sharded = ShardedAdam(groups, lr=lr, betas=betas, eps=eps, process_group=process_group)
-        self.optimizers: Dict[str, Adam] = {} if self.sharded is not None else {
-            k: Adam(v, lr=lr, betas=betas, eps=eps) for k, v in groups.items()}
+            self.arena = ShardedAdam.make_arena(groups, process_group)
+            self.sharded = ShardedAdam(self.arena, lr=lr, betas=betas, eps=eps, process_group=process_group)
+        else:
+            self.arena = ParamArena(groups)
+            self.opt = ArenaAdam(self.arena, lr=lr, betas=betas, eps=eps)
+        self.keep_grads = bool(keep_grads)
+        self._inv_world = torch.full((), 1.0 / self.world_size, device=p0.device) if self.world_size > 1 else None
         self.use_graph = use_graph
         self.graph_warmup = graph_warmup
         self.step = 0
         self._graphs: Dict[bool, torch.cuda.CUDAGraph] = {}
         self._graph_loss: Dict[bool, Dict[str, torch.Tensor]] = {}
+        self._graph_outputs: Dict[bool, Dict] = {}
+        self.outputs: Dict = {}  # model outputs of the last step (graph replays: the captured static tensors)
         self._pool = None
         self._eager_steps = 0
         self._calls_per_graph: Dict[bool, int] = {}
@@ -110,7 +125,16 @@ class Trainer:
         }
         if self.needs_labels:
             self.buf["semantics_label"] = torch.zeros(self.R, device=dev, dtype=torch.int64)
+        n_levels = model.proposal_sampler.num_proposal_network_iterations + 1
+        self.jitter = torch.zeros(n_levels, self.R, 1, device=dev) if inject_jitter else None
         self.pinned = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True) for k, v in self.buf.items()}
+        # the collider's near / far planes are static inputs of the captured step as well: the graphs bake in their
+        # addresses, so they are owned here and not by the collider's (evictable) cache
+        col = getattr(model, "collider", None)
+        self._planes = None
+        if col is not None and hasattr(col, "near_plane"):
+            self._planes = (torch.full((self.R, 1), float(col.near_plane), device=dev),
+                            torch.full((self.R, 1), float(col.far_plane), device=dev))
         self.anneal_t = torch.ones((), device=dev)
         model.proposal_sampler.pdf_sampler.anneal_dev = self.anneal_t
         self._loss_host = torch.zeros((), pin_memory=True)
@@ -151,22 +175,36 @@ class Trainer:
 
     def _bundle(self) -> RayBundle:
         b = self.buf
+        nears, fars = self._planes if self._planes is not None else (None, None)
         return RayBundle(origins=b["origins"], directions=b["directions"], pixel_area=b["pixel_area"],
-                         camera_indices=b["camera_indices"], metadata={})
+                         camera_indices=b["camera_indices"], nears=nears, fars=fars, metadata={})
 
     # -- the step ----------------------------------------------------------------------------------
-    def _zero_grad(self) -> None:
+    def zero_grad(self) -> None:
+        """Zero the arena's gradient buffer (the step itself never needs this: the optimizer leaves it zeroed)."""
+        self.arena.G.zero_()
+
+    def active_groups(self, updated: bool) -> List[str]:
+        """Parameter groups that receive gradients in a step: the proposal networks only when the sampler's
+        ``updated`` gating lets them train; torch.optim.Adam skips them otherwise (``grad is None``)."""
+        return [k for k in self.arena.layout if updated or k != "proposal_networks"]
+
+    def optimizer_step(self, updated: bool = True) -> None:
+        active = self.active_groups(updated)
         if self.sharded is not None:
-            self.sharded.zero_grad()
-        for o in self.optimizers.values():
-            o.zero_grad(set_to_none=True)
+            self.sharded.step(active)
+            return
+        if self.world_size > 1:
+            for name in active:
+                dist.all_reduce(self.arena.group_slice(name, self.arena.G), op=dist.ReduceOp.SUM, group=self.group)
+        self.opt.step(active, inv_scale=self._inv_world, zero_grads=not self.keep_grads)
 
-    def _grads(self) -> List[torch.Tensor]:
-        return [p.grad for o in self.optimizers.values() for p in o.params if p.grad is not None]
-
-    def _step_body(self) -> Dict[str, torch.Tensor]:
-        self._zero_grad()
-        outputs = self.model(self._bundle())
+    def _step_body(self, updated: bool) -> Dict[str, torch.Tensor]:
+        if self.keep_grads:
+            self.zero_grad()
+        jitter = list(self.jitter.unbind(0)) if self.jitter is not None else None
+        outputs = self.model(self._bundle(), jitter=jitter)
+        self.outputs = outputs
         batch = {"image": self.buf["image"]}
         if self.needs_labels:
             batch["semantics_label"] = self.buf["semantics_label"]
@@ -179,13 +217,7 @@ class Trainer:
             loss_dict = self.model.get_loss_dict(outputs, batch)
             loss = sum(loss_dict.values())
         loss.backward()
-        if self.sharded is not None:
-            self.sharded.step()
-        else:
-            if self.world_size > 1:
-                allreduce_mean_(self._grads(), self.group, self.world_size)
-            for o in self.optimizers.values():
-                o.step()
+        self.optimizer_step(updated)
         out = {k: v.detach() for k, v in loss_dict.items()}
         out["loss"] = loss.detach()
         return out
@@ -194,14 +226,23 @@ class Trainer:
         g = torch.cuda.CUDAGraph()
         if self._pool is None:
             self._pool = torch.cuda.graph_pool_handle()
-        self._zero_grad()
         torch.cuda.synchronize(self.device)
         c0 = sum(_lib.call_counts.values())
         with torch.cuda.graph(g, pool=self._pool):
-            out = self._step_body()
+            out = self._step_body(key)
         self._calls_per_graph[key] = sum(_lib.call_counts.values()) - c0
         self._graphs[key] = g
         self._graph_loss[key] = out
+        self._graph_outputs[key] = self.outputs  # static tensors of the graph's pool: rewritten by every replay
+
+    def close(self) -> None:
+        """Drop the captured graphs and detach the parameters from the gradient arena.  Call before tearing the
+        process group down: a CUDA graph that captured a collective keeps its communicator referenced."""
+        self._graphs.clear()
+        self._graph_loss.clear()
+        self._graph_outputs.clear()
+        self.outputs, self.loss_dict = {}, {}
+        self.arena.release()
 
     def prepare(self) -> None:
         """Run the eager warm-up steps and capture every CUDA-graph variant up front (these are real
@@ -220,12 +261,17 @@ class Trainer:
                 finally:
                     sampler.force_updated = None
 
-    def train_step(self, ray_bundle: Optional[RayBundle] = None, batch: Optional[Dict[str, torch.Tensor]] = None
-                   ) -> torch.Tensor:
+    def train_step(self, ray_bundle: Optional[RayBundle] = None, batch: Optional[Dict[str, torch.Tensor]] = None,
+                   jitter: Optional[Sequence[torch.Tensor]] = None) -> torch.Tensor:
         """Run one step on the given batch (or on whatever the static buffers hold).  Returns the total loss
         as a device scalar; ``self.loss_dict`` holds the individual terms."""
         if ray_bundle is not None:
             self.load_batch(ray_bundle, batch)
+        if jitter is not None:
+            if self.jitter is None:
+                raise ValueError("Trainer(inject_jitter=True) is needed to feed the jitter draws")
+            for dst, src in zip(self.jitter, jitter):
+                dst.copy_(src.reshape(dst.shape), non_blocking=True)
         m = self.model
         m.set_step(self.step)
         self.anneal_t.fill_(float(m.proposal_sampler._anneal))  # scalar travels as a kernel argument
@@ -236,6 +282,7 @@ class Trainer:
             self._graphs[updated].replay()
             self.nkbs_calls += self._calls_per_graph[updated]
             out = self._graph_loss[updated]
+            self.outputs = self._graph_outputs[updated]
             if updated:  # the eager path resets this inside the sampler; the replay has no host side
                 m.proposal_sampler._steps_since_update = 0
         else:
@@ -245,10 +292,10 @@ class Trainer:
                 s = torch.cuda.Stream(self.device)
                 s.wait_stream(torch.cuda.current_stream(self.device))
                 with torch.cuda.stream(s):
-                    out = self._step_body()
+                    out = self._step_body(updated)
                 torch.cuda.current_stream(self.device).wait_stream(s)
             else:
-                out = self._step_body()
+                out = self._step_body(updated)
             self._eager_steps += 1
             self.nkbs_calls += sum(_lib.call_counts.values()) - c0
         m.after_step(self.step)

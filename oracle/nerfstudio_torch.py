@@ -1048,3 +1048,24 @@ def semantic_colormap(logits: torch.Tensor, palette) -> Tuple[torch.Tensor, torc
     labels = torch.argmax(torch.nn.functional.softmax(logits, dim=-1), dim=-1)
     pal = torch.tensor(palette, dtype=torch.uint8)
     return labels, pal[labels]
+
+
+def apply_colormap(image: torch.Tensor, lut: torch.Tensor) -> torch.Tensor:
+    """nerfstudio utils.colormaps.apply_colormap [NS-recalled], called at ref:nerfacto.py:574, semantic_nerfw.py:305:
+    ``colormap[(image * 255).long()[..., 0]]`` with ``lut`` = the [256,3] colour table (matplotlib's in nerfstudio)."""
+    image_long = (image * 255).long()
+    assert int(image_long.min()) >= 0 and int(image_long.max()) <= 255
+    return lut[image_long[..., 0]]
+
+
+def apply_depth_colormap(depth: torch.Tensor, lut: torch.Tensor, accumulation: Optional[torch.Tensor] = None,
+                         near_plane: Optional[float] = None, far_plane: Optional[float] = None) -> torch.Tensor:
+    """nerfstudio utils.colormaps.apply_depth_colormap [NS-recalled], called at ref:nerfacto.py:575-578,608-613."""
+    near_plane = near_plane or float(torch.min(depth))
+    far_plane = far_plane or float(torch.max(depth))
+    depth = (depth - near_plane) / (far_plane - near_plane + 1e-10)
+    depth = torch.clip(depth, 0, 1)
+    colored_image = apply_colormap(depth, lut)
+    if accumulation is not None:
+        colored_image = colored_image * accumulation + (1 - accumulation)
+    return colored_image

@@ -111,3 +111,65 @@ def test_render_camera_matches_oracle_chunks():
     assert_close(out["depth"].reshape(-1, 1), want["depth"], 1e-3, "median depth")
     assert_close(out["semantics"].reshape(-1, 19), want["semantics"], 1e-4, "semantics")
     assert float(out["rgb"].min()) >= 0.0 and float(out["rgb"].max()) <= 1.0
+
+
+def test_colormaps_full_kitti_frame_match_oracle():
+    """N4: accumulation / depth colour maps of a full 1242x375 frame against the oracle (torch restatement of
+    nerfstudio utils.colormaps), same colour tables in both arms: bit-exact table indices, hence equal colours."""
+    H, W = 375, 1242
+    g = torch.Generator().manual_seed(3)
+    acc = torch.rand(H, W, 1, generator=g)
+    acc[0, :7, 0] = torch.tensor([0.0, 1.0, 0.5, 1.0 / 255.0, 254.999 / 255.0, 0.999999, 2.0 / 255.0])
+    depth = torch.rand(H, W, 1, generator=g) * 80.0 + 0.5
+    depth[1, :3, 0] = torch.tensor([0.05, 1000.0, 3.0])  # sets the frame's own range
+    for name in ("viridis", "turbo"):
+        lut = nk.colormap_table(name)
+        assert lut.shape == (256, 3) and float(lut.min()) >= 0.0 and float(lut.max()) <= 1.0
+        got = nk.apply_colormap(acc.to(DEV), cmap=name)
+        assert got.shape == (H, W, 3)
+        assert torch.equal(got.cpu(), O.apply_colormap(acc, lut))
+    lut = nk.colormap_table("turbo")
+    for kw in (dict(), dict(near_plane=0.5), dict(far_plane=60.0), dict(near_plane=1.0, far_plane=50.0)):
+        for use_acc in (True, False):
+            want = O.apply_depth_colormap(depth, lut, accumulation=acc if use_acc else None, **kw)
+            got = nk.apply_depth_colormap(depth.to(DEV), accumulation=acc.to(DEV) if use_acc else None, **kw)
+            assert torch.equal(got.cpu(), want), (kw, use_acc, (got.cpu() - want).abs().max())
+    # a caller-supplied table (what matplotlib would hand over) is used as given
+    custom = torch.rand(256, 3, generator=g)
+    assert torch.equal(nk.apply_colormap(acc.to(DEV), cmap=custom).cpu(), O.apply_colormap(acc, custom))
+
+
+def test_render_camera_emits_colormapped_images():
+    torch.manual_seed(0)
+    nm = nk.NerfactoModel(nk.ModelConfig(use_semantic=True)).to(DEV).eval()
+    cams = _cameras(n=2, H=10, W=16)
+    gen = nk.RayGenerator(cams).to(DEV)
+    out = nk.render_camera(nm, gen, 0, num_rays_per_chunk=50, palette=nk.SemanticPalette(PALETTE, DEV))
+    lut_t, lut_v = nk.colormap_table("turbo"), nk.colormap_table("viridis")
+    assert torch.equal(out["accumulation_colormap"].cpu(), O.apply_colormap(out["accumulation"].cpu(), lut_v))
+    for k in ("depth", "prop_depth_0", "prop_depth_1"):
+        want = O.apply_depth_colormap(out[k].cpu(), lut_t, accumulation=out["accumulation"].cpu())
+        assert torch.equal(out[k + "_colormap"].cpu(), want), k
+
+
+def test_composite_backward_at_max_samples():
+    """S = 512 needs more than 48 KB of dynamic shared memory in the backward kernel."""
+    g = torch.Generator().manual_seed(0)
+    R, S = 33, 512
+    dens = (torch.rand(R, S, generator=g) * 3).to(DEV).requires_grad_(True)
+    rgb = torch.rand(R, S, 3, generator=g).to(DEV).requires_grad_(True)
+    bins = torch.sort(torch.rand(R, S + 1, generator=g) * 4, dim=-1).values
+    out = nk.ops.composite(density=dens, rgb=rgb, starts=bins[:, :-1].to(DEV), ends=bins[:, 1:].to(DEV),
+                           want=("rgb", "acc"))
+    (out["rgb"].sum() + out["accumulation"].sum()).backward()
+    d2 = dens.detach().cpu().double().requires_grad_(True)
+    c2 = rgb.detach().cpu().double().requires_grad_(True)
+    delta = (bins[:, 1:] - bins[:, :-1]).double()
+    ds = d2 * delta
+    T = torch.exp(-torch.cat([torch.zeros(R, 1, dtype=torch.float64), torch.cumsum(ds, -1)[:, :-1]], -1))
+    w = (1 - torch.exp(-ds)) * T
+    acc = w.sum(-1)
+    col = (w[..., None] * c2).sum(1) + c2[:, -1] * (1 - acc[:, None])
+    (col.sum() + acc.sum()).backward()
+    assert_close(dens.grad, d2.grad.float(), 2e-4, "d density at S=512")
+    assert_close(rgb.grad, c2.grad.float(), 2e-4, "d rgb at S=512")

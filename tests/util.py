@@ -101,3 +101,55 @@ def to_nk_bundle(rb: "O.RayBundle", device="cuda"):
 def make_jitter(R, levels=(256, 96, 48), seed=1, single=True):
     g = torch.Generator().manual_seed(seed)
     return [torch.rand(R, 1 if single else (n + 1), generator=g) for n in levels]
+
+
+# ------------------------------------------------------------------------------------------------
+# analytic scene for the fixed-step PSNR run: a normal-shaded sphere over a checkered ground plane under a
+# graded sky, rendered by a closed-form ray caster (no images on disk, nothing learned)
+# ------------------------------------------------------------------------------------------------
+def analytic_scene_colors(origins, directions):
+    """rgb [N,3] seen along each ray.  Sphere: centre 0, radius 0.35, colour 0.5 + 0.5 n.  Plane z = -0.35 with a
+    0.25-wide checker (inside |x|,|y| < 1.5).  Sky: vertical gradient."""
+    o, d = origins.double(), directions.double()
+    b = (o * d).sum(-1)
+    c = (o * o).sum(-1) - 0.35 ** 2
+    disc = b * b - c
+    t_s = -b - torch.sqrt(disc.clamp_min(0))
+    hit_s = (disc > 0) & (t_s > 0)
+    t_p = (-0.35 - o[:, 2]) / torch.where(d[:, 2].abs() < 1e-9, torch.full_like(d[:, 2], 1e-9), d[:, 2])
+    pp = o + t_p[:, None] * d
+    hit_p = (t_p > 0) & (pp[:, 0].abs() < 1.5) & (pp[:, 1].abs() < 1.5)
+    sky = torch.stack([0.55 + 0.2 * d[:, 2], 0.65 + 0.2 * d[:, 2], 0.85 + 0.1 * d[:, 2]], -1)
+    n = (o + t_s[:, None] * d) / 0.35
+    col_s = 0.5 + 0.5 * n
+    chk = ((torch.floor(pp[:, 0] / 0.25) + torch.floor(pp[:, 1] / 0.25)) % 2)[:, None]
+    col_p = chk * torch.tensor([0.85, 0.8, 0.7], dtype=torch.float64) + (1 - chk) * torch.tensor([0.2, 0.25, 0.3], dtype=torch.float64)
+    use_p = hit_p & (~hit_s | (t_p < t_s))
+    rgb = torch.where(use_p[:, None], col_p, torch.where(hit_s[:, None], col_s, sky))
+    return rgb.float().clamp(0, 1)
+
+
+def analytic_scene_rays(n, num_images=8, seed=0):
+    """n rays of ``num_images`` pinhole-like views on a shell around the sphere: (O.RayBundle, rgb [n,3])."""
+    g = torch.Generator().manual_seed(seed)
+    cam = torch.randint(0, num_images, (n, 1), generator=g)
+    gc = torch.Generator().manual_seed(12345)  # the views are the same for every ray set
+    az = torch.rand(num_images, generator=gc) * 6.2831853
+    el = 0.15 + 0.5 * torch.rand(num_images, generator=gc)
+    centers = 0.85 * torch.stack([torch.cos(az) * torch.cos(el), torch.sin(az) * torch.cos(el), torch.sin(el)], -1)
+    o = centers[cam[:, 0]]
+    target = (torch.rand(n, 3, generator=g) - 0.5) * torch.tensor([1.0, 1.0, 0.8])
+    d = target - o
+    d = d / d.norm(dim=-1, keepdim=True)
+    rb = O.RayBundle(origins=o, directions=d, pixel_area=torch.full((n, 1), 1e-6), camera_indices=cam, metadata={})
+    return rb, analytic_scene_colors(o, d)
+
+
+def psnr(pred, target):
+    mse = ((pred.detach().float().cpu() - target.float().cpu()) ** 2).mean().item()
+    return -10.0 * __import__("math").log10(max(mse, 1e-12))
+
+
+PSNR_PROPOSAL_ARGS = ({"hidden_dim": 16, "log2_hashmap_size": 13, "num_levels": 5, "max_res": 128, "use_linear": False},
+                      {"hidden_dim": 16, "log2_hashmap_size": 13, "num_levels": 5, "max_res": 256, "use_linear": False})
+PSNR_CFG = dict(log2_hashmap_size=15, proposal_net_args_list=PSNR_PROPOSAL_ARGS, num_images=8)
