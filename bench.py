@@ -39,10 +39,9 @@ SAMPLES = (256, 96, 48)
 L2_BYTES = 126 * 2**20
 L2_BYTES_PER_CYCLE = 6300  # whole-chip L2 (LTS) throughput cap, /opt/skills/guides/B300_MICROARCH.md
 # Kernels whose tables are cache-resident are reported against L2 throughput, not HBM: the proposal grids are 5-16 MiB
-# (L1/L2 hits, ncu: DRAM 2 %), and the gradient scatter of the main table is bound by L2 reductions (ncu:
-# lts__throughput 67 %, DRAM 10 %).  The main-grid gather (64 MiB table evicted by the 540 MB optimizer stream of
-# every step) and everything ray-major stay HBM kernels.
-L2_BOUND = {"nkbs_density_fwd", "nkbs_density_bwd", "nkbs_encode_bwd"}
+# (L1/L2 hits, ncu: DRAM 2 %).  The main-grid gather and scatter (64 MiB table + 64 MiB gradient, evicted by the
+# 620 MB optimizer stream of every step) and everything ray-major stay HBM kernels.
+L2_BOUND = {"nkbs_density_fwd", "nkbs_density_bwd", "nkbs_proposal_level_fwd"}
 BOUND_NOTE = {"l2": "table traffic of this kernel is served by L1/L2 (tables of 5-64 MiB against a 126 MiB L2): achieved = "
                     "algorithmic gather/scatter bytes per second against the L2 throughput cap, not HBM",
               "hbm": "achieved = algorithmic bytes per second against the measured HBM copy bandwidth",
@@ -225,6 +224,11 @@ def kernel_work(name, a):
         N, L = a[7] * a[8], a[13]
         gathers = 8 * L * 2 * 4
         return "hbm", N * ((8 + gathers + 4) if name.endswith("fwd") else (8 + 4 + 2 * gathers))
+    if name == "nkbs_proposal_level_fwd":
+        # per sample: 8 corner rows of 2 floats on each of L levels gathered, density and weight written; per ray: the
+        # level's bin edges (both domains) and the next level's
+        R, S, L, nb = a[0], a[1], a[15], a[25]
+        return "hbm", R * (S * (8 * L * 2 * 4 + 8) + 8 * (S + 1) + 8 * nb)
     if name in ("nkbs_ray_losses", "nkbs_ray_losses_weighted"):
         R, S, n_prop = a[0], a[1], a[5]
         sp = list(a[6])[:n_prop]
@@ -233,7 +237,7 @@ def kernel_work(name, a):
     return "hbm", 0
 
 
-NCU_NAMES = {"nkbs_density_bwd": "density_bwd_kernel", "nkbs_density_fwd": "density_fwd_kernel", "nkbs_encode_bwd": "encode_bwd_kernel",
+NCU_NAMES = {"nkbs_proposal_level_fwd": "proposal_level_fwd_kernel", "nkbs_density_bwd": "density_bwd_kernel", "nkbs_density_fwd": "density_fwd_kernel", "nkbs_encode_bwd": "encode_bwd_kernel",
              "nkbs_encode_fwd": "encode_fwd_kernel", "nkbs_mlp_tc_bwd": "mlp_tc_bwd_kernel", "nkbs_mlp_tc_fwd": "mlp_tc_fwd_kernel",
              "nkbs_head_tc_bwd": "mlp_tc_bwd_kernel", "nkbs_head_tc_fwd": "mlp_tc_fwd_kernel", "nkbs_adam_step": "adam_kernel",
              "nkbs_composite_fwd": "composite_fwd_kernel", "nkbs_composite_bwd": "composite_bwd_kernel",

@@ -224,6 +224,24 @@ int nkbs_dp_adam_step(int32_t world, int32_t rank, const float* const* grad_peer
                       int64_t lo, int64_t n, float* exp_avg, float* exp_avg_sq, float lr, float beta1, float beta2,
                       float eps, float weight_decay, const float* step_dev, void* stream);
 
+/* One proposal level of ProposalNetworkSampler in one ray-major pass (forward): the level's bins (gen_bins != 0:
+ * produced here by the initial piecewise sampler from lin [S+1] and the per-ray jitter t_rand [R] (NULL in
+ * evaluation) and WRITTEN to sbins / ebins [R,S+1]; gen_bins == 0: READ from them) -> density [R,S] of the fused
+ * HashMLPDensityField (arguments as nkbs_density_fwd) -> weights [R,S] (RaySamples.get_weights) and the median depth
+ * [R] (may be NULL) -> the next level's num_bins spacing / euclidean bin edges out_sbins / out_ebins [R,num_bins] by
+ * inverse-CDF resampling (arguments as nkbs_pdf_sample; rand [R] per-ray jitter, NULL = centred evaluation points).
+ * Same arithmetic as the four stand-alone entry points it fuses; nothing else leaves the SM.
+ * replaces: one iteration of ProposalNetworkSampler.generate_ray_samples (nerfacto.py:325-332,397;
+ *           semantic_nerfw.py:132-137,187). */
+int nkbs_proposal_level_fwd(int64_t R, int32_t S, const float* origins, const float* directions, const float* nears,
+                            const float* fars, int32_t gen_bins, const float* lin, const float* t_rand, float* sbins,
+                            float* ebins, int32_t contraction, const float* aabb, const float* table,
+                            const float* scalings, int32_t L, int32_t log2_T, const float* W1, const float* b1,
+                            const float* W2, const float* b2, int32_t H, float* density, float* weights,
+                            float* depth_med, int32_t num_bins, float anneal, const float* anneal_dev,
+                            float histogram_padding, float eps, const float* u_base, const float* rand,
+                            float* out_sbins, float* out_ebins, void* stream);
+
 /* N4 — scalar colour maps of the rendered frame.  lut: DEVICE float [256,3] colour table (the caller's data:
  * matplotlib's "viridis" / "turbo" tables in nerfstudio).  apply_colormap: image [N] in [0,1] -> rgb [N,3] =
  * lut[(long)(image * 255)].  apply_depth_colormap: depth [N] normalised by (near, far) — each either given

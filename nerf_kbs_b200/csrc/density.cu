@@ -9,8 +9,10 @@
 // sum (no shuffles: 32 rows x 32 lanes per pass).
 // Replaces HashMLPDensityField.get_density / density_fn reached from ref:nerfacto.py:299-311,325-332 and
 // ref:semantic_nerfw.py:119-137.
+#include <stdlib.h>
 #include "common.cuh"
 #include "encode.cuh"
+#include "sampler.cuh"
 
 namespace {
 
@@ -465,6 +467,186 @@ int fill(DensityArgs& a, const char* who, int mode, const float* x, const float*
   return 0;
 }
 
+
+// ---- one proposal level in ONE ray-major pass (forward) ---------------------------------------------------------
+// [bins of the level] -> density of every sample (the fused field above) -> alpha / transmittance / weights and the
+// median depth (RaySamples.get_weights + DepthRenderer("median")) -> inverse-CDF resampling of the next level's bins
+// (PDFSampler).  A CTA of G warps owns G rays at a time: all threads evaluate the field for the G*S samples (adjacent
+// lanes = adjacent samples of one ray), then warp g composites and resamples ray g out of shared memory.  Only what
+// later kernels read leaves the SM: the level's bins (when they are generated here: the initial sampler of level 0),
+// density, weights, median depth and the next level's bins.  Replaces, per level, nkbs_initial_sampler (level 0) +
+// nkbs_density_fwd + nkbs_composite_fwd + nkbs_pdf_sample and the [R,S] round trips between them
+// (ref:nerfacto.py:325-332,397; ProposalNetworkSampler.generate_ray_samples).
+struct LevelArgs {
+  DensityArgs d;          // field parameters, origins / directions; S = samples of this level; N = R * S
+  int64_t R;
+  int gen_bins;           // 1: the level's bins are the initial sampler's (written to sbins / ebins); 0: read them
+  const float* lin;       // [S+1] torch.linspace(0, 1, S+1)               (gen_bins)
+  const float* t_rand;    // [R] per-ray jitter or null (evaluation)        (gen_bins)
+  const float* nears;     // [R]
+  const float* fars;      // [R]
+  float* sbins;           // [R,S+1] spacing-domain bin edges of this level
+  float* ebins;           // [R,S+1] euclidean bin edges of this level
+  float* density;         // [R,S]
+  float* weights;         // [R,S]
+  float* depth_med;       // [R] or null
+  // resampling of the next level
+  int nb;                 // bins of the next level = its samples + 1
+  float anneal;
+  const float* anneal_dev;
+  float hist_pad, eps;
+  const float* u_base;    // [nb]
+  const float* rand;      // [R] per-ray jitter or null (evaluation: centred)
+  float* out_sbins;       // [R,nb]
+  float* out_ebins;       // [R,nb]
+};
+
+#define LVL_PI(s) ((s) + ((s) >> 5))
+__host__ __device__ constexpr int lvl_strip(int S) { return S + (S >> 5) + 1; }
+// floats of dynamic shared memory per ray: euclid bins, spacing bins, strip (delta*sigma -> weights -> pdf values), cdf
+__host__ __device__ constexpr int lvl_ray_floats(int S) { return 2 * (S + 1) + lvl_strip(S) + (S + 1); }
+
+__device__ __forceinline__ float lvl_nan_to_num(float w) {
+  if (w != w) return 0.f;
+  if (w > FLT_MAX) return FLT_MAX;
+  if (w < -FLT_MAX) return -FLT_MAX;
+  return w;
+}
+
+// G rays per group, W >= G warps per CTA: all W warps evaluate the field, warps 0..G-1 then own one ray each
+template <int H, int L, int G, int W>
+__global__ void __launch_bounds__(32 * W) proposal_level_fwd_kernel(const LevelArgs a) {
+  __shared__ float s_scale[NKBS_MAX_LEVELS];
+  __shared__ __align__(16) Smem<H, L> s;
+  extern __shared__ float s_dyn[];
+  constexpr int kT = 32 * W;
+  const DensityArgs& d = a.d;
+  if (threadIdx.x < NKBS_MAX_LEVELS) s_scale[threadIdx.x] = d.lv.scale[threadIdx.x];
+  {
+    constexpr int K = 2 * L, KP = Smem<H, L>::KP;
+    for (int e = threadIdx.x; e < H * KP; e += kT) {
+      int j = e / KP, i = e - j * KP;
+      s.w1[e] = i < K ? __ldg(d.W1 + j * K + i) : 0.f;
+    }
+    for (int j = threadIdx.x; j < H; j += kT) {
+      s.b1[j] = __ldg(d.b1 + j);
+      s.w2[j] = __ldg(d.W2 + j);
+    }
+    if (threadIdx.x == 0) s.b2 = __ldg(d.b2);
+  }
+  const int S = d.S, nbin = S + 1;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int per_ray = lvl_ray_floats(S);
+  const PdfParams pp{S, a.nb, a.anneal_dev ? *a.anneal_dev : a.anneal, a.hist_pad, a.eps, a.u_base};
+  __syncthreads();
+  for (int64_t g0 = (int64_t)blockIdx.x * G; g0 < a.R; g0 += (int64_t)gridDim.x * G) {
+    const int rays = a.R - g0 < G ? (int)(a.R - g0) : G;
+    // ---- bins of the group -> shared memory (generated here for level 0) ----
+    for (int e = threadIdx.x; e < rays * nbin; e += kT) {
+      const int g = e / nbin, i = e - g * nbin;
+      const int64_t r = g0 + g;
+      float* ray = s_dyn + g * per_ray;
+      float sb, eb;
+      if (a.gen_bins) {
+        sb = nkbs_initial_bin(a.lin, i, S, a.t_rand != nullptr, a.t_rand ? a.t_rand[r] : 0.f);
+        eb = nkbs_to_euclid(sb, nkbs_spacing_fn(a.nears[r]), nkbs_spacing_fn(a.fars[r]));
+        a.sbins[r * nbin + i] = sb;
+        a.ebins[r * nbin + i] = eb;
+      } else {
+        sb = a.sbins[r * nbin + i];
+        eb = a.ebins[r * nbin + i];
+      }
+      ray[i] = eb;
+      ray[nbin + i] = sb;
+    }
+    __syncthreads();
+    // ---- the field on every sample of the group ----
+    for (int e = threadIdx.x; e < rays * S; e += kT) {
+      const int g = e / S, sidx = e - g * S;
+      const int64_t r = g0 + g;
+      float* ray = s_dyn + g * per_ray;
+      const float st = ray[sidx], en = ray[sidx + 1];
+      const float3 o = make_float3(d.origins[3 * r], d.origins[3 * r + 1], d.origins[3 * r + 2]);
+      const float3 dir = make_float3(d.directions[3 * r], d.directions[3 * r + 1], d.directions[3 * r + 2]);
+      float sel;
+      const float3 x = nkbs_normalise(nkbs_frustum_position(o, dir, st, en), d.norm, sel);
+      float f[2 * L];
+      encode_sample<L>(d, s_scale, x, f);
+      float out = s.b2;
+#pragma unroll
+      for (int j = 0; j < H; ++j) out = fmaf(s.w2[j], fmaxf(hidden_pre<H, L>(s, f, j), 0.f), out);
+      const float sigma = expf(out) * sel;
+      a.density[r * S + sidx] = sigma;
+      ray[2 * nbin + LVL_PI(sidx)] = (en - st) * sigma;
+    }
+    __syncthreads();
+    // ---- warp g: weights, median depth and the next level's bins of ray g ----
+    if (wid < rays) {
+      const int64_t r = g0 + wid;
+      float* ray = s_dyn + wid * per_ray;
+      const float* eb = ray;
+      const float* sb = ray + nbin;
+      float* sw = ray + 2 * nbin;
+      float* scdf = sw + lvl_strip(S);
+      const int per = (S + 31) >> 5;
+      const int r0 = min(lane * per, S), r1 = min(r0 + per, S);
+      // transmittance: serial prefix inside the lane's contiguous run + one warp scan of the run totals
+      // (same arithmetic as composite_fwd_kernel)
+      float tot = 0.f;
+      for (int q = r0; q < r1; ++q) tot += sw[LVL_PI(q)];
+      float incl = tot;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const float n = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += n;
+      }
+      float run = incl - tot;
+      for (int q = r0; q < r1; ++q) {
+        const float x = sw[LVL_PI(q)];
+        sw[LVL_PI(q)] = lvl_nan_to_num((1.f - expf(-x)) * expf(-run));
+        run += x;
+      }
+      __syncwarp();
+      for (int q = lane; q < S; q += 32) a.weights[r * S + q] = sw[LVL_PI(q)];
+      if (a.depth_med) {
+        // first sample whose inclusive cumulative weight (double accumulator rounded per element) reaches 0.5
+        double local = 0.0;
+        for (int q = r0; q < r1; ++q) local += (double)sw[LVL_PI(q)];
+        double inc = local;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const double t = __shfl_up_sync(0xffffffffu, inc, o);
+          if (lane >= o) inc += t;
+        }
+        double cum = inc - local;
+        int idx = S;
+        for (int q = r0; q < r1; ++q) {
+          cum += (double)sw[LVL_PI(q)];
+          if ((float)cum >= 0.5f) {
+            idx = q;
+            break;
+          }
+        }
+        const unsigned hit = __ballot_sync(0xffffffffu, idx < S);
+        idx = hit ? __shfl_sync(0xffffffffu, idx, __ffs(hit) - 1) : S - 1;
+        if (lane == 0) a.depth_med[r] = (eb[idx] + eb[idx + 1]) / 2.f;
+      }
+      __syncwarp();
+      // resampling: the pdf values overwrite the weights in the strip (sv and the weight source are the same
+      // padded strip: element s is read before it is rewritten by the same lane)
+      struct Strip {
+        float* p;
+        __device__ __forceinline__ float& operator[](int q) const { return p[LVL_PI(q)]; }
+      };
+      Strip sv{sw};
+      nkbs_pdf_ray_warp(pp, [&](int q) { return sw[LVL_PI(q)]; }, [&](int k) { return sb[k]; }, sv, scdf, lane,
+                        a.rand != nullptr, a.rand ? a.rand[r] : 0.f, nullptr, a.nears[r], a.fars[r],
+                        a.out_sbins + r * a.nb, a.out_ebins + r * a.nb, nullptr);
+    }
+    __syncthreads();
+  }
+}
+
 }  // namespace
 
 extern "C" int nkbs_density_fwd(int32_t mode, const float* x, const float* origins, const float* directions,
@@ -515,5 +697,77 @@ extern "C" int nkbs_density_bwd(int32_t mode, const float* x, const float* origi
   else
     density_bwd_kernel<64, 8><<<grid_for(density_bwd_kernel<64, 8>, a.N), kThreads, 0, st>>>(a);
   NKBS_CHECK_LAUNCH("nkbs_density_bwd");
+  return 0;
+}
+
+extern "C" int nkbs_proposal_level_fwd(int64_t R, int32_t S, const float* origins, const float* directions,
+                                       const float* nears, const float* fars, int32_t gen_bins, const float* lin,
+                                       const float* t_rand, float* sbins, float* ebins, int32_t contraction,
+                                       const float* aabb, const float* table, const float* scalings, int32_t L,
+                                       int32_t log2_T, const float* W1, const float* b1, const float* W2,
+                                       const float* b2, int32_t H, float* density, float* weights, float* depth_med,
+                                       int32_t num_bins, float anneal, const float* anneal_dev, float histogram_padding,
+                                       float eps, const float* u_base, const float* rand, float* out_sbins,
+                                       float* out_ebins, void* stream) {
+  LevelArgs a;
+  // the bin arrays double as the frustum source: starts = ebins[:, :-1], ends = ebins[:, 1:]
+  if (fill(a.d, "nkbs_proposal_level_fwd", 2, nullptr, origins, directions, ebins, ebins ? ebins + 1 : nullptr, S + 1, R, S,
+           contraction, aabb, table, scalings, L, log2_T, W1, b1, W2, b2, H))
+    return -1;
+  if (R == 0) return 0;
+  NKBS_CHECK_ARG(S <= 1024 && num_bins >= 2, "nkbs_proposal_level_fwd: S=%d (max 1024), bins=%d", S, num_bins);
+  NKBS_CHECK_ARG(nears && fars && sbins && density && weights && u_base && out_sbins && out_ebins,
+                 "nkbs_proposal_level_fwd: null argument");
+  NKBS_CHECK_ARG(!gen_bins || lin, "nkbs_proposal_level_fwd: the initial sampler needs the linspace table");
+  a.R = R;
+  a.gen_bins = gen_bins;
+  a.lin = lin;
+  a.t_rand = t_rand;
+  a.nears = nears;
+  a.fars = fars;
+  a.sbins = sbins;
+  a.ebins = ebins;
+  a.density = density;
+  a.weights = weights;
+  a.depth_med = depth_med;
+  a.nb = num_bins;
+  a.anneal = anneal;
+  a.anneal_dev = anneal_dev;
+  a.hist_pad = histogram_padding;
+  a.eps = eps;
+  a.u_base = u_base;
+  a.rand = rand;
+  a.out_sbins = out_sbins;
+  a.out_ebins = out_ebins;
+  // CTA shape: as many threads as the group has samples where possible (one field evaluation per thread keeps the
+  // gathers of a whole wave in flight, like nkbs_density_fwd), G rays per group.  NKBS_LEVEL_SHAPE=<G><W> overrides.
+  static const int forced = [] { const char* e = getenv("NKBS_LEVEL_SHAPE"); return e ? atoi(e) : 0; }();
+  int shape = forced ? forced : (S >= 224 ? 18 : (S >= 80 && S <= 96 ? 26 : 44));
+  const int G = shape / 10, Wn = shape % 10;
+  NKBS_CHECK_ARG((G == 1 && Wn == 8) || (G == 2 && Wn == 6) || (G == 4 && Wn == 4) || (G == 2 && Wn == 8),
+                 "nkbs_proposal_level_fwd: unsupported NKBS_LEVEL_SHAPE %d", shape);
+  const size_t smem = (size_t)G * lvl_ray_floats(S) * sizeof(float);
+  int64_t groups = (R + G - 1) / G;
+  const int64_t cap = (int64_t)nkbs_num_sms() * 32;
+  const int grid = (int)(groups < cap ? groups : cap);
+  cudaStream_t st = (cudaStream_t)stream;
+  auto launch = [&](auto kernel) -> int {
+    if (smem > 48 * 1024) {
+      cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      NKBS_CHECK_ARG(e == cudaSuccess, "nkbs_proposal_level_fwd: %zu bytes of shared memory refused (%s)", smem, cudaGetErrorString(e));
+    }
+    kernel<<<grid, 32 * Wn, smem, st>>>(a);
+    return 0;
+  };
+  int rc;
+#define NKBS_LVL(HH, LL)                                                        \
+  (shape == 18   ? launch(proposal_level_fwd_kernel<HH, LL, 1, 8>)              \
+   : shape == 26 ? launch(proposal_level_fwd_kernel<HH, LL, 2, 6>)              \
+   : shape == 28 ? launch(proposal_level_fwd_kernel<HH, LL, 2, 8>)              \
+                 : launch(proposal_level_fwd_kernel<HH, LL, 4, 4>))
+  rc = H == 16 ? NKBS_LVL(16, 5) : NKBS_LVL(64, 8);
+#undef NKBS_LVL
+  if (rc) return rc;
+  NKBS_CHECK_LAUNCH("nkbs_proposal_level_fwd");
   return 0;
 }

@@ -9,23 +9,14 @@
 // linspace tables come from the host (torch.linspace on the CPU) so their rounding is the oracle's.
 #include <float.h>
 #include "common.cuh"
+#include "sampler.cuh"
 
 namespace {
 
 constexpr int kThreads = 128;
 
-__device__ __forceinline__ float spacing_fn(float x) {
-  // where(x < 1, x / 2, 1 - 1 / (2 * x))
-  return x < 1.f ? __fmul_rn(x, 0.5f) : __fsub_rn(1.f, __fdiv_rn(1.f, __fmul_rn(2.f, x)));
-}
-__device__ __forceinline__ float spacing_inv(float x) {
-  // where(x < 0.5, 2 * x, 1 / (2 - 2 * x))
-  return x < 0.5f ? __fmul_rn(2.f, x) : __fdiv_rn(1.f, __fsub_rn(2.f, __fmul_rn(2.f, x)));
-}
-__device__ __forceinline__ float to_euclid(float s, float s_near, float s_far) {
-  // spacing_inv(x * s_far + (1 - x) * s_near)
-  return spacing_inv(__fadd_rn(__fmul_rn(s, s_far), __fmul_rn(__fsub_rn(1.f, s), s_near)));
-}
+__device__ __forceinline__ float spacing_fn(float x) { return nkbs_spacing_fn(x); }
+__device__ __forceinline__ float to_euclid(float s, float s_near, float s_far) { return nkbs_to_euclid(s, s_near, s_far); }
 
 struct InitArgs {
   int64_t R;
@@ -45,14 +36,8 @@ __global__ void __launch_bounds__(256) initial_sampler_kernel(const InitArgs a) 
   for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
     int64_t r = e / nb;
     int i = (int)(e - r * nb);
-    float b = a.lin[i];
-    if (a.t_rand) {
-      float tr = a.rand_per_bin ? a.t_rand[e] : a.t_rand[r];
-      // centers = (bins[1:] + bins[:-1]) / 2 ; upper = cat[centers, last] ; lower = cat[first, centers]
-      float upper = (i < a.S) ? __fmul_rn(__fadd_rn(a.lin[i + 1], b), 0.5f) : b;
-      float lower = (i > 0) ? __fmul_rn(__fadd_rn(b, a.lin[i - 1]), 0.5f) : b;
-      b = __fadd_rn(lower, __fmul_rn(__fsub_rn(upper, lower), tr));
-    }
+    const float tr = a.t_rand ? (a.rand_per_bin ? a.t_rand[e] : a.t_rand[r]) : 0.f;
+    const float b = nkbs_initial_bin(a.lin, i, a.S, a.t_rand != nullptr, tr);
     float s_near = spacing_fn(a.nears[r]), s_far = spacing_fn(a.fars[r]);
     a.sbins[e] = b;
     a.ebins[e] = to_euclid(b, s_near, s_far);
@@ -165,89 +150,20 @@ __global__ void __launch_bounds__(kThreads) pdf_sample_kernel(const PdfArgs a) {
 constexpr int kWarpPdfMaxS = 1024;
 constexpr int kPdfWarps = 8;
 
-__device__ __forceinline__ double warp_sum_d(double v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
-}
-
 __global__ void __launch_bounds__(kPdfWarps * 32) pdf_sample_warp_kernel(const PdfArgs a) {
   extern __shared__ float s_pdf[];  // per warp: v[S] then cdf[S+1]
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int S = a.S, nb = a.nb;
   float* sv = s_pdf + wid * (2 * S + 1);
   float* scdf = sv + S;
-  const float anneal = a.anneal_dev ? *a.anneal_dev : a.anneal;
-  const bool do_pow = anneal != 1.0f;
-  const float fS = (float)S, fnb = (float)nb;
-  const float eval_off = (float)(1.0 / (2.0 * (double)nb));
+  const PdfParams p{S, nb, a.anneal_dev ? *a.anneal_dev : a.anneal, a.hist_pad, a.eps, a.u_base};
   for (int64_t r = blockIdx.x * (int64_t)kPdfWarps + wid; r < a.R; r += (int64_t)gridDim.x * kPdfWarps) {
     const float* w = a.weights + r * S;
     const float* eb = a.sbins + r * (S + 1);
-    // pass 1: v = pow(w, anneal); weights_sum = sum(v + histogram_padding)
-    double dsum = 0.0;
-    for (int s = lane; s < S; s += 32) {
-      float v = w[s];
-      if (do_pow) v = powf(v, anneal);
-      sv[s] = v;
-      dsum += (double)__fadd_rn(v, a.hist_pad);
-    }
-    dsum = warp_sum_d(dsum);
-    float sum = (float)dsum;
-    const float padding = fmaxf(__fsub_rn(a.eps, sum), 0.f);
-    const float pad_each = __fdiv_rn(padding, fS);
-    sum = __fadd_rn(sum, padding);
-    // pass 2: cdf[k] = min(1, float(sum_{s<k} pdf_s)), running sum in double, 32 samples per round
-    double carry = 0.0;
-    if (lane == 0) scdf[0] = 0.f;
-    for (int s0 = 0; s0 < S; s0 += 32) {
-      const int s = s0 + lane;
-      double x = 0.0;
-      if (s < S) x = (double)__fdiv_rn(__fadd_rn(__fadd_rn(sv[s], a.hist_pad), pad_each), sum);
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        double n = __shfl_up_sync(0xffffffffu, x, o);
-        if (lane >= o) x += n;
-      }
-      x += carry;
-      if (s < S) scdf[s + 1] = fminf(1.f, (float)x);
-      carry = __shfl_sync(0xffffffffu, x, 31);
-    }
-    __syncwarp();
-    const float s_near = spacing_fn(a.nears[r]), s_far = spacing_fn(a.fars[r]);
-    float rj = 0.f;
-    if (a.rand && !a.rand_per_bin) rj = __fdiv_rn(a.rand[r], fnb);
-    for (int i = lane; i < nb; i += 32) {
-      float u = a.u_base[i];
-      if (a.rand) {
-        if (a.rand_per_bin) rj = __fdiv_rn(a.rand[r * nb + i], fnb);
-        u = __fadd_rn(u, rj);
-      } else {
-        u = __fadd_rn(u, eval_off);
-      }
-      // idx = number of entries of cdf[0..S] that are <= u  (side="right")
-      int lo = 0, hi = S + 1;
-      while (lo < hi) {
-        const int mid = (lo + hi) >> 1;
-        if (scdf[mid] <= u) lo = mid + 1;
-        else hi = mid;
-      }
-      const int idx = lo;
-      const int below = idx - 1 < 0 ? 0 : (idx - 1 > S ? S : idx - 1);
-      const int above = idx > S ? S : idx;
-      const float g0 = scdf[below], g1 = scdf[above];
-      const float b0 = eb[below], b1 = eb[above];
-      float t = __fdiv_rn(__fsub_rn(u, g0), __fsub_rn(g1, g0));
-      if (t != t) t = 0.f;
-      else if (t > FLT_MAX) t = FLT_MAX;
-      else if (t < -FLT_MAX) t = -FLT_MAX;
-      t = fminf(fmaxf(t, 0.f), 1.f);
-      const float b = __fadd_rn(b0, __fmul_rn(t, __fsub_rn(b1, b0)));
-      a.out_sbins[r * nb + i] = b;
-      a.out_ebins[r * nb + i] = to_euclid(b, s_near, s_far);
-      if (a.out_inds) a.out_inds[r * nb + i] = idx;
-    }
-    __syncwarp();
+    nkbs_pdf_ray_warp(p, [&](int s) { return w[s]; }, [&](int k) { return eb[k]; }, sv, scdf, lane, a.rand != nullptr,
+                      (a.rand && !a.rand_per_bin) ? a.rand[r] : 0.f, (a.rand && a.rand_per_bin) ? a.rand + r * nb : nullptr,
+                      a.nears[r], a.fars[r], a.out_sbins + r * nb, a.out_ebins + r * nb,
+                      a.out_inds ? a.out_inds + r * nb : nullptr);
   }
 }
 

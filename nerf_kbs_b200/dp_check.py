@@ -47,6 +47,7 @@ def run_dp_check(dev, rank: int, world: int, rays: int = 1024, steps: int = 8, g
         for i in range(steps):
             b = batches[i % len(batches)]
             losses.append(float(tr.train_step(RayBundle(b["origins"], b["directions"], b["pixel_area"], b["camera_indices"]), b)))
+        tr.flush()
         torch.cuda.synchronize()
         flat = torch.cat([p.detach().reshape(-1) for p in m.parameters()]).clone()
         tr.close()

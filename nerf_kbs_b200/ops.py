@@ -496,6 +496,96 @@ def pdf_sample(weights, spacing_bins, nears, fars, num_samples: int, anneal: flo
 
 
 # ----------------------------------------------------------------------------------------------
+# one proposal level in one ray-major pass: [initial sampler] + density field + get_weights + median depth + PDF sampler
+# ----------------------------------------------------------------------------------------------
+# Measured on the B200 (round 2, same box A/B, 4096-ray captured step): four launches 0.796 ms, one fused launch 0.815 ms
+# (4 rays x 4 warps per CTA), 0.85 / 0.89 ms with one field evaluation per thread (2 or 1 rays per 8-warp CTA): the
+# per-ray scan + resampling phases keep one warp per ray busy while the CTA's other warps wait, which costs more than
+# the three launch boundaries and [R,S] round trips it removes.  Hence off by default; NKBS_FUSED_LEVEL=1 selects it.
+_FUSED_LEVEL = {"enabled": __import__("os").environ.get("NKBS_FUSED_LEVEL", "0") == "1"}
+
+
+def set_fused_level(enabled: bool) -> None:
+    """ProposalNetworkSampler runs each proposal level as ONE launch (default) or as sampler + field + compositing
+    + PDF launches."""
+    _FUSED_LEVEL["enabled"] = bool(enabled)
+
+
+def fused_level_enabled() -> bool:
+    return _FUSED_LEVEL["enabled"]
+
+
+class _ProposalLevel(torch.autograd.Function):
+    """weights of one proposal level and the next level's bins (nkbs_proposal_level_fwd).  Differentiable output:
+    the weights (w.r.t. the field's table and MLP; bins and positions are detached in the reference).
+    Backward: d weights -> d density (nkbs_composite_bwd) -> table / MLP gradients (nkbs_density_bwd)."""
+
+    @staticmethod
+    def forward(ctx, table, W1, b1, W2, b2, cfg, origins, directions, nears, fars, sbins, ebins, t_rand, rand, sinks):
+        grid, norm, S, nb, anneal, anneal_dev, hist_pad, eps, dedup = cfg
+        table, W1, b1, W2, b2 = _c(table), _c(W1), _c(b1), _c(W2), _c(b2)
+        origins, directions = _c(origins), _c(directions)
+        nears, fars = _c(nears).reshape(-1), _c(fars).reshape(-1)
+        require_cuda(table, W1, origins, nears, sbins, t_rand, rand)
+        R, dev = origins.shape[0], origins.device
+        gen = sbins is None
+        if gen:
+            sbins = torch.empty((R, S + 1), device=dev, dtype=torch.float32)
+            ebins = torch.empty_like(sbins)
+        else:
+            sbins, ebins = _c(sbins), _c(ebins)
+        f32 = dict(device=dev, dtype=torch.float32)
+        density, weights = torch.empty((R, S), **f32), torch.empty((R, S), **f32)
+        dmed = torch.empty((R,), **f32)
+        nsb, neb = torch.empty((R, nb), **f32), torch.empty((R, nb), **f32)
+        t_rand = _c(t_rand).reshape(-1) if t_rand is not None else None
+        rand = _c(rand).reshape(-1) if rand is not None else None
+        call("nkbs_proposal_level_fwd", R, S, ptr(origins), ptr(directions), ptr(nears), ptr(fars), int(gen),
+             ptr(_lin_table("bins", S, dev)) if gen else None, ptr(t_rand), ptr(sbins), ptr(ebins), int(norm.contraction),
+             host_floats(norm.aabb), ptr(table), host_floats(grid.scalings), grid.L, grid.log2_T, ptr(W1), ptr(b1), ptr(W2),
+             ptr(b2), W1.shape[0], ptr(density), ptr(weights), ptr(dmed), nb, float(anneal), ptr(anneal_dev),
+             float(hist_pad), float(eps), ptr(_lin_table("u", nb, dev)), ptr(rand), ptr(nsb), ptr(neb), stream())
+        ctx.cfg = (grid, norm, S, R, dedup if dedup >= 0 else grid.L)
+        ctx.sinks = sinks
+        ctx.set_materialize_grads(False)
+        ctx.save_for_backward(table, W1, b1, W2, b2, origins, directions, ebins, density, weights)
+        ctx.mark_non_differentiable(dmed, sbins, ebins, nsb, neb)
+        return weights, dmed, sbins, ebins, nsb, neb
+
+    @staticmethod
+    def backward(ctx, g_w, *_unused):
+        grid, norm, S, R, dedup = ctx.cfg
+        table, W1, b1, W2, b2, origins, directions, ebins, density, weights = ctx.saved_tensors
+        if g_w is None:
+            return (None,) * 15
+        g_w = _c(g_w)
+        ddensity = torch.empty_like(density)
+        st, en = ebins.data_ptr(), ebins.data_ptr() + 4
+        call("nkbs_composite_bwd", R, S, ptr(density), ptr(weights), st, en, S + 1, None, None, 0, 0, 0, None, None,
+             ptr(g_w), None, None, None, None, ptr(ddensity), None, None, None, stream())
+        (dtable, dW1, db1, dW2, db2), ret = _grad_buffers(ctx.sinks, [table, W1, b1, W2, b2])
+        call("nkbs_density_bwd", 2, None, ptr(origins), ptr(directions), st, en, S + 1, R, S, int(norm.contraction),
+             host_floats(norm.aabb), ptr(table), host_floats(grid.scalings), grid.L, grid.log2_T, ptr(W1), ptr(b1), ptr(W2),
+             ptr(b2), W1.shape[0], ptr(ddensity), dedup, ptr(dtable), ptr(dW1), ptr(db1), ptr(dW2), ptr(db2), stream())
+        return (*ret,) + (None,) * 10
+
+
+def proposal_level(table, grid: GridSpec, norm: NormSpec, W1, b1, W2, b2, origins, directions, nears, fars,
+                   num_samples: int, num_next: int, sbins=None, ebins=None, t_rand=None, rand=None, anneal: float = 1.0,
+                   anneal_dev=None, histogram_padding: float = 0.01, eps: float = 1e-5, dedup_levels: int = -1):
+    """One proposal level: returns (weights [R,S], median depth [R], spacing bins [R,S+1], euclidean bins [R,S+1],
+    next spacing bins [R,num_next+1], next euclidean bins [R,num_next+1]).  ``sbins`` / ``ebins`` None: the level's
+    bins are the initial sampler's (``t_rand`` [R,1] per-ray jitter or None); ``rand`` [R,1]: per-ray jitter of the
+    resampling (None: centred, evaluation)."""
+    if (grid.L, W1.shape[0]) not in FUSED_DENSITY_SHAPES or W1.shape[1] != grid.out_dim or W2.shape[0] != 1:
+        raise ValueError(f"no fused proposal-level kernel for L={grid.L}, MLP {tuple(W1.shape)} -> {tuple(W2.shape)}")
+    cfg = (grid, norm, int(num_samples), int(num_next) + 1, float(anneal), anneal_dev, float(histogram_padding),
+           float(eps), int(dedup_levels))
+    return _ProposalLevel.apply(table, W1, b1, W2, b2, cfg, origins, directions, nears, fars, sbins, ebins, t_rand, rand,
+                                _sinks([table, W1, b1, W2, b2]))
+
+
+# ----------------------------------------------------------------------------------------------
 # K6/K7 compositing
 # ----------------------------------------------------------------------------------------------
 class _Composite(torch.autograd.Function):

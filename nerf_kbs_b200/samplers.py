@@ -144,6 +144,22 @@ class ProposalNetworkSampler(nn.Module):
             return bool(self.force_updated)
         return self._steps_since_update > self.update_sched(self._step) or self._step < 10
 
+    def _level_fusable(self, owner, i_level: int, jitter, stratified: bool) -> bool:
+        """A proposal level runs as one launch (ops.proposal_level) when its field is a fused-shape
+        HashMLPDensityField and the jitter is per ray (the reference's use_single_jitter) or absent (evaluation)."""
+        if not ops.fused_level_enabled() or owner is None or not hasattr(owner, "_fused_ok") or not owner._fused_ok():
+            return False
+        if getattr(owner, "_norm", None) is None:
+            return False
+        if not isinstance(self.initial_sampler, UniformLinDispPiecewiseSampler) and i_level == 0:
+            return False
+        if stratified:
+            if jitter is None or not (getattr(self.initial_sampler, "single_jitter", False) and self.pdf_sampler.single_jitter):
+                return False
+            if any(t is not None and t.shape[-1] != 1 for t in (jitter[i_level], jitter[i_level + 1])):
+                return False
+        return True
+
     def generate_ray_samples(self, ray_bundle: Optional[RayBundle] = None, density_fns: Optional[List[Callable]] = None,
                              jitter=None) -> Tuple[RaySamples, List, List]:
         """``jitter`` (optional [t_rand0, rand1, rand2]) injects the random draws, for parity tests."""
@@ -158,26 +174,61 @@ class ProposalNetworkSampler(nn.Module):
             # one launch draws the per-ray jitter of every level (the samplers would draw [R,1] each)
             dev = ray_bundle.origins.device
             jitter = torch.rand((n + 1, ray_bundle.origins.shape[0], 1), dtype=torch.float32, device=dev).unbind(0)
+        stratified = self.training and getattr(self.initial_sampler, "train_stratified", False) \
+            and self.pdf_sampler.train_stratified
+        next_bins = None  # (spacing, euclidean) bins of the coming level, produced by the previous level's fused pass
         for i_level in range(n + 1):
             is_prop = i_level < n
             num_samples = self.num_proposal_samples_per_ray[i_level] if is_prop else self.num_nerf_samples_per_ray
             j = None if jitter is None else jitter[i_level]
-            if i_level == 0:
+            fn = density_fns[i_level] if is_prop else None
+            owner = getattr(fn, "__self__", None) if is_prop else None
+            train_level = is_prop and updated and torch.is_grad_enabled()
+            # A level that trains runs on its own CUDA stream.  The forward gains nothing (the next level waits
+            # for these weights) but autograd replays each node on the stream of its forward, so the backward of
+            # the proposal fields (atomics-bound table scatters) overlaps the main field's backward (tensor-core
+            # MLPs + its own scatter) instead of queueing behind it.  Works the same under CUDA-graph capture.
+            side = self._side_stream(i_level, ray_bundle.origins.device) if (train_level and self.side_streams) else None
+            cur = torch.cuda.current_stream() if side is not None else None
+            if is_prop and self._level_fusable(owner, i_level, jitter, stratified):
+                # ONE launch: [initial sampler] -> field -> weights + median depth -> the next level's bins
+                num_next = (self.num_proposal_samples_per_ray[i_level + 1] if i_level + 1 < n
+                            else self.num_nerf_samples_per_ray)
+                net = owner.mlp_base[1]
+                (W1, W2), (b1, b2) = net.weights_biases()
+                enc = owner.encoding
+                if side is not None:
+                    side.wait_stream(cur)
+                with torch.set_grad_enabled(train_level), (torch.cuda.stream(side) if side is not None else contextlib.nullcontext()):
+                    sb_in, eb_in = next_bins if next_bins is not None else (None, None)
+                    w, dmed, sb, eb, nsb, neb = ops.proposal_level(
+                        enc.hash_table, enc.grid, owner._norm, W1, b1, W2, b2, ray_bundle.origins, ray_bundle.directions,
+                        ray_bundle.nears, ray_bundle.fars, num_samples, num_next, sbins=sb_in, ebins=eb_in,
+                        t_rand=j if (i_level == 0 and stratified) else None,
+                        rand=(jitter[i_level + 1] if stratified else None), anneal=float(self._anneal),
+                        anneal_dev=self.pdf_sampler.anneal_dev, histogram_padding=self.pdf_sampler.histogram_padding)
+                    weights = w[..., None]
+                    weights._nkbs_depth_med = dmed[..., None]
+                if side is not None:
+                    cur.wait_stream(side)
+                    for t in (w, dmed, sb, eb, nsb, neb):
+                        t.record_stream(cur)
+                ray_samples = ray_bundle.samples_from_bins(
+                    sb, eb, _make_s2e(ray_bundle.nears, ray_bundle.fars) if i_level == 0 else ray_samples.spacing_to_euclidean_fn)
+                next_bins = (nsb, neb)
+                weights_list.append(weights)
+                ray_samples_list.append(ray_samples)
+                continue
+            if next_bins is not None:
+                ray_samples = ray_bundle.samples_from_bins(next_bins[0], next_bins[1], ray_samples.spacing_to_euclidean_fn)
+                next_bins = None
+            elif i_level == 0:
                 ray_samples = self.initial_sampler(ray_bundle, num_samples=num_samples, t_rand=j)
             else:
                 # pow(weights, anneal) happens inside the PDF kernel
                 ray_samples = self.pdf_sampler(ray_bundle, ray_samples, weights, num_samples=num_samples, rand=j,
                                                anneal=float(self._anneal))
             if is_prop:
-                fn = density_fns[i_level]
-                owner = getattr(fn, "__self__", None)
-                train_level = updated and torch.is_grad_enabled()
-                # A level that trains runs on its own CUDA stream.  The forward gains nothing (the next level waits
-                # for these weights) but autograd replays each node on the stream of its forward, so the backward of
-                # the proposal fields (atomics-bound table scatters) overlaps the main field's backward (tensor-core
-                # MLPs + its own scatter) instead of queueing behind it.  Works the same under CUDA-graph capture.
-                side = self._side_stream(i_level, ray_bundle.origins.device) if (train_level and self.side_streams) else None
-                cur = torch.cuda.current_stream() if side is not None else None
                 if side is not None:
                     side.wait_stream(cur)
                 with torch.set_grad_enabled(train_level), (torch.cuda.stream(side) if side is not None else contextlib.nullcontext()):

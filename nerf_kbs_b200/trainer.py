@@ -60,6 +60,17 @@ def allreduce_mean_(tensors: Sequence[torch.Tensor], group=None, world_size: Opt
             off += n
 
 
+def _detach_tree(x):
+    """Same nesting with every tensor detached; ray-sample containers keep their bin arrays only."""
+    if isinstance(x, torch.Tensor):
+        return x.detach()
+    if isinstance(x, dict):
+        return {k: _detach_tree(v) for k, v in x.items()}
+    if isinstance(x, (list, tuple)):
+        return type(x)(_detach_tree(v) for v in x)
+    return x
+
+
 def shard_rays(num_rays_total: int, rank: int, world_size: int) -> range:
     """Strong-scaling split used by the reference's datamanager: ``train_num_rays_per_batch // world_size``
     rays per rank (ref:dataparser/datamanager_z.py:225-231)."""
@@ -101,11 +112,24 @@ class Trainer:
             self.arena = ParamArena(groups)
             self.opt = ArenaAdam(self.arena, lr=lr, betas=betas, eps=eps)
         self.keep_grads = bool(keep_grads)
+        # Deferred optimizer step of the "fields" group: its Adam (a 0.6 GB stream over the main table, gradient and
+        # moments) runs at the START of the next step on a side stream, beside the proposal levels' forward — which
+        # reads none of those parameters — and is joined before the main field's forward.  Same updates in the same
+        # order; only the schedule changes.  flush() applies a pending update (called for you before any forward of the
+        # model outside train_step, by close() and by state readers).  NKBS_DEFER_ADAM=0 keeps Adam at the step's end.
+        self.defer_adam = os.environ.get("NKBS_DEFER_ADAM", "1") != "0" and not self.keep_grads
+        self._pending = False
+        self._in_step = False
+        self._join_adam = False
+        self._adam_stream = torch.cuda.Stream(p0.device, priority=0)   # lowest priority: fills what the step leaves idle
+        self._step_stream = torch.cuda.Stream(p0.device, priority=-1)  # captured steps run at high priority
+        self._hooks = [model.register_forward_pre_hook(self._pre_model_forward),
+                       model.field.register_forward_pre_hook(self._pre_field_forward)]
         self._inv_world = torch.full((), 1.0 / self.world_size, device=p0.device) if self.world_size > 1 else None
         self.use_graph = use_graph
         self.graph_warmup = graph_warmup
         self.step = 0
-        self._graphs: Dict[bool, torch.cuda.CUDAGraph] = {}
+        self._graphs: Dict = {}  # (updated, pending deferred Adam) -> captured step
         self._graph_loss: Dict[bool, Dict[str, torch.Tensor]] = {}
         self._graph_outputs: Dict[bool, Dict] = {}
         self.outputs: Dict = {}  # model outputs of the last step (graph replays: the captured static tensors)
@@ -189,8 +213,31 @@ class Trainer:
         ``updated`` gating lets them train; torch.optim.Adam skips them otherwise (``grad is None``)."""
         return [k for k in self.arena.layout if updated or k != "proposal_networks"]
 
+    def _pre_model_forward(self, module, args):
+        if self._pending and not self._in_step:
+            self.flush()  # somebody evaluates the model between steps: the parameters must be up to date
+
+    def _pre_field_forward(self, module, args):
+        if self._join_adam:  # the main field reads the parameters the side-stream Adam is writing
+            torch.cuda.current_stream(self.device).wait_stream(self._adam_stream)
+            self._join_adam = False
+
+    def flush(self) -> None:
+        """Apply the deferred optimizer step of the previous ``train_step`` now (no-op when nothing is pending)."""
+        if self._pending:
+            self._run_adam(self.deferred_groups())
+            self._pending = False
+
+    def deferred_groups(self) -> List[str]:
+        return [k for k in self.arena.layout if k != "proposal_networks"]
+
     def optimizer_step(self, updated: bool = True) -> None:
-        active = self.active_groups(updated)
+        """Adam on every group that received gradients (eager callers; train_step schedules the groups itself)."""
+        self._run_adam(self.active_groups(updated))
+
+    def _run_adam(self, active: List[str]) -> None:
+        if not active:
+            return
         if self.sharded is not None:
             self.sharded.step(active)
             return
@@ -199,12 +246,24 @@ class Trainer:
                 dist.all_reduce(self.arena.group_slice(name, self.arena.G), op=dist.ReduceOp.SUM, group=self.group)
         self.opt.step(active, inv_scale=self._inv_world, zero_grads=not self.keep_grads)
 
-    def _step_body(self, updated: bool) -> Dict[str, torch.Tensor]:
+    def _step_body(self, updated: bool, pending: bool = False) -> Dict[str, torch.Tensor]:
         if self.keep_grads:
             self.zero_grad()
+        if pending:
+            # the previous step's Adam of the deferred groups, beside the proposal levels of this step
+            cur = torch.cuda.current_stream(self.device)
+            self._adam_stream.wait_stream(cur)
+            with torch.cuda.stream(self._adam_stream):
+                self._run_adam(self.deferred_groups())
+            self._join_adam = True
         jitter = list(self.jitter.unbind(0)) if self.jitter is not None else None
-        outputs = self.model(self._bundle(), jitter=jitter)
-        self.outputs = outputs
+        self._in_step = True
+        try:
+            outputs = self.model(self._bundle(), jitter=jitter)
+        finally:
+            self._in_step = False
+        if self._join_adam:  # a model that never called its field
+            self._pre_field_forward(None, None)
         batch = {"image": self.buf["image"]}
         if self.needs_labels:
             batch["semantics_label"] = self.buf["semantics_label"]
@@ -217,19 +276,26 @@ class Trainer:
             loss_dict = self.model.get_loss_dict(outputs, batch)
             loss = sum(loss_dict.values())
         loss.backward()
-        self.optimizer_step(updated)
+        # detached views only: a reference to the live outputs would keep this step's autograd graph — and with it the
+        # parameters' AccumulateGrad nodes, bound to THIS step's stream — alive into the next step's capture
+        self.outputs = _detach_tree(outputs)
+        del outputs
+        if self.defer_adam:
+            self._run_adam([k for k in self.active_groups(updated) if k not in self.deferred_groups()])
+        else:
+            self._run_adam(self.active_groups(updated))
         out = {k: v.detach() for k, v in loss_dict.items()}
         out["loss"] = loss.detach()
         return out
 
-    def _capture(self, key: bool) -> None:
+    def _capture(self, key) -> None:
         g = torch.cuda.CUDAGraph()
         if self._pool is None:
             self._pool = torch.cuda.graph_pool_handle()
         torch.cuda.synchronize(self.device)
         c0 = sum(_lib.call_counts.values())
-        with torch.cuda.graph(g, pool=self._pool):
-            out = self._step_body(key)
+        with torch.cuda.graph(g, pool=self._pool, stream=self._step_stream):
+            out = self._step_body(*key)
         self._calls_per_graph[key] = sum(_lib.call_counts.values()) - c0
         self._graphs[key] = g
         self._graph_loss[key] = out
@@ -238,6 +304,10 @@ class Trainer:
     def close(self) -> None:
         """Drop the captured graphs and detach the parameters from the gradient arena.  Call before tearing the
         process group down: a CUDA graph that captured a collective keeps its communicator referenced."""
+        self.flush()
+        for h in self._hooks:
+            h.remove()
+        self._hooks = []
         self._graphs.clear()
         self._graph_loss.clear()
         self._graph_outputs.clear()
@@ -254,7 +324,7 @@ class Trainer:
             self.train_step()
         gated = self.model.__class__.__name__ != "SemanticNerfWModel"  # no step_cb there: always updated
         for key in ((True, False) if gated else (True,)):
-            if key not in self._graphs:
+            if (key, self._pending) not in self._graphs:
                 sampler.force_updated = key
                 try:
                     self.train_step()
@@ -276,13 +346,14 @@ class Trainer:
         m.set_step(self.step)
         self.anneal_t.fill_(float(m.proposal_sampler._anneal))  # scalar travels as a kernel argument
         updated = bool(m.proposal_sampler.will_update())
+        key = (updated, self._pending)
         if self.use_graph and self._eager_steps >= self.graph_warmup:
-            if updated not in self._graphs:
-                self._capture(updated)
-            self._graphs[updated].replay()
-            self.nkbs_calls += self._calls_per_graph[updated]
-            out = self._graph_loss[updated]
-            self.outputs = self._graph_outputs[updated]
+            if key not in self._graphs:
+                self._capture(key)
+            self._graphs[key].replay()
+            self.nkbs_calls += self._calls_per_graph[key]
+            out = self._graph_loss[key]
+            self.outputs = self._graph_outputs[key]
             if updated:  # the eager path resets this inside the sampler; the replay has no host side
                 m.proposal_sampler._steps_since_update = 0
         else:
@@ -292,12 +363,13 @@ class Trainer:
                 s = torch.cuda.Stream(self.device)
                 s.wait_stream(torch.cuda.current_stream(self.device))
                 with torch.cuda.stream(s):
-                    out = self._step_body(updated)
+                    out = self._step_body(*key)
                 torch.cuda.current_stream(self.device).wait_stream(s)
             else:
-                out = self._step_body(updated)
+                out = self._step_body(*key)
             self._eager_steps += 1
             self.nkbs_calls += sum(_lib.call_counts.values()) - c0
+        self._pending = self.defer_adam
         m.after_step(self.step)
         self.step += 1
         self.loss_dict = out

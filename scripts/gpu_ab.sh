@@ -1,13 +1,21 @@
 #!/bin/bash
-# quick pass after a kernel change: encode / model parity tests, then the kernel tables of both bench sizes
+# A/B of env toggles on ONE box: usage gpu_ab.sh [--args "<bench args>"] "<VAR=a VAR2=b>" "<VAR=c>" ...
+cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?"; tail -3 gpurun_out/pytest_gpu.log
-for R in 4096 65536; do
-  timeout 300 python bench.py --rays $R --steps 50 --warmup 5 --no-cpu-baseline --no-render > gpurun_out/ab_$R.json 2> gpurun_out/ab_$R.err; echo "bench $R exit $?"
-  python - <<PY
+EXTRA=""
+if [ "$1" == "--args" ]; then EXTRA="$2"; shift 2; fi
+for rep in 1 2; do
+  for cfg in "$@"; do
+    tag=$(echo "$cfg" | tr -c 'A-Za-z0-9=' '_')
+    env $cfg timeout 600 python bench.py --steps 100 --warmup 10 --no-cpu-baseline --no-render --no-legs --no-kernel-pass $EXTRA > gpurun_out/ab_${tag}_${rep}.json 2> gpurun_out/ab_${tag}_${rep}.err
+    python - <<PY
 import json
-d=json.loads(open("gpurun_out/ab_$R.json").read().strip().splitlines()[-1])
-print($R, "ms/step", round(d["ms_per_step"],4), "e2e", round(d["e2e"]["ms_per_step"],4))
-for k,v in d["kernels"].items(): print("  ",k, v["ms_per_step"], v["achieved"], v["unit"])
+try:
+    d=json.load(open("gpurun_out/ab_${tag}_${rep}.json"))
+    print("$cfg rep $rep: ms/step %.4f  e2e %.4f  loss %.5f" % (d["ms_per_step"], d["e2e"]["ms_per_step"], d["final_loss"]))
+except Exception as e:
+    print("$cfg rep $rep: FAILED", e)
+    print(open("gpurun_out/ab_${tag}_${rep}.err").read()[-600:])
 PY
+  done
 done

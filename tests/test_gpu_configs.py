@@ -108,42 +108,76 @@ def test_config2_semantic_nerfw_8192_rays_tc_graph_trainer_tracks_oracle():
     _run_config("semantic_nerfw", 8192, 3, dict(use_semantic=True, use_transient_embedding=True), labels=True)
 
 
-# measured on the B200 (driver smoke, round 1): 4.75e-2 relative L2 on the main table at R = 256; bars are <= 2x that
-GRAD_BARS = {"hash_table": 9e-2, "default": 9e-2}
+def _round_field_mlps_to_fp16(om):
+    """The oracle with the weights of the main field's MLPs rounded to fp16 (what the tensor-core path feeds its
+    GEMMs): the change of each gradient tensor under that perturbation is the tensor's mixed-precision noise floor."""
+    import copy
+    pm = copy.deepcopy(om)
+    with torch.no_grad():
+        for name, p in pm.field.named_parameters():
+            if p.dim() == 2 and p.shape[1] != 2 and "embedding" not in name:
+                p.copy_(p.half().float())
+    return pm
+
+
+def _all_grad_pairs(nm, om):
+    pairs = [("field." + n, a, b) for n, a, b in field_grad_pairs(nm.field, om.field)]
+    for i, (a, b) in enumerate(zip(nm.proposal_networks, om.proposal_networks)):
+        pairs += [(f"prop{i}." + n, x, y) for n, x, y in density_grad_pairs(a, b)]
+    return pairs
 
 
 @pytest.mark.parametrize("kind,R", [("nerfacto", 4096), ("semantic_nerfw", 8192)])
 def test_config_gradients_per_tensor(kind, R):
-    """First step of the configurations above with the gradients left in the arena: relative L2 per parameter
-    tensor against the oracle's autograd, mixed-precision MLPs, reported and bounded."""
+    """Gradients of the configurations above, per parameter tensor, accumulated into the step driver's arena by the
+    backward kernels: relative L2 against the oracle's autograd.  fp32 MLP kernels: 2e-2 on every tensor (the bar of the
+    fp32 end-to-end tests).  Mixed precision: 9e-2 (2x the 4.75e-2 measured on the main table by the round-1 driver
+    smoke) or 4x the tensor's own mixed-precision noise floor, whichever is larger — the floor is what the ORACLE's
+    gradient moves by when the field MLP weights are rounded to fp16: tensors whose gradient is a near-cancelling sum
+    (proposal networks through the clipped interlevel loss, first-layer weights behind the table) move by tens of
+    percent under that rounding in the oracle itself, so no 16-bit path can be held tighter there.  All numbers are
+    printed."""
     cfg = dict() if kind == "nerfacto" else dict(use_semantic=True, use_transient_embedding=True)
     om, nm = _pair(kind, **cfg)
-    ops.set_mlp_precision("tc")
-    tr = Trainer(nm, R, use_graph=False, inject_jitter=True, keep_grads=True)
     rb = O.synthetic_ray_bundle(R, seed=20)
     g = torch.Generator().manual_seed(40)
     batch = {"image": torch.rand(R, 3, generator=g)}
     if kind != "nerfacto":
         batch["semantics_label"] = torch.randint(0, 19, (R,), generator=g)
     jit = make_jitter(R, seed=60)
-    out = om(rb, jitter=jit)
-    sum(om.get_loss_dict(out, batch).values()).backward()
-    tr.train_step(to_nk_bundle(rb, DEV), {k: v.to(DEV) for k, v in batch.items()}, jitter=[j.to(DEV) for j in jit])
-    torch.cuda.synchronize()
-    pairs = [("field." + n, a, b) for n, a, b in field_grad_pairs(nm.field, om.field)]
-    for i, (a, b) in enumerate(zip(nm.proposal_networks, om.proposal_networks)):
-        pairs += [(f"prop{i}." + n, x, y) for n, x, y in density_grad_pairs(a, b)]
-    worst = []
-    for name, got, want in pairs:
-        if want is None:
-            continue
-        assert got is not None, name
-        e = _rel_l2(got, want)
-        print(f"[{kind} R={R}] grad {name}: relative L2 {e:.3e} (|oracle| {want.norm().item():.3e})")
-        bar = GRAD_BARS["hash_table"] if name.endswith("hash_table") else GRAD_BARS["default"]
-        if e > bar:
-            worst.append((name, e))
-    assert not worst, worst
+    sum(om.get_loss_dict(om(rb, jitter=jit), batch).values()).backward()
+    pm = _round_field_mlps_to_fp16(om)
+    pm.zero_grad()
+    sum(pm.get_loss_dict(pm(rb, jitter=jit), batch).values()).backward()
+    floor = {n: _rel_l2(gp, go) for (n, gp), (_, go) in zip(
+        [(n, p.grad) for n, p in pm.named_parameters() if p.grad is not None],
+        [(n, p.grad) for n, p in om.named_parameters() if p.grad is not None])}
+    # noise floor by tensor in the naming of the grad pairs: match through the oracle gradient tensor itself
+    floor_by_id = {id(p.grad): floor[n] for n, p in om.named_parameters() if p.grad is not None}
+    tr = Trainer(nm, R, use_graph=False, inject_jitter=True, keep_grads=True)  # parameters + gradients in the arena
+    nb, nbatch = to_nk_bundle(rb, DEV), {k: v.to(DEV) for k, v in batch.items()}
+    njit = [j.to(DEV) for j in jit]
+    failures = []
+    for prec in ("fp32", "tc"):
+        ops.set_mlp_precision(prec)
+        tr.zero_grad()
+        out = nm(nb, jitter=njit)
+        fused = nm.get_loss_total(out, nbatch) if hasattr(nm, "get_loss_total") else None
+        loss = fused[0] if fused is not None else sum(nm.get_loss_dict(out, nbatch).values())
+        loss.backward()
+        torch.cuda.synchronize()
+        for name, got, want in _all_grad_pairs(nm, om):
+            if want is None:
+                continue
+            assert got is not None, name
+            e = _rel_l2(got, want)
+            fl = floor_by_id.get(id(want), 0.0)
+            bar = 2e-2 if prec == "fp32" else max(9e-2, 4.0 * fl)
+            print(f"[{kind} R={R} {prec}] grad {name}: relative L2 {e:.3e} (|oracle| {want.norm().item():.3e}, "
+                  f"fp16-weight noise floor {fl:.3e}, bar {bar:.1e})")
+            if e > bar:
+                failures.append((prec, name, e, bar))
+    assert not failures, failures
 
 
 # ------------------------------------------------------------------------------------------------

@@ -293,4 +293,6 @@ def test_tensor_core_train_step_gradients():
     for name, g, w in pairs:
         g, w = g.detach().float().cpu(), w.detach().float().cpu()
         e = ((g - w).norm() / (w.norm() + 1e-30)).item()
-        assert e <= 0.15, f"grad {name}: relative L2 error {e:.3e}"
+        print(f"[tc grads R={R}] {name}: relative L2 {e:.3e}")
+        # measured on the B200 (round 1 driver smoke): 4.75e-2 on the main table; the bar is 2x the measurement
+        assert e <= 9e-2, f"grad {name}: relative L2 error {e:.3e}"

@@ -102,6 +102,7 @@ def test_gated_steps_leave_proposal_optimizer_state_alone():
     rb = O.synthetic_ray_bundle(R, seed=1)
     batch = {"image": torch.rand(R, 3, generator=torch.Generator().manual_seed(2)).to(DEV)}
     tr.train_step(to_nk_bundle(rb, DEV), batch)  # eager, updated (step 0 < 10)
+    tr.flush()  # the field group's Adam is deferred into the next step: apply it now
     before = nm.proposal_networks[0].encoding.hash_table.detach().clone()
     t_prop, t_field = float(tr.opt.step_t["proposal_networks"]), float(tr.opt.step_t["fields"])
     nm.proposal_sampler.force_updated = False
@@ -110,6 +111,7 @@ def test_gated_steps_leave_proposal_optimizer_state_alone():
             tr.train_step(to_nk_bundle(rb, DEV), batch)
     finally:
         nm.proposal_sampler.force_updated = None
+    tr.flush()
     assert float(tr.opt.step_t["proposal_networks"]) == t_prop
     assert float(tr.opt.step_t["fields"]) == t_field + 3
     assert torch.equal(nm.proposal_networks[0].encoding.hash_table.detach(), before)
@@ -143,7 +145,7 @@ def test_graph_step_equals_eager_step():
             ls.append(tr.train_step(to_nk_bundle(rb, DEV), batch).item())
         losses[mode] = ls
         if mode:
-            assert set(tr._graphs) == {True, False}
+            assert set(tr._graphs) == {(True, True), (False, True)}  # (proposal gating, deferred Adam pending)
     # the jitter draws differ between eager and replayed RNG consumption only if the philox offsets diverge
     for a, b in zip(losses[False], losses[True]):
         assert abs(a - b) <= 2e-4 * abs(a), (losses[False], losses[True])
@@ -163,6 +165,7 @@ def test_fused_loss_route_equals_loss_dict_route():
         ls = []
         for _ in range(6):
             ls.append(tr.train_step(to_nk_bundle(rb, DEV), batch).item())
+        tr.flush()
         runs[fused] = (ls, {k: v.item() for k, v in tr.loss_dict.items()}, nm)
     for a, b in zip(runs[False][0], runs[True][0]):
         assert abs(a - b) <= 1e-5 * abs(a), (runs[False][0], runs[True][0])
@@ -254,3 +257,38 @@ def test_fused_dp_step_equals_nccl_route():
         # Adam (eps 1e-15) moves an entry whose gradient is summation-order noise by about lr per step in either
         # direction (nerf_kbs_b200/dp_check.py)
         assert d["rank_spread"] == 0.0 and d["ok"], d
+
+
+def test_deferred_adam_equals_adam_at_step_end():
+    """The field group's Adam overlapped with the next step's proposal levels (default) against Adam at the end of the
+    step (NKBS_DEFER_ADAM=0): same updates in the same order, so the losses of every step and the parameters after a
+    flush agree to rounding of the atomics order; an evaluation between steps sees flushed parameters."""
+    import os
+    R = 512
+    rb = O.synthetic_ray_bundle(R, seed=8)
+    batch = {"image": torch.rand(R, 3, generator=torch.Generator().manual_seed(9)).to(DEV)}
+    runs = {}
+    for defer in ("0", "1"):
+        os.environ["NKBS_DEFER_ADAM"] = defer
+        try:
+            _, nm = _train_pair(R, 0, True)
+            tr = Trainer(nm, R, use_graph=True, graph_warmup=1, inject_jitter=True)
+        finally:
+            os.environ.pop("NKBS_DEFER_ADAM", None)
+        assert tr.defer_adam == (defer == "1")
+        ls = []
+        for i in range(8):
+            ls.append(tr.train_step(to_nk_bundle(rb, DEV), batch, jitter=[j.to(DEV) for j in make_jitter(R, seed=30 + i)]).item())
+            if i == 4:  # an evaluation between two steps must see the updated parameters
+                nm.eval()
+                with torch.no_grad():
+                    ev = nm(to_nk_bundle(rb, DEV))["rgb"].clone()
+                nm.train()
+                assert not tr._pending
+        tr.flush()
+        runs[defer] = (ls, ev, nm.field.mlp_head.layers[0].weight.detach().clone(), nm.field.mlp_base_grid.hash_table.detach().clone())
+    for a, b in zip(runs["0"][0], runs["1"][0]):
+        assert abs(a - b) <= 2e-4 * abs(a), (runs["0"][0], runs["1"][0])
+    assert rel_err(runs["1"][1], runs["0"][1]) < 2e-3
+    assert rel_err(runs["1"][2], runs["0"][2]) < 5e-2   # Adam eps = 1e-15 noise, see test_training_loop_tracks_oracle
+    assert rel_err(runs["1"][3], runs["0"][3]) < 2e-2
