@@ -255,6 +255,19 @@ int nkbs_apply_depth_colormap(int64_t N, const float* depth, const float* accumu
                               int32_t have_near, float near_plane, int32_t have_far, float far_plane,
                               int32_t* minmax_ws, float* rgb, void* stream);
 
+/* Expected depth (DepthRenderer("expected")) of R rays with NO allocation by the library or the caller beyond inputs
+ * and output: the scratch that nkbs_composite_fwd takes from the caller (unclipped depth per ray, the batch-wide
+ * min / max sample position) lives in a device array built into the library (4 MiB + 256 B per GPU that loads it, held
+ * until exit).  weights [R,S], starts / ends [R,S] with row stride bin_stride (0 = S), depth out [R].
+ * R > NKBS_NOALLOC_MAX_RAYS is refused (-1, nkbs_last_error says so).  Calls no cudaMalloc / cudaFree; capturable.
+ * All calls share the scratch: calls that overlap on the GPU (different streams, concurrent graphs) race on it;
+ * calls ordered on one stream are safe (every call re-initialises what it reads).
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it). */
+#define NKBS_NOALLOC_MAX_RAYS (1 << 20)
+int nkbs_expected_depth_noalloc(int64_t R, int32_t S, const float* weights, const float* starts, const float* ends,
+                                int32_t bin_stride, float* depth, void* stream);
+
 /* Zero `bytes` bytes of device memory on `stream` (cudaMemsetAsync: a memset node inside a captured CUDA graph).
  * Used for gradient buffers that cannot be re-zeroed by the optimizer kernel that reads them (peers still read
  * them over NVLink until the closing barrier of nkbs_dp_adam_step).

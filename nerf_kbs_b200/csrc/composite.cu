@@ -4,6 +4,7 @@
 // (SURVEY a11, a13-a18, A.8).
 #include <float.h>
 #include "common.cuh"
+#include "nkbs.h"
 
 namespace {
 
@@ -418,5 +419,66 @@ extern "C" int nkbs_composite_bwd(int64_t R, int32_t S, const float* density, co
   }
   composite_bwd_kernel<<<comp_grid(R), kThreads, smem, (cudaStream_t)stream>>>(a);
   NKBS_CHECK_LAUNCH("nkbs_composite_bwd");
+  return 0;
+}
+
+// ---- expected depth without any allocation by anybody (no counterpart in the reference) -------
+// DepthRenderer("expected") needs two pieces of scratch besides its output: the unclipped depth of every ray and the
+// batch-wide minimum / maximum sample position it is clipped to.  nkbs_composite_fwd takes them from the caller; this
+// variant keeps them in a file-scope device array, so a caller that may not allocate (CUDA-graph capture, a tight
+// serving loop, a harness that forbids cudaMalloc) passes inputs and the output only.  The array is part of the
+// library image: every GPU that loads libnkbs.so holds its 4 MiB + 256 B until the process exits.  All calls share it
+// and it keeps the last call's contents: the min / max keys are re-initialised by every call and the raw depths of rays
+// [0, R) are overwritten before they are read; two calls that overlap on the GPU (different streams) race on it.
+namespace {
+constexpr int64_t kNoAllocMaxRays = NKBS_NOALLOC_MAX_RAYS;  // include/nkbs.h
+constexpr int kNoAllocHeader = 256;  // bytes: the two ordered-int min / max keys, padded to the array's alignment
+constexpr int kNoAllocMaxDevices = 64;
+}  // namespace
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocHeader + kNoAllocMaxRays * sizeof(float)];
+
+namespace {
+// Device address of g_noalloc_scratch on the CURRENT device.  In host code the array's name is only a stand-in for
+// the symbol, not a device pointer: the address comes from cudaGetSymbolAddress, asked once per device with that device
+// current, and is cached per device ordinal (racing first calls store the same value).
+int noalloc_scratch(unsigned char** out) {
+  static void* cache[kNoAllocMaxDevices] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  NKBS_CHECK_ARG(e == cudaSuccess, "nkbs_expected_depth_noalloc: cudaGetDevice: %s", cudaGetErrorString(e));
+  NKBS_CHECK_ARG(dev >= 0 && dev < kNoAllocMaxDevices, "nkbs_expected_depth_noalloc: device ordinal %d not supported", dev);
+  void* p = __atomic_load_n(&cache[dev], __ATOMIC_ACQUIRE);
+  if (!p) {
+    e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    NKBS_CHECK_ARG(e == cudaSuccess && p, "nkbs_expected_depth_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+    __atomic_store_n(&cache[dev], p, __ATOMIC_RELEASE);
+  }
+  *out = static_cast<unsigned char*>(p);
+  return 0;
+}
+}  // namespace
+
+extern "C" int nkbs_expected_depth_noalloc(int64_t R, int32_t S, const float* weights, const float* starts,
+                                           const float* ends, int32_t bin_stride, float* depth, void* stream) {
+  NKBS_CHECK_ARG(R >= 0 && S >= 1 && S <= kMaxS, "nkbs_expected_depth_noalloc: S=%d outside 1..%d", S, kMaxS);
+  NKBS_CHECK_ARG(R <= kNoAllocMaxRays,
+                 "nkbs_expected_depth_noalloc: %lld rays exceed the built-in scratch of %lld rays (split the batch, or use "
+                 "nkbs_composite_fwd with caller-owned scratch)", (long long)R, (long long)kNoAllocMaxRays);
+  if (R == 0) return 0;
+  NKBS_CHECK_ARG(weights && starts && ends && depth, "nkbs_expected_depth_noalloc: null argument");
+  NKBS_CHECK_ARG(bin_stride == 0 || bin_stride >= S, "nkbs_expected_depth_noalloc: bin_stride %d < S", bin_stride);
+  unsigned char* scratch = nullptr;
+  if (noalloc_scratch(&scratch)) return -1;
+  int* mm = reinterpret_cast<int*>(scratch);
+  float* raw = reinterpret_cast<float*>(scratch + kNoAllocHeader);
+  cudaStream_t st = (cudaStream_t)stream;
+  CompArgs a{R, S, nullptr, weights, starts, ends, bin_stride ? bin_stride : S, nullptr, nullptr, 0, 0, 0,
+             nullptr, nullptr, nullptr, raw, nullptr, nullptr, mm};
+  minmax_init_kernel<<<1, 1, 0, st>>>(mm);
+  const size_t smem = (size_t)kWarpsPerCta * strip_len(S) * sizeof(float);
+  composite_fwd_kernel<<<comp_grid(R), kThreads, smem, st>>>(a);
+  NKBS_CHECK_LAUNCH("nkbs_expected_depth_noalloc");
+  clip_depth_kernel<<<(int)((R + 255) / 256), 256, 0, st>>>(raw, mm, R, depth, nullptr);
+  NKBS_CHECK_LAUNCH("nkbs_expected_depth_noalloc(clip)");
   return 0;
 }
