@@ -150,6 +150,9 @@ __device__ __forceinline__ float row_total(const float* scratch, int lane) {
 #ifndef NKBS_DENSITY_BWD_MMA
 #define NKBS_DENSITY_BWD_MMA 1
 #endif
+#ifndef NKBS_DENSITY_BWD_MMA_MAXH
+#define NKBS_DENSITY_BWD_MMA_MAXH 64  // 16: only the nerfacto proposal shape takes the tensor-core route (A/B builds)
+#endif
 constexpr int kTileStride = 20;
 
 __device__ __forceinline__ void split_tf32(float v, uint32_t& hi, uint32_t& lo) {
@@ -176,11 +179,35 @@ __device__ __forceinline__ void mma_3xtf32(float (&d)[4], const float (&a)[4], c
   mma_tf32(d, ah, bh);
 }
 
-// A fragment of the k-step `ks` (samples 8ks .. 8ks+7) from a [32 samples][16] tile read TRANSPOSED (row = column
-// of the tile, contraction index = sample): a0 (g, t), a1 (g+8, t), a2 (g, t+4), a3 (g+8, t+4), g = lane/4, t = lane%4
-__device__ __forceinline__ void load_a_transposed(const float* tile, int ks, int g, int t, float (&a)[4]) {
-  const float* r0 = tile + (8 * ks + t) * kTileStride;
-  const float* r1 = r0 + 4 * kTileStride;
+// Geometry of the tensor-core route for hidden width H (a multiple of 16) and K = 2L inputs: kMT m-tiles of 16 hidden
+// units, kNT n-tiles of 8 columns of [F | 1 | 0].  Per warp: tile A [32 samples][kStrideA] (relu(z), then GH) and tile
+// B [32 samples][kStrideB].  H = 16 keeps the layout it was tuned with (stride 20).  H = 64: strides = 4 mod 32 floats
+// keep the row-wise 128-bit stores conflict-free, and the contraction index k of an MMA step is mapped to the samples
+// (0, 2, 4, 6 | 1, 3, 5, 7) of its group of eight — any fixed permutation is legal as long as A and B use the same one —
+// so that the four rows a transposed fragment load touches start 8 banks apart: conflict-free as well.
+template <int H, int L>
+struct MmaGeom {
+  static constexpr int K = 2 * L;
+  static constexpr bool kMma = NKBS_DENSITY_BWD_MMA && (H % 16 == 0) && H <= NKBS_DENSITY_BWD_MMA_MAXH;
+  static constexpr int kMT = H / 16;
+  static constexpr int kNT = (K + 1 + 7) / 8;
+  static constexpr bool kPermute = H != 16;
+  static constexpr int kStrideA = H == 16 ? kTileStride : H + 4;
+  static constexpr int kStrideB = H == 16 ? kTileStride : 8 * kNT + 4;
+  static constexpr int kScratch = kMma ? 32 * (kStrideA + kStrideB) : 32 * kRedStride;  // floats per warp
+  static_assert(!kMma || (kStrideA % 4 == 0 && kStrideB % 4 == 0 && 8 * kNT <= kStrideB), "tile rows are float4 rows");
+  // sample (= lane) that contraction index kk (0..7) of k-step ks stands for
+  __device__ static __forceinline__ int sample(int ks, int kk) {
+    return 8 * ks + (kPermute ? ((kk & 3) * 2 + (kk >> 2)) : kk);
+  }
+};
+
+// A fragment of the k-step `ks` for m-tile `mt` from tile A read TRANSPOSED (row = hidden unit, contraction index =
+// sample): a0 (g, t), a1 (g+8, t), a2 (g, t+4), a3 (g+8, t+4), g = lane/4, t = lane%4
+template <typename G>
+__device__ __forceinline__ void load_a_transposed(const float* tile, int ks, int mt, int g, int t, float (&a)[4]) {
+  const float* r0 = tile + G::sample(ks, t) * G::kStrideA + 16 * mt;
+  const float* r1 = tile + G::sample(ks, t + 4) * G::kStrideA + 16 * mt;
   a[0] = r0[g];
   a[1] = r0[g + 8];
   a[2] = r1[g];
@@ -200,24 +227,36 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
   constexpr int kPasses = (kRows + 31) / 32;
   __shared__ float s_scale[NKBS_MAX_LEVELS];
   __shared__ __align__(16) Smem<H, L> s;
-  constexpr bool kMma = NKBS_DENSITY_BWD_MMA && H == 16 && K + 1 <= 16;
-  // transposed-sum scratch, or (tensor-core route) two [32][kTileStride] operand tiles per warp
-  constexpr int kScratch = kMma ? 2 * 32 * kTileStride : 32 * kRedStride;
-  __shared__ __align__(16) float s_red[kWarps][kScratch];
+  using G = MmaGeom<H, L>;
+  constexpr bool kMma = G::kMma;
+  constexpr int kMT = G::kMT, kNT = G::kNT;
+  // transposed-sum scratch, or (tensor-core route) the two operand tiles of every warp: dynamic shared memory
+  constexpr int kScratch = G::kScratch;
+  extern __shared__ __align__(16) float s_red[];  // [kWarps][kScratch]
   __shared__ float s_tot[kPasses * 32];
   if (threadIdx.x < NKBS_MAX_LEVELS) s_scale[threadIdx.x] = a.lv.scale[threadIdx.x];
   for (int e = threadIdx.x; e < kPasses * 32; e += kThreads) s_tot[e] = 0.f;
   stage<H, L>(a, s);
   __syncthreads();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  float* red = s_red[wid];
+  float* red = s_red + wid * kScratch;
   const uint32_t mask = a.lv.table_mask;
   float acc[kPasses];
 #pragma unroll
   for (int p = 0; p < kPasses; ++p) acc[p] = 0.f;
-  // tensor-core route: D1 = dW1|db1 as two 16x8 tiles (hidden unit x input column), D2 = dW2 in column 0 of one tile
-  float d1[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
-  float d2[4] = {0.f, 0.f, 0.f, 0.f};
+  // tensor-core route: D1 = dW1|db1 as kMT x kNT tiles of 16 x 8 (hidden unit x input column), D2 = dW2 in column 0 of
+  // one tile per m-tile
+  float d1[kMma ? kMT : 1][kMma ? kNT : 1][4];
+  float d2[kMma ? kMT : 1][4];
+#pragma unroll
+  for (int mt = 0; mt < (kMma ? kMT : 1); ++mt) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      d2[mt][i] = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < (kMma ? kNT : 1); ++nt) d1[mt][nt][i] = 0.f;
+    }
+  }
   float db2_acc = 0.f;
   const int fg = lane >> 2, ft = lane & 3;
   const int64_t n_round = (a.N + 31) / 32 * 32;  // whole warps reach the collectives
@@ -242,11 +281,11 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
     float g_out;
     if constexpr (kMma) {
       // ---- weight gradients on the tensor cores (see mma_3xtf32 above) ----
-      float* tA = red;                       // [32][kTileStride]: relu(z), then GH
-      float* tB = red + 32 * kTileStride;    // [32][kTileStride]: F | 1 | 0
-      float4* rowA = reinterpret_cast<float4*>(tA + lane * kTileStride);
-      float4* rowB = reinterpret_cast<float4*>(tB + lane * kTileStride);
-      uint32_t positive = 0u;  // bit j: hidden unit j is active for this sample
+      float* tA = red;                        // [32][kStrideA]: relu(z), then GH
+      float* tB = red + 32 * G::kStrideA;     // [32][kStrideB]: F | 1 | 0
+      float4* rowA = reinterpret_cast<float4*>(tA + lane * G::kStrideA);
+      float4* rowB = reinterpret_cast<float4*>(tB + lane * G::kStrideB);
+      uint64_t positive = 0ull;  // bit j: hidden unit j is active for this sample
 #pragma unroll
       for (int q = 0; q < H / 4; ++q) {
         float r[4];
@@ -255,7 +294,7 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
           const int j = 4 * q + i;
           const float zj = hidden_pre<H, L>(s, f, j);
           r[i] = fmaxf(zj, 0.f);
-          if (zj > 0.f) positive |= 1u << j;
+          if (zj > 0.f) positive |= 1ull << j;
           out = fmaf(s.w2[j], r[i], out);
         }
         rowA[q] = make_float4(r[0], r[1], r[2], r[3]);
@@ -266,11 +305,15 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
       // dW2 = RZ^T . g_out: B carries g_out in column 0 (k = sample), i.e. on the lanes with g == 0
 #pragma unroll
       for (int ks = 0; ks < 4; ++ks) {
-        float af[4];
-        load_a_transposed(tA, ks, fg, ft, af);
-        const float g0 = __shfl_sync(0xffffffffu, g_out, 8 * ks + ft), g1 = __shfl_sync(0xffffffffu, g_out, 8 * ks + ft + 4);
-        float bf[2] = {fg == 0 ? g0 : 0.f, fg == 0 ? g1 : 0.f};
-        mma_3xtf32(d2, af, bf);
+        const float g0 = __shfl_sync(0xffffffffu, g_out, G::sample(ks, ft));
+        const float g1 = __shfl_sync(0xffffffffu, g_out, G::sample(ks, ft + 4));
+        const float bf[2] = {fg == 0 ? g0 : 0.f, fg == 0 ? g1 : 0.f};
+#pragma unroll
+        for (int mt = 0; mt < kMT; ++mt) {
+          float af[4];
+          load_a_transposed<G>(tA, ks, mt, fg, ft, af);
+          mma_3xtf32(d2[mt], af, bf);
+        }
       }
       __syncwarp();
 #pragma unroll
@@ -279,7 +322,7 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const int j = 4 * q + i;
-          gq[i] = (positive >> j) & 1u ? g_out * s.w2[j] : 0.f;
+          gq[i] = (positive >> j) & 1ull ? g_out * s.w2[j] : 0.f;
           const float4* w = reinterpret_cast<const float4*>(s.w1 + j * KP);
 #pragma unroll
           for (int qq = 0; qq < KP / 4; ++qq) {
@@ -291,6 +334,9 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
           }
         }
         rowA[q] = make_float4(gq[0], gq[1], gq[2], gq[3]);
+      }
+#pragma unroll
+      for (int q = 0; q < 2 * kNT; ++q) {
         float e[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -303,15 +349,19 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
       // dW1 | db1 = GH^T . [F | 1]
 #pragma unroll
       for (int ks = 0; ks < 4; ++ks) {
-        float af[4];
-        load_a_transposed(tA, ks, fg, ft, af);
+        // B (k = sample, n = input column): b0 (t, g), b1 (t+4, g); the fragments of all n-tiles stay in registers
+        float bf[kNT][2];
 #pragma unroll
-        for (int nt = 0; nt < 2; ++nt) {
-          // B (k = sample, n = input column): b0 (t, g), b1 (t+4, g)
-          float bf[2];
-          bf[0] = tB[(8 * ks + ft) * kTileStride + 8 * nt + fg];
-          bf[1] = tB[(8 * ks + ft + 4) * kTileStride + 8 * nt + fg];
-          mma_3xtf32(d1[nt], af, bf);
+        for (int nt = 0; nt < kNT; ++nt) {
+          bf[nt][0] = tB[G::sample(ks, ft) * G::kStrideB + 8 * nt + fg];
+          bf[nt][1] = tB[G::sample(ks, ft + 4) * G::kStrideB + 8 * nt + fg];
+        }
+#pragma unroll
+        for (int mt = 0; mt < kMT; ++mt) {
+          float af[4];
+          load_a_transposed<G>(tA, ks, mt, fg, ft, af);
+#pragma unroll
+          for (int nt = 0; nt < kNT; ++nt) mma_3xtf32(d1[mt][nt], af, bf[nt]);
         }
       }
       __syncwarp();
@@ -382,18 +432,21 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
   }
   // ---- warp totals -> CTA totals -> global ----
   if constexpr (kMma) {
-    // D1 tile nt: d0 (j = g, c = 8nt + 2t), d1 (g, c + 1), d2 (g + 8, c), d3 (g + 8, c + 1); columns c <= K are real
+    // D1 tile (mt, nt): d0 (j = 16mt + g, c = 8nt + 2t), d1 (j, c + 1), d2 (j + 8, c), d3 (j + 8, c + 1); columns c <= K are real
 #pragma unroll
-    for (int nt = 0; nt < 2; ++nt) {
+    for (int mt = 0; mt < kMT; ++mt) {
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int j = fg + (i >= 2 ? 8 : 0), c = 8 * nt + 2 * ft + (i & 1);
-        if (c <= K && d1[nt][i] != 0.f) atomicAdd(&s_tot[j * kPerJ + c], d1[nt][i]);
+      for (int nt = 0; nt < kNT; ++nt) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int j = 16 * mt + fg + (i >= 2 ? 8 : 0), c = 8 * nt + 2 * ft + (i & 1);
+          if (c <= K && d1[mt][nt][i] != 0.f) atomicAdd(&s_tot[j * kPerJ + c], d1[mt][nt][i]);
+        }
       }
-    }
-    if (ft == 0) {  // column 0 of D2: dW2[g], dW2[g + 8]
-      if (d2[0] != 0.f) atomicAdd(&s_tot[fg * kPerJ + K + 1], d2[0]);
-      if (d2[2] != 0.f) atomicAdd(&s_tot[(fg + 8) * kPerJ + K + 1], d2[2]);
+      if (ft == 0) {  // column 0 of D2: dW2[16mt + g], dW2[16mt + g + 8]
+        if (d2[mt][0] != 0.f) atomicAdd(&s_tot[(16 * mt + fg) * kPerJ + K + 1], d2[mt][0]);
+        if (d2[mt][2] != 0.f) atomicAdd(&s_tot[(16 * mt + fg + 8) * kPerJ + K + 1], d2[mt][2]);
+      }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) db2_acc += __shfl_xor_sync(0xffffffffu, db2_acc, o);
@@ -418,9 +471,9 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
 }
 
 template <typename Kern>
-int grid_for(Kern kern, int64_t N) {
+int grid_for(Kern kern, int64_t N, size_t smem = 0) {
   int per_sm = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
   int64_t blocks = (N + kThreads - 1) / kThreads;
   int64_t cap = (int64_t)nkbs_num_sms() * per_sm;
   return (int)(blocks < cap ? blocks : cap);
@@ -692,10 +745,18 @@ extern "C" int nkbs_density_bwd(int32_t mode, const float* x, const float* origi
   a.db2 = db2;
   a.dedup_levels = dedup_levels < 0 ? L : dedup_levels;
   cudaStream_t st = (cudaStream_t)stream;
-  if (H == 16)
-    density_bwd_kernel<16, 5><<<grid_for(density_bwd_kernel<16, 5>, a.N), kThreads, 0, st>>>(a);
-  else
-    density_bwd_kernel<64, 8><<<grid_for(density_bwd_kernel<64, 8>, a.N), kThreads, 0, st>>>(a);
+  if (H == 16) {
+    constexpr size_t smem = (size_t)kWarps * MmaGeom<16, 5>::kScratch * sizeof(float);
+    static_assert(smem <= 48 * 1024, "default dynamic shared memory limit");
+    density_bwd_kernel<16, 5><<<grid_for(density_bwd_kernel<16, 5>, a.N, smem), kThreads, smem, st>>>(a);
+  } else {
+    constexpr size_t smem = (size_t)kWarps * MmaGeom<64, 8>::kScratch * sizeof(float);
+    if (smem > 48 * 1024) {
+      cudaError_t e = cudaFuncSetAttribute(density_bwd_kernel<64, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      NKBS_CHECK_ARG(e == cudaSuccess, "nkbs_density_bwd: %zu bytes of shared memory refused (%s)", smem, cudaGetErrorString(e));
+    }
+    density_bwd_kernel<64, 8><<<grid_for(density_bwd_kernel<64, 8>, a.N, smem), kThreads, smem, st>>>(a);
+  }
   NKBS_CHECK_LAUNCH("nkbs_density_bwd");
   return 0;
 }

@@ -205,7 +205,12 @@ class HashMLPDensityField(_Field):
         if self.use_linear or not ops.fused_density_enabled():
             return False
         net = self.mlp_base[1]
-        return len(net.layers) == 2 and (self.encoding.grid.L, net.layers[0].out_features) in ops.FUSED_DENSITY_SHAPES
+        shape = (self.encoding.grid.L, net.layers[0].out_features)
+        if len(net.layers) != 2 or shape not in ops.FUSED_DENSITY_SHAPES:
+            return False
+        if torch.is_grad_enabled() and self.encoding.hash_table.requires_grad:
+            return shape in ops.FUSED_DENSITY_TRAIN_SHAPES  # see ops.FUSED_DENSITY_TRAIN_SHAPES
+        return True
 
     def get_density(self, ray_samples: RaySamples) -> Tuple[torch.Tensor, None]:
         if self._fused_ok():

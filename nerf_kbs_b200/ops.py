@@ -159,6 +159,12 @@ def contract_encode(table, grid: GridSpec, norm: NormSpec, positions=None, origi
 # K8 fused proposal density field (encode + two-layer MLP + trunc_exp * selector)
 # ----------------------------------------------------------------------------------------------
 FUSED_DENSITY_SHAPES = ((5, 16), (8, 64))  # (levels, hidden width) instantiated in csrc/density.cu
+# Shapes whose TRAINING passes take the fused kernels too.  The hidden-64 field (semantic-NeRF-W's default proposals)
+# does not: its fused backward holds 64 + 16 accumulator registers per lane next to the recomputed forward (255
+# registers, one 8-warp CTA per SM) and is latency-bound — measured on the B200 at 8192 x 256 samples: fused forward +
+# backward 0.37 + 1.47 ms, encode + tensor-core MLP route 0.52 + 0.65 ms (scripts/density_bench.py,
+# profiles/r02_density_h64.txt).  Without gradients (evaluation, gated steps) every shape uses the fused forward.
+FUSED_DENSITY_TRAIN_SHAPES = ((5, 16),) if __import__("os").environ.get("NKBS_FUSED_DENSITY_H64_BWD", "0") != "1" else FUSED_DENSITY_SHAPES
 _FUSED_DENSITY = {"enabled": True}
 
 

@@ -6,8 +6,11 @@ import nerf_kbs_b200 as nk
 from nerf_kbs_b200 import ops
 R = int(os.environ.get("R", "65536"))
 torch.manual_seed(0)
-cfgs = {"nerfacto": nk.ModelConfig()}
-m = nk.NerfactoModel(nk.ModelConfig()).cuda().train()
+# MODEL=semantic_nerfw: the default HashMLPDensityField proposals (8 levels, 2^18, hidden 64)
+if os.environ.get("MODEL", "nerfacto") == "semantic_nerfw":
+    m = nk.SemanticNerfWModel(nk.ModelConfig(use_semantic=True)).cuda().train()
+else:
+    m = nk.NerfactoModel(nk.ModelConfig()).cuda().train()
 g = torch.Generator().manual_seed(1)
 o = torch.rand(R, 3, generator=g) - 0.5
 d = torch.randn(R, 3, generator=g); d = d / d.norm(dim=-1, keepdim=True)

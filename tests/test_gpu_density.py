@@ -45,7 +45,8 @@ def test_fused_density_matches_oracle(kind, R, S):
     dy = torch.rand(want.shape, generator=torch.Generator().manual_seed(9))
     want.backward(dy)
     fr = rs_o.frustums
-    assert ops.fused_density_enabled() and n._fused_ok()
+    with torch.no_grad():
+        assert ops.fused_density_enabled() and n._fused_ok()
     W, b = n.mlp_base[1].weights_biases()
     got = ops.fused_density(n.encoding.hash_table, n.encoding.grid, n._norm, W[0], b[0], W[1], b[1],
                             origins=rb.origins.to(DEV), directions=rb.directions.to(DEV),
@@ -66,9 +67,11 @@ def test_fused_density_equals_unfused_route(kind):
     pos = ((torch.rand(5000, 3, generator=g) - 0.5) * 6.0).to(DEV)  # inside and outside the unit box (contraction)
     dy = torch.rand(5000, 1, generator=g).to(DEV)
     prev = ops.get_mlp_precision()
+    prev_train = ops.FUSED_DENSITY_TRAIN_SHAPES
     res = {}
     try:
         ops.set_mlp_precision("fp32")
+        ops.FUSED_DENSITY_TRAIN_SHAPES = ops.FUSED_DENSITY_SHAPES  # exercise the fused backward of every shape
         for fused in (True, False):
             ops.set_fused_density(fused)
             for p in n.parameters():
@@ -79,6 +82,7 @@ def test_fused_density_equals_unfused_route(kind):
     finally:
         ops.set_fused_density(True)
         ops.set_mlp_precision(prev)
+        ops.FUSED_DENSITY_TRAIN_SHAPES = prev_train
     assert_close(res[True][0], res[False][0], 1e-5, "density")
     for a, b in zip(res[True][1], res[False][1]):
         assert_close(a, b, 1e-4, "grad")
@@ -104,3 +108,25 @@ def test_fused_density_rejects_other_shapes():
     with pytest.raises(ValueError):
         ops.fused_density(t, grid, norm, torch.zeros(16, 8, device=DEV), torch.zeros(16, device=DEV),
                           torch.zeros(1, 16, device=DEV), torch.zeros(1, device=DEV), positions=torch.zeros(3, 3, device=DEV))
+
+
+def test_training_route_of_the_hidden64_field():
+    """The semantic-NeRF-W default proposal field trains through encode + MLP kernels (faster backward, see
+    ops.FUSED_DENSITY_TRAIN_SHAPES) and evaluates through the fused forward; both give the same density."""
+    _, n = _pair("snw_default", seed=5)
+    _, n16 = _pair("nerfacto_prop0", seed=5)
+    assert not n._fused_ok() and n16._fused_ok()
+    with torch.no_grad():
+        assert n._fused_ok()
+    g = torch.Generator().manual_seed(6)
+    pos = ((torch.rand(3000, 3, generator=g) - 0.5) * 4.0).to(DEV)
+    prev = ops.get_mlp_precision()
+    try:
+        ops.set_mlp_precision("fp32")
+        d_train = n.density_fn(pos)
+        assert d_train.requires_grad
+        with torch.no_grad():
+            d_eval = n.density_fn(pos)
+    finally:
+        ops.set_mlp_precision(prev)
+    assert_close(d_train, d_eval, 1e-5, "density, training route vs fused forward")
