@@ -161,6 +161,11 @@ __device__ __forceinline__ void nkbs_red_add_v2(float* addr, float a, float b) {
   asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(a), "f"(b) : "memory");
 }
 
+__device__ __forceinline__ void nkbs_red_add_v4(float* addr, float a, float b, float c, float d) {
+  // one 16-byte vector reduction (sm_90+); addr must be 16-byte aligned
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 __device__ __forceinline__ float nkbs_sigmoid(float x) { return 1.f / (1.f + expf(-x)); }
 __device__ __forceinline__ float nkbs_softplus(float x) {
   // torch softplus: beta=1, threshold=20

@@ -39,6 +39,7 @@ struct DensityArgs : SampleSource {
   float* dW2;
   float* db2;
   int dedup_levels;
+  float v4_min_scale;  // see encode.cuh
 };
 
 // shared weights: W1 rows padded to KP floats (16-byte rows -> LDS.128 broadcasts), then b1, W2, b2
@@ -420,13 +421,15 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
       nkbs_corner_weights(cl.o[0], cl.o[1], cl.o[2], w);
       float* base = a.dtable + ((size_t)l << (a.lv.log2_T + 1));
       if (l < a.dedup_levels) {
-        scatter_level_runs(base, cl, h, w, df[2 * l], df[2 * l + 1], lane);
+        scatter_level_runs(base, cl, h, w, df[2 * l], df[2 * l + 1], lane, s_scale[l] >= a.v4_min_scale);
       } else {
+        float vx[8], vy[8];
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-          float gx = w[k] * df[2 * l], gy = w[k] * df[2 * l + 1];
-          if (gx != 0.f || gy != 0.f) nkbs_red_add_v2(base + 2 * (size_t)h[k], gx, gy);
+          vx[k] = w[k] * df[2 * l];
+          vy[k] = w[k] * df[2 * l + 1];
         }
+        scatter_cell(base, cl, h, vx, vy, s_scale[l] >= a.v4_min_scale);
       }
     }
   }
@@ -517,6 +520,7 @@ int fill(DensityArgs& a, const char* who, int mode, const float* x, const float*
   a.ddensity = nullptr;
   a.dtable = a.dW1 = a.db1 = a.dW2 = a.db2 = nullptr;
   a.dedup_levels = 0;
+  a.v4_min_scale = v4_min_scale(1e30f);
   return 0;
 }
 
@@ -737,6 +741,7 @@ extern "C" int nkbs_density_bwd(int32_t mode, const float* x, const float* origi
     return -1;
   if (a.N == 0) return 0;
   NKBS_CHECK_ARG(ddensity && dtable && dW1 && db1 && dW2 && db2, "nkbs_density_bwd: null gradient buffers");
+  NKBS_CHECK_ARG((reinterpret_cast<uintptr_t>(dtable) & 15u) == 0, "nkbs_density_bwd: dtable must be 16-byte aligned");
   a.ddensity = ddensity;
   a.dtable = dtable;
   a.dW1 = dW1;

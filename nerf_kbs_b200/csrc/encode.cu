@@ -94,6 +94,7 @@ struct EncodeBwdArgs {
   LevelParams lv;
   float* dtable;          // [L*T,2], accumulated into
   int dedup_levels;       // levels below this index use warp-level duplicate merging
+  float v4_min_scale;     // levels of at least this resolution pair their reductions (16-byte red)
 };
 
 __global__ void __launch_bounds__(kEncThreads) encode_bwd_kernel(const EncodeBwdArgs a) {
@@ -120,13 +121,15 @@ __global__ void __launch_bounds__(kEncThreads) encode_bwd_kernel(const EncodeBwd
       float2 gl = live ? __ldg(g + l) : make_float2(0.f, 0.f);
       float* base = a.dtable + ((size_t)l << (a.lv.log2_T + 1));
       if (l < a.dedup_levels) {
-        scatter_level_runs(base, cl, h, w, gl.x, gl.y, lane);
+        scatter_level_runs(base, cl, h, w, gl.x, gl.y, lane, s_scale[l] >= a.v4_min_scale);
       } else {
+        float vx[8], vy[8];
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-          float gx = w[k] * gl.x, gy = w[k] * gl.y;
-          if (gx != 0.f || gy != 0.f) nkbs_red_add_v2(base + 2 * (size_t)h[k], gx, gy);
+          vx[k] = w[k] * gl.x;
+          vy[k] = w[k] * gl.y;
         }
+        scatter_cell(base, cl, h, vx, vy, s_scale[l] >= a.v4_min_scale);
       }
     }
   }
@@ -201,6 +204,7 @@ extern "C" int nkbs_encode_bwd(const float* xn, const float* dfeat, int64_t N, c
                                int32_t log2_T, int32_t F, int32_t dedup_levels, float* dtable, void* stream) {
   NKBS_CHECK_ARG(F == 2, "nkbs_encode_bwd: features_per_level must be 2 (got %d)", F);
   NKBS_CHECK_ARG(N >= 0 && dtable && scalings, "nkbs_encode_bwd: bad arguments");
+  NKBS_CHECK_ARG((reinterpret_cast<uintptr_t>(dtable) & 15u) == 0, "nkbs_encode_bwd: dtable must be 16-byte aligned");
   EncodeBwdArgs a;
   a.xn = xn;
   a.dfeat = dfeat;
@@ -208,6 +212,7 @@ extern "C" int nkbs_encode_bwd(const float* xn, const float* dfeat, int64_t N, c
   NKBS_CHECK_ARG(fill_levels(a.lv, scalings, L, log2_T) == 0, "nkbs_encode_bwd: unsupported grid L=%d log2_T=%d", L, log2_T);
   a.dtable = dtable;
   a.dedup_levels = dedup_levels < 0 ? L : dedup_levels;
+  a.v4_min_scale = v4_min_scale(0.f);
   if (N == 0) return 0;
   NKBS_CHECK_ARG(xn && dfeat, "nkbs_encode_bwd: null xn/dfeat");
   int64_t blocks = (N + kEncThreads - 1) / kEncThreads;

@@ -1,6 +1,7 @@
 // Pieces shared by the encoding kernels (encode.cu) and the fused proposal-density kernels (density.cu):
 // where a sample's position comes from, the warp-merged gradient scatter, and the level table.
 #pragma once
+#include <stdlib.h>
 #include "common.cuh"
 
 struct SampleSource {
@@ -33,13 +34,40 @@ __device__ __forceinline__ float3 load_sample_position(const SampleSource& a, in
   return nkbs_normalise(p, a.norm, sel);
 }
 
+// Gradient of the 8 corner rows of one cell -> table gradient.  The x prime of the hash is 1, so the two corners of an x
+// edge (ceil-x corner kc, floor-x corner kf) are rows h and h ^ 1 of one 16-byte aligned pair whenever floor(x) is even
+// (as in the forward's paired gathers): one 16-byte vector reduction then carries both rows.  A quarter fewer L2
+// reduction operations on average (the scatter is bound by their count).  NKBS_SCATTER_V4 = 0: always two 8-byte ones.
+#ifndef NKBS_SCATTER_V4
+#define NKBS_SCATTER_V4 1
+#endif
+__device__ __forceinline__ void scatter_cell(float* base, const Cell& cl, const uint32_t h[8], const float vx[8],
+                                             const float vy[8], bool v4) {
+  constexpr int kC[4] = {0, 1, 4, 5}, kF[4] = {3, 2, 7, 6};  // x edges as (ceil-x corner, floor-x corner)
+  const bool pair = NKBS_SCATTER_V4 && v4 && !(cl.f[0] & 1u) && cl.c[0] != cl.f[0];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int kc = kC[j], kf = kF[j];
+    const bool nzc = vx[kc] != 0.f || vy[kc] != 0.f, nzf = vx[kf] != 0.f || vy[kf] != 0.f;
+    if (pair && nzc && nzf) {
+      const bool f_hi = h[kf] & 1u;  // the floor-x corner is the odd row of the pair
+      float* p = base + 2 * (size_t)(h[kf] & ~1u);
+      if (f_hi) nkbs_red_add_v4(p, vx[kc], vy[kc], vx[kf], vy[kf]);
+      else nkbs_red_add_v4(p, vx[kf], vy[kf], vx[kc], vy[kc]);
+    } else {
+      if (nzc) nkbs_red_add_v2(base + 2 * (size_t)h[kc], vx[kc], vy[kc]);
+      if (nzf) nkbs_red_add_v2(base + 2 * (size_t)h[kf], vx[kf], vy[kf]);
+    }
+  }
+}
+
 // Gradient scatter of one level with duplicate merging.  Adjacent lanes are adjacent samples of one ray, so the
 // samples of a warp that fall into the same cell (all 8 corner rows equal) form RUNS of neighbouring lanes.  A run
 // is summed with a segmented shuffle-down reduction (5 fixed steps for the 8 corners x 2 features), after which
 // only the first lane of each run issues the 8 vector reductions: coarse levels drop from 32 to 1-4 reductions
 // per corner and warp, at a cost that does not depend on the run length.  The whole warp must be converged.
 __device__ __forceinline__ void scatter_level_runs(float* base, const Cell& cl, const uint32_t h[8], const float w[8],
-                                                   float gx, float gy, int lane) {
+                                                   float gx, float gy, int lane, bool v4) {
   // cell key: floor coordinates and the ceil-floor bits (scale < 65536 is checked on the host)
   const uint32_t k0 = (cl.f[0] & 0xffffu) | (cl.f[1] << 16);
   const uint32_t k1 = (cl.f[2] & 0xffffu) | ((cl.c[0] - cl.f[0]) << 16) | ((cl.c[1] - cl.f[1]) << 17) |
@@ -75,11 +103,20 @@ __device__ __forceinline__ void scatter_level_runs(float* base, const Cell& cl, 
       }
     }
   }
-  if (head) {
-#pragma unroll
-    for (int k = 0; k < 8; ++k)
-      if (vx[k] != 0.f || vy[k] != 0.f) nkbs_red_add_v2(base + 2 * (size_t)h[k], vx[k], vy[k]);
-  }
+  if (head) scatter_cell(base, cl, h, vx, vy, v4);
+}
+
+// Levels of at least this resolution pair their reductions (scatter_cell).  Pairing pays where the scatter is bound by
+// the number of L2 reductions — the main grid, 48 samples per ray: 120 -> 102 us at 4096 rays, 1.55 -> 1.26 ms at
+// 65 536 — and loses a little where run merging has already removed most of them and the kernel is bound by its own
+// instructions (proposal grids at 256 samples per ray: 90 -> 103 us); profiles/r02_encode_bwd_v4.txt.  Hence on for
+// nkbs_encode_bwd, off for the fused proposal field.  NKBS_V4_MIN_SCALE overrides both.
+inline float v4_min_scale(float dflt) {
+  static const float v = [] {
+    const char* e = getenv("NKBS_V4_MIN_SCALE");
+    return e ? (float)atof(e) : -1.f;
+  }();
+  return v >= 0.f ? v : dflt;
 }
 
 inline int fill_levels(LevelParams& lv, const float* scalings, int L, int log2_T) {
