@@ -381,7 +381,7 @@ KITTI_H, KITTI_W = 375, 1242
 def render_run(dev, frames, warmup, rank=0, world=1, chunk=1 << 16):
     """BASELINE configs[3]: full-frame 1242x375 inference (rgb, depth, semantics) from synthetic poses on a straight
     KITTI-like trajectory, rays generated on the device, 65 536-ray chunks, eval mode.  Returns rays/s over all ranks
-    (chunks are dealt round-robin) and the end-to-end figure that includes the D2H copy of the three images."""
+    (every rank renders a contiguous block of the rays, one all-gather merges them) and the end-to-end figure that includes the D2H copy of the three images."""
     import torch
     import torch.distributed as dist
     import nerf_kbs_b200 as nk
@@ -698,7 +698,7 @@ def run_nkbs(args):
     e2e = {"value": world * R * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
            "h2d_bytes_per_step": tr.h2d_bytes() + 4, "d2h_bytes_per_step": 4}
 
-    # (2b) render rays/s (BASELINE configs[3]); every rank takes part (chunks are dealt round-robin)
+    # (2b) render rays/s (BASELINE configs[3]); every rank renders its block of every frame
     render = None
     if not args.no_render:
         del devb

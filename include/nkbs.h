@@ -51,10 +51,14 @@ int nkbs_encode_bwd(const float* xn, const float* dfeat, int64_t N, const float*
  * bwd recomputes the forward from x; dx may be NULL; dW/db are accumulated into. */
 int nkbs_mlp_fwd(const float* x, int64_t N, int32_t nl, const int32_t* dims, const float* const* W,
                  const float* const* b, int32_t relu_mask, int32_t out_act, const float* selector, float* y,
-                 void* stream);
+                 float* y0, void* stream);
 int nkbs_mlp_bwd(const float* x, const float* dy, int64_t N, int32_t nl, const int32_t* dims,
                  const float* const* W, const float* const* b, int32_t relu_mask, int32_t out_act,
-                 const float* selector, float* dx, float* const* dW, float* const* db, void* stream);
+                 const float* selector, const float* dy0, float* dx, float* const* dW, float* const* db,
+                 void* stream);
+/* y0 (may be NULL): column 0 of y written once more as a contiguous [N] array — torch.split(h, [1, geo_feat_dim])
+ * of NerfactoField.get_density without a copy kernel; dy0 (may be NULL): [N], added to column 0 of dy inside the
+ * kernel (the gradient that arrives through y0) instead of a separate add kernel.  dW / db are ACCUMULATED into. */
 
 /* K3 (tensor cores) — the same fused MLP on tcgen05 tensor cores: 16-bit operands (fmt 0 = fp16, 1 = bf16),
  * fp32 accumulation in TMEM, weights resident in shared memory, bias folded into the GEMM.  Same argument
@@ -62,11 +66,11 @@ int nkbs_mlp_bwd(const float* x, const float* dy, int64_t N, int32_t nl, const i
  * train.py:50); parity bar 1e-2 relative. */
 int nkbs_mlp_tc_fwd(const float* x, int64_t N, int32_t nl, const int32_t* dims, const float* const* W,
                     const float* const* b, int32_t relu_mask, int32_t out_act, int32_t fmt,
-                    const float* selector, float* y, void* stream);
+                    const float* selector, float* y, float* y0, void* stream);
 int nkbs_mlp_tc_bwd(const float* x, const float* dy, int64_t N, int32_t nl, const int32_t* dims,
                     const float* const* W, const float* const* b, int32_t relu_mask, int32_t out_act,
-                    int32_t fmt, const float* selector, float* dx, float* const* dW, float* const* db,
-                    void* stream);
+                    int32_t fmt, const float* selector, const float* dy0, float* dx, float* const* dW,
+                    float* const* db, void* stream);
 
 /* K8 — the proposal density field fused: ray point -> contraction -> HashEncoding -> MLP(2L -> H -> 1, ReLU) ->
  * trunc_exp * selector in one kernel per direction; only the density [N] is written.  fp32 throughout.
@@ -106,12 +110,17 @@ int nkbs_ray_losses(int64_t R, int32_t S, const float* sdist, const float* w, fl
  * (colour MSE, interlevel, distortion) as in the loss dict of nerfacto.py:483-489 (1, interlevel_loss_mult,
  * distortion_loss_mult).  The gradients dw / dw_prop / drgb come out already multiplied by their term's weight, so they
  * seed the backward pass as they are; out [5] still receives the UNWEIGHTED terms; total [1] (optional, accumulated
- * into) receives the weighted sum of the three terms.  The cross-entropy outputs are as in nkbs_ray_losses. */
+ * into) receives the weighted sum of the three terms.  The cross-entropy outputs are as in nkbs_ray_losses.
+ * scratch (may be NULL): DEVICE float [8] that is all zero between launches.  With it the CTAs accumulate into the
+ * scratch, and the last CTA to finish WRITES out[0..4], total[0] and the weighted terms total[1..3] (total is then
+ * [4]) and zeroes the scratch again — out / total need no zero fill before the launch.  Launches that share a
+ * scratch must not overlap on the GPU. */
 int nkbs_ray_losses_weighted(int64_t R, int32_t S, const float* sdist, const float* w, float* dw, int32_t n_prop,
                              const int32_t* S_prop, const float* const* sdist_prop, const float* const* w_prop,
                              float* const* dw_prop, const float* rgb, const float* image, float* drgb,
                              const float* logits, const int64_t* labels, int32_t C, int64_t ignore_index,
-                             float* dlogits, float* out, const float* term_weights, float* total, void* stream);
+                             float* dlogits, float* out, const float* term_weights, float* total, float* scratch,
+                             void* stream);
 
 /* N3 — pinhole ray generation: ray_indices [N,3] int64 (camera, row, col), c2w [num_cameras,3,4], intrinsics
  * [num_cameras,4] = fx, fy, cx, cy.  Pixel centres at +0.5; camera looks down -z with +y up; directions are unit
@@ -156,8 +165,10 @@ int nkbs_head_tc_bwd(int32_t sh_dim, int32_t geo_dim, int32_t emb_dim, const flo
                      const float* directions, int32_t dir_per_ray, const int64_t* cam, int32_t cam_per_ray,
                      const float* emb, const float* emb_const, int32_t S, const float* dy, int64_t N, int32_t nl,
                      const int32_t* dims, const float* const* W, const float* const* b, int32_t relu_mask,
-                     int32_t out_act, int32_t fmt, float* dgeo, int32_t dgeo_stride, float* demb, float* const* dW,
-                     float* const* db, void* stream);
+                     int32_t out_act, int32_t fmt, float* dgeo, int32_t dgeo_stride, int32_t dgeo_lead, float* demb,
+                     float* const* dW, float* const* db, void* stream);
+/* dgeo_lead: this many floats in FRONT of every dgeo row are set to zero by the kernel (dgeo pointing at column 1 of a
+ * [N,16] gradient of the base MLP's output: dgeo_lead = 1 zeroes the density column, no fill kernel needed). */
 
 /* K4 — head-MLP input assembly  h = [SH16((d+1)/2) | geo | embedding row]  and its backward.
  * replaces: SHEncoding + Embedding + torch.cat in NerfactoField.get_outputs (nerfacto.py:398;
@@ -211,8 +222,11 @@ int nkbs_composite_bwd(int64_t R, int32_t S, const float* density, const float* 
  * accumulate into the same buffers without a separate fill pass. */
 int nkbs_adam_step(int32_t num_tensors, float* const* params, float* const* grads,
                    float* const* exp_avg, float* const* exp_avg_sq, const int64_t* numel, float lr,
-                   float beta1, float beta2, float eps, float weight_decay, const float* step_dev,
-                   const float* inv_scale_dev, int32_t zero_grads, void* stream);
+                   float beta1, float beta2, float eps, float weight_decay, float* step_dev,
+                   const float* inv_scale_dev, int32_t zero_grads, uint32_t* step_counter, void* stream);
+/* step_counter NULL: *step_dev is the count t of THIS step (the caller advanced it).  step_counter = a device uint32
+ * that is 0 between launches: *step_dev is the count before this step, the kernel uses t = *step_dev + 1 and stores it
+ * when its last CTA finishes (single launch: at most 24 tensors), so no separate increment kernel is needed. */
 
 /* N2 (data parallel) — reduce-scatter + Adam + all-gather in one kernel over NVLink peer memory.  grad_peers /
  * param_peers: HOST arrays of `world` DEVICE pointers to the flat gradient / parameter buffer of every rank
@@ -222,7 +236,7 @@ int nkbs_adam_step(int32_t num_tensors, float* const* params, float* const* grad
  * replaces: NCCL allreduce of the gradients + nkbs_adam_step (datamanager_z.py:225-231 DDP setup; train.py:85-98). */
 int nkbs_dp_adam_step(int32_t world, int32_t rank, const float* const* grad_peers, float* const* param_peers,
                       int64_t lo, int64_t n, float* exp_avg, float* exp_avg_sq, float lr, float beta1, float beta2,
-                      float eps, float weight_decay, const float* step_dev, void* stream);
+                      float eps, float weight_decay, float* step_dev, uint32_t* step_counter, void* stream);
 
 /* One proposal level of ProposalNetworkSampler in one ray-major pass (forward): the level's bins (gen_bins != 0:
  * produced here by the initial piecewise sampler from lin [S+1] and the per-ray jitter t_rand [R] (NULL in

@@ -20,16 +20,16 @@ _f = C.c_float
 SIGNATURES = {
     "nkbs_encode_fwd": [_i32, _p, _p, _p, _p, _p, _i32, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p],
     "nkbs_encode_bwd": [_p, _p, _i64, _p, _i32, _i32, _i32, _i32, _p, _p],
-    "nkbs_mlp_fwd": [_p, _i64, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p],
-    "nkbs_mlp_bwd": [_p, _p, _i64, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _p],
-    "nkbs_mlp_tc_fwd": [_p, _i64, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p],
-    "nkbs_mlp_tc_bwd": [_p, _p, _i64, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p],
+    "nkbs_mlp_fwd": [_p, _i64, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p],
+    "nkbs_mlp_bwd": [_p, _p, _i64, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _p, _p],
+    "nkbs_mlp_tc_fwd": [_p, _i64, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p],
+    "nkbs_mlp_tc_bwd": [_p, _p, _i64, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p],
     "nkbs_density_fwd": [_i32, _p, _p, _p, _p, _p, _i32, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _i32, _p, _p],
     "nkbs_density_bwd": [_i32, _p, _p, _p, _p, _p, _i32, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _i32, _p, _i32,
                          _p, _p, _p, _p, _p, _p],
     "nkbs_ray_losses": [_i64, _i32, _p, _p, _p, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _i64, _p, _p, _p],
     "nkbs_ray_losses_weighted": [_i64, _i32, _p, _p, _p, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _i64, _p, _p, _p, _p,
-                                 _p],
+                                 _p, _p],
     "nkbs_generate_rays": [_i64, _p, _p, _p, _i64, _p, _p, _p, _p, _p, _p],
     "nkbs_compact_masked": [_i64, _p, _p, _p, _i64, _i64, _p, _p, _p, _p],
     "nkbs_color_to_label": [_i64, _p, _p, _i64, _p, _p],
@@ -37,20 +37,20 @@ SIGNATURES = {
     "nkbs_head_tc_fwd": [_i32, _i32, _i32, _p, _i32, _p, _i32, _p, _i32, _p, _p, _i32, _i64, _i32, _p, _p, _p, _i32, _i32, _i32,
                          _p, _p],
     "nkbs_head_tc_bwd": [_i32, _i32, _i32, _p, _i32, _p, _i32, _p, _i32, _p, _p, _i32, _p, _i64, _i32, _p, _p, _p, _i32, _i32,
-                         _i32, _p, _i32, _p, _p, _p, _p],
+                         _i32, _p, _i32, _i32, _p, _p, _p, _p],
     "nkbs_assemble_fwd": [_i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32, _p, _p, _i64, _p, _p],
     "nkbs_assemble_bwd": [_i64, _i32, _i32, _i32, _i32, _p, _p, _p, _i32, _p, _p],
     "nkbs_initial_sampler": [_i64, _i32, _p, _p, _i32, _p, _p, _p, _p, _p],
     "nkbs_pdf_sample": [_i64, _i32, _i32, _p, _f, _p, _f, _f, _p, _p, _p, _i32, _p, _p, _p, _p, _p, _p],
     "nkbs_composite_fwd": [_i64, _i32, _p, _p, _p, _p, _i32, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
-    "nkbs_adam_step": [_i32, _p, _p, _p, _p, _p, _f, _f, _f, _f, _f, _p, _p, _i32, _p],
+    "nkbs_adam_step": [_i32, _p, _p, _p, _p, _p, _f, _f, _f, _f, _f, _p, _p, _i32, _p, _p],
     "nkbs_zero_async": [_p, _i64, _p],
     "nkbs_expected_depth_noalloc": [_i64, _i32, _p, _p, _p, _i32, _p, _p],
     "nkbs_proposal_level_fwd": [_i64, _i32, _p, _p, _p, _p, _i32, _p, _p, _p, _p, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p,
                                 _p, _i32, _p, _p, _p, _i32, _f, _p, _f, _f, _p, _p, _p, _p, _p],
     "nkbs_apply_colormap": [_i64, _p, _p, _p, _p],
     "nkbs_apply_depth_colormap": [_i64, _p, _p, _p, _i32, _f, _i32, _f, _p, _p, _p],
-    "nkbs_dp_adam_step": [_i32, _i32, _p, _p, _i64, _i64, _p, _p, _f, _f, _f, _f, _f, _p, _p],
+    "nkbs_dp_adam_step": [_i32, _i32, _p, _p, _i64, _i64, _p, _p, _f, _f, _f, _f, _f, _p, _p, _p],
     "nkbs_composite_bwd": [_i64, _i32, _p, _p, _p, _p, _i32, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
 }
 

@@ -23,7 +23,9 @@ struct AdamArgs {
   int block_start[kMaxSegs + 1];  // first CTA of every segment
   int nseg;
   float lr, beta1, beta2, eps, weight_decay;
-  const float* step_dev;   // device scalar: step count t >= 1 (float), read by every thread
+  float* step_dev;         // device scalar: step count t >= 1 (float), read by every thread
+  unsigned* counter;       // null: *step_dev is this step's count.  Else *step_dev counts the steps BEFORE this one: the
+                           // kernel uses t = *step_dev + 1 and the last CTA to finish stores it (no separate add launch)
   const float* inv_scale;  // optional device scalar multiplied into the gradient (GradScaler unscale / 1/world)
   int zero_grads;          // write 0 back over every gradient read: the buffer is ready for the next backward pass
 };
@@ -37,12 +39,26 @@ __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, 
   p -= step_size * (m / denom);
 }
 
+// Every CTA has read the old count before it arrives here, and the CTA that arrives last knows that all have: it
+// publishes the new count and re-arms the counter for the next launch (graph replays included).
+__device__ __forceinline__ void advance_step(float* step_dev, unsigned* counter, float t) {
+  if (!counter) return;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(counter, 1u) == gridDim.x - 1) {
+      *step_dev = t;
+      *counter = 0u;
+    }
+  }
+}
+
 __global__ void __launch_bounds__(kThreads) adam_kernel(const AdamArgs a) {
   int s = 0;
 #pragma unroll 1
   while (s + 1 < a.nseg && (int)blockIdx.x >= a.block_start[s + 1]) ++s;
   const AdamSeg sg = a.seg[s];
-  const float t = *a.step_dev;
+  const float t = a.counter ? *a.step_dev + 1.f : *a.step_dev;
   const float bc1 = 1.f - powf(a.beta1, t);
   const float bc2 = 1.f - powf(a.beta2, t);
   const float step_size = a.lr / bc1;
@@ -79,6 +95,7 @@ __global__ void __launch_bounds__(kThreads) adam_kernel(const AdamArgs a) {
       if (a.zero_grads) sg.g[i] = 0.f;
     }
   }
+  advance_step(a.step_dev, a.counter, t);
 }
 
 // ---- data-parallel step over NVLink peer memory: reduce-scatter + Adam + all-gather in ONE kernel ----
@@ -96,14 +113,15 @@ struct DpAdamArgs {
   float* m;                   // [n] first moments of the slice
   float* v;                   // [n]
   float lr, beta1, beta2, eps, weight_decay;
-  const float* step_dev;
+  float* step_dev;
+  unsigned* counter;          // as AdamArgs::counter
 };
 
 // WORLD > 0: number of ranks known at compile time, the peer loads of one element are all in flight together
 // (NVLink round trips are ~2 us: the loop over ranks must not serialise them); WORLD = 0: any rank count.
 template <int WORLD>
 __global__ void __launch_bounds__(kThreads) dp_adam_kernel(const DpAdamArgs a) {
-  const float t = *a.step_dev;
+  const float t = a.counter ? *a.step_dev + 1.f : *a.step_dev;
   const float bc1 = 1.f - powf(a.beta1, t);
   const float bc2 = 1.f - powf(a.beta2, t);
   const float step_size = a.lr / bc1;
@@ -152,15 +170,20 @@ __global__ void __launch_bounds__(kThreads) dp_adam_kernel(const DpAdamArgs a) {
       for (int r = 0; r < world; ++r) *reinterpret_cast<float4*>(a.p[r] + i) = p;
     }
   }
+  advance_step(a.step_dev, a.counter, t);
 }
 
 }  // namespace
 
 extern "C" int nkbs_adam_step(int32_t num_tensors, float* const* params, float* const* grads,
                               float* const* exp_avg, float* const* exp_avg_sq, const int64_t* numel, float lr,
-                              float beta1, float beta2, float eps, float weight_decay, const float* step_dev,
-                              const float* inv_scale_dev, int32_t zero_grads, void* stream) {
+                              float beta1, float beta2, float eps, float weight_decay, float* step_dev,
+                              const float* inv_scale_dev, int32_t zero_grads, uint32_t* step_counter, void* stream) {
   NKBS_CHECK_ARG(num_tensors >= 0 && step_dev, "nkbs_adam_step: bad arguments");
+  int64_t total_blocks = 0;
+  for (int j = 0; j < num_tensors; ++j) total_blocks += (numel[j] + kPerBlock - 1) / kPerBlock;
+  NKBS_CHECK_ARG(!step_counter || (num_tensors <= kMaxSegs && total_blocks > 0),
+                 "nkbs_adam_step: the in-kernel step count needs a single launch (at most %d tensors, at least one element)", kMaxSegs);
   int i = 0;
   while (i < num_tensors) {
     AdamArgs a;
@@ -188,6 +211,7 @@ extern "C" int nkbs_adam_step(int32_t num_tensors, float* const* params, float* 
     a.step_dev = step_dev;
     a.inv_scale = inv_scale_dev;
     a.zero_grads = zero_grads;
+    a.counter = step_counter;
     adam_kernel<<<blocks, kThreads, 0, (cudaStream_t)stream>>>(a);
     NKBS_CHECK_LAUNCH("nkbs_adam_step");
   }
@@ -196,7 +220,8 @@ extern "C" int nkbs_adam_step(int32_t num_tensors, float* const* params, float* 
 
 extern "C" int nkbs_dp_adam_step(int32_t world, int32_t rank, const float* const* grad_peers, float* const* param_peers,
                                  int64_t lo, int64_t n, float* exp_avg, float* exp_avg_sq, float lr, float beta1,
-                                 float beta2, float eps, float weight_decay, const float* step_dev, void* stream) {
+                                 float beta2, float eps, float weight_decay, float* step_dev, uint32_t* step_counter,
+                                 void* stream) {
   NKBS_CHECK_ARG(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world, "nkbs_dp_adam_step: bad world/rank %d/%d", world, rank);
   NKBS_CHECK_ARG(lo >= 0 && n >= 0 && (lo & 3) == 0 && (n & 3) == 0, "nkbs_dp_adam_step: slice must be 4-element aligned");
   if (n == 0) return 0;
@@ -221,6 +246,7 @@ extern "C" int nkbs_dp_adam_step(int32_t world, int32_t rank, const float* const
   a.eps = eps;
   a.weight_decay = weight_decay;
   a.step_dev = step_dev;
+  a.counter = step_counter;
   int64_t blocks = ((n >> 2) + kThreads - 1) / kThreads;
   int64_t cap = (int64_t)nkbs_num_sms() * 8;
   const int grid = (int)(blocks < cap ? blocks : cap);

@@ -41,6 +41,9 @@ struct LossArgs {
   float g_R, g_RS, g_R3;        // normalisers x term weights, applied to the gradients (weighted entry point)
   float tw[3];                  // term weights (rgb, interlevel, distortion)
   float* total;                 // optional [1]: weighted sum of the three terms, accumulated
+  float* scratch;               // optional [8], zero between launches: the CTAs accumulate here instead, and the last
+                                // CTA to finish WRITES out[0..4], total[0] and total[1..3] (the weighted terms) and
+                                // zeroes the scratch again: out / total need no zero fill before the launch
 };
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -201,14 +204,36 @@ __global__ void __launch_bounds__(kThreads) ray_losses_kernel(const LossArgs a, 
     atomicAdd(&s_out[4], t_cnt);
   }
   __syncthreads();
+  float* acc = a.scratch ? a.scratch : a.out;
   if (threadIdx.x < 5) {
     const float scale = threadIdx.x == 0 ? a.inv_R3 : (threadIdx.x == 1 ? a.inv_RS : (threadIdx.x == 2 ? a.inv_R : 1.f));
     const float v = s_out[threadIdx.x] * scale;
-    if (v != 0.f) atomicAdd(a.out + threadIdx.x, v);
+    if (v != 0.f) atomicAdd(acc + threadIdx.x, v);
   }
   if (a.total && threadIdx.x == 0) {
     const float v = a.tw[0] * (s_out[0] * a.inv_R3) + a.tw[1] * (s_out[1] * a.inv_RS) + a.tw[2] * (s_out[2] * a.inv_R);
-    if (v != 0.f) atomicAdd(a.total, v);
+    if (v != 0.f) atomicAdd(a.scratch ? a.scratch + 5 : a.total, v);
+  }
+  if (a.scratch) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      unsigned* counter = reinterpret_cast<unsigned*>(a.scratch + 7);
+      if (atomicAdd(counter, 1u) == gridDim.x - 1) {  // every CTA's sums have arrived
+        __threadfence();
+        float t[6];
+#pragma unroll
+        for (int i = 0; i < 6; ++i) t[i] = atomicExch(a.scratch + i, 0.f);  // read and re-arm
+#pragma unroll
+        for (int i = 0; i < 5; ++i) a.out[i] = t[i];
+        if (a.total) {
+          a.total[0] = t[5];
+#pragma unroll
+          for (int i = 0; i < 3; ++i) a.total[1 + i] = a.tw[i] * t[i];
+        }
+        *counter = 0u;
+      }
+    }
   }
 }
 
@@ -218,7 +243,8 @@ static int ray_losses_launch(int64_t R, int32_t S, const float* sdist, const flo
                              const int32_t* S_prop, const float* const* sdist_prop, const float* const* w_prop,
                              float* const* dw_prop, const float* rgb, const float* image, float* drgb,
                              const float* logits, const int64_t* labels, int32_t C, int64_t ignore_index,
-                             float* dlogits, float* out, const float* term_weights, float* total, void* stream) {
+                             float* dlogits, float* out, const float* term_weights, float* total, float* scratch,
+                             void* stream) {
   NKBS_CHECK_ARG(R >= 0 && out, "nkbs_ray_losses: bad arguments");
   NKBS_CHECK_ARG(n_prop >= 0 && n_prop <= kMaxProp, "nkbs_ray_losses: at most %d proposal levels (got %d)", kMaxProp, n_prop);
   const bool hist = dw != nullptr || n_prop > 0;
@@ -260,6 +286,7 @@ static int ray_losses_launch(int64_t R, int32_t S, const float* sdist, const flo
   a.g_RS = a.inv_RS * a.tw[1];
   a.g_R = a.inv_R * a.tw[2];
   a.total = total;
+  a.scratch = scratch;
   const size_t smem = (size_t)kWarpsPerCta * ((a.S + 1) + 2 * a.S + 3 * (smax + 2)) * sizeof(float);
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(ray_losses_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -279,7 +306,7 @@ extern "C" int nkbs_ray_losses(int64_t R, int32_t S, const float* sdist, const f
                                const float* logits, const int64_t* labels, int32_t C, int64_t ignore_index,
                                float* dlogits, float* out, void* stream) {
   return ray_losses_launch(R, S, sdist, w, dw, n_prop, S_prop, sdist_prop, w_prop, dw_prop, rgb, image, drgb, logits,
-                           labels, C, ignore_index, dlogits, out, nullptr, nullptr, stream);
+                           labels, C, ignore_index, dlogits, out, nullptr, nullptr, nullptr, stream);
 }
 
 extern "C" int nkbs_ray_losses_weighted(int64_t R, int32_t S, const float* sdist, const float* w, float* dw,
@@ -287,8 +314,8 @@ extern "C" int nkbs_ray_losses_weighted(int64_t R, int32_t S, const float* sdist
                                         const float* const* w_prop, float* const* dw_prop, const float* rgb,
                                         const float* image, float* drgb, const float* logits, const int64_t* labels,
                                         int32_t C, int64_t ignore_index, float* dlogits, float* out,
-                                        const float* term_weights, float* total, void* stream) {
+                                        const float* term_weights, float* total, float* scratch, void* stream) {
   NKBS_CHECK_ARG(term_weights != nullptr, "nkbs_ray_losses_weighted: null term_weights");
   return ray_losses_launch(R, S, sdist, w, dw, n_prop, S_prop, sdist_prop, w_prop, dw_prop, rgb, image, drgb, logits,
-                           labels, C, ignore_index, dlogits, out, term_weights, total, stream);
+                           labels, C, ignore_index, dlogits, out, term_weights, total, scratch, stream);
 }

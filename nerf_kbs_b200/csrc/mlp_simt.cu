@@ -31,7 +31,9 @@ struct MlpArgs {
   const float* x;         // [N,K0]
   const float* selector;  // [N] or null (ACT_DENSITY)
   float* y;               // [N,Kn]
+  float* y0;              // [N] or null: column 0 of y once more, contiguous
   const float* dy;        // [N,Kn]
+  const float* dy0;       // [N] or null: added to column 0 of dy
   float* dx;              // [N,K0] or null
   int out_act;
   int64_t N;
@@ -180,6 +182,7 @@ __global__ void __launch_bounds__(kThreads) mlp_fwd_kernel(const MlpArgs a) {
       for (int n = half; n < Kn; n += 2) cur[n * kTS + t] = apply_out_act(a.out_act, n, cur[n * kTS + t], sel);
       __syncthreads();
     }
+    if (a.y0 && half == 0 && row0 + t < a.N) a.y0[row0 + t] = cur[t];  // feature 0 of sample t
     store_tile(a.y, row0, a.N, Kn, cur);
   }
 }
@@ -310,6 +313,7 @@ __global__ void __launch_bounds__(kThreads) mlp_bwd_kernel(const MlpArgs a) {
     load_tile(a.x, row0, a.N, a.layer[0].K, acts[0]);
     load_tile(a.dy, row0, a.N, Kn, gB);
     __syncthreads();
+    if (a.dy0 && half == 0 && row0 + t < a.N) gB[t] += __ldg(a.dy0 + row0 + t);  // read after the barriers of the recompute
     // recompute the forward pass, keeping every layer input
 #pragma unroll
     for (int l = 0; l < kMaxLayers; ++l) {
@@ -400,7 +404,7 @@ int build_args(MlpArgs& a, int nl, const int32_t* dims, const float* const* W, c
 
 extern "C" int nkbs_mlp_fwd(const float* x, int64_t N, int32_t nl, const int32_t* dims, const float* const* W,
                             const float* const* b, int32_t relu_mask, int32_t out_act, const float* selector,
-                            float* y, void* stream) {
+                            float* y, float* y0, void* stream) {
   MlpArgs a;
   if (build_args(a, nl, dims, W, b, relu_mask, out_act, "nkbs_mlp_fwd")) return -1;
   NKBS_CHECK_ARG(N >= 0, "nkbs_mlp_fwd: negative N");
@@ -408,8 +412,10 @@ extern "C" int nkbs_mlp_fwd(const float* x, int64_t N, int32_t nl, const int32_t
   NKBS_CHECK_ARG(x && y, "nkbs_mlp_fwd: null x/y");
   a.x = x;
   a.y = y;
+  a.y0 = y0;
   a.selector = selector;
   a.dy = nullptr;
+  a.dy0 = nullptr;
   a.dx = nullptr;
   a.N = N;
   size_t smem = (size_t)(a.w_floats + 2 * kMaxWidth * kTS) * sizeof(float);
@@ -428,7 +434,8 @@ extern "C" int nkbs_mlp_fwd(const float* x, int64_t N, int32_t nl, const int32_t
 
 extern "C" int nkbs_mlp_bwd(const float* x, const float* dy, int64_t N, int32_t nl, const int32_t* dims,
                             const float* const* W, const float* const* b, int32_t relu_mask, int32_t out_act,
-                            const float* selector, float* dx, float* const* dW, float* const* db, void* stream) {
+                            const float* selector, const float* dy0, float* dx, float* const* dW, float* const* db,
+                            void* stream) {
   MlpArgs a;
   if (build_args(a, nl, dims, W, b, relu_mask, out_act, "nkbs_mlp_bwd")) return -1;
   NKBS_CHECK_ARG(N >= 0, "nkbs_mlp_bwd: negative N");
@@ -441,8 +448,10 @@ extern "C" int nkbs_mlp_bwd(const float* x, const float* dy, int64_t N, int32_t 
   }
   a.x = x;
   a.y = nullptr;
+  a.y0 = nullptr;
   a.selector = selector;
   a.dy = dy;
+  a.dy0 = dy0;
   a.dx = dx;
   a.N = N;
   size_t smem = (size_t)(a.w_floats + (nl + 2) * kMaxWidth * kTS) * sizeof(float);

@@ -68,6 +68,7 @@ struct HeadIn {
   int emb_vec;             // embedding rows (and the constant row) are 16-byte aligned
   float* dgeo;             // backward: row n at dgeo + n * dgeo_stride, or null
   int dgeo_stride;
+  int dgeo_lead;           // backward: this many floats in front of every dgeo row are set to zero (the density column)
   float* demb;             // backward: [num_images, emb_dim], accumulated into, or null
 };
 
@@ -78,7 +79,9 @@ struct TcArgs {
   const float* x;         // [N,K0]
   const float* selector;  // [N] or null
   float* y;               // [N,Kn]   (forward)
+  float* y0;              // [N] or null: column 0 of y once more, contiguous (the density of the base MLP)
   const float* dy;        // [N,Kn]   (backward)
+  const float* dy0;       // [N] or null: added to column 0 of dy (gradient of y0)
   float* dx;              // [N,K0] or null (backward)
   int out_act;
   int fmt;                // 0 fp16, 1 bf16
@@ -654,6 +657,7 @@ __global__ void __launch_bounds__((NWG + 1) * kThreads, 1) mlp_tc_fwd_kernel(con
           const int stride = NO + 4;
           tmem_foreach16<kMaxWidth / 16>(tmem_row, last.Np, last.Np, [&](int c0, float v[16]) {
             apply_out_act16(a.out_act, c0, NO, v, sel);
+            if (c0 == 0 && a.y0 && live) a.y0[row] = v[0];
             float4* p = reinterpret_cast<float4*>(st + tid * stride + c0);
 #pragma unroll
             for (int q = 0; q < 4; ++q)
@@ -679,6 +683,7 @@ __global__ void __launch_bounds__((NWG + 1) * kThreads, 1) mlp_tc_fwd_kernel(con
           float* srow = st + tid * stride;
           tmem_foreach16<kMaxWidth / 16>(tmem_row, last.Np, last.Np, [&](int c0, float v[16]) {
             apply_out_act16(a.out_act, c0, NO, v, sel);
+            if (c0 == 0 && a.y0 && live) a.y0[row] = v[0];
 #pragma unroll
             for (int j = 0; j < 16; ++j)
               if (c0 + j < NO) srow[c0 + j] = v[j];
@@ -703,6 +708,7 @@ __global__ void __launch_bounds__((NWG + 1) * kThreads, 1) mlp_tc_fwd_kernel(con
         float* yo = a.y + row * last.N;
         tmem_foreach16<kMaxWidth / 16>(tmem_row, last.Np, last.Np, [&](int c0, float v[16]) {
           apply_out_act16(a.out_act, c0, last.N, v, sel);
+          if (c0 == 0 && a.y0 && live) a.y0[row] = v[0];
           if (live) {
 #pragma unroll
             for (int j = 0; j < 16; ++j)
@@ -854,6 +860,7 @@ __global__ void __launch_bounds__((NWG + 1) * kThreads, 1) mlp_tc_bwd_kernel(con
       {
         cp_async_wait_all();
         wg_sync(wg);  // every thread's part of the dy tile has landed
+        if (a.dy0 && live) dys[r * Kn] += __ldg(a.dy0 + row);  // row r is read by thread r only
         const float* dyr = dys + r * Kn;
         unsigned char* g = base + a.g_off;
         tmem_foreach16<kMaxWidth / 16>(tmem_row, last.Np, last.Np, [&](int c0, float v[16]) {
@@ -956,6 +963,8 @@ __global__ void __launch_bounds__((NWG + 1) * kThreads, 1) mlp_tc_bwd_kernel(con
               const int rr = e / GEO, c = e - rr * GEO;
               a.hin.dgeo[(row0 + rr) * (int64_t)a.hin.dgeo_stride + c] = st[rr * stride + SHD + c];
             }
+            if (a.hin.dgeo_lead > 0 && tid < (int)rows)
+              for (int c = 1; c <= a.hin.dgeo_lead; ++c) a.hin.dgeo[(row0 + tid) * (int64_t)a.hin.dgeo_stride - c] = 0.f;
           }
           if (a.hin.demb && a.hin.cam) {
             const int G = a.hin.cam_per_ray ? a.hin.S : 1;
@@ -1279,6 +1288,7 @@ int fill_head(TcArgs& a, const char* who, int sh_dim, int geo_dim, int emb_dim, 
                   (reinterpret_cast<uintptr_t>(a.hin.cam ? (const void*)emb : (const void*)emb_const) & 15) == 0;
   a.hin.dgeo = nullptr;
   a.hin.dgeo_stride = 0;
+  a.hin.dgeo_lead = 0;
   a.hin.demb = nullptr;
   return 0;
 }
@@ -1298,7 +1308,7 @@ extern "C" int nkbs_debug_trace(long long* host, int* n) {
 
 extern "C" int nkbs_mlp_tc_fwd(const float* x, int64_t N, int32_t nl, const int32_t* dims, const float* const* W,
                                const float* const* b, int32_t relu_mask, int32_t out_act, int32_t fmt,
-                               const float* selector, float* y, void* stream) {
+                               const float* selector, float* y, float* y0, void* stream) {
   TcArgs a;
   if (build_args(a, false, nl, dims, W, b, relu_mask, out_act, fmt, "nkbs_mlp_tc_fwd")) return -1;
   NKBS_CHECK_ARG(N >= 0, "nkbs_mlp_tc_fwd: negative N");
@@ -1307,8 +1317,10 @@ extern "C" int nkbs_mlp_tc_fwd(const float* x, int64_t N, int32_t nl, const int3
   a.hin = HeadIn{};
   a.x = x;
   a.y = y;
+  a.y0 = y0;
   a.selector = selector;
   a.dy = nullptr;
+  a.dy0 = nullptr;
   a.dx = nullptr;
   a.N = N;
   if (launch_tc<false, 0>(a, N, (cudaStream_t)stream, "nkbs_mlp_tc_fwd")) return -1;
@@ -1318,8 +1330,8 @@ extern "C" int nkbs_mlp_tc_fwd(const float* x, int64_t N, int32_t nl, const int3
 
 extern "C" int nkbs_mlp_tc_bwd(const float* x, const float* dy, int64_t N, int32_t nl, const int32_t* dims,
                                const float* const* W, const float* const* b, int32_t relu_mask, int32_t out_act,
-                               int32_t fmt, const float* selector, float* dx, float* const* dW, float* const* db,
-                               void* stream) {
+                               int32_t fmt, const float* selector, const float* dy0, float* dx, float* const* dW,
+                               float* const* db, void* stream) {
   TcArgs a;
   if (build_args(a, true, nl, dims, W, b, relu_mask, out_act, fmt, "nkbs_mlp_tc_bwd")) return -1;
   NKBS_CHECK_ARG(N >= 0, "nkbs_mlp_tc_bwd: negative N");
@@ -1333,8 +1345,10 @@ extern "C" int nkbs_mlp_tc_bwd(const float* x, const float* dy, int64_t N, int32
   a.hin = HeadIn{};
   a.x = x;
   a.y = nullptr;
+  a.y0 = nullptr;
   a.selector = selector;
   a.dy = dy;
+  a.dy0 = dy0;
   a.dx = dx;
   a.N = N;
   if (launch_tc<true, 0>(a, N, (cudaStream_t)stream, "nkbs_mlp_tc_bwd")) return -1;
@@ -1359,8 +1373,10 @@ extern "C" int nkbs_head_tc_fwd(int32_t sh_dim, int32_t geo_dim, int32_t emb_dim
   NKBS_CHECK_ARG(y, "nkbs_head_tc_fwd: null y");
   a.x = nullptr;
   a.y = y;
+  a.y0 = nullptr;
   a.selector = nullptr;
   a.dy = nullptr;
+  a.dy0 = nullptr;
   a.dx = nullptr;
   a.N = N;
   const int rc = in_mode == 1   ? launch_tc<false, 1>(a, N, (cudaStream_t)stream, "nkbs_head_tc_fwd")
@@ -1376,7 +1392,7 @@ extern "C" int nkbs_head_tc_bwd(int32_t sh_dim, int32_t geo_dim, int32_t emb_dim
                                 const float* emb, const float* emb_const, int32_t S, const float* dy, int64_t N,
                                 int32_t nl, const int32_t* dims, const float* const* W, const float* const* b,
                                 int32_t relu_mask, int32_t out_act, int32_t fmt, float* dgeo, int32_t dgeo_stride,
-                                float* demb, float* const* dW, float* const* db, void* stream) {
+                                int32_t dgeo_lead, float* demb, float* const* dW, float* const* db, void* stream) {
   TcArgs a;
   if (build_args(a, true, nl, dims, W, b, relu_mask, out_act, fmt, "nkbs_head_tc_bwd")) return -1;
   NKBS_CHECK_ARG(N >= 0, "nkbs_head_tc_bwd: negative N");
@@ -1393,13 +1409,17 @@ extern "C" int nkbs_head_tc_bwd(int32_t sh_dim, int32_t geo_dim, int32_t emb_dim
     a.layer[l].dW = dW[l];
     a.layer[l].db = db[l];
   }
+  NKBS_CHECK_ARG(dgeo_lead >= 0 && (!dgeo || dgeo_lead + geo_dim <= dgeo_stride), "nkbs_head_tc_bwd: bad dgeo_lead %d", dgeo_lead);
   a.hin.dgeo = dgeo;
   a.hin.dgeo_stride = dgeo_stride;
+  a.hin.dgeo_lead = dgeo ? dgeo_lead : 0;
   a.hin.demb = a.hin.cam ? demb : nullptr;
   a.x = nullptr;
   a.y = nullptr;
+  a.y0 = nullptr;
   a.selector = nullptr;
   a.dy = dy;
+  a.dy0 = nullptr;
   a.dx = nullptr;
   a.N = N;
   const int rc = in_mode == 1   ? launch_tc<true, 1>(a, N, (cudaStream_t)stream, "nkbs_head_tc_bwd")

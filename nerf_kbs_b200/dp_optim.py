@@ -51,6 +51,7 @@ class ShardedAdam:
         self.exp_avg = {k: torch.zeros(v["n"], device=dev) for k, v in self.layout.items()}
         self.exp_avg_sq = {k: torch.zeros(v["n"], device=dev) for k, v in self.layout.items()}
         self.step_t = {k: torch.zeros((), device=dev, dtype=torch.float32) for k in self.layout}
+        self._counters = {k: torch.zeros((), device=dev, dtype=torch.int32) for k in self.layout}
         torch.cuda.synchronize(dev)
         self.hP.barrier()
         torch.cuda.synchronize(dev)
@@ -65,10 +66,10 @@ class ShardedAdam:
         self.hG.barrier()  # every rank's gradients are complete and visible
         for name in active:
             lay = self.layout[name]
-            self.step_t[name].add_(1.0)
             call("nkbs_dp_adam_step", self.world, self.rank, self._g_ptrs, self._p_ptrs, lay["lo"], lay["n"],
                  self.exp_avg[name].data_ptr(), self.exp_avg_sq[name].data_ptr(), float(self.lr), float(self.betas[0]),
-                 float(self.betas[1]), float(self.eps), float(self.weight_decay), self.step_t[name].data_ptr(), stream())
+                 float(self.betas[1]), float(self.eps), float(self.weight_decay), self.step_t[name].data_ptr(),
+                 self._counters[name].data_ptr(), stream())
         self.hP.barrier()  # every rank's parameters are complete (and every peer has read this rank's gradients)
         for name in active:
             lay = self.layout[name]

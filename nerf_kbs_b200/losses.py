@@ -44,8 +44,8 @@ def training_losses(weights_list, ray_samples_list, rgb=None, image=None, logits
 
 
 def training_loss_total(weights_list, ray_samples_list, rgb, image, term_weights, unit_seed=True):
-    """(total, (mse, interlevel, distortion)): the weighted total as the root of the backward pass, gradients weighted
-    inside the kernel (``ops.ray_loss_total``).  Used by the step driver; the loss dict route stays ``training_losses``."""
+    """(total, (mse, interlevel, distortion), the same three weighted): the weighted total as the root of the backward
+    pass, gradients weighted inside the kernel (``ops.ray_loss_total``).  Used by the step driver; the loss dict route stays ``training_losses``."""
     return ops.ray_loss_total(
         _w(weights_list[-1]), ray_samples_to_sdist(ray_samples_list[-1]),
         [_w(w) for w in weights_list[:-1]], [ray_samples_to_sdist(rs) for rs in ray_samples_list[:-1]],

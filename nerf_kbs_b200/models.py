@@ -182,14 +182,9 @@ class NerfactoModel(_ModelBase):
         c = self.config
         if not self.training or c.use_semantic:
             return None
-        total, terms = training_loss_total(outputs["weights_list"], outputs["ray_samples_list"], outputs["rgb"],
-                                           batch["image"], (1.0, c.interlevel_loss_mult, c.distortion_loss_mult))
-        # the dict holds the weighted terms like get_loss_dict does (one launch, for whoever logs them)
-        wv = getattr(self, "_term_weights_dev", None)
-        if wv is None or wv.device != terms.device:
-            wv = self._term_weights_dev = torch.tensor([1.0, c.interlevel_loss_mult, c.distortion_loss_mult],
-                                                       device=terms.device)
-        weighted = terms * wv
+        total, _terms, weighted = training_loss_total(outputs["weights_list"], outputs["ray_samples_list"], outputs["rgb"],
+                                                      batch["image"], (1.0, c.interlevel_loss_mult, c.distortion_loss_mult))
+        # the dict holds the weighted terms like get_loss_dict does (written by the same launch)
         return total, {"rgb_loss": weighted[0], "interlevel_loss": weighted[1], "distortion_loss": weighted[2]}
 
 

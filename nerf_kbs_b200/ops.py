@@ -261,20 +261,22 @@ class _Mlp(torch.autograd.Function):
         dims = [Ws[0].shape[1]] + [w.shape[0] for w in Ws]
         N = x.shape[0]
         y = torch.empty((N, dims[-1]), device=x.device, dtype=torch.float32)
+        # column 0 as its own contiguous output, written by the same launch (no copy kernel)
+        y0 = torch.empty((N,), device=x.device, dtype=torch.float32) if col0 else None
         tc = _MLP_CFG["precision"] == "tc"
         if tc:
             call("nkbs_mlp_tc_fwd", ptr(x), N, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask, out_act,
-                 _MLP_CFG["fwd_fmt"], ptr(selector), ptr(y), stream())
+                 _MLP_CFG["fwd_fmt"], ptr(selector), ptr(y), ptr(y0), stream())
         else:
             call("nkbs_mlp_fwd", ptr(x), N, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask, out_act,
-                 ptr(selector), ptr(y), stream())
+                 ptr(selector), ptr(y), ptr(y0), stream())
         ctx.cfg = (nl, dims, relu_mask, out_act, tc, _MLP_CFG["bwd_fmt"])
         ctx.save_for_backward(x, selector, *Ws, *bs)
         if col0:
             # column 0 also leaves as its own contiguous output (the density of the base MLP): its gradient comes back
             # to THIS node and is added into column 0 of dy, instead of a split node that zero-fills, concatenates and
             # adds three [N,16] tensors
-            return y, y[:, 0].contiguous()
+            return y, y0
         return y
 
     @staticmethod
@@ -288,20 +290,17 @@ class _Mlp(torch.autograd.Function):
         if dy is None:
             dy = torch.zeros((x.shape[0], dims[-1]), device=x.device, dtype=torch.float32)
         dy = _c(dy)
-        if dy0 is not None:
-            if dy._base is not None:  # never write into somebody else's storage
-                dy = dy.clone()
-            dy[:, 0] += dy0.reshape(-1)
+        dy0 = _c(dy0).reshape(-1) if dy0 is not None else None  # added to column 0 of dy inside the kernel
         N = x.shape[0]
         dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
         zs, ret = _grad_buffers(ctx.sinks, Ws + bs)
         dWs, dbs = zs[:nl], zs[nl:]
         if tc:
             call("nkbs_mlp_tc_bwd", ptr(x), ptr(dy), N, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask,
-                 out_act, bwd_fmt, ptr(selector), ptr(dx), host_ptrs(dWs), host_ptrs(dbs), stream())
+                 out_act, bwd_fmt, ptr(selector), ptr(dy0), ptr(dx), host_ptrs(dWs), host_ptrs(dbs), stream())
         else:
             call("nkbs_mlp_bwd", ptr(x), ptr(dy), N, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask,
-                 out_act, ptr(selector), ptr(dx), host_ptrs(dWs), host_ptrs(dbs), stream())
+                 out_act, ptr(selector), ptr(dy0), ptr(dx), host_ptrs(dWs), host_ptrs(dbs), stream())
         grads = []
         for w, b in zip(ret[:nl], ret[nl:]):
             grads += [w, b]
@@ -406,7 +405,10 @@ class _HeadMlp(torch.autograd.Function):
         Ws, bs = list(saved[5:5 + nl]), list(saved[5 + nl:5 + 2 * nl])
         dy = _c(dy)
         N, stride = src.shape
-        dsrc = torch.zeros_like(src) if ctx.needs_input_grad[0] else None
+        # a [N, col + 15] source (the base MLP's [N,16] output, col = 1) is written whole by the kernel: geometry
+        # columns from dX_0, the `col` leading ones zeroed (dgeo_lead); any other layout starts from a zero fill
+        whole = col + 15 == stride
+        dsrc = (torch.empty_like(src) if whole else torch.zeros_like(src)) if ctx.needs_input_grad[0] else None
         demb, demb_ret = None, None
         if use_cam and ctx.needs_input_grad[2]:
             if ctx.emb_sink is not None:
@@ -419,8 +421,8 @@ class _HeadMlp(torch.autograd.Function):
         dgeo = dsrc.reshape(-1)[col:] if dsrc is not None else None
         call("nkbs_head_tc_bwd", sh_dim, 15, emb_dim, ptr(geo), stride, ptr(directions), int(dpr),
              ptr(cam) if use_cam else None, int(cpr), ptr(emb) if use_cam else None, ptr(emb_const), S, ptr(dy), N, nl,
-             host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask, out_act, bwd_fmt, ptr(dgeo), stride, ptr(demb),
-             host_ptrs(dWs), host_ptrs(dbs), stream())
+             host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask, out_act, bwd_fmt, ptr(dgeo), stride,
+             col if (whole and dgeo is not None) else 0, ptr(demb), host_ptrs(dWs), host_ptrs(dbs), stream())
         grads = []
         for w, b in zip(ret[:nl], ret[nl:]):
             grads += [w, b]
@@ -741,6 +743,21 @@ def ray_losses(w_final=None, sdist_final=None, w_props=(), sdist_props=(), rgb=N
     return _RayLosses.apply(meta, w_final, rgb, logits, *w_props)
 
 
+_LOSS_SCRATCH = {}
+
+
+def loss_scratch(device) -> torch.Tensor:
+    """The zero-between-launches accumulator of nkbs_ray_losses_weighted, one per device (loss launches of one device
+    must not overlap on the GPU: one training step at a time per device).  Created on first use: a step driver that
+    captures CUDA graphs asks for it before the capture (trainer.Trainer.__init__), so that it does not live in a
+    graph's private memory pool."""
+    key = torch.device(device).index
+    t = _LOSS_SCRATCH.get(key)
+    if t is None:
+        t = _LOSS_SCRATCH[key] = torch.zeros(8, device=device, dtype=torch.float32)
+    return t
+
+
 class _RayLossTotal(torch.autograd.Function):
     """Weighted total of the colour / interlevel / distortion terms as the ROOT of the backward pass (step driver).
 
@@ -754,7 +771,10 @@ class _RayLossTotal(torch.autograd.Function):
         sdist, sdist_props, image, term_weights, unit_seed = meta
         require_cuda(w_final, rgb, *w_props)
         R, S = w_final.shape
-        out = torch.zeros(6, device=w_final.device, dtype=torch.float32)  # five terms of the kernel + the total
+        # five terms of the kernel, the total, the three weighted terms: written (not accumulated) by the kernel's last
+        # CTA, which also re-zeroes the accumulator scratch: no fill launch around the loss
+        out = torch.empty(9, device=w_final.device, dtype=torch.float32)
+        scratch = loss_scratch(w_final.device)
         w_final, rgb, image = _c(w_final), _c(rgb), _c(image)
         w_props = [_c(t) for t in w_props]
         sdist_props = [_c(t) for t in sdist_props]
@@ -763,16 +783,16 @@ class _RayLossTotal(torch.autograd.Function):
         call("nkbs_ray_losses_weighted", R, S, ptr(_c(sdist)), ptr(w_final), ptr(dw), len(w_props),
              host_i32([t.shape[1] for t in w_props]), host_ptrs(sdist_props), host_ptrs(w_props), host_ptrs(dw_props),
              ptr(rgb), ptr(image), ptr(drgb), None, None, 0, 0, None, ptr(out), host_floats(term_weights),
-             out.data_ptr() + 5 * 4, stream())
+             out.data_ptr() + 5 * 4, ptr(scratch), stream())
         ctx.unit_seed = bool(unit_seed)
         ctx.set_materialize_grads(False)
         ctx.save_for_backward(dw, drgb, *dw_props)
-        terms = out[:3]
-        ctx.mark_non_differentiable(terms)
-        return out[5], terms
+        terms, weighted = out[:3], out[6:9]
+        ctx.mark_non_differentiable(terms, weighted)
+        return out[5], terms, weighted
 
     @staticmethod
-    def backward(ctx, g_total, _g_terms):
+    def backward(ctx, g_total, _g_terms, _g_weighted):
         dw, drgb, *dw_props = ctx.saved_tensors
         if g_total is None:
             return (None,) * (3 + len(dw_props))
@@ -782,7 +802,8 @@ class _RayLossTotal(torch.autograd.Function):
 
 
 def ray_loss_total(w_final, sdist_final, w_props, sdist_props, rgb, image, term_weights, unit_seed=True):
-    """(total, terms[3]) with total = w_rgb * mse + w_inter * interlevel + w_dist * distortion; ``terms`` are the
-    unweighted (mse, interlevel, distortion), not differentiable.  See ``_RayLossTotal`` for ``unit_seed``."""
+    """(total, terms[3], weighted[3]) with total = w_rgb * mse + w_inter * interlevel + w_dist * distortion; ``terms``
+    are the unweighted (mse, interlevel, distortion) and ``weighted`` the same times their weights, neither
+    differentiable.  See ``_RayLossTotal`` for ``unit_seed``."""
     meta = (sdist_final, list(sdist_props), image, tuple(float(v) for v in term_weights), unit_seed)
     return _RayLossTotal.apply(meta, w_final, rgb, *w_props)

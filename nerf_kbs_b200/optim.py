@@ -61,7 +61,8 @@ class Adam:
         arr = lambda xs: (C.c_void_p * n)(*xs)
         call("nkbs_adam_step", n, arr(ps), arr(gs), arr(ms), arr(vs), (C.c_int64 * n)(*ns), float(self.lr),
              float(self.betas[0]), float(self.betas[1]), float(self.eps), float(self.weight_decay),
-             self.step_t.data_ptr(), inv_scale.data_ptr() if inv_scale is not None else None, int(zero_grads), stream())
+             self.step_t.data_ptr(), inv_scale.data_ptr() if inv_scale is not None else None, int(zero_grads), None,
+             stream())
 
     def state_dict(self):
         return {"step": self.step_t.clone(), "exp_avg": [m.clone() for m in self.exp_avg],
@@ -162,6 +163,8 @@ class ArenaAdam:
         self.exp_avg = {k: torch.zeros(v["len"], device=dev) for k, v in arena.layout.items()}
         self.exp_avg_sq = {k: torch.zeros(v["len"], device=dev) for k, v in arena.layout.items()}
         self.step_t = {k: torch.zeros((), device=dev, dtype=torch.float32) for k in arena.layout}
+        # arrival counters of the kernels' last-CTA step-count store (nkbs_adam_step: step_counter)
+        self._counters = {k: torch.zeros((), device=dev, dtype=torch.int32) for k in arena.layout}
 
     @torch.no_grad()
     def step(self, active: Optional[Sequence[str]] = None, inv_scale: Optional[torch.Tensor] = None,
@@ -169,14 +172,13 @@ class ArenaAdam:
         a = self.arena
         for name in (active if active is not None else list(a.layout)):
             lay = a.layout[name]
-            self.step_t[name].add_(1.0)
             one = lambda x: (C.c_void_p * 1)(x)
             off = lay["start"] * 4
             call("nkbs_adam_step", 1, one(a.P.data_ptr() + off), one(a.G.data_ptr() + off),
                  one(self.exp_avg[name].data_ptr()), one(self.exp_avg_sq[name].data_ptr()), (C.c_int64 * 1)(lay["len"]),
                  float(self.lr), float(self.betas[0]), float(self.betas[1]), float(self.eps), float(self.weight_decay),
                  self.step_t[name].data_ptr(), inv_scale.data_ptr() if inv_scale is not None else None, int(zero_grads),
-                 stream())
+                 self._counters[name].data_ptr(), stream())
 
     def moments_of(self, p: torch.nn.Parameter):
         """(exp_avg, exp_avg_sq) views shaped like ``p`` (checkpointing, tests)."""

@@ -122,7 +122,7 @@ class Trainer:
         self._in_step = False
         self._join_adam = False
         self._adam_stream = torch.cuda.Stream(p0.device, priority=0)   # lowest priority: fills what the step leaves idle
-        self._step_stream = torch.cuda.Stream(p0.device, priority=-1)  # captured steps run at high priority
+        self._step_stream = torch.cuda.Stream(p0.device, priority=int(os.environ.get("NKBS_STEP_PRIO", "-1")))  # captured steps run at high priority
         self._hooks = [model.register_forward_pre_hook(self._pre_model_forward),
                        model.field.register_forward_pre_hook(self._pre_field_forward)]
         self._inv_world = torch.full((), 1.0 / self.world_size, device=p0.device) if self.world_size > 1 else None
@@ -151,6 +151,9 @@ class Trainer:
             self.buf["semantics_label"] = torch.zeros(self.R, device=dev, dtype=torch.int64)
         n_levels = model.proposal_sampler.num_proposal_network_iterations + 1
         self.jitter = torch.zeros(n_levels, self.R, 1, device=dev) if inject_jitter else None
+        from . import ops
+        ops.loss_scratch(dev)  # created outside any capture
+        self._unit = torch.ones((), device=dev)  # seed of the backward pass (backward() would fill one per step)
         self.pinned = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True) for k, v in self.buf.items()}
         # the collider's near / far planes are static inputs of the captured step as well: the graphs bake in their
         # addresses, so they are owned here and not by the collider's (evictable) cache
@@ -275,7 +278,7 @@ class Trainer:
         else:
             loss_dict = self.model.get_loss_dict(outputs, batch)
             loss = sum(loss_dict.values())
-        loss.backward()
+        torch.autograd.backward([loss], [self._unit])
         # detached views only: a reference to the live outputs would keep this step's autograd graph — and with it the
         # parameters' AccumulateGrad nodes, bound to THIS step's stream — alive into the next step's capture
         self.outputs = _detach_tree(outputs)

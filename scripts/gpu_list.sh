@@ -1,0 +1,8 @@
+#!/bin/bash
+# ncu launch list of the eager 4096-ray step
+cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
+mkdir -p gpurun_out
+CMD="python bench.py --no-graph --no-cpu-baseline --no-kernel-pass --no-render --no-legs --steps 2 --warmup 3"
+timeout 300 $CMD > gpurun_out/plain.log 2>&1 && \
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
+echo "launch list exit $?"

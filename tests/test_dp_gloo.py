@@ -75,3 +75,16 @@ def test_sharded_adam_flat_layout():
             sl.sort()
             assert sl[0][0] == lay[name]["start"] and sl[-1][1] == lay[name]["start"] + lay[name]["len"]
             assert all(a[1] == b[0] for a, b in zip(sl, sl[1:]))
+
+
+def test_rank_ray_ranges_partition_a_frame():
+    """Full-frame render over several ranks: contiguous, ordered, balanced blocks that cover every ray exactly once."""
+    from nerf_kbs_b200.render import rank_ray_range
+    N = 375 * 1242
+    for ws in (1, 2, 4, 8):
+        blocks = [rank_ray_range(N, r, ws) for r in range(ws)]
+        assert [i for b in blocks for i in (b.start, b.stop)][0] == 0 and blocks[-1].stop == N
+        assert all(a.stop == b.start for a, b in zip(blocks, blocks[1:]))
+        assert max(len(b) for b in blocks) - min(len(b) for b in blocks) < ws
+    # ceil-sized blocks: a frame much smaller than the rank count leaves the last ranks empty (the driver refuses that)
+    assert [len(rank_ray_range(5, r, 4)) for r in range(4)] == [2, 2, 1, 0]

@@ -197,8 +197,9 @@ def test_weighted_loss_kernel_scales_its_gradients():
     want = [t.grad.clone() for t in (w, wp, rgb)]
     for t in (w, wp, rgb):
         t.grad = None
-    total, terms = ops.ray_loss_total(w, sd, [wp], [sdp], rgb, img, tw)
+    total, terms, weighted = ops.ray_loss_total(w, sd, [wp], [sdp], rgb, img, tw)
     total.backward()
+    assert torch.allclose(weighted, torch.tensor(tw, device=DEV) * terms, rtol=1e-6, atol=0)
     assert abs(total.item() - (tw[0] * mse + tw[1] * inter + tw[2] * dist).item()) <= 1e-6 * abs(total.item())
     assert torch.allclose(terms, torch.stack([mse, inter, dist]).detach(), rtol=1e-6, atol=0)
     for got, ref in zip((w.grad, wp.grad, rgb.grad), want):
@@ -206,7 +207,7 @@ def test_weighted_loss_kernel_scales_its_gradients():
     # a non-unit seed is honoured when the caller says so
     for t in (w, wp, rgb):
         t.grad = None
-    total, _ = ops.ray_loss_total(w, sd, [wp], [sdp], rgb, img, tw, unit_seed=False)
+    total, _, _ = ops.ray_loss_total(w, sd, [wp], [sdp], rgb, img, tw, unit_seed=False)
     (3.0 * total).backward()
     assert rel_err(rgb.grad, 3.0 * want[2]) < 1e-6
 
