@@ -456,8 +456,9 @@ def _finish(dist):
 
 
 
-COLLECTIVE = ("symmetric-memory reduce-scatter + Adam + all-gather in one kernel over NVLink peer memory "
-              "(nkbs_dp_adam_step); NCCL: barriers and the timing reduce only")
+COLLECTIVE = ("symmetric-memory reduce-scatter + Adam + all-gather in one kernel over NVLink (nkbs_dp_adam_step: peer "
+              "loads / stores at N = 2, in-switch multimem.ld_reduce / multimem.st from N = 4); NCCL: barriers and the "
+              "timing reduce only")
 
 
 def _collective(world):

@@ -236,7 +236,12 @@ int nkbs_adam_step(int32_t num_tensors, float* const* params, float* const* grad
  * replaces: NCCL allreduce of the gradients + nkbs_adam_step (datamanager_z.py:225-231 DDP setup; train.py:85-98). */
 int nkbs_dp_adam_step(int32_t world, int32_t rank, const float* const* grad_peers, float* const* param_peers,
                       int64_t lo, int64_t n, float* exp_avg, float* exp_avg_sq, float lr, float beta1, float beta2,
-                      float eps, float weight_decay, float* step_dev, uint32_t* step_counter, void* stream);
+                      float eps, float weight_decay, float* step_dev, uint32_t* step_counter,
+                      const float* grad_multicast, float* param_multicast, void* stream);
+/* grad_multicast / param_multicast (both or neither): the NVSwitch multicast (NVLS) addresses of the two symmetric
+ * buffers.  With them the gradient sum of the owned slice is one `multimem.ld_reduce` (reduced inside the switch) and
+ * the new parameters one `multimem.st` (replicated by the switch) per 16 bytes, instead of `world` peer loads and
+ * `world` peer stores. */
 
 /* One proposal level of ProposalNetworkSampler in one ray-major pass (forward): the level's bins (gen_bins != 0:
  * produced here by the initial piecewise sampler from lin [S+1] and the per-ray jitter t_rand [R] (NULL in

@@ -50,7 +50,7 @@ SIGNATURES = {
                                 _p, _i32, _p, _p, _p, _i32, _f, _p, _f, _f, _p, _p, _p, _p, _p],
     "nkbs_apply_colormap": [_i64, _p, _p, _p, _p],
     "nkbs_apply_depth_colormap": [_i64, _p, _p, _p, _i32, _f, _i32, _f, _p, _p, _p],
-    "nkbs_dp_adam_step": [_i32, _i32, _p, _p, _i64, _i64, _p, _p, _f, _f, _f, _f, _f, _p, _p, _p],
+    "nkbs_dp_adam_step": [_i32, _i32, _p, _p, _i64, _i64, _p, _p, _f, _f, _f, _f, _f, _p, _p, _p, _p, _p],
     "nkbs_composite_bwd": [_i64, _i32, _p, _p, _p, _p, _i32, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
 }
 

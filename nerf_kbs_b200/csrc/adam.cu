@@ -115,6 +115,8 @@ struct DpAdamArgs {
   float lr, beta1, beta2, eps, weight_decay;
   float* step_dev;
   unsigned* counter;          // as AdamArgs::counter
+  const float* g_mc;          // multicast (NVLS) address of the gradient buffer, or null
+  float* p_mc;                // multicast address of the parameter buffer, or null
 };
 
 // WORLD > 0: number of ranks known at compile time, the peer loads of one element are all in flight together
@@ -173,6 +175,72 @@ __global__ void __launch_bounds__(kThreads) dp_adam_kernel(const DpAdamArgs a) {
   advance_step(a.step_dev, a.counter, t);
 }
 
+
+// The same step through the NVSwitch's multicast objects (NVLS): `multimem.ld_reduce` returns the SUM over all ranks of
+// one 16-byte piece of the gradient — the reduction happens inside the switch, this GPU receives one slice instead of
+// `world` of them — and `multimem.st` hands one store of the new parameters to the switch, which replicates it into
+// every rank's buffer (this rank's included).  NVLink traffic per GPU drops from 2 (world - 1) / world to 2 / world of
+// the parameter bytes.  The sum's order inside the switch is not specified, but only the owner of a slice reduces it and
+// every rank receives the owner's result: ranks stay bit-identical.
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st(float* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w)
+               : "memory");
+}
+
+__global__ void __launch_bounds__(kThreads) dp_adam_multimem_kernel(const DpAdamArgs a) {
+  const float t = a.counter ? *a.step_dev + 1.f : *a.step_dev;
+  const float bc1 = 1.f - powf(a.beta1, t);
+  const float bc2 = 1.f - powf(a.beta2, t);
+  const float step_size = a.lr / bc1;
+  const float sqrt_bc2 = sqrtf(bc2);
+  const float inv_world = 1.f / (float)a.world;
+  const int64_t nvec = a.n >> 2;
+  // kU pieces per thread and pass, all reductions issued before the first is used: a switch round trip is several
+  // microseconds, the loop must keep many of them in flight
+  constexpr int kU = 4;
+  const int64_t stride = (int64_t)gridDim.x * kThreads;
+  for (int64_t q0 = blockIdx.x * (int64_t)kThreads + threadIdx.x; q0 < nvec; q0 += kU * stride) {
+    float4 g[kU], p[kU], m[kU], v[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int64_t q = q0 + u * stride;
+      if (q < nvec) g[u] = multimem_ld_reduce_add(a.g_mc + a.lo + 4 * q);
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int64_t q = q0 + u * stride;
+      if (q < nvec) {
+        p[u] = *reinterpret_cast<const float4*>(a.p[a.rank] + a.lo + 4 * q);
+        m[u] = *reinterpret_cast<const float4*>(a.m + 4 * q);
+        v[u] = *reinterpret_cast<const float4*>(a.v + 4 * q);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int64_t q = q0 + u * stride;
+      if (q < nvec) {
+        adam_one(p[u].x, g[u].x * inv_world, m[u].x, v[u].x, a.beta1, a.beta2, a.eps, step_size, sqrt_bc2, a.weight_decay);
+        adam_one(p[u].y, g[u].y * inv_world, m[u].y, v[u].y, a.beta1, a.beta2, a.eps, step_size, sqrt_bc2, a.weight_decay);
+        adam_one(p[u].z, g[u].z * inv_world, m[u].z, v[u].z, a.beta1, a.beta2, a.eps, step_size, sqrt_bc2, a.weight_decay);
+        adam_one(p[u].w, g[u].w * inv_world, m[u].w, v[u].w, a.beta1, a.beta2, a.eps, step_size, sqrt_bc2, a.weight_decay);
+        *reinterpret_cast<float4*>(a.m + 4 * q) = m[u];
+        *reinterpret_cast<float4*>(a.v + 4 * q) = v[u];
+        multimem_st(a.p_mc + a.lo + 4 * q, p[u]);
+      }
+    }
+  }
+  advance_step(a.step_dev, a.counter, t);
+}
+
 }  // namespace
 
 extern "C" int nkbs_adam_step(int32_t num_tensors, float* const* params, float* const* grads,
@@ -221,7 +289,7 @@ extern "C" int nkbs_adam_step(int32_t num_tensors, float* const* params, float* 
 extern "C" int nkbs_dp_adam_step(int32_t world, int32_t rank, const float* const* grad_peers, float* const* param_peers,
                                  int64_t lo, int64_t n, float* exp_avg, float* exp_avg_sq, float lr, float beta1,
                                  float beta2, float eps, float weight_decay, float* step_dev, uint32_t* step_counter,
-                                 void* stream) {
+                                 const float* grad_multicast, float* param_multicast, void* stream) {
   NKBS_CHECK_ARG(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world, "nkbs_dp_adam_step: bad world/rank %d/%d", world, rank);
   NKBS_CHECK_ARG(lo >= 0 && n >= 0 && (lo & 3) == 0 && (n & 3) == 0, "nkbs_dp_adam_step: slice must be 4-element aligned");
   if (n == 0) return 0;
@@ -247,10 +315,20 @@ extern "C" int nkbs_dp_adam_step(int32_t world, int32_t rank, const float* const
   a.weight_decay = weight_decay;
   a.step_dev = step_dev;
   a.counter = step_counter;
+  NKBS_CHECK_ARG((grad_multicast == nullptr) == (param_multicast == nullptr), "nkbs_dp_adam_step: both multicast addresses or none");
+  NKBS_CHECK_ARG(((reinterpret_cast<uintptr_t>(grad_multicast) | reinterpret_cast<uintptr_t>(param_multicast)) & 15) == 0,
+                 "nkbs_dp_adam_step: multicast addresses must be 16-byte aligned");
+  a.g_mc = grad_multicast;
+  a.p_mc = param_multicast;
   int64_t blocks = ((n >> 2) + kThreads - 1) / kThreads;
   int64_t cap = (int64_t)nkbs_num_sms() * 8;
   const int grid = (int)(blocks < cap ? blocks : cap);
   cudaStream_t st = (cudaStream_t)stream;
+  if (a.g_mc) {
+    dp_adam_multimem_kernel<<<grid, kThreads, 0, st>>>(a);
+    NKBS_CHECK_LAUNCH("nkbs_dp_adam_step(multimem)");
+    return 0;
+  }
   switch (world) {
     case 2: dp_adam_kernel<2><<<grid, kThreads, 0, st>>>(a); break;
     case 4: dp_adam_kernel<4><<<grid, kThreads, 0, st>>>(a); break;

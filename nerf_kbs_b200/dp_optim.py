@@ -48,6 +48,17 @@ class ShardedAdam:
         self.hG = symm_mem.rendezvous(arena.G, pg.group_name)
         self._p_ptrs = (C.c_void_p * self.world)(*[int(x) for x in self.hP.buffer_ptrs])
         self._g_ptrs = (C.c_void_p * self.world)(*[int(x) for x in self.hG.buffer_ptrs])
+        # NVSwitch multicast addresses of the two buffers (0 where the fabric / driver has no NVLS): in-switch reduction
+        # of the gradients and replicated parameter stores (csrc/adam.cu).  Used from 4 ranks on: measured on the
+        # B200 box, 4096-ray step, peer loads / stores vs multimem: N=2 0.814 / 0.886 ms, N=4 0.867 / 0.840 ms,
+        # N=8 0.905 / 0.841 ms (profiles/r02_dp_multimem.txt) — per GPU the switch route moves 2/N of the parameter
+        # bytes instead of 2 (N-1)/N, but one multimem round trip is slower than a peer access.
+        # NKBS_DP_MULTIMEM=0 / 1 forces the choice.
+        import os
+        g_mc, p_mc = int(getattr(self.hG, "multicast_ptr", 0) or 0), int(getattr(self.hP, "multicast_ptr", 0) or 0)
+        want = os.environ.get("NKBS_DP_MULTIMEM", "auto")
+        self.multimem = bool(g_mc and p_mc) and (want == "1" or (want not in ("0", "1") and self.world >= 4))
+        self._g_mc, self._p_mc = (g_mc, p_mc) if self.multimem else (None, None)
         self.exp_avg = {k: torch.zeros(v["n"], device=dev) for k, v in self.layout.items()}
         self.exp_avg_sq = {k: torch.zeros(v["n"], device=dev) for k, v in self.layout.items()}
         self.step_t = {k: torch.zeros((), device=dev, dtype=torch.float32) for k in self.layout}
@@ -69,7 +80,7 @@ class ShardedAdam:
             call("nkbs_dp_adam_step", self.world, self.rank, self._g_ptrs, self._p_ptrs, lay["lo"], lay["n"],
                  self.exp_avg[name].data_ptr(), self.exp_avg_sq[name].data_ptr(), float(self.lr), float(self.betas[0]),
                  float(self.betas[1]), float(self.eps), float(self.weight_decay), self.step_t[name].data_ptr(),
-                 self._counters[name].data_ptr(), stream())
+                 self._counters[name].data_ptr(), self._g_mc, self._p_mc, stream())
         self.hP.barrier()  # every rank's parameters are complete (and every peer has read this rank's gradients)
         for name in active:
             lay = self.layout[name]
