@@ -290,8 +290,13 @@ def kernel_pass(trainer, batches, steps):
     sampler = trainer.model.proposal_sampler
     was_side, sampler.side_streams = sampler.side_streams, False
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    _lib.launch_observer = observer
     try:
+        # one untimed eager step first: after graph replays the caching allocator has no free blocks for the eager
+        # intermediates, and the first eager step pays for their cudaMalloc calls
+        b = batches[0]
+        trainer.train_step(RayBundle(b["origins"], b["directions"], b["pixel_area"], b["camera_indices"]), b)
+        torch.cuda.synchronize()
+        _lib.launch_observer = observer
         t0.record()
         for i in range(steps):
             b = batches[i % len(batches)]
