@@ -211,6 +211,18 @@ int nkbs_composite_bwd(int64_t R, int32_t S, const float* density, const float* 
                        const float* g_sem, float* d_density, float* d_weights, float* d_rgb, float* d_sem,
                        void* stream);
 
+/* K6 + K5 — one proposal level's RaySamples.get_weights (+ median depth, may be NULL) and the NEXT level's PDFSampler in
+ * one ray-major launch: the warp that has computed a ray's weights resamples that ray straight from shared memory (no
+ * [R,S] weights round trip, one launch instead of two).  density [R,S]; ebins / sbins [R,S+1] euclidean / spacing bin
+ * edges of this level; the remaining arguments as nkbs_pdf_sample (rand: [R] per-ray jitter or NULL).  Same arithmetic
+ * as nkbs_composite_fwd followed by nkbs_pdf_sample (bit-identical outputs).
+ * replaces: RaySamples.get_weights + PDFSampler inside ProposalNetworkSampler (nerfacto.py:325-332,397). */
+int nkbs_weights_resample_fwd(int64_t R, int32_t S, const float* density, const float* ebins, const float* sbins,
+                              const float* nears, const float* fars, int32_t num_bins, float anneal,
+                              const float* anneal_dev, float histogram_padding, float eps, const float* u_base,
+                              const float* rand, float* weights, float* depth_med, float* out_sbins, float* out_ebins,
+                              void* stream);
+
 /* N2 — multi-tensor Adam (torch.optim.Adam semantics, amsgrad off).
  * replaces: the Adam(lr=1e-3, eps=1e-15) optimizers the reference configures for the "fields" and
  *           "proposal_networks" groups (train.py:85-98; groups nerfacto.py:359-363).

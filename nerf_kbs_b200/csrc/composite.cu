@@ -5,6 +5,7 @@
 #include <float.h>
 #include "common.cuh"
 #include "nkbs.h"
+#include "sampler.cuh"
 
 namespace {
 
@@ -39,6 +40,19 @@ struct CompArgs {
   float* depth_med;       // [R]
   float* sem_out;         // [R,C]
   int* minmax;            // [2] ordered-int keys of min/max step (for the expected-depth clip)
+  // optional tail: inverse-CDF resampling of the NEXT level's bins from this level's weights (PDFSampler), done by the
+  // warp that has just computed the ray's weights, straight from its shared-memory strip (pdf_nb = 0: none)
+  int pdf_nb;
+  float pdf_anneal;
+  const float* pdf_anneal_dev;
+  float pdf_hist_pad, pdf_eps;
+  const float* pdf_sbins;     // [R,S+1] spacing-domain bin edges of this level
+  const float* pdf_u;         // [pdf_nb] torch.linspace(0, 1 - 1/nb, nb)
+  const float* pdf_rand;      // [R] per-ray jitter or null (centred evaluation points)
+  const float* nears;         // [R]
+  const float* fars;          // [R]
+  float* pdf_out_sbins;       // [R,pdf_nb]
+  float* pdf_out_ebins;       // [R,pdf_nb]
 };
 
 __device__ __forceinline__ int float_key(float f) {
@@ -68,10 +82,11 @@ __device__ __forceinline__ float nan_to_num(float w) {
 }
 
 __global__ void __launch_bounds__(kThreads) composite_fwd_kernel(const CompArgs a) {
-  extern __shared__ float s_w[];  // [kWarpsPerCta][S]
+  extern __shared__ float s_w[];  // [kWarpsPerCta][strip (+ S + 1 floats of cdf when resampling)]
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  float* sw = s_w + wid * strip_len(a.S);
   const int S = a.S;
+  float* sw = s_w + wid * (strip_len(S) + (a.pdf_nb ? S + 1 : 0));
+  const PdfParams pp{S, a.pdf_nb, (a.pdf_nb && a.pdf_anneal_dev) ? *a.pdf_anneal_dev : a.pdf_anneal, a.pdf_hist_pad, a.pdf_eps, a.pdf_u};
   float lmin = FLT_MAX, lmax = -FLT_MAX;
   for (int64_t r = blockIdx.x * (int64_t)kWarpsPerCta + wid; r < a.R; r += (int64_t)gridDim.x * kWarpsPerCta) {
     const int64_t base = r * S;
@@ -190,6 +205,19 @@ __global__ void __launch_bounds__(kThreads) composite_fwd_kernel(const CompArgs 
           for (int s = 0; s < S; ++s) v += sw[PI(s)] * sem[(int64_t)s * a.C + c];
         if (c < a.C) a.sem_out[r * a.C + c] = v;
       }
+    }
+    if (a.pdf_nb) {
+      // last use of the strip for this ray: the pdf values overwrite the weights in place (element s is read and then
+      // written by the same lane)
+      __syncwarp();
+      struct Strip {
+        float* p;
+        __device__ __forceinline__ float& operator[](int q) const { return p[PI(q)]; }
+      };
+      const float* sb = a.pdf_sbins + r * (S + 1);
+      nkbs_pdf_ray_warp(pp, [&](int q) { return sw[PI(q)]; }, [&](int k) { return sb[k]; }, Strip{sw}, sw + strip_len(S),
+                        lane, a.pdf_rand != nullptr, a.pdf_rand ? a.pdf_rand[r] : 0.f, nullptr, a.nears[r], a.fars[r],
+                        a.pdf_out_sbins + r * a.pdf_nb, a.pdf_out_ebins + r * a.pdf_nb, nullptr);
     }
     __syncwarp();
   }
@@ -383,6 +411,8 @@ extern "C" int nkbs_composite_fwd(int64_t R, int32_t S, const float* density, co
   NKBS_CHECK_ARG(bin_stride == 0 || bin_stride >= S, "nkbs_composite_fwd: bin_stride %d < S", bin_stride);
   CompArgs a{R, S, density, weights_in, starts, ends, bin_stride ? bin_stride : S, rgb, sem, C, bg_mode, eval_mode,
              weights, rgb_out, acc_out, depth_exp_raw, depth_med, sem_out, depth_exp ? minmax_ws : nullptr};
+  a.pdf_nb = 0;
+  a.pdf_anneal_dev = nullptr;
   if (depth_exp) minmax_init_kernel<<<1, 1, 0, st>>>(minmax_ws);
   size_t smem = (size_t)kWarpsPerCta * strip_len(S) * sizeof(float);
   composite_fwd_kernel<<<comp_grid(R), kThreads, smem, st>>>(a);
@@ -474,11 +504,44 @@ extern "C" int nkbs_expected_depth_noalloc(int64_t R, int32_t S, const float* we
   cudaStream_t st = (cudaStream_t)stream;
   CompArgs a{R, S, nullptr, weights, starts, ends, bin_stride ? bin_stride : S, nullptr, nullptr, 0, 0, 0,
              nullptr, nullptr, nullptr, raw, nullptr, nullptr, mm};
+  a.pdf_nb = 0;
+  a.pdf_anneal_dev = nullptr;
   minmax_init_kernel<<<1, 1, 0, st>>>(mm);
   const size_t smem = (size_t)kWarpsPerCta * strip_len(S) * sizeof(float);
   composite_fwd_kernel<<<comp_grid(R), kThreads, smem, st>>>(a);
   NKBS_CHECK_LAUNCH("nkbs_expected_depth_noalloc");
   clip_depth_kernel<<<(int)((R + 255) / 256), 256, 0, st>>>(raw, mm, R, depth, nullptr);
   NKBS_CHECK_LAUNCH("nkbs_expected_depth_noalloc(clip)");
+  return 0;
+}
+
+// ---- get_weights + median depth of one proposal level and PDFSampler of the next, one ray-major launch ----------------
+extern "C" int nkbs_weights_resample_fwd(int64_t R, int32_t S, const float* density, const float* ebins,
+                                         const float* sbins, const float* nears, const float* fars, int32_t num_bins,
+                                         float anneal, const float* anneal_dev, float histogram_padding, float eps,
+                                         const float* u_base, const float* rand, float* weights, float* depth_med,
+                                         float* out_sbins, float* out_ebins, void* stream) {
+  NKBS_CHECK_ARG(R >= 0 && S >= 1 && S <= kMaxS && num_bins >= 2, "nkbs_weights_resample_fwd: S=%d outside 1..%d or bins=%d < 2",
+                 S, kMaxS, num_bins);
+  if (R == 0) return 0;
+  NKBS_CHECK_ARG(density && ebins && sbins && nears && fars && u_base && weights && out_sbins && out_ebins,
+                 "nkbs_weights_resample_fwd: null argument");
+  CompArgs a{R, S, density, nullptr, ebins, ebins + 1, S + 1, nullptr, nullptr, 0, 0, 0,
+             weights, nullptr, nullptr, nullptr, depth_med, nullptr, nullptr};
+  a.pdf_nb = num_bins;
+  a.pdf_anneal = anneal;
+  a.pdf_anneal_dev = anneal_dev;
+  a.pdf_hist_pad = histogram_padding;
+  a.pdf_eps = eps;
+  a.pdf_sbins = sbins;
+  a.pdf_u = u_base;
+  a.pdf_rand = rand;
+  a.nears = nears;
+  a.fars = fars;
+  a.pdf_out_sbins = out_sbins;
+  a.pdf_out_ebins = out_ebins;
+  const size_t smem = (size_t)kWarpsPerCta * (strip_len(S) + S + 1) * sizeof(float);
+  composite_fwd_kernel<<<comp_grid(R), kThreads, smem, (cudaStream_t)stream>>>(a);
+  NKBS_CHECK_LAUNCH("nkbs_weights_resample_fwd");
   return 0;
 }

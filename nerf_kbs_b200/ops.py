@@ -683,6 +683,69 @@ def composite(density=None, weights=None, rgb=None, sem=None, starts=None, ends=
 
 
 # ----------------------------------------------------------------------------------------------
+# get_weights (+ median depth) of a proposal level and the next level's PDF resampling, one ray-major launch
+# ----------------------------------------------------------------------------------------------
+_FUSED_RESAMPLE = {"enabled": __import__("os").environ.get("NKBS_FUSED_RESAMPLE", "1") != "0"}
+
+
+def set_fused_resample(enabled: bool) -> None:
+    _FUSED_RESAMPLE["enabled"] = bool(enabled)
+
+
+def fused_resample_enabled() -> bool:
+    return _FUSED_RESAMPLE["enabled"]
+
+
+class _WeightsResample(torch.autograd.Function):
+    """(weights [R,S], median depth [R], next spacing bins, next euclidean bins) of one proposal level from its density
+    (nkbs_weights_resample_fwd).  Differentiable: weights w.r.t. density (nkbs_composite_bwd); bins are detached in
+    the reference."""
+
+    @staticmethod
+    def forward(ctx, density, ebins, sbins, nears, fars, cfg, rand):
+        nb, anneal, anneal_dev, hist_pad, eps = cfg
+        density = _c(density)
+        R, S = density.shape
+        ebins, sbins = _c(ebins), _c(sbins)
+        nears, fars = _c(nears).reshape(-1), _c(fars).reshape(-1)
+        require_cuda(density, ebins, sbins, nears, rand)
+        dev = density.device
+        f32 = dict(device=dev, dtype=torch.float32)
+        weights, dmed = torch.empty((R, S), **f32), torch.empty((R,), **f32)
+        nsb, neb = torch.empty((R, nb), **f32), torch.empty((R, nb), **f32)
+        rand = _c(rand).reshape(-1) if rand is not None else None
+        call("nkbs_weights_resample_fwd", R, S, ptr(density), ptr(ebins), ptr(sbins), ptr(nears), ptr(fars), nb,
+             float(anneal), ptr(anneal_dev), float(hist_pad), float(eps), ptr(_lin_table("u", nb, dev)), ptr(rand),
+             ptr(weights), ptr(dmed), ptr(nsb), ptr(neb), stream())
+        ctx.shape = (R, S)
+        ctx.set_materialize_grads(False)
+        ctx.save_for_backward(density, weights, ebins)
+        ctx.mark_non_differentiable(dmed, nsb, neb)
+        return weights, dmed, nsb, neb
+
+    @staticmethod
+    def backward(ctx, g_w, *_unused):
+        R, S = ctx.shape
+        density, weights, ebins = ctx.saved_tensors
+        if g_w is None or not ctx.needs_input_grad[0]:
+            return (None,) * 7
+        g_w = _c(g_w)
+        ddensity = torch.empty_like(density)
+        call("nkbs_composite_bwd", R, S, ptr(density), ptr(weights), ebins.data_ptr(), ebins.data_ptr() + 4, S + 1, None,
+             None, 0, 0, 0, None, None, ptr(g_w), None, None, None, None, ptr(ddensity), None, None, None, stream())
+        return (ddensity,) + (None,) * 6
+
+
+def weights_resample(density, euclid_bins, spacing_bins, nears, fars, num_next: int, rand=None, anneal: float = 1.0,
+                     anneal_dev=None, histogram_padding: float = 0.01, eps: float = 1e-5):
+    """``density`` [R,S(,1)] of a proposal level over its [R,S+1] bin edges -> (weights [R,S], median depth [R], next
+    spacing bins [R,num_next+1], next euclidean bins [R,num_next+1]); ``rand`` [R,1] per-ray jitter, None = centred."""
+    d = density.squeeze(-1) if density.dim() == 3 else density
+    cfg = (int(num_next) + 1, float(anneal), anneal_dev, float(histogram_padding), float(eps))
+    return _WeightsResample.apply(d, euclid_bins, spacing_bins, nears, fars, cfg, rand)
+
+
+# ----------------------------------------------------------------------------------------------
 # N1 per-ray losses (interlevel, distortion, colour MSE, semantic cross-entropy) in one launch
 # ----------------------------------------------------------------------------------------------
 class _RayLosses(torch.autograd.Function):

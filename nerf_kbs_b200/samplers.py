@@ -165,6 +165,23 @@ class ProposalNetworkSampler(nn.Module):
                 return False
         return True
 
+    def _resample_fusable(self, ray_samples, density, jitter, i_level: int, stratified: bool) -> bool:
+        """get_weights of a level and the PDF resampling of the next run as one launch (ops.weights_resample) when the
+        samples carry their [R,S+1] bin arrays and the jitter is per ray (use_single_jitter) or absent (evaluation)."""
+        if not ops.fused_resample_enabled() or ray_samples.spacing_bins is None or ray_samples.euclid_bins is None:
+            return False
+        if density.dim() != 3 or density.shape[-1] != 1 or density.shape[1] > 512:
+            return False
+        if stratified:
+            if jitter is None or not self.pdf_sampler.single_jitter:
+                return False
+            t = jitter[i_level + 1]
+            if t is None or t.shape[-1] != 1:
+                return False
+        elif self.training and self.pdf_sampler.train_stratified:
+            return False  # stratified training without injected / pre-drawn jitter: the sampler draws its own
+        return True
+
     def generate_ray_samples(self, ray_bundle: Optional[RayBundle] = None, density_fns: Optional[List[Callable]] = None,
                              jitter=None) -> Tuple[RaySamples, List, List]:
         """``jitter`` (optional [t_rand0, rand1, rand2]) injects the random draws, for parity tests."""
@@ -241,10 +258,22 @@ class ProposalNetworkSampler(nn.Module):
                         density, _ = owner.get_density(ray_samples)  # per-ray frustum path, no [R,S,3] tensor
                     else:
                         density = fn(ray_samples.frustums.get_positions())
-                    weights = ray_samples.get_weights(density)
+                    if self._resample_fusable(ray_samples, density, jitter, i_level, stratified):
+                        # weights + median depth of this level and the bins of the next one in ONE ray-major launch
+                        num_next = (self.num_proposal_samples_per_ray[i_level + 1] if i_level + 1 < n
+                                    else self.num_nerf_samples_per_ray)
+                        w, dmed, nsb, neb = ops.weights_resample(
+                            density, ray_samples.euclid_bins, ray_samples.spacing_bins, ray_bundle.nears, ray_bundle.fars,
+                            num_next, rand=(jitter[i_level + 1] if stratified else None), anneal=float(self._anneal),
+                            anneal_dev=self.pdf_sampler.anneal_dev, histogram_padding=self.pdf_sampler.histogram_padding)
+                        weights = w[..., None]
+                        weights._nkbs_depth_med = dmed[..., None]
+                        next_bins = (nsb, neb)
+                    else:
+                        weights = ray_samples.get_weights(density)
                 if side is not None:
                     cur.wait_stream(side)
-                    for t in (weights, getattr(weights, "_nkbs_depth_med", None)):
+                    for t in (weights, getattr(weights, "_nkbs_depth_med", None)) + (tuple(next_bins) if next_bins is not None else ()):
                         if t is not None:
                             t.record_stream(cur)
                 weights_list.append(weights)
