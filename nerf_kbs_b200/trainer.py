@@ -141,20 +141,28 @@ class Trainer:
         dev = self.device
         C = getattr(model.config, "num_semantic_classes", 0)
         self.needs_labels = bool(getattr(model.config, "use_semantic", False)) or model.__class__.__name__ == "SemanticNerfWModel"
-        # static device-side inputs of the step (CUDA-graph replay reads these addresses)
-        self.buf = {
-            "origins": torch.zeros(self.R, 3, device=dev), "directions": torch.zeros(self.R, 3, device=dev),
-            "camera_indices": torch.zeros(self.R, 1, device=dev, dtype=torch.int64),
-            "pixel_area": torch.zeros(self.R, 1, device=dev), "image": torch.zeros(self.R, 3, device=dev),
-        }
+        # static device-side inputs of the step (CUDA-graph replay reads these addresses): views of ONE flat buffer, so a
+        # batch that arrives packed in the same layout (``pack_batch``) is one copy — one H2D transfer per step from a
+        # pinned host batch, one D2D copy from a device-resident one — instead of one per tensor
+        spec = [("origins", (self.R, 3), torch.float32), ("directions", (self.R, 3), torch.float32),
+                ("camera_indices", (self.R, 1), torch.int64), ("pixel_area", (self.R, 1), torch.float32),
+                ("image", (self.R, 3), torch.float32)]
         if self.needs_labels:
-            self.buf["semantics_label"] = torch.zeros(self.R, device=dev, dtype=torch.int64)
+            spec.append(("semantics_label", (self.R,), torch.int64))
+        self._layout, off = {}, 0
+        for k, shape, dt in spec:
+            n = int(torch.tensor(shape).prod()) * torch.empty((), dtype=dt).element_size()
+            self._layout[k] = (off, n, shape, dt)
+            off += (n + 255) // 256 * 256
+        self._flat = torch.zeros(off, dtype=torch.uint8, device=dev)
+        self._flat_pin = torch.zeros(off, dtype=torch.uint8).pin_memory()
+        self.buf = self._views(self._flat)
+        self.pinned = self._views(self._flat_pin)
         n_levels = model.proposal_sampler.num_proposal_network_iterations + 1
         self.jitter = torch.zeros(n_levels, self.R, 1, device=dev) if inject_jitter else None
         from . import ops
         ops.loss_scratch(dev)  # created outside any capture
         self._unit = torch.ones((), device=dev)  # seed of the backward pass (backward() would fill one per step)
-        self.pinned = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True) for k, v in self.buf.items()}
         # the collider's near / far planes are static inputs of the captured step as well: the graphs bake in their
         # addresses, so they are owned here and not by the collider's (evictable) cache
         col = getattr(model, "collider", None)
@@ -164,41 +172,76 @@ class Trainer:
                             torch.full((self.R, 1), float(col.far_plane), device=dev))
         self.anneal_t = torch.ones((), device=dev)
         model.proposal_sampler.pdf_sampler.anneal_dev = self.anneal_t
-        self._loss_host = torch.zeros((), pin_memory=True)
+        self._loss_slots = [torch.zeros((), pin_memory=True), torch.zeros((), pin_memory=True)]
+        self._slot, self._loss_pending = 0, None
         self.loss_dict: Dict[str, torch.Tensor] = {}
         if seed is not None:
             torch.cuda.manual_seed(seed)
 
     # -- inputs ------------------------------------------------------------------------------------
-    def h2d_bytes(self) -> int:
-        return sum(v.numel() * v.element_size() for v in self.buf.values())
+    def _views(self, flat: torch.Tensor) -> Dict[str, torch.Tensor]:
+        return {k: flat[o:o + n].view(dt).view(shape) for k, (o, n, shape, dt) in self._layout.items()}
 
-    def load_batch(self, ray_bundle: RayBundle, batch: Dict[str, torch.Tensor]) -> None:
-        """Copy one ray batch (host or device tensors) into the step's static input buffers.  Host tensors go
-        through pinned staging memory unless they already are pinned."""
+    def h2d_bytes(self) -> int:
+        return sum(n for _, n, _, _ in self._layout.values())
+
+    def _sources(self, ray_bundle: RayBundle, batch: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
         src = {"origins": ray_bundle.origins, "directions": ray_bundle.directions,
                "camera_indices": ray_bundle.camera_indices, "pixel_area": ray_bundle.pixel_area,
                "image": batch["image"]}
         if self.needs_labels:
             src["semantics_label"] = batch["semantics_label"]
-        staged = False
         for k, t in src.items():
-            dst = self.buf[k]
-            if t is None:
-                continue
-            if t.shape != dst.shape:
-                raise ValueError(f"{k}: expected shape {tuple(dst.shape)}, got {tuple(t.shape)}")
-            if t.device.type == "cpu" and not t.is_pinned():
-                if self._h2d_done is not None:  # the staging buffer may still feed the previous step's copy
-                    self._h2d_done.synchronize()
-                    self._h2d_done = None
-                self.pinned[k].copy_(t)
-                t = self.pinned[k]
-                staged = True
-            dst.copy_(t, non_blocking=True)
-        if staged:
+            if t is not None and tuple(t.shape) != tuple(self._layout[k][2]):
+                raise ValueError(f"{k}: expected shape {tuple(self._layout[k][2])}, got {tuple(t.shape)}")
+        return src
+
+    def pack_batch(self, ray_bundle: RayBundle, batch: Dict[str, torch.Tensor], device=None) -> torch.Tensor:
+        """One flat uint8 tensor holding the batch in the layout of the step's input buffer: pinned host memory
+        (``device=None``: what a data loader hands to ``train_step_host``) or device memory.  ``train_step(packed=...)``
+        loads it with a single copy."""
+        flat = (torch.zeros(self._flat.numel(), dtype=torch.uint8).pin_memory() if device is None
+                else torch.zeros(self._flat.numel(), dtype=torch.uint8, device=device))
+        views = self._views(flat)
+        for k, t in self._sources(ray_bundle, batch).items():
+            if t is not None:
+                views[k].copy_(t)
+        return flat
+
+    def load_packed(self, flat: torch.Tensor) -> None:
+        if flat.dtype != torch.uint8 or flat.numel() != self._flat.numel():
+            raise ValueError("not a batch packed by Trainer.pack_batch for this trainer")
+        if flat.device.type == "cpu" and not flat.is_pinned():
+            self._wait_staging()
+            self._flat_pin.copy_(flat)
+            flat = self._flat_pin
+            self._flat.copy_(flat, non_blocking=True)
             self._h2d_done = torch.cuda.Event()
             self._h2d_done.record()
+            return
+        self._flat.copy_(flat, non_blocking=True)
+
+    def _wait_staging(self) -> None:
+        if self._h2d_done is not None:  # the staging buffer may still feed the previous step's copy
+            self._h2d_done.synchronize()
+            self._h2d_done = None
+
+    def load_batch(self, ray_bundle: RayBundle, batch: Dict[str, torch.Tensor]) -> None:
+        """Copy one ray batch (host or device tensors) into the step's static input buffers.  Host tensors are
+        gathered in the pinned staging buffer and cross in ONE transfer; device tensors are copied one by one."""
+        src = self._sources(ray_bundle, batch)
+        if all(t is None or t.device.type == "cpu" for t in src.values()):
+            self._wait_staging()
+            for k, t in src.items():
+                if t is not None:
+                    self.pinned[k].copy_(t)
+            self._flat.copy_(self._flat_pin, non_blocking=True)
+            self._h2d_done = torch.cuda.Event()
+            self._h2d_done.record()
+            return
+        for k, t in src.items():
+            if t is not None:
+                self.buf[k].copy_(t, non_blocking=True)
 
     def _bundle(self) -> RayBundle:
         b = self.buf
@@ -335,10 +378,13 @@ class Trainer:
                     sampler.force_updated = None
 
     def train_step(self, ray_bundle: Optional[RayBundle] = None, batch: Optional[Dict[str, torch.Tensor]] = None,
-                   jitter: Optional[Sequence[torch.Tensor]] = None) -> torch.Tensor:
-        """Run one step on the given batch (or on whatever the static buffers hold).  Returns the total loss
-        as a device scalar; ``self.loss_dict`` holds the individual terms."""
-        if ray_bundle is not None:
+                   jitter: Optional[Sequence[torch.Tensor]] = None, packed: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Run one step on the given batch (``ray_bundle`` + ``batch``, or ``packed``: a batch from ``pack_batch``), or
+        on whatever the static buffers hold.  Returns the total loss as a device scalar; ``self.loss_dict`` holds the
+        individual terms."""
+        if packed is not None:
+            self.load_packed(packed)
+        elif ray_bundle is not None:
             self.load_batch(ray_bundle, batch)
         if jitter is not None:
             if self.jitter is None:
@@ -378,10 +424,35 @@ class Trainer:
         self.loss_dict = out
         return out["loss"]
 
-    def train_step_host(self, ray_bundle: RayBundle, batch: Dict[str, torch.Tensor]) -> float:
-        """Host in, host out: H2D of the batch, the step, D2H of the loss (what a datamanager-driven loop
-        sees per iteration)."""
-        loss = self.train_step(ray_bundle, batch)
-        self._loss_host.copy_(loss, non_blocking=True)
-        torch.cuda.current_stream(self.device).synchronize()
-        return float(self._loss_host)
+    def train_step_host(self, ray_bundle: Optional[RayBundle] = None, batch: Optional[Dict[str, torch.Tensor]] = None,
+                        packed: Optional[torch.Tensor] = None, lag: int = 0) -> float:
+        """Host in, host out: H2D of the batch, the step, D2H of the loss (what a datamanager-driven loop sees per
+        iteration).  ``packed``: a pinned batch from ``pack_batch`` (one transfer).
+
+        ``lag=0``: returns this step's loss (the host waits for the step).  ``lag=1``: double-buffered read-back — the
+        loss of every step is still copied to the host, but the call returns the loss of the PREVIOUS step (NaN on the
+        first call) and waits only for that one, so the host enqueues step k+1 while step k runs and the GPU never idles
+        on the round trip; ``drain_host()`` returns the last step's loss."""
+        loss = self.train_step(ray_bundle, batch, packed=packed)
+        slot = self._loss_slots[self._slot]
+        self._slot ^= 1
+        slot.copy_(loss, non_blocking=True)
+        if lag == 0:
+            torch.cuda.current_stream(self.device).synchronize()
+            self._loss_pending = None
+            return float(slot)
+        ev = torch.cuda.Event()
+        ev.record()
+        prev, self._loss_pending = self._loss_pending, (slot, ev)
+        if prev is None:
+            return float("nan")
+        prev[1].synchronize()
+        return float(prev[0])
+
+    def drain_host(self) -> float:
+        """Wait for the loss read-back still in flight (``train_step_host(lag=1)``) and return it."""
+        prev, self._loss_pending = self._loss_pending, None
+        if prev is None:
+            return float("nan")
+        prev[1].synchronize()
+        return float(prev[0])

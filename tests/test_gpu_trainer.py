@@ -293,3 +293,55 @@ def test_deferred_adam_equals_adam_at_step_end():
     assert rel_err(runs["1"][1], runs["0"][1]) < 2e-3
     assert rel_err(runs["1"][2], runs["0"][2]) < 5e-2   # Adam eps = 1e-15 noise, see test_training_loop_tracks_oracle
     assert rel_err(runs["1"][3], runs["0"][3]) < 2e-2
+
+
+def test_packed_batch_equals_tensor_batch():
+    """A batch packed in the layout of the step's input buffer (one copy: pinned host -> device, or device -> device)
+    feeds the step the same inputs as the per-tensor route, host tensors included."""
+    R = 256
+    rb = O.synthetic_ray_bundle(R, seed=11)
+    img = torch.rand(R, 3, generator=torch.Generator().manual_seed(12))
+    _, nm = _train_pair(R, 0, False)
+    tr = Trainer(nm, R, use_graph=False)
+    nrb_host = nk.RayBundle(rb.origins, rb.directions, rb.pixel_area, rb.camera_indices)
+    host_packed = tr.pack_batch(nrb_host, {"image": img})
+    assert host_packed.is_pinned() and host_packed.dtype == torch.uint8
+    dev_packed = tr.pack_batch(to_nk_bundle(rb, DEV), {"image": img.to(DEV)}, device=DEV)
+    want = {}
+    tr.load_batch(to_nk_bundle(rb, DEV), {"image": img.to(DEV)})
+    torch.cuda.synchronize()
+    want = {k: v.clone() for k, v in tr.buf.items()}
+    for route in ("host tensors", "host packed", "device packed"):
+        tr._flat.zero_()
+        if route == "host tensors":
+            tr.load_batch(nrb_host, {"image": img})
+        else:
+            tr.load_packed(host_packed if route == "host packed" else dev_packed)
+        torch.cuda.synchronize()
+        for k, v in want.items():
+            assert torch.equal(tr.buf[k], v), (route, k)
+    torch.cuda.manual_seed(3)
+    a = tr.train_step_host(packed=host_packed)
+    assert a == a and tr.h2d_bytes() == R * (12 + 12 + 8 + 4 + 12)
+
+
+def test_lagged_loss_readback_returns_every_loss_one_step_late():
+    R = 256
+    rb = O.synthetic_ray_bundle(R, seed=13)
+    batch = {"image": torch.rand(R, 3, generator=torch.Generator().manual_seed(14)).to(DEV)}
+    runs = []
+    for lag in (0, 1):
+        _, nm = _train_pair(R, 0, False)
+        tr = Trainer(nm, R, use_graph=True, graph_warmup=1, inject_jitter=True)
+        ls = []
+        for i in range(6):
+            tr.train_step(jitter=[j.to(DEV) for j in make_jitter(R, seed=50 + i)]) if False else None
+            for dst, src in zip(tr.jitter, make_jitter(R, seed=50 + i)):
+                dst.copy_(src.reshape(dst.shape))
+            ls.append(tr.train_step_host(to_nk_bundle(rb, DEV), batch, lag=lag))
+        if lag:
+            assert ls[0] != ls[0]  # NaN: nothing to report yet
+            ls = ls[1:] + [tr.drain_host()]
+        runs.append(ls)
+    for a, b in zip(*runs):
+        assert abs(a - b) <= 2e-4 * abs(a), runs
