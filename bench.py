@@ -531,7 +531,7 @@ def cfg5_leg(args, dev, rank, world, steps, warmup, n1_value=None):
     for i in range(3):
         tr.train_step_host(packed=host_packed[i % 4])
     def host_step(i):
-        tr.train_step_host(packed=host_packed[i % 4], lag=1)
+        tr.train_step_host(packed=host_packed[i % 4], lag=1, prefetch=host_packed[(i + 1) % 4] if i + 1 < steps else None)
         if i == steps - 1:
             tr.drain_host()
     ms_e2e = timed_steps(host_step, steps, dev, world)
@@ -705,7 +705,9 @@ def run_nkbs(args):
     for i in range(args.steps):
         # every step: one H2D transfer of its pinned batch, the step, and the D2H read of its loss; the read-back is
         # double-buffered (the host waits for the loss of step k-1 while step k runs), the last one is drained here
-        tr.train_step_host(packed=host_packed[i % len(host_packed)], lag=1)
+        # ... and the transfer of step k+1's batch is started while step k runs (copy stream, second device buffer)
+        nxt = host_packed[(i + 1) % len(host_packed)] if i + 1 < args.steps else None
+        tr.train_step_host(packed=host_packed[i % len(host_packed)], lag=1, prefetch=nxt)
     last_loss_host = tr.drain_host()
     e1.record()
     barrier()
@@ -716,7 +718,9 @@ def run_nkbs(args):
     e2e = {"value": world * R * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
            "h2d_bytes_per_step": tr.h2d_bytes() + 4, "d2h_bytes_per_step": 4,
            "readback": "loss of every step copied to pinned host memory; the host reads it one step late (double "
-                       "buffered) and drains the last one inside the timed region", "last_loss": last_loss_host}
+                       "buffered) and drains the last one inside the timed region",
+           "h2d": "one transfer per step of the step's packed pinned batch; the transfer of step k+1 runs on a copy stream "
+                  "while step k computes (the first one is not overlapped)", "last_loss": last_loss_host}
 
     # (2b) render rays/s (BASELINE configs[3]); every rank renders its block of every frame
     render = None

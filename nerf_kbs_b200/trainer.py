@@ -174,6 +174,7 @@ class Trainer:
         model.proposal_sampler.pdf_sampler.anneal_dev = self.anneal_t
         self._loss_slots = [torch.zeros((), pin_memory=True), torch.zeros((), pin_memory=True)]
         self._slot, self._loss_pending = 0, None
+        self._copy_stream, self._flat_next, self._prefetched, self._prefetch_done, self._d2d_done = None, None, None, None, None
         self.loss_dict: Dict[str, torch.Tensor] = {}
         if seed is not None:
             torch.cuda.manual_seed(seed)
@@ -208,9 +209,34 @@ class Trainer:
                 views[k].copy_(t)
         return flat
 
+    def prefetch_packed(self, flat_host: torch.Tensor) -> None:
+        """Start the host -> device transfer of a LATER step's pinned packed batch now, on a copy stream, into a second
+        device buffer: it overlaps whatever the step stream is running.  ``train_step(packed=<the same tensor>)`` then
+        waits for the transfer and moves the batch into the step's input buffer with one device-side copy."""
+        if flat_host.dtype != torch.uint8 or flat_host.numel() != self._flat.numel() or not flat_host.is_pinned():
+            raise ValueError("prefetch_packed takes a pinned batch from Trainer.pack_batch")
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(self.device)
+            self._flat_next = torch.empty_like(self._flat)
+        if self._d2d_done is not None:  # the staging buffer's previous content has been consumed
+            self._copy_stream.wait_event(self._d2d_done)
+        with torch.cuda.stream(self._copy_stream):
+            self._flat_next.copy_(flat_host, non_blocking=True)
+            self._prefetch_done = torch.cuda.Event()
+            self._prefetch_done.record()
+        self._prefetched = flat_host
+
     def load_packed(self, flat: torch.Tensor) -> None:
         if flat.dtype != torch.uint8 or flat.numel() != self._flat.numel():
             raise ValueError("not a batch packed by Trainer.pack_batch for this trainer")
+        if flat is self._prefetched:
+            cur = torch.cuda.current_stream(self.device)
+            cur.wait_event(self._prefetch_done)
+            self._flat.copy_(self._flat_next, non_blocking=True)
+            self._d2d_done = torch.cuda.Event()
+            self._d2d_done.record()
+            self._prefetched = None
+            return
         if flat.device.type == "cpu" and not flat.is_pinned():
             self._wait_staging()
             self._flat_pin.copy_(flat)
@@ -425,15 +451,19 @@ class Trainer:
         return out["loss"]
 
     def train_step_host(self, ray_bundle: Optional[RayBundle] = None, batch: Optional[Dict[str, torch.Tensor]] = None,
-                        packed: Optional[torch.Tensor] = None, lag: int = 0) -> float:
+                        packed: Optional[torch.Tensor] = None, lag: int = 0,
+                        prefetch: Optional[torch.Tensor] = None) -> float:
         """Host in, host out: H2D of the batch, the step, D2H of the loss (what a datamanager-driven loop sees per
         iteration).  ``packed``: a pinned batch from ``pack_batch`` (one transfer).
 
         ``lag=0``: returns this step's loss (the host waits for the step).  ``lag=1``: double-buffered read-back — the
         loss of every step is still copied to the host, but the call returns the loss of the PREVIOUS step (NaN on the
         first call) and waits only for that one, so the host enqueues step k+1 while step k runs and the GPU never idles
-        on the round trip; ``drain_host()`` returns the last step's loss."""
+        on the round trip; ``drain_host()`` returns the last step's loss.  ``prefetch``: the NEXT step's pinned packed
+        batch; its transfer is started as soon as this step is enqueued (``prefetch_packed``)."""
         loss = self.train_step(ray_bundle, batch, packed=packed)
+        if prefetch is not None:
+            self.prefetch_packed(prefetch)
         slot = self._loss_slots[self._slot]
         self._slot ^= 1
         slot.copy_(loss, non_blocking=True)

@@ -320,6 +320,13 @@ def test_packed_batch_equals_tensor_batch():
         torch.cuda.synchronize()
         for k, v in want.items():
             assert torch.equal(tr.buf[k], v), (route, k)
+    # prefetched on the copy stream, consumed by identity
+    tr._flat.zero_()
+    tr.prefetch_packed(host_packed)
+    tr.load_packed(host_packed)
+    torch.cuda.synchronize()
+    for k, v in want.items():
+        assert torch.equal(tr.buf[k], v), ("prefetched", k)
     torch.cuda.manual_seed(3)
     a = tr.train_step_host(packed=host_packed)
     assert a == a and tr.h2d_bytes() == R * (12 + 12 + 8 + 4 + 12)
