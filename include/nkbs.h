@@ -133,10 +133,13 @@ int nkbs_generate_rays(int64_t N, const int64_t* ray_indices, const float* c2w, 
 
 /* N3 — masked pixel sampling: keeps, in order, the candidates (image_indices[m], pixel_indices[m]) whose byte in
  * masks [num_images, pixels_per_image] is non-zero, up to R of them; if fewer survive they repeat cyclically.
- * *n_kept (device int32) receives the number of survivors.  replaces: dataparser/dataset_z.py:180-191. */
+ * *n_kept (device int32) receives the number of survivors.  block_ws NULL: one CTA walks the list (per-step candidate
+ * lists, M <= 2^22).  block_ws = DEVICE int32 [ceil(M / 1024) + 1]: per-CTA counts + scan + ordered scatter, for
+ * candidate lists of any length (the reference loads pixel chunks of 12.8 M, dataparser/datamanager_z.py:49).
+ * replaces: dataparser/dataset_z.py:180-191. */
 int nkbs_compact_masked(int64_t M, const int64_t* image_indices, const int64_t* pixel_indices, const uint8_t* masks,
                         int64_t pixels_per_image, int64_t R, int64_t* out_image, int64_t* out_pixel, int32_t* n_kept,
-                        void* stream);
+                        int32_t* block_ws, void* stream);
 
 /* N3/N4 — semantic palette.  palette: device int32 [1 + 256] = {n, r|g<<8|b<<16 per class}.
  * color_to_label: rgb uint8 [N,3] -> labels int64 [N] (default_label when the colour is not in the palette);

@@ -31,7 +31,7 @@ SIGNATURES = {
     "nkbs_ray_losses_weighted": [_i64, _i32, _p, _p, _p, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _i64, _p, _p, _p, _p,
                                  _p, _p],
     "nkbs_generate_rays": [_i64, _p, _p, _p, _i64, _p, _p, _p, _p, _p, _p],
-    "nkbs_compact_masked": [_i64, _p, _p, _p, _i64, _i64, _p, _p, _p, _p],
+    "nkbs_compact_masked": [_i64, _p, _p, _p, _i64, _i64, _p, _p, _p, _p, _p],
     "nkbs_color_to_label": [_i64, _p, _p, _i64, _p, _p],
     "nkbs_semantic_colormap": [_i64, _i32, _p, _p, _p, _p, _p],
     "nkbs_head_tc_fwd": [_i32, _i32, _i32, _p, _i32, _p, _i32, _p, _i32, _p, _p, _i32, _i64, _i32, _p, _p, _p, _i32, _i32, _i32,

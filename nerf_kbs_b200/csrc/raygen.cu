@@ -125,6 +125,97 @@ __global__ void __launch_bounds__(1024) compact_masked_kernel(int64_t M, const i
   }
 }
 
+// ---- the same compaction for candidate lists of any length (the reference loads pixel chunks of 12.8 M,
+// ref:dataparser/datamanager_z.py:49): per-CTA counts, one scan of the counts, ordered scatter, cyclic fill ----
+constexpr int kCompactCta = 1024;
+
+__device__ __forceinline__ int block_exclusive_scan_1024(int v, int* s_warp, int& total) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  int incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) s_warp[wid] = incl;
+  __syncthreads();
+  if (wid == 0) {
+    const int w = s_warp[lane];
+    int wi = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, wi, o);
+      if (lane >= o) wi += t;
+    }
+    s_warp[lane] = wi - w;
+    if (lane == 31) s_warp[32] = wi;
+  }
+  __syncthreads();
+  total = s_warp[32];
+  const int r = s_warp[wid] + incl - v;
+  __syncthreads();
+  return r;
+}
+
+__global__ void __launch_bounds__(kCompactCta) compact_count_kernel(int64_t M, const int64_t* img, const int64_t* pix,
+                                                                    const uint8_t* mask, int64_t ppi, int32_t* counts) {
+  __shared__ int s_warp[33];
+  const int64_t m = blockIdx.x * (int64_t)kCompactCta + threadIdx.x;
+  const int keep = (m < M && mask[img[m] * ppi + pix[m]] != 0) ? 1 : 0;
+  int total;
+  block_exclusive_scan_1024(keep, s_warp, total);
+  if (threadIdx.x == 0) counts[blockIdx.x] = total;
+}
+
+// exclusive scan of counts[0..nb) in place, counts[nb] = *n_kept = total
+__global__ void __launch_bounds__(kCompactCta) compact_scan_kernel(int nb, int32_t* counts, int32_t* n_kept) {
+  __shared__ int s_warp[33];
+  int carry = 0;
+  for (int b0 = 0; b0 < nb; b0 += kCompactCta) {
+    const int b = b0 + threadIdx.x;
+    const int v = b < nb ? counts[b] : 0;
+    int total;
+    const int ex = block_exclusive_scan_1024(v, s_warp, total);
+    if (b < nb) counts[b] = carry + ex;
+    carry += total;
+  }
+  if (threadIdx.x == 0) {
+    counts[nb] = carry;
+    *n_kept = carry;
+  }
+}
+
+__global__ void __launch_bounds__(kCompactCta) compact_scatter_kernel(int64_t M, const int64_t* img, const int64_t* pix,
+                                                                      const uint8_t* mask, int64_t ppi, int64_t R,
+                                                                      const int32_t* offsets, int64_t* out_img,
+                                                                      int64_t* out_pix) {
+  __shared__ int s_warp[33];
+  const int64_t m = blockIdx.x * (int64_t)kCompactCta + threadIdx.x;
+  int64_t im = 0, px = 0;
+  int keep = 0;
+  if (m < M) {
+    im = img[m];
+    px = pix[m];
+    keep = mask[im * ppi + px] != 0;
+  }
+  int total;
+  const int64_t pos = (int64_t)offsets[blockIdx.x] + block_exclusive_scan_1024(keep, s_warp, total);
+  if (keep && pos < R) {
+    out_img[pos] = im;
+    out_pix[pos] = px;
+  }
+}
+
+__global__ void __launch_bounds__(kThreads) compact_fill_kernel(int64_t R, const int32_t* n_kept, int64_t* out_img,
+                                                                int64_t* out_pix) {
+  const int64_t kept = *n_kept;
+  if (kept <= 0 || kept >= R) return;
+  for (int64_t k = kept + blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < R; k += (int64_t)gridDim.x * blockDim.x) {
+    out_img[k] = out_img[k % kept];  // k % kept < kept: written by the scatter kernel, never by this one
+    out_pix[k] = out_pix[k % kept];
+  }
+}
+
 constexpr int kMaxPalette = 256;
 struct Palette {
   int n;
@@ -262,12 +353,34 @@ extern "C" int nkbs_generate_rays(int64_t N, const int64_t* ray_indices, const f
 
 extern "C" int nkbs_compact_masked(int64_t M, const int64_t* image_indices, const int64_t* pixel_indices,
                                    const uint8_t* masks, int64_t pixels_per_image, int64_t R, int64_t* out_image,
-                                   int64_t* out_pixel, int32_t* n_kept, void* stream) {
+                                   int64_t* out_pixel, int32_t* n_kept, int32_t* block_ws, void* stream) {
   NKBS_CHECK_ARG(M >= 0 && R >= 0 && pixels_per_image >= 1, "nkbs_compact_masked: bad sizes");
   NKBS_CHECK_ARG(image_indices && pixel_indices && masks && out_image && out_pixel && n_kept, "nkbs_compact_masked: null pointers");
-  compact_masked_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(M, image_indices, pixel_indices, masks, pixels_per_image, R,
-                                                             out_image, out_pixel, n_kept);
-  NKBS_CHECK_LAUNCH("nkbs_compact_masked");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!block_ws) {  // one CTA walks the list: per-step candidate lists of a few thousand entries
+    NKBS_CHECK_ARG(M <= (1ll << 22), "nkbs_compact_masked: %lld candidates need the block workspace", (long long)M);
+    compact_masked_kernel<<<1, 1024, 0, st>>>(M, image_indices, pixel_indices, masks, pixels_per_image, R, out_image,
+                                              out_pixel, n_kept);
+    NKBS_CHECK_LAUNCH("nkbs_compact_masked");
+    return 0;
+  }
+  const int64_t nb = (M + kCompactCta - 1) / kCompactCta;
+  NKBS_CHECK_ARG(nb < (1ll << 30), "nkbs_compact_masked: too many candidates");
+  if (nb > 0) {
+    compact_count_kernel<<<(int)nb, kCompactCta, 0, st>>>(M, image_indices, pixel_indices, masks, pixels_per_image, block_ws);
+    NKBS_CHECK_LAUNCH("nkbs_compact_masked(count)");
+  }
+  compact_scan_kernel<<<1, kCompactCta, 0, st>>>((int)nb, block_ws, n_kept);
+  NKBS_CHECK_LAUNCH("nkbs_compact_masked(scan)");
+  if (nb > 0) {
+    compact_scatter_kernel<<<(int)nb, kCompactCta, 0, st>>>(M, image_indices, pixel_indices, masks, pixels_per_image, R,
+                                                           block_ws, out_image, out_pixel);
+    NKBS_CHECK_LAUNCH("nkbs_compact_masked(scatter)");
+  }
+  if (R > 0) {
+    compact_fill_kernel<<<grid_for(R), kThreads, 0, st>>>(R, n_kept, out_image, out_pixel);
+    NKBS_CHECK_LAUNCH("nkbs_compact_masked(fill)");
+  }
   return 0;
 }
 

@@ -82,14 +82,20 @@ def sample_masked_pixels(masks: torch.Tensor, num_rays: int, oversample: float =
     return compact_masked(img, pix, masks, num_rays)
 
 
+COMPACT_ONE_CTA_MAX = 1 << 15  # candidates one 1024-thread CTA still walks faster than four launches
+
+
 def compact_masked(image_indices, pixel_indices, masks, num_rays: int):
     require_cuda(masks, image_indices, pixel_indices)
     dev = masks.device
     out_i = torch.zeros(num_rays, device=dev, dtype=torch.int64)
     out_p = torch.zeros(num_rays, device=dev, dtype=torch.int64)
     kept = torch.zeros(1, device=dev, dtype=torch.int32)
-    call("nkbs_compact_masked", image_indices.shape[0], ptr(image_indices.contiguous()), ptr(pixel_indices.contiguous()),
-         ptr(masks.contiguous()), masks.shape[1], num_rays, ptr(out_i), ptr(out_p), ptr(kept), stream())
+    M = image_indices.shape[0]
+    # long candidate lists (pixel chunks) take the multi-CTA route; per-step lists one CTA
+    ws = torch.empty((M + 1023) // 1024 + 1, device=dev, dtype=torch.int32) if M > COMPACT_ONE_CTA_MAX else None
+    call("nkbs_compact_masked", M, ptr(image_indices.contiguous()), ptr(pixel_indices.contiguous()),
+         ptr(masks.contiguous()), masks.shape[1], num_rays, ptr(out_i), ptr(out_p), ptr(kept), ptr(ws), stream())
     return out_i, out_p, kept
 
 

@@ -66,6 +66,27 @@ def test_masked_compaction_matches_oracle(keep, R):
         assert masks[gi.cpu(), gp.cpu()].ne(0).all()
 
 
+@pytest.mark.parametrize("keep,R,M", [(0.8, 200000, 300001), (0.02, 50000, 1200000), (0.0, 64, 70000), (1.0, 1000, 40000)])
+def test_masked_compaction_long_candidate_lists(keep, R, M, monkeypatch):
+    """The multi-CTA route (per-CTA counts, scan, ordered scatter, cyclic fill) for candidate lists beyond one CTA's
+    reach — pixel chunks like the reference's (ref:dataparser/datamanager_z.py:49) — against the oracle and against the
+    one-CTA kernel."""
+    g = torch.Generator().manual_seed(R)
+    n_img, n_pix = 3, 1242 * 375
+    masks = (torch.rand(n_img, n_pix, generator=g) < keep).to(torch.uint8)
+    img = torch.randint(0, n_img, (M,), generator=g)
+    pix = torch.randint(0, n_pix, (M,), generator=g)
+    wi, wp, wn = O.compact_masked(img, pix, masks, R)
+    assert M > D.COMPACT_ONE_CTA_MAX
+    gi, gp, gn = D.compact_masked(img.to(DEV), pix.to(DEV), masks.to(DEV), R)
+    assert int(gn) == wn
+    if wn > 0:
+        assert torch.equal(gi.cpu(), wi) and torch.equal(gp.cpu(), wp)
+    monkeypatch.setattr(D, "COMPACT_ONE_CTA_MAX", 1 << 22)  # force the one-CTA kernel on the same list
+    oi, op, on = D.compact_masked(img.to(DEV), pix.to(DEV), masks.to(DEV), R)
+    assert int(on) == int(gn) and (wn == 0 or (torch.equal(oi, gi) and torch.equal(op, gp)))
+
+
 def test_palette_round_trip_and_colormap():
     pal = nk.SemanticPalette(PALETTE, DEV)
     g = torch.Generator().manual_seed(2)
