@@ -30,17 +30,25 @@ struct InitArgs {
   float* ebins;         // [R,S+1] euclidean bins
 };
 
+// One warp per ray: the two spacing_fn divisions of the ray's near / far planes are evaluated once per ray (a thread per
+// bin edge re-evaluated them, and a 64-bit division for its ray index, for each of the S + 1 edges), lanes stride over the
+// edges (coalesced stores).
 __global__ void __launch_bounds__(256) initial_sampler_kernel(const InitArgs a) {
   const int nb = a.S + 1;
-  const int64_t total = a.R * nb;
-  for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
-    int64_t r = e / nb;
-    int i = (int)(e - r * nb);
-    const float tr = a.t_rand ? (a.rand_per_bin ? a.t_rand[e] : a.t_rand[r]) : 0.f;
-    const float b = nkbs_initial_bin(a.lin, i, a.S, a.t_rand != nullptr, tr);
-    float s_near = spacing_fn(a.nears[r]), s_far = spacing_fn(a.fars[r]);
-    a.sbins[e] = b;
-    a.ebins[e] = to_euclid(b, s_near, s_far);
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp; r < a.R; r += nwarps) {
+    const float s_near = spacing_fn(a.nears[r]), s_far = spacing_fn(a.fars[r]);
+    const float tr = (a.t_rand && !a.rand_per_bin) ? a.t_rand[r] : 0.f;
+    float* sb = a.sbins + r * nb;
+    float* eb = a.ebins + r * nb;
+    for (int i = lane; i < nb; i += 32) {
+      const float t = (a.t_rand && a.rand_per_bin) ? a.t_rand[r * nb + i] : tr;
+      const float b = nkbs_initial_bin(a.lin, i, a.S, a.t_rand != nullptr, t);
+      sb[i] = b;
+      eb[i] = to_euclid(b, s_near, s_far);
+    }
   }
 }
 
@@ -176,8 +184,7 @@ extern "C" int nkbs_initial_sampler(int64_t R, int32_t S, const float* lin, cons
   if (R == 0) return 0;
   NKBS_CHECK_ARG(lin && nears && fars && sbins && ebins, "nkbs_initial_sampler: null argument");
   InitArgs a{R, S, lin, t_rand, rand_per_bin, nears, fars, sbins, ebins};
-  int64_t total = R * (S + 1);
-  int64_t blocks = (total + 255) / 256;
+  int64_t blocks = (R + 7) / 8;  // eight rays (warps) per CTA
   int64_t cap = (int64_t)nkbs_num_sms() * 16;
   initial_sampler_kernel<<<(int)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>(a);
   NKBS_CHECK_LAUNCH("nkbs_initial_sampler");
