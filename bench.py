@@ -41,7 +41,7 @@ L2_BYTES_PER_CYCLE = 6300  # whole-chip L2 (LTS) throughput cap, /opt/skills/gui
 # Kernels whose tables are cache-resident are reported against L2 throughput, not HBM: the proposal grids are 5-16 MiB
 # (L1/L2 hits, ncu: DRAM 2 %).  The main-grid gather and scatter (64 MiB table + 64 MiB gradient, evicted by the
 # 620 MB optimizer stream of every step) and everything ray-major stay HBM kernels.
-L2_BOUND = {"nkbs_density_fwd", "nkbs_density_bwd", "nkbs_proposal_level_fwd"}
+L2_BOUND = {"nkbs_density_fwd", "nkbs_density_bwd", "nkbs_proposal_level_fwd", "nkbs_encode_bwd_rays"}
 BOUND_NOTE = {"l2": "table traffic of this kernel is served by L1/L2 (tables of 5-64 MiB against a 126 MiB L2): achieved = "
                     "algorithmic gather/scatter bytes per second against the L2 throughput cap, not HBM",
               "hbm": "achieved = algorithmic bytes per second against the measured HBM copy bandwidth",
@@ -227,12 +227,20 @@ def kernel_work(name, a):
         # bwd additionally reads d(density) and scatters the same 8*L rows once each
         N, L = a[7] * a[8], a[13]
         gathers = 8 * L * 2 * 4
-        return "hbm", N * ((8 + gathers + 4) if name.endswith("fwd") else (8 + 4 + 2 * gathers))
+        if name.endswith("fwd"):
+            return "hbm", N * (8 + gathers + 4)
+        if a[22] is None:  # feature gradients written out, scattered by nkbs_encode_bwd_rays
+            return "hbm", N * (8 + 4 + gathers + 2 * L * 4)
+        return "hbm", N * (8 + 4 + 2 * gathers)
     if name == "nkbs_proposal_level_fwd":
         # per sample: 8 corner rows of 2 floats on each of L levels gathered, density and weight written; per ray: the
         # level's bin edges (both domains) and the next level's
         R, S, L, nb = a[0], a[1], a[15], a[25]
         return "hbm", R * (S * (8 * L * 2 * 4 + 8) + 8 * (S + 1) + 8 * nb)
+    if name == "nkbs_encode_bwd_rays":
+        # feature gradients in, every corner row of every sample scattered once (upper bound before the in-register merge)
+        N, L = a[0] * a[1], a[11]
+        return "hbm", N * (8 + 2 * L * 4 + 8 * L * 2 * 4)
     if name in ("nkbs_ray_losses", "nkbs_ray_losses_weighted"):
         R, S, n_prop = a[0], a[1], a[5]
         sp = list(a[6])[:n_prop]

@@ -89,7 +89,7 @@ int nkbs_density_bwd(int32_t mode, const float* x, const float* origins, const f
                      const float* aabb, const float* table, const float* scalings, int32_t L, int32_t log2_T,
                      const float* W1, const float* b1, const float* W2, const float* b2, int32_t H,
                      const float* ddensity, int32_t dedup_levels, float* dtable, float* dW1, float* db1,
-                     float* dW2, float* db2, void* stream);
+                     float* dW2, float* db2, float* dfeat_out, void* stream);
 
 /* N1 — per-ray training losses and their gradients in one ray-major pass (one warp per ray).
  * replaces: losses.interlevel_loss / distortion_loss, MSELoss and CrossEntropyLoss as called at
@@ -257,6 +257,20 @@ int nkbs_dp_adam_step(int32_t world, int32_t rank, const float* const* grad_peer
  * buffers.  With them the gradient sum of the owned slice is one `multimem.ld_reduce` (reduced inside the switch) and
  * the new parameters one `multimem.st` (replicated by the switch) per 16 bytes, instead of `world` peer loads and
  * `world` peer stores. */
+
+/* nkbs_density_bwd, dfeat_out (may be NULL): DEVICE float [N, 2L].  When given, the gradient w.r.t. the hash-grid
+ * features of every sample is written there INSTEAD of being scattered into dtable (which may then be NULL); the caller
+ * follows with nkbs_encode_bwd_rays.  The weight / bias gradients are accumulated as usual. */
+
+/* K2 (ray-major) — gradient scatter for samples that come as rays (origins / directions [R,3], starts / ends [R,S] with
+ * row stride bin_stride, S <= 256): one warp per ray, every lane walks a contiguous run of samples and sums the corner
+ * gradients of consecutive samples that share a cell in registers; the table sees one set of reductions per cell
+ * crossing.  dfeat [R*S, 2L] must be zero for samples outside the grid; dtable [L*T, 2] is ACCUMULATED into.
+ * replaces: the autograd of HashEncoding inside HashMLPDensityField (nerfacto.py:299-311) for the proposal levels. */
+int nkbs_encode_bwd_rays(int64_t R, int32_t S, const float* origins, const float* directions, const float* starts,
+                         const float* ends, int32_t bin_stride, int32_t contraction, const float* aabb,
+                         const float* dfeat, const float* scalings, int32_t L, int32_t log2_T, float* dtable,
+                         void* stream);
 
 /* One proposal level of ProposalNetworkSampler in one ray-major pass (forward): the level's bins (gen_bins != 0:
  * produced here by the initial piecewise sampler from lin [S+1] and the per-ray jitter t_rand [R] (NULL in

@@ -40,6 +40,8 @@ struct DensityArgs : SampleSource {
   float* db2;
   int dedup_levels;
   float v4_min_scale;  // see encode.cuh
+  float* df_out;       // backward, optional [N, 2L]: the feature gradients are written here INSTEAD of being scattered
+                       // (the ray-major scatter nkbs_encode_bwd_rays follows)
 };
 
 // shared weights: W1 rows padded to KP floats (16-byte rows -> LDS.128 broadcasts), then b1, W2, b2
@@ -271,7 +273,14 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
       g_up = a.ddensity[n] * sel;
     }
     // a warp whose samples all lie outside the grid (or carry no gradient) has nothing to add
-    if (!__any_sync(0xffffffffu, g_up != 0.f)) continue;
+    if (!__any_sync(0xffffffffu, g_up != 0.f)) {
+      if (a.df_out && live) {
+        float2* o = reinterpret_cast<float2*>(a.df_out + n * K);
+#pragma unroll
+        for (int i = 0; i < L; ++i) o[i] = make_float2(0.f, 0.f);
+      }
+      continue;
+    }
     float f[K];
     encode_sample<L>(a, s_scale, x, f);
     float z[kMma ? 1 : H];
@@ -412,6 +421,14 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
     __syncwarp();
     }
     // ---- feature gradient -> table gradient ----
+    if (a.df_out) {
+      if (live) {
+        float2* o = reinterpret_cast<float2*>(a.df_out + n * K);
+#pragma unroll
+        for (int i = 0; i < L; ++i) o[i] = make_float2(df[2 * i], df[2 * i + 1]);
+      }
+      continue;
+    }
 #pragma unroll
     for (int l = 0; l < L; ++l) {
       Cell cl = nkbs_cell(x, s_scale[l]);
@@ -521,6 +538,7 @@ int fill(DensityArgs& a, const char* who, int mode, const float* x, const float*
   a.dtable = a.dW1 = a.db1 = a.dW2 = a.db2 = nullptr;
   a.dedup_levels = 0;
   a.v4_min_scale = v4_min_scale(1e30f);
+  a.df_out = nullptr;
   return 0;
 }
 
@@ -734,14 +752,16 @@ extern "C" int nkbs_density_bwd(int32_t mode, const float* x, const float* origi
                                 const float* aabb, const float* table, const float* scalings, int32_t L,
                                 int32_t log2_T, const float* W1, const float* b1, const float* W2, const float* b2,
                                 int32_t H, const float* ddensity, int32_t dedup_levels, float* dtable, float* dW1,
-                                float* db1, float* dW2, float* db2, void* stream) {
+                                float* db1, float* dW2, float* db2, float* dfeat_out, void* stream) {
   DensityArgs a;
   if (fill(a, "nkbs_density_bwd", mode, x, origins, directions, starts, ends, bin_stride, R, S, contraction, aabb, table, scalings,
            L, log2_T, W1, b1, W2, b2, H))
     return -1;
   if (a.N == 0) return 0;
-  NKBS_CHECK_ARG(ddensity && dtable && dW1 && db1 && dW2 && db2, "nkbs_density_bwd: null gradient buffers");
+  NKBS_CHECK_ARG(ddensity && (dtable || dfeat_out) && dW1 && db1 && dW2 && db2, "nkbs_density_bwd: null gradient buffers");
   NKBS_CHECK_ARG((reinterpret_cast<uintptr_t>(dtable) & 15u) == 0, "nkbs_density_bwd: dtable must be 16-byte aligned");
+  NKBS_CHECK_ARG((reinterpret_cast<uintptr_t>(dfeat_out) & 7u) == 0, "nkbs_density_bwd: dfeat_out must be 8-byte aligned");
+  a.df_out = dfeat_out;
   a.ddensity = ddensity;
   a.dtable = dtable;
   a.dW1 = dW1;

@@ -135,6 +135,94 @@ __global__ void __launch_bounds__(kEncThreads) encode_bwd_kernel(const EncodeBwd
   }
 }
 
+// ---- ray-major gradient scatter (proposal grids: 96-256 samples per ray on 5-8 coarse levels) -------------------------
+// One warp per ray, every lane owns a CONTIGUOUS run of ceil(S / 32) samples and walks it serially, level by level:
+// while consecutive samples stay in one cell their 8 x 2 corner gradients are summed in registers, and only a change of
+// cell (or the end of the lane's run) sends the 8 rows to the table.  On these grids neighbouring samples of a ray share
+// their cell on most levels, so this replaces the warp-wide segmented shuffle reduction of scatter_level_runs — up to
+// 5 steps x 16 shuffles per level and sample, the dominant instruction cost of the sample-major scatter there — by 16
+// FMAs per sample and one flush per cell crossing (plus one per lane boundary).
+struct RayScatterArgs : SampleSource {
+  int64_t R;
+  LevelParams lv;
+  const float* dfeat;   // [R*S, 2L], zero for samples outside the grid
+  float* dtable;        // [L*T, 2], accumulated into
+  float v4_min_scale;
+};
+
+template <int CMAX>
+__global__ void __launch_bounds__(kEncThreads) encode_bwd_rays_kernel(const RayScatterArgs a) {
+  __shared__ float s_scale[NKBS_MAX_LEVELS];
+  if (threadIdx.x < NKBS_MAX_LEVELS) s_scale[threadIdx.x] = a.lv.scale[threadIdx.x];
+  __syncthreads();
+  const int L = a.lv.num_levels, S = a.S;
+  const uint32_t mask = a.lv.table_mask;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int C = (S + 31) >> 5;
+  for (int64_t r = warp; r < a.R; r += nwarps) {
+    const float3 o = make_float3(a.origins[3 * r], a.origins[3 * r + 1], a.origins[3 * r + 2]);
+    const float3 d = make_float3(a.directions[3 * r], a.directions[3 * r + 1], a.directions[3 * r + 2]);
+    float3 xs[CMAX];
+#pragma unroll
+    for (int c = 0; c < CMAX; ++c) {
+      const int sidx = lane * C + c;
+      xs[c] = make_float3(0.f, 0.f, 0.f);
+      if (c < C && sidx < S) {
+        const int64_t b = r * a.bstride + sidx;
+        float sel;
+        xs[c] = nkbs_normalise(nkbs_frustum_position(o, d, a.starts[b], a.ends[b]), a.norm, sel);
+      }
+    }
+    const float2* g_ray = reinterpret_cast<const float2*>(a.dfeat + (r * S) * (int64_t)(2 * L));
+    for (int l = 0; l < L; ++l) {
+      const float scale = s_scale[l];
+      const bool v4 = scale >= a.v4_min_scale;
+      float* base = a.dtable + ((size_t)l << (a.lv.log2_T + 1));
+      uint32_t ck0 = 0xffffffffu, ck1 = 0xffffffffu;  // no open run
+      Cell cc;
+      float ax[8], ay[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) ax[k] = ay[k] = 0.f;
+      auto flush = [&]() {
+        uint32_t h[8];
+        nkbs_corner_hashes(cc, mask, h);
+        scatter_cell(base, cc, h, ax, ay, v4);
+      };
+#pragma unroll
+      for (int c = 0; c < CMAX; ++c) {
+        const int sidx = lane * C + c;
+        if (c < C && sidx < S) {
+          const float2 g = __ldg(g_ray + (int64_t)sidx * L + l);
+          if (g.x != 0.f || g.y != 0.f) {
+            const Cell cl = nkbs_cell(xs[c], scale);
+            const uint32_t k0 = (cl.f[0] & 0xffffu) | (cl.f[1] << 16);
+            const uint32_t k1 = (cl.f[2] & 0xffffu) | ((cl.c[0] - cl.f[0]) << 16) | ((cl.c[1] - cl.f[1]) << 17) |
+                                ((cl.c[2] - cl.f[2]) << 18);
+            if (k0 != ck0 || k1 != ck1) {
+              if (ck1 != 0xffffffffu) flush();
+              cc = cl;
+              ck0 = k0;
+              ck1 = k1;
+#pragma unroll
+              for (int k = 0; k < 8; ++k) ax[k] = ay[k] = 0.f;
+            }
+            float w[8];
+            nkbs_corner_weights(cl.o[0], cl.o[1], cl.o[2], w);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              ax[k] = fmaf(w[k], g.x, ax[k]);
+              ay[k] = fmaf(w[k], g.y, ay[k]);
+            }
+          }
+        }
+      }
+      if (ck1 != 0xffffffffu) flush();
+    }
+  }
+}
+
 // A batch of fewer CTAs than two waves (148 SMs x 8 resident CTAs) leaves SMs idle or unevenly loaded: the level range
 // is then cut into slices along gridDim.y, each CTA looping over L / slices levels of its 256 samples, so that coarse
 // (shuffle-merged) and fine (L2-bound) levels also run side by side.  NKBS_ENCODE_SLICES overrides (a divisor of L).
@@ -220,5 +308,46 @@ extern "C" int nkbs_encode_bwd(const float* xn, const float* dfeat, int64_t N, c
   int grid = (int)(blocks < cap ? blocks : cap);
   encode_bwd_kernel<<<dim3(grid, level_slices(blocks, L)), kEncThreads, 0, (cudaStream_t)stream>>>(a);
   NKBS_CHECK_LAUNCH("nkbs_encode_bwd");
+  return 0;
+}
+
+extern "C" int nkbs_encode_bwd_rays(int64_t R, int32_t S, const float* origins, const float* directions, const float* starts,
+                                    const float* ends, int32_t bin_stride, int32_t contraction, const float* aabb,
+                                    const float* dfeat, const float* scalings, int32_t L, int32_t log2_T, float* dtable,
+                                    void* stream) {
+  NKBS_CHECK_ARG(R >= 0 && S >= 1 && S <= 256, "nkbs_encode_bwd_rays: S=%d outside 1..256 (use nkbs_encode_bwd)", S);
+  NKBS_CHECK_ARG(dtable && scalings, "nkbs_encode_bwd_rays: bad arguments");
+  NKBS_CHECK_ARG((reinterpret_cast<uintptr_t>(dtable) & 15u) == 0, "nkbs_encode_bwd_rays: dtable must be 16-byte aligned");
+  if (R == 0) return 0;
+  NKBS_CHECK_ARG(origins && directions && starts && ends && dfeat, "nkbs_encode_bwd_rays: null argument");
+  NKBS_CHECK_ARG((reinterpret_cast<uintptr_t>(dfeat) & 7u) == 0, "nkbs_encode_bwd_rays: dfeat must be 8-byte aligned");
+  NKBS_CHECK_ARG(bin_stride == 0 || bin_stride >= S, "nkbs_encode_bwd_rays: bin_stride %d < S", bin_stride);
+  RayScatterArgs a;
+  a.mode = 2;
+  a.x = nullptr;
+  a.origins = origins;
+  a.directions = directions;
+  a.starts = starts;
+  a.ends = ends;
+  a.S = S;
+  a.bstride = bin_stride ? bin_stride : S;
+  a.norm.contraction = contraction;
+  for (int i = 0; i < 3; ++i) {
+    a.norm.aabb_min[i] = aabb ? aabb[i] : 0.f;
+    a.norm.aabb_len[i] = aabb ? aabb[3 + i] - aabb[i] : 1.f;
+  }
+  a.R = R;
+  NKBS_CHECK_ARG(fill_levels(a.lv, scalings, L, log2_T) == 0, "nkbs_encode_bwd_rays: unsupported grid L=%d log2_T=%d", L, log2_T);
+  a.dfeat = dfeat;
+  a.dtable = dtable;
+  a.v4_min_scale = v4_min_scale(1e30f);
+  const int64_t blocks = (R + kEncThreads / 32 - 1) / (kEncThreads / 32);
+  const int64_t cap = (int64_t)nkbs_num_sms() * 8;
+  const int grid = (int)(blocks < cap ? blocks : cap);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (S <= 64) encode_bwd_rays_kernel<2><<<grid, kEncThreads, 0, st>>>(a);
+  else if (S <= 128) encode_bwd_rays_kernel<4><<<grid, kEncThreads, 0, st>>>(a);
+  else encode_bwd_rays_kernel<8><<<grid, kEncThreads, 0, st>>>(a);
+  NKBS_CHECK_LAUNCH("nkbs_encode_bwd_rays");
   return 0;
 }

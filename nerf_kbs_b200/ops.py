@@ -177,6 +177,31 @@ def fused_density_enabled() -> bool:
     return _FUSED_DENSITY["enabled"]
 
 
+# Backward of the fused proposal field for samples that come as rays: the kernel writes the feature gradients and a
+# ray-major kernel scatters them (nkbs_encode_bwd_rays: consecutive samples of a ray that share a cell are summed in
+# registers).  NKBS_RAY_SCATTER=0 keeps the sample-major scatter inside nkbs_density_bwd.
+_RAY_SCATTER = {"enabled": __import__("os").environ.get("NKBS_RAY_SCATTER", "1") != "0"}
+
+
+def set_ray_scatter(enabled: bool) -> None:
+    _RAY_SCATTER["enabled"] = bool(enabled)
+
+
+def _density_backward(mode, x, origins, directions, p_st, p_en, bstride, R, S, norm, table, grid, W1, b1, W2, b2,
+                      ddensity, dedup, dtable, dW1, db1, dW2, db2):
+    """nkbs_density_bwd, with the table-gradient scatter done ray-major when the samples come as rays of <= 256."""
+    head = (mode, ptr(x), ptr(origins), ptr(directions), p_st, p_en, bstride, R, S, int(norm.contraction),
+            host_floats(norm.aabb), ptr(table), host_floats(grid.scalings), grid.L, grid.log2_T, ptr(W1), ptr(b1), ptr(W2),
+            ptr(b2), W1.shape[0], ptr(ddensity), dedup)
+    if _RAY_SCATTER["enabled"] and mode == 2 and S <= 256 and R > 0:
+        dfeat = torch.empty((R * S, grid.out_dim), device=table.device, dtype=torch.float32)
+        call("nkbs_density_bwd", *head, None, ptr(dW1), ptr(db1), ptr(dW2), ptr(db2), ptr(dfeat), stream())
+        call("nkbs_encode_bwd_rays", R, S, ptr(origins), ptr(directions), p_st, p_en, bstride, int(norm.contraction),
+             host_floats(norm.aabb), ptr(dfeat), host_floats(grid.scalings), grid.L, grid.log2_T, ptr(dtable), stream())
+        return
+    call("nkbs_density_bwd", *head, ptr(dtable), ptr(dW1), ptr(db1), ptr(dW2), ptr(db2), None, stream())
+
+
 class _FusedDensity(torch.autograd.Function):
     @staticmethod
     def forward(ctx, table, W1, b1, W2, b2, grid, norm, dedup_levels, x, origins, directions, starts, ends, sinks=None):
@@ -206,10 +231,8 @@ class _FusedDensity(torch.autograd.Function):
         ddensity = _c(ddensity)
         (dtable, dW1, db1, dW2, db2), ret = _grad_buffers(ctx.sinks, [table, W1, b1, W2, b2])
         p_st, p_en, bstride, _keep = rows(starts, ends)
-        call("nkbs_density_bwd", mode, ptr(x), ptr(origins), ptr(directions), p_st, p_en, bstride, R, S,
-             int(norm.contraction), host_floats(norm.aabb), ptr(table), host_floats(grid.scalings), grid.L, grid.log2_T,
-             ptr(W1), ptr(b1), ptr(W2), ptr(b2), H, ptr(ddensity), dedup, ptr(dtable), ptr(dW1), ptr(db1), ptr(dW2),
-             ptr(db2), stream())
+        _density_backward(mode, x, origins, directions, p_st, p_en, bstride, R, S, norm, table, grid, W1, b1, W2, b2,
+                          ddensity, dedup, dtable, dW1, db1, dW2, db2)
         return (*ret,) + (None,) * 9
 
 
@@ -572,9 +595,8 @@ class _ProposalLevel(torch.autograd.Function):
         call("nkbs_composite_bwd", R, S, ptr(density), ptr(weights), st, en, S + 1, None, None, 0, 0, 0, None, None,
              ptr(g_w), None, None, None, None, ptr(ddensity), None, None, None, stream())
         (dtable, dW1, db1, dW2, db2), ret = _grad_buffers(ctx.sinks, [table, W1, b1, W2, b2])
-        call("nkbs_density_bwd", 2, None, ptr(origins), ptr(directions), st, en, S + 1, R, S, int(norm.contraction),
-             host_floats(norm.aabb), ptr(table), host_floats(grid.scalings), grid.L, grid.log2_T, ptr(W1), ptr(b1), ptr(W2),
-             ptr(b2), W1.shape[0], ptr(ddensity), dedup, ptr(dtable), ptr(dW1), ptr(db1), ptr(dW2), ptr(db2), stream())
+        _density_backward(2, None, origins, directions, st, en, S + 1, R, S, norm, table, grid, W1, b1, W2, b2, ddensity,
+                          dedup, dtable, dW1, db1, dW2, db2)
         return (*ret,) + (None,) * 10
 
 

@@ -130,3 +130,32 @@ def test_training_route_of_the_hidden64_field():
     finally:
         ops.set_mlp_precision(prev)
     assert_close(d_train, d_eval, 1e-5, "density, training route vs fused forward")
+
+
+@pytest.mark.parametrize("kind", ["nerfacto_prop0", "nerfacto_prop1"])
+@pytest.mark.parametrize("R,S", [(200, 256), (333, 96), (50, 48), (7, 33)])
+def test_ray_major_scatter_equals_sample_major_scatter(kind, R, S):
+    """Backward of the fused field on ray samples: feature gradients + nkbs_encode_bwd_rays (default) against the
+    scatter inside nkbs_density_bwd — same sums, different association."""
+    if kind not in SHAPES:
+        pytest.skip("shape not in this file's table")
+    _, n = _pair(kind, seed=7)
+    rb, rs_o = _samples(R, S)
+    fr = rs_o.frustums
+    W, b = n.mlp_base[1].weights_biases()
+    dy = torch.rand(R * S, generator=torch.Generator().manual_seed(8)).to(DEV)
+    res = {}
+    try:
+        for ray in (False, True):
+            ops.set_ray_scatter(ray)
+            for p in n.parameters():
+                p.grad = None
+            d = ops.fused_density(n.encoding.hash_table, n.encoding.grid, n._norm, W[0], b[0], W[1], b[1],
+                                  origins=rb.origins.to(DEV), directions=rb.directions.to(DEV),
+                                  starts=fr.starts[..., 0].to(DEV), ends=fr.ends[..., 0].to(DEV))
+            d.backward(dy)
+            res[ray] = [p.grad.clone() for p in n.parameters()]
+    finally:
+        ops.set_ray_scatter(True)
+    for a, bb in zip(res[True], res[False]):
+        assert_close(a, bb, 2e-5, "gradient, ray-major vs sample-major scatter")
