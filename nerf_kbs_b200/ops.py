@@ -117,18 +117,34 @@ class _HashEncode(torch.autograd.Function):
         # never loses on B200 (scripts/encode_bench.py sweep): -1 = every level
         ctx.dedup = dedup_levels if dedup_levels >= 0 else grid.L
         ctx.table_shape = table.shape
-        ctx.save_for_backward(xn)
+        # Optional (set_ray_scatter(encode=True)): proposal-sized ray samples (64..256 per ray) take the ray-major
+        # scatter in the backward pass.  Off by default: on the 8-level grids that reach this unfused route (the
+        # semantic-NeRF-W proposals) it measured slower than the run-merged sample-major scatter (8192-ray step 2.676 ->
+        # 2.714 ms), unlike on the 5-level grids of the fused field (see _density_backward).
+        ctx.rays = None
+        if mode == 2 and _RAY_SCATTER["encode"] and norm is not None and 64 <= starts.shape[1] <= 256:
+            ctx.rays = (norm, starts.shape[0], starts.shape[1])
+            ctx.save_for_backward(xn, origins, directions, starts, ends)
+        else:
+            ctx.save_for_backward(xn)
         ctx.mark_non_differentiable(sel, xn)
         return feats, sel, xn
 
     @staticmethod
     def backward(ctx, dfeat, _dsel, _dxn):
-        (xn,) = ctx.saved_tensors
+        xn = ctx.saved_tensors[0]
         g = ctx.grid
         if dfeat is None:
             return (None,) * 11
         (dtable,), (ret,) = _grad_buffers([ctx.sink] if ctx.sink is not None else None, [xn.new_empty(ctx.table_shape)])
         dfeat = _c(dfeat)
+        if ctx.rays is not None:
+            norm, R, S = ctx.rays
+            _, origins, directions, starts, ends = ctx.saved_tensors
+            p_st, p_en, bstride, _keep = rows(starts, ends)
+            call("nkbs_encode_bwd_rays", R, S, ptr(origins), ptr(directions), p_st, p_en, bstride, int(norm.contraction),
+                 host_floats(norm.aabb), ptr(dfeat), host_floats(g.scalings), g.L, g.log2_T, ptr(dtable), stream())
+            return (ret,) + (None,) * 10
         call("nkbs_encode_bwd", ptr(xn), ptr(dfeat), xn.shape[0], host_floats(g.scalings), g.L, g.log2_T,
              g.features_per_level, ctx.dedup, ptr(dtable), stream())
         return (ret,) + (None,) * 10
@@ -180,11 +196,13 @@ def fused_density_enabled() -> bool:
 # Backward of the fused proposal field for samples that come as rays: the kernel writes the feature gradients and a
 # ray-major kernel scatters them (nkbs_encode_bwd_rays: consecutive samples of a ray that share a cell are summed in
 # registers).  NKBS_RAY_SCATTER=0 keeps the sample-major scatter inside nkbs_density_bwd.
-_RAY_SCATTER = {"enabled": __import__("os").environ.get("NKBS_RAY_SCATTER", "1") != "0"}
+_RAY_SCATTER = {"enabled": __import__("os").environ.get("NKBS_RAY_SCATTER", "1") != "0", "encode": False}
 
 
-def set_ray_scatter(enabled: bool) -> None:
+def set_ray_scatter(enabled: bool, encode: bool = False) -> None:
+    """``enabled``: backward of the fused proposal field; ``encode``: backward of contract_encode on ray samples."""
     _RAY_SCATTER["enabled"] = bool(enabled)
+    _RAY_SCATTER["encode"] = bool(encode)
 
 
 def _density_backward(mode, x, origins, directions, p_st, p_en, bstride, R, S, norm, table, grid, W1, b1, W2, b2,

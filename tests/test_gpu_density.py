@@ -159,3 +159,28 @@ def test_ray_major_scatter_equals_sample_major_scatter(kind, R, S):
         ops.set_ray_scatter(True)
     for a, bb in zip(res[True], res[False]):
         assert_close(a, bb, 2e-5, "gradient, ray-major vs sample-major scatter")
+
+
+@pytest.mark.parametrize("S", [96, 256, 64])
+def test_unfused_encode_backward_ray_major_scatter(S):
+    """contract_encode on proposal-sized ray samples: the backward takes nkbs_encode_bwd_rays; same table gradient as
+    the sample-major nkbs_encode_bwd."""
+    _, n = _pair("snw_default", seed=9)
+    R = 150
+    rb, rs_o = _samples(R, S)
+    fr = rs_o.frustums
+    g = torch.Generator().manual_seed(10)
+    dy = torch.randn(R * S, n.encoding.grid.out_dim, generator=g).to(DEV)
+    res = {}
+    try:
+        for ray in (False, True):
+            ops.set_ray_scatter(True, encode=ray)
+            n.encoding.hash_table.grad = None
+            feats, sel = ops.contract_encode(n.encoding.hash_table, n.encoding.grid, n._norm, origins=rb.origins.to(DEV),
+                                             directions=rb.directions.to(DEV), starts=fr.starts[..., 0].to(DEV),
+                                             ends=fr.ends[..., 0].to(DEV))
+            (feats * dy * sel[:, None]).sum().backward()
+            res[ray] = n.encoding.hash_table.grad.clone()
+    finally:
+        ops.set_ray_scatter(True)
+    assert_close(res[True], res[False], 2e-5, "table gradient, ray-major vs sample-major scatter")
