@@ -547,52 +547,6 @@ def timed_steps(step_fn, steps, dev, world):
     return _max_over_ranks(e0.elapsed_time(e1), dev, world)
 
 
-def dp_exchange_probe(tr, dev_packed, dev, world, steps=12):
-    """Device time of the gradient exchange + optimizer of the data-parallel step (ShardedAdam.step: opening barrier,
-    nkbs_dp_adam_step, closing barrier, re-zeroing of the gradient buffer), per parameter group, in eager steps with a
-    CUDA-event pair on the launching stream; max over ranks of the per-rank median.  This stands in for a profiler
-    timeline of the N > 1 step (ncu / nsys may not wrap a multi-rank command here)."""
-    import statistics
-    import torch
-    import torch.distributed as dist
-    rec = {}
-    orig = tr.sharded.step
-
-    def timed(active=None):
-        names = tuple(active) if active is not None else tuple(tr.sharded.layout)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        orig(active)
-        e1.record()
-        rec.setdefault("+".join(names), []).append((e0, e1))
-
-    was = tr.use_graph
-    tr.use_graph = False
-    tr.sharded.step = timed
-    try:
-        for i in range(steps):
-            tr.train_step(packed=dev_packed[i % len(dev_packed)])
-        tr.flush()
-        torch.cuda.synchronize()
-    finally:
-        tr.sharded.step = orig
-        tr.use_graph = was
-    out = {}
-    for k in sorted(rec):
-        ms = statistics.median(a.elapsed_time(b) for a, b in rec[k][2:]) if len(rec[k]) > 2 else float("nan")
-        t = torch.tensor([ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        lay = [tr.sharded.layout[n] for n in k.split("+")]
-        out[k] = {"ms": round(t.item(), 4), "owned_parameters_per_rank": sum(l["n"] for l in lay),
-                  "parameters": sum(l["len"] for l in lay)}
-    out["route"] = "multimem (in-switch reduction + replicated stores)" if tr.sharded.multimem else "peer loads / stores"
-    out["note"] = ("eager steps: each figure includes the wait for the slowest rank at the opening barrier (host-side skew "
-                   "that a replayed graph does not have); in the captured step the 'fields' exchange runs on a side "
-                   "stream beside the next step's proposal forward (deferred Adam), so only what exceeds that forward is "
-                   "exposed in ms_per_step")
-    return out
-
-
 def cfg5_leg(args, dev, rank, world, steps, warmup, n1_value=None):
     """BASELINE configs[4]: the nerfacto training step at 65 536 rays per GPU, data parallel over this run's N GPUs."""
     import torch
@@ -858,8 +812,6 @@ def run_nkbs(args):
 
     # (2c) the other BASELINE configurations as sub-legs, and the data-parallel correctness check (every rank)
     legs = {}
-    if world > 1 and tr.sharded is not None and not args.no_kernel_pass:
-        legs["dp_exchange"] = dp_exchange_probe(tr, dev_packed, dev, world)
     if not args.no_legs and args.model == "nerfacto" and R == 4096:
         tr.close()
         del devb
