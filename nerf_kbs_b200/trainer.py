@@ -125,6 +125,8 @@ class Trainer:
         self._step_stream = torch.cuda.Stream(p0.device, priority=int(os.environ.get("NKBS_STEP_PRIO", "-1")))  # captured steps run at high priority
         self._hooks = [model.register_forward_pre_hook(self._pre_model_forward),
                        model.field.register_forward_pre_hook(self._pre_field_forward)]
+        if hasattr(model, "register_state_dict_pre_hook"):  # a checkpoint must see the update that is still pending
+            self._hooks.append(model.register_state_dict_pre_hook(lambda module, prefix, keep_vars: self.flush()))
         self._inv_world = torch.full((), 1.0 / self.world_size, device=p0.device) if self.world_size > 1 else None
         self.use_graph = use_graph
         self.graph_warmup = graph_warmup

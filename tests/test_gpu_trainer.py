@@ -352,3 +352,20 @@ def test_lagged_loss_readback_returns_every_loss_one_step_late():
         runs.append(ls)
     for a, b in zip(*runs):
         assert abs(a - b) <= 2e-4 * abs(a), runs
+
+
+def test_state_dict_sees_the_deferred_update():
+    """A checkpoint taken right after train_step includes the optimizer update the driver defers into the next step."""
+    R = 256
+    rb = O.synthetic_ray_bundle(R, seed=15)
+    batch = {"image": torch.rand(R, 3, generator=torch.Generator().manual_seed(16)).to(DEV)}
+    _, nm = _train_pair(R, 0, False)
+    tr = Trainer(nm, R, use_graph=False)
+    before = nm.field.mlp_head.layers[0].weight.detach().clone()
+    tr.train_step(to_nk_bundle(rb, DEV), batch)
+    assert tr._pending and torch.equal(nm.field.mlp_head.layers[0].weight.detach(), before)
+    sd = nm.state_dict()
+    assert not tr._pending
+    assert not torch.equal(sd["field.mlp_head.layers.0.weight"], before)
+    tr.close()
+    assert "field.mlp_base_grid.hash_table" in nm.state_dict()
