@@ -322,6 +322,22 @@ int nkbs_expected_depth_noalloc(int64_t R, int32_t S, const float* weights, cons
  * replaces: optimizer.zero_grad() of the nerfstudio Trainer loop (train.py:85-98 optimizers). */
 int nkbs_zero_async(void* dev_ptr, int64_t bytes, void* stream);
 
+/* Deterministic gradient accumulation (opt-in).  nkbs_fixed_point_register pairs a DEVICE float gradient buffer
+ * grad_base [n] with a zero-filled DEVICE int64 shadow [n] (shadow == NULL removes the pair).  From then on every
+ * backward entry point (nkbs_encode_bwd, nkbs_encode_bwd_rays, nkbs_density_bwd, nkbs_mlp_bwd, nkbs_mlp_tc_bwd,
+ * nkbs_head_tc_bwd, nkbs_assemble_bwd) whose parameter-gradient destinations lie inside grad_base adds its partial sums to
+ * the shadow as 64-bit fixed point (2^log2_scale units per 1.0; log2_scale in [16, 60]; |sum| must stay below
+ * 2^(63 - log2_scale), partial sums below 2^-log2_scale are dropped) instead of issuing float atomics: integer additions
+ * commute, so the result does not depend on the arrival order of warps and CTAs and two runs of the same step produce
+ * the same bits.  nkbs_fixed_point_flush(dst, n): dst[i] += shadow[i] / 2^log2_scale and shadow[i] = 0 for a range
+ * [dst, dst + n) inside a registered buffer — one thread per element, no atomics; call it before the optimizer reads the
+ * gradients (dst an even number of elements into the buffer, shadow 16-byte aligned).  The registry is process-wide host state read at launch time (so a captured graph keeps the mode it was
+ * captured in); registering is not thread-safe against concurrent launches into the same buffer.
+ * replaces: nothing in the reference (torch's index_put / scatter backward there is non-deterministic as well); answers
+ *           north_star's "atomic-free gradient scatter" with an order-independent one. */
+int nkbs_fixed_point_register(float* grad_base, int64_t n, int64_t* shadow, int32_t log2_scale);
+int nkbs_fixed_point_flush(float* dst, int64_t n, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

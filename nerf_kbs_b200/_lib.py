@@ -46,6 +46,8 @@ SIGNATURES = {
     "nkbs_composite_fwd": [_i64, _i32, _p, _p, _p, _p, _i32, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
     "nkbs_adam_step": [_i32, _p, _p, _p, _p, _p, _f, _f, _f, _f, _f, _p, _p, _i32, _p, _p],
     "nkbs_zero_async": [_p, _i64, _p],
+    "nkbs_fixed_point_register": [_p, _i64, _p, _i32],
+    "nkbs_fixed_point_flush": [_p, _i64, _p],
     "nkbs_weights_resample_fwd": [_i64, _i32, _p, _p, _p, _p, _p, _i32, _f, _p, _f, _f, _p, _p, _p, _p, _p, _p, _p],
     "nkbs_expected_depth_noalloc": [_i64, _i32, _p, _p, _p, _i32, _p, _p],
     "nkbs_proposal_level_fwd": [_i64, _i32, _p, _p, _p, _p, _i32, _p, _p, _p, _p, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p,

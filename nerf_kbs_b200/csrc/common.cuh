@@ -28,6 +28,37 @@ void nkbs_set_error(const char* fmt, ...);
 
 int nkbs_num_sms();
 
+// ---- deterministic gradient accumulation (opt-in, nkbs_fixed_point_register) ----
+// A registered gradient buffer [base, base + n) has a 64-bit fixed-point shadow (2^log2_scale units per 1.0).  Kernels
+// that would add a float partial sum to an address inside the buffer with an atomic add it to the shadow instead:
+// integer additions commute exactly, so the total does not depend on the order in which CTAs and warps arrive.
+// nkbs_fixed_point_flush adds the shadow into the float buffer (one thread per element, no atomics) and re-zeroes it.
+// Addresses outside every registered buffer (and all addresses when nothing is registered) take the float atomics.
+struct FixedMap {
+  const float* base;
+  long long* shadow;  // null: not registered
+  long long n;
+  float scale;        // 2^log2_scale
+  __device__ __forceinline__ long long* at(const float* p) const {
+    if (!shadow) return nullptr;
+    const long long i = p - base;
+    return (i >= 0 && i < n) ? shadow + i : nullptr;
+  }
+};
+FixedMap nkbs_fixed_map_for(const void* p);  // host side (abi.cu): the registered buffer that holds p, or a null map
+
+#ifdef __CUDACC__
+__device__ __forceinline__ void nkbs_fixed_add(long long* addr, float v, float scale) {
+  if (v != 0.f) atomicAdd(reinterpret_cast<unsigned long long*>(addr), (unsigned long long)__float2ll_rn(v * scale));
+}
+// float partial sum v -> *p: fixed-point shadow when p lies in a registered buffer, float atomic otherwise
+__device__ __forceinline__ void nkbs_acc(float* p, const FixedMap& fm, float v) {
+  long long* f = fm.at(p);
+  if (f) nkbs_fixed_add(f, v, fm.scale);
+  else atomicAdd(p, v);
+}
+#endif
+
 struct LevelParams {
   float scale[NKBS_MAX_LEVELS];
   int num_levels;

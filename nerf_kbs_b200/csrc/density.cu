@@ -40,6 +40,7 @@ struct DensityArgs : SampleSource {
   float* db2;
   int dedup_levels;
   float v4_min_scale;  // see encode.cuh
+  FixedMap fm;         // backward, deterministic mode (common.cuh): shadow of the gradient buffer, or a null map
   float* df_out;       // backward, optional [N, 2L]: the feature gradients are written here INSTEAD of being scattered
                        // (the ray-major scatter nkbs_encode_bwd_rays follows)
 };
@@ -221,7 +222,7 @@ __device__ __forceinline__ void load_a_transposed(const float* tile, int ks, int
 template <int H>
 constexpr int bwd_ctas() { return H <= 16 ? NKBS_DENSITY_BWD_CTAS : 1; }
 
-template <int H, int L>
+template <int H, int L, bool FX>
 __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(const DensityArgs a) {
   constexpr int K = 2 * L, KP = Smem<H, L>::KP;
   // gradient rows, in this order: for each hidden unit j: dW1[j][0..K), db1[j], dW2[j]; then db2
@@ -437,8 +438,9 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
       float w[8];
       nkbs_corner_weights(cl.o[0], cl.o[1], cl.o[2], w);
       float* base = a.dtable + ((size_t)l << (a.lv.log2_T + 1));
+      long long* fixed = FX ? a.fm.at(base) : nullptr;
       if (l < a.dedup_levels) {
-        scatter_level_runs(base, cl, h, w, df[2 * l], df[2 * l + 1], lane, s_scale[l] >= a.v4_min_scale);
+        scatter_level_runs<FX>(base, cl, h, w, df[2 * l], df[2 * l + 1], lane, s_scale[l] >= a.v4_min_scale, fixed, a.fm.scale);
       } else {
         float vx[8], vy[8];
 #pragma unroll
@@ -446,11 +448,28 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
           vx[k] = w[k] * df[2 * l];
           vy[k] = w[k] * df[2 * l + 1];
         }
-        scatter_cell(base, cl, h, vx, vy, s_scale[l] >= a.v4_min_scale);
+        scatter_cell<FX>(base, cl, h, vx, vy, s_scale[l] >= a.v4_min_scale, fixed, a.fm.scale);
       }
     }
   }
   // ---- warp totals -> CTA totals -> global ----
+  // row r of the totals -> its gradient element
+  auto dest = [&](int r) -> float* {
+    if (r == kRows - 1) return a.db2;
+    const int j = r / kPerJ, c = r - j * kPerJ;
+    return c < K ? a.dW1 + j * K + c : (c == K ? a.db1 + j : a.dW2 + j);
+  };
+  // deterministic mode: the float atomics on the CTA totals depend on the order of the warps, so every warp adds its
+  // totals to the fixed-point shadow directly
+  constexpr bool det = FX;
+  auto add = [&](int r, float v) {
+    if (v == 0.f) return;
+    if constexpr (det) {
+      if (r < kRows) nkbs_acc(dest(r), a.fm, v);
+    } else {
+      atomicAdd(&s_tot[r], v);
+    }
+  };
   if constexpr (kMma) {
     // D1 tile (mt, nt): d0 (j = 16mt + g, c = 8nt + 2t), d1 (j, c + 1), d2 (j + 8, c), d3 (j + 8, c + 1); columns c <= K are real
 #pragma unroll
@@ -460,33 +479,25 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const int j = 16 * mt + fg + (i >= 2 ? 8 : 0), c = 8 * nt + 2 * ft + (i & 1);
-          if (c <= K && d1[mt][nt][i] != 0.f) atomicAdd(&s_tot[j * kPerJ + c], d1[mt][nt][i]);
+          if (c <= K) add(j * kPerJ + c, d1[mt][nt][i]);
         }
       }
       if (ft == 0) {  // column 0 of D2: dW2[16mt + g], dW2[16mt + g + 8]
-        if (d2[mt][0] != 0.f) atomicAdd(&s_tot[(16 * mt + fg) * kPerJ + K + 1], d2[mt][0]);
-        if (d2[mt][2] != 0.f) atomicAdd(&s_tot[(16 * mt + fg + 8) * kPerJ + K + 1], d2[mt][2]);
+        add((16 * mt + fg) * kPerJ + K + 1, d2[mt][0]);
+        add((16 * mt + fg + 8) * kPerJ + K + 1, d2[mt][2]);
       }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) db2_acc += __shfl_xor_sync(0xffffffffu, db2_acc, o);
-    if (lane == 0 && db2_acc != 0.f) atomicAdd(&s_tot[kRows - 1], db2_acc);
+    if (lane == 0) add(kRows - 1, db2_acc);
   }
 #pragma unroll
-  for (int p = 0; p < kPasses; ++p)
-    if (acc[p] != 0.f) atomicAdd(&s_tot[p * 32 + lane], acc[p]);
+  for (int p = 0; p < kPasses; ++p) add(p * 32 + lane, acc[p]);
+  if constexpr (det) return;
   __syncthreads();
   for (int r = threadIdx.x; r < kRows; r += kThreads) {
     const float v = s_tot[r];
-    if (v == 0.f) continue;
-    if (r == kRows - 1) {
-      atomicAdd(a.db2, v);
-    } else {
-      const int j = r / kPerJ, c = r - j * kPerJ;
-      if (c < K) atomicAdd(a.dW1 + j * K + c, v);
-      else if (c == K) atomicAdd(a.db1 + j, v);
-      else atomicAdd(a.dW2 + j, v);
-    }
+    if (v != 0.f) atomicAdd(dest(r), v);
   }
 }
 
@@ -539,6 +550,7 @@ int fill(DensityArgs& a, const char* who, int mode, const float* x, const float*
   a.dedup_levels = 0;
   a.v4_min_scale = v4_min_scale(1e30f);
   a.df_out = nullptr;
+  a.fm = FixedMap{nullptr, nullptr, 0, 0.f};
   return 0;
 }
 
@@ -762,6 +774,7 @@ extern "C" int nkbs_density_bwd(int32_t mode, const float* x, const float* origi
   NKBS_CHECK_ARG((reinterpret_cast<uintptr_t>(dtable) & 15u) == 0, "nkbs_density_bwd: dtable must be 16-byte aligned");
   NKBS_CHECK_ARG((reinterpret_cast<uintptr_t>(dfeat_out) & 7u) == 0, "nkbs_density_bwd: dfeat_out must be 8-byte aligned");
   a.df_out = dfeat_out;
+  a.fm = nkbs_fixed_map_for(dW1 ? (const void*)dW1 : (const void*)dtable);
   a.ddensity = ddensity;
   a.dtable = dtable;
   a.dW1 = dW1;
@@ -773,14 +786,17 @@ extern "C" int nkbs_density_bwd(int32_t mode, const float* x, const float* origi
   if (H == 16) {
     constexpr size_t smem = (size_t)kWarps * MmaGeom<16, 5>::kScratch * sizeof(float);
     static_assert(smem <= 48 * 1024, "default dynamic shared memory limit");
-    density_bwd_kernel<16, 5><<<grid_for(density_bwd_kernel<16, 5>, a.N, smem), kThreads, smem, st>>>(a);
+    if (a.fm.shadow) density_bwd_kernel<16, 5, true><<<grid_for(density_bwd_kernel<16, 5, true>, a.N, smem), kThreads, smem, st>>>(a);
+    else density_bwd_kernel<16, 5, false><<<grid_for(density_bwd_kernel<16, 5, false>, a.N, smem), kThreads, smem, st>>>(a);
   } else {
     constexpr size_t smem = (size_t)kWarps * MmaGeom<64, 8>::kScratch * sizeof(float);
     if (smem > 48 * 1024) {
-      cudaError_t e = cudaFuncSetAttribute(density_bwd_kernel<64, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaError_t e = cudaFuncSetAttribute(density_bwd_kernel<64, 8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(density_bwd_kernel<64, 8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       NKBS_CHECK_ARG(e == cudaSuccess, "nkbs_density_bwd: %zu bytes of shared memory refused (%s)", smem, cudaGetErrorString(e));
     }
-    density_bwd_kernel<64, 8><<<grid_for(density_bwd_kernel<64, 8>, a.N, smem), kThreads, smem, st>>>(a);
+    if (a.fm.shadow) density_bwd_kernel<64, 8, true><<<grid_for(density_bwd_kernel<64, 8, true>, a.N, smem), kThreads, smem, st>>>(a);
+    else density_bwd_kernel<64, 8, false><<<grid_for(density_bwd_kernel<64, 8, false>, a.N, smem), kThreads, smem, st>>>(a);
   }
   NKBS_CHECK_LAUNCH("nkbs_density_bwd");
   return 0;

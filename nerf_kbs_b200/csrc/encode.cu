@@ -95,8 +95,10 @@ struct EncodeBwdArgs {
   float* dtable;          // [L*T,2], accumulated into
   int dedup_levels;       // levels below this index use warp-level duplicate merging
   float v4_min_scale;     // levels of at least this resolution pair their reductions (16-byte red)
+  FixedMap fm;            // deterministic mode (common.cuh): shadow of the buffer that holds dtable, or a null map
 };
 
+template <bool FX>
 __global__ void __launch_bounds__(kEncThreads) encode_bwd_kernel(const EncodeBwdArgs a) {
   __shared__ float s_scale[NKBS_MAX_LEVELS];
   if (threadIdx.x < NKBS_MAX_LEVELS) s_scale[threadIdx.x] = a.lv.scale[threadIdx.x];
@@ -120,8 +122,9 @@ __global__ void __launch_bounds__(kEncThreads) encode_bwd_kernel(const EncodeBwd
       nkbs_corner_weights(cl.o[0], cl.o[1], cl.o[2], w);
       float2 gl = live ? __ldg(g + l) : make_float2(0.f, 0.f);
       float* base = a.dtable + ((size_t)l << (a.lv.log2_T + 1));
+      long long* fixed = FX ? a.fm.at(base) : nullptr;
       if (l < a.dedup_levels) {
-        scatter_level_runs(base, cl, h, w, gl.x, gl.y, lane, s_scale[l] >= a.v4_min_scale);
+        scatter_level_runs<FX>(base, cl, h, w, gl.x, gl.y, lane, s_scale[l] >= a.v4_min_scale, fixed, a.fm.scale);
       } else {
         float vx[8], vy[8];
 #pragma unroll
@@ -129,7 +132,7 @@ __global__ void __launch_bounds__(kEncThreads) encode_bwd_kernel(const EncodeBwd
           vx[k] = w[k] * gl.x;
           vy[k] = w[k] * gl.y;
         }
-        scatter_cell(base, cl, h, vx, vy, s_scale[l] >= a.v4_min_scale);
+        scatter_cell<FX>(base, cl, h, vx, vy, s_scale[l] >= a.v4_min_scale, fixed, a.fm.scale);
       }
     }
   }
@@ -148,9 +151,10 @@ struct RayScatterArgs : SampleSource {
   const float* dfeat;   // [R*S, 2L], zero for samples outside the grid
   float* dtable;        // [L*T, 2], accumulated into
   float v4_min_scale;
+  FixedMap fm;          // deterministic mode, see EncodeBwdArgs
 };
 
-template <int CMAX>
+template <int CMAX, bool FX>
 __global__ void __launch_bounds__(kEncThreads) encode_bwd_rays_kernel(const RayScatterArgs a) {
   __shared__ float s_scale[NKBS_MAX_LEVELS];
   if (threadIdx.x < NKBS_MAX_LEVELS) s_scale[threadIdx.x] = a.lv.scale[threadIdx.x];
@@ -180,6 +184,7 @@ __global__ void __launch_bounds__(kEncThreads) encode_bwd_rays_kernel(const RayS
       const float scale = s_scale[l];
       const bool v4 = scale >= a.v4_min_scale;
       float* base = a.dtable + ((size_t)l << (a.lv.log2_T + 1));
+      long long* fixed = FX ? a.fm.at(base) : nullptr;
       uint32_t ck0 = 0xffffffffu, ck1 = 0xffffffffu;  // no open run
       Cell cc;
       float ax[8], ay[8];
@@ -188,7 +193,7 @@ __global__ void __launch_bounds__(kEncThreads) encode_bwd_rays_kernel(const RayS
       auto flush = [&]() {
         uint32_t h[8];
         nkbs_corner_hashes(cc, mask, h);
-        scatter_cell(base, cc, h, ax, ay, v4);
+        scatter_cell<FX>(base, cc, h, ax, ay, v4, fixed, a.fm.scale);
       };
 #pragma unroll
       for (int c = 0; c < CMAX; ++c) {
@@ -301,12 +306,14 @@ extern "C" int nkbs_encode_bwd(const float* xn, const float* dfeat, int64_t N, c
   a.dtable = dtable;
   a.dedup_levels = dedup_levels < 0 ? L : dedup_levels;
   a.v4_min_scale = v4_min_scale(0.f);
+  a.fm = nkbs_fixed_map_for(dtable);
   if (N == 0) return 0;
   NKBS_CHECK_ARG(xn && dfeat, "nkbs_encode_bwd: null xn/dfeat");
   int64_t blocks = (N + kEncThreads - 1) / kEncThreads;
   int64_t cap = (int64_t)nkbs_num_sms() * 32;
   int grid = (int)(blocks < cap ? blocks : cap);
-  encode_bwd_kernel<<<dim3(grid, level_slices(blocks, L)), kEncThreads, 0, (cudaStream_t)stream>>>(a);
+  if (a.fm.shadow) encode_bwd_kernel<true><<<dim3(grid, level_slices(blocks, L)), kEncThreads, 0, (cudaStream_t)stream>>>(a);
+  else encode_bwd_kernel<false><<<dim3(grid, level_slices(blocks, L)), kEncThreads, 0, (cudaStream_t)stream>>>(a);
   NKBS_CHECK_LAUNCH("nkbs_encode_bwd");
   return 0;
 }
@@ -341,13 +348,20 @@ extern "C" int nkbs_encode_bwd_rays(int64_t R, int32_t S, const float* origins, 
   a.dfeat = dfeat;
   a.dtable = dtable;
   a.v4_min_scale = v4_min_scale(1e30f);
+  a.fm = nkbs_fixed_map_for(dtable);
   const int64_t blocks = (R + kEncThreads / 32 - 1) / (kEncThreads / 32);
   const int64_t cap = (int64_t)nkbs_num_sms() * 8;
   const int grid = (int)(blocks < cap ? blocks : cap);
   cudaStream_t st = (cudaStream_t)stream;
-  if (S <= 64) encode_bwd_rays_kernel<2><<<grid, kEncThreads, 0, st>>>(a);
-  else if (S <= 128) encode_bwd_rays_kernel<4><<<grid, kEncThreads, 0, st>>>(a);
-  else encode_bwd_rays_kernel<8><<<grid, kEncThreads, 0, st>>>(a);
+  if (a.fm.shadow) {
+    if (S <= 64) encode_bwd_rays_kernel<2, true><<<grid, kEncThreads, 0, st>>>(a);
+    else if (S <= 128) encode_bwd_rays_kernel<4, true><<<grid, kEncThreads, 0, st>>>(a);
+    else encode_bwd_rays_kernel<8, true><<<grid, kEncThreads, 0, st>>>(a);
+  } else {
+    if (S <= 64) encode_bwd_rays_kernel<2, false><<<grid, kEncThreads, 0, st>>>(a);
+    else if (S <= 128) encode_bwd_rays_kernel<4, false><<<grid, kEncThreads, 0, st>>>(a);
+    else encode_bwd_rays_kernel<8, false><<<grid, kEncThreads, 0, st>>>(a);
+  }
   NKBS_CHECK_LAUNCH("nkbs_encode_bwd_rays");
   return 0;
 }

@@ -41,8 +41,24 @@ __device__ __forceinline__ float3 load_sample_position(const SampleSource& a, in
 #ifndef NKBS_SCATTER_V4
 #define NKBS_SCATTER_V4 1
 #endif
+// Deterministic mode (common.cuh, FixedMap): `fixed` != nullptr is the fixed-point shadow of this level's table gradient
+// and takes the additions instead of the float reductions.
+// FX is a compile-time switch so that the default kernels carry no trace of the mode.
+template <bool FX = false>
 __device__ __forceinline__ void scatter_cell(float* base, const Cell& cl, const uint32_t h[8], const float vx[8],
-                                             const float vy[8], bool v4) {
+                                             const float vy[8], bool v4, long long* fixed = nullptr, float fscale = 0.f) {
+  if constexpr (FX) {
+    if (!fixed) {  // a destination outside the registered buffer
+      scatter_cell<false>(base, cl, h, vx, vy, v4);
+      return;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      nkbs_fixed_add(fixed + 2 * (size_t)h[k], vx[k], fscale);
+      nkbs_fixed_add(fixed + 2 * (size_t)h[k] + 1, vy[k], fscale);
+    }
+    return;
+  }
   constexpr int kC[4] = {0, 1, 4, 5}, kF[4] = {3, 2, 7, 6};  // x edges as (ceil-x corner, floor-x corner)
   const bool pair = NKBS_SCATTER_V4 && v4 && !(cl.f[0] & 1u) && cl.c[0] != cl.f[0];
 #pragma unroll
@@ -66,8 +82,10 @@ __device__ __forceinline__ void scatter_cell(float* base, const Cell& cl, const 
 // is summed with a segmented shuffle-down reduction (5 fixed steps for the 8 corners x 2 features), after which
 // only the first lane of each run issues the 8 vector reductions: coarse levels drop from 32 to 1-4 reductions
 // per corner and warp, at a cost that does not depend on the run length.  The whole warp must be converged.
+template <bool FX = false>
 __device__ __forceinline__ void scatter_level_runs(float* base, const Cell& cl, const uint32_t h[8], const float w[8],
-                                                   float gx, float gy, int lane, bool v4) {
+                                                   float gx, float gy, int lane, bool v4, long long* fixed = nullptr,
+                                                   float fscale = 0.f) {
   // cell key: floor coordinates and the ceil-floor bits (scale < 65536 is checked on the host)
   const uint32_t k0 = (cl.f[0] & 0xffffu) | (cl.f[1] << 16);
   const uint32_t k1 = (cl.f[2] & 0xffffu) | ((cl.c[0] - cl.f[0]) << 16) | ((cl.c[1] - cl.f[1]) << 17) |
@@ -103,7 +121,7 @@ __device__ __forceinline__ void scatter_level_runs(float* base, const Cell& cl, 
       }
     }
   }
-  if (head) scatter_cell(base, cl, h, vx, vy, v4);
+  if (head) scatter_cell<FX>(base, cl, h, vx, vy, v4, fixed, fscale);
 }
 
 // Levels of at least this resolution pair their reductions (scatter_cell).  Pairing pays where the scatter is bound by

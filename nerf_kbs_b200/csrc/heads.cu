@@ -64,6 +64,7 @@ struct AssembleBwdArgs {
   const int64_t* cam;  // null -> no embedding gradient (eval)
   int cam_per_ray;
   float* demb;         // [num_images, emb_dim], accumulated into
+  FixedMap fm;         // deterministic mode (common.cuh): shadow of the buffer that holds demb, or a null map
 };
 
 __global__ void __launch_bounds__(kThreads) assemble_bwd_geo_kernel(const AssembleBwdArgs a) {
@@ -90,7 +91,7 @@ __global__ void __launch_bounds__(kThreads) assemble_bwd_emb_kernel(const Assemb
     float s = 0.f;
     for (int i = 0; i < G; ++i) s += src[(int64_t)i * W];
     int64_t ci = a.cam[g];
-    if (s != 0.f) atomicAdd(a.demb + ci * a.emb_dim + j, s);
+    if (s != 0.f) nkbs_acc(a.demb + ci * a.emb_dim + j, a.fm, s);
   }
 }
 
@@ -125,7 +126,7 @@ extern "C" int nkbs_assemble_bwd(int64_t N, int32_t S, int32_t sh_dim, int32_t g
                                  float* demb, void* stream) {
   NKBS_CHECK_ARG(N >= 0 && S >= 1 && dh, "nkbs_assemble_bwd: bad arguments");
   if (N == 0) return 0;
-  AssembleBwdArgs a{N, S, sh_dim, geo_dim, emb_dim, dh, dgeo, cam, cam_per_ray, demb};
+  AssembleBwdArgs a{N, S, sh_dim, geo_dim, emb_dim, dh, dgeo, cam, cam_per_ray, demb, nkbs_fixed_map_for(demb)};
   if (dgeo && geo_dim > 0) {
     assemble_bwd_geo_kernel<<<grid_for(N * geo_dim), kThreads, 0, (cudaStream_t)stream>>>(a);
     NKBS_CHECK_LAUNCH("nkbs_assemble_bwd(geo)");

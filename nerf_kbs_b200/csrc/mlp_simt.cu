@@ -35,6 +35,7 @@ struct MlpArgs {
   const float* dy;        // [N,Kn]
   const float* dy0;       // [N] or null: added to column 0 of dy
   float* dx;              // [N,K0] or null
+  FixedMap fm;            // backward, deterministic mode (common.cuh): shadow of the gradient buffer, or a null map
   int out_act;
   int64_t N;
   int w_floats;           // total floats of the weight arena
@@ -265,7 +266,8 @@ __device__ __forceinline__ void dense_bwd_weight(int K, int Npad, const float* _
   }
 }
 
-__device__ __forceinline__ void flush_weight_grad(const Layer& ly, const float accW[16], const float accB[4]) {
+__device__ __forceinline__ void flush_weight_grad(const Layer& ly, const FixedMap& fm, const float accW[16],
+                                                  const float accB[4]) {
   const int kb = threadIdx.x & 15, nb = threadIdx.x >> 4;
   const int k0 = kb * 4, n0 = nb * 4;
   if (k0 >= ly.K || n0 >= ly.N) return;
@@ -273,11 +275,11 @@ __device__ __forceinline__ void flush_weight_grad(const Layer& ly, const float a
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j)
-      if (k0 + i < ly.K && n0 + j < ly.N) atomicAdd(ly.dW + (size_t)(n0 + j) * ly.K + k0 + i, accW[i * 4 + j]);
+      if (k0 + i < ly.K && n0 + j < ly.N) nkbs_acc(ly.dW + (size_t)(n0 + j) * ly.K + k0 + i, fm, accW[i * 4 + j]);
   if (kb == 0) {
 #pragma unroll
     for (int j = 0; j < 4; ++j)
-      if (n0 + j < ly.N) atomicAdd(ly.db + n0 + j, accB[j]);
+      if (n0 + j < ly.N) nkbs_acc(ly.db + n0 + j, fm, accB[j]);
   }
 }
 
@@ -360,7 +362,7 @@ __global__ void __launch_bounds__(kThreads) mlp_bwd_kernel(const MlpArgs a) {
   }
 #pragma unroll
   for (int l = 0; l < kMaxLayers; ++l)
-    if (l < a.nl) flush_weight_grad(a.layer[l], accW[l], accB[l]);
+    if (l < a.nl) flush_weight_grad(a.layer[l], a.fm, accW[l], accB[l]);
 }
 
 int pick_nc(int n) {
@@ -384,6 +386,7 @@ int build_args(MlpArgs& a, int nl, const int32_t* dims, const float* const* W, c
     ly.b = b[l];
     ly.dW = nullptr;
     ly.db = nullptr;
+    a.fm = FixedMap{nullptr, nullptr, 0, 0.f};
     ly.K = dims[l];
     ly.N = dims[l + 1];
     ly.NC = pick_nc(ly.N);
@@ -445,6 +448,7 @@ extern "C" int nkbs_mlp_bwd(const float* x, const float* dy, int64_t N, int32_t 
     NKBS_CHECK_ARG(dW[l] && db[l], "nkbs_mlp_bwd: null dW/db for layer %d", l);
     a.layer[l].dW = dW[l];
     a.layer[l].db = db[l];
+    if (l == 0) a.fm = nkbs_fixed_map_for(dW[0]);
   }
   a.x = x;
   a.y = nullptr;

@@ -83,6 +83,8 @@ struct TcArgs {
   const float* dy;        // [N,Kn]   (backward)
   const float* dy0;       // [N] or null: added to column 0 of dy (gradient of y0)
   float* dx;              // [N,K0] or null (backward)
+  FixedMap fm;            // backward, deterministic mode (common.cuh): shadow of the buffer that holds dW / db, or a null map
+  FixedMap fm_emb;        // the same for the buffer that holds hin.demb
   int out_act;
   int fmt;                // 0 fp16, 1 bf16
   int64_t N;
@@ -975,7 +977,7 @@ __global__ void __launch_bounds__((NWG + 1) * kThreads, 1) mlp_tc_bwd_kernel(con
               if (lane_ < EMBD) {
                 float sum = 0.f;
                 for (int rr = lo; rr < hi; ++rr) sum += st[rr * stride + SHD + GEO + lane_];
-                if (sum != 0.f) atomicAdd(a.hin.demb + __ldg(a.hin.cam + g) * EMBD + lane_, sum);
+                if (sum != 0.f) nkbs_acc(a.hin.demb + __ldg(a.hin.cam + g) * EMBD + lane_, a.fm_emb, sum);
               }
             }
           }
@@ -1047,8 +1049,8 @@ __global__ void __launch_bounds__((NWG + 1) * kThreads, 1) mlp_tc_bwd_kernel(con
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
               int k = c0 + j;
-              if (k < ly.K) atomicAdd(ly.dW + (size_t)n * ly.K + k, v[j]);
-              else if (k == ly.K) atomicAdd(ly.db + n, v[j]);
+              if (k < ly.K) nkbs_acc(ly.dW + (size_t)n * ly.K + k, a.fm, v[j]);
+              else if (k == ly.K) nkbs_acc(ly.db + n, a.fm, v[j]);
             }
           }
         }
@@ -1079,6 +1081,7 @@ int build_args(TcArgs& a, bool backward, int nl, const int32_t* dims, const floa
     ly.b = b[l];
     ly.dW = nullptr;
     ly.db = nullptr;
+    a.fm = a.fm_emb = FixedMap{nullptr, nullptr, 0, 0.f};
     ly.K = dims[l];
     ly.N = dims[l + 1];
     ly.relu = (relu_mask >> l) & 1;
@@ -1341,6 +1344,7 @@ extern "C" int nkbs_mlp_tc_bwd(const float* x, const float* dy, int64_t N, int32
     NKBS_CHECK_ARG(dW[l] && db[l], "nkbs_mlp_tc_bwd: null dW/db for layer %d", l);
     a.layer[l].dW = dW[l];
     a.layer[l].db = db[l];
+    if (l == 0) a.fm = nkbs_fixed_map_for(dW[0]);
   }
   a.hin = HeadIn{};
   a.x = x;
@@ -1408,12 +1412,14 @@ extern "C" int nkbs_head_tc_bwd(int32_t sh_dim, int32_t geo_dim, int32_t emb_dim
     NKBS_CHECK_ARG(dW[l] && db[l], "nkbs_head_tc_bwd: null dW/db for layer %d", l);
     a.layer[l].dW = dW[l];
     a.layer[l].db = db[l];
+    if (l == 0) a.fm = nkbs_fixed_map_for(dW[0]);
   }
   NKBS_CHECK_ARG(dgeo_lead >= 0 && (!dgeo || dgeo_lead + geo_dim <= dgeo_stride), "nkbs_head_tc_bwd: bad dgeo_lead %d", dgeo_lead);
   a.hin.dgeo = dgeo;
   a.hin.dgeo_stride = dgeo_stride;
   a.hin.dgeo_lead = dgeo ? dgeo_lead : 0;
   a.hin.demb = a.hin.cam ? demb : nullptr;
+  a.fm_emb = nkbs_fixed_map_for(a.hin.demb);
   a.x = nullptr;
   a.y = nullptr;
   a.y0 = nullptr;

@@ -28,12 +28,12 @@ class ShardedAdam:
     process group and ``alloc=ShardedAdam.symmetric_alloc(...)`` so that ``P`` and ``G`` are peer-mapped."""
 
     @staticmethod
-    def make_arena(groups: Dict[str, Sequence[torch.nn.Parameter]], process_group=None) -> ParamArena:
+    def make_arena(groups: Dict[str, Sequence[torch.nn.Parameter]], process_group=None, deterministic: bool = False) -> ParamArena:
         import torch.distributed._symmetric_memory as symm_mem
         pg = process_group if process_group is not None else dist.group.WORLD
         dev = next(p for ps in groups.values() for p in ps).device
         return ParamArena(groups, world=dist.get_world_size(pg), rank=dist.get_rank(pg),
-                          alloc=lambda n: symm_mem.empty(n, dtype=torch.float32, device=dev))
+                          alloc=lambda n: symm_mem.empty(n, dtype=torch.float32, device=dev), deterministic=deterministic)
 
     def __init__(self, arena: ParamArena, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-15,
                  weight_decay: float = 0.0, process_group=None):
@@ -74,6 +74,9 @@ class ShardedAdam:
         active = list(active) if active is not None else list(self.layout)
         if not active:
             return
+        # deterministic mode: every rank's local sums are order-independent; the cross-rank sum is taken in rank order
+        # by the peer-load route (the in-switch multimem reduction has no documented order)
+        self.arena.flush_fixed(active)
         self.hG.barrier()  # every rank's gradients are complete and visible
         for name in active:
             lay = self.layout[name]

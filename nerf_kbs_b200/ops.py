@@ -26,7 +26,7 @@ def _zeros_like_many(tensors):
     for t, n in zip(tensors, sizes):
         out.append(flat[o:o + t.numel()].view(t.shape))
         o += n
-    return out
+    return out, flat
 
 
 def _sinks(params):
@@ -37,13 +37,40 @@ def _sinks(params):
     return sinks if sinks and all(s is not None for s in sinks) else None
 
 
+# Deterministic mode (optim.ParamArena(deterministic=True), include/nkbs.h: nkbs_fixed_point_register): gradient buffers
+# that are NOT views of the arena — parameters the model feeds through torch ops first, like the concatenated transient
+# heads — get a fixed-point shadow of their own for the duration of the backward call: registered here, folded into the
+# float buffer and unregistered by ``_finish_temps`` right after the kernel launches.
+_DET = {"count": 0, "log2_scale": 56}
+_TEMPS: List = []
+
+
+def deterministic_enabled() -> bool:
+    return _DET["count"] > 0
+
+
+def _temp_shadow(flat: torch.Tensor) -> None:
+    if _DET["count"] > 0 and flat is not None and flat.numel() > 0:
+        shadow = torch.zeros(flat.numel(), device=flat.device, dtype=torch.int64)
+        call("nkbs_fixed_point_register", flat.data_ptr(), flat.numel(), shadow.data_ptr(), _DET["log2_scale"])
+        _TEMPS.append((flat, shadow))
+
+
+def _finish_temps() -> None:
+    while _TEMPS:
+        flat, _shadow = _TEMPS.pop()
+        call("nkbs_fixed_point_flush", flat.data_ptr(), flat.numel(), stream())
+        call("nkbs_fixed_point_register", flat.data_ptr(), flat.numel(), None, 0)
+
+
 def _grad_buffers(sinks, like):
     """(buffers the backward kernel accumulates the parameter gradients into, what ``backward`` returns for them).
     With sinks the kernel adds into the step driver's buffer and autograd sees no gradient for the parameter (no
     fill launch, no AccumulateGrad); without, fresh zero-filled tensors are handed to autograd."""
     if sinks is not None:
         return list(sinks), [None] * len(sinks)
-    zs = _zeros_like_many(like)
+    zs, flat = _zeros_like_many(like)
+    _temp_shadow(flat)
     return zs, zs
 
 
@@ -144,9 +171,11 @@ class _HashEncode(torch.autograd.Function):
             p_st, p_en, bstride, _keep = rows(starts, ends)
             call("nkbs_encode_bwd_rays", R, S, ptr(origins), ptr(directions), p_st, p_en, bstride, int(norm.contraction),
                  host_floats(norm.aabb), ptr(dfeat), host_floats(g.scalings), g.L, g.log2_T, ptr(dtable), stream())
+            _finish_temps()
             return (ret,) + (None,) * 10
         call("nkbs_encode_bwd", ptr(xn), ptr(dfeat), xn.shape[0], host_floats(g.scalings), g.L, g.log2_T,
              g.features_per_level, ctx.dedup, ptr(dtable), stream())
+        _finish_temps()
         return (ret,) + (None,) * 10
 
 
@@ -216,8 +245,10 @@ def _density_backward(mode, x, origins, directions, p_st, p_en, bstride, R, S, n
         call("nkbs_density_bwd", *head, None, ptr(dW1), ptr(db1), ptr(dW2), ptr(db2), ptr(dfeat), stream())
         call("nkbs_encode_bwd_rays", R, S, ptr(origins), ptr(directions), p_st, p_en, bstride, int(norm.contraction),
              host_floats(norm.aabb), ptr(dfeat), host_floats(grid.scalings), grid.L, grid.log2_T, ptr(dtable), stream())
+        _finish_temps()
         return
     call("nkbs_density_bwd", *head, ptr(dtable), ptr(dW1), ptr(db1), ptr(dW2), ptr(db2), None, stream())
+    _finish_temps()
 
 
 class _FusedDensity(torch.autograd.Function):
@@ -342,6 +373,7 @@ class _Mlp(torch.autograd.Function):
         else:
             call("nkbs_mlp_bwd", ptr(x), ptr(dy), N, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask,
                  out_act, ptr(selector), ptr(dy0), ptr(dx), host_ptrs(dWs), host_ptrs(dbs), stream())
+        _finish_temps()
         grads = []
         for w, b in zip(ret[:nl], ret[nl:]):
             grads += [w, b]
@@ -363,8 +395,9 @@ def mlp(x, weights: Sequence[torch.Tensor], biases: Sequence[torch.Tensor], relu
 # ----------------------------------------------------------------------------------------------
 class _Assemble(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, geo, emb, emb_const, directions, cam, S, sh_dim, dir_per_ray, cam_per_ray):
+    def forward(ctx, geo, emb, emb_const, directions, cam, S, sh_dim, dir_per_ray, cam_per_ray, sink=None):
         geo = _c(geo)
+        ctx.sink = sink
         N, geo_dim = geo.shape
         emb_dim = emb.shape[1] if emb is not None else emb_const.shape[0]
         h = torch.empty((N, sh_dim + geo_dim + emb_dim), device=geo.device, dtype=torch.float32)
@@ -382,18 +415,23 @@ class _Assemble(torch.autograd.Function):
         (cam,) = ctx.saved_tensors
         dh = _c(dh)
         dgeo = torch.empty((N, geo_dim), device=dh.device, dtype=torch.float32) if ctx.needs_input_grad[0] else None
-        demb = None
+        demb, ret = None, None
         if use_cam and ctx.needs_input_grad[1]:
-            demb = torch.zeros(emb_shape, device=dh.device, dtype=torch.float32)
+            if ctx.sink is not None:  # the step driver's gradient arena (accumulated into; autograd sees no gradient)
+                demb = ctx.sink
+            else:
+                demb = ret = torch.zeros(emb_shape, device=dh.device, dtype=torch.float32)
+                _temp_shadow(ret)
         call("nkbs_assemble_bwd", N, S, sh_dim, geo_dim, emb_dim, ptr(dh), ptr(dgeo), ptr(cam) if demb is not None else None,
              int(cam_per_ray), ptr(demb), stream())
-        return dgeo, demb, None, None, None, None, None, None, None
+        _finish_temps()
+        return dgeo, ret, None, None, None, None, None, None, None, None
 
 
 def assemble(geo, emb_table, emb_const, directions, cam, S: int, sh_dim: int, dir_per_ray: bool, cam_per_ray: bool):
     """h = [SH16((d+1)/2) | geo | embedding[cam] or emb_const]; see nkbs_assemble_fwd."""
     return _Assemble.apply(geo, emb_table, emb_const, _c(directions), _c(cam, torch.int64), S, sh_dim, dir_per_ray,
-                           cam_per_ray)
+                           cam_per_ray, getattr(emb_table, "_nkbs_grad_sink", None) if emb_table is not None else None)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -456,6 +494,7 @@ class _HeadMlp(torch.autograd.Function):
                 demb = ctx.emb_sink
             else:
                 demb = demb_ret = torch.zeros(emb_shape, device=src.device, dtype=torch.float32)
+                _temp_shadow(demb_ret)
         zs, ret = _grad_buffers(ctx.sinks, Ws + bs)
         dWs, dbs = zs[:nl], zs[nl:]
         geo = src.reshape(-1)[col:]
@@ -464,6 +503,7 @@ class _HeadMlp(torch.autograd.Function):
              ptr(cam) if use_cam else None, int(cpr), ptr(emb) if use_cam else None, ptr(emb_const), S, ptr(dy), N, nl,
              host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask, out_act, bwd_fmt, ptr(dgeo), stride,
              col if (whole and dgeo is not None) else 0, ptr(demb), host_ptrs(dWs), host_ptrs(dbs), stream())
+        _finish_temps()
         grads = []
         for w, b in zip(ret[:nl], ret[nl:]):
             grads += [w, b]

@@ -105,9 +105,17 @@ class ParamArena:
     matching view of ``G`` for good, and ``p._nkbs_grad_sink`` tells the nkbs backward kernels to ACCUMULATE their
     parameter gradients straight into ``G`` (ops.py) instead of returning fresh zero-filled tensors to autograd: no
     fill launches, no AccumulateGrad copies, and the optimizer is one launch per group that re-zeroes ``G`` as it
-    reads it.  ``alloc(numel)`` lets the data-parallel step place the buffers in symmetric (peer-mapped) memory."""
+    reads it.  ``alloc(numel)`` lets the data-parallel step place the buffers in symmetric (peer-mapped) memory.
 
-    def __init__(self, groups: Dict[str, Sequence[torch.nn.Parameter]], world: int = 1, rank: int = 0, alloc=None):
+    ``deterministic``: the backward kernels add their partial sums to a 64-bit fixed-point shadow ``F`` of ``G``
+    (include/nkbs.h: nkbs_fixed_point_register; 2^log2_scale units per 1.0) instead of issuing float atomics, and
+    ``flush_fixed`` (called by the optimizers before they read ``G``) folds it into ``G``: the gradients, and with them
+    the whole training run, no longer depend on the arrival order of warps and CTAs.  8 more bytes per parameter; until
+    the flush ``p.grad`` does not hold the step's gradient.  ``log2_scale`` = 56: partial sums are kept to 1.4e-17
+    (70 times below Adam's eps of 1e-15) and a gradient element must stay below 128 in magnitude."""
+
+    def __init__(self, groups: Dict[str, Sequence[torch.nn.Parameter]], world: int = 1, rank: int = 0, alloc=None,
+                 deterministic: bool = False, log2_scale: int = 56):
         self.groups: Dict[str, List[torch.nn.Parameter]] = {k: [p for p in v if p.requires_grad] for k, v in groups.items()}
         first = next(p for ps in self.groups.values() for p in ps)
         dev = first.device
@@ -124,6 +132,13 @@ class ParamArena:
         self.P, self.G = alloc(self.total), alloc(self.total)
         self.P.zero_()
         self.G.zero_()
+        self.F = None
+        if deterministic:
+            self.F = torch.zeros(self.total, dtype=torch.int64, device=dev)
+            call("nkbs_fixed_point_register", self.G.data_ptr(), self.total, self.F.data_ptr(), int(log2_scale))
+            from . import ops
+            ops._DET["count"] += 1  # gradient buffers outside the arena get a shadow per backward call (ops._temp_shadow)
+            ops._DET["log2_scale"] = int(log2_scale)
         self.grad_view: Dict[int, torch.Tensor] = {}
         with torch.no_grad():
             for name, ps in self.groups.items():
@@ -140,8 +155,29 @@ class ParamArena:
         lay = self.layout[name]
         return buf[lay["start"]:lay["start"] + lay["len"]]
 
+    def flush_fixed(self, names: Optional[Sequence[str]] = None) -> None:
+        """Deterministic mode: fold the fixed-point shadow of the groups ``names`` (default all) into ``G``."""
+        if self.F is None:
+            return
+        for name in (names if names is not None else list(self.layout)):
+            lay = self.layout[name]
+            call("nkbs_fixed_point_flush", self.G.data_ptr() + lay["start"] * 4, lay["len"], stream())
+
+    def __del__(self):
+        # a registered buffer must not outlive its memory: later allocations could land inside the stale range
+        try:
+            if getattr(self, "F", None) is not None:
+                self.release()
+        except Exception:
+            pass
+
     def release(self) -> None:
         """Detach the parameters from the arena's gradient buffer (they keep their storage in ``P``)."""
+        if self.F is not None:
+            call("nkbs_fixed_point_register", self.G.data_ptr(), self.total, None, 0)
+            self.F = None
+            from . import ops
+            ops._DET["count"] -= 1
         for ps in self.groups.values():
             for p in ps:
                 if hasattr(p, "_nkbs_grad_sink"):
@@ -170,6 +206,7 @@ class ArenaAdam:
     def step(self, active: Optional[Sequence[str]] = None, inv_scale: Optional[torch.Tensor] = None,
              zero_grads: bool = True) -> None:
         a = self.arena
+        a.flush_fixed(active)
         for name in (active if active is not None else list(a.layout)):
             lay = a.layout[name]
             one = lambda x: (C.c_void_p * 1)(x)

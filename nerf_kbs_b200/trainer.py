@@ -84,11 +84,15 @@ class Trainer:
 
     def __init__(self, model, num_rays: int, lr: float = 1e-3, eps: float = 1e-15, betas=(0.9, 0.999),
                  use_graph: bool = True, process_group=None, graph_warmup: int = 3, seed: Optional[int] = None,
-                 fused_loss: Optional[bool] = None, inject_jitter: bool = False, keep_grads: bool = False):
+                 fused_loss: Optional[bool] = None, inject_jitter: bool = False, keep_grads: bool = False,
+                 deterministic: Optional[bool] = None):
         """``inject_jitter``: the per-ray jitter of the three sampling levels is an input of the step
         (``train_step(..., jitter=[t0, t1, t2])``, each [R,1]) instead of being drawn on the device — parity tests feed
         the oracle the same draws.  ``keep_grads``: debugging / tests — the optimizer leaves the gradients in the arena
-        (``p.grad`` readable after the step) and the step starts with a fill instead."""
+        (``p.grad`` readable after the step) and the step starts with a fill instead.  ``deterministic`` (default: env
+        ``NKBS_DETERMINISTIC=1``): parameter gradients are accumulated in 64-bit fixed point (optim.ParamArena), so a
+        step's result does not depend on the arrival order of warps / CTAs / streams — two runs from the same state
+        and inputs give the same bits; costs one flush pass over the shadow per optimizer step."""
         self.model = model
         # weighted total straight out of the loss kernel (models.get_loss_total); NKBS_FUSED_LOSS=0 keeps the loss-dict route
         self.fused_loss = (os.environ.get("NKBS_FUSED_LOSS", "1") != "0") if fused_loss is None else bool(fused_loss)
@@ -104,12 +108,13 @@ class Trainer:
         # several GPUs: reduce-scatter + Adam + all-gather fused over NVLink peer memory (dp_optim.py);
         # NKBS_DP_FUSED=0 keeps the NCCL allreduce + per-rank Adam route
         self.sharded, self.opt = None, None
+        self.deterministic = (os.environ.get("NKBS_DETERMINISTIC", "0") == "1") if deterministic is None else bool(deterministic)
         if self.world_size > 1 and os.environ.get("NKBS_DP_FUSED", "1") != "0":
             from .dp_optim import ShardedAdam
-            self.arena = ShardedAdam.make_arena(groups, process_group)
+            self.arena = ShardedAdam.make_arena(groups, process_group, deterministic=self.deterministic)
             self.sharded = ShardedAdam(self.arena, lr=lr, betas=betas, eps=eps, process_group=process_group)
         else:
-            self.arena = ParamArena(groups)
+            self.arena = ParamArena(groups, deterministic=self.deterministic)
             self.opt = ArenaAdam(self.arena, lr=lr, betas=betas, eps=eps)
         self.keep_grads = bool(keep_grads)
         # Deferred optimizer step of the "fields" group: its Adam (a 0.6 GB stream over the main table, gradient and
@@ -281,6 +286,8 @@ class Trainer:
     def zero_grad(self) -> None:
         """Zero the arena's gradient buffer (the step itself never needs this: the optimizer leaves it zeroed)."""
         self.arena.G.zero_()
+        if self.arena.F is not None:
+            self.arena.F.zero_()
 
     def active_groups(self, updated: bool) -> List[str]:
         """Parameter groups that receive gradients in a step: the proposal networks only when the sampler's
@@ -316,6 +323,7 @@ class Trainer:
             self.sharded.step(active)
             return
         if self.world_size > 1:
+            self.arena.flush_fixed(active)  # deterministic mode: the allreduce reads G
             for name in active:
                 dist.all_reduce(self.arena.group_slice(name, self.arena.G), op=dist.ReduceOp.SUM, group=self.group)
         self.opt.step(active, inv_scale=self._inv_world, zero_grads=not self.keep_grads)
