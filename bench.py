@@ -241,6 +241,8 @@ def kernel_work(name, a):
         # feature gradients in, every corner row of every sample scattered once (upper bound before the in-register merge)
         N, L = a[0] * a[1], a[11]
         return "hbm", N * (8 + 2 * L * 4 + 8 * L * 2 * 4)
+    if name == "nkbs_fixed_point_flush":  # deterministic mode: the 8-byte shadow is streamed once (writes are sparse)
+        return "hbm", a[1] * 8
     if name in ("nkbs_ray_losses", "nkbs_ray_losses_weighted"):
         R, S, n_prop = a[0], a[1], a[5]
         sp = list(a[6])[:n_prop]
