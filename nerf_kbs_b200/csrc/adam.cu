@@ -2,6 +2,7 @@
 // Replaces torch.optim.Adam(lr=1e-3, eps=1e-15) that the reference configures for both parameter
 // groups (ref:train.py:85-98; groups ref:nerfacto.py:359-363) [nerfstudio Optimizers, NS-recalled].
 // HBM streaming kernel: 4 words read + 3 written per parameter, 128-bit accesses.
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace {
@@ -53,6 +54,24 @@ __device__ __forceinline__ void advance_step(float* step_dev, unsigned* counter,
   }
 }
 
+// The denominator and the quotient with the hardware approximations (sqrt.approx, div.approx: <= 3 ulp on the update
+// term, which is ~lr relative to the parameter: the stored parameter differs from the IEEE kernel's by at most one ulp
+// on ~1/5 of the elements after 5 steps, 3e-8 relative L2).  The IEEE sequences cost ~50 instructions per element with
+// their range checks and slow paths and made the kernel issue-bound (issue slots 49 % busy at 58 % of DRAM throughput,
+// profiles/r02_top_kernels_ncu_full.csv): 108.5 -> 96.3 us on the main field's 16.8 M parameters (0.77 -> 0.87 of the
+// measured copy bandwidth, scripts/adam_bench.py).  NKBS_ADAM_IEEE=1 selects the IEEE kernel.
+__device__ __forceinline__ void adam_one_fast(float& p, float g, float& m, float& v, float b1, float b2, float eps,
+                                              float step_size, float inv_sqrt_bc2, float wd) {
+  if (wd != 0.f) g = fmaf(wd, p, g);
+  m = fmaf(b1, m, (1.f - b1) * g);
+  v = fmaf(b2, v, (1.f - b2) * g * g);
+  float r;
+  asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(v));
+  const float denom = fmaf(r, inv_sqrt_bc2, eps);
+  p -= step_size * __fdividef(m, denom);
+}
+
+template <bool FAST>
 __global__ void __launch_bounds__(kThreads) adam_kernel(const AdamArgs a) {
   int s = 0;
 #pragma unroll 1
@@ -63,7 +82,12 @@ __global__ void __launch_bounds__(kThreads) adam_kernel(const AdamArgs a) {
   const float bc2 = 1.f - powf(a.beta2, t);
   const float step_size = a.lr / bc1;
   const float sqrt_bc2 = sqrtf(bc2);
+  const float c2 = FAST ? 1.f / sqrt_bc2 : sqrt_bc2;  // what the per-element routine takes
   const float gs = a.inv_scale ? *a.inv_scale : 1.f;
+  auto one = [&](float& p, float g, float& m, float& v) {
+    if (FAST) adam_one_fast(p, g * gs, m, v, a.beta1, a.beta2, a.eps, step_size, c2, a.weight_decay);
+    else adam_one(p, g * gs, m, v, a.beta1, a.beta2, a.eps, step_size, c2, a.weight_decay);
+  };
   const int64_t base = (int64_t)(blockIdx.x - a.block_start[s]) * kPerBlock;
   const bool vec = ((reinterpret_cast<uintptr_t>(sg.p) | reinterpret_cast<uintptr_t>(sg.g) |
                      reinterpret_cast<uintptr_t>(sg.m) | reinterpret_cast<uintptr_t>(sg.v)) & 15) == 0;
@@ -75,10 +99,10 @@ __global__ void __launch_bounds__(kThreads) adam_kernel(const AdamArgs a) {
       float4 g = __ldcs(reinterpret_cast<const float4*>(sg.g + i));
       float4 m = *reinterpret_cast<float4*>(sg.m + i);
       float4 v = *reinterpret_cast<float4*>(sg.v + i);
-      adam_one(p.x, g.x * gs, m.x, v.x, a.beta1, a.beta2, a.eps, step_size, sqrt_bc2, a.weight_decay);
-      adam_one(p.y, g.y * gs, m.y, v.y, a.beta1, a.beta2, a.eps, step_size, sqrt_bc2, a.weight_decay);
-      adam_one(p.z, g.z * gs, m.z, v.z, a.beta1, a.beta2, a.eps, step_size, sqrt_bc2, a.weight_decay);
-      adam_one(p.w, g.w * gs, m.w, v.w, a.beta1, a.beta2, a.eps, step_size, sqrt_bc2, a.weight_decay);
+      one(p.x, g.x, m.x, v.x);
+      one(p.y, g.y, m.y, v.y);
+      one(p.z, g.z, m.z, v.z);
+      one(p.w, g.w, m.w, v.w);
       *reinterpret_cast<float4*>(sg.p + i) = p;
       *reinterpret_cast<float4*>(sg.m + i) = m;
       *reinterpret_cast<float4*>(sg.v + i) = v;
@@ -88,7 +112,7 @@ __global__ void __launch_bounds__(kThreads) adam_kernel(const AdamArgs a) {
     int64_t end = base + kPerBlock < sg.n ? base + kPerBlock : sg.n;
     for (int64_t i = base + threadIdx.x; i < end; i += kThreads) {
       float p = sg.p[i], m = sg.m[i], v = sg.v[i];
-      adam_one(p, sg.g[i] * gs, m, v, a.beta1, a.beta2, a.eps, step_size, sqrt_bc2, a.weight_decay);
+      one(p, sg.g[i], m, v);
       sg.p[i] = p;
       sg.m[i] = m;
       sg.v[i] = v;
@@ -280,7 +304,9 @@ extern "C" int nkbs_adam_step(int32_t num_tensors, float* const* params, float* 
     a.inv_scale = inv_scale_dev;
     a.zero_grads = zero_grads;
     a.counter = step_counter;
-    adam_kernel<<<blocks, kThreads, 0, (cudaStream_t)stream>>>(a);
+    const char* ev = getenv("NKBS_ADAM_IEEE");
+    if (ev && ev[0] == '1') adam_kernel<false><<<blocks, kThreads, 0, (cudaStream_t)stream>>>(a);
+    else adam_kernel<true><<<blocks, kThreads, 0, (cudaStream_t)stream>>>(a);
     NKBS_CHECK_LAUNCH("nkbs_adam_step");
   }
   return 0;

@@ -13,7 +13,10 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda"
 
 
-def test_adam_matches_torch_adam():
+@pytest.mark.parametrize("ieee", ["0", "1"])
+def test_adam_matches_torch_adam(ieee, monkeypatch):
+    """Default kernel (hardware sqrt / division approximations on the update term) and the IEEE one."""
+    monkeypatch.setenv("NKBS_ADAM_IEEE", ieee)
     g = torch.Generator().manual_seed(0)
     shapes = [(4096 * 3 + 5, 2), (64, 32), (16,), (1,), (300, 7)]
     ref = [torch.nn.Parameter(torch.randn(s, generator=g)) for s in shapes]
