@@ -1,5 +1,6 @@
 // C-ABI plumbing shared by every entry point: version, per-thread error string, device query.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 #include <mutex>
 #include <vector>
@@ -28,6 +29,14 @@ int nkbs_num_sms() {
     cached_sms = sms;
   }
   return cached_sms;
+}
+
+bool nkbs_pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("NKBS_PDL");
+    return e && e[0] == '1';
+  }();
+  return on;
 }
 
 extern "C" int nkbs_version(void) { return NKBS_VERSION; }
@@ -72,6 +81,7 @@ extern "C" int nkbs_fixed_point_register(float* base, int64_t n, int64_t* shadow
 // Mostly-zero input (a step touches a few percent of a hash table): 16-byte loads, four in flight per thread, and the
 // float buffer / the shadow are only written where the shadow is not zero.
 __global__ void __launch_bounds__(256) fixed_point_flush_kernel(long long* acc, float* dst, int64_t n, double inv_scale) {
+  nkbs_pdl_sync();
   const int64_t pairs = n >> 1, stride = (int64_t)gridDim.x * blockDim.x;
   longlong2* acc2 = reinterpret_cast<longlong2*>(acc);
   for (int64_t i0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i0 < pairs; i0 += 4 * stride) {
@@ -108,7 +118,7 @@ extern "C" int nkbs_fixed_point_flush(float* dst, int64_t n, void* stream) {
                      (reinterpret_cast<uintptr_t>(fm.shadow) & 15u) == 0,
                  "nkbs_fixed_point_flush: dst must start an even number of elements into a 16-byte aligned shadow and be 8-byte aligned");
   const int64_t blocks = (n / 8 + 255) / 256 + 1, cap = (int64_t)nkbs_num_sms() * 8;
-  fixed_point_flush_kernel<<<(int)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>(
+  nkbs_launch(fixed_point_flush_kernel, (int)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream, 
       fm.shadow + (dst - fm.base), dst, n, 1.0 / (double)fm.scale);
   NKBS_CHECK_LAUNCH("nkbs_fixed_point_flush");
   return 0;

@@ -73,6 +73,7 @@ __device__ __forceinline__ void adam_one_fast(float& p, float g, float& m, float
 
 template <bool FAST>
 __global__ void __launch_bounds__(kThreads) adam_kernel(const AdamArgs a) {
+  nkbs_pdl_sync();
   int s = 0;
 #pragma unroll 1
   while (s + 1 < a.nseg && (int)blockIdx.x >= a.block_start[s + 1]) ++s;
@@ -147,6 +148,7 @@ struct DpAdamArgs {
 // (NVLink round trips are ~2 us: the loop over ranks must not serialise them); WORLD = 0: any rank count.
 template <int WORLD>
 __global__ void __launch_bounds__(kThreads) dp_adam_kernel(const DpAdamArgs a) {
+  nkbs_pdl_sync();
   const float t = a.counter ? *a.step_dev + 1.f : *a.step_dev;
   const float bc1 = 1.f - powf(a.beta1, t);
   const float bc2 = 1.f - powf(a.beta2, t);
@@ -221,6 +223,7 @@ __device__ __forceinline__ void multimem_st(float* mc, float4 v) {
 }
 
 __global__ void __launch_bounds__(kThreads) dp_adam_multimem_kernel(const DpAdamArgs a) {
+  nkbs_pdl_sync();
   const float t = a.counter ? *a.step_dev + 1.f : *a.step_dev;
   const float bc1 = 1.f - powf(a.beta1, t);
   const float bc2 = 1.f - powf(a.beta2, t);
@@ -305,8 +308,8 @@ extern "C" int nkbs_adam_step(int32_t num_tensors, float* const* params, float* 
     a.zero_grads = zero_grads;
     a.counter = step_counter;
     const char* ev = getenv("NKBS_ADAM_IEEE");
-    if (ev && ev[0] == '1') adam_kernel<false><<<blocks, kThreads, 0, (cudaStream_t)stream>>>(a);
-    else adam_kernel<true><<<blocks, kThreads, 0, (cudaStream_t)stream>>>(a);
+    if (ev && ev[0] == '1') nkbs_launch(adam_kernel<false>, blocks, kThreads, 0, (cudaStream_t)stream, a);
+    else nkbs_launch(adam_kernel<true>, blocks, kThreads, 0, (cudaStream_t)stream, a);
     NKBS_CHECK_LAUNCH("nkbs_adam_step");
   }
   return 0;
@@ -351,15 +354,15 @@ extern "C" int nkbs_dp_adam_step(int32_t world, int32_t rank, const float* const
   const int grid = (int)(blocks < cap ? blocks : cap);
   cudaStream_t st = (cudaStream_t)stream;
   if (a.g_mc) {
-    dp_adam_multimem_kernel<<<grid, kThreads, 0, st>>>(a);
+    nkbs_launch(dp_adam_multimem_kernel, grid, kThreads, 0, st, a);
     NKBS_CHECK_LAUNCH("nkbs_dp_adam_step(multimem)");
     return 0;
   }
   switch (world) {
-    case 2: dp_adam_kernel<2><<<grid, kThreads, 0, st>>>(a); break;
-    case 4: dp_adam_kernel<4><<<grid, kThreads, 0, st>>>(a); break;
-    case 8: dp_adam_kernel<8><<<grid, kThreads, 0, st>>>(a); break;
-    default: dp_adam_kernel<0><<<grid, kThreads, 0, st>>>(a); break;
+    case 2: nkbs_launch(dp_adam_kernel<2>, grid, kThreads, 0, st, a); break;
+    case 4: nkbs_launch(dp_adam_kernel<4>, grid, kThreads, 0, st, a); break;
+    case 8: nkbs_launch(dp_adam_kernel<8>, grid, kThreads, 0, st, a); break;
+    default: nkbs_launch(dp_adam_kernel<0>, grid, kThreads, 0, st, a); break;
   }
   NKBS_CHECK_LAUNCH("nkbs_dp_adam_step");
   return 0;

@@ -82,6 +82,7 @@ __device__ __forceinline__ float nan_to_num(float w) {
 }
 
 __global__ void __launch_bounds__(kThreads) composite_fwd_kernel(const CompArgs a) {
+  nkbs_pdl_sync();
   extern __shared__ float s_w[];  // [kWarpsPerCta][strip (+ S + 1 floats of cdf when resampling)]
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int S = a.S;
@@ -235,12 +236,14 @@ __global__ void __launch_bounds__(kThreads) composite_fwd_kernel(const CompArgs 
 }
 
 __global__ void minmax_init_kernel(int* mm) {
+  nkbs_pdl_sync();
   mm[0] = float_key(FLT_MAX);
   mm[1] = float_key(-FLT_MAX);
 }
 
 // depth = clip(raw, steps.min(), steps.max()); mask = 1 where the clip passed the value through
 __global__ void clip_depth_kernel(const float* raw, const int* mm, int64_t R, float* out, float* mask) {
+  nkbs_pdl_sync();
   float lo = key_float(mm[0]), hi = key_float(mm[1]);
   for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < R; r += (int64_t)gridDim.x * blockDim.x) {
     float v = raw[r];
@@ -278,6 +281,7 @@ struct CompBwdArgs {
 };
 
 __global__ void __launch_bounds__(kThreads) composite_bwd_kernel(const CompBwdArgs a) {
+  nkbs_pdl_sync();
   extern __shared__ float s_buf[];  // [kWarpsPerCta][3][S]: weights, dL/dw, exp(-incl)
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int S = a.S;
@@ -413,12 +417,12 @@ extern "C" int nkbs_composite_fwd(int64_t R, int32_t S, const float* density, co
              weights, rgb_out, acc_out, depth_exp_raw, depth_med, sem_out, depth_exp ? minmax_ws : nullptr};
   a.pdf_nb = 0;
   a.pdf_anneal_dev = nullptr;
-  if (depth_exp) minmax_init_kernel<<<1, 1, 0, st>>>(minmax_ws);
+  if (depth_exp) nkbs_launch(minmax_init_kernel, 1, 1, 0, st, minmax_ws);
   size_t smem = (size_t)kWarpsPerCta * strip_len(S) * sizeof(float);
-  composite_fwd_kernel<<<comp_grid(R), kThreads, smem, st>>>(a);
+  nkbs_launch(composite_fwd_kernel, comp_grid(R), kThreads, smem, st, a);
   NKBS_CHECK_LAUNCH("nkbs_composite_fwd");
   if (depth_exp) {
-    clip_depth_kernel<<<(int)((R + 255) / 256), 256, 0, st>>>(depth_exp_raw, minmax_ws, R, depth_exp, depth_mask);
+    nkbs_launch(clip_depth_kernel, (int)((R + 255) / 256), 256, 0, st, depth_exp_raw, minmax_ws, R, depth_exp, depth_mask);
     NKBS_CHECK_LAUNCH("nkbs_composite_fwd(clip)");
   }
   return 0;
@@ -447,7 +451,7 @@ extern "C" int nkbs_composite_bwd(int64_t R, int32_t S, const float* density, co
     cudaError_t e = cudaFuncSetAttribute(composite_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     NKBS_CHECK_ARG(e == cudaSuccess, "nkbs_composite_bwd: %zu bytes of shared memory refused (%s)", smem, cudaGetErrorString(e));
   }
-  composite_bwd_kernel<<<comp_grid(R), kThreads, smem, (cudaStream_t)stream>>>(a);
+  nkbs_launch(composite_bwd_kernel, comp_grid(R), kThreads, smem, (cudaStream_t)stream, a);
   NKBS_CHECK_LAUNCH("nkbs_composite_bwd");
   return 0;
 }
@@ -506,11 +510,11 @@ extern "C" int nkbs_expected_depth_noalloc(int64_t R, int32_t S, const float* we
              nullptr, nullptr, nullptr, raw, nullptr, nullptr, mm};
   a.pdf_nb = 0;
   a.pdf_anneal_dev = nullptr;
-  minmax_init_kernel<<<1, 1, 0, st>>>(mm);
+  nkbs_launch(minmax_init_kernel, 1, 1, 0, st, mm);
   const size_t smem = (size_t)kWarpsPerCta * strip_len(S) * sizeof(float);
-  composite_fwd_kernel<<<comp_grid(R), kThreads, smem, st>>>(a);
+  nkbs_launch(composite_fwd_kernel, comp_grid(R), kThreads, smem, st, a);
   NKBS_CHECK_LAUNCH("nkbs_expected_depth_noalloc");
-  clip_depth_kernel<<<(int)((R + 255) / 256), 256, 0, st>>>(raw, mm, R, depth, nullptr);
+  nkbs_launch(clip_depth_kernel, (int)((R + 255) / 256), 256, 0, st, raw, mm, R, depth, nullptr);
   NKBS_CHECK_LAUNCH("nkbs_expected_depth_noalloc(clip)");
   return 0;
 }
@@ -541,7 +545,7 @@ extern "C" int nkbs_weights_resample_fwd(int64_t R, int32_t S, const float* dens
   a.pdf_out_sbins = out_sbins;
   a.pdf_out_ebins = out_ebins;
   const size_t smem = (size_t)kWarpsPerCta * (strip_len(S) + S + 1) * sizeof(float);
-  composite_fwd_kernel<<<comp_grid(R), kThreads, smem, (cudaStream_t)stream>>>(a);
+  nkbs_launch(composite_fwd_kernel, comp_grid(R), kThreads, smem, (cudaStream_t)stream, a);
   NKBS_CHECK_LAUNCH("nkbs_weights_resample_fwd");
   return 0;
 }

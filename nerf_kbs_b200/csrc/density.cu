@@ -112,6 +112,7 @@ __device__ __forceinline__ float hidden_pre(const Smem<H, L>& s, const float (&f
 
 template <int H, int L>
 __global__ void __launch_bounds__(kThreads) density_fwd_kernel(const DensityArgs a) {
+  nkbs_pdl_sync();
   __shared__ float s_scale[NKBS_MAX_LEVELS];
   __shared__ __align__(16) Smem<H, L> s;
   if (threadIdx.x < NKBS_MAX_LEVELS) s_scale[threadIdx.x] = a.lv.scale[threadIdx.x];
@@ -224,6 +225,7 @@ constexpr int bwd_ctas() { return H <= 16 ? NKBS_DENSITY_BWD_CTAS : 1; }
 
 template <int H, int L, bool FX>
 __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(const DensityArgs a) {
+  nkbs_pdl_sync();
   constexpr int K = 2 * L, KP = Smem<H, L>::KP;
   // gradient rows, in this order: for each hidden unit j: dW1[j][0..K), db1[j], dW2[j]; then db2
   constexpr int kPerJ = K + 2;
@@ -603,6 +605,7 @@ __device__ __forceinline__ float lvl_nan_to_num(float w) {
 // G rays per group, W >= G warps per CTA: all W warps evaluate the field, warps 0..G-1 then own one ray each
 template <int H, int L, int G, int W>
 __global__ void __launch_bounds__(32 * W) proposal_level_fwd_kernel(const LevelArgs a) {
+  nkbs_pdl_sync();
   __shared__ float s_scale[NKBS_MAX_LEVELS];
   __shared__ __align__(16) Smem<H, L> s;
   extern __shared__ float s_dyn[];
@@ -751,9 +754,9 @@ extern "C" int nkbs_density_fwd(int32_t mode, const float* x, const float* origi
   a.density = density;
   cudaStream_t st = (cudaStream_t)stream;
   if (H == 16)
-    density_fwd_kernel<16, 5><<<grid_for(density_fwd_kernel<16, 5>, a.N), kThreads, 0, st>>>(a);
+    nkbs_launch(density_fwd_kernel<16, 5>, grid_for(density_fwd_kernel<16, 5>, a.N), kThreads, 0, st, a);
   else
-    density_fwd_kernel<64, 8><<<grid_for(density_fwd_kernel<64, 8>, a.N), kThreads, 0, st>>>(a);
+    nkbs_launch(density_fwd_kernel<64, 8>, grid_for(density_fwd_kernel<64, 8>, a.N), kThreads, 0, st, a);
   NKBS_CHECK_LAUNCH("nkbs_density_fwd");
   return 0;
 }
@@ -786,8 +789,8 @@ extern "C" int nkbs_density_bwd(int32_t mode, const float* x, const float* origi
   if (H == 16) {
     constexpr size_t smem = (size_t)kWarps * MmaGeom<16, 5>::kScratch * sizeof(float);
     static_assert(smem <= 48 * 1024, "default dynamic shared memory limit");
-    if (a.fm.shadow) density_bwd_kernel<16, 5, true><<<grid_for(density_bwd_kernel<16, 5, true>, a.N, smem), kThreads, smem, st>>>(a);
-    else density_bwd_kernel<16, 5, false><<<grid_for(density_bwd_kernel<16, 5, false>, a.N, smem), kThreads, smem, st>>>(a);
+    if (a.fm.shadow) nkbs_launch(density_bwd_kernel<16, 5, true>, grid_for(density_bwd_kernel<16, 5, true>, a.N, smem), kThreads, smem, st, a);
+    else nkbs_launch(density_bwd_kernel<16, 5, false>, grid_for(density_bwd_kernel<16, 5, false>, a.N, smem), kThreads, smem, st, a);
   } else {
     constexpr size_t smem = (size_t)kWarps * MmaGeom<64, 8>::kScratch * sizeof(float);
     if (smem > 48 * 1024) {
@@ -795,8 +798,8 @@ extern "C" int nkbs_density_bwd(int32_t mode, const float* x, const float* origi
       if (e == cudaSuccess) e = cudaFuncSetAttribute(density_bwd_kernel<64, 8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       NKBS_CHECK_ARG(e == cudaSuccess, "nkbs_density_bwd: %zu bytes of shared memory refused (%s)", smem, cudaGetErrorString(e));
     }
-    if (a.fm.shadow) density_bwd_kernel<64, 8, true><<<grid_for(density_bwd_kernel<64, 8, true>, a.N, smem), kThreads, smem, st>>>(a);
-    else density_bwd_kernel<64, 8, false><<<grid_for(density_bwd_kernel<64, 8, false>, a.N, smem), kThreads, smem, st>>>(a);
+    if (a.fm.shadow) nkbs_launch(density_bwd_kernel<64, 8, true>, grid_for(density_bwd_kernel<64, 8, true>, a.N, smem), kThreads, smem, st, a);
+    else nkbs_launch(density_bwd_kernel<64, 8, false>, grid_for(density_bwd_kernel<64, 8, false>, a.N, smem), kThreads, smem, st, a);
   }
   NKBS_CHECK_LAUNCH("nkbs_density_bwd");
   return 0;
@@ -858,7 +861,7 @@ extern "C" int nkbs_proposal_level_fwd(int64_t R, int32_t S, const float* origin
       cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       NKBS_CHECK_ARG(e == cudaSuccess, "nkbs_proposal_level_fwd: %zu bytes of shared memory refused (%s)", smem, cudaGetErrorString(e));
     }
-    kernel<<<grid, 32 * Wn, smem, st>>>(a);
+    nkbs_launch(kernel, grid, 32 * Wn, smem, st, a);
     return 0;
   };
   int rc;

@@ -27,6 +27,7 @@ struct EncodeArgs : SampleSource {
 // the compiler overlaps two levels (unroll 2).  Level scales live in shared memory.
 template <bool kWriteIdx>
 __global__ void __launch_bounds__(kEncThreads) encode_fwd_kernel(const EncodeArgs a) {
+  nkbs_pdl_sync();
   __shared__ float s_scale[NKBS_MAX_LEVELS];
   if (threadIdx.x < NKBS_MAX_LEVELS) s_scale[threadIdx.x] = a.lv.scale[threadIdx.x];
   __syncthreads();
@@ -100,6 +101,7 @@ struct EncodeBwdArgs {
 
 template <bool FX>
 __global__ void __launch_bounds__(kEncThreads) encode_bwd_kernel(const EncodeBwdArgs a) {
+  nkbs_pdl_sync();
   __shared__ float s_scale[NKBS_MAX_LEVELS];
   if (threadIdx.x < NKBS_MAX_LEVELS) s_scale[threadIdx.x] = a.lv.scale[threadIdx.x];
   __syncthreads();
@@ -156,6 +158,7 @@ struct RayScatterArgs : SampleSource {
 
 template <int CMAX, bool FX>
 __global__ void __launch_bounds__(kEncThreads) encode_bwd_rays_kernel(const RayScatterArgs a) {
+  nkbs_pdl_sync();
   __shared__ float s_scale[NKBS_MAX_LEVELS];
   if (threadIdx.x < NKBS_MAX_LEVELS) s_scale[threadIdx.x] = a.lv.scale[threadIdx.x];
   __syncthreads();
@@ -286,9 +289,9 @@ extern "C" int nkbs_encode_fwd(int mode, const float* x, const float* origins, c
   int grid = (int)(blocks < cap ? blocks : cap);
   const dim3 grid2(grid, level_slices(blocks, L));
   if (indices)
-    encode_fwd_kernel<true><<<grid2, kEncThreads, 0, (cudaStream_t)stream>>>(a);
+    nkbs_launch(encode_fwd_kernel<true>, grid2, kEncThreads, 0, (cudaStream_t)stream, a);
   else
-    encode_fwd_kernel<false><<<grid2, kEncThreads, 0, (cudaStream_t)stream>>>(a);
+    nkbs_launch(encode_fwd_kernel<false>, grid2, kEncThreads, 0, (cudaStream_t)stream, a);
   NKBS_CHECK_LAUNCH("nkbs_encode_fwd");
   return 0;
 }
@@ -312,8 +315,8 @@ extern "C" int nkbs_encode_bwd(const float* xn, const float* dfeat, int64_t N, c
   int64_t blocks = (N + kEncThreads - 1) / kEncThreads;
   int64_t cap = (int64_t)nkbs_num_sms() * 32;
   int grid = (int)(blocks < cap ? blocks : cap);
-  if (a.fm.shadow) encode_bwd_kernel<true><<<dim3(grid, level_slices(blocks, L)), kEncThreads, 0, (cudaStream_t)stream>>>(a);
-  else encode_bwd_kernel<false><<<dim3(grid, level_slices(blocks, L)), kEncThreads, 0, (cudaStream_t)stream>>>(a);
+  if (a.fm.shadow) nkbs_launch(encode_bwd_kernel<true>, dim3(grid, level_slices(blocks, L)), kEncThreads, 0, (cudaStream_t)stream, a);
+  else nkbs_launch(encode_bwd_kernel<false>, dim3(grid, level_slices(blocks, L)), kEncThreads, 0, (cudaStream_t)stream, a);
   NKBS_CHECK_LAUNCH("nkbs_encode_bwd");
   return 0;
 }
@@ -354,13 +357,13 @@ extern "C" int nkbs_encode_bwd_rays(int64_t R, int32_t S, const float* origins, 
   const int grid = (int)(blocks < cap ? blocks : cap);
   cudaStream_t st = (cudaStream_t)stream;
   if (a.fm.shadow) {
-    if (S <= 64) encode_bwd_rays_kernel<2, true><<<grid, kEncThreads, 0, st>>>(a);
-    else if (S <= 128) encode_bwd_rays_kernel<4, true><<<grid, kEncThreads, 0, st>>>(a);
-    else encode_bwd_rays_kernel<8, true><<<grid, kEncThreads, 0, st>>>(a);
+    if (S <= 64) nkbs_launch(encode_bwd_rays_kernel<2, true>, grid, kEncThreads, 0, st, a);
+    else if (S <= 128) nkbs_launch(encode_bwd_rays_kernel<4, true>, grid, kEncThreads, 0, st, a);
+    else nkbs_launch(encode_bwd_rays_kernel<8, true>, grid, kEncThreads, 0, st, a);
   } else {
-    if (S <= 64) encode_bwd_rays_kernel<2, false><<<grid, kEncThreads, 0, st>>>(a);
-    else if (S <= 128) encode_bwd_rays_kernel<4, false><<<grid, kEncThreads, 0, st>>>(a);
-    else encode_bwd_rays_kernel<8, false><<<grid, kEncThreads, 0, st>>>(a);
+    if (S <= 64) nkbs_launch(encode_bwd_rays_kernel<2, false>, grid, kEncThreads, 0, st, a);
+    else if (S <= 128) nkbs_launch(encode_bwd_rays_kernel<4, false>, grid, kEncThreads, 0, st, a);
+    else nkbs_launch(encode_bwd_rays_kernel<8, false>, grid, kEncThreads, 0, st, a);
   }
   NKBS_CHECK_LAUNCH("nkbs_encode_bwd_rays");
   return 0;

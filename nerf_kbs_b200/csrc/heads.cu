@@ -28,6 +28,7 @@ struct AssembleArgs {
 };
 
 __global__ void __launch_bounds__(kThreads) assemble_fwd_kernel(const AssembleArgs a) {
+  nkbs_pdl_sync();
   const int W = a.sh_dim + a.geo_dim + a.emb_dim;
   const int64_t total = a.N * W;
   for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
@@ -68,6 +69,7 @@ struct AssembleBwdArgs {
 };
 
 __global__ void __launch_bounds__(kThreads) assemble_bwd_geo_kernel(const AssembleBwdArgs a) {
+  nkbs_pdl_sync();
   const int W = a.sh_dim + a.geo_dim + a.emb_dim;
   const int64_t total = a.N * a.geo_dim;
   for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
@@ -80,6 +82,7 @@ __global__ void __launch_bounds__(kThreads) assemble_bwd_geo_kernel(const Assemb
 // one thread per (group, column): a group is the S samples of one ray when the camera index is per
 // ray (they share the embedding row), so the row receives one reduction per ray instead of S.
 __global__ void __launch_bounds__(kThreads) assemble_bwd_emb_kernel(const AssembleBwdArgs a) {
+  nkbs_pdl_sync();
   const int W = a.sh_dim + a.geo_dim + a.emb_dim;
   const int G = a.cam_per_ray ? a.S : 1;
   const int64_t groups = a.N / G;
@@ -116,7 +119,7 @@ extern "C" int nkbs_assemble_fwd(int64_t N, int32_t S, int32_t sh_dim, int32_t g
   NKBS_CHECK_ARG(!(dir_per_ray || cam_per_ray) || N % S == 0, "nkbs_assemble_fwd: N not a multiple of S");
   if (N == 0) return 0;
   AssembleArgs a{N, S, sh_dim, geo_dim, emb_dim, directions, dir_per_ray, geo, cam, cam_per_ray, emb, emb_const, num_images, h};
-  assemble_fwd_kernel<<<grid_for(N * (sh_dim + geo_dim + emb_dim)), kThreads, 0, (cudaStream_t)stream>>>(a);
+  nkbs_launch(assemble_fwd_kernel, grid_for(N * (sh_dim + geo_dim + emb_dim)), kThreads, 0, (cudaStream_t)stream, a);
   NKBS_CHECK_LAUNCH("nkbs_assemble_fwd");
   return 0;
 }
@@ -128,13 +131,13 @@ extern "C" int nkbs_assemble_bwd(int64_t N, int32_t S, int32_t sh_dim, int32_t g
   if (N == 0) return 0;
   AssembleBwdArgs a{N, S, sh_dim, geo_dim, emb_dim, dh, dgeo, cam, cam_per_ray, demb, nkbs_fixed_map_for(demb)};
   if (dgeo && geo_dim > 0) {
-    assemble_bwd_geo_kernel<<<grid_for(N * geo_dim), kThreads, 0, (cudaStream_t)stream>>>(a);
+    nkbs_launch(assemble_bwd_geo_kernel, grid_for(N * geo_dim), kThreads, 0, (cudaStream_t)stream, a);
     NKBS_CHECK_LAUNCH("nkbs_assemble_bwd(geo)");
   }
   if (cam && demb && emb_dim > 0) {
     NKBS_CHECK_ARG(!cam_per_ray || N % S == 0, "nkbs_assemble_bwd: N not a multiple of S");
     int64_t groups = cam_per_ray ? N / S : N;
-    assemble_bwd_emb_kernel<<<grid_for(groups * emb_dim), kThreads, 0, (cudaStream_t)stream>>>(a);
+    nkbs_launch(assemble_bwd_emb_kernel, grid_for(groups * emb_dim), kThreads, 0, (cudaStream_t)stream, a);
     NKBS_CHECK_LAUNCH("nkbs_assemble_bwd(emb)");
   }
   return 0;

@@ -77,6 +77,7 @@ __device__ __forceinline__ int upper_bound(const float* a, int n, float v) {
 }
 
 __global__ void __launch_bounds__(kThreads) ray_losses_kernel(const LossArgs a, int smax) {
+  nkbs_pdl_sync();
   extern __shared__ float s_all[];
   __shared__ float s_out[5];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -295,7 +296,7 @@ static int ray_losses_launch(int64_t R, int32_t S, const float* sdist, const flo
   int64_t blocks = (R + kWarpsPerCta - 1) / kWarpsPerCta;
   int64_t cap = (int64_t)nkbs_num_sms() * 8;
   int grid = (int)(blocks < cap ? blocks : cap);
-  ray_losses_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(a, smax);
+  nkbs_launch(ray_losses_kernel, grid, kThreads, smem, (cudaStream_t)stream, a, smax);
   NKBS_CHECK_LAUNCH("nkbs_ray_losses");
   return 0;
 }

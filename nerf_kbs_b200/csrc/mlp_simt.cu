@@ -155,6 +155,7 @@ __device__ __forceinline__ float out_act_grad(int act, int n, float raw, float s
 }
 
 __global__ void __launch_bounds__(kThreads) mlp_fwd_kernel(const MlpArgs a) {
+  nkbs_pdl_sync();
   extern __shared__ __align__(16) float smem[];
   float* sw = smem;
   float* buf0 = smem + a.w_floats;
@@ -284,6 +285,7 @@ __device__ __forceinline__ void flush_weight_grad(const Layer& ly, const FixedMa
 }
 
 __global__ void __launch_bounds__(kThreads) mlp_bwd_kernel(const MlpArgs a) {
+  nkbs_pdl_sync();
   extern __shared__ __align__(16) float smem[];
   float* sw = smem;
   float* acts[kMaxLayers];
@@ -430,7 +432,7 @@ extern "C" int nkbs_mlp_fwd(const float* x, int64_t N, int32_t nl, const int32_t
   int64_t ntiles = (N + kTile - 1) / kTile;
   int64_t cap = (int64_t)nkbs_num_sms() * 2;
   int grid = (int)(ntiles < cap ? ntiles : cap);
-  mlp_fwd_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(a);
+  nkbs_launch(mlp_fwd_kernel, grid, kThreads, smem, (cudaStream_t)stream, a);
   NKBS_CHECK_LAUNCH("nkbs_mlp_fwd");
   return 0;
 }
@@ -468,7 +470,7 @@ extern "C" int nkbs_mlp_bwd(const float* x, const float* dy, int64_t N, int32_t 
   int64_t ntiles = (N + kTile - 1) / kTile;
   int64_t cap = (int64_t)nkbs_num_sms();
   int grid = (int)(ntiles < cap ? ntiles : cap);
-  mlp_bwd_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(a);
+  nkbs_launch(mlp_bwd_kernel, grid, kThreads, smem, (cudaStream_t)stream, a);
   NKBS_CHECK_LAUNCH("nkbs_mlp_bwd");
   return 0;
 }

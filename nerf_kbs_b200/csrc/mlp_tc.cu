@@ -569,6 +569,7 @@ __device__ __forceinline__ void rebalance_registers(bool issuer_wg) {
 
 template <int FMT, int NWG, int IN>
 __global__ void __launch_bounds__((NWG + 1) * kThreads, 1) mlp_tc_fwd_kernel(const TcArgs a) {
+  nkbs_pdl_sync();
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ Sh sh;
   constexpr int nwg = NWG;
@@ -728,6 +729,7 @@ __global__ void __launch_bounds__((NWG + 1) * kThreads, 1) mlp_tc_fwd_kernel(con
 
 template <int FMT, int NWG, int IN>
 __global__ void __launch_bounds__((NWG + 1) * kThreads, 1) mlp_tc_bwd_kernel(const TcArgs a) {
+  nkbs_pdl_sync();
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ Sh sh;
   constexpr int nwg = NWG;
@@ -1237,12 +1239,12 @@ int launch_one(const TcArgs& a, int64_t N, cudaStream_t st, const char* who) {
     static const int ok = check_register_pool(mlp_tc_bwd_kernel<FMT, NWG, IN>, NWG, who);
     if (ok) return -1;
     if (set_smem(mlp_tc_bwd_kernel<FMT, NWG, IN>, a.smem_bytes, who)) return -1;
-    mlp_tc_bwd_kernel<FMT, NWG, IN><<<grid, threads, a.smem_bytes, st>>>(a);
+    nkbs_launch(mlp_tc_bwd_kernel<FMT, NWG, IN>, grid, threads, a.smem_bytes, st, a);
   } else {
     static const int ok = check_register_pool(mlp_tc_fwd_kernel<FMT, NWG, IN>, NWG, who);
     if (ok) return -1;
     if (set_smem(mlp_tc_fwd_kernel<FMT, NWG, IN>, a.smem_bytes, who)) return -1;
-    mlp_tc_fwd_kernel<FMT, NWG, IN><<<grid, threads, a.smem_bytes, st>>>(a);
+    nkbs_launch(mlp_tc_fwd_kernel<FMT, NWG, IN>, grid, threads, a.smem_bytes, st, a);
   }
   return 0;
 }

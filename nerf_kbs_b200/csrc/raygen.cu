@@ -43,6 +43,7 @@ __device__ __forceinline__ float norm3(float3 v) {
 }
 
 __global__ void __launch_bounds__(kThreads) generate_rays_kernel(const RayGenArgs a) {
+  nkbs_pdl_sync();
   for (int64_t n = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; n < a.N; n += (int64_t)gridDim.x * blockDim.x) {
     int64_t cam = a.idx[3 * n];
     cam = cam < 0 ? 0 : (cam >= a.num_cameras ? a.num_cameras - 1 : cam);
@@ -80,6 +81,7 @@ __global__ void __launch_bounds__(kThreads) generate_rays_kernel(const RayGenArg
 __global__ void __launch_bounds__(1024) compact_masked_kernel(int64_t M, const int64_t* img, const int64_t* pix,
                                                               const uint8_t* mask, int64_t pixels_per_image, int64_t R,
                                                               int64_t* out_img, int64_t* out_pix, int32_t* n_kept) {
+  nkbs_pdl_sync();
   __shared__ int s_warp[32];
   __shared__ int s_base, s_total;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -159,6 +161,7 @@ __device__ __forceinline__ int block_exclusive_scan_1024(int v, int* s_warp, int
 
 __global__ void __launch_bounds__(kCompactCta) compact_count_kernel(int64_t M, const int64_t* img, const int64_t* pix,
                                                                     const uint8_t* mask, int64_t ppi, int32_t* counts) {
+  nkbs_pdl_sync();
   __shared__ int s_warp[33];
   const int64_t m = blockIdx.x * (int64_t)kCompactCta + threadIdx.x;
   const int keep = (m < M && mask[img[m] * ppi + pix[m]] != 0) ? 1 : 0;
@@ -169,6 +172,7 @@ __global__ void __launch_bounds__(kCompactCta) compact_count_kernel(int64_t M, c
 
 // exclusive scan of counts[0..nb) in place, counts[nb] = *n_kept = total
 __global__ void __launch_bounds__(kCompactCta) compact_scan_kernel(int nb, int32_t* counts, int32_t* n_kept) {
+  nkbs_pdl_sync();
   __shared__ int s_warp[33];
   int carry = 0;
   for (int b0 = 0; b0 < nb; b0 += kCompactCta) {
@@ -189,6 +193,7 @@ __global__ void __launch_bounds__(kCompactCta) compact_scatter_kernel(int64_t M,
                                                                       const uint8_t* mask, int64_t ppi, int64_t R,
                                                                       const int32_t* offsets, int64_t* out_img,
                                                                       int64_t* out_pix) {
+  nkbs_pdl_sync();
   __shared__ int s_warp[33];
   const int64_t m = blockIdx.x * (int64_t)kCompactCta + threadIdx.x;
   int64_t im = 0, px = 0;
@@ -208,6 +213,7 @@ __global__ void __launch_bounds__(kCompactCta) compact_scatter_kernel(int64_t M,
 
 __global__ void __launch_bounds__(kThreads) compact_fill_kernel(int64_t R, const int32_t* n_kept, int64_t* out_img,
                                                                 int64_t* out_pix) {
+  nkbs_pdl_sync();
   const int64_t kept = *n_kept;
   if (kept <= 0 || kept >= R) return;
   for (int64_t k = kept + blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < R; k += (int64_t)gridDim.x * blockDim.x) {
@@ -224,6 +230,7 @@ struct Palette {
 
 __global__ void __launch_bounds__(kThreads) color_to_label_kernel(int64_t N, const uint8_t* rgb, const Palette* pal,
                                                                   int64_t default_label, int64_t* labels) {
+  nkbs_pdl_sync();
   __shared__ uint32_t s_key[kMaxPalette];
   const int n = pal->n;
   for (int i = threadIdx.x; i < n; i += blockDim.x) s_key[i] = pal->key[i];
@@ -242,6 +249,7 @@ __global__ void __launch_bounds__(kThreads) color_to_label_kernel(int64_t N, con
 
 __global__ void __launch_bounds__(kThreads) semantic_colormap_kernel(int64_t N, int C, const float* logits,
                                                                      const Palette* pal, int64_t* labels, uint8_t* rgb) {
+  nkbs_pdl_sync();
   for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < N; p += (int64_t)gridDim.x * blockDim.x) {
     const float* x = logits + p * C;
     int best = 0;
@@ -271,11 +279,13 @@ __device__ __forceinline__ int cm_float_key(float f) {
 __device__ __forceinline__ float cm_key_float(int k) { return __int_as_float(k >= 0 ? k : k ^ 0x7fffffff); }
 
 __global__ void cm_minmax_init_kernel(int* mm) {
+  nkbs_pdl_sync();
   mm[0] = cm_float_key(FLT_MAX);
   mm[1] = cm_float_key(-FLT_MAX);
 }
 
 __global__ void __launch_bounds__(kThreads) cm_minmax_kernel(int64_t N, const float* x, int* mm) {
+  nkbs_pdl_sync();
   float lo = FLT_MAX, hi = -FLT_MAX;
   for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < N; p += (int64_t)gridDim.x * blockDim.x) {
     const float v = x[p];
@@ -301,6 +311,7 @@ __global__ void __launch_bounds__(kThreads) cm_minmax_kernel(int64_t N, const fl
 __global__ void __launch_bounds__(kThreads) colormap_kernel(int64_t N, const float* x, const float* acc, const float* lut,
                                                             int depth_mode, const int* mm, float near_in, float far_in,
                                                             int have_near, int have_far, float* out) {
+  nkbs_pdl_sync();
   float near = 0.f, den = 1.f;
   if (depth_mode) {
     near = have_near ? near_in : cm_key_float(mm[0]);
@@ -346,7 +357,7 @@ extern "C" int nkbs_generate_rays(int64_t N, const int64_t* ray_indices, const f
   if (N == 0) return 0;
   NKBS_CHECK_ARG(ray_indices && c2w && intrinsics && origins && directions, "nkbs_generate_rays: null pointers");
   RayGenArgs a{N, ray_indices, c2w, intrinsics, num_cameras, origins, directions, directions_norm, pixel_area, camera_indices};
-  generate_rays_kernel<<<grid_for(N), kThreads, 0, (cudaStream_t)stream>>>(a);
+  nkbs_launch(generate_rays_kernel, grid_for(N), kThreads, 0, (cudaStream_t)stream, a);
   NKBS_CHECK_LAUNCH("nkbs_generate_rays");
   return 0;
 }
@@ -359,7 +370,7 @@ extern "C" int nkbs_compact_masked(int64_t M, const int64_t* image_indices, cons
   cudaStream_t st = (cudaStream_t)stream;
   if (!block_ws) {  // one CTA walks the list: per-step candidate lists of a few thousand entries
     NKBS_CHECK_ARG(M <= (1ll << 22), "nkbs_compact_masked: %lld candidates need the block workspace", (long long)M);
-    compact_masked_kernel<<<1, 1024, 0, st>>>(M, image_indices, pixel_indices, masks, pixels_per_image, R, out_image,
+    nkbs_launch(compact_masked_kernel, 1, 1024, 0, st, M, image_indices, pixel_indices, masks, pixels_per_image, R, out_image,
                                               out_pixel, n_kept);
     NKBS_CHECK_LAUNCH("nkbs_compact_masked");
     return 0;
@@ -367,18 +378,18 @@ extern "C" int nkbs_compact_masked(int64_t M, const int64_t* image_indices, cons
   const int64_t nb = (M + kCompactCta - 1) / kCompactCta;
   NKBS_CHECK_ARG(nb < (1ll << 30), "nkbs_compact_masked: too many candidates");
   if (nb > 0) {
-    compact_count_kernel<<<(int)nb, kCompactCta, 0, st>>>(M, image_indices, pixel_indices, masks, pixels_per_image, block_ws);
+    nkbs_launch(compact_count_kernel, (int)nb, kCompactCta, 0, st, M, image_indices, pixel_indices, masks, pixels_per_image, block_ws);
     NKBS_CHECK_LAUNCH("nkbs_compact_masked(count)");
   }
-  compact_scan_kernel<<<1, kCompactCta, 0, st>>>((int)nb, block_ws, n_kept);
+  nkbs_launch(compact_scan_kernel, 1, kCompactCta, 0, st, (int)nb, block_ws, n_kept);
   NKBS_CHECK_LAUNCH("nkbs_compact_masked(scan)");
   if (nb > 0) {
-    compact_scatter_kernel<<<(int)nb, kCompactCta, 0, st>>>(M, image_indices, pixel_indices, masks, pixels_per_image, R,
+    nkbs_launch(compact_scatter_kernel, (int)nb, kCompactCta, 0, st, M, image_indices, pixel_indices, masks, pixels_per_image, R,
                                                            block_ws, out_image, out_pixel);
     NKBS_CHECK_LAUNCH("nkbs_compact_masked(scatter)");
   }
   if (R > 0) {
-    compact_fill_kernel<<<grid_for(R), kThreads, 0, st>>>(R, n_kept, out_image, out_pixel);
+    nkbs_launch(compact_fill_kernel, grid_for(R), kThreads, 0, st, R, n_kept, out_image, out_pixel);
     NKBS_CHECK_LAUNCH("nkbs_compact_masked(fill)");
   }
   return 0;
@@ -389,7 +400,7 @@ extern "C" int nkbs_color_to_label(int64_t N, const uint8_t* rgb, const void* pa
   NKBS_CHECK_ARG(N >= 0, "nkbs_color_to_label: negative N");
   if (N == 0) return 0;
   NKBS_CHECK_ARG(rgb && palette && labels, "nkbs_color_to_label: null pointers");
-  color_to_label_kernel<<<grid_for(N), kThreads, 0, (cudaStream_t)stream>>>(N, rgb, (const Palette*)palette, default_label, labels);
+  nkbs_launch(color_to_label_kernel, grid_for(N), kThreads, 0, (cudaStream_t)stream, N, rgb, (const Palette*)palette, default_label, labels);
   NKBS_CHECK_LAUNCH("nkbs_color_to_label");
   return 0;
 }
@@ -399,7 +410,7 @@ extern "C" int nkbs_semantic_colormap(int64_t N, int32_t C, const float* logits,
   NKBS_CHECK_ARG(N >= 0 && C >= 1, "nkbs_semantic_colormap: bad sizes");
   if (N == 0) return 0;
   NKBS_CHECK_ARG(logits && (labels || rgb) && (!rgb || palette), "nkbs_semantic_colormap: null pointers");
-  semantic_colormap_kernel<<<grid_for(N), kThreads, 0, (cudaStream_t)stream>>>(N, C, logits, (const Palette*)palette, labels, rgb);
+  nkbs_launch(semantic_colormap_kernel, grid_for(N), kThreads, 0, (cudaStream_t)stream, N, C, logits, (const Palette*)palette, labels, rgb);
   NKBS_CHECK_LAUNCH("nkbs_semantic_colormap");
   return 0;
 }
@@ -408,7 +419,7 @@ extern "C" int nkbs_apply_colormap(int64_t N, const float* image, const float* l
   NKBS_CHECK_ARG(N >= 0, "nkbs_apply_colormap: negative N");
   if (N == 0) return 0;
   NKBS_CHECK_ARG(image && lut && rgb, "nkbs_apply_colormap: null pointers");
-  colormap_kernel<<<grid_for(N), kThreads, 0, (cudaStream_t)stream>>>(N, image, nullptr, lut, 0, nullptr, 0.f, 0.f, 0, 0, rgb);
+  nkbs_launch(colormap_kernel, grid_for(N), kThreads, 0, (cudaStream_t)stream, N, image, nullptr, lut, 0, nullptr, 0.f, 0.f, 0, 0, rgb);
   NKBS_CHECK_LAUNCH("nkbs_apply_colormap");
   return 0;
 }
@@ -422,11 +433,11 @@ extern "C" int nkbs_apply_depth_colormap(int64_t N, const float* depth, const fl
   NKBS_CHECK_ARG((have_near && have_far) || minmax_ws, "nkbs_apply_depth_colormap: the depth range needs a workspace");
   cudaStream_t st = (cudaStream_t)stream;
   if (!(have_near && have_far)) {
-    cm_minmax_init_kernel<<<1, 1, 0, st>>>(minmax_ws);
-    cm_minmax_kernel<<<grid_for(N), kThreads, 0, st>>>(N, depth, minmax_ws);
+    nkbs_launch(cm_minmax_init_kernel, 1, 1, 0, st, minmax_ws);
+    nkbs_launch(cm_minmax_kernel, grid_for(N), kThreads, 0, st, N, depth, minmax_ws);
     NKBS_CHECK_LAUNCH("nkbs_apply_depth_colormap(range)");
   }
-  colormap_kernel<<<grid_for(N), kThreads, 0, st>>>(N, depth, accumulation, lut, 1, minmax_ws, near_plane, far_plane,
+  nkbs_launch(colormap_kernel, grid_for(N), kThreads, 0, st, N, depth, accumulation, lut, 1, minmax_ws, near_plane, far_plane,
                                                     have_near, have_far, rgb);
   NKBS_CHECK_LAUNCH("nkbs_apply_depth_colormap");
   return 0;

@@ -34,6 +34,7 @@ struct InitArgs {
 // bin edge re-evaluated them, and a 64-bit division for its ray index, for each of the S + 1 edges), lanes stride over the
 // edges (coalesced stores).
 __global__ void __launch_bounds__(256) initial_sampler_kernel(const InitArgs a) {
+  nkbs_pdl_sync();
   const int nb = a.S + 1;
   const int lane = threadIdx.x & 31;
   const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
@@ -75,6 +76,7 @@ struct PdfArgs {
 // One thread per ray.  The query points u are increasing, so searchsorted(cdf, u, right) is a merge
 // walk: the cdf is produced on the fly in sample order and never stored.
 __global__ void __launch_bounds__(kThreads) pdf_sample_kernel(const PdfArgs a) {
+  nkbs_pdl_sync();
   const int S = a.S, nb = a.nb;
   const float anneal = a.anneal_dev ? *a.anneal_dev : a.anneal;
   const float fS = (float)S, fnb = (float)nb;
@@ -159,6 +161,7 @@ constexpr int kWarpPdfMaxS = 1024;
 constexpr int kPdfWarps = 8;
 
 __global__ void __launch_bounds__(kPdfWarps * 32) pdf_sample_warp_kernel(const PdfArgs a) {
+  nkbs_pdl_sync();
   extern __shared__ float s_pdf[];  // per warp: v[S] then cdf[S+1]
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int S = a.S, nb = a.nb;
@@ -186,7 +189,7 @@ extern "C" int nkbs_initial_sampler(int64_t R, int32_t S, const float* lin, cons
   InitArgs a{R, S, lin, t_rand, rand_per_bin, nears, fars, sbins, ebins};
   int64_t blocks = (R + 7) / 8;  // eight rays (warps) per CTA
   int64_t cap = (int64_t)nkbs_num_sms() * 16;
-  initial_sampler_kernel<<<(int)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>(a);
+  nkbs_launch(initial_sampler_kernel, (int)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream, a);
   NKBS_CHECK_LAUNCH("nkbs_initial_sampler");
   return 0;
 }
@@ -210,10 +213,10 @@ extern "C" int nkbs_pdf_sample(int64_t R, int32_t S, int32_t num_bins, const flo
       cudaFuncSetAttribute(pdf_sample_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       configured = smem;
     }
-    pdf_sample_warp_kernel<<<(int)(blocks < cap ? blocks : cap), kPdfWarps * 32, smem, (cudaStream_t)stream>>>(a);
+    nkbs_launch(pdf_sample_warp_kernel, (int)(blocks < cap ? blocks : cap), kPdfWarps * 32, smem, (cudaStream_t)stream, a);
   } else {
     int64_t blocks = (R + kThreads - 1) / kThreads;
-    pdf_sample_kernel<<<(int)blocks, kThreads, 0, (cudaStream_t)stream>>>(a);
+    nkbs_launch(pdf_sample_kernel, (int)blocks, kThreads, 0, (cudaStream_t)stream, a);
   }
   NKBS_CHECK_LAUNCH("nkbs_pdf_sample");
   return 0;
