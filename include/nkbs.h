@@ -84,6 +84,15 @@ int nkbs_density_fwd(int32_t mode, const float* x, const float* origins, const f
                      const float* aabb, const float* table, const float* scalings, int32_t L, int32_t log2_T,
                      const float* W1, const float* b1, const float* W2, const float* b2, int32_t H,
                      float* density, void* stream);
+/* nkbs_density_fwd that also leaves what a backward pass through the UNFUSED kernels needs: feat_out [N, 2L] hash-grid
+ * features (16-byte aligned), xn_out [N,3] normalised positions x selector, sel_out [N] selector.  The hidden-64 field
+ * trains this way: one fused forward launch, then nkbs_mlp_tc_bwd / nkbs_mlp_bwd (x = feat_out, out_act = density,
+ * selector = sel_out) and nkbs_encode_bwd (xn = xn_out) — its fused backward is register-bound. */
+int nkbs_density_fwd_save(int32_t mode, const float* x, const float* origins, const float* directions,
+                          const float* starts, const float* ends, int32_t bin_stride, int64_t R, int32_t S, int32_t contraction,
+                          const float* aabb, const float* table, const float* scalings, int32_t L, int32_t log2_T,
+                          const float* W1, const float* b1, const float* W2, const float* b2, int32_t H,
+                          float* density, float* feat_out, float* xn_out, float* sel_out, void* stream);
 int nkbs_density_bwd(int32_t mode, const float* x, const float* origins, const float* directions,
                      const float* starts, const float* ends, int32_t bin_stride, int64_t R, int32_t S, int32_t contraction,
                      const float* aabb, const float* table, const float* scalings, int32_t L, int32_t log2_T,

@@ -25,6 +25,8 @@ SIGNATURES = {
     "nkbs_mlp_tc_fwd": [_p, _i64, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p],
     "nkbs_mlp_tc_bwd": [_p, _p, _i64, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p],
     "nkbs_density_fwd": [_i32, _p, _p, _p, _p, _p, _i32, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _i32, _p, _p],
+    "nkbs_density_fwd_save": [_i32, _p, _p, _p, _p, _p, _i32, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _i32, _p, _p, _p,
+                              _p, _p],
     "nkbs_density_bwd": [_i32, _p, _p, _p, _p, _p, _i32, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _i32, _p, _i32,
                          _p, _p, _p, _p, _p, _p, _p],
     "nkbs_encode_bwd_rays": [_i64, _i32, _p, _p, _p, _p, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p],

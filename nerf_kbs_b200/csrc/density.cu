@@ -32,6 +32,9 @@ struct DensityArgs : SampleSource {
   const float* W2;  // [1, H]
   const float* b2;  // [1]
   float* density;   // [N]            (forward)
+  float* feat_out;  // forward, optional (nkbs_density_fwd_save): hash-grid features [N, 2L],
+  float* xn_out;    //   normalised positions x selector [N, 3]
+  float* sel_out;   //   and selector [N] of every sample, for a backward pass through nkbs_mlp_*_bwd + nkbs_encode_bwd
   const float* ddensity;  // [N]      (backward)
   float* dtable;    // [L*T, 2]
   float* dW1;
@@ -110,7 +113,7 @@ __device__ __forceinline__ float hidden_pre(const Smem<H, L>& s, const float (&f
   return z;
 }
 
-template <int H, int L>
+template <int H, int L, bool SAVE>
 __global__ void __launch_bounds__(kThreads) density_fwd_kernel(const DensityArgs a) {
   nkbs_pdl_sync();
   __shared__ float s_scale[NKBS_MAX_LEVELS];
@@ -123,6 +126,21 @@ __global__ void __launch_bounds__(kThreads) density_fwd_kernel(const DensityArgs
     float3 x = load_sample_position(a, n, sel);
     float f[2 * L];
     encode_sample<L>(a, s_scale, x, f);
+    if constexpr (SAVE) {
+      if constexpr (L % 2 == 0) {  // rows of 2L floats are 16-byte aligned
+        float4* fo = reinterpret_cast<float4*>(a.feat_out + n * (2 * L));
+#pragma unroll
+        for (int i = 0; i < L / 2; ++i) fo[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+      } else {
+        float2* fo = reinterpret_cast<float2*>(a.feat_out + n * (2 * L));
+#pragma unroll
+        for (int i = 0; i < L; ++i) fo[i] = make_float2(f[2 * i], f[2 * i + 1]);
+      }
+      a.xn_out[3 * n] = x.x;
+      a.xn_out[3 * n + 1] = x.y;
+      a.xn_out[3 * n + 2] = x.z;
+      a.sel_out[n] = sel;
+    }
     float out = s.b2;
 #pragma unroll
     for (int j = 0; j < H; ++j) out = fmaf(s.w2[j], fmaxf(hidden_pre<H, L>(s, f, j), 0.f), out);
@@ -739,26 +757,58 @@ __global__ void __launch_bounds__(32 * W) proposal_level_fwd_kernel(const LevelA
 
 }  // namespace
 
+static int density_fwd_launch(const char* who, int32_t mode, const float* x, const float* origins, const float* directions,
+                              const float* starts, const float* ends, int32_t bin_stride, int64_t R, int32_t S,
+                              int32_t contraction, const float* aabb, const float* table, const float* scalings, int32_t L,
+                              int32_t log2_T, const float* W1, const float* b1, const float* W2, const float* b2,
+                              int32_t H, float* density, float* feat_out, float* xn_out, float* sel_out, void* stream) {
+  DensityArgs a;
+  if (fill(a, who, mode, x, origins, directions, starts, ends, bin_stride, R, S, contraction, aabb, table, scalings,
+           L, log2_T, W1, b1, W2, b2, H))
+    return -1;
+  if (a.N == 0) return 0;
+  NKBS_CHECK_ARG(density, "%s: null output", who);
+  a.density = density;
+  a.feat_out = feat_out;
+  a.xn_out = xn_out;
+  a.sel_out = sel_out;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (feat_out) {
+    NKBS_CHECK_ARG(xn_out && sel_out, "%s: feat_out, xn_out and sel_out come together", who);
+    NKBS_CHECK_ARG((reinterpret_cast<uintptr_t>(feat_out) & 15u) == 0, "%s: feat_out must be 16-byte aligned", who);
+    if (H == 16)
+      nkbs_launch(density_fwd_kernel<16, 5, true>, grid_for(density_fwd_kernel<16, 5, true>, a.N), kThreads, 0, st, a);
+    else
+      nkbs_launch(density_fwd_kernel<64, 8, true>, grid_for(density_fwd_kernel<64, 8, true>, a.N), kThreads, 0, st, a);
+  } else {
+    if (H == 16)
+      nkbs_launch(density_fwd_kernel<16, 5, false>, grid_for(density_fwd_kernel<16, 5, false>, a.N), kThreads, 0, st, a);
+    else
+      nkbs_launch(density_fwd_kernel<64, 8, false>, grid_for(density_fwd_kernel<64, 8, false>, a.N), kThreads, 0, st, a);
+  }
+  NKBS_CHECK_LAUNCH(who);
+  return 0;
+}
+
 extern "C" int nkbs_density_fwd(int32_t mode, const float* x, const float* origins, const float* directions,
                                 const float* starts, const float* ends, int32_t bin_stride, int64_t R, int32_t S,
                                 int32_t contraction,
                                 const float* aabb, const float* table, const float* scalings, int32_t L,
                                 int32_t log2_T, const float* W1, const float* b1, const float* W2, const float* b2,
                                 int32_t H, float* density, void* stream) {
-  DensityArgs a;
-  if (fill(a, "nkbs_density_fwd", mode, x, origins, directions, starts, ends, bin_stride, R, S, contraction, aabb, table, scalings,
-           L, log2_T, W1, b1, W2, b2, H))
-    return -1;
-  if (a.N == 0) return 0;
-  NKBS_CHECK_ARG(density, "nkbs_density_fwd: null output");
-  a.density = density;
-  cudaStream_t st = (cudaStream_t)stream;
-  if (H == 16)
-    nkbs_launch(density_fwd_kernel<16, 5>, grid_for(density_fwd_kernel<16, 5>, a.N), kThreads, 0, st, a);
-  else
-    nkbs_launch(density_fwd_kernel<64, 8>, grid_for(density_fwd_kernel<64, 8>, a.N), kThreads, 0, st, a);
-  NKBS_CHECK_LAUNCH("nkbs_density_fwd");
-  return 0;
+  return density_fwd_launch("nkbs_density_fwd", mode, x, origins, directions, starts, ends, bin_stride, R, S, contraction, aabb,
+                            table, scalings, L, log2_T, W1, b1, W2, b2, H, density, nullptr, nullptr, nullptr, stream);
+}
+
+extern "C" int nkbs_density_fwd_save(int32_t mode, const float* x, const float* origins, const float* directions,
+                                     const float* starts, const float* ends, int32_t bin_stride, int64_t R, int32_t S,
+                                     int32_t contraction, const float* aabb, const float* table, const float* scalings,
+                                     int32_t L, int32_t log2_T, const float* W1, const float* b1, const float* W2,
+                                     const float* b2, int32_t H, float* density, float* feat_out, float* xn_out,
+                                     float* sel_out, void* stream) {
+  NKBS_CHECK_ARG(feat_out && xn_out && sel_out, "nkbs_density_fwd_save: null outputs");
+  return density_fwd_launch("nkbs_density_fwd_save", mode, x, origins, directions, starts, ends, bin_stride, R, S, contraction,
+                            aabb, table, scalings, L, log2_T, W1, b1, W2, b2, H, density, feat_out, xn_out, sel_out, stream);
 }
 
 extern "C" int nkbs_density_bwd(int32_t mode, const float* x, const float* origins, const float* directions,

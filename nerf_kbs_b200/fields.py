@@ -209,7 +209,8 @@ class HashMLPDensityField(_Field):
         if len(net.layers) != 2 or shape not in ops.FUSED_DENSITY_SHAPES:
             return False
         if torch.is_grad_enabled() and self.encoding.hash_table.requires_grad:
-            return shape in ops.FUSED_DENSITY_TRAIN_SHAPES  # see ops.FUSED_DENSITY_TRAIN_SHAPES
+            # other shapes: fused forward + backward through the MLP / encode kernels (ops.HYBRID_DENSITY)
+            return shape in ops.FUSED_DENSITY_TRAIN_SHAPES or ops.HYBRID_DENSITY
         return True
 
     def get_density(self, ray_samples: RaySamples) -> Tuple[torch.Tensor, None]:

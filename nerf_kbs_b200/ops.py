@@ -210,6 +210,11 @@ FUSED_DENSITY_SHAPES = ((5, 16), (8, 64))  # (levels, hidden width) instantiated
 # backward 0.37 + 1.47 ms, encode + tensor-core MLP route 0.52 + 0.65 ms (scripts/density_bench.py,
 # profiles/r02_density_h64.txt).  Without gradients (evaluation, gated steps) every shape uses the fused forward.
 FUSED_DENSITY_TRAIN_SHAPES = ((5, 16),) if __import__("os").environ.get("NKBS_FUSED_DENSITY_H64_BWD", "0") != "1" else FUSED_DENSITY_SHAPES
+# The other shapes still take the fused FORWARD when they train (nkbs_density_fwd_save: the kernel also leaves the
+# features, normalised positions and selectors) and run their backward through the MLP and encode kernels — measured at
+# 8192 x 256 samples of the hidden-64 field: forward 0.52 ms (encode + MLP) -> 0.37 ms + the extra stores.
+# NKBS_HYBRID_DENSITY=0: encode + MLP kernels in both directions.
+HYBRID_DENSITY = __import__("os").environ.get("NKBS_HYBRID_DENSITY", "1") != "0"
 _FUSED_DENSITY = {"enabled": True}
 
 
@@ -265,9 +270,20 @@ class _FusedDensity(torch.autograd.Function):
         density = torch.empty((R * S,), device=dev, dtype=torch.float32)
         aabb = host_floats(norm.aabb)
         p_st, p_en, bstride, _keep = rows(starts, ends)
-        call("nkbs_density_fwd", mode, ptr(x), ptr(origins), ptr(directions), p_st, p_en, bstride, R, S,
-             int(norm.contraction), aabb, ptr(table), host_floats(grid.scalings), grid.L, grid.log2_T, ptr(W1), ptr(b1),
-             ptr(W2), ptr(b2), H, ptr(density), stream())
+        head = (mode, ptr(x), ptr(origins), ptr(directions), p_st, p_en, bstride, R, S, int(norm.contraction), aabb,
+                ptr(table), host_floats(grid.scalings), grid.L, grid.log2_T, ptr(W1), ptr(b1), ptr(W2), ptr(b2), H, ptr(density))
+        ctx.hybrid = (grid.L, H) not in FUSED_DENSITY_TRAIN_SHAPES and any(ctx.needs_input_grad[:5])
+        if ctx.hybrid:
+            # fused forward, backward through the MLP and encode kernels (see HYBRID_DENSITY)
+            N = R * S
+            feat = torch.empty((N, grid.out_dim), device=dev, dtype=torch.float32)
+            xn = torch.empty((N, 3), device=dev, dtype=torch.float32)
+            sel = torch.empty((N,), device=dev, dtype=torch.float32)
+            call("nkbs_density_fwd_save", *head, ptr(feat), ptr(xn), ptr(sel), stream())
+            ctx.cfg = (grid, dedup_levels, _MLP_CFG["precision"] == "tc", _MLP_CFG["bwd_fmt"])
+            ctx.save_for_backward(table, W1, b1, W2, b2, feat, xn, sel)
+            return density
+        call("nkbs_density_fwd", *head, stream())
         # proposal rays carry 96-256 samples: neighbouring samples share cells on every level of these grids
         ctx.cfg = (mode, R, S, H, grid, norm, dedup_levels if dedup_levels >= 0 else grid.L)
         ctx.save_for_backward(table, W1, b1, W2, b2, x, origins, directions, starts, ends)
@@ -275,6 +291,24 @@ class _FusedDensity(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, ddensity):
+        if ctx.hybrid:
+            grid, dedup, tc, bwd_fmt = ctx.cfg
+            table, W1, b1, W2, b2, feat, xn, sel = ctx.saved_tensors
+            ddensity = _c(ddensity).reshape(-1, 1)
+            N = feat.shape[0]
+            (dtable, dW1, db1, dW2, db2), ret = _grad_buffers(ctx.sinks, [table, W1, b1, W2, b2])
+            dfeat = torch.empty_like(feat)
+            dims, Ws, bs, dWs, dbs = [grid.out_dim, W1.shape[0], 1], [W1, W2], [b1, b2], [dW1, dW2], [db1, db2]
+            if tc:
+                call("nkbs_mlp_tc_bwd", ptr(feat), ptr(ddensity), N, 2, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), 1,
+                     ACT_DENSITY, bwd_fmt, ptr(sel), None, ptr(dfeat), host_ptrs(dWs), host_ptrs(dbs), stream())
+            else:
+                call("nkbs_mlp_bwd", ptr(feat), ptr(ddensity), N, 2, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), 1,
+                     ACT_DENSITY, ptr(sel), None, ptr(dfeat), host_ptrs(dWs), host_ptrs(dbs), stream())
+            call("nkbs_encode_bwd", ptr(xn), ptr(dfeat), N, host_floats(grid.scalings), grid.L, grid.log2_T,
+                 grid.features_per_level, dedup, ptr(dtable), stream())
+            _finish_temps()
+            return (*ret,) + (None,) * 9
         mode, R, S, H, grid, norm, dedup = ctx.cfg
         table, W1, b1, W2, b2, x, origins, directions, starts, ends = ctx.saved_tensors
         ddensity = _c(ddensity)

@@ -111,25 +111,41 @@ def test_fused_density_rejects_other_shapes():
 
 
 def test_training_route_of_the_hidden64_field():
-    """The semantic-NeRF-W default proposal field trains through encode + MLP kernels (faster backward, see
-    ops.FUSED_DENSITY_TRAIN_SHAPES) and evaluates through the fused forward; both give the same density."""
+    """The semantic-NeRF-W default proposal field trains through the fused forward (nkbs_density_fwd_save: features,
+    normalised positions and selectors are left for the backward) and the MLP + encode backward kernels (see
+    ops.HYBRID_DENSITY); density and every gradient agree with the encode + MLP route in both directions (ray-sample inputs: test_fused_density_matches_oracle[snw_default])."""
+    from nerf_kbs_b200 import _lib
     _, n = _pair("snw_default", seed=5)
-    _, n16 = _pair("nerfacto_prop0", seed=5)
-    assert not n._fused_ok() and n16._fused_ok()
-    with torch.no_grad():
-        assert n._fused_ok()
+    assert n._fused_ok()
     g = torch.Generator().manual_seed(6)
     pos = ((torch.rand(3000, 3, generator=g) - 0.5) * 4.0).to(DEV)
+    dy = torch.rand(3000, 1, generator=g).to(DEV)
     prev = ops.get_mlp_precision()
+    res = {}
     try:
-        ops.set_mlp_precision("fp32")
-        d_train = n.density_fn(pos)
-        assert d_train.requires_grad
+        for precision, tol in (("fp32", 1e-4), ("tc", 3e-2)):
+            ops.set_mlp_precision(precision)
+            for hybrid in (True, False):
+                ops.HYBRID_DENSITY = hybrid
+                assert n._fused_ok() == hybrid
+                for p in n.parameters():
+                    p.grad = None
+                c0 = dict(_lib.call_counts)
+                d = n.density_fn(pos)
+                d.backward(dy)
+                used = {k for k, v in _lib.call_counts.items() if v != c0.get(k, 0)}
+                assert ("nkbs_density_fwd_save" in used) == hybrid and ("nkbs_encode_fwd" in used) == (not hybrid)
+                assert "nkbs_density_bwd" not in used and "nkbs_encode_bwd" in used
+                res[hybrid] = (d.detach().clone(), [p.grad.clone() for p in n.parameters()])
+            assert_close(res[True][0], res[False][0], 1e-5 if precision == "fp32" else 1e-2, "density")
+            for a, b in zip(res[True][1], res[False][1]):
+                assert_close(a, b, tol, f"grad ({precision})")
         with torch.no_grad():
             d_eval = n.density_fn(pos)
+        assert_close(res[True][0], d_eval, 1e-5 if precision == "fp32" else 1e-2, "training forward vs evaluation forward")
     finally:
+        ops.HYBRID_DENSITY = True
         ops.set_mlp_precision(prev)
-    assert_close(d_train, d_eval, 1e-5, "density, training route vs fused forward")
 
 
 @pytest.mark.parametrize("kind", ["nerfacto_prop0", "nerfacto_prop1"])
