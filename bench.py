@@ -41,7 +41,7 @@ L2_BYTES_PER_CYCLE = 6300  # whole-chip L2 (LTS) throughput cap, /opt/skills/gui
 # Kernels whose tables are cache-resident are reported against L2 throughput, not HBM: the proposal grids are 5-16 MiB
 # (L1/L2 hits, ncu: DRAM 2 %).  The main-grid gather and scatter (64 MiB table + 64 MiB gradient, evicted by the
 # 620 MB optimizer stream of every step) and everything ray-major stay HBM kernels.
-L2_BOUND = {"nkbs_density_fwd", "nkbs_density_bwd", "nkbs_proposal_level_fwd", "nkbs_encode_bwd_rays"}
+L2_BOUND = {"nkbs_density_fwd", "nkbs_density_fwd_save", "nkbs_density_bwd", "nkbs_proposal_level_fwd", "nkbs_encode_bwd_rays"}
 BOUND_NOTE = {"l2": "table traffic of this kernel is served by L1/L2 (tables of 5-64 MiB against a 126 MiB L2): achieved = "
                     "algorithmic gather/scatter bytes per second against the L2 throughput cap, not HBM",
               "hbm": "achieved = algorithmic bytes per second against the measured HBM copy bandwidth",
@@ -222,13 +222,15 @@ def kernel_work(name, a):
     if name == "nkbs_adam_step":
         # p, g, m, v read; p, m, v written; + g re-zeroed when the step driver asks for it
         return "hbm", (7 + (1 if a[13] else 0)) * 4 * sum(list(a[5])[:a[0]])
-    if name in ("nkbs_density_fwd", "nkbs_density_bwd"):
+    if name in ("nkbs_density_fwd", "nkbs_density_bwd", "nkbs_density_fwd_save"):
         # fused proposal field: bin edges in, 8 corner rows of F=2 floats per level gathered, density out;
         # bwd additionally reads d(density) and scatters the same 8*L rows once each
         N, L = a[7] * a[8], a[13]
         gathers = 8 * L * 2 * 4
         if name.endswith("fwd"):
             return "hbm", N * (8 + gathers + 4)
+        if name.endswith("fwd_save"):  # + features, normalised positions and selectors stored for the backward
+            return "hbm", N * (8 + gathers + 4 + 2 * L * 4 + 16)
         if a[22] is None:  # feature gradients written out, scattered by nkbs_encode_bwd_rays
             return "hbm", N * (8 + 4 + gathers + 2 * L * 4)
         return "hbm", N * (8 + 4 + 2 * gathers)
@@ -659,11 +661,21 @@ def cfg3_leg(args, dev, rank, world, steps, warmup):
     ms_e2e = timed_steps(step_host, steps, dev, world)
     final_loss = float(tr.loss_dict["loss"])
     kept = int(kept_min.item())
+    kernels = None
+    if world == 1 and not args.no_kernel_pass:
+        # per-kernel rooflines of this configuration (hidden-64 proposal fields, semantic + transient heads)
+        img_i, pix_i, _ = D.compact_masked(cand_dev[0][0], cand_dev[0][1], masks, R)
+        rb = gen(torch.stack([img_i, pix_i // W, pix_i % W], dim=-1))
+        kb = {"origins": rb.origins, "directions": rb.directions, "pixel_area": rb.pixel_area,
+              "camera_indices": rb.camera_indices, "image": images[img_i, pix_i], "semantics_label": labels[img_i, pix_i]}
+        agg, _ = kernel_pass(tr, [kb], 3)
+        kernels = kernel_table(agg, 3, load_peaks()[0])
     tr.close()
     return {"metric": METRIC, "unit": UNIT,
             "workload": "semantic_nerfw training step (semantic + transient heads), 8192 motion-masked rays/GPU "
                         "(Bernoulli keep 0.8, candidates compacted and rays generated on the device inside the timed "
                         "region), 8-level 2^18 hidden-64 proposal fields (BASELINE configs[2])",
+            "kernels": kernels,
             "rays_per_gpu": R, "candidates_per_step": M, "min_kept_candidates": kept, "n_gpus": world, "steps": steps,
             "value": world * R * steps / (ms * 1e-3), "ms_per_step": ms / steps, "scaling": "weak",
             "collective": _collective(world), "gpu_launches": launches,
