@@ -26,23 +26,34 @@ def _batches(n, R, seed, dev):
     return out
 
 
-def run_dp_check(dev, rank: int, world: int, rays: int = 1024, steps: int = 8, graph: bool = True) -> Dict:
+def run_dp_check(dev, rank: int, world: int, rays: int = 1024, steps: int = 8, graph: bool = True,
+                 deterministic: bool = False) -> Dict:
     """Returns {"max_param_diff", "max_param", "rank_spread", "loss_fused", "loss_nccl", "ok"} (identical on every
     rank).  ``rank_spread`` = max |parameter difference| between rank 0 and any rank under the fused route: must be
     exactly 0 (every rank receives the owner's stores).  The two routes sum the ranks' gradients in different orders,
     and Adam (eps 1e-15) turns an entry whose gradient is rounding noise into a step of about lr in either direction,
-    so parameters are compared against ``steps * lr`` and the losses at 1e-4 relative."""
+    so parameters are compared against ``steps * lr`` and the losses at 1e-4 relative.
+
+    ``deterministic``: both routes run with fixed-point gradient accumulation (Trainer(deterministic=True)), the IEEE
+    Adam kernel on the NCCL route (the fused kernel's arithmetic) and peer loads instead of the in-switch reduction.
+    Every rank's local sums are then order-independent, and with two ranks the cross-rank sum is one commutative
+    addition on either route: the parameters must agree bit for bit (``max_param_diff`` == 0); with more ranks NCCL's
+    reduction order is its own and the loose bar applies."""
     from . import NerfactoModel, ModelConfig, RayBundle
     from .trainer import Trainer
     batches = _batches(4, rays, 100 + rank, dev)
-    prev = os.environ.get("NKBS_DP_FUSED")
+    keys = ("NKBS_DP_FUSED", "NKBS_ADAM_IEEE", "NKBS_DP_MULTIMEM")
+    prev = {k: os.environ.get(k) for k in keys}
+    if deterministic:
+        os.environ["NKBS_ADAM_IEEE"] = "1"
+        os.environ["NKBS_DP_MULTIMEM"] = "0"
 
     def run(fused: bool, use_graph: bool):
         os.environ["NKBS_DP_FUSED"] = "1" if fused else "0"
         torch.manual_seed(0)
         m = NerfactoModel(ModelConfig()).to(dev).train()
         torch.cuda.manual_seed(7 + rank)
-        tr = Trainer(m, rays, use_graph=use_graph, graph_warmup=2)
+        tr = Trainer(m, rays, use_graph=use_graph, graph_warmup=2, deterministic=deterministic)
         losses = []
         for i in range(steps):
             b = batches[i % len(batches)]
@@ -57,10 +68,11 @@ def run_dp_check(dev, rank: int, world: int, rays: int = 1024, steps: int = 8, g
         ref, l_nccl = run(False, False)
         got, l_fused = run(True, graph)
     finally:
-        if prev is None:
-            os.environ.pop("NKBS_DP_FUSED", None)
-        else:
-            os.environ["NKBS_DP_FUSED"] = prev
+        for k, v in prev.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
     other = got.clone()
     dist.broadcast(other, src=0)
     stats = torch.tensor([float((got - ref).abs().max()), float(ref.abs().max()), float((got - other).abs().max()),
@@ -71,6 +83,8 @@ def run_dp_check(dev, rank: int, world: int, rays: int = 1024, steps: int = 8, g
     d, scale, spread = float(mx[0]), float(mx[1]), float(mx[2])
     lf, ln = float(stats[3]), float(stats[4])
     ok = spread == 0.0 and abs(lf - ln) <= 1e-4 * abs(ln) and d <= 1.5 * steps * 1e-3
+    if deterministic and world == 2:
+        ok = ok and d == 0.0
     return {"max_param_diff": d, "max_param": scale, "rank_spread": spread, "loss_fused": lf, "loss_nccl": ln,
-            "rays_per_rank": rays, "steps": steps, "graph": bool(graph), "ok": bool(ok),
+            "rays_per_rank": rays, "steps": steps, "graph": bool(graph), "deterministic": bool(deterministic), "ok": bool(ok),
             "what": "fused NVLink reduce-scatter+Adam+all-gather vs NCCL allreduce + local Adam, same seeds"}

@@ -1,5 +1,5 @@
 """2+ GPU check (torchrun): the fused NVLink reduce-Adam-broadcast step equals NCCL allreduce + per-rank Adam
-(nerf_kbs_b200/dp_check.py).  Prints one JSON line per graph mode on rank 0."""
+(nerf_kbs_b200/dp_check.py).  Prints one JSON line per mode (eager, graph, graph + deterministic accumulation) on rank 0."""
 import json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch, torch.distributed as dist
@@ -8,8 +8,8 @@ torch.cuda.set_device(local)
 dev = torch.device("cuda", local)
 dist.init_process_group("nccl", device_id=dev)
 from nerf_kbs_b200.dp_check import run_dp_check
-for graph in (False, True):
-    r = run_dp_check(dev, rank, world, rays=1024, steps=int(os.environ.get("STEPS", "8")), graph=graph)
+for graph, det in ((False, False), (True, False), (True, True)):
+    r = run_dp_check(dev, rank, world, rays=1024, steps=int(os.environ.get("STEPS", "8")), graph=graph, deterministic=det)
     if rank == 0:
         print("DP_CHECK " + json.dumps(r), flush=True)
 dist.barrier(); torch.cuda.synchronize(); os._exit(0)

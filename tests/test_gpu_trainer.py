@@ -255,7 +255,9 @@ def test_fused_dp_step_equals_nccl_route():
     assert r.returncode == 0, r.stderr[-2000:]
     import json
     lines = [json.loads(l[len("DP_CHECK "):]) for l in r.stdout.splitlines() if l.startswith("DP_CHECK ")]
-    assert len(lines) == 2
+    assert len(lines) == 3
+    # deterministic accumulation on both routes, two ranks: bit-identical parameters
+    assert lines[2]["deterministic"] and lines[2]["max_param_diff"] == 0.0, lines[2]
     for d in lines:
         # ranks hold bit-identical parameters; the two routes reach the same loss.  Parameters are compared loosely:
         # Adam (eps 1e-15) moves an entry whose gradient is summation-order noise by about lr per step in either
