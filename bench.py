@@ -305,6 +305,9 @@ def kernel_pass(trainer, batches, steps):
     # main field's backward and an event pair around one launch would also time its neighbours
     sampler = trainer.model.proposal_sampler
     was_side, sampler.side_streams = sampler.side_streams, False
+    from nerf_kbs_b200 import ops as _ops
+    was_split = _ops._BWD_SPLIT["fraction"]
+    _ops.set_bwd_split(0.0)  # same reason: the split backward overlaps the scatter with the base MLP's backward
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     try:
         # one untimed eager step first: after graph replays the caching allocator has no free blocks for the eager
@@ -325,6 +328,7 @@ def kernel_pass(trainer, batches, steps):
         _lib.launch_observer = None
         trainer.use_graph = was
         sampler.side_streams = was_side
+        _ops.set_bwd_split(was_split)
     agg = {}
     for name, (kind, amount), s, e in rec:
         d = agg.setdefault(name, {"ms": 0.0, "launches": 0, "work": 0.0, "kind": kind})

@@ -295,7 +295,8 @@ class NerfactoField(_Field):
     def get_density(self, ray_samples: RaySamples):
         feats, sel = self._encode(ray_samples, self.mlp_base_grid, self._norm)
         W, b = self.mlp_base_mlp.weights_biases()
-        h, d0 = ops.mlp(feats, W, b, self.mlp_base_mlp.relu_mask, ops.ACT_DENSITY, selector=sel, col0=True)
+        # split_bwd: x is the hash grid's output — its backward overlaps the scatter with the MLP (ops._BWD_SPLIT)
+        h, d0 = ops.mlp(feats, W, b, self.mlp_base_mlp.relu_mask, ops.ACT_DENSITY, selector=sel, col0=True, split_bwd=True)
         h3 = h.reshape(*ray_samples.frustums.shape, -1)
         # torch.split(h3, [1, geo]) of the reference, without a split node in the backward pass (ops._Mlp, col0)
         density = d0.reshape(*ray_samples.frustums.shape, 1)

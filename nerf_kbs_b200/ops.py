@@ -129,6 +129,31 @@ def encode_raw(mode: int, grid: GridSpec, norm: Optional[NormSpec], table, x=Non
     return feats, sel, xn, idx
 
 
+# Split backward of the main field's base MLP + hash grid (opt-in: NKBS_BWD_SPLIT = a fraction in (0, 1)): the MLP's
+# backward runs as two launches over [0, k) and [k, N) samples, and the gradient scatter of the first part starts on a
+# side stream as soon as ITS feature gradients exist, beside the MLP backward of the second part — the tensor-core
+# kernel leaves most issue slots and all of L2's reduction bandwidth idle, the scatter is bound by exactly that
+# bandwidth.  _Mlp.backward leaves (event after part one, k) here under the feature gradient's address and
+# _HashEncode.backward picks it up; any other consumer of that gradient just sees a complete tensor on the stream.
+# MEASURED on the B200 (scripts/gpu_ab5.sh, same build back to back): 4096-ray step 0.753 ms without, 0.771-0.773 ms
+# with (fractions 0.375 / 0.5 / 0.625); 65 536 rays 7.65 / 7.66 ms; 8192-ray semantic step 2.754 / 2.759 ms.  The
+# proposal fields' backward on the sampler's side streams already fills what the tensor-core kernels leave idle, and
+# the two extra launches and half-size grids cost more than the overlap returns.  Hence OFF by default.
+_BWD_SPLIT = {"fraction": float(__import__("os").environ.get("NKBS_BWD_SPLIT", "0")), "min_rows": 1 << 16,
+              "pending": {}, "streams": {}}
+
+
+def set_bwd_split(fraction: float) -> None:
+    _BWD_SPLIT["fraction"] = float(fraction)
+
+
+def _split_stream(device) -> "torch.cuda.Stream":
+    st = _BWD_SPLIT["streams"].get(device)
+    if st is None:
+        st = _BWD_SPLIT["streams"][device] = torch.cuda.Stream(device, priority=-1)
+    return st
+
+
 class _HashEncode(torch.autograd.Function):
     """features = HashEncoding(normalise(positions)); gradient w.r.t. the table only (sample positions
     are detached in the reference path: PDF bins are detached)."""
@@ -173,7 +198,22 @@ class _HashEncode(torch.autograd.Function):
                  host_floats(norm.aabb), ptr(dfeat), host_floats(g.scalings), g.L, g.log2_T, ptr(dtable), stream())
             _finish_temps()
             return (ret,) + (None,) * 10
-        call("nkbs_encode_bwd", ptr(xn), ptr(dfeat), xn.shape[0], host_floats(g.scalings), g.L, g.log2_T,
+        split = _BWD_SPLIT["pending"].pop(dfeat.data_ptr(), None)
+        N = xn.shape[0]
+        if split is not None and split[1] < N and not _TEMPS:
+            ev, k = split
+            cur = torch.cuda.current_stream(xn.device)
+            side = _split_stream(xn.device)
+            side.wait_event(ev)  # part one of the MLP backward: dfeat[:k] is complete
+            W = dfeat.shape[1]
+            with torch.cuda.stream(side):
+                call("nkbs_encode_bwd", ptr(xn), ptr(dfeat), k, host_floats(g.scalings), g.L, g.log2_T,
+                     g.features_per_level, ctx.dedup, ptr(dtable), stream())
+            call("nkbs_encode_bwd", xn.data_ptr() + 12 * k, dfeat.data_ptr() + 4 * W * k, N - k, host_floats(g.scalings),
+                 g.L, g.log2_T, g.features_per_level, ctx.dedup, ptr(dtable), stream())
+            cur.wait_stream(side)
+            return (ret,) + (None,) * 10
+        call("nkbs_encode_bwd", ptr(xn), ptr(dfeat), N, host_floats(g.scalings), g.L, g.log2_T,
              g.features_per_level, ctx.dedup, ptr(dtable), stream())
         _finish_temps()
         return (ret,) + (None,) * 10
@@ -356,8 +396,9 @@ def get_mlp_precision() -> str:
 
 class _Mlp(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, selector, relu_mask, out_act, col0, sinks, *params):
-        ctx.sinks = sinks  # gradient sinks in the order W_0..W_{n-1}, b_0..b_{n-1}, or None
+    def forward(ctx, x, selector, relu_mask, out_act, col0, split, sinks, *params):
+        ctx.sinks = sinks
+        ctx.split = bool(split)  # see _BWD_SPLIT  # gradient sinks in the order W_0..W_{n-1}, b_0..b_{n-1}, or None
         nl = len(params) // 2
         Ws = [_c(p) for p in params[0::2]]
         bs = [_c(p) for p in params[1::2]]
@@ -392,7 +433,7 @@ class _Mlp(torch.autograd.Function):
         x, selector = saved[0], saved[1]
         Ws, bs = list(saved[2:2 + nl]), list(saved[2 + nl:2 + 2 * nl])
         if dy is None and dy0 is None:
-            return (None,) * (6 + 2 * nl)
+            return (None,) * (7 + 2 * nl)
         if dy is None:
             dy = torch.zeros((x.shape[0], dims[-1]), device=x.device, dtype=torch.float32)
         dy = _c(dy)
@@ -401,27 +442,42 @@ class _Mlp(torch.autograd.Function):
         dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
         zs, ret = _grad_buffers(ctx.sinks, Ws + bs)
         dWs, dbs = zs[:nl], zs[nl:]
-        if tc:
-            call("nkbs_mlp_tc_bwd", ptr(x), ptr(dy), N, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask,
-                 out_act, bwd_fmt, ptr(selector), ptr(dy0), ptr(dx), host_ptrs(dWs), host_ptrs(dbs), stream())
+        def launch(lo, n):
+            off = lambda t, width: None if t is None else t.data_ptr() + 4 * width * lo
+            if tc:
+                call("nkbs_mlp_tc_bwd", off(x, dims[0]), off(dy, dims[-1]), n, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs),
+                     relu_mask, out_act, bwd_fmt, off(selector, 1), off(dy0, 1), off(dx, dims[0]), host_ptrs(dWs),
+                     host_ptrs(dbs), stream())
+            else:
+                call("nkbs_mlp_bwd", off(x, dims[0]), off(dy, dims[-1]), n, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs),
+                     relu_mask, out_act, off(selector, 1), off(dy0, 1), off(dx, dims[0]), host_ptrs(dWs), host_ptrs(dbs), stream())
+
+        frac = _BWD_SPLIT["fraction"]
+        if ctx.split and dx is not None and 0.0 < frac < 1.0 and N >= _BWD_SPLIT["min_rows"] and not _TEMPS:
+            k = max(128, int(N * frac) // 128 * 128)  # whole 128-sample tiles in part one
+            launch(0, k)
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(x.device))
+            launch(k, N - k)
+            _BWD_SPLIT["pending"].clear()  # one producer / consumer pair at a time
+            _BWD_SPLIT["pending"][dx.data_ptr()] = (ev, k)
         else:
-            call("nkbs_mlp_bwd", ptr(x), ptr(dy), N, nl, host_i32(dims), host_ptrs(Ws), host_ptrs(bs), relu_mask,
-                 out_act, ptr(selector), ptr(dy0), ptr(dx), host_ptrs(dWs), host_ptrs(dbs), stream())
+            launch(0, N)
         _finish_temps()
         grads = []
         for w, b in zip(ret[:nl], ret[nl:]):
             grads += [w, b]
-        return (dx, None, None, None, None, None, *grads)
+        return (dx, None, None, None, None, None, None, *grads)
 
 
 def mlp(x, weights: Sequence[torch.Tensor], biases: Sequence[torch.Tensor], relu_mask: int, out_act: int = ACT_NONE,
-        selector: Optional[torch.Tensor] = None, col0: bool = False):
+        selector: Optional[torch.Tensor] = None, col0: bool = False, split_bwd: bool = False):
     """y = MLP(x) with up to three nn.Linear layers; x [N,K0] -> y [N,Kn].  ``col0=True`` returns (y, y[:, 0] as a
     contiguous [N] tensor) from one autograd node."""
     params = []
     for w, b in zip(weights, biases):
         params += [w, b]
-    return _Mlp.apply(x, selector, relu_mask, out_act, bool(col0), _sinks(list(weights) + list(biases)), *params)
+    return _Mlp.apply(x, selector, relu_mask, out_act, bool(col0), bool(split_bwd), _sinks(list(weights) + list(biases)), *params)
 
 
 # ----------------------------------------------------------------------------------------------

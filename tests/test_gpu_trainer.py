@@ -374,3 +374,37 @@ def test_state_dict_sees_the_deferred_update():
     assert not torch.equal(sd["field.mlp_head.layers.0.weight"], before)
     tr.close()
     assert "field.mlp_base_grid.hash_table" in nm.state_dict()
+
+
+def test_split_backward_of_base_mlp_and_hash_grid_equals_the_single_launches():
+    """ops._BWD_SPLIT: the base MLP's backward in two launches with the first part's gradient scatter on a side stream
+    (default) against one launch each (fraction 0).  Same sums, other partial-sum grouping in the MLP kernel: losses
+    agree to rounding, parameters at the Adam-noise bar of the neighbouring tests; the split route itself is
+    reproducible bit for bit in deterministic mode, eager against captured."""
+    from nerf_kbs_b200 import ops, _lib
+    R = 2048  # 98 304 samples: above the split threshold
+    rb = O.synthetic_ray_bundle(R, seed=3)
+    batch = {"image": torch.rand(R, 3, generator=torch.Generator().manual_seed(4)).to(DEV)}
+    prev = ops._BWD_SPLIT["fraction"]
+    runs = {}
+    try:
+        for key, frac, graph in (("single", 0.0, False), ("split", 0.5, False), ("split_graph", 0.5, True)):
+            ops.set_bwd_split(frac)
+            _, nm = _train_pair(R, 0, graph)
+            tr = Trainer(nm, R, use_graph=graph, graph_warmup=1, inject_jitter=True, deterministic=True)
+            c0 = _lib.call_counts.get("nkbs_encode_bwd", 0)
+            ls = [tr.train_step(to_nk_bundle(rb, DEV), batch, jitter=[j.to(DEV) for j in make_jitter(R, seed=50 + i)]).item()
+                  for i in range(4)]
+            calls = _lib.call_counts.get("nkbs_encode_bwd", 0) - c0
+            tr.flush()
+            runs[key] = (ls, {n: p.detach().clone() for n, p in nm.named_parameters()}, calls)
+            tr.close()
+    finally:
+        ops.set_bwd_split(prev)
+    assert runs["split"][2] == runs["single"][2] + 4, "the split route launches the main grid's scatter twice per step"
+    for n, p in runs["split"][1].items():
+        assert torch.equal(runs["split_graph"][1][n], p), (n, (runs["split_graph"][1][n] - p).abs().max().item())
+    for a, b in zip(runs["split"][0], runs["single"][0]):
+        assert abs(a - b) <= 2e-4 * abs(b), (runs["split"][0], runs["single"][0])
+    for n in ("field.mlp_base_grid.hash_table", "field.mlp_head.layers.0.weight"):
+        assert rel_err(runs["split"][1][n], runs["single"][1][n]) < 5e-2, n
