@@ -239,6 +239,9 @@ def kernel_work(name, a):
         # level's bin edges (both domains) and the next level's
         R, S, L, nb = a[0], a[1], a[15], a[25]
         return "hbm", R * (S * (8 * L * 2 * 4 + 8) + 8 * (S + 1) + 8 * nb)
+    if name == "nkbs_density_bwd_saved":  # features + selector + d(density) in, feature gradients out
+        N, L = a[0], a[1]
+        return "hbm", N * (2 * L * 4 + 8 + 2 * L * 4)
     if name == "nkbs_encode_bwd_rays":
         # feature gradients in, every corner row of every sample scattered once (upper bound before the in-register merge)
         N, L = a[0] * a[1], a[11]

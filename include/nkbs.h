@@ -87,12 +87,20 @@ int nkbs_density_fwd(int32_t mode, const float* x, const float* origins, const f
 /* nkbs_density_fwd that also leaves what a backward pass through the UNFUSED kernels needs: feat_out [N, 2L] hash-grid
  * features (16-byte aligned), xn_out [N,3] normalised positions x selector, sel_out [N] selector.  The hidden-64 field
  * trains this way: one fused forward launch, then nkbs_mlp_tc_bwd / nkbs_mlp_bwd (x = feat_out, out_act = density,
- * selector = sel_out) and nkbs_encode_bwd (xn = xn_out) — its fused backward is register-bound. */
+ * selector = sel_out) and nkbs_encode_bwd (xn = xn_out) — its fused backward is register-bound.
+ * xn_out may be NULL (the ray-major scatter recomputes the positions).
+ * nkbs_density_bwd_saved: backward of the (L=5, H=16) field from those saved features and selectors — no positions, no
+ * table gathers: reads feat_in [N,2L], sel_in [N], ddensity [N], accumulates dW1 / db1 / dW2 / db2 and writes the
+ * feature gradients dfeat_out [N,2L] (zero where the selector is zero); nkbs_encode_bwd_rays / nkbs_encode_bwd
+ * scatter them. */
 int nkbs_density_fwd_save(int32_t mode, const float* x, const float* origins, const float* directions,
                           const float* starts, const float* ends, int32_t bin_stride, int64_t R, int32_t S, int32_t contraction,
                           const float* aabb, const float* table, const float* scalings, int32_t L, int32_t log2_T,
                           const float* W1, const float* b1, const float* W2, const float* b2, int32_t H,
                           float* density, float* feat_out, float* xn_out, float* sel_out, void* stream);
+int nkbs_density_bwd_saved(int64_t N, int32_t L, int32_t H, const float* feat_in, const float* sel_in,
+                           const float* ddensity, const float* W1, const float* b1, const float* W2, const float* b2,
+                           float* dW1, float* db1, float* dW2, float* db2, float* dfeat_out, void* stream);
 int nkbs_density_bwd(int32_t mode, const float* x, const float* origins, const float* directions,
                      const float* starts, const float* ends, int32_t bin_stride, int64_t R, int32_t S, int32_t contraction,
                      const float* aabb, const float* table, const float* scalings, int32_t L, int32_t log2_T,

@@ -27,6 +27,7 @@ SIGNATURES = {
     "nkbs_density_fwd": [_i32, _p, _p, _p, _p, _p, _i32, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _i32, _p, _p],
     "nkbs_density_fwd_save": [_i32, _p, _p, _p, _p, _p, _i32, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _i32, _p, _p, _p,
                               _p, _p],
+    "nkbs_density_bwd_saved": [_i64, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
     "nkbs_density_bwd": [_i32, _p, _p, _p, _p, _p, _i32, _i64, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p, _p, _p, _i32, _p, _i32,
                          _p, _p, _p, _p, _p, _p, _p],
     "nkbs_encode_bwd_rays": [_i64, _i32, _p, _p, _p, _p, _i32, _i32, _p, _p, _p, _i32, _i32, _p, _p],

@@ -36,6 +36,8 @@ struct DensityArgs : SampleSource {
   float* xn_out;    //   normalised positions x selector [N, 3]
   float* sel_out;   //   and selector [N] of every sample, for a backward pass through nkbs_mlp_*_bwd + nkbs_encode_bwd
   const float* ddensity;  // [N]      (backward)
+  const float* feat_in;   // backward, optional (nkbs_density_bwd_saved): the forward's features [N, 2L] and
+  const float* sel_in;    //   selectors [N] — no positions, no gathers
   float* dtable;    // [L*T, 2]
   float* dW1;
   float* db1;
@@ -136,9 +138,11 @@ __global__ void __launch_bounds__(kThreads) density_fwd_kernel(const DensityArgs
 #pragma unroll
         for (int i = 0; i < L; ++i) fo[i] = make_float2(f[2 * i], f[2 * i + 1]);
       }
-      a.xn_out[3 * n] = x.x;
-      a.xn_out[3 * n + 1] = x.y;
-      a.xn_out[3 * n + 2] = x.z;
+      if (a.xn_out) {
+        a.xn_out[3 * n] = x.x;
+        a.xn_out[3 * n + 1] = x.y;
+        a.xn_out[3 * n + 2] = x.z;
+      }
       a.sel_out[n] = sel;
     }
     float out = s.b2;
@@ -241,7 +245,9 @@ __device__ __forceinline__ void load_a_transposed(const float* tile, int ks, int
 template <int H>
 constexpr int bwd_ctas() { return H <= 16 ? NKBS_DENSITY_BWD_CTAS : 1; }
 
-template <int H, int L, bool FX>
+// FEAT: features and selectors come from the forward pass (feat_in / sel_in) instead of being recomputed from the
+// sample positions; the feature gradients go to df_out.
+template <int H, int L, bool FX, bool FEAT = false>
 __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(const DensityArgs a) {
   nkbs_pdl_sync();
   constexpr int K = 2 * L, KP = Smem<H, L>::KP;
@@ -290,7 +296,8 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
     float3 x = make_float3(0.f, 0.f, 0.f);
     float g_up = 0.f;
     if (live) {
-      x = load_sample_position(a, n, sel);
+      if constexpr (FEAT) sel = a.sel_in[n];
+      else x = load_sample_position(a, n, sel);
       g_up = a.ddensity[n] * sel;
     }
     // a warp whose samples all lie outside the grid (or carry no gradient) has nothing to add
@@ -303,7 +310,17 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
       continue;
     }
     float f[K];
-    encode_sample<L>(a, s_scale, x, f);
+    if constexpr (FEAT) {
+      const float2* fi = reinterpret_cast<const float2*>(a.feat_in + n * K);
+#pragma unroll
+      for (int i = 0; i < L; ++i) {
+        const float2 v = live ? fi[i] : make_float2(0.f, 0.f);
+        f[2 * i] = v.x;
+        f[2 * i + 1] = v.y;
+      }
+    } else {
+      encode_sample<L>(a, s_scale, x, f);
+    }
     float z[kMma ? 1 : H];
     float out = s.b2;
     float df[K];
@@ -442,7 +459,7 @@ __global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(co
     __syncwarp();
     }
     // ---- feature gradient -> table gradient ----
-    if (a.df_out) {
+    if (FEAT || a.df_out) {
       if (live) {
         float2* o = reinterpret_cast<float2*>(a.df_out + n * K);
 #pragma unroll
@@ -566,6 +583,7 @@ int fill(DensityArgs& a, const char* who, int mode, const float* x, const float*
   a.b2 = b2;
   a.density = nullptr;
   a.ddensity = nullptr;
+  a.feat_in = a.sel_in = nullptr;
   a.dtable = a.dW1 = a.db1 = a.dW2 = a.db2 = nullptr;
   a.dedup_levels = 0;
   a.v4_min_scale = v4_min_scale(1e30f);
@@ -774,7 +792,7 @@ static int density_fwd_launch(const char* who, int32_t mode, const float* x, con
   a.sel_out = sel_out;
   cudaStream_t st = (cudaStream_t)stream;
   if (feat_out) {
-    NKBS_CHECK_ARG(xn_out && sel_out, "%s: feat_out, xn_out and sel_out come together", who);
+    NKBS_CHECK_ARG(sel_out, "%s: feat_out and sel_out come together", who);
     NKBS_CHECK_ARG((reinterpret_cast<uintptr_t>(feat_out) & 15u) == 0, "%s: feat_out must be 16-byte aligned", who);
     if (H == 16)
       nkbs_launch(density_fwd_kernel<16, 5, true>, grid_for(density_fwd_kernel<16, 5, true>, a.N), kThreads, 0, st, a);
@@ -806,7 +824,7 @@ extern "C" int nkbs_density_fwd_save(int32_t mode, const float* x, const float* 
                                      int32_t L, int32_t log2_T, const float* W1, const float* b1, const float* W2,
                                      const float* b2, int32_t H, float* density, float* feat_out, float* xn_out,
                                      float* sel_out, void* stream) {
-  NKBS_CHECK_ARG(feat_out && xn_out && sel_out, "nkbs_density_fwd_save: null outputs");
+  NKBS_CHECK_ARG(feat_out && sel_out, "nkbs_density_fwd_save: null outputs");
   return density_fwd_launch("nkbs_density_fwd_save", mode, x, origins, directions, starts, ends, bin_stride, R, S, contraction,
                             aabb, table, scalings, L, log2_T, W1, b1, W2, b2, H, density, feat_out, xn_out, sel_out, stream);
 }
@@ -852,6 +870,46 @@ extern "C" int nkbs_density_bwd(int32_t mode, const float* x, const float* origi
     else nkbs_launch(density_bwd_kernel<64, 8, false>, grid_for(density_bwd_kernel<64, 8, false>, a.N, smem), kThreads, smem, st, a);
   }
   NKBS_CHECK_LAUNCH("nkbs_density_bwd");
+  return 0;
+}
+
+extern "C" int nkbs_density_bwd_saved(int64_t N, int32_t L, int32_t H, const float* feat_in, const float* sel_in,
+                                      const float* ddensity, const float* W1, const float* b1, const float* W2,
+                                      const float* b2, float* dW1, float* db1, float* dW2, float* db2, float* dfeat_out,
+                                      void* stream) {
+  NKBS_CHECK_ARG(N >= 0, "nkbs_density_bwd_saved: negative N");
+  NKBS_CHECK_ARG(H == 16 && L == 5, "nkbs_density_bwd_saved: built for the (L=5, H=16) field; got L=%d H=%d", L, H);
+  if (N == 0) return 0;
+  NKBS_CHECK_ARG(feat_in && sel_in && ddensity && W1 && b1 && W2 && b2 && dW1 && db1 && dW2 && db2 && dfeat_out,
+                 "nkbs_density_bwd_saved: null pointers");
+  NKBS_CHECK_ARG(((reinterpret_cast<uintptr_t>(feat_in) | reinterpret_cast<uintptr_t>(dfeat_out)) & 7u) == 0,
+                 "nkbs_density_bwd_saved: feat_in / dfeat_out must be 8-byte aligned");
+  DensityArgs a = {};
+  a.mode = 1;
+  a.S = 1;
+  a.bstride = 1;
+  a.N = N;
+  a.lv.num_levels = L;
+  a.W1 = W1;
+  a.b1 = b1;
+  a.W2 = W2;
+  a.b2 = b2;
+  a.feat_in = feat_in;
+  a.sel_in = sel_in;
+  a.ddensity = ddensity;
+  a.dW1 = dW1;
+  a.db1 = db1;
+  a.dW2 = dW2;
+  a.db2 = db2;
+  a.df_out = dfeat_out;
+  a.fm = nkbs_fixed_map_for(dW1);
+  cudaStream_t st = (cudaStream_t)stream;
+  constexpr size_t smem = (size_t)kWarps * MmaGeom<16, 5>::kScratch * sizeof(float);
+  if (a.fm.shadow)
+    nkbs_launch(density_bwd_kernel<16, 5, true, true>, grid_for(density_bwd_kernel<16, 5, true, true>, N, smem), kThreads, smem, st, a);
+  else
+    nkbs_launch(density_bwd_kernel<16, 5, false, true>, grid_for(density_bwd_kernel<16, 5, false, true>, N, smem), kThreads, smem, st, a);
+  NKBS_CHECK_LAUNCH("nkbs_density_bwd_saved");
   return 0;
 }
 

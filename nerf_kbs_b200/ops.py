@@ -255,6 +255,10 @@ FUSED_DENSITY_TRAIN_SHAPES = ((5, 16),) if __import__("os").environ.get("NKBS_FU
 # 8192 x 256 samples of the hidden-64 field: forward 0.52 ms (encode + MLP) -> 0.37 ms + the extra stores.
 # NKBS_HYBRID_DENSITY=0: encode + MLP kernels in both directions.
 HYBRID_DENSITY = __import__("os").environ.get("NKBS_HYBRID_DENSITY", "1") != "0"
+# Shapes with a fused backward (the nerfacto proposal fields) on ray samples: the forward also stores features and
+# selectors (44 B/sample) and the backward reads them back (nkbs_density_bwd_saved) instead of recomputing positions
+# and the 8 L table gathers per sample; the ray-major scatter follows as before.  NKBS_SAVED_DENSITY_BWD=0: recompute.
+SAVED_DENSITY_BWD = __import__("os").environ.get("NKBS_SAVED_DENSITY_BWD", "1") != "0"
 _FUSED_DENSITY = {"enabled": True}
 
 
@@ -323,9 +327,17 @@ class _FusedDensity(torch.autograd.Function):
             ctx.cfg = (grid, dedup_levels, _MLP_CFG["precision"] == "tc", _MLP_CFG["bwd_fmt"])
             ctx.save_for_backward(table, W1, b1, W2, b2, feat, xn, sel)
             return density
+        ctx.saved_feat = (SAVED_DENSITY_BWD and any(ctx.needs_input_grad[:5]) and (grid.L, H) == (5, 16) and mode == 2
+                          and _RAY_SCATTER["enabled"] and S <= 256 and R > 0)
+        ctx.cfg = (mode, R, S, H, grid, norm, dedup_levels if dedup_levels >= 0 else grid.L)
+        if ctx.saved_feat:
+            feat = torch.empty((R * S, grid.out_dim), device=dev, dtype=torch.float32)
+            sel = torch.empty((R * S,), device=dev, dtype=torch.float32)
+            call("nkbs_density_fwd_save", *head, ptr(feat), None, ptr(sel), stream())
+            ctx.save_for_backward(table, W1, b1, W2, b2, feat, sel, origins, directions, starts, ends)
+            return density
         call("nkbs_density_fwd", *head, stream())
         # proposal rays carry 96-256 samples: neighbouring samples share cells on every level of these grids
-        ctx.cfg = (mode, R, S, H, grid, norm, dedup_levels if dedup_levels >= 0 else grid.L)
         ctx.save_for_backward(table, W1, b1, W2, b2, x, origins, directions, starts, ends)
         return density
 
@@ -350,6 +362,18 @@ class _FusedDensity(torch.autograd.Function):
             _finish_temps()
             return (*ret,) + (None,) * 9
         mode, R, S, H, grid, norm, dedup = ctx.cfg
+        if ctx.saved_feat:
+            table, W1, b1, W2, b2, feat, sel, origins, directions, starts, ends = ctx.saved_tensors
+            ddensity = _c(ddensity)
+            (dtable, dW1, db1, dW2, db2), ret = _grad_buffers(ctx.sinks, [table, W1, b1, W2, b2])
+            p_st, p_en, bstride, _keep = rows(starts, ends)
+            dfeat = torch.empty_like(feat)
+            call("nkbs_density_bwd_saved", R * S, grid.L, H, ptr(feat), ptr(sel), ptr(ddensity), ptr(W1), ptr(b1), ptr(W2),
+                 ptr(b2), ptr(dW1), ptr(db1), ptr(dW2), ptr(db2), ptr(dfeat), stream())
+            call("nkbs_encode_bwd_rays", R, S, ptr(origins), ptr(directions), p_st, p_en, bstride, int(norm.contraction),
+                 host_floats(norm.aabb), ptr(dfeat), host_floats(grid.scalings), grid.L, grid.log2_T, ptr(dtable), stream())
+            _finish_temps()
+            return (*ret,) + (None,) * 9
         table, W1, b1, W2, b2, x, origins, directions, starts, ends = ctx.saved_tensors
         ddensity = _c(ddensity)
         (dtable, dW1, db1, dW2, db2), ret = _grad_buffers(ctx.sinks, [table, W1, b1, W2, b2])

@@ -177,6 +177,42 @@ def test_ray_major_scatter_equals_sample_major_scatter(kind, R, S):
         assert_close(a, bb, 2e-5, "gradient, ray-major vs sample-major scatter")
 
 
+@pytest.mark.parametrize("kind", ["nerfacto_prop0", "nerfacto_prop1"])
+@pytest.mark.parametrize("R,S", [(200, 256), (333, 96), (7, 33)])
+def test_backward_from_saved_features_equals_recomputed_backward(kind, R, S):
+    """Default training route of the nerfacto proposal fields on ray samples: the forward stores features and selectors
+    (nkbs_density_fwd_save) and the backward reads them (nkbs_density_bwd_saved) — against the backward that recomputes
+    positions and gathers (NKBS_SAVED_DENSITY_BWD=0).  Same arithmetic on the same values: identical feature
+    gradients, hence identical densities and (up to the order of the float reductions) identical gradients."""
+    from nerf_kbs_b200 import _lib
+    _, n = _pair(kind, seed=11)
+    rb, rs_o = _samples(R, S)
+    fr = rs_o.frustums
+    W, b = n.mlp_base[1].weights_biases()
+    g = torch.Generator().manual_seed(12)
+    dy = (torch.rand(R * S, generator=g) * (torch.rand(R * S, generator=g) < 0.7)).to(DEV)  # some exact zeros
+    res = {}
+    prev = ops.SAVED_DENSITY_BWD
+    try:
+        for saved in (False, True):
+            ops.SAVED_DENSITY_BWD = saved
+            for p in n.parameters():
+                p.grad = None
+            c0 = dict(_lib.call_counts)
+            d = ops.fused_density(n.encoding.hash_table, n.encoding.grid, n._norm, W[0], b[0], W[1], b[1],
+                                  origins=rb.origins.to(DEV), directions=rb.directions.to(DEV),
+                                  starts=fr.starts[..., 0].to(DEV), ends=fr.ends[..., 0].to(DEV))
+            d.backward(dy)
+            used = {k for k, v in _lib.call_counts.items() if v != c0.get(k, 0)}
+            assert ("nkbs_density_bwd_saved" in used) == saved and ("nkbs_density_fwd_save" in used) == saved
+            res[saved] = (d.detach().clone(), [p.grad.clone() for p in n.parameters()])
+    finally:
+        ops.SAVED_DENSITY_BWD = prev
+    assert torch.equal(res[True][0], res[False][0])
+    for a, bb in zip(res[True][1], res[False][1]):
+        assert_close(a, bb, 2e-5, "gradient, saved features vs recomputed")
+
+
 @pytest.mark.parametrize("S", [96, 256, 64])
 def test_unfused_encode_backward_ray_major_scatter(S):
     """contract_encode on proposal-sized ray samples: the backward takes nkbs_encode_bwd_rays; same table gradient as
