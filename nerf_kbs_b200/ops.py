@@ -135,7 +135,7 @@ def encode_raw(mode: int, grid: GridSpec, norm: Optional[NormSpec], table, x=Non
 # kernel leaves most issue slots and all of L2's reduction bandwidth idle, the scatter is bound by exactly that
 # bandwidth.  _Mlp.backward leaves (event after part one, k) here under the feature gradient's address and
 # _HashEncode.backward picks it up; any other consumer of that gradient just sees a complete tensor on the stream.
-# MEASURED on the B200 (scripts/gpu_ab5.sh, same build back to back): 4096-ray step 0.753 ms without, 0.771-0.773 ms
+# MEASURED on the B200 (scripts/gpu_ab_split.sh, same build back to back): 4096-ray step 0.753 ms without, 0.771-0.773 ms
 # with (fractions 0.375 / 0.5 / 0.625); 65 536 rays 7.65 / 7.66 ms; 8192-ray semantic step 2.754 / 2.759 ms.  The
 # proposal fields' backward on the sampler's side streams already fills what the tensor-core kernels leave idle, and
 # the two extra launches and half-size grids cost more than the overlap returns.  Hence OFF by default.
