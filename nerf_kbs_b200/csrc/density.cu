@@ -247,8 +247,8 @@ constexpr int bwd_ctas() { return H <= 16 ? NKBS_DENSITY_BWD_CTAS : 1; }
 
 // FEAT: features and selectors come from the forward pass (feat_in / sel_in) instead of being recomputed from the
 // sample positions; the feature gradients go to df_out.
-template <int H, int L, bool FX, bool FEAT = false>
-__global__ void __launch_bounds__(kThreads, bwd_ctas<H>()) density_bwd_kernel(const DensityArgs a) {
+template <int H, int L, bool FX, bool FEAT = false, int MINB = 0>
+__global__ void __launch_bounds__(kThreads, MINB ? MINB : bwd_ctas<H>()) density_bwd_kernel(const DensityArgs a) {
   nkbs_pdl_sync();
   constexpr int K = 2 * L, KP = Smem<H, L>::KP;
   // gradient rows, in this order: for each hidden unit j: dW1[j][0..K), db1[j], dW2[j]; then db2
@@ -905,8 +905,16 @@ extern "C" int nkbs_density_bwd_saved(int64_t N, int32_t L, int32_t H, const flo
   a.fm = nkbs_fixed_map_for(dW1);
   cudaStream_t st = (cudaStream_t)stream;
   constexpr size_t smem = (size_t)kWarps * MmaGeom<16, 5>::kScratch * sizeof(float);
+  // resident CTAs per SM the kernel is compiled for (registers 128 / 80 / 64 at 2 / 3 / 4): without the gathers the
+  // kernel streams, and more warps in flight win slightly — 4096-ray step 0.7466 / 0.7463 / 0.7445 ms, 65 536 rays
+  // 7.538 / 7.535 / 7.482 ms.  NKBS_SAVED_BWD_CTAS = 2, 3 overrides.
+  static const int minb = [] { const char* e = getenv("NKBS_SAVED_BWD_CTAS"); return e ? atoi(e) : 4; }();
   if (a.fm.shadow)
     nkbs_launch(density_bwd_kernel<16, 5, true, true>, grid_for(density_bwd_kernel<16, 5, true, true>, N, smem), kThreads, smem, st, a);
+  else if (minb == 3)
+    nkbs_launch(density_bwd_kernel<16, 5, false, true, 3>, grid_for(density_bwd_kernel<16, 5, false, true, 3>, N, smem), kThreads, smem, st, a);
+  else if (minb == 4)
+    nkbs_launch(density_bwd_kernel<16, 5, false, true, 4>, grid_for(density_bwd_kernel<16, 5, false, true, 4>, N, smem), kThreads, smem, st, a);
   else
     nkbs_launch(density_bwd_kernel<16, 5, false, true>, grid_for(density_bwd_kernel<16, 5, false, true>, N, smem), kThreads, smem, st, a);
   NKBS_CHECK_LAUNCH("nkbs_density_bwd_saved");
