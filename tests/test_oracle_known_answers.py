@@ -298,6 +298,28 @@ def test_c_abi_refuses_bad_arguments_without_a_gpu():
     assert lib.nkbs_version() > 0
     err = lib.nkbs_last_error()
     assert err is None or isinstance(err, (bytes, str))
+    fake = 1 << 20  # never dereferenced: every call below is refused (or is host-only) before any launch
+    refused = [
+        ("nkbs_fixed_point_register", (fake, 16, fake, 61)),       # scale outside [16, 60]
+        ("nkbs_fixed_point_register", (None, 16, fake, 52)),       # null buffer
+        ("nkbs_fixed_point_flush", (fake + 4096, 16, None)),       # not inside a registered buffer
+        ("nkbs_density_bwd_saved", (128, 8, 64) + (fake,) * 12 + (None,)),   # only the (L=5, H=16) field
+        ("nkbs_expected_depth_noalloc", ((1 << 20) + 1, 48, fake, fake, fake, 0, fake, None)),  # beyond the scratch
+        ("nkbs_adam_step", (-1,) + (None,) * 4 + (None, 1e-3, 0.9, 0.999, 1e-15, 0.0, None, None, 1, None, None)),
+    ]
+    for name, args in refused:
+        with pytest.raises(RuntimeError) as e:
+            _lib.call(name, *args)
+        assert name.split("(")[0] in str(e.value), (name, str(e.value))
+    # the deterministic-mode registry is host state: register, look up through a refused flush, unregister
+    _lib.call("nkbs_fixed_point_register", fake, 1024, fake * 2, 56)
+    with pytest.raises(RuntimeError):  # odd element offset into the shadow
+        _lib.call("nkbs_fixed_point_flush", fake + 4, 8, None)
+    with pytest.raises(RuntimeError):  # range runs past the registered buffer
+        _lib.call("nkbs_fixed_point_flush", fake + 4 * 1000, 100, None)
+    _lib.call("nkbs_fixed_point_register", fake, 1024, None, 0)
+    with pytest.raises(RuntimeError):
+        _lib.call("nkbs_fixed_point_flush", fake, 8, None)
 
 
 def test_host_ray_containers_keep_the_reference_attributes():
